@@ -1,0 +1,122 @@
+"""ctypes mirror of include/hsq_b200.h (struct layouts + small packing helpers).
+
+Only layouts live here; no compute.  Both the product binding (`_lib.py`) and the test-only oracle
+binding (`oracle/oracle.py`) use these definitions so that the same Python objects can be handed to
+either side.
+"""
+import ctypes as C
+
+import numpy as np
+
+HSQ_OK = 0
+HSQ_ERR_INVALID_ARGUMENT = -1
+HSQ_ERR_CUDA = -2
+HSQ_ERR_NO_DEVICE = -3
+HSQ_ERR_BAD_CHARACTER = -4
+HSQ_ERR_UNSUPPORTED = -5
+HSQ_ERR_OUT_OF_RANGE = -6
+HSQ_ERR_OVERFLOW = -7
+HSQ_PRIMER_NOT_FOUND = -2147483647
+HSQ_ALIGN_PENALIZE_START = 1
+HSQ_ALIGN_PENALIZE_END = 2
+
+u8p = C.POINTER(C.c_uint8)
+i32p = C.POINTER(C.c_int32)
+i64p = C.POINTER(C.c_int64)
+
+
+class Scorer(C.Structure):
+    _fields_ = [("match", C.c_int32), ("mismatch", C.c_int32), ("gap_extend", C.c_int32), ("gap_start", C.c_int32)]
+
+
+class Seqs(C.Structure):
+    _fields_ = [("data", u8p), ("offsets", i64p), ("n", C.c_int64)]
+
+
+class ProbeTable(C.Structure):
+    _fields_ = [("n", C.c_int64), ("reverse_strand", u8p), ("ext_start", i32p), ("ext_stop", i32p), ("lig_start", i32p),
+                ("lig_stop", i32p), ("target_start", i32p), ("target_stop", i32p), ("ext", Seqs), ("lig", Seqs),
+                ("target", Seqs)]
+
+
+class PairBatch(C.Structure):
+    _fields_ = [("n", C.c_int64), ("probe_id", i32p), ("read_index", i32p), ("r1", Seqs), ("r2", Seqs), ("q1", u8p),
+                ("q2", u8p)]
+
+
+class ExtendOut(C.Structure):
+    _fields_ = [("cigar_cap", C.c_int32), ("md_cap", C.c_int32), ("ok", u8p), ("primer_end", i32p), ("score", i32p),
+                ("pos", i32p), ("read_start", i32p), ("read_stop", i32p), ("nm", i32p), ("tlen", i32p),
+                ("cigar_len", i32p), ("cigar", u8p), ("md_len", i32p), ("md", u8p), ("overflow", u8p), ("pair_ok", u8p),
+                ("cells", C.c_int64)]
+
+
+class AlignOut(C.Structure):
+    _fields_ = [("cols_cap", C.c_int32), ("md_cap", C.c_int32), ("score", i32p), ("n_cols", i32p), ("ref_aln", u8p),
+                ("qry_aln", u8p), ("ops", u8p), ("first_q", i32p), ("last_q", i32p), ("first_r", i32p), ("last_r", i32p),
+                ("matches", i32p), ("mismatches", i32p), ("non_terminal_gaps", i32p), ("edit_distance", i32p),
+                ("md_len", i32p), ("md", u8p), ("rmd_len", i32p), ("rmd", u8p), ("overflow", u8p), ("cells", C.c_int64)]
+
+
+class ProbeStats(C.Structure):
+    _fields_ = [("n_probes", C.c_int64), ("unique_pairs", i32p), ("duplicate_pairs", i32p), ("max_pairs_per_uid", i32p)]
+
+
+class Candidates(C.Structure):
+    _fields_ = [("n", C.c_int64), ("r1", Seqs), ("r2", Seqs), ("cand_offsets", i64p), ("cand_probe", i32p)]
+
+
+def ptr(a, typ):
+    """Pointer to a numpy array's buffer (None -> NULL)."""
+    if a is None:
+        return C.cast(None, typ)
+    return C.cast(a.ctypes.data, typ)
+
+
+class SeqBatch:
+    """Host-side ragged ASCII batch: `data` uint8[total], `offsets` int64[n+1]. Keeps arrays alive."""
+
+    def __init__(self, data, offsets):
+        self.data = np.ascontiguousarray(data, dtype=np.uint8)
+        self.offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        self.n = len(self.offsets) - 1
+
+    @classmethod
+    def from_strings(cls, strings):
+        bs = [s.encode("ascii") if isinstance(s, str) else bytes(s) for s in strings]
+        offsets = np.zeros(len(bs) + 1, dtype=np.int64)
+        if bs:
+            offsets[1:] = np.cumsum([len(b) for b in bs])
+        data = np.frombuffer(b"".join(bs), dtype=np.uint8).copy() if bs else np.zeros(0, dtype=np.uint8)
+        return cls(data, offsets)
+
+    @classmethod
+    def from_fixed(cls, arr2d):
+        """uint8[n, L] -> batch of n strings of length L (no copy when contiguous)."""
+        arr2d = np.ascontiguousarray(arr2d, dtype=np.uint8)
+        n, L = arr2d.shape
+        return cls(arr2d.reshape(-1), np.arange(n + 1, dtype=np.int64) * L)
+
+    def string(self, k):
+        return self.data[self.offsets[k]:self.offsets[k + 1]].tobytes().decode("ascii")
+
+    def strings(self):
+        return [self.string(k) for k in range(self.n)]
+
+    def lengths(self):
+        return np.diff(self.offsets)
+
+    def c(self):
+        if len(self.data) == 0:  # keep a valid pointer even for empty batches
+            self._pad = np.zeros(1, dtype=np.uint8)
+            return Seqs(ptr(self._pad, u8p), ptr(self.offsets, i64p), self.n)
+        return Seqs(ptr(self.data, u8p), ptr(self.offsets, i64p), self.n)
+
+
+def slot_strings(buf, lens, cap):
+    """Decode an [n][cap] slot array + lengths into python strings (truncated at cap)."""
+    out = []
+    for k in range(len(lens)):
+        ln = min(int(lens[k]), cap)
+        out.append(buf[k * cap:k * cap + ln].tobytes().decode("ascii"))
+    return out

@@ -1,0 +1,166 @@
+"""Host-side batch containers (numpy) for the C ABI of include/hsq_b200.h.
+
+They mirror the data the reference hands to its per-probe task
+(HSQ/process/PrimerReadExtensionAndPcrDuplicateIdentification.java:836-846): a parsed probe file
+(COMMON/utils/probeinfo/Probe.java:53-69) and raw read pairs with qualities and FASTQ ordinals.
+No compute happens here.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _abi as A
+
+
+class ProbeTableHost:
+    def __init__(self, reverse_strand, ext_start, ext_stop, lig_start, lig_stop, target_start, target_stop, ext, lig,
+                 target, probe_ids=None, chromosomes=None):
+        self.reverse_strand = np.ascontiguousarray(reverse_strand, dtype=np.uint8)
+        self.ext_start = np.ascontiguousarray(ext_start, dtype=np.int32)
+        self.ext_stop = np.ascontiguousarray(ext_stop, dtype=np.int32)
+        self.lig_start = np.ascontiguousarray(lig_start, dtype=np.int32)
+        self.lig_stop = np.ascontiguousarray(lig_stop, dtype=np.int32)
+        self.target_start = np.ascontiguousarray(target_start, dtype=np.int32)
+        self.target_stop = np.ascontiguousarray(target_stop, dtype=np.int32)
+        self.ext = ext if isinstance(ext, A.SeqBatch) else A.SeqBatch.from_strings(ext)
+        self.lig = lig if isinstance(lig, A.SeqBatch) else A.SeqBatch.from_strings(lig)
+        self.target = target if isinstance(target, A.SeqBatch) else A.SeqBatch.from_strings(target)
+        self.n = len(self.reverse_strand)
+        self.probe_ids = probe_ids
+        self.chromosomes = chromosomes
+
+    def c(self):
+        return A.ProbeTable(self.n, A.ptr(self.reverse_strand, A.u8p), A.ptr(self.ext_start, A.i32p),
+                            A.ptr(self.ext_stop, A.i32p), A.ptr(self.lig_start, A.i32p), A.ptr(self.lig_stop, A.i32p),
+                            A.ptr(self.target_start, A.i32p), A.ptr(self.target_stop, A.i32p), self.ext.c(),
+                            self.lig.c(), self.target.c())
+
+
+class PairBatchHost:
+    def __init__(self, probe_id, r1, r2, q1=None, q2=None, read_index=None):
+        self.probe_id = np.ascontiguousarray(probe_id, dtype=np.int32)
+        self.n = len(self.probe_id)
+        self.read_index = None if read_index is None else np.ascontiguousarray(read_index, dtype=np.int32)
+        self.r1 = r1 if isinstance(r1, A.SeqBatch) else A.SeqBatch.from_strings(r1)
+        self.r2 = r2 if isinstance(r2, A.SeqBatch) else A.SeqBatch.from_strings(r2)
+        self.q1 = None if q1 is None else (q1 if isinstance(q1, A.SeqBatch) else A.SeqBatch.from_strings(q1))
+        self.q2 = None if q2 is None else (q2 if isinstance(q2, A.SeqBatch) else A.SeqBatch.from_strings(q2))
+
+    def c(self):
+        return A.PairBatch(self.n, A.ptr(self.probe_id, A.i32p), A.ptr(self.read_index, A.i32p), self.r1.c(),
+                           self.r2.c(), A.ptr(None if self.q1 is None else self.q1.data, A.u8p),
+                           A.ptr(None if self.q2 is None else self.q2.data, A.u8p))
+
+    def subset(self, idx):
+        idx = np.asarray(idx)
+
+        def take(sb):
+            if sb is None:
+                return None
+            return A.SeqBatch.from_strings([sb.data[sb.offsets[k]:sb.offsets[k + 1]].tobytes() for k in idx])
+
+        return PairBatchHost(self.probe_id[idx], take(self.r1), take(self.r2), take(self.q1), take(self.q2),
+                             None if self.read_index is None else self.read_index[idx])
+
+
+class ExtendResult:
+    """Owns the output arrays of hsq_extend_batch for n pairs."""
+    FIELDS_I32 = ("primer_end", "score", "pos", "read_start", "read_stop", "nm", "tlen", "cigar_len", "md_len")
+
+    def __init__(self, n, cigar_cap=32, md_cap=48):
+        self.n, self.cigar_cap, self.md_cap = n, cigar_cap, md_cap
+        for f in self.FIELDS_I32:
+            setattr(self, f, np.zeros(2 * n, dtype=np.int32))
+        self.ok = np.zeros(2 * n, dtype=np.uint8)
+        self.overflow = np.zeros(2 * n, dtype=np.uint8)
+        self.pair_ok = np.zeros(n, dtype=np.uint8)
+        self.cigar = np.zeros(2 * n * cigar_cap, dtype=np.uint8)
+        self.md = np.zeros(2 * n * md_cap, dtype=np.uint8)
+        self.cells = 0
+        self._c = None
+
+    def c(self):
+        p = A.ptr
+        self._c = A.ExtendOut(self.cigar_cap, self.md_cap, p(self.ok, A.u8p), p(self.primer_end, A.i32p),
+                              p(self.score, A.i32p), p(self.pos, A.i32p), p(self.read_start, A.i32p),
+                              p(self.read_stop, A.i32p), p(self.nm, A.i32p), p(self.tlen, A.i32p),
+                              p(self.cigar_len, A.i32p), p(self.cigar, A.u8p), p(self.md_len, A.i32p), p(self.md, A.u8p),
+                              p(self.overflow, A.u8p), p(self.pair_ok, A.u8p), 0)
+        return self._c
+
+    def finish(self):
+        self.cells = int(self._c.cells)
+        return self
+
+    def cigars(self):
+        return A.slot_strings(self.cigar, self.cigar_len, self.cigar_cap)
+
+    def mds(self):
+        return A.slot_strings(self.md, self.md_len, self.md_cap)
+
+
+class AlignResult:
+    FIELDS_I32 = ("score", "n_cols", "first_q", "last_q", "first_r", "last_r", "matches", "mismatches",
+                  "non_terminal_gaps", "edit_distance", "md_len", "rmd_len")
+
+    def __init__(self, n, cols_cap=640, md_cap=640):
+        self.n, self.cols_cap, self.md_cap = n, cols_cap, md_cap
+        for f in self.FIELDS_I32:
+            setattr(self, f, np.zeros(n, dtype=np.int32))
+        self.ref_aln = np.zeros(n * cols_cap, dtype=np.uint8)
+        self.qry_aln = np.zeros(n * cols_cap, dtype=np.uint8)
+        self.ops = np.zeros(n * cols_cap, dtype=np.uint8)
+        self.md = np.zeros(n * md_cap, dtype=np.uint8)
+        self.rmd = np.zeros(n * md_cap, dtype=np.uint8)
+        self.overflow = np.zeros(n, dtype=np.uint8)
+        self.cells = 0
+        self._c = None
+
+    def c(self):
+        p = A.ptr
+        self._c = A.AlignOut(self.cols_cap, self.md_cap, p(self.score, A.i32p), p(self.n_cols, A.i32p),
+                             p(self.ref_aln, A.u8p), p(self.qry_aln, A.u8p), p(self.ops, A.u8p), p(self.first_q, A.i32p),
+                             p(self.last_q, A.i32p), p(self.first_r, A.i32p), p(self.last_r, A.i32p),
+                             p(self.matches, A.i32p), p(self.mismatches, A.i32p), p(self.non_terminal_gaps, A.i32p),
+                             p(self.edit_distance, A.i32p), p(self.md_len, A.i32p), p(self.md, A.u8p),
+                             p(self.rmd_len, A.i32p), p(self.rmd, A.u8p), p(self.overflow, A.u8p), 0)
+        return self._c
+
+    def finish(self):
+        self.cells = int(self._c.cells)
+        return self
+
+    def ref_alns(self):
+        return A.slot_strings(self.ref_aln, self.n_cols, self.cols_cap)
+
+    def qry_alns(self):
+        return A.slot_strings(self.qry_aln, self.n_cols, self.cols_cap)
+
+    def op_strings(self):
+        return A.slot_strings(self.ops, self.n_cols, self.cols_cap)
+
+    def mds(self):
+        return A.slot_strings(self.md, self.md_len, self.md_cap)
+
+    def rmds(self):
+        return A.slot_strings(self.rmd, self.rmd_len, self.md_cap)
+
+
+class ProbeStatsHost:
+    def __init__(self, n_probes):
+        self.n_probes = n_probes
+        self.unique_pairs = np.zeros(n_probes, dtype=np.int32)
+        self.duplicate_pairs = np.zeros(n_probes, dtype=np.int32)
+        self.max_pairs_per_uid = np.zeros(n_probes, dtype=np.int32)
+
+    def c(self):
+        return A.ProbeStats(self.n_probes, A.ptr(self.unique_pairs, A.i32p), A.ptr(self.duplicate_pairs, A.i32p),
+                            A.ptr(self.max_pairs_per_uid, A.i32p))
+
+
+def scorer(match=1, mismatch=-4, gap_extend=-1, gap_start=-6):
+    """SimpleAlignmentScorer defaults (COMMON/alignment/SimpleAlignmentScorer.java:23-26)."""
+    return A.Scorer(match, mismatch, gap_extend, gap_start)
+
+
+byref = C.byref

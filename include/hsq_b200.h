@@ -1,0 +1,185 @@
+/* hsq_b200.h -- C ABI of the B200-native HSQUtils hot path (trim / UID dedup / primer extension).
+ *
+ * This is the drop-in boundary.  The reference (NimbleGen/bioinformatics, pure Java) has no FFI;
+ * the seams this ABI sits behind are ordinary Java entry points.  Each function cites the one it
+ * replaces.  Roots under /root/reference:
+ *   COMMON/ = bioinformatics_common/src/main/java/com/roche/sequencing/bioinformatics/common/
+ *   HSQ/    = nimblegen_heatseq/src/main/java/com/roche/heatseq/
+ *
+ * Conventions
+ *   - plain C, no C++/torch types; every function returns int32 status (0 = HSQ_OK, <0 = error);
+ *     hsq_last_error(ctx) gives a message.  No exception crosses the boundary, nothing is dropped
+ *     silently, and there is NO CPU fallback: without a usable sm_100 device hsq_ctx_create fails.
+ *   - caller owns every input/output buffer (host memory; pinned via hsq_pinned_alloc is fastest),
+ *     the library owns only the opaque context and its device scratch.
+ *   - one context per GPU; a context is used by one thread at a time; contexts are independent.
+ *   - sequences are ASCII (IUPAC letters, any case, '_' '.' '-' = gap) exactly as the Java side
+ *     holds them in Strings; encoding to device codes happens on the GPU.
+ *   - "read end" index m = 2*pair + mate (mate 0 = read one / extension side, 1 = read two).
+ */
+#ifndef HSQ_B200_H
+#define HSQ_B200_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HSQ_OK 0
+#define HSQ_ERR_INVALID_ARGUMENT (-1)
+#define HSQ_ERR_CUDA (-2)
+#define HSQ_ERR_NO_DEVICE (-3)
+#define HSQ_ERR_BAD_CHARACTER (-4) /* a sequence holds a byte that is not an IUPAC code (Java: IllegalArgumentException) */
+#define HSQ_ERR_UNSUPPORTED (-5)   /* input outside the accelerated domain (e.g. UID longer than 32 bases) */
+#define HSQ_ERR_OUT_OF_RANGE (-6)  /* Java would throw IndexOutOfBounds / IllegalArgument (e.g. trim start >= read length) */
+#define HSQ_ERR_OVERFLOW (-7)      /* an output slot was too small; the per-item overflow flags say which */
+
+#define HSQ_PRIMER_NOT_FOUND (-2147483647) /* Java `null` from getPrimerEndIndexInRead */
+
+#define HSQ_ALIGN_PENALIZE_START 1u /* IAlignmentScorer.shouldPenalizeStartingTerminalGaps */
+#define HSQ_ALIGN_PENALIZE_END 2u   /* IAlignmentScorer.shouldPenalizeEndingTerminalGaps */
+
+typedef struct hsq_ctx hsq_ctx;
+
+/* SimpleAlignmentScorer's four numbers (COMMON/alignment/SimpleAlignmentScorer.java:28-31).
+ * Integer valued in every reachable configuration (HSQ/cli/DeduplicationCli.java:288-327). */
+typedef struct hsq_scorer {
+    int32_t match, mismatch, gap_extend, gap_start;
+} hsq_scorer;
+
+/* Ragged batch of ASCII strings: string k is data[offsets[k] .. offsets[k+1]). */
+typedef struct hsq_seqs {
+    const uint8_t* data;
+    const int64_t* offsets; /* n+1 entries */
+    int64_t n;
+} hsq_seqs;
+
+/* Probe table = the fields of COMMON/utils/probeinfo/Probe.java:53-69 the hot path reads. */
+typedef struct hsq_probe_table {
+    int64_t n;
+    const uint8_t* reverse_strand; /* 1 when probe_strand is '-' */
+    const int32_t* ext_start;
+    const int32_t* ext_stop;
+    const int32_t* lig_start;
+    const int32_t* lig_stop;
+    const int32_t* target_start;
+    const int32_t* target_stop;
+    hsq_seqs ext, lig, target; /* primer and capture-target sequences as in the probe-info file */
+} hsq_probe_table;
+
+/* Read pairs as they reach PrimerReadExtensionAndFilteringOfUniquePcrProbesTask
+ * (HSQ/process/PrimerReadExtensionAndPcrDuplicateIdentification.java:836): raw reads + qualities,
+ * read name = FASTQ ordinal, assigned probe. */
+typedef struct hsq_pair_batch {
+    int64_t n;
+    const int32_t* probe_id;   /* row of the probe table */
+    const int32_t* read_index; /* Integer.parseInt(readName); may be NULL for hsq_extend_batch */
+    hsq_seqs r1, r2;           /* raw read strings */
+    const uint8_t* q1;         /* base-quality chars, laid out by r1.offsets; may be NULL for hsq_extend_batch */
+    const uint8_t* q2;         /* laid out by r2.offsets */
+} hsq_pair_batch;
+
+/* Per read end results of ExtendReadsToPrimer.calculateDetailsForReadExtensionToPrimer
+ * (HSQ/process/ExtendReadsToPrimer.java:200-245).  Arrays have 2*n entries (index 2*pair+mate). */
+typedef struct hsq_extend_out {
+    int32_t cigar_cap, md_cap; /* in: bytes per slot */
+    uint8_t* ok;               /* 1 = ReadExtensionDetails != null */
+    int32_t* primer_end;       /* getPrimerEndIndexInRead, HSQ_PRIMER_NOT_FOUND for null */
+    int32_t* score;            /* capture-target alignment score (0 when that DP was not reached) */
+    int32_t* pos;              /* alignmentStartInReference */
+    int32_t* read_start;       /* first kept base of the raw read */
+    int32_t* read_stop;        /* last kept base (inclusive) */
+    int32_t* nm;               /* editDistance (NM tag) */
+    int32_t* tlen;             /* inferred insert size (+-capture target length) */
+    int32_t* cigar_len;
+    uint8_t* cigar;            /* [2n][cigar_cap] standard CIGAR (M/I/D), not NUL terminated */
+    int32_t* md_len;
+    uint8_t* md;               /* [2n][md_cap] MD tag */
+    uint8_t* overflow;         /* bit0: cigar slot too small, bit1: md slot too small */
+    uint8_t* pair_ok;          /* [n] both mates extended (ExtendReadsToPrimer.java:364) */
+    int64_t cells;             /* out: DP cells filled = sum len(q)*len(r) over the DPs the reference runs */
+} hsq_extend_out;
+
+/* Operator seam: one NeedlemanWunschGlobalAlignment per item
+ * (COMMON/alignment/NeedlemanWunschGlobalAlignment.java:44,85,131,236,250; AlignmentPair.java). */
+typedef struct hsq_align_out {
+    int32_t cols_cap, md_cap;  /* in: bytes per slot */
+    int32_t* score;            /* getAlignmentScore */
+    int32_t* n_cols;           /* alignment length */
+    uint8_t* ref_aln;          /* [n][cols_cap] reference alignment as characters (gap = '_') */
+    uint8_t* qry_aln;          /* [n][cols_cap] query alignment */
+    uint8_t* ops;              /* [n][cols_cap] expanded cigar: '=' 'X' 'I' 'D' (CigarStringUtil.java:61-83) */
+    int32_t* first_q;          /* AlignmentPair.firstNonDeletionIndexInQuery */
+    int32_t* last_q;
+    int32_t* first_r;
+    int32_t* last_r;
+    int32_t* matches;          /* getNumberOfMatches */
+    int32_t* mismatches;       /* getNumberOfMismatches */
+    int32_t* non_terminal_gaps;/* getNumberOfNonTerminalGaps */
+    int32_t* edit_distance;    /* AlignmentPair.getEditDistance (equality based) */
+    int32_t* md_len;
+    uint8_t* md;               /* [n][md_cap] getMismatchDetailsString */
+    int32_t* rmd_len;
+    uint8_t* rmd;              /* [n][md_cap] getReverseMismatchDetailsString */
+    uint8_t* overflow;         /* bit0 cols, bit1 md, bit2 rmd */
+    int64_t cells;             /* out */
+} hsq_align_out;
+
+/* Per probe counters of FilterByUid.reduceReadsByProbeAndUid (HSQ/process/FilterByUid.java:149-171,251). */
+typedef struct hsq_probe_stats {
+    int64_t n_probes;          /* in: rows in the arrays below */
+    int32_t* unique_pairs;     /* number of UID groups */
+    int32_t* duplicate_pairs;
+    int32_t* max_pairs_per_uid;
+} hsq_probe_stats;
+
+/* Candidates of the multi-probe tie-break (…Identification.java:704-765): read k has candidate
+ * probes cand_probe[cand_offsets[k] .. cand_offsets[k+1]). */
+typedef struct hsq_candidates {
+    int64_t n;                 /* reads */
+    hsq_seqs r1, r2;
+    const int64_t* cand_offsets;
+    const int32_t* cand_probe;
+} hsq_candidates;
+
+/* ---- context ------------------------------------------------------------------------------ */
+int32_t hsq_ctx_create(int32_t device, hsq_ctx** out);
+void hsq_ctx_destroy(hsq_ctx* ctx);
+const char* hsq_last_error(const hsq_ctx* ctx); /* ctx may be NULL: last create error */
+const char* hsq_version(void);
+int32_t hsq_pinned_alloc(hsq_ctx* ctx, size_t bytes, void** out);
+int32_t hsq_pinned_free(hsq_ctx* ctx, void* p);
+/* ApplicationSettings.getAlignmentScorer(): the user scorer for the capture-target DP. */
+int32_t hsq_set_scorer(hsq_ctx* ctx, const hsq_scorer* scorer);
+/* ParsedProbeFile -> device resident probe table (copied; caller may free its arrays). */
+int32_t hsq_set_probes(hsq_ctx* ctx, const hsq_probe_table* probes);
+/* Device time (ms, CUDA events on the context's stream) of the kernels of the last batch call,
+ * and how many kernels it launched. */
+int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches);
+
+/* ---- batch entry points (host buffers in, host buffers out) -------------------------------- */
+/* new NeedlemanWunschGlobalAlignment(ref[k], qry[k], SimpleAlignmentScorer(scorer, flags)).getAlignmentPair() */
+int32_t hsq_align_batch(hsq_ctx* ctx, const hsq_seqs* refs, const hsq_seqs* queries, const hsq_scorer* scorer,
+                        uint32_t flags, hsq_align_out* out);
+/* FastqReadTrimmer.trim(String,String,int,int,boolean) (HSQ/process/FastqReadTrimmer.java:309-328) per read.
+ * out_offsets gets n+1 entries; out_seq/out_qual must hold the input's total bytes. */
+int32_t hsq_trim_batch(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int32_t first_base_to_keep,
+                       int32_t last_base_to_keep, int32_t three_prime, uint8_t* out_seq, uint8_t* out_qual,
+                       int64_t* out_offsets);
+/* FilterByUid.reduceReadsByProbeAndUid + findBestData over every probe of the batch at once
+ * (HSQ/process/FilterByUid.java:71-203,281-297).  is_best[k]=1: pair k represents its (probe,UID) group. */
+int32_t hsq_dedup_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len,
+                        uint8_t* is_best, int32_t* group_size, hsq_probe_stats* stats);
+/* ExtendReadsToPrimer.extendReadsToPrimers (HSQ/process/ExtendReadsToPrimer.java:347-380) for a batch that
+ * may span probes.  Needs hsq_set_probes and hsq_set_scorer first. */
+int32_t hsq_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, hsq_extend_out* out);
+/* Multi-probe tie-break (…Identification.java:704-765): best_probe[k] = winning probe row or -1 when
+ * the read must be removed from all probes.  matches/edit (per candidate, may be NULL) expose the two metrics. */
+int32_t hsq_resolve_multi_probe(hsq_ctx* ctx, const hsq_candidates* cands, int32_t ext_uid_len, int32_t lig_uid_len,
+                                int32_t* best_probe, int32_t* cand_matches, int32_t* cand_edit);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HSQ_B200_H */

@@ -1,0 +1,261 @@
+// hsq_oracle.cpp -- TEST INFRASTRUCTURE ONLY (parity oracle / timed CPU baseline); see hsq_oracle_core.hpp.
+// C entry points with the same batch structs as include/hsq_b200.h so tests compare array to array.
+#include "hsq_oracle_heatseq.hpp"
+#include "../include/hsq_b200.h"
+#include <cstring>
+#include <thread>
+#include <atomic>
+#include <unordered_map>
+
+using namespace hsqo;
+
+static thread_local std::string g_err;
+
+static seq_t get_seq(const hsq_seqs& s, int64_t k) {
+    return encode_string((const char*)s.data + s.offsets[k], s.offsets[k + 1] - s.offsets[k]);
+}
+static std::string get_str(const uint8_t* data, const int64_t* off, int64_t k) {
+    return std::string((const char*)data + off[k], (size_t)(off[k + 1] - off[k]));
+}
+static void put_slot(const std::string& s, uint8_t* base, int32_t cap, int64_t k, int32_t* len, uint8_t* ovf, uint8_t bit) {
+    if (len) len[k] = (int32_t)s.size();
+    if ((int)s.size() > cap) { if (ovf) ovf[k] |= bit; }
+    if (base) memcpy(base + (size_t)k * cap, s.data(), std::min((size_t)cap, s.size()));
+}
+static Probe get_probe(const hsq_probe_table& t, int64_t k) {
+    Probe p;
+    p.reverse_strand = t.reverse_strand[k] != 0;
+    p.ext_start = t.ext_start[k]; p.ext_stop = t.ext_stop[k];
+    p.lig_start = t.lig_start[k]; p.lig_stop = t.lig_stop[k];
+    p.target_start = t.target_start[k]; p.target_stop = t.target_stop[k];
+    p.ext = get_seq(t.ext, k); p.lig = get_seq(t.lig, k); p.target = get_seq(t.target, k);
+    return p;
+}
+
+template <class F>
+static int run_parallel(int64_t n, int nthreads, F f) {
+    if (nthreads < 1) nthreads = 1;
+    std::atomic<int64_t> next(0);
+    std::atomic<int> status(0);
+    std::vector<std::string> errs((size_t)nthreads);
+    auto worker = [&](int t) {
+        NwWorkspace ws;
+        const int64_t chunk = 64;
+        while (true) {
+            int64_t b = next.fetch_add(chunk);
+            if (b >= n) break;
+            int64_t e = std::min(n, b + chunk);
+            try {
+                for (int64_t k = b; k < e; k++) f(k, ws, t);
+            } catch (const std::exception& ex) {
+                errs[(size_t)t] = ex.what();
+                status = HSQ_ERR_OUT_OF_RANGE;
+                if (dynamic_cast<const std::invalid_argument*>(&ex)) status = HSQ_ERR_BAD_CHARACTER;
+                break;
+            }
+        }
+    };
+    std::vector<std::thread> th;
+    for (int t = 1; t < nthreads; t++) th.emplace_back(worker, t);
+    worker(0);
+    for (auto& x : th) x.join();
+    for (auto& e : errs) if (!e.empty()) g_err = e;
+    return status;
+}
+
+extern "C" {
+
+const char* hsqo_last_error(void) { return g_err.c_str(); }
+
+int32_t hsqo_align_batch(const hsq_seqs* refs, const hsq_seqs* qrys, const hsq_scorer* scorer, uint32_t flags,
+                         hsq_align_out* o, int32_t nthreads) {
+    Scorer sc;
+    sc.match = scorer->match; sc.mismatch = scorer->mismatch; sc.gap_extend = scorer->gap_extend; sc.gap_start = scorer->gap_start;
+    sc.penalize_start = (flags & HSQ_ALIGN_PENALIZE_START) != 0;
+    sc.penalize_end = (flags & HSQ_ALIGN_PENALIZE_END) != 0;
+    int64_t n = refs->n;
+    std::vector<int64_t> cells((size_t)std::max(1, nthreads), 0);
+    int st = run_parallel(n, nthreads, [&](int64_t k, NwWorkspace& ws, int t) {
+        NwResult r = nw_align(get_seq(*refs, k), get_seq(*qrys, k), sc, &ws);
+        cells[(size_t)t] += r.cells;
+        const AlignmentPair& p = r.pair;
+        if (o->overflow) o->overflow[k] = 0;
+        if (o->score) o->score[k] = r.score;
+        if (o->n_cols) o->n_cols[k] = p.size();
+        put_slot(decode_seq(p.ref_aln), o->ref_aln, o->cols_cap, k, nullptr, o->overflow, 1);
+        put_slot(decode_seq(p.qry_aln), o->qry_aln, o->cols_cap, k, nullptr, o->overflow, 1);
+        put_slot(expanded_cigar(p), o->ops, o->cols_cap, k, nullptr, o->overflow, 1);
+        if (o->first_q) o->first_q[k] = p.first_q;
+        if (o->last_q) o->last_q[k] = p.last_q;
+        if (o->first_r) o->first_r[k] = p.first_r;
+        if (o->last_r) o->last_r[k] = p.last_r;
+        if (o->matches) o->matches[k] = p.number_of_matches();
+        if (o->mismatches) o->mismatches[k] = p.number_of_mismatches();
+        if (o->non_terminal_gaps) o->non_terminal_gaps[k] = p.number_of_non_terminal_gaps();
+        if (o->edit_distance) o->edit_distance[k] = p.edit_distance();
+        put_slot(md_string(p), o->md, o->md_cap, k, o->md_len, o->overflow, 2);
+        put_slot(reverse_md_string(p), o->rmd, o->md_cap, k, o->rmd_len, o->overflow, 4);
+    });
+    o->cells = 0;
+    for (auto c : cells) o->cells += c;
+    return st;
+}
+
+int32_t hsqo_trim_batch(const hsq_seqs* reads, const uint8_t* quals, int32_t first, int32_t last, int32_t three_prime,
+                        uint8_t* out_seq, uint8_t* out_qual, int64_t* out_offsets) {
+    try {
+        int64_t pos = 0;
+        out_offsets[0] = 0;
+        for (int64_t k = 0; k < reads->n; k++) {
+            int64_t b = reads->offsets[k];
+            int len = (int)(reads->offsets[k + 1] - b);
+            int f, l;
+            trim_range(len, first, last, three_prime != 0, &f, &l);
+            int keep = l - f + 1;
+            memcpy(out_seq + pos, reads->data + b + f, (size_t)keep);
+            memcpy(out_qual + pos, quals + b + f, (size_t)keep);
+            pos += keep;
+            out_offsets[k + 1] = pos;
+        }
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+        return HSQ_ERR_OUT_OF_RANGE;
+    }
+    return HSQ_OK;
+}
+
+// FilterByUid.reduceReadsByProbeAndUid over all probes (HSQ/process/FilterByUid.java:134-203) + findBestData (:281-297)
+int32_t hsqo_dedup_batch(const hsq_pair_batch* pb, int32_t u, int32_t v, uint8_t* is_best, int32_t* group_size,
+                         hsq_probe_stats* stats) {
+    try {
+        std::map<std::pair<int32_t, std::string>, std::vector<int64_t>> groups;
+        for (int64_t k = 0; k < pb->n; k++) {
+            std::string r1 = get_str(pb->r1.data, pb->r1.offsets, k), r2 = get_str(pb->r2.data, pb->r2.offsets, k);
+            if ((int)r1.size() < u || (int)r2.size() < v) throw std::out_of_range("UID longer than read");
+            std::string uid = r1.substr(0, (size_t)u) + r2.substr(0, (size_t)v);  // :136-138, SAMRecordUtil.java:73-86
+            groups[{pb->probe_id[k], uid}].push_back(k);
+        }
+        if (stats) for (int64_t p = 0; p < stats->n_probes; p++) {
+            stats->unique_pairs[p] = 0; stats->duplicate_pairs[p] = 0; stats->max_pairs_per_uid[p] = 0;
+        }
+        for (auto& g : groups) {
+            int64_t best = -1;
+            int best_score = INT32_MIN;
+            int32_t best_id = 0;
+            for (int64_t k : g.second) {
+                int score = total_quality_score((const char*)pb->q1 + pb->r1.offsets[k], pb->r1.offsets[k + 1] - pb->r1.offsets[k],
+                                                (const char*)pb->q2 + pb->r2.offsets[k], pb->r2.offsets[k + 1] - pb->r2.offsets[k]);
+                int32_t id = pb->read_index[k];
+                if (score > best_score || (score == best_score && id < best_id)) { best_score = score; best = k; best_id = id; }
+            }
+            for (int64_t k : g.second) {
+                is_best[k] = (k == best) ? 1 : 0;
+                if (group_size) group_size[k] = (int32_t)g.second.size();
+            }
+            if (stats) {
+                int32_t p = g.first.first;
+                stats->unique_pairs[p] += 1;
+                stats->duplicate_pairs[p] += (int32_t)g.second.size() - 1;
+                stats->max_pairs_per_uid[p] = std::max(stats->max_pairs_per_uid[p], (int32_t)g.second.size());
+            }
+        }
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+        return HSQ_ERR_OUT_OF_RANGE;
+    }
+    return HSQ_OK;
+}
+
+int32_t hsqo_extend_batch(const hsq_probe_table* pt, const hsq_scorer* scorer, const hsq_pair_batch* pb, hsq_extend_out* o,
+                          int32_t nthreads) {
+    Scorer sc;
+    sc.match = scorer->match; sc.mismatch = scorer->mismatch; sc.gap_extend = scorer->gap_extend; sc.gap_start = scorer->gap_start;
+    std::vector<Probe> probes;
+    try {
+        for (int64_t k = 0; k < pt->n; k++) probes.push_back(get_probe(*pt, k));
+    } catch (const std::exception& ex) { g_err = ex.what(); return HSQ_ERR_BAD_CHARACTER; }
+    std::vector<int64_t> cells((size_t)std::max(1, nthreads), 0);
+    int st = run_parallel(pb->n, nthreads, [&](int64_t k, NwWorkspace& ws, int t) {
+        const Probe& p = probes[(size_t)pb->probe_id[k]];
+        seq_t s1 = get_seq(pb->r1, k), s2 = get_seq(pb->r2, k);
+        std::string q1(s1.size(), 'I'), q2(s2.size(), 'I');
+        if (pb->q1) q1 = get_str(pb->q1, pb->r1.offsets, k);
+        if (pb->q2) q2 = get_str(pb->q2, pb->r2.offsets, k);
+        PairExtension e = extend_read_pair(p, s1, q1, s2, q2, sc, &ws, &cells[(size_t)t]);
+        const ReadEndDetails* d[2] = {&e.one, &e.two};
+        int tl[2] = {e.tlen1, e.tlen2};
+        for (int m = 0; m < 2; m++) {
+            int64_t i = 2 * k + m;
+            o->ok[i] = d[m]->ok;
+            o->primer_end[i] = d[m]->primer_end;
+            o->score[i] = d[m]->score;
+            o->pos[i] = d[m]->ok ? d[m]->pos : 0;
+            o->read_start[i] = d[m]->ok ? d[m]->read_start : 0;
+            o->read_stop[i] = d[m]->ok ? d[m]->read_stop : 0;
+            o->nm[i] = d[m]->ok ? d[m]->nm : 0;
+            if (o->tlen) o->tlen[i] = d[m]->ok ? tl[m] : 0;
+            o->overflow[i] = 0;
+            put_slot(d[m]->cigar, o->cigar, o->cigar_cap, i, o->cigar_len, o->overflow, 1);
+            put_slot(d[m]->md, o->md, o->md_cap, i, o->md_len, o->overflow, 2);
+        }
+        o->pair_ok[k] = e.pair_ok();
+    });
+    o->cells = 0;
+    for (auto c : cells) o->cells += c;
+    return st;
+}
+
+int32_t hsqo_resolve_multi_probe(const hsq_probe_table* pt, const hsq_candidates* c, int32_t u, int32_t v, int32_t* best_probe,
+                                 int32_t* cand_matches, int32_t* cand_edit) {
+    try {
+        NwWorkspace ws;
+        int64_t cells = 0;
+        for (int64_t k = 0; k < c->n; k++) {
+            seq_t r1 = get_seq(c->r1, k), r2 = get_seq(c->r2, k);
+            int lowest = INT32_MAX, most = 0;
+            std::vector<int32_t> best;  // …Identification.java:704-751
+            for (int64_t j = c->cand_offsets[k]; j < c->cand_offsets[k + 1]; j++) {
+                int m, e;
+                tie_break_metrics(get_probe(*pt, c->cand_probe[j]), r1, r2, u, v, &ws, &cells, &m, &e);
+                if (cand_matches) cand_matches[j] = m;
+                if (cand_edit) cand_edit[j] = e;
+                if (m > most) { best.clear(); best.push_back(c->cand_probe[j]); lowest = e; most = m; }
+                else if (m == most) {
+                    if (e == lowest) best.push_back(c->cand_probe[j]);
+                    else if (e < lowest) { best.clear(); best.push_back(c->cand_probe[j]); lowest = e; most = m; }
+                }
+            }
+            best_probe[k] = (best.size() == 1) ? best[0] : -1;  // :757-765
+        }
+    } catch (const std::exception& ex) { g_err = ex.what(); return HSQ_ERR_OUT_OF_RANGE; }
+    return HSQ_OK;
+}
+
+// single-call helpers for the KAT tests
+int32_t hsqo_primer_end(const char* primer, const char* read, double* weighted) {
+    int64_t cells = 0;
+    NwWorkspace ws;
+    return primer_end_index_in_read(encode_string(primer), encode_string(read), &ws, &cells, weighted);
+}
+int32_t hsqo_index_of_first_match_in_reference(const char* ref, const char* qry) {
+    Scorer sc;
+    return index_of_first_match_in_reference(nw_align(encode_string(ref), encode_string(qry), sc).pair);
+}
+int32_t hsqo_cigar_edit_distance(const char* ref, const char* qry) {
+    Scorer sc;
+    return cigar_edit_distance(expanded_cigar(nw_align(encode_string(ref), encode_string(qry), sc).pair));
+}
+// MD over the begin/end-trimmed alignment with the UNTRIMMED cigar (CigarStringUtilTest.java:75-109); reverse!=0 reverses both.
+int32_t hsqo_md_trimmed_with_full_cigar(const char* ref, const char* qry, int32_t reverse, char* out, int32_t cap) {
+    Scorer sc;
+    NwResult r = nw_align(encode_string(ref), encode_string(qry), sc);
+    AlignmentPair t = r.pair.without_ending_and_beginning_query_inserts();
+    std::string cig = expanded_cigar(r.pair);
+    seq_t ra = t.ref_aln;
+    if (reverse) { std::reverse(cig.begin(), cig.end()); ra = seq_reverse(ra); }
+    std::string md = md_string(ra, cig);
+    snprintf(out, (size_t)cap, "%s", md.c_str());
+    return (int32_t)md.size();
+}
+
+}  // extern "C"

@@ -1,0 +1,130 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes binding of the CPU parity oracle (oracle/libhsq_oracle.so).
+
+Importable only from tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+legs.  The product package never imports this module.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from bioinformatics_b200 import _abi as A
+from bioinformatics_b200.batches import (AlignResult, ExtendResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
+                                         scorer)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libhsq_oracle.so")
+_lib = None
+
+
+def build(force=False):
+    if force or not os.path.exists(_SO):
+        subprocess.check_call(["make", "-C", _HERE] + (["-B"] if force else []), stdout=subprocess.DEVNULL)
+    return _SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        build()
+        try:
+            _lib = C.CDLL(_SO)
+        except OSError:
+            build(force=True)
+            _lib = C.CDLL(_SO)
+        _lib.hsqo_last_error.restype = C.c_char_p
+        for name in ("hsqo_align_batch", "hsqo_trim_batch", "hsqo_dedup_batch", "hsqo_extend_batch",
+                     "hsqo_resolve_multi_probe", "hsqo_primer_end", "hsqo_index_of_first_match_in_reference",
+                     "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar"):
+            getattr(_lib, name).restype = C.c_int32
+    return _lib
+
+
+class OracleError(RuntimeError):
+    def __init__(self, status):
+        super().__init__("oracle status %d: %s" % (status, lib().hsqo_last_error().decode()))
+        self.status = status
+
+
+def _check(st):
+    if st != 0:
+        raise OracleError(st)
+
+
+def align_batch(refs, qrys, sc=None, flags=0, cols_cap=640, md_cap=640, nthreads=1):
+    refs = refs if isinstance(refs, A.SeqBatch) else A.SeqBatch.from_strings(refs)
+    qrys = qrys if isinstance(qrys, A.SeqBatch) else A.SeqBatch.from_strings(qrys)
+    sc = sc or scorer()
+    out = AlignResult(refs.n, cols_cap, md_cap)
+    rc, qc, oc = refs.c(), qrys.c(), out.c()
+    _check(lib().hsqo_align_batch(C.byref(rc), C.byref(qc), C.byref(sc), C.c_uint32(flags), C.byref(oc),
+                                  C.c_int32(nthreads)))
+    return out.finish()
+
+
+def trim_batch(reads, quals, first, last, three_prime=True):
+    reads = reads if isinstance(reads, A.SeqBatch) else A.SeqBatch.from_strings(reads)
+    quals = quals if isinstance(quals, A.SeqBatch) else A.SeqBatch.from_strings(quals)
+    out_seq = np.zeros(max(1, len(reads.data)), dtype=np.uint8)
+    out_qual = np.zeros(max(1, len(reads.data)), dtype=np.uint8)
+    out_off = np.zeros(reads.n + 1, dtype=np.int64)
+    rc = reads.c()
+    _check(lib().hsqo_trim_batch(C.byref(rc), A.ptr(quals.data, A.u8p), C.c_int32(first), C.c_int32(last),
+                                 C.c_int32(1 if three_prime else 0), A.ptr(out_seq, A.u8p), A.ptr(out_qual, A.u8p),
+                                 A.ptr(out_off, A.i64p)))
+    total = int(out_off[-1])
+    return A.SeqBatch(out_seq[:total], out_off), A.SeqBatch(out_qual[:total], out_off)
+
+
+def dedup_batch(pairs, ext_uid_len, lig_uid_len, n_probes):
+    is_best = np.zeros(pairs.n, dtype=np.uint8)
+    group_size = np.zeros(pairs.n, dtype=np.int32)
+    stats = ProbeStatsHost(n_probes)
+    pc, sc = pairs.c(), stats.c()
+    _check(lib().hsqo_dedup_batch(C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len), A.ptr(is_best, A.u8p),
+                                  A.ptr(group_size, A.i32p), C.byref(sc)))
+    return is_best, group_size, stats
+
+
+def extend_batch(probes, pairs, sc=None, cigar_cap=32, md_cap=48, nthreads=1):
+    sc = sc or scorer()
+    out = ExtendResult(pairs.n, cigar_cap, md_cap)
+    tc, pc, oc = probes.c(), pairs.c(), out.c()
+    _check(lib().hsqo_extend_batch(C.byref(tc), C.byref(sc), C.byref(pc), C.byref(oc), C.c_int32(nthreads)))
+    return out.finish()
+
+
+def resolve_multi_probe(probes, r1, r2, cand_offsets, cand_probe, ext_uid_len, lig_uid_len):
+    r1 = r1 if isinstance(r1, A.SeqBatch) else A.SeqBatch.from_strings(r1)
+    r2 = r2 if isinstance(r2, A.SeqBatch) else A.SeqBatch.from_strings(r2)
+    cand_offsets = np.ascontiguousarray(cand_offsets, dtype=np.int64)
+    cand_probe = np.ascontiguousarray(cand_probe, dtype=np.int32)
+    best = np.zeros(r1.n, dtype=np.int32)
+    m = np.zeros(len(cand_probe), dtype=np.int32)
+    e = np.zeros(len(cand_probe), dtype=np.int32)
+    cc = A.Candidates(r1.n, r1.c(), r2.c(), A.ptr(cand_offsets, A.i64p), A.ptr(cand_probe, A.i32p))
+    tc = probes.c()
+    _check(lib().hsqo_resolve_multi_probe(C.byref(tc), C.byref(cc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                          A.ptr(best, A.i32p), A.ptr(m, A.i32p), A.ptr(e, A.i32p)))
+    return best, m, e
+
+
+def primer_end(primer, read):
+    w = C.c_double(0)
+    r = lib().hsqo_primer_end(primer.encode(), read.encode(), C.byref(w))
+    return (None if r == A.HSQ_PRIMER_NOT_FOUND else r), w.value
+
+
+def index_of_first_match_in_reference(ref, qry):
+    return lib().hsqo_index_of_first_match_in_reference(ref.encode(), qry.encode())
+
+
+def cigar_edit_distance(ref, qry):
+    return lib().hsqo_cigar_edit_distance(ref.encode(), qry.encode())
+
+
+def md_trimmed_with_full_cigar(ref, qry, reverse=False):
+    buf = C.create_string_buffer(4096)
+    lib().hsqo_md_trimmed_with_full_cigar(ref.encode(), qry.encode(), C.c_int32(1 if reverse else 0), buf, 4096)
+    return buf.value.decode()
