@@ -1,0 +1,159 @@
+"""Loads the CUDA C-ABI library (bioinformatics_b200/libhsq_b200.so) and wraps a context.
+
+There is no CPU fallback anywhere in this package: if the library is missing or no B200-class GPU is
+present, creating a context raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import _abi as A
+from .batches import AlignResult, ExtendResult, PairBatchHost, ProbeStatsHost, ProbeTableHost, scorer
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_PKG, "libhsq_b200.so")
+_lib = None
+
+EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version", "hsq_pinned_alloc", "hsq_pinned_free",
+           "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
+           "hsq_extend_batch", "hsq_resolve_multi_probe")
+
+
+class HsqError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__("hsq status %d: %s" % (status, message))
+        self.status = status
+
+
+def load():
+    """dlopen the CUDA library.  Raises if it has not been built (python -m bioinformatics_b200.build)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise HsqError(A.HSQ_ERR_NO_DEVICE, "CUDA extension %s is missing; run __graft_entry__.build()" % SO_PATH)
+        lib = C.CDLL(SO_PATH)
+        lib.hsq_last_error.restype = C.c_char_p
+        lib.hsq_last_error.argtypes = [C.c_void_p]
+        lib.hsq_version.restype = C.c_char_p
+        lib.hsq_ctx_destroy.restype = None
+        lib.hsq_ctx_destroy.argtypes = [C.c_void_p]
+        for name in EXPORTS:
+            if name not in ("hsq_last_error", "hsq_version", "hsq_ctx_destroy"):
+                getattr(lib, name).restype = C.c_int32
+        _lib = lib
+    return _lib
+
+
+class Context:
+    """One hsq_ctx (one GPU)."""
+
+    def __init__(self, device=0, scorer_=None):
+        self.lib = load()
+        h = C.c_void_p()
+        st = self.lib.hsq_ctx_create(C.c_int32(device), C.byref(h))
+        if st != 0:
+            raise HsqError(st, self.lib.hsq_last_error(None).decode())
+        self.h = h
+        self.device = device
+        self.n_probes = 0
+        self.set_scorer(scorer_ or scorer())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.hsq_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, st):
+        if st != 0:
+            raise HsqError(st, self.lib.hsq_last_error(self.h).decode())
+
+    def last_timing(self):
+        ms, n = C.c_float(0), C.c_int32(0)
+        self.lib.hsq_last_timing(self.h, C.byref(ms), C.byref(n))
+        return ms.value, n.value
+
+    def pinned_array(self, nbytes):
+        """uint8 numpy array backed by pinned host memory owned by this context."""
+        p = C.c_void_p()
+        self._check(self.lib.hsq_pinned_alloc(self.h, C.c_size_t(nbytes), C.byref(p)))
+        buf = (C.c_uint8 * max(1, nbytes)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=np.uint8, count=nbytes)
+        arr._hsq_pinned = p  # keep the address for pinned_free
+        return arr
+
+    def set_scorer(self, sc):
+        self.scorer = sc
+        self._check(self.lib.hsq_set_scorer(self.h, C.byref(sc)))
+
+    def set_probes(self, probes: ProbeTableHost):
+        t = probes.c()
+        self._check(self.lib.hsq_set_probes(self.h, C.byref(t)))
+        self.n_probes = probes.n
+
+    def align_batch(self, refs, qrys, sc=None, flags=0, cols_cap=640, md_cap=640):
+        refs = refs if isinstance(refs, A.SeqBatch) else A.SeqBatch.from_strings(refs)
+        qrys = qrys if isinstance(qrys, A.SeqBatch) else A.SeqBatch.from_strings(qrys)
+        sc = sc or scorer()
+        out = AlignResult(refs.n, cols_cap, md_cap)
+        rc, qc, oc = refs.c(), qrys.c(), out.c()
+        st = self.lib.hsq_align_batch(self.h, C.byref(rc), C.byref(qc), C.byref(sc), C.c_uint32(flags), C.byref(oc))
+        out.finish()
+        self._check(st)
+        return out
+
+    def trim_batch(self, reads, quals, first, last, three_prime=True):
+        reads = reads if isinstance(reads, A.SeqBatch) else A.SeqBatch.from_strings(reads)
+        quals = quals if isinstance(quals, A.SeqBatch) else A.SeqBatch.from_strings(quals)
+        out_seq = np.zeros(max(1, len(reads.data)), dtype=np.uint8)
+        out_qual = np.zeros(max(1, len(reads.data)), dtype=np.uint8)
+        out_off = np.zeros(reads.n + 1, dtype=np.int64)
+        rc = reads.c()
+        self._check(self.lib.hsq_trim_batch(self.h, C.byref(rc), A.ptr(quals.data, A.u8p), C.c_int32(first), C.c_int32(last),
+                                            C.c_int32(1 if three_prime else 0), A.ptr(out_seq, A.u8p),
+                                            A.ptr(out_qual, A.u8p), A.ptr(out_off, A.i64p)))
+        total = int(out_off[-1])
+        return A.SeqBatch(out_seq[:total], out_off), A.SeqBatch(out_qual[:total], out_off)
+
+    def dedup_batch(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, n_probes=None):
+        n_probes = n_probes or self.n_probes
+        is_best = np.zeros(pairs.n, dtype=np.uint8)
+        group_size = np.zeros(pairs.n, dtype=np.int32)
+        stats = ProbeStatsHost(n_probes)
+        pc, sc = pairs.c(), stats.c()
+        self._check(self.lib.hsq_dedup_batch(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                             A.ptr(is_best, A.u8p), A.ptr(group_size, A.i32p), C.byref(sc)))
+        return is_best, group_size, stats
+
+    def extend_batch(self, pairs: PairBatchHost, cigar_cap=32, md_cap=48, out=None):
+        out = out or ExtendResult(pairs.n, cigar_cap, md_cap)
+        pc, oc = pairs.c(), out.c()
+        st = self.lib.hsq_extend_batch(self.h, C.byref(pc), C.byref(oc))
+        out.finish()
+        self._check(st)
+        return out
+
+    def resolve_multi_probe(self, r1, r2, cand_offsets, cand_probe, ext_uid_len, lig_uid_len):
+        r1 = r1 if isinstance(r1, A.SeqBatch) else A.SeqBatch.from_strings(r1)
+        r2 = r2 if isinstance(r2, A.SeqBatch) else A.SeqBatch.from_strings(r2)
+        cand_offsets = np.ascontiguousarray(cand_offsets, dtype=np.int64)
+        cand_probe = np.ascontiguousarray(cand_probe, dtype=np.int32)
+        best = np.zeros(r1.n, dtype=np.int32)
+        m = np.zeros(max(1, len(cand_probe)), dtype=np.int32)
+        e = np.zeros(max(1, len(cand_probe)), dtype=np.int32)
+        cc = A.Candidates(r1.n, r1.c(), r2.c(), A.ptr(cand_offsets, A.i64p), A.ptr(cand_probe, A.i32p))
+        self._check(self.lib.hsq_resolve_multi_probe(self.h, C.byref(cc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                                     A.ptr(best, A.i32p), A.ptr(m, A.i32p), A.ptr(e, A.i32p)))
+        return best, m[:len(cand_probe)], e[:len(cand_probe)]

@@ -1,0 +1,183 @@
+// hsq_capi.cu -- the C ABI of include/hsq_b200.h.  Host buffers in, host buffers out; all compute on the GPU.
+// There is no CPU fallback: every entry point needs a context, and a context needs a CUDA device.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include "hsq_host.cuh"
+
+using namespace hsq;
+
+namespace {
+
+struct CallTimer {  // brackets the kernels + copies of one batch call with events on the context's stream
+    hsq_ctx* ctx;
+    explicit CallTimer(hsq_ctx* c) : ctx(c) {
+        ctx->launches = 0;
+        cudaEventRecord(ctx->ev0, ctx->stream);
+    }
+    int finish() {
+        cudaEventRecord(ctx->ev1, ctx->stream);
+        cudaError_t e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) return fail(ctx, HSQ_ERR_CUDA, std::string("stream sync: ") + cudaGetErrorString(e));
+        cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev0, ctx->ev1);
+        ctx->last_launches = ctx->launches;
+        return HSQ_OK;
+    }
+};
+
+int reset_status(hsq_ctx* ctx) {
+    HSQ_CUDA(ctx, ctx->status.ensure(64));
+    HSQ_CUDA(ctx, ctx->cells.ensure(64));
+    HSQ_CUDA(ctx, cudaMemsetAsync(ctx->status.p, 0, 64, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemsetAsync(ctx->cells.p, 0, 64, ctx->stream));
+    return HSQ_OK;
+}
+
+// status word 0 = error code, words 1.. = max lengths
+int* d_status(hsq_ctx* ctx) { return ctx->status.as<int>(); }
+int* d_maxlen(hsq_ctx* ctx, int slot) { return ctx->status.as<int>() + 1 + slot; }
+
+int read_status(hsq_ctx* ctx, int* host_words, int n_words) {
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_status, ctx->status.p, sizeof(int) * (size_t)n_words, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < n_words; k++) host_words[k] = ctx->h_status[k];
+    return HSQ_OK;
+}
+
+// resident threads of a persistent launch
+template <class K>
+int persistent_grid(hsq_ctx* ctx, K kernel, int block, int64_t n_tasks, int* grid_out) {
+    int per_sm = 0;
+    HSQ_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, block, 0));
+    if (per_sm < 1) per_sm = 1;
+    int64_t grid = (int64_t)per_sm * ctx->sm_count;
+    int64_t need = (n_tasks + block - 1) / block;
+    if (need < 1) need = 1;
+    *grid_out = (int)std::min(grid, need);
+    return HSQ_OK;
+}
+
+int alloc_scratch(hsq_ctx* ctx, int64_t nthreads, int q_max, int r_max, ScratchPool* pool) {
+    int n_strips = (q_max + KROWS - 1) / KROWS;
+    if (n_strips < 1) n_strips = 1;
+    pool->r_stride = r_max + 1;
+    HSQ_CUDA(ctx, ctx->ptr_words.ensure((size_t)nthreads * n_strips * (size_t)(r_max + 1) * sizeof(uint32_t)));
+    HSQ_CUDA(ctx, ctx->brow.ensure((size_t)nthreads * (size_t)(r_max + 1) * sizeof(int32_t)));
+    HSQ_CUDA(ctx, ctx->cols.ensure((size_t)nthreads * (size_t)(q_max + r_max + 1) * sizeof(uint16_t)));
+    pool->ptr_words = ctx->ptr_words.as<uint32_t>();
+    pool->brow = ctx->brow.as<int32_t>();
+    pool->cols = ctx->cols.as<uint16_t>();
+    return HSQ_OK;
+}
+
+DeviceProbes probe_view(const hsq_ctx* ctx) {
+    DeviceProbes p;
+    p.reverse_strand = ctx->p_rev.as<uint8_t>();
+    p.ext_start = ctx->p_ext_start.as<int32_t>();
+    p.ext_stop = ctx->p_ext_stop.as<int32_t>();
+    p.lig_start = ctx->p_lig_start.as<int32_t>();
+    p.lig_stop = ctx->p_lig_stop.as<int32_t>();
+    p.ext = ctx->p_ext.view();
+    p.lig = ctx->p_lig.view();
+    p.target = ctx->p_target.view();
+    return p;
+}
+
+template <class T>
+int d2h(hsq_ctx* ctx, T* host, const T* dev, size_t count) {
+    if (!host || count == 0) return HSQ_OK;
+    HSQ_CUDA(ctx, cudaMemcpyAsync(host, dev, count * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+    return HSQ_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* hsq_version(void) { return "hsq-b200 0.1 (sm_100a)"; }
+
+const char* hsq_last_error(const hsq_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
+
+int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) {
+    if (!out) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, HSQ_ERR_NO_DEVICE, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count is 0") +
+                                                    " (this library has no CPU fallback)");
+    if (device < 0 || device >= count) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "device index out of range");
+    cudaDeviceProp prop;
+    HSQ_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(nullptr, HSQ_ERR_NO_DEVICE, std::string("device ") + prop.name + " is not sm_100 class; kernels are built for sm_100a only");
+    HSQ_CUDA(nullptr, cudaSetDevice(device));
+    hsq_ctx* ctx = new hsq_ctx();
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
+    HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
+    HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_status, 64));
+    HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_cells, 64));
+    std::vector<double> tbl(POW95_N);
+    for (int d = 0; d < POW95_N; d++) tbl[(size_t)d] = std::pow(0.95, (double)d);
+    HSQ_CUDA(nullptr, cudaMemcpyToSymbol(c_pow95, tbl.data(), sizeof(double) * POW95_N));
+    *out = ctx;
+    return HSQ_OK;
+}
+
+void hsq_ctx_destroy(hsq_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    hsq::DevBuf* bufs[] = {&ctx->p_rev, &ctx->p_ext_start, &ctx->p_ext_stop, &ctx->p_lig_start, &ctx->p_lig_stop, &ctx->q1, &ctx->q2,
+                           &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
+                           &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
+                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags};
+    for (auto* b : bufs) b->release();
+    hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb};
+    for (auto* s : seqs) s->release();
+    cudaFreeHost(ctx->h_status);
+    cudaFreeHost(ctx->h_cells);
+    cudaEventDestroy(ctx->ev0);
+    cudaEventDestroy(ctx->ev1);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int32_t hsq_pinned_alloc(hsq_ctx* ctx, size_t bytes, void** out) {
+    if (!ctx || !out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    HSQ_CUDA(ctx, cudaMallocHost(out, bytes ? bytes : 1));
+    return HSQ_OK;
+}
+
+int32_t hsq_pinned_free(hsq_ctx* ctx, void* p) {
+    if (!ctx) return HSQ_ERR_INVALID_ARGUMENT;
+    HSQ_CUDA(ctx, cudaFreeHost(p));
+    return HSQ_OK;
+}
+
+int32_t hsq_set_scorer(hsq_ctx* ctx, const hsq_scorer* scorer) {
+    if (!ctx || !scorer) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    ctx->scorer = *scorer;
+    ctx->have_scorer = true;
+    return HSQ_OK;
+}
+
+int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches) {
+    if (!ctx) return HSQ_ERR_INVALID_ARGUMENT;
+    if (kernel_ms) *kernel_ms = ctx->last_kernel_ms;
+    if (launches) *launches = ctx->last_launches;
+    return HSQ_OK;
+}
+
+}  // extern "C"
+
+#include "hsq_capi_probes.inl"
+#include "hsq_capi_align.inl"
+#include "hsq_capi_extend.inl"
+#include "hsq_capi_trim.inl"
+#include "hsq_capi_dedup.inl"
+#include "hsq_capi_resolve.inl"

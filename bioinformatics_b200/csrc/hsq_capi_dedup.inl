@@ -1,0 +1,205 @@
+// hsq_capi_dedup.inl -- hsq_dedup_batch: FilterByUid.reduceReadsByProbeAndUid + findBestData for all probes of a batch.
+//   UID         = R1[0:u] ++ R2[0:v]                       HSQ/process/FilterByUid.java:100-101,136-138
+//   group key   = (probe, UID)                              :134-147 (one HashMap per probe task)
+//   best pair   = max (short)(sum(q1-33)+sum(q2-33)), tie -> smaller Integer.parseInt(readName)   :281-297,
+//                 HSQ/utils/BamFileUtil.java:74-85, HSQ/objects/ReadPair.java:101-103 (Java short wrap-around)
+// Device plan: key generation (HBM-bound, one warp per pair) -> stable LSD radix sorts by rank, UID, probe
+// (so each group is contiguous with its best pair first) -> head flags -> per-group sizes and per-probe counters.
+// Round 1 uses cub::DeviceRadixSort for the sort passes; the surrounding kernels are hand-written.
+#include <cub/device/device_radix_sort.cuh>
+namespace hsq {
+
+__global__ void dedup_keygen_kernel(const uint8_t* __restrict__ r1, const int64_t* __restrict__ off1, const uint8_t* __restrict__ q1,
+                                    const uint8_t* __restrict__ r2, const int64_t* __restrict__ off2, const uint8_t* __restrict__ q2,
+                                    const int32_t* __restrict__ read_index, int64_t n, int u, int v, uint64_t* __restrict__ uid_out,
+                                    uint64_t* __restrict__ rank_out, uint32_t* __restrict__ idx_out, int* status) {
+    const int lane = threadIdx.x & 31;
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; w < n; w += stride) {
+        const int64_t b1 = off1[w], b2 = off2[w];
+        const int l1 = (int)(off1[w + 1] - b1), l2 = (int)(off2[w + 1] - b2);
+        int sum = 0;
+        for (int i = lane; i < l1; i += 32) sum += (int)q1[b1 + i] - 33;
+        for (int i = lane; i < l2; i += 32) sum += (int)q2[b2 + i] - 33;
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        // UID bases: lane i < u reads R1[i], lane u <= i < u+v reads R2[i-u]   (u + v <= 32)
+        uint64_t code = 0;
+        bool bad = false, short_read = false;
+        if (lane < u + v) {
+            uint8_t ch;
+            if (lane < u) { short_read = lane >= l1; ch = short_read ? 'A' : r1[b1 + lane]; }
+            else { short_read = (lane - u) >= l2; ch = short_read ? 'A' : r2[b2 + lane - u]; }
+            switch (ch) {
+                case 'A': code = 0; break;
+                case 'C': code = 1; break;
+                case 'G': code = 2; break;
+                case 'T': code = 3; break;
+                default: bad = true;
+            }
+            code <<= 2 * (u + v - 1 - lane);
+        }
+        for (int o = 16; o > 0; o >>= 1) code |= __shfl_xor_sync(0xffffffffu, code, o);
+        if (__any_sync(0xffffffffu, short_read)) { if (lane == 0) atomicMin(status, HSQ_ERR_OUT_OF_RANGE); }
+        else if (__any_sync(0xffffffffu, bad)) { if (lane == 0) atomicMin(status, HSQ_ERR_UNSUPPORTED); }
+        if (lane == 0) {
+            const int16_t qsum = (int16_t)sum;  // Java short arithmetic wraps mod 2^16
+            uid_out[w] = code;
+            rank_out[w] = ((uint64_t)(uint16_t)(32767 - (int)qsum) << 32) | (uint64_t)((uint32_t)read_index[w] ^ 0x80000000u);
+            idx_out[w] = (uint32_t)w;
+        }
+    }
+}
+
+template <class T>
+__global__ void gather_u64_kernel(const T* __restrict__ src, const uint32_t* __restrict__ idx, int64_t n, uint64_t* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) out[i] = (uint64_t)src[idx[i]];
+}
+
+// sorted position i holds pair idx[i]; a head starts a (probe, UID) group and is its best pair
+__global__ void dedup_heads_kernel(const uint32_t* __restrict__ idx, const int32_t* __restrict__ probe, const uint64_t* __restrict__ uid,
+                                   int64_t n, uint8_t* __restrict__ head, uint8_t* __restrict__ is_best) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        const uint32_t p = idx[i];
+        bool h = true;
+        if (i > 0) {
+            const uint32_t pp = idx[i - 1];
+            h = probe[p] != probe[pp] || uid[p] != uid[pp];
+        }
+        head[i] = h ? 1 : 0;
+        is_best[p] = h ? 1 : 0;
+    }
+}
+
+// each head walks its group: size -> every member, per-probe counters (FilterByUid.java:149-171,251)
+__global__ void dedup_groups_kernel(const uint32_t* __restrict__ idx, const int32_t* __restrict__ probe, const uint8_t* __restrict__ head,
+                                    int64_t n, int32_t* __restrict__ group_size, int32_t* __restrict__ unique_pairs,
+                                    int32_t* __restrict__ duplicate_pairs, int32_t* __restrict__ max_pairs) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        if (!head[i]) continue;
+        int64_t e = i + 1;
+        while (e < n && !head[e]) e++;
+        const int size = (int)(e - i);
+        for (int64_t k = i; k < e; k++) group_size[idx[k]] = size;
+        const int pr = probe[idx[i]];
+        atomicAdd(&unique_pairs[pr], 1);
+        if (size > 1) atomicAdd(&duplicate_pairs[pr], size - 1);
+        atomicMax(&max_pairs[pr], size);
+    }
+}
+
+inline int bits_for(uint64_t max_value) {
+    int b = 1;
+    while (b < 64 && (max_value >> b) != 0) b++;
+    return b;
+}
+
+}  // namespace hsq
+
+namespace {
+
+int sort_pass(hsq_ctx* ctx, const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out, int64_t n, int end_bit) {
+    size_t tmp_bytes = 0;
+    HSQ_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, end_bit, ctx->stream));
+    HSQ_CUDA(ctx, ctx->sort_tmp.ensure(tmp_bytes + 16));
+    HSQ_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, end_bit, ctx->stream));
+    ctx->launches += (end_bit + 7) / 8 + 2;  // library kernels (approximate; they are not counted as ours in bench.py)
+    return HSQ_OK;
+}
+
+int run_dedup(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, uint8_t* is_best, int32_t* group_size, hsq_probe_stats* stats) {
+    const int64_t n = pb->n;
+    const size_t nn = (size_t)n;
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    // raw bytes: UID grouping is on the read strings themselves, qualities are summed as chars
+    struct { hsq::DevBuf* d; const void* h; size_t bytes; } up[] = {
+        {&ctx->r1.ascii, pb->r1.data, (size_t)pb->r1.offsets[n]}, {&ctx->r2.ascii, pb->r2.data, (size_t)pb->r2.offsets[n]},
+        {&ctx->q1, pb->q1, (size_t)pb->r1.offsets[n]},            {&ctx->q2, pb->q2, (size_t)pb->r2.offsets[n]},
+        {&ctx->r1.offsets, pb->r1.offsets, (nn + 1) * 8},         {&ctx->r2.offsets, pb->r2.offsets, (nn + 1) * 8},
+        {&ctx->probe_id, pb->probe_id, nn * 4},                   {&ctx->read_index, pb->read_index, nn * 4}};
+    for (auto& c : up) {
+        if (c.bytes && !c.h) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_dedup_batch: null input array");
+        HSQ_CUDA(ctx, c.d->ensure(c.bytes + 16));
+        if (c.bytes) HSQ_CUDA(ctx, cudaMemcpyAsync(c.d->p, c.h, c.bytes, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    const int64_t np = stats ? stats->n_probes : 0;
+    HSQ_CUDA(ctx, ctx->sort_a.ensure(nn * 8 + 16));   // uid per pair
+    HSQ_CUDA(ctx, ctx->sort_b.ensure(nn * 8 + 16));   // keys ping
+    HSQ_CUDA(ctx, ctx->sort_c.ensure(nn * 8 + 16));   // keys pong
+    HSQ_CUDA(ctx, ctx->sort_d.ensure(nn * 8 + 16));   // idx ping | idx pong (2 x u32)
+    HSQ_CUDA(ctx, ctx->flags.ensure(2 * nn + 32));    // head | is_best
+    HSQ_CUDA(ctx, ctx->out_i32.ensure((nn + 3 * (size_t)np) * 4 + 16));
+    uint64_t* uid = ctx->sort_a.as<uint64_t>();
+    uint64_t* ka = ctx->sort_b.as<uint64_t>();
+    uint64_t* kb = ctx->sort_c.as<uint64_t>();
+    uint32_t* ia = ctx->sort_d.as<uint32_t>();
+    uint32_t* ib = ia + nn;
+    uint8_t* head = ctx->flags.as<uint8_t>();
+    uint8_t* best = head + nn + 16;
+    int32_t* d_gs = ctx->out_i32.as<int32_t>();
+    int32_t* d_stats = d_gs + nn;
+    if (np) HSQ_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 3 * (size_t)np * 4, ctx->stream));
+    if (n > 0) {
+        const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
+        const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        check_probe_ids_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, np > 0 ? np : INT32_MAX, d_status(ctx));
+        dedup_keygen_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), ctx->q1.as<uint8_t>(),
+                                                            ctx->r2.ascii.as<uint8_t>(), ctx->r2.offsets.as<int64_t>(), ctx->q2.as<uint8_t>(),
+                                                            ctx->read_index.as<int32_t>(), n, u, v, uid, ka, ia, d_status(ctx));
+        ctx->launches += 2;
+        int w[1];
+        if ((rc = read_status(ctx, w, 1))) return rc;
+        if (w[0] != 0)
+            return fail(ctx, w[0], w[0] == HSQ_ERR_UNSUPPORTED ? "hsq_dedup_batch: a UID holds a character other than A,C,G,T (filter N reads first, "
+                                                                 "PrimerReadExtensionAndPcrDuplicateIdentification.java:815-821)"
+                                   : w[0] == HSQ_ERR_INVALID_ARGUMENT ? "hsq_dedup_batch: probe_id out of range"
+                                                                      : "hsq_dedup_batch: a read is shorter than its UID");
+        // pass 1: by rank (48 bits) -> ib;  pass 2: by UID -> ia;  pass 3: by probe -> ib
+        if ((rc = sort_pass(ctx, ka, kb, ia, ib, n, 48))) return rc;
+        if (u + v > 0) {
+            gather_u64_kernel<uint64_t><<<gblocks, 256, 0, ctx->stream>>>(uid, ib, n, ka);
+            ctx->launches++;
+            if ((rc = sort_pass(ctx, ka, kb, ib, ia, n, 2 * (u + v)))) return rc;
+        } else {
+            HSQ_CUDA(ctx, cudaMemcpyAsync(ia, ib, nn * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        }
+        gather_u64_kernel<int32_t><<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), ia, n, ka);
+        ctx->launches++;
+        if ((rc = sort_pass(ctx, ka, kb, ia, ib, n, bits_for((uint64_t)std::max<int64_t>(np, 1))))) return rc;
+        dedup_heads_kernel<<<gblocks, 256, 0, ctx->stream>>>(ib, ctx->probe_id.as<int32_t>(), uid, n, head, best);
+        dedup_groups_kernel<<<gblocks, 256, 0, ctx->stream>>>(ib, ctx->probe_id.as<int32_t>(), head, n, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
+        ctx->launches += 2;
+        HSQ_CUDA(ctx, cudaGetLastError());
+    }
+    if ((rc = d2h(ctx, is_best, best, nn))) return rc;
+    if ((rc = d2h(ctx, group_size, d_gs, nn))) return rc;
+    if (stats && np) {
+        if ((rc = d2h(ctx, stats->unique_pairs, d_stats, (size_t)np))) return rc;
+        if ((rc = d2h(ctx, stats->duplicate_pairs, d_stats + np, (size_t)np))) return rc;
+        if ((rc = d2h(ctx, stats->max_pairs_per_uid, d_stats + 2 * np, (size_t)np))) return rc;
+    }
+    return HSQ_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_dedup_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len, uint8_t* is_best,
+                                   int32_t* group_size, hsq_probe_stats* stats) {
+    if (!ctx || !pairs || !is_best) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (pairs->n < 0 || pairs->r1.n != pairs->n || pairs->r2.n != pairs->n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
+    if (ext_uid_len < 0 || lig_uid_len < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative UID length");
+    if (ext_uid_len + lig_uid_len > 32) return fail(ctx, HSQ_ERR_UNSUPPORTED, "UID longer than 32 bases in total is outside the accelerated domain");
+    if (!stats || stats->n_probes <= 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe stats (with n_probes) are required");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = run_dedup(ctx, pairs, ext_uid_len, lig_uid_len, is_best, group_size, stats);
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}

@@ -1,0 +1,119 @@
+// hsq_capi_extend.inl -- hsq_extend_batch: ExtendReadsToPrimer.extendReadsToPrimers for a batch spanning probes.
+namespace {
+
+__global__ void check_probe_ids_kernel(const int32_t* __restrict__ probe_id, int64_t n, int64_t n_probes, int* status) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride)
+        if (probe_id[k] < 0 || probe_id[k] >= n_probes) atomicMin(status, HSQ_ERR_INVALID_ARGUMENT);
+}
+
+int upload_pairs(hsq_ctx* ctx, const hsq_pair_batch* pb, bool need_quals, bool need_index) {
+    int rc;
+    const size_t n = (size_t)pb->n;
+    if (pb->r1.n != pb->n || pb->r2.n != pb->n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
+    if (n && !pb->probe_id) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe_id is null");
+    HSQ_CUDA(ctx, ctx->probe_id.ensure(n * 4 + 16));
+    if (n) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->probe_id.p, pb->probe_id, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = upload_seqs(ctx, &pb->r1, &ctx->r1, d_status(ctx), d_maxlen(ctx, 0)))) return rc;
+    if ((rc = upload_seqs(ctx, &pb->r2, &ctx->r2, d_status(ctx), d_maxlen(ctx, 1)))) return rc;
+    if (need_quals) {
+        if (n && (!pb->q1 || !pb->q2)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "quality strings are required");
+        HSQ_CUDA(ctx, ctx->q1.ensure((size_t)ctx->r1.total + 16));
+        HSQ_CUDA(ctx, ctx->q2.ensure((size_t)ctx->r2.total + 16));
+        if (ctx->r1.total) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q1.p, pb->q1, (size_t)ctx->r1.total, cudaMemcpyHostToDevice, ctx->stream));
+        if (ctx->r2.total) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q2.p, pb->q2, (size_t)ctx->r2.total, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (need_index) {
+        if (n && !pb->read_index) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "read_index is required");
+        HSQ_CUDA(ctx, ctx->read_index.ensure(n * 4 + 16));
+        if (n) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->read_index.p, pb->read_index, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    return HSQ_OK;
+}
+
+int run_extend(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o) {
+    const int64_t n = pb->n;
+    const size_t n2 = (size_t)(2 * n);
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    if ((rc = upload_pairs(ctx, pb, false, false))) return rc;
+    if (n > 0) {
+        int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+        check_probe_ids_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, ctx->n_probes, d_status(ctx));
+        ctx->launches++;
+    }
+    int w[3];
+    if ((rc = read_status(ctx, w, 3))) return rc;
+    if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend_batch: ") + (w[0] == HSQ_ERR_INVALID_ARGUMENT ? "probe_id out of range" : status_message(w[0])));
+    const int read_max = std::max(w[1], w[2]);
+    const int primer_max = std::max(ctx->p_ext.max_len, ctx->p_lig.max_len);
+    if (2 * primer_max + PRIMER_ALIGNMENT_BUFFER + 2 > POW95_N) return fail(ctx, HSQ_ERR_UNSUPPORTED, "primer longer than the 0.95^d table supports");
+    // DP#1: rows = primer, cols = read prefix (<= primer+26); DP#2: rows = read remainder, cols = capture target
+    const int q_max = std::max(primer_max, read_max);
+    const int r_max = std::max(ctx->p_target.max_len, std::min(read_max, primer_max + PRIMER_ALIGNMENT_BUFFER + 1));
+    ScoreParams sp_default = make_score_params(1, -4, -1, -6);  // SimpleAlignmentScorer defaults (ExtendReadsToPrimer.java:290-291)
+    ScoreParams sp_user = make_score_params(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start);
+    int grid = 1;
+    if (sp_user.lut_ok) rc = persistent_grid(ctx, extend_kernel<true>, 128, 2 * n, &grid);
+    else rc = persistent_grid(ctx, extend_kernel<false>, 128, 2 * n, &grid);
+    if (rc) return rc;
+    ScratchPool pool;
+    if ((rc = alloc_scratch(ctx, (int64_t)grid * 128, q_max, r_max, &pool))) return rc;
+    HSQ_CUDA(ctx, ctx->out_i32.ensure(10 * n2 * sizeof(int32_t) + 16));
+    HSQ_CUDA(ctx, ctx->out_u8.ensure(2 * n2 + 16));
+    HSQ_CUDA(ctx, ctx->out_slots.ensure(n2 * ((size_t)o->cigar_cap + (size_t)o->md_cap) + 16));
+    HSQ_CUDA(ctx, ctx->pair_ok.ensure((size_t)n + 16));
+    int32_t* i32 = ctx->out_i32.as<int32_t>();
+    ExtendDeviceOut d;
+    d.cigar_cap = o->cigar_cap;
+    d.md_cap = o->md_cap;
+    d.primer_end = i32; d.score = i32 + n2; d.pos = i32 + 2 * n2; d.read_start = i32 + 3 * n2; d.read_stop = i32 + 4 * n2;
+    d.nm = i32 + 5 * n2; d.tlen = i32 + 6 * n2; d.cigar_len = i32 + 7 * n2; d.md_len = i32 + 8 * n2; d.ref_len = i32 + 9 * n2;
+    d.ok = ctx->out_u8.as<uint8_t>();
+    d.overflow = d.ok + n2;
+    d.cigar = ctx->out_slots.as<uint8_t>();
+    d.md = d.cigar + n2 * (size_t)o->cigar_cap;
+    if (n > 0) {
+        DeviceProbes pv = probe_view(ctx);
+        if (sp_user.lut_ok)
+            extend_kernel<true><<<grid, 128, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), n, sp_default,
+                                                             sp_user, pool, d, d_status(ctx), ctx->cells.as<unsigned long long>());
+        else
+            extend_kernel<false><<<grid, 128, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), n, sp_default,
+                                                              sp_user, pool, d, d_status(ctx), ctx->cells.as<unsigned long long>());
+        ctx->launches++;
+        HSQ_CUDA(ctx, cudaGetLastError());
+        finalize_extend_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), n, d,
+                                                                                     ctx->pair_ok.as<uint8_t>(), d_status(ctx));
+        ctx->launches++;
+        HSQ_CUDA(ctx, cudaGetLastError());
+    }
+    int32_t* hosts[9] = {o->primer_end, o->score, o->pos, o->read_start, o->read_stop, o->nm, o->tlen, o->cigar_len, o->md_len};
+    for (int f = 0; f < 9; f++)
+        if ((rc = d2h(ctx, hosts[f], i32 + f * n2, n2))) return rc;
+    if ((rc = d2h(ctx, o->ok, d.ok, n2))) return rc;
+    if ((rc = d2h(ctx, o->overflow, d.overflow, n2))) return rc;
+    if ((rc = d2h(ctx, o->cigar, d.cigar, n2 * (size_t)o->cigar_cap))) return rc;
+    if ((rc = d2h(ctx, o->md, d.md, n2 * (size_t)o->md_cap))) return rc;
+    if ((rc = d2h(ctx, o->pair_ok, ctx->pair_ok.as<uint8_t>(), (size_t)n))) return rc;
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if ((rc = read_status(ctx, w, 1))) return rc;
+    o->cells = (int64_t)ctx->h_cells[0];
+    if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend_batch: ") + status_message(w[0]));
+    return HSQ_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, hsq_extend_out* out) {
+    if (!ctx || !pairs || !out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (!ctx->have_probes) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_set_probes has not been called");
+    if (!ctx->have_scorer) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_set_scorer has not been called");
+    if (pairs->n < 0 || out->cigar_cap < 0 || out->md_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = run_extend(ctx, pairs, out);
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}

@@ -1,0 +1,101 @@
+// hsq_capi_trim.inl -- hsq_trim_batch: FastqReadTrimmer.trim (HSQ/process/FastqReadTrimmer.java:309-328) per read.
+#include "hsq_scan.cuh"
+namespace hsq {
+
+// kept length per read; flags the reads for which Java throws (first >= length, or substring end < begin)
+__global__ void trim_len_kernel(const int64_t* __restrict__ offsets, int64_t n, int first, int last, int three_prime,
+                                int64_t* __restrict__ keep, int* status) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride) {
+        int len = (int)(offsets[k + 1] - offsets[k]);
+        int lb = len - 1;
+        if (three_prime) lb = min(last, len - 1);  // :319-322
+        int kp = lb + 1 - first;
+        if (first >= len || kp < 0) {  // :310-312 IllegalArgumentException / String.substring bounds
+            atomicMin(status, HSQ_ERR_OUT_OF_RANGE);
+            kp = 0;
+        }
+        keep[k] = kp;
+    }
+}
+
+// One warp per read: copies bases and qualities of [first, first+keep) to the packed outputs.
+__global__ void trim_copy_kernel(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, const int64_t* __restrict__ offsets,
+                                 const int64_t* __restrict__ out_offsets, int64_t n, int first, uint8_t* __restrict__ out_seq,
+                                 uint8_t* __restrict__ out_qual) {
+    const int lane = threadIdx.x & 31;
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; w < n; w += stride) {
+        const int64_t src = offsets[w] + first, dst = out_offsets[w];
+        const int keep = (int)(out_offsets[w + 1] - dst);
+        for (int i = lane; i < keep; i += 32) {
+            out_seq[dst + i] = seq[src + i];
+            out_qual[dst + i] = qual[src + i];
+        }
+    }
+}
+
+}  // namespace hsq
+
+extern "C" int32_t hsq_trim_batch(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int32_t first, int32_t last,
+                                  int32_t three_prime, uint8_t* out_seq, uint8_t* out_qual, int64_t* out_offsets) {
+    if (!ctx || !reads || !reads->offsets || !out_offsets) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (first < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "first base to keep must be >= 0");  // FastqReadTrimmer.java:263-265
+    const int64_t n = reads->n;
+    const int64_t total = reads->offsets[n];
+    if (total > 0 && (!reads->data || !quals || !out_seq || !out_qual)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null buffer");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    // raw bytes only: trim never decodes bases
+    HSQ_CUDA(ctx, ctx->r1.ascii.ensure((size_t)total + 16));
+    HSQ_CUDA(ctx, ctx->q1.ensure((size_t)total + 16));
+    HSQ_CUDA(ctx, ctx->r1.offsets.ensure((size_t)(n + 1) * 8));
+    HSQ_CUDA(ctx, ctx->sort_a.ensure((size_t)(n + 1) * 8));  // keep lengths
+    HSQ_CUDA(ctx, ctx->sort_b.ensure((size_t)(n + 1) * 8));  // out offsets
+    const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
+    HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)n_tiles * 8 + 16));
+    HSQ_CUDA(ctx, ctx->out_slots.ensure(2 * (size_t)total + 32));
+    if (total) {
+        HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->r1.ascii.p, reads->data, (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+        HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q1.p, quals, (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->r1.offsets.p, reads->offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+    int64_t* keep = ctx->sort_a.as<int64_t>();
+    int64_t* d_out_off = ctx->sort_b.as<int64_t>();
+    uint8_t* d_out_seq = ctx->out_slots.as<uint8_t>();
+    uint8_t* d_out_qual = d_out_seq + total + 16;
+    if (n > 0) {
+        int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+        trim_len_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.offsets.as<int64_t>(), n, first, last, three_prime, keep, d_status(ctx));
+        ctx->launches++;
+    }
+    scan_tile_sums_kernel<<<(unsigned)n_tiles, SCAN_BLOCK, 0, ctx->stream>>>(keep, n, ctx->sort_c.as<int64_t>());
+    scan_sums_kernel<<<1, SCAN_BLOCK, 0, ctx->stream>>>(ctx->sort_c.as<int64_t>(), n_tiles);
+    scan_apply_kernel<<<(unsigned)n_tiles, SCAN_BLOCK, 0, ctx->stream>>>(keep, n, ctx->sort_c.as<int64_t>(), d_out_off);
+    ctx->launches += 3;
+    if (n > 0) {
+        int64_t warps = n;
+        int blocks = (int)std::min<int64_t>((warps * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
+        trim_copy_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->q1.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(),
+                                                         d_out_off, n, first, d_out_seq, d_out_qual);
+        ctx->launches++;
+    }
+    HSQ_CUDA(ctx, cudaGetLastError());
+    HSQ_CUDA(ctx, cudaMemcpyAsync(out_offsets, d_out_off, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    int w[1];
+    if ((rc = read_status(ctx, w, 1))) return rc;
+    if (w[0] != 0) {
+        timer.finish();
+        return fail(ctx, w[0], "hsq_trim_batch: unable to trim: first base to keep is beyond the end of a read");
+    }
+    const int64_t out_total = out_offsets[n];
+    if (out_total) {
+        HSQ_CUDA(ctx, cudaMemcpyAsync(out_seq, d_out_seq, (size_t)out_total, cudaMemcpyDeviceToHost, ctx->stream));
+        HSQ_CUDA(ctx, cudaMemcpyAsync(out_qual, d_out_qual, (size_t)out_total, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    return timer.finish();
+}

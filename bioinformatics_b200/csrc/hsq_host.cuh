@@ -1,0 +1,122 @@
+// hsq_host.cuh -- host-side plumbing shared by the C ABI entry points: context, grow-only device buffers,
+// error capture.  No compute.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include <cstdio>
+#include "hsq_kernels.cuh"
+
+namespace hsq {
+
+struct DevBuf {  // grow-only device allocation reused across batch calls
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 8 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct DevSeqsOwned {  // encoded ragged batch resident on the device
+    DevBuf ascii, codes, offsets;
+    int64_t n = 0, total = 0;
+    int max_len = 0;
+    DeviceSeqs view() const { return DeviceSeqs{codes.as<uint8_t>(), offsets.as<int64_t>()}; }
+    void release() { ascii.release(); codes.release(); offsets.release(); }
+};
+
+}  // namespace hsq
+
+struct hsq_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::string error;
+    float last_kernel_ms = 0.f;
+    int last_launches = 0;
+    int launches = 0;  // running count inside a call
+    bool have_scorer = false, have_probes = false;
+    hsq_scorer scorer{1, -4, -1, -6};
+    // probe table
+    int64_t n_probes = 0;
+    hsq::DevBuf p_rev, p_ext_start, p_ext_stop, p_lig_start, p_lig_stop;
+    hsq::DevSeqsOwned p_ext, p_lig, p_target, p_full;  // p_full = ext ++ target ++ lig (Probe.getProbeSequence)
+    // batch inputs
+    hsq::DevSeqsOwned r1, r2, sa, sb;
+    hsq::DevBuf q1, q2, probe_id, read_index;
+    // scratch + outputs
+    hsq::DevBuf ptr_words, brow, cols, status, cells, misc, out_i32, out_u8, out_slots, pair_ok;
+    hsq::DevBuf sort_a, sort_b, sort_c, sort_d, sort_tmp, flags;
+    int* h_status = nullptr;  // pinned
+    unsigned long long* h_cells = nullptr;
+};
+
+namespace hsq {
+
+static thread_local std::string g_create_error;
+
+inline int fail(hsq_ctx* ctx, int code, const std::string& msg) {
+    if (ctx) ctx->error = msg;
+    else g_create_error = msg;
+    return code;
+}
+
+#define HSQ_CUDA(ctx, expr)                                                                               \
+    do {                                                                                                  \
+        cudaError_t _e = (expr);                                                                          \
+        if (_e != cudaSuccess)                                                                            \
+            return hsq::fail(ctx, HSQ_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));    \
+    } while (0)
+
+inline const char* status_message(int st) {
+    switch (st) {
+        case HSQ_ERR_BAD_CHARACTER: return "a sequence holds a character that is not an IUPAC nucleotide code";
+        case HSQ_ERR_OUT_OF_RANGE: return "index out of range (the reference would throw here)";
+        case HSQ_ERR_OVERFLOW: return "an output slot was too small; see the overflow flags";
+        case HSQ_ERR_UNSUPPORTED: return "input outside the accelerated domain";
+        default: return "error";
+    }
+}
+
+// Copies a host ragged ASCII batch to the device and encodes it.  max_len is read back lazily by the caller.
+inline int upload_seqs(hsq_ctx* ctx, const hsq_seqs* s, DevSeqsOwned* d, int* d_status, int* d_maxlen /*device int or null*/) {
+    if (!s || s->n < 0 || !s->offsets) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null sequence batch");
+    d->n = s->n;
+    d->total = s->offsets[s->n] - s->offsets[0];
+    if (s->offsets[0] != 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "offsets must start at 0");
+    if (d->total < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative batch size");
+    HSQ_CUDA(ctx, d->ascii.ensure((size_t)d->total + 16));
+    HSQ_CUDA(ctx, d->codes.ensure((size_t)d->total + 16));
+    HSQ_CUDA(ctx, d->offsets.ensure((size_t)(s->n + 1) * sizeof(int64_t)));
+    if (d->total > 0) HSQ_CUDA(ctx, cudaMemcpyAsync(d->ascii.p, s->data, (size_t)d->total, cudaMemcpyHostToDevice, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(d->offsets.p, s->offsets, (size_t)(s->n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+    if (d->total > 0) {
+        int64_t threads = (d->total + 15) / 16;
+        int blocks = (int)std::min<int64_t>((threads + 255) / 256, (int64_t)ctx->sm_count * 16);
+        encode_kernel<<<blocks, 256, 0, ctx->stream>>>(d->ascii.as<uint8_t>(), d->codes.as<uint8_t>(), d->total, d_status);
+        ctx->launches++;
+    }
+    if (d_maxlen && s->n > 0) {
+        int blocks = (int)std::min<int64_t>((s->n + 255) / 256, (int64_t)ctx->sm_count * 8);
+        max_len_kernel<<<blocks, 256, 0, ctx->stream>>>(d->offsets.as<int64_t>(), s->n, d_maxlen);
+        ctx->launches++;
+    }
+    return HSQ_OK;
+}
+
+}  // namespace hsq

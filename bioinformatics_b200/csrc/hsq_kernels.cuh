@@ -1,0 +1,280 @@
+// hsq_kernels.cuh -- sm_100a kernels of the HSQUtils hot path (one alignment task per thread, persistent grid).
+#pragma once
+#include <stdint.h>
+#include "hsq_emit.cuh"
+#include "../../include/hsq_b200.h"
+
+namespace hsq {
+
+static constexpr int POW95_N = 2048;
+__constant__ double c_pow95[POW95_N];  // Math.pow(0.95, d), filled by the host with pow() (ExtendReadsToPrimer.java:326)
+
+static constexpr int PRIMER_ALIGNMENT_BUFFER = 25;             // HSQ/process/ExtendReadsToPrimer.java:54
+static constexpr int LENGTH_THRESHOLD_FOR_EXTENDED_READ = 10;  // :56
+static constexpr double WEIGHTED_ALIGNMENT_SCORE_THRESHOLD = 4.0;  // :58
+
+// ---------------------------------------------------------------------------------------------
+// ASCII -> device codes; 16 bytes per thread.  HBM-bound: 1 B read + 1 B written per base.
+// ---------------------------------------------------------------------------------------------
+__global__ void encode_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int64_t n, int* __restrict__ status) {
+    int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * 16;
+    bool bad = false;
+    for (; i < n; i += stride) {
+        if (i + 16 <= n) {
+            uint4 v = *reinterpret_cast<const uint4*>(in + i);
+            uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                uint32_t o = 0;
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    uint8_t c = encode_ascii((uint8_t)(w[k] >> (8 * b)));
+                    bad |= (c == CODE_BAD);
+                    o |= (uint32_t)c << (8 * b);
+                }
+                w[k] = o;
+            }
+            *reinterpret_cast<uint4*>(out + i) = make_uint4(w[0], w[1], w[2], w[3]);
+        } else {
+            for (int64_t k = i; k < n; k++) {
+                uint8_t c = encode_ascii(in[k]);
+                bad |= (c == CODE_BAD);
+                out[k] = c;
+            }
+        }
+    }
+    if (bad) atomicMin(status, HSQ_ERR_BAD_CHARACTER);
+}
+
+// max element length of a ragged batch (offsets has n+1 entries)
+__global__ void max_len_kernel(const int64_t* __restrict__ offsets, int64_t n, int* __restrict__ out_max) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int mx = 0;
+    for (; i < n; i += stride) mx = max(mx, (int)(offsets[i + 1] - offsets[i]));
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0 && mx > 0) atomicMax(out_max, mx);
+}
+
+struct DeviceSeqs {
+    const uint8_t* codes;
+    const int64_t* offsets;
+};
+
+struct DeviceProbes {
+    const uint8_t* reverse_strand;
+    const int32_t *ext_start, *ext_stop, *lig_start, *lig_stop;
+    DeviceSeqs ext, lig, target;
+};
+
+struct ExtendDeviceOut {
+    int32_t cigar_cap, md_cap;
+    uint8_t* ok;
+    int32_t *primer_end, *score, *pos, *read_start, *read_stop, *nm, *tlen, *cigar_len, *md_len, *ref_len;
+    uint8_t *cigar, *md, *overflow;
+};
+
+struct ScratchPool {
+    uint32_t* ptr_words;
+    int32_t* brow;
+    uint16_t* cols;
+    int r_stride;
+};
+
+__device__ inline DpScratch thread_scratch(const ScratchPool& pool) {
+    DpScratch sc;
+    sc.ptr_words = pool.ptr_words;
+    sc.brow = pool.brow;
+    sc.cols = pool.cols;
+    sc.nthreads = (int64_t)gridDim.x * blockDim.x;
+    sc.tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    sc.r_stride = pool.r_stride;
+    return sc;
+}
+
+// getPrimerEndIndexInRead (HSQ/process/ExtendReadsToPrimer.java:286-345)
+template <bool LUT>
+__device__ inline int primer_end_index(const SeqView& primer, const SeqView& read, const ScoreParams& sp_default,
+                                       const DpScratch& sc, int* status, int64_t* cells) {
+    int L = read.len;
+    SeqView prefix = sub_view(read, 0, min(L, primer.len + PRIMER_ALIGNMENT_BUFFER + 1));  // [0 .. min(L-1, p+25)] inclusive (:288)
+    if (primer.len == 0) {  // Java: IndexOutOfBounds at :299 (all-gap primer alignment)
+        atomicMin(status, HSQ_ERR_OUT_OF_RANGE);
+        return HSQ_PRIMER_NOT_FOUND;
+    }
+    dp_fill<LUT>(prefix, primer, sp_default, /*pen_start=*/1, /*pen_end=*/0, sc);  // ref = read prefix, query = primer (:290-293)
+    *cells += (int64_t)prefix.len * primer.len;
+    int n = dp_traceback(prefix, primer, sc);
+    bool passed = false;
+    int pe = 0, first = -1;
+    double w = 0.0;
+    for (int i = 0; i < n; i++) {  // stored order == the reversed alignments of :305-333
+        uint32_t c = sc.col(i);
+        uint32_t rc = col_ref(c), pc = col_qry(c);
+        if (!passed && pc != CODE_GAP) { passed = true; first = i; }
+        if (passed && rc != CODE_GAP) {
+            pe++;
+            if (codes_match(rc, pc)) w += c_pow95[i - first];
+        }
+    }
+    if (w < WEIGHTED_ALIGNMENT_SCORE_THRESHOLD) return HSQ_PRIMER_NOT_FOUND;
+    return pe - 1;
+}
+
+// One read end per thread: ExtendReadsToPrimer.extendReadPair strand logic (:96-198) +
+// calculateDetailsForReadExtensionToPrimer (:200-245).
+template <bool LUT_USER>
+__global__ void __launch_bounds__(128) extend_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
+                                                     DeviceSeqs r2, int64_t n_pairs, ScoreParams sp_default, ScoreParams sp_user,
+                                                     ScratchPool pool, ExtendDeviceOut out, int* status,
+                                                     unsigned long long* cells_total) {
+    DpScratch sc = thread_scratch(pool);
+    int64_t cells = 0;
+    const int64_t n_tasks = 2 * n_pairs;
+    for (int64_t m = sc.tid; m < n_tasks; m += sc.nthreads) {
+        const int64_t k = m >> 1;
+        const int mate = (int)(m & 1);
+        const int pid = probe_id[k];
+        const bool one_rev = probes.reverse_strand[pid] != 0;
+        SeqView primer, capture, read;
+        bool is_reversed;
+        int adjacent;
+        {
+            int64_t t0 = probes.target.offsets[pid];
+            int tl = (int)(probes.target.offsets[pid + 1] - t0);
+            if (mate == 0) {  // :114-126
+                int64_t p0 = probes.ext.offsets[pid];
+                primer = make_view(probes.ext.codes + p0, (int)(probes.ext.offsets[pid + 1] - p0), false, one_rev);
+                capture = make_view(probes.target.codes + t0, tl, false, one_rev);
+                int64_t s0 = r1.offsets[k];
+                read = make_view(r1.codes + s0, (int)(r1.offsets[k + 1] - s0), false, one_rev);
+                is_reversed = one_rev;
+                adjacent = one_rev ? probes.ext_start[pid] : probes.ext_stop[pid];  // :108-112
+            } else {  // :150-162 (sequenceTwo was complemented at :104)
+                int64_t p0 = probes.lig.offsets[pid];
+                primer = make_view(probes.lig.codes + p0, (int)(probes.lig.offsets[pid + 1] - p0), true, one_rev);
+                capture = make_view(probes.target.codes + t0, tl, true, one_rev);
+                int64_t s0 = r2.offsets[k];
+                read = make_view(r2.codes + s0, (int)(r2.offsets[k + 1] - s0), false, !one_rev);
+                is_reversed = !one_rev;
+                adjacent = one_rev ? probes.lig_stop[pid] : probes.lig_start[pid];  // :137,:143 (finalize_kernel restores the :133 quirk)
+            }
+        }
+        int ok = 0, score = 0, pos = 0, read_start = 0, read_stop = 0, nm = 0, ref_len = 0;
+        SlotWriter cw{out.cigar + m * out.cigar_cap, out.cigar_cap, 0};
+        SlotWriter mw{out.md + m * out.md_cap, out.md_cap, 0};
+        const int L = read.len;
+        int e = primer_end_index<true>(primer, read, sp_default, sc, status, &cells);
+        if (e != HSQ_PRIMER_NOT_FOUND && e >= 0 && e < L) {  // :206
+            const int start = e + 1;
+            SeqView rw = sub_view(read, start, L - start);  // read[e+1 .. L-1] (:210)
+            score = dp_fill<LUT_USER>(capture, rw, sp_user, 0, 0, sc);  // :211
+            cells += (int64_t)capture.len * rw.len;
+            const int read_length = rw.len - 1;  // :225
+            // score/alignmentLength > 0 (:212): the alignment has max(Q,R) >= 1 columns whenever score != 0
+            if (score > 0 && read_length > LENGTH_THRESHOLD_FOR_EXTENDED_READ) {
+                Columns cv{sc, dp_traceback(capture, rw, sc)};
+                int last_q = cv.n - 1;  // getAlignmentWithoutEndingQueryInserts (:218)
+                while (last_q >= 0 && col_qry(cv.fwd(last_q)) == CODE_GAP) last_q--;
+                emit_cigar_md(cv, 0, last_q, is_reversed, &cw, &mw, &nm, &ref_len);  // :220-231
+                pos = is_reversed ? adjacent - ref_len : adjacent + 1;                 // :234,:236
+                read_start = start;
+                read_stop = start + read_length;
+                ok = 1;
+            }
+        }
+        out.ok[m] = (uint8_t)ok;
+        out.primer_end[m] = e;
+        out.score[m] = score;
+        out.pos[m] = pos;
+        out.read_start[m] = read_start;
+        out.read_stop[m] = read_stop;
+        out.nm[m] = nm;
+        out.ref_len[m] = ref_len;
+        out.cigar_len[m] = cw.len;
+        out.md_len[m] = mw.len;
+        out.overflow[m] = (uint8_t)((cw.len > cw.cap ? 1 : 0) | (mw.len > mw.cap ? 2 : 0));
+    }
+    for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
+    if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
+}
+
+// Per pair: both-mates flag (ExtendReadsToPrimer.java:364), TLEN (:136-142,:168-178), and the reference's quirk that
+// read two's adjacent primer position is only switched to the ligation primer when read one extended (:133-144).
+__global__ void finalize_extend_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, int64_t n_pairs,
+                                       ExtendDeviceOut out, uint8_t* __restrict__ pair_ok, int* status) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_pairs) return;
+    const int pid = probe_id[k];
+    const bool one_rev = probes.reverse_strand[pid] != 0;
+    const int tl = (int)(probes.target.offsets[pid + 1] - probes.target.offsets[pid]);
+    const bool ok1 = out.ok[2 * k] != 0, ok2 = out.ok[2 * k + 1] != 0;
+    out.tlen[2 * k] = ok1 ? (one_rev ? -tl : tl) : 0;
+    out.tlen[2 * k + 1] = ok2 ? (!one_rev ? -tl : tl) : 0;
+    if (!ok1 && ok2) {
+        int adjacent = one_rev ? probes.ext_start[pid] : probes.ext_stop[pid];
+        out.pos[2 * k + 1] = (!one_rev) ? adjacent - out.ref_len[2 * k + 1] : adjacent + 1;
+    }
+    pair_ok[k] = (ok1 && ok2) ? 1 : 0;
+    if ((out.overflow[2 * k] | out.overflow[2 * k + 1]) != 0) atomicMin(status, HSQ_ERR_OVERFLOW);
+}
+
+struct AlignDeviceOut {
+    int32_t cols_cap, md_cap;
+    int32_t *score, *n_cols, *first_q, *last_q, *first_r, *last_r, *matches, *mismatches, *non_terminal_gaps, *edit_distance,
+        *md_len, *rmd_len;
+    uint8_t *ref_aln, *qry_aln, *ops, *md, *rmd, *overflow;
+};
+
+// Operator seam: NeedlemanWunschGlobalAlignment + AlignmentPair getters, one alignment per thread.
+template <bool LUT>
+__global__ void __launch_bounds__(128) align_kernel(DeviceSeqs refs, DeviceSeqs qrys, int64_t n, ScoreParams sp, int pen_start,
+                                                    int pen_end, ScratchPool pool, AlignDeviceOut out, int* status,
+                                                    unsigned long long* cells_total) {
+    DpScratch sc = thread_scratch(pool);
+    int64_t cells = 0;
+    for (int64_t k = sc.tid; k < n; k += sc.nthreads) {
+        int64_t r0 = refs.offsets[k], q0 = qrys.offsets[k];
+        SeqView ref = make_view(refs.codes + r0, (int)(refs.offsets[k + 1] - r0), false, false);
+        SeqView qry = make_view(qrys.codes + q0, (int)(qrys.offsets[k + 1] - q0), false, false);
+        int score = dp_fill<LUT>(ref, qry, sp, pen_start, pen_end, sc);
+        cells += (int64_t)ref.len * qry.len;
+        Columns cv{sc, dp_traceback(ref, qry, sc)};
+        PairIndices ix = pair_indices(cv);
+        out.score[k] = score;
+        out.n_cols[k] = cv.n;
+        out.first_q[k] = ix.first_q;
+        out.last_q[k] = ix.last_q;
+        out.first_r[k] = ix.first_r;
+        out.last_r[k] = ix.last_r;
+        int m, x, rg, qg;
+        count_columns(cv, 0, cv.n - 1, &m, &x, &rg, &qg);
+        out.matches[k] = m;
+        out.mismatches[k] = x;
+        out.non_terminal_gaps[k] = non_terminal_gaps(cv, ix);
+        uint8_t ovf = cv.n > out.cols_cap ? 1 : 0;
+        for (int c = 0; c < cv.n && c < out.cols_cap; c++) {
+            uint32_t w = cv.fwd(c);
+            out.ref_aln[k * out.cols_cap + c] = decode_code((uint8_t)col_ref(w));
+            out.qry_aln[k * out.cols_cap + c] = decode_code((uint8_t)col_qry(w));
+            out.ops[k * out.cols_cap + c] = column_op(w);
+        }
+        SlotWriter mw{out.md + k * out.md_cap, out.md_cap, 0};
+        SlotWriter rw{out.rmd + k * out.md_cap, out.md_cap, 0};
+        int nm, rl;
+        emit_cigar_md(cv, 0, cv.n - 1, false, nullptr, &mw, &nm, &rl);
+        out.edit_distance[k] = nm;
+        emit_cigar_md(cv, 0, cv.n - 1, true, nullptr, &rw, &nm, &rl);
+        out.md_len[k] = mw.len;
+        out.rmd_len[k] = rw.len;
+        if (mw.len > mw.cap) ovf |= 2;
+        if (rw.len > rw.cap) ovf |= 4;
+        out.overflow[k] = ovf;
+        if (ovf) atomicMin(status, HSQ_ERR_OVERFLOW);
+    }
+    for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
+    if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
+}
+
+}  // namespace hsq

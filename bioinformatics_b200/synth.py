@@ -1,0 +1,187 @@
+"""Seeded synthetic HEAT-Seq-shaped probes and read pairs; numpy only, vectorised.
+
+Probe layout follows the probe-info columns of COMMON/utils/probeinfo/ProbeFileUtil.java:45-46.  Read
+orientation follows what ExtendReadsToPrimer expects (HSQ/process/ExtendReadsToPrimer.java:104-165):
+  R1 = UID_ext ++ extPrimer ++ target ++ ligPrimer ++ filler
+  R2 = UID_lig ++ revcomp(ligPrimer) ++ revcomp(target) ++ revcomp(extPrimer) ++ filler
+(the same construction serves '+' and '-' probes, because the reference complements both the probe
+sequences and the read for the '-' strand).
+"""
+import numpy as np
+
+from . import _abi as A
+from .batches import PairBatchHost, ProbeTableHost
+
+SEED_PROBES = 20240501
+SEED_READS = 20240502
+_ACGT = np.frombuffer(b"ACGT", dtype=np.uint8)
+_COMP = np.zeros(256, dtype=np.uint8)
+for a, b in zip(b"ACGTN", b"TGCAN"):
+    _COMP[a] = b
+
+
+def revcomp_bytes(arr):
+    return _COMP[arr[::-1]]
+
+
+def make_probes(n_probes, seed=SEED_PROBES, target_len=(100, 160), primer_len=(18, 25)):
+    rng = np.random.default_rng(seed)
+    le = rng.integers(primer_len[0], primer_len[1] + 1, n_probes)
+    ll = rng.integers(primer_len[0], primer_len[1] + 1, n_probes)
+    lt = rng.integers(target_len[0], target_len[1] + 1, n_probes)
+    rev = (np.arange(n_probes) % 2).astype(np.uint8)
+
+    def rand_batch(lens):
+        off = np.zeros(n_probes + 1, dtype=np.int64)
+        off[1:] = np.cumsum(lens)
+        return A.SeqBatch(_ACGT[rng.integers(0, 4, int(off[-1]))], off)
+
+    ext, lig, target = rand_batch(le), rand_batch(ll), rand_batch(lt)
+    per_contig = max(1, (n_probes + 21) // 22)
+    base = (np.arange(n_probes) % per_contig) * 1000 + 10000
+    chrom = ["chr%d" % (1 + k // per_contig) for k in range(n_probes)]
+    left_len = np.where(rev == 1, ll, le)
+    right_len = np.where(rev == 1, le, ll)
+    left_start = base
+    left_stop = base + left_len - 1
+    t_start = left_stop + 1
+    t_stop = t_start + lt - 1
+    right_start = t_stop + 1
+    right_stop = right_start + right_len - 1
+    ext_start = np.where(rev == 1, right_start, left_start)
+    ext_stop = np.where(rev == 1, right_stop, left_stop)
+    lig_start = np.where(rev == 1, left_start, right_start)
+    lig_stop = np.where(rev == 1, left_stop, right_stop)
+    ids = ["probe_%d" % k for k in range(n_probes)]
+    return ProbeTableHost(rev, ext_start, ext_stop, lig_start, lig_stop, t_start, t_stop, ext, lig, target, ids, chrom)
+
+
+def _templates(probes, read_len, rng):
+    """Per-probe molecule templates for both mates, padded with random filler to read_len + slack."""
+    n = probes.n
+    width = read_len + 8
+    t1 = _ACGT[rng.integers(0, 4, (n, width))]
+    t2 = _ACGT[rng.integers(0, 4, (n, width))]
+    for k in range(n):
+        e = probes.ext.data[probes.ext.offsets[k]:probes.ext.offsets[k + 1]]
+        t = probes.target.data[probes.target.offsets[k]:probes.target.offsets[k + 1]]
+        g = probes.lig.data[probes.lig.offsets[k]:probes.lig.offsets[k + 1]]
+        m1 = np.concatenate([e, t, g])[:width]
+        m2 = revcomp_bytes(np.concatenate([e, t, g]))[:width]
+        t1[k, :len(m1)] = m1
+        t2[k, :len(m2)] = m2
+    return t1, t2
+
+
+def _noisy_copy(tmpl_rows, body_len, rng, sub_rate, ins_rate, del_rate):
+    """Rows of templates -> body_len-long noisy copies (at most one insertion and one deletion per read)."""
+    n, width = tmpl_rows.shape
+    j = np.arange(body_len, dtype=np.int32)[None, :]
+    p_del = np.where(rng.random(n) < del_rate * body_len, rng.integers(0, body_len, n), 1 << 20).astype(np.int32)[:, None]
+    p_ins = np.where(rng.random(n) < ins_rate * body_len, rng.integers(0, body_len, n), 1 << 20).astype(np.int32)[:, None]
+    src = j + (j >= p_del).astype(np.int32) - (j > p_ins).astype(np.int32)
+    np.clip(src, 0, width - 1, out=src)
+    out = np.take_along_axis(tmpl_rows, src, axis=1)
+    ins_rows = np.nonzero(p_ins[:, 0] < body_len)[0]
+    out[ins_rows, p_ins[ins_rows, 0]] = _ACGT[rng.integers(0, 4, len(ins_rows))]
+    sub = rng.random((n, body_len)) < sub_rate
+    k = int(sub.sum())
+    if k:
+        cur = out[sub]
+        idx = np.searchsorted(_ACGT, cur)  # A,C,G,T are ascending ASCII
+        out[sub] = _ACGT[(idx + rng.integers(1, 4, k)) % 4]
+    return out
+
+
+_QTABLE = None
+
+
+def _qual_table():
+    global _QTABLE
+    if _QTABLE is None:
+        rng = np.random.default_rng(7)
+        q = np.round(np.clip(rng.normal(36, 4, 4096), 2, 41)).astype(np.uint8) + 33
+        _QTABLE = q
+    return _QTABLE
+
+
+def make_pairs(probes, n_pairs, read_len=150, ext_uid_len=10, lig_uid_len=0, seed=SEED_READS, mean_family=3.0,
+               sub_rate=0.005, ins_rate=0.0005, del_rate=0.0005, n_rate=0.001, with_quals=True, chunk=1 << 20,
+               sort_by_probe=False):
+    """Returns PairBatchHost with fixed-length reads.  Families: size ~ 1 + Geometric(mean mean_family)."""
+    rng = np.random.default_rng(seed)
+    t1, t2 = _templates(probes, read_len, rng)
+    # molecules until we have n_pairs reads
+    n_mol_guess = int(n_pairs / (1.0 + mean_family) * 1.2) + 16
+    fam = 1 + rng.geometric(1.0 / (mean_family + 1.0), n_mol_guess) - 1
+    fam = np.maximum(fam, 1)
+    while fam.sum() < n_pairs:
+        fam = np.concatenate([fam, np.maximum(1, rng.geometric(1.0 / (mean_family + 1.0), n_mol_guess))])
+    n_mol = int(np.searchsorted(np.cumsum(fam), n_pairs) + 1)
+    fam = fam[:n_mol]
+    mol_probe = rng.integers(0, probes.n, n_mol).astype(np.int32)
+    mol_uid1 = _ACGT[rng.integers(0, 4, (n_mol, max(1, ext_uid_len)))][:, :ext_uid_len]
+    mol_uid2 = _ACGT[rng.integers(0, 4, (n_mol, max(1, lig_uid_len)))][:, :lig_uid_len]
+    mol_of_read = np.repeat(np.arange(n_mol), fam)[:n_pairs]
+    if sort_by_probe:
+        order = np.argsort(mol_probe[mol_of_read], kind="stable")
+        mol_of_read = mol_of_read[order]
+    else:
+        mol_of_read = mol_of_read[rng.permutation(n_pairs)]
+    probe_id = mol_probe[mol_of_read]
+    r1 = np.empty((n_pairs, read_len), dtype=np.uint8)
+    r2 = np.empty((n_pairs, read_len), dtype=np.uint8)
+    for b in range(0, n_pairs, chunk):
+        e = min(n_pairs, b + chunk)
+        mo = mol_of_read[b:e]
+        r1[b:e, :ext_uid_len] = mol_uid1[mo]
+        r2[b:e, :lig_uid_len] = mol_uid2[mo]
+        r1[b:e, ext_uid_len:] = _noisy_copy(t1[probe_id[b:e]], read_len - ext_uid_len, rng, sub_rate, ins_rate, del_rate)
+        r2[b:e, lig_uid_len:] = _noisy_copy(t2[probe_id[b:e]], read_len - lig_uid_len, rng, sub_rate, ins_rate, del_rate)
+    n_n = int(n_pairs * n_rate)
+    if n_n:
+        rows = rng.integers(0, n_pairs, n_n)
+        colsn = rng.integers(0, read_len, n_n)
+        mate = rng.integers(0, 2, n_n)
+        r1[rows[mate == 0], colsn[mate == 0]] = ord("N")
+        r2[rows[mate == 1], colsn[mate == 1]] = ord("N")
+    q1 = q2 = None
+    if with_quals:
+        tbl = _qual_table()
+        q1 = A.SeqBatch.from_fixed(tbl[rng.integers(0, len(tbl), (n_pairs, read_len))])
+        q2 = A.SeqBatch.from_fixed(tbl[rng.integers(0, len(tbl), (n_pairs, read_len))])
+    return PairBatchHost(probe_id, A.SeqBatch.from_fixed(r1), A.SeqBatch.from_fixed(r2), q1, q2,
+                         np.arange(n_pairs, dtype=np.int32))
+
+
+def drop_n_pairs(pairs):
+    """The caller-side filter of …Identification.java:815-821: pairs with an 'N'/'n' in either mate are not deduplicated."""
+    L1 = pairs.r1.lengths()
+    L2 = pairs.r2.lengths()
+    if not ((L1 == L1[0]).all() and (L2 == L2[0]).all()):
+        keep = [k for k in range(pairs.n) if "n" not in (pairs.r1.string(k) + pairs.r2.string(k)).lower()]
+        return pairs.subset(keep), np.asarray(keep)
+    a = pairs.r1.data.reshape(pairs.n, -1)
+    b = pairs.r2.data.reshape(pairs.n, -1)
+    bad = ((a | 0x20) == ord("n")).any(axis=1) | ((b | 0x20) == ord("n")).any(axis=1)
+    keep = np.nonzero(~bad)[0]
+
+    def take(sb):
+        return None if sb is None else A.SeqBatch.from_fixed(sb.data.reshape(pairs.n, -1)[keep])
+
+    return PairBatchHost(pairs.probe_id[keep], take(pairs.r1), take(pairs.r2), take(pairs.q1), take(pairs.q2),
+                         pairs.read_index[keep]), keep
+
+
+def write_probe_info_file(probes, path, ext_uid_len=10, lig_uid_len=0):
+    """Probe-info TSV with the 13 named columns the reference parses (ProbeFileUtil.java:45-46) and its #key=value header."""
+    cols = ["probe_id", "chromosome", "probe_strand", "ext_start", "ext_stop", "ext_sequence", "lig_start", "lig_stop",
+            "lig_sequence", "target_start", "target_stop", "target_sequence", "annotation"]
+    with open(path, "w") as f:
+        f.write("#extension_uid=%d ligation_uid=%d genome=synthetic\n" % (ext_uid_len, lig_uid_len))
+        f.write("\t".join(cols) + "\n")
+        for k in range(probes.n):
+            f.write("\t".join([probes.probe_ids[k], probes.chromosomes[k], "-" if probes.reverse_strand[k] else "+",
+                               str(probes.ext_start[k]), str(probes.ext_stop[k]), probes.ext.string(k),
+                               str(probes.lig_start[k]), str(probes.lig_stop[k]), probes.lig.string(k),
+                               str(probes.target_start[k]), str(probes.target_stop[k]), probes.target.string(k), ""]) + "\n")
