@@ -17,7 +17,8 @@ _lib = None
 
 EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version", "hsq_pinned_alloc", "hsq_pinned_free",
            "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
-           "hsq_extend_batch", "hsq_resolve_multi_probe")
+           "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
+           "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak")
 
 
 class HsqError(RuntimeError):
@@ -57,10 +58,14 @@ class Context:
         self.h = h
         self.device = device
         self.n_probes = 0
+        self._pinned = []
         self.set_scorer(scorer_ or scorer())
 
     def close(self):
         if getattr(self, "h", None):
+            for p in self._pinned:
+                self.lib.hsq_pinned_free(self.h, p)
+            self._pinned = []
             self.lib.hsq_ctx_destroy(self.h)
             self.h = None
 
@@ -91,7 +96,7 @@ class Context:
         self._check(self.lib.hsq_pinned_alloc(self.h, C.c_size_t(nbytes), C.byref(p)))
         buf = (C.c_uint8 * max(1, nbytes)).from_address(p.value)
         arr = np.frombuffer(buf, dtype=np.uint8, count=nbytes)
-        arr._hsq_pinned = p  # keep the address for pinned_free
+        self._pinned.append(p)  # freed in close()
         return arr
 
     def set_scorer(self, sc):
@@ -144,6 +149,33 @@ class Context:
         out.finish()
         self._check(st)
         return out
+
+    def extend_stage(self, pairs: PairBatchHost):
+        pc = pairs.c()
+        self._check(self.lib.hsq_extend_stage(self.h, C.byref(pc)))
+
+    def extend_run(self, cigar_cap=32, md_cap=48):
+        self._check(self.lib.hsq_extend_run(self.h, C.c_int32(cigar_cap), C.c_int32(md_cap)))
+
+    def extend_fetch(self, out: ExtendResult):
+        oc = out.c()
+        st = self.lib.hsq_extend_fetch(self.h, C.byref(oc))
+        out.finish()
+        self._check(st)
+        return out
+
+    def timer_start(self):
+        self._check(self.lib.hsq_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        self._check(self.lib.hsq_timer_stop(self.h, C.byref(ms)))
+        return ms.value
+
+    def int32_peak(self, seconds=1.0):
+        v = C.c_double(0)
+        self._check(self.lib.hsq_int32_peak(self.h, C.c_double(seconds), C.byref(v)))
+        return v.value
 
     def resolve_multi_probe(self, r1, r2, cand_offsets, cand_probe, ext_uid_len, lig_uid_len):
         r1 = r1 if isinstance(r1, A.SeqBatch) else A.SeqBatch.from_strings(r1)

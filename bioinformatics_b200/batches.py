@@ -51,6 +51,18 @@ class PairBatchHost:
                            self.r2.c(), A.ptr(None if self.q1 is None else self.q1.data, A.u8p),
                            A.ptr(None if self.q2 is None else self.q2.data, A.u8p))
 
+    def head(self, k):
+        """First k pairs (views, no copies)."""
+        k = min(k, self.n)
+
+        def cut(sb):
+            if sb is None:
+                return None
+            return A.SeqBatch(sb.data[:sb.offsets[k]], sb.offsets[:k + 1])
+
+        return PairBatchHost(self.probe_id[:k], cut(self.r1), cut(self.r2), cut(self.q1), cut(self.q2),
+                             None if self.read_index is None else self.read_index[:k])
+
     def subset(self, idx):
         idx = np.asarray(idx)
 

@@ -118,6 +118,8 @@ int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) {
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
+    HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev_user0));
+    HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev_user1));
     HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_status, 64));
     HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_cells, 64));
     std::vector<double> tbl(POW95_N);
@@ -142,6 +144,8 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     cudaFreeHost(ctx->h_cells);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
+    cudaEventDestroy(ctx->ev_user0);
+    cudaEventDestroy(ctx->ev_user1);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -181,3 +185,4 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_trim.inl"
 #include "hsq_capi_dedup.inl"
 #include "hsq_capi_resolve.inl"
+#include "hsq_capi_peak.inl"

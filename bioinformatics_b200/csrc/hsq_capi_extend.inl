@@ -8,36 +8,36 @@ __global__ void check_probe_ids_kernel(const int32_t* __restrict__ probe_id, int
         if (probe_id[k] < 0 || probe_id[k] >= n_probes) atomicMin(status, HSQ_ERR_INVALID_ARGUMENT);
 }
 
-int upload_pairs(hsq_ctx* ctx, const hsq_pair_batch* pb, bool need_quals, bool need_index) {
+int upload_pairs_raw(hsq_ctx* ctx, const hsq_pair_batch* pb) {
     int rc;
     const size_t n = (size_t)pb->n;
     if (pb->r1.n != pb->n || pb->r2.n != pb->n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
     if (n && !pb->probe_id) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe_id is null");
     HSQ_CUDA(ctx, ctx->probe_id.ensure(n * 4 + 16));
     if (n) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->probe_id.p, pb->probe_id, n * 4, cudaMemcpyHostToDevice, ctx->stream));
-    if ((rc = upload_seqs(ctx, &pb->r1, &ctx->r1, d_status(ctx), d_maxlen(ctx, 0)))) return rc;
-    if ((rc = upload_seqs(ctx, &pb->r2, &ctx->r2, d_status(ctx), d_maxlen(ctx, 1)))) return rc;
-    if (need_quals) {
-        if (n && (!pb->q1 || !pb->q2)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "quality strings are required");
-        HSQ_CUDA(ctx, ctx->q1.ensure((size_t)ctx->r1.total + 16));
-        HSQ_CUDA(ctx, ctx->q2.ensure((size_t)ctx->r2.total + 16));
-        if (ctx->r1.total) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q1.p, pb->q1, (size_t)ctx->r1.total, cudaMemcpyHostToDevice, ctx->stream));
-        if (ctx->r2.total) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q2.p, pb->q2, (size_t)ctx->r2.total, cudaMemcpyHostToDevice, ctx->stream));
-    }
-    if (need_index) {
-        if (n && !pb->read_index) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "read_index is required");
-        HSQ_CUDA(ctx, ctx->read_index.ensure(n * 4 + 16));
-        if (n) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->read_index.p, pb->read_index, n * 4, cudaMemcpyHostToDevice, ctx->stream));
-    }
+    if ((rc = copy_seqs(ctx, &pb->r1, &ctx->r1))) return rc;
+    if ((rc = copy_seqs(ctx, &pb->r2, &ctx->r2))) return rc;
     return HSQ_OK;
 }
 
-int run_extend(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o) {
-    const int64_t n = pb->n;
+// stage: host -> device copies of one pair batch (raw ASCII reads, probe ids)
+int extend_stage(hsq_ctx* ctx, const hsq_pair_batch* pb) {
+    int rc;
+    ctx->ext_n = -1;
+    if ((rc = upload_pairs_raw(ctx, pb))) return rc;
+    ctx->ext_n = pb->n;
+    return HSQ_OK;
+}
+
+// run: encode + DP + finalize on the staged batch; results stay on the device
+int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
+    const int64_t n = ctx->ext_n;
+    if (n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "no staged batch");
     const size_t n2 = (size_t)(2 * n);
     int rc = reset_status(ctx);
     if (rc) return rc;
-    if ((rc = upload_pairs(ctx, pb, false, false))) return rc;
+    if ((rc = encode_seqs(ctx, &ctx->r1, d_status(ctx), d_maxlen(ctx, 0)))) return rc;
+    if ((rc = encode_seqs(ctx, &ctx->r2, d_status(ctx), d_maxlen(ctx, 1)))) return rc;
     if (n > 0) {
         int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
         check_probe_ids_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, ctx->n_probes, d_status(ctx));
@@ -45,7 +45,7 @@ int run_extend(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o) {
     }
     int w[3];
     if ((rc = read_status(ctx, w, 3))) return rc;
-    if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend_batch: ") + (w[0] == HSQ_ERR_INVALID_ARGUMENT ? "probe_id out of range" : status_message(w[0])));
+    if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend: ") + (w[0] == HSQ_ERR_INVALID_ARGUMENT ? "probe_id out of range" : status_message(w[0])));
     const int read_max = std::max(w[1], w[2]);
     const int primer_max = std::max(ctx->p_ext.max_len, ctx->p_lig.max_len);
     if (2 * primer_max + PRIMER_ALIGNMENT_BUFFER + 2 > POW95_N) return fail(ctx, HSQ_ERR_UNSUPPORTED, "primer longer than the 0.95^d table supports");
@@ -62,18 +62,18 @@ int run_extend(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o) {
     if ((rc = alloc_scratch(ctx, (int64_t)grid * 128, q_max, r_max, &pool))) return rc;
     HSQ_CUDA(ctx, ctx->out_i32.ensure(10 * n2 * sizeof(int32_t) + 16));
     HSQ_CUDA(ctx, ctx->out_u8.ensure(2 * n2 + 16));
-    HSQ_CUDA(ctx, ctx->out_slots.ensure(n2 * ((size_t)o->cigar_cap + (size_t)o->md_cap) + 16));
+    HSQ_CUDA(ctx, ctx->out_slots.ensure(n2 * ((size_t)cigar_cap + (size_t)md_cap) + 16));
     HSQ_CUDA(ctx, ctx->pair_ok.ensure((size_t)n + 16));
     int32_t* i32 = ctx->out_i32.as<int32_t>();
-    ExtendDeviceOut d;
-    d.cigar_cap = o->cigar_cap;
-    d.md_cap = o->md_cap;
+    ExtendDeviceOut& d = ctx->ext_out;
+    d.cigar_cap = cigar_cap;
+    d.md_cap = md_cap;
     d.primer_end = i32; d.score = i32 + n2; d.pos = i32 + 2 * n2; d.read_start = i32 + 3 * n2; d.read_stop = i32 + 4 * n2;
     d.nm = i32 + 5 * n2; d.tlen = i32 + 6 * n2; d.cigar_len = i32 + 7 * n2; d.md_len = i32 + 8 * n2; d.ref_len = i32 + 9 * n2;
     d.ok = ctx->out_u8.as<uint8_t>();
     d.overflow = d.ok + n2;
     d.cigar = ctx->out_slots.as<uint8_t>();
-    d.md = d.cigar + n2 * (size_t)o->cigar_cap;
+    d.md = d.cigar + n2 * (size_t)cigar_cap;
     if (n > 0) {
         DeviceProbes pv = probe_view(ctx);
         if (sp_user.lut_ok)
@@ -89,31 +89,82 @@ int run_extend(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o) {
         ctx->launches++;
         HSQ_CUDA(ctx, cudaGetLastError());
     }
+    ctx->ext_ran = true;
+    return HSQ_OK;
+}
+
+// fetch: device -> host copies of the results of the last run
+int extend_fetch(hsq_ctx* ctx, hsq_extend_out* o) {
+    if (!ctx->ext_ran || ctx->ext_n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "no results to fetch");
+    const int64_t n = ctx->ext_n;
+    const size_t n2 = (size_t)(2 * n);
+    const ExtendDeviceOut& d = ctx->ext_out;
+    if (o->cigar_cap != d.cigar_cap || o->md_cap != d.md_cap) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "slot capacities differ from the run");
+    int rc;
+    int32_t* i32 = ctx->out_i32.as<int32_t>();
     int32_t* hosts[9] = {o->primer_end, o->score, o->pos, o->read_start, o->read_stop, o->nm, o->tlen, o->cigar_len, o->md_len};
     for (int f = 0; f < 9; f++)
         if ((rc = d2h(ctx, hosts[f], i32 + f * n2, n2))) return rc;
     if ((rc = d2h(ctx, o->ok, d.ok, n2))) return rc;
     if ((rc = d2h(ctx, o->overflow, d.overflow, n2))) return rc;
-    if ((rc = d2h(ctx, o->cigar, d.cigar, n2 * (size_t)o->cigar_cap))) return rc;
-    if ((rc = d2h(ctx, o->md, d.md, n2 * (size_t)o->md_cap))) return rc;
+    if ((rc = d2h(ctx, o->cigar, d.cigar, n2 * (size_t)d.cigar_cap))) return rc;
+    if ((rc = d2h(ctx, o->md, d.md, n2 * (size_t)d.md_cap))) return rc;
     if ((rc = d2h(ctx, o->pair_ok, ctx->pair_ok.as<uint8_t>(), (size_t)n))) return rc;
     HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    int w[1];
     if ((rc = read_status(ctx, w, 1))) return rc;
     o->cells = (int64_t)ctx->h_cells[0];
-    if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend_batch: ") + status_message(w[0]));
+    if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend: ") + status_message(w[0]));
     return HSQ_OK;
 }
 
 }  // namespace
 
-extern "C" int32_t hsq_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, hsq_extend_out* out) {
-    if (!ctx || !pairs || !out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+static int extend_args_ok(hsq_ctx* ctx) {
     if (!ctx->have_probes) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_set_probes has not been called");
     if (!ctx->have_scorer) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_set_scorer has not been called");
+    return HSQ_OK;
+}
+
+extern "C" int32_t hsq_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, hsq_extend_out* out) {
+    if (!ctx || !pairs || !out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    int rc = extend_args_ok(ctx);
+    if (rc) return rc;
     if (pairs->n < 0 || out->cigar_cap < 0 || out->md_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
-    int rc = run_extend(ctx, pairs, out);
+    rc = extend_stage(ctx, pairs);
+    if (!rc) rc = extend_run(ctx, out->cigar_cap, out->md_cap);
+    if (!rc || rc == HSQ_ERR_OVERFLOW) { int r2 = extend_fetch(ctx, out); if (!rc) rc = r2; }
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}
+
+extern "C" int32_t hsq_extend_stage(hsq_ctx* ctx, const hsq_pair_batch* pairs) {
+    if (!ctx || !pairs || pairs->n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = extend_stage(ctx, pairs);
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}
+
+extern "C" int32_t hsq_extend_run(hsq_ctx* ctx, int32_t cigar_cap, int32_t md_cap) {
+    if (!ctx || cigar_cap < 0 || md_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "bad argument");
+    int rc = extend_args_ok(ctx);
+    if (rc) return rc;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    rc = extend_run(ctx, cigar_cap, md_cap);
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}
+
+extern "C" int32_t hsq_extend_fetch(hsq_ctx* ctx, hsq_extend_out* out) {
+    if (!ctx || !out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = extend_fetch(ctx, out);
     int rc2 = timer.finish();
     return rc ? rc : rc2;
 }

@@ -45,7 +45,7 @@ struct hsq_ctx {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_user0 = nullptr, ev_user1 = nullptr;
     std::string error;
     float last_kernel_ms = 0.f;
     int last_launches = 0;
@@ -62,6 +62,9 @@ struct hsq_ctx {
     // scratch + outputs
     hsq::DevBuf ptr_words, brow, cols, status, cells, misc, out_i32, out_u8, out_slots, pair_ok;
     hsq::DevBuf sort_a, sort_b, sort_c, sort_d, sort_tmp, flags;
+    int64_t ext_n = -1;  // staged extend batch
+    bool ext_ran = false;
+    hsq::ExtendDeviceOut ext_out{};
     int* h_status = nullptr;  // pinned
     unsigned long long* h_cells = nullptr;
 };
@@ -93,30 +96,42 @@ inline const char* status_message(int st) {
     }
 }
 
-// Copies a host ragged ASCII batch to the device and encodes it.  max_len is read back lazily by the caller.
-inline int upload_seqs(hsq_ctx* ctx, const hsq_seqs* s, DevSeqsOwned* d, int* d_status, int* d_maxlen /*device int or null*/) {
+// host -> device copy of a ragged ASCII batch (no kernels)
+inline int copy_seqs(hsq_ctx* ctx, const hsq_seqs* s, DevSeqsOwned* d) {
     if (!s || s->n < 0 || !s->offsets) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null sequence batch");
-    d->n = s->n;
-    d->total = s->offsets[s->n] - s->offsets[0];
     if (s->offsets[0] != 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "offsets must start at 0");
+    d->n = s->n;
+    d->total = s->offsets[s->n];
     if (d->total < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative batch size");
+    if (d->total > 0 && !s->data) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null sequence data");
     HSQ_CUDA(ctx, d->ascii.ensure((size_t)d->total + 16));
     HSQ_CUDA(ctx, d->codes.ensure((size_t)d->total + 16));
     HSQ_CUDA(ctx, d->offsets.ensure((size_t)(s->n + 1) * sizeof(int64_t)));
     if (d->total > 0) HSQ_CUDA(ctx, cudaMemcpyAsync(d->ascii.p, s->data, (size_t)d->total, cudaMemcpyHostToDevice, ctx->stream));
     HSQ_CUDA(ctx, cudaMemcpyAsync(d->offsets.p, s->offsets, (size_t)(s->n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+    return HSQ_OK;
+}
+
+// ASCII -> device codes of a staged batch (+ optional max length into a device int)
+inline int encode_seqs(hsq_ctx* ctx, DevSeqsOwned* d, int* d_status, int* d_maxlen) {
     if (d->total > 0) {
         int64_t threads = (d->total + 15) / 16;
         int blocks = (int)std::min<int64_t>((threads + 255) / 256, (int64_t)ctx->sm_count * 16);
         encode_kernel<<<blocks, 256, 0, ctx->stream>>>(d->ascii.as<uint8_t>(), d->codes.as<uint8_t>(), d->total, d_status);
         ctx->launches++;
     }
-    if (d_maxlen && s->n > 0) {
-        int blocks = (int)std::min<int64_t>((s->n + 255) / 256, (int64_t)ctx->sm_count * 8);
-        max_len_kernel<<<blocks, 256, 0, ctx->stream>>>(d->offsets.as<int64_t>(), s->n, d_maxlen);
+    if (d_maxlen && d->n > 0) {
+        int blocks = (int)std::min<int64_t>((d->n + 255) / 256, (int64_t)ctx->sm_count * 8);
+        max_len_kernel<<<blocks, 256, 0, ctx->stream>>>(d->offsets.as<int64_t>(), d->n, d_maxlen);
         ctx->launches++;
     }
     return HSQ_OK;
+}
+
+inline int upload_seqs(hsq_ctx* ctx, const hsq_seqs* s, DevSeqsOwned* d, int* d_status, int* d_maxlen) {
+    int rc = copy_seqs(ctx, s, d);
+    if (rc) return rc;
+    return encode_seqs(ctx, d, d_status, d_maxlen);
 }
 
 }  // namespace hsq

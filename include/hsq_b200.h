@@ -174,10 +174,24 @@ int32_t hsq_dedup_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_u
 /* ExtendReadsToPrimer.extendReadsToPrimers (HSQ/process/ExtendReadsToPrimer.java:347-380) for a batch that
  * may span probes.  Needs hsq_set_probes and hsq_set_scorer first. */
 int32_t hsq_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, hsq_extend_out* out);
+/* The three phases of hsq_extend_batch, separately callable so a caller can keep a batch resident in HBM
+ * (stage = host->device copies; run = encode + DP + traceback + CIGAR/MD kernels; fetch = device->host copies). */
+int32_t hsq_extend_stage(hsq_ctx* ctx, const hsq_pair_batch* pairs);
+int32_t hsq_extend_run(hsq_ctx* ctx, int32_t cigar_cap, int32_t md_cap);
+int32_t hsq_extend_fetch(hsq_ctx* ctx, hsq_extend_out* out);
 /* Multi-probe tie-break (…Identification.java:704-765): best_probe[k] = winning probe row or -1 when
  * the read must be removed from all probes.  matches/edit (per candidate, may be NULL) expose the two metrics. */
 int32_t hsq_resolve_multi_probe(hsq_ctx* ctx, const hsq_candidates* cands, int32_t ext_uid_len, int32_t lig_uid_len,
                                 int32_t* best_probe, int32_t* cand_matches, int32_t* cand_edit);
+
+
+/* ---- measurement helpers ------------------------------------------------------------------- */
+/* CUDA-event stopwatch on the context's stream (the stream every kernel of this library is launched on). */
+int32_t hsq_timer_start(hsq_ctx* ctx);
+int32_t hsq_timer_stop(hsq_ctx* ctx, float* ms);
+/* Sustained INT32 issue rate (lane-ops/s) of the device from an IMAD/VIMNMX/LOP3 micro-kernel run for `seconds`:
+ * the roofline denominator of the DP kernels. */
+int32_t hsq_int32_peak(hsq_ctx* ctx, double seconds, double* int_ops_per_s);
 
 #ifdef __cplusplus
 }
