@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstring>
 #include "hsq_host.cuh"
+#include "hsq_extend.cuh"
 
 using namespace hsq;
 

@@ -14,11 +14,9 @@ int run_align(hsq_ctx* ctx, const hsq_seqs* refs, const hsq_seqs* qrys, const hs
     const int r_max = w[1], q_max = w[2];
     ScoreParams sp = make_score_params(scorer->match, scorer->mismatch, scorer->gap_extend, scorer->gap_start);
     int grid = 1;
-    if (sp.lut_ok) rc = persistent_grid(ctx, align_kernel<true>, 128, n, &grid);
-    else rc = persistent_grid(ctx, align_kernel<false>, 128, n, &grid);
-    if (rc) return rc;
+    if ((rc = persistent_grid(ctx, align_kernel, DP_BLOCK, n, &grid))) return rc;
     ScratchPool pool;
-    if ((rc = alloc_scratch(ctx, (int64_t)grid * 128, q_max, r_max, &pool))) return rc;
+    if ((rc = alloc_scratch(ctx, (int64_t)grid * DP_BLOCK, q_max, r_max, &pool))) return rc;
     const size_t nn = (size_t)n;
     HSQ_CUDA(ctx, ctx->out_i32.ensure(12 * nn * sizeof(int32_t) + 16));
     HSQ_CUDA(ctx, ctx->out_u8.ensure(nn + 16));
@@ -36,12 +34,8 @@ int run_align(hsq_ctx* ctx, const hsq_seqs* refs, const hsq_seqs* qrys, const hs
     d.overflow = ctx->out_u8.as<uint8_t>();
     const int ps = (flags & HSQ_ALIGN_PENALIZE_START) ? 1 : 0, pe = (flags & HSQ_ALIGN_PENALIZE_END) ? 1 : 0;
     if (n > 0) {
-        if (sp.lut_ok)
-            align_kernel<true><<<grid, 128, 0, ctx->stream>>>(ctx->sa.view(), ctx->sb.view(), n, sp, ps, pe, pool, d, d_status(ctx),
-                                                            ctx->cells.as<unsigned long long>());
-        else
-            align_kernel<false><<<grid, 128, 0, ctx->stream>>>(ctx->sa.view(), ctx->sb.view(), n, sp, ps, pe, pool, d, d_status(ctx),
-                                                             ctx->cells.as<unsigned long long>());
+        align_kernel<<<grid, DP_BLOCK, 0, ctx->stream>>>(ctx->sa.view(), ctx->sb.view(), n, sp, ps, pe, pool, d, d_status(ctx),
+                                                        ctx->cells.as<unsigned long long>());
         ctx->launches++;
         HSQ_CUDA(ctx, cudaGetLastError());
     }

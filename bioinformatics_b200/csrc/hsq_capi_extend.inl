@@ -54,12 +54,24 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
     const int r_max = std::max(ctx->p_target.max_len, std::min(read_max, primer_max + PRIMER_ALIGNMENT_BUFFER + 1));
     ScoreParams sp_default = make_score_params(1, -4, -1, -6);  // SimpleAlignmentScorer defaults (ExtendReadsToPrimer.java:290-291)
     ScoreParams sp_user = make_score_params(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start);
-    int grid = 1;
-    if (sp_user.lut_ok) rc = persistent_grid(ctx, extend_kernel<true>, 128, 2 * n, &grid);
-    else rc = persistent_grid(ctx, extend_kernel<false>, 128, 2 * n, &grid);
-    if (rc) return rc;
+    int grid1 = 1, grid2 = 1;
+    if ((rc = persistent_grid(ctx, primer_kernel, DP_BLOCK, 2 * n, &grid1))) return rc;
+    if ((rc = persistent_grid(ctx, capture_kernel, DP_BLOCK, 2 * n, &grid2))) return rc;
     ScratchPool pool;
-    if ((rc = alloc_scratch(ctx, (int64_t)grid * 128, q_max, r_max, &pool))) return rc;
+    if ((rc = alloc_scratch(ctx, (int64_t)std::max(grid1, grid2) * DP_BLOCK, q_max, r_max, &pool))) return rc;
+    // bucket keys: (strips of DP#2, capture-target length); the last key collects read ends that stop after DP#1
+    BucketKeys keys;
+    keys.key_stride = ctx->p_target.max_len + 1;
+    const int n_keys = ((read_max + KROWS - 1) / KROWS + 1) * keys.key_stride + 1;
+    keys.skip_key = (uint32_t)(n_keys - 1);
+    HSQ_CUDA(ctx, ctx->sort_a.ensure(n2 * 4 + 16));
+    HSQ_CUDA(ctx, ctx->sort_b.ensure(n2 * 4 + 16));
+    HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)(2 * n_keys + 4) * 4));
+    keys.key = ctx->sort_a.as<uint32_t>();
+    uint32_t* order = ctx->sort_b.as<uint32_t>();
+    uint32_t* hist = ctx->sort_c.as<uint32_t>();
+    uint32_t* cursor = hist + n_keys;
+    uint32_t* n_active = cursor + n_keys;
     HSQ_CUDA(ctx, ctx->out_i32.ensure(10 * n2 * sizeof(int32_t) + 16));
     HSQ_CUDA(ctx, ctx->out_u8.ensure(2 * n2 + 16));
     HSQ_CUDA(ctx, ctx->out_slots.ensure(n2 * ((size_t)cigar_cap + (size_t)md_cap) + 16));
@@ -76,13 +88,17 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
     d.md = d.cigar + n2 * (size_t)cigar_cap;
     if (n > 0) {
         DeviceProbes pv = probe_view(ctx);
-        if (sp_user.lut_ok)
-            extend_kernel<true><<<grid, 128, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), n, sp_default,
-                                                             sp_user, pool, d, d_status(ctx), ctx->cells.as<unsigned long long>());
-        else
-            extend_kernel<false><<<grid, 128, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), n, sp_default,
-                                                              sp_user, pool, d, d_status(ctx), ctx->cells.as<unsigned long long>());
-        ctx->launches++;
+        HSQ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t)n_keys * 4, ctx->stream));
+        primer_kernel<<<grid1, DP_BLOCK, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), n, sp_default,
+                                                          pool, d, keys, d_status(ctx), ctx->cells.as<unsigned long long>());
+        const int sblocks = (int)std::min<int64_t>((2 * n + 255) / 256, (int64_t)ctx->sm_count * 8);
+        bucket_hist_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, 2 * n, hist);
+        bucket_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist, n_keys, cursor);
+        HSQ_CUDA(ctx, cudaMemcpyAsync(n_active, cursor + keys.skip_key, 4, cudaMemcpyDeviceToDevice, ctx->stream));
+        bucket_scatter_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, 2 * n, cursor, order);
+        capture_kernel<<<grid2, DP_BLOCK, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), order, n_active,
+                                                           sp_user, pool, d, ctx->cells.as<unsigned long long>());
+        ctx->launches += 5;
         HSQ_CUDA(ctx, cudaGetLastError());
         finalize_extend_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), n, d,
                                                                                      ctx->pair_ok.as<uint8_t>(), d_status(ctx));

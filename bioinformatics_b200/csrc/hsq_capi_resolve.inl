@@ -4,12 +4,12 @@ namespace hsq {
 
 // one thread per (candidate, mate): NW(reference = read minus UID, query = probe sequence | its reverse complement),
 // default scorer (:722,:731); metrics of :723-734
-template <bool LUT>
-__global__ void __launch_bounds__(128) tie_break_kernel(DeviceSeqs r1, DeviceSeqs r2, DeviceSeqs probe_full, const int64_t* __restrict__ cand_offsets,
+__global__ void __launch_bounds__(DP_BLOCK) tie_break_kernel(DeviceSeqs r1, DeviceSeqs r2, DeviceSeqs probe_full, const int64_t* __restrict__ cand_offsets,
                                                         const int32_t* __restrict__ cand_probe, int64_t n_reads, int64_t n_cand, int u, int v,
                                                         ScoreParams sp, ScratchPool pool, int32_t* __restrict__ matches,
                                                         int32_t* __restrict__ edit, unsigned long long* cells_total) {
-    DpScratch sc = thread_scratch(pool);
+    __shared__ int4 prof[PROF_INT4_PER_THREAD * DP_BLOCK];
+    DpScratch sc = thread_scratch(pool, prof);
     int64_t cells = 0;
     for (int64_t t = sc.tid; t < 2 * n_cand; t += sc.nthreads) {
         const int64_t j = t >> 1;
@@ -30,7 +30,7 @@ __global__ void __launch_bounds__(128) tie_break_kernel(DeviceSeqs r1, DeviceSeq
         SeqView read = make_view(rs.codes + s0, rl, false, false);
         SeqView ref = sub_view(read, skip, max(0, rl - skip));           // subSequence(uidLength) (:718,:729)
         SeqView qry = make_view(probe_full.codes + p0, pl, mate != 0, mate != 0);  // getReverseCompliment for read two (:731)
-        dp_fill<LUT>(ref, qry, sp, 0, 0, sc);
+        dp_fill(ref, qry, sp, 0, 0, sc);
         cells += (int64_t)ref.len * qry.len;
         Columns cv{sc, dp_traceback(ref, qry, sc)};
         PairIndices ix = pair_indices(cv);
@@ -98,10 +98,10 @@ extern "C" int32_t hsq_resolve_multi_probe(hsq_ctx* ctx, const hsq_candidates* c
     ScoreParams sp = make_score_params(1, -4, -1, -6);  // new NeedlemanWunschGlobalAlignment(ref, query): default scorer
     if (nc > 0) {
         int grid = 1;
-        if ((rc = persistent_grid(ctx, tie_break_kernel<true>, 128, 2 * nc, &grid))) return rc;
+        if ((rc = persistent_grid(ctx, tie_break_kernel, DP_BLOCK, 2 * nc, &grid))) return rc;
         ScratchPool pool;
-        if ((rc = alloc_scratch(ctx, (int64_t)grid * 128, ctx->p_full.max_len, std::max(w[1], w[2]), &pool))) return rc;
-        tie_break_kernel<true><<<grid, 128, 0, ctx->stream>>>(ctx->r1.view(), ctx->r2.view(), ctx->p_full.view(), ctx->sort_a.as<int64_t>(),
+        if ((rc = alloc_scratch(ctx, (int64_t)grid * DP_BLOCK, ctx->p_full.max_len, std::max(w[1], w[2]), &pool))) return rc;
+        tie_break_kernel<<<grid, DP_BLOCK, 0, ctx->stream>>>(ctx->r1.view(), ctx->r2.view(), ctx->p_full.view(), ctx->sort_a.as<int64_t>(),
                                                             ctx->sort_b.as<int32_t>(), n, nc, u, v, sp, pool, m2, e2,
                                                             ctx->cells.as<unsigned long long>());
         ctx->launches++;

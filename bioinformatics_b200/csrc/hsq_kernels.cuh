@@ -82,8 +82,9 @@ struct ScratchPool {
     int r_stride;
 };
 
-__device__ inline DpScratch thread_scratch(const ScratchPool& pool) {
+__device__ inline DpScratch thread_scratch(const ScratchPool& pool, int4* prof) {
     DpScratch sc;
+    sc.prof = prof;
     sc.ptr_words = pool.ptr_words;
     sc.brow = pool.brow;
     sc.cols = pool.cols;
@@ -94,7 +95,6 @@ __device__ inline DpScratch thread_scratch(const ScratchPool& pool) {
 }
 
 // getPrimerEndIndexInRead (HSQ/process/ExtendReadsToPrimer.java:286-345)
-template <bool LUT>
 __device__ inline int primer_end_index(const SeqView& primer, const SeqView& read, const ScoreParams& sp_default,
                                        const DpScratch& sc, int* status, int64_t* cells) {
     int L = read.len;
@@ -103,7 +103,7 @@ __device__ inline int primer_end_index(const SeqView& primer, const SeqView& rea
         atomicMin(status, HSQ_ERR_OUT_OF_RANGE);
         return HSQ_PRIMER_NOT_FOUND;
     }
-    dp_fill<LUT>(prefix, primer, sp_default, /*pen_start=*/1, /*pen_end=*/0, sc);  // ref = read prefix, query = primer (:290-293)
+    dp_fill(prefix, primer, sp_default, /*pen_start=*/1, /*pen_end=*/0, sc);  // ref = read prefix, query = primer (:290-293)
     *cells += (int64_t)prefix.len * primer.len;
     int n = dp_traceback(prefix, primer, sc);
     bool passed = false;
@@ -122,83 +122,8 @@ __device__ inline int primer_end_index(const SeqView& primer, const SeqView& rea
     return pe - 1;
 }
 
-// One read end per thread: ExtendReadsToPrimer.extendReadPair strand logic (:96-198) +
-// calculateDetailsForReadExtensionToPrimer (:200-245).
-template <bool LUT_USER>
-__global__ void __launch_bounds__(128) extend_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
-                                                     DeviceSeqs r2, int64_t n_pairs, ScoreParams sp_default, ScoreParams sp_user,
-                                                     ScratchPool pool, ExtendDeviceOut out, int* status,
-                                                     unsigned long long* cells_total) {
-    DpScratch sc = thread_scratch(pool);
-    int64_t cells = 0;
-    const int64_t n_tasks = 2 * n_pairs;
-    for (int64_t m = sc.tid; m < n_tasks; m += sc.nthreads) {
-        const int64_t k = m >> 1;
-        const int mate = (int)(m & 1);
-        const int pid = probe_id[k];
-        const bool one_rev = probes.reverse_strand[pid] != 0;
-        SeqView primer, capture, read;
-        bool is_reversed;
-        int adjacent;
-        {
-            int64_t t0 = probes.target.offsets[pid];
-            int tl = (int)(probes.target.offsets[pid + 1] - t0);
-            if (mate == 0) {  // :114-126
-                int64_t p0 = probes.ext.offsets[pid];
-                primer = make_view(probes.ext.codes + p0, (int)(probes.ext.offsets[pid + 1] - p0), false, one_rev);
-                capture = make_view(probes.target.codes + t0, tl, false, one_rev);
-                int64_t s0 = r1.offsets[k];
-                read = make_view(r1.codes + s0, (int)(r1.offsets[k + 1] - s0), false, one_rev);
-                is_reversed = one_rev;
-                adjacent = one_rev ? probes.ext_start[pid] : probes.ext_stop[pid];  // :108-112
-            } else {  // :150-162 (sequenceTwo was complemented at :104)
-                int64_t p0 = probes.lig.offsets[pid];
-                primer = make_view(probes.lig.codes + p0, (int)(probes.lig.offsets[pid + 1] - p0), true, one_rev);
-                capture = make_view(probes.target.codes + t0, tl, true, one_rev);
-                int64_t s0 = r2.offsets[k];
-                read = make_view(r2.codes + s0, (int)(r2.offsets[k + 1] - s0), false, !one_rev);
-                is_reversed = !one_rev;
-                adjacent = one_rev ? probes.lig_stop[pid] : probes.lig_start[pid];  // :137,:143 (finalize_kernel restores the :133 quirk)
-            }
-        }
-        int ok = 0, score = 0, pos = 0, read_start = 0, read_stop = 0, nm = 0, ref_len = 0;
-        SlotWriter cw{out.cigar + m * out.cigar_cap, out.cigar_cap, 0};
-        SlotWriter mw{out.md + m * out.md_cap, out.md_cap, 0};
-        const int L = read.len;
-        int e = primer_end_index<true>(primer, read, sp_default, sc, status, &cells);
-        if (e != HSQ_PRIMER_NOT_FOUND && e >= 0 && e < L) {  // :206
-            const int start = e + 1;
-            SeqView rw = sub_view(read, start, L - start);  // read[e+1 .. L-1] (:210)
-            score = dp_fill<LUT_USER>(capture, rw, sp_user, 0, 0, sc);  // :211
-            cells += (int64_t)capture.len * rw.len;
-            const int read_length = rw.len - 1;  // :225
-            // score/alignmentLength > 0 (:212): the alignment has max(Q,R) >= 1 columns whenever score != 0
-            if (score > 0 && read_length > LENGTH_THRESHOLD_FOR_EXTENDED_READ) {
-                Columns cv{sc, dp_traceback(capture, rw, sc)};
-                int last_q = cv.n - 1;  // getAlignmentWithoutEndingQueryInserts (:218)
-                while (last_q >= 0 && col_qry(cv.fwd(last_q)) == CODE_GAP) last_q--;
-                emit_cigar_md(cv, 0, last_q, is_reversed, &cw, &mw, &nm, &ref_len);  // :220-231
-                pos = is_reversed ? adjacent - ref_len : adjacent + 1;                 // :234,:236
-                read_start = start;
-                read_stop = start + read_length;
-                ok = 1;
-            }
-        }
-        out.ok[m] = (uint8_t)ok;
-        out.primer_end[m] = e;
-        out.score[m] = score;
-        out.pos[m] = pos;
-        out.read_start[m] = read_start;
-        out.read_stop[m] = read_stop;
-        out.nm[m] = nm;
-        out.ref_len[m] = ref_len;
-        out.cigar_len[m] = cw.len;
-        out.md_len[m] = mw.len;
-        out.overflow[m] = (uint8_t)((cw.len > cw.cap ? 1 : 0) | (mw.len > mw.cap ? 2 : 0));
-    }
-    for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
-    if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
-}
+// The extend pipeline (primer stage, bucketing, capture stage) lives in hsq_extend.cuh.
+#define HSQ_EXTEND_KERNELS_HERE
 
 // Per pair: both-mates flag (ExtendReadsToPrimer.java:364), TLEN (:136-142,:168-178), and the reference's quirk that
 // read two's adjacent primer position is only switched to the ligation primer when read one extended (:133-144).
@@ -228,17 +153,17 @@ struct AlignDeviceOut {
 };
 
 // Operator seam: NeedlemanWunschGlobalAlignment + AlignmentPair getters, one alignment per thread.
-template <bool LUT>
-__global__ void __launch_bounds__(128) align_kernel(DeviceSeqs refs, DeviceSeqs qrys, int64_t n, ScoreParams sp, int pen_start,
+__global__ void __launch_bounds__(DP_BLOCK) align_kernel(DeviceSeqs refs, DeviceSeqs qrys, int64_t n, ScoreParams sp, int pen_start,
                                                     int pen_end, ScratchPool pool, AlignDeviceOut out, int* status,
                                                     unsigned long long* cells_total) {
-    DpScratch sc = thread_scratch(pool);
+    __shared__ int4 prof[PROF_INT4_PER_THREAD * DP_BLOCK];
+    DpScratch sc = thread_scratch(pool, prof);
     int64_t cells = 0;
     for (int64_t k = sc.tid; k < n; k += sc.nthreads) {
         int64_t r0 = refs.offsets[k], q0 = qrys.offsets[k];
         SeqView ref = make_view(refs.codes + r0, (int)(refs.offsets[k + 1] - r0), false, false);
         SeqView qry = make_view(qrys.codes + q0, (int)(qrys.offsets[k + 1] - q0), false, false);
-        int score = dp_fill<LUT>(ref, qry, sp, pen_start, pen_end, sc);
+        int score = dp_fill(ref, qry, sp, pen_start, pen_end, sc);
         cells += (int64_t)ref.len * qry.len;
         Columns cv{sc, dp_traceback(ref, qry, sc)};
         PairIndices ix = pair_indices(cv);
