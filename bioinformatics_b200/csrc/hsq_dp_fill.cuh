@@ -25,6 +25,83 @@ __device__ inline void build_profile(const uint32_t (&q)[KROWS], const ScorePara
     }
 }
 
+// profile slot of a raw reference code: 0..3 for A,C,G,T (after the view's complement), 4 = build the column on the fly
+__device__ __forceinline__ int prof_slot(uint32_t raw, int comp) {
+    const bool one_hot = (raw - 1u) < 8u && (raw & (raw - 1u)) == 0u;
+    const int idx = 31 - __clz((int)raw);
+    return one_hot ? (comp ? 3 - idx : idx) : 4;
+}
+
+// One strip (16 query rows starting below row i0) swept over all R columns.  The row above the strip is read from the
+// boundary row in scratch (X per column) and replaced by the strip's last row.  Reference code and boundary value of
+// column j+1 are fetched while column j is computed.
+template <bool HFREE>
+__device__ __forceinline__ void dp_strip(const SeqView& ref, const SeqView& qry, const ScoreParams& sp, int pen_start, bool free_end,
+                                         const DpScratch& sc, int s, bool last_strip, int* final_d4) {
+    const int R = ref.len, Q = qry.len;
+    const int i0 = s * KROWS;
+    const int rstar = last_strip ? (Q - 1 - i0) : -1;  // strip-local index of row Q
+    int D4[KROWS], H0[KROWS];
+    {
+        uint32_t q[KROWS];
+#pragma unroll
+        for (int r = 0; r < KROWS; r++) {
+            const int i = i0 + 1 + r;
+            q[r] = (i <= Q) ? (uint32_t)qry.get(i - 1) : 0u;
+            const int s0 = 4 * border_score(i, pen_start, sp.gap_start);
+            D4[r] = s0;
+            // column-0 cells point UP: never a LEFT continuation -> hout0 = D4
+            H0[r] = (HFREE && r == rstar) ? s0 + (2 - sp.kh) : s0;
+        }
+        build_profile(q, sp, sc.prof);
+    }
+    int diag_d4 = (i0 == 0) ? 0 : 4 * border_score(i0, pen_start, sp.gap_start);
+    uint32_t* wordp = &sc.word(s, 1);
+    int32_t* browp = &sc.b(1);
+    const uint8_t* rp = ref.base + ref.start;
+    const int64_t rstep = ref.step;
+    const int64_t nt = sc.nthreads;
+    uint32_t next_raw = *rp;
+    int next_up = *browp;
+    for (int j = 1; j <= R; j++) {
+        const uint32_t raw = next_raw;
+        const int upx = next_up;
+        if (j < R) {  // prefetch column j+1
+            rp += rstep;
+            next_raw = *rp;
+            next_up = browp[nt];
+        }
+        const int up_d4 = upx & ~3;
+        const bool vfree = free_end && (j == R);
+        const int up_v0 = vfree ? up_d4 + (1 - sp.kv) : (upx & 1) * sp.c4 + up_d4;
+        int b = prof_slot(raw, ref.comp);
+        if (b == 4) {  // ambiguity code, N, U or gap character in the reference: build this column's scores in the scratch slot
+            const uint32_t rcode = ref.comp ? complement_code((uint8_t)raw) : raw;
+            int* slot = reinterpret_cast<int*>(sc.prof + 16 * DP_BLOCK + threadIdx.x);
+#pragma unroll 1
+            for (int r = 0; r < KROWS; r++) {
+                const int i = i0 + 1 + r;
+                slot[(r >> 2) * DP_BLOCK * 4 + (r & 3)] = match4((i <= Q) ? (uint32_t)qry.get(i - 1) : 0u, rcode, sp);
+            }
+        }
+        const int4* pcol = sc.prof + b * 4 * DP_BLOCK + threadIdx.x;
+        uint32_t w;
+        int xlast;
+        if (!vfree) xlast = dp_column<HFREE, false>(D4, H0, pcol, up_v0, diag_d4, sp, rstar, &w);
+        else xlast = dp_column<HFREE, true>(D4, H0, pcol, up_v0, diag_d4, sp, rstar, &w);
+        *wordp = w;
+        if (!last_strip) *browp = xlast;
+        diag_d4 = up_d4;
+        wordp += nt;
+        browp += nt;
+    }
+    if (last_strip) {
+#pragma unroll
+        for (int r = 0; r < KROWS; r++)
+            if (r == rstar) *final_d4 = D4[r];
+    }
+}
+
 // Fills the matrix for (ref R columns, query Q rows); pointer words go to scratch.  Returns the score S[Q][R].
 __device__ inline int dp_fill(const SeqView& ref, const SeqView& qry, const ScoreParams& sp, int pen_start, int pen_end,
                               const DpScratch& sc) {
@@ -33,74 +110,15 @@ __device__ inline int dp_fill(const SeqView& ref, const SeqView& qry, const Scor
     if (R == 0) return border_score(Q, pen_start, sp.gap_start);
     const int n_strips = (Q + KROWS - 1) / KROWS;
     const bool free_end = !pen_end;
-    int final_d4 = 0;
-    for (int s = 0; s < n_strips; s++) {
-        const int i0 = s * KROWS;  // row above the strip
-        const bool last_strip = (s == n_strips - 1);
-        const int rstar = last_strip ? (Q - 1 - i0) : -1;  // strip-local index of row Q
-        int D4[KROWS], H0[KROWS];
-        {
-            uint32_t q[KROWS];
-#pragma unroll
-            for (int r = 0; r < KROWS; r++) {
-                const int i = i0 + 1 + r;
-                q[r] = (i <= Q) ? (uint32_t)qry.get(i - 1) : 0u;
-                const int s0 = 4 * border_score(i, pen_start, sp.gap_start);
-                D4[r] = s0;
-                // column-0 cells point UP: never a LEFT continuation -> hout0 = D4
-                H0[r] = (free_end && r == rstar) ? s0 + (2 - sp.kh) : s0;
-            }
-            build_profile(q, sp, sc.prof);
-        }
-        int diag_d4 = (i0 == 0) ? 0 : 4 * border_score(i0, pen_start, sp.gap_start);
-        const bool hfree = free_end && last_strip;
-        uint32_t* wordp = &sc.word(s, 1);
-        int32_t* browp = &sc.b(1);
-        for (int j = 1; j <= R; j++, wordp += sc.nthreads, browp += sc.nthreads) {
-            const bool vfree = free_end && (j == R);
-            const uint32_t rcode = (uint32_t)ref.get(j - 1);
-            int up_d4, up_v0;
-            if (s == 0) {  // row-0 cells point LEFT: never an UP continuation
-                up_d4 = 4 * border_score(j, pen_start, sp.gap_start);
-                up_v0 = up_d4;
-            } else {
-                const int x = *browp;
-                up_d4 = x & ~3;
-                up_v0 = (x & 1) * sp.c4 + up_d4;
-            }
-            if (vfree) up_v0 = up_d4 + (1 - sp.kv);
-            int b;
-            if (rcode == 1u || rcode == 2u || rcode == 4u || rcode == 8u) {
-                b = 31 - __clz(rcode);
-            } else {  // ambiguity code, N, U or gap character in the reference: build this column's scores in the scratch slot
-                b = 4;
-                int* slot = reinterpret_cast<int*>(sc.prof + 16 * DP_BLOCK + threadIdx.x);
-#pragma unroll 1
-                for (int r = 0; r < KROWS; r++) {
-                    const int i = i0 + 1 + r;
-                    slot[(r >> 2) * DP_BLOCK * 4 + (r & 3)] = match4((i <= Q) ? (uint32_t)qry.get(i - 1) : 0u, rcode, sp);
-                }
-            }
-            const int4* pcol = sc.prof + b * 4 * DP_BLOCK + threadIdx.x;
-            uint32_t w;
-            int xlast;
-            if (!hfree) {
-                if (!vfree) xlast = dp_column<false, false>(D4, H0, pcol, up_v0, diag_d4, sp, rstar, &w);
-                else xlast = dp_column<false, true>(D4, H0, pcol, up_v0, diag_d4, sp, rstar, &w);
-            } else {
-                if (!vfree) xlast = dp_column<true, false>(D4, H0, pcol, up_v0, diag_d4, sp, rstar, &w);
-                else xlast = dp_column<true, true>(D4, H0, pcol, up_v0, diag_d4, sp, rstar, &w);
-            }
-            *wordp = w;
-            if (!last_strip) *browp = xlast;
-            diag_d4 = up_d4;
-        }
-        if (last_strip) {
-#pragma unroll
-            for (int r = 0; r < KROWS; r++)
-                if (r == rstar) final_d4 = D4[r];
-        }
+    // boundary row for strip 0 = matrix row 0: cells point LEFT (never an UP continuation)
+    {
+        int32_t* bp = &sc.b(1);
+        for (int j = 1; j <= R; j++, bp += sc.nthreads) *bp = 4 * border_score(j, pen_start, sp.gap_start) + (int)P_LEFT;
     }
+    int final_d4 = 0;
+    for (int s = 0; s < n_strips - 1; s++) dp_strip<false>(ref, qry, sp, pen_start, free_end, sc, s, false, &final_d4);
+    if (free_end) dp_strip<true>(ref, qry, sp, pen_start, true, sc, n_strips - 1, true, &final_d4);
+    else dp_strip<false>(ref, qry, sp, pen_start, false, sc, n_strips - 1, true, &final_d4);
     return final_d4 >> 2;
 }
 

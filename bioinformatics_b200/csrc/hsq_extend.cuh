@@ -151,7 +151,7 @@ __global__ void bucket_scatter_kernel(const uint32_t* __restrict__ key, int64_t 
 }
 
 // Stage 2: calculateDetailsForReadExtensionToPrimer (:200-245) for the read ends that reached DP#2, in bucket order.
-__global__ void __launch_bounds__(DP_BLOCK) capture_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
+__global__ void __launch_bounds__(DP_BLOCK, 5) capture_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
                                                            DeviceSeqs r2, const uint32_t* __restrict__ order,
                                                            const uint32_t* __restrict__ n_active_ptr, ScoreParams sp_user,
                                                            ScratchPool pool, ExtendDeviceOut out, unsigned long long* cells_total) {
