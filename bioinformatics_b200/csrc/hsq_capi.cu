@@ -2,6 +2,7 @@
 // There is no CPU fallback: every entry point needs a context, and a context needs a CUDA device.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include "hsq_host.cuh"
 #include "hsq_extend.cuh"
@@ -58,16 +59,27 @@ int persistent_grid(hsq_ctx* ctx, K kernel, int block, int64_t n_tasks, int* gri
     return HSQ_OK;
 }
 
-int alloc_scratch(hsq_ctx* ctx, int64_t nthreads, int q_max, int r_max, ScratchPool* pool) {
-    int n_strips = (q_max + KROWS - 1) / KROWS;
+// Scratch of the DP kernels: `nthreads` resident threads of the 32-bit kernels and `nthreads2` of the packed kernels
+// (which run one after the other on the context's stream and share the same allocations).
+int alloc_scratch(hsq_ctx* ctx, int64_t nthreads, int64_t nthreads2, int q_max, int r_max, ScratchPool* pool, ScratchPool2* pool2) {
+    size_t n_strips = (size_t)(q_max + KROWS - 1) / KROWS;
     if (n_strips < 1) n_strips = 1;
+    const size_t rs = (size_t)r_max + 1, t1 = (size_t)nthreads, t2 = (size_t)nthreads2;
+    HSQ_CUDA(ctx, ctx->ptr_words.ensure(std::max(t1 * sizeof(uint32_t), t2 * sizeof(uint2)) * n_strips * rs));
+    HSQ_CUDA(ctx, ctx->brow.ensure(std::max(t1, t2) * rs * sizeof(int32_t)));
+    HSQ_CUDA(ctx, ctx->cols.ensure(std::max(t1, t2) * (size_t)(q_max + r_max + 1) * sizeof(uint16_t)));
+    HSQ_CUDA(ctx, ctx->slow.ensure(t2 * KROWS * sizeof(uint32_t) + 16));
     pool->r_stride = r_max + 1;
-    HSQ_CUDA(ctx, ctx->ptr_words.ensure((size_t)nthreads * n_strips * (size_t)(r_max + 1) * sizeof(uint32_t)));
-    HSQ_CUDA(ctx, ctx->brow.ensure((size_t)nthreads * (size_t)(r_max + 1) * sizeof(int32_t)));
-    HSQ_CUDA(ctx, ctx->cols.ensure((size_t)nthreads * (size_t)(q_max + r_max + 1) * sizeof(uint16_t)));
     pool->ptr_words = ctx->ptr_words.as<uint32_t>();
     pool->brow = ctx->brow.as<int32_t>();
     pool->cols = ctx->cols.as<uint16_t>();
+    if (pool2) {
+        pool2->r_stride = r_max + 1;
+        pool2->ptr_words = ctx->ptr_words.as<uint2>();
+        pool2->brow = ctx->brow.as<uint32_t>();
+        pool2->cols = ctx->cols.as<uint16_t>();
+        pool2->slow = ctx->slow.as<uint32_t>();
+    }
     return HSQ_OK;
 }
 
@@ -126,6 +138,8 @@ int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) {
     std::vector<double> tbl(POW95_N);
     for (int d = 0; d < POW95_N; d++) tbl[(size_t)d] = std::pow(0.95, (double)d);
     HSQ_CUDA(nullptr, cudaMemcpyToSymbol(c_pow95, tbl.data(), sizeof(double) * POW95_N));
+    const char* f32 = getenv("HSQ_FORCE_DP32");  // development / test switch: always use the 32-bit DP kernels
+    ctx->force_dp32 = f32 && f32[0] == '1';
     *out = ctx;
     return HSQ_OK;
 }
@@ -137,7 +151,7 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     hsq::DevBuf* bufs[] = {&ctx->p_rev, &ctx->p_ext_start, &ctx->p_ext_stop, &ctx->p_lig_start, &ctx->p_lig_stop, &ctx->q1, &ctx->q2,
                            &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
                            &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
-                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags};
+                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow};
     for (auto* b : bufs) b->release();
     hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb};
     for (auto* s : seqs) s->release();

@@ -16,7 +16,7 @@ int run_align(hsq_ctx* ctx, const hsq_seqs* refs, const hsq_seqs* qrys, const hs
     int grid = 1;
     if ((rc = persistent_grid(ctx, align_kernel, DP_BLOCK, n, &grid))) return rc;
     ScratchPool pool;
-    if ((rc = alloc_scratch(ctx, (int64_t)grid * DP_BLOCK, q_max, r_max, &pool))) return rc;
+    if ((rc = alloc_scratch(ctx, (int64_t)grid * DP_BLOCK, 0, q_max, r_max, &pool, nullptr))) return rc;
     const size_t nn = (size_t)n;
     HSQ_CUDA(ctx, ctx->out_i32.ensure(12 * nn * sizeof(int32_t) + 16));
     HSQ_CUDA(ctx, ctx->out_u8.ensure(nn + 16));

@@ -54,18 +54,29 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
     const int r_max = std::max(ctx->p_target.max_len, std::min(read_max, primer_max + PRIMER_ALIGNMENT_BUFFER + 1));
     ScoreParams sp_default = make_score_params(1, -4, -1, -6);  // SimpleAlignmentScorer defaults (ExtendReadsToPrimer.java:290-291)
     ScoreParams sp_user = make_score_params(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start);
+    // packed u16x2 cells when every score fits 14 bits (always, for HSQUtils' scorers at these lengths), else 32-bit cells
+    const bool packed = !ctx->force_dp32 &&
+                        dp2_score_range_ok(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start, q_max, r_max);
+    ScoreParams2 sp_user2 = make_score_params2(sp_user);
     int grid1 = 1, grid2 = 1;
     if ((rc = persistent_grid(ctx, primer_kernel, DP_BLOCK, 2 * n, &grid1))) return rc;
-    if ((rc = persistent_grid(ctx, capture_kernel, DP_BLOCK, 2 * n, &grid2))) return rc;
+    if (packed) rc = persistent_grid(ctx, capture2_kernel, DP2_BLOCK, n + 1, &grid2);
+    else rc = persistent_grid(ctx, capture_kernel, DP_BLOCK, 2 * n, &grid2);
+    if (rc) return rc;
     ScratchPool pool;
-    if ((rc = alloc_scratch(ctx, (int64_t)std::max(grid1, grid2) * DP_BLOCK, q_max, r_max, &pool))) return rc;
-    // bucket keys: (strips of DP#2, capture-target length); the last key collects read ends that stop after DP#1
+    ScratchPool2 pool2;
+    if ((rc = alloc_scratch(ctx, (int64_t)std::max(grid1, packed ? 1 : grid2) * DP_BLOCK, packed ? (int64_t)grid2 * DP2_BLOCK : 0, q_max, r_max,
+                            &pool, &pool2)))
+        return rc;
+    // bucket keys: exact DP#2 shape (rows = read remainder, columns = capture-target length); the last key collects the
+    // read ends that stop after DP#1.  Buckets are padded to even sizes (holes = ORDER_HOLE).
     BucketKeys keys;
     keys.key_stride = ctx->p_target.max_len + 1;
-    const int n_keys = ((read_max + KROWS - 1) / KROWS + 1) * keys.key_stride + 1;
+    const int n_keys = (read_max + 1) * keys.key_stride + 1;
     keys.skip_key = (uint32_t)(n_keys - 1);
+    const size_t order_bytes = (n2 + (size_t)n_keys + 2) * 4;
     HSQ_CUDA(ctx, ctx->sort_a.ensure(n2 * 4 + 16));
-    HSQ_CUDA(ctx, ctx->sort_b.ensure(n2 * 4 + 16));
+    HSQ_CUDA(ctx, ctx->sort_b.ensure(order_bytes + 16));
     HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)(2 * n_keys + 4) * 4));
     keys.key = ctx->sort_a.as<uint32_t>();
     uint32_t* order = ctx->sort_b.as<uint32_t>();
@@ -89,6 +100,7 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
     if (n > 0) {
         DeviceProbes pv = probe_view(ctx);
         HSQ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t)n_keys * 4, ctx->stream));
+        HSQ_CUDA(ctx, cudaMemsetAsync(order, 0xFF, order_bytes, ctx->stream));
         primer_kernel<<<grid1, DP_BLOCK, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), n, sp_default,
                                                           pool, d, keys, d_status(ctx), ctx->cells.as<unsigned long long>());
         const int sblocks = (int)std::min<int64_t>((2 * n + 255) / 256, (int64_t)ctx->sm_count * 8);
@@ -96,8 +108,12 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
         bucket_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist, n_keys, cursor);
         HSQ_CUDA(ctx, cudaMemcpyAsync(n_active, cursor + keys.skip_key, 4, cudaMemcpyDeviceToDevice, ctx->stream));
         bucket_scatter_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, 2 * n, cursor, order);
-        capture_kernel<<<grid2, DP_BLOCK, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), order, n_active,
-                                                           sp_user, pool, d, ctx->cells.as<unsigned long long>());
+        if (packed)
+            capture2_kernel<<<grid2, DP2_BLOCK, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), order,
+                                                                 n_active, sp_user2, pool2, d, ctx->cells.as<unsigned long long>());
+        else
+            capture_kernel<<<grid2, DP_BLOCK, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), order,
+                                                               n_active, sp_user, pool, d, ctx->cells.as<unsigned long long>());
         ctx->launches += 5;
         HSQ_CUDA(ctx, cudaGetLastError());
         finalize_extend_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), n, d,

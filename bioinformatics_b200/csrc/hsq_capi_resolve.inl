@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(DP_BLOCK) tie_break_kernel(DeviceSeqs r1, Devi
         SeqView qry = make_view(probe_full.codes + p0, pl, mate != 0, mate != 0);  // getReverseCompliment for read two (:731)
         dp_fill(ref, qry, sp, 0, 0, sc);
         cells += (int64_t)ref.len * qry.len;
-        Columns cv{sc, dp_traceback(ref, qry, sc)};
+        Columns cv{sc.colstore(), dp_traceback(ref, qry, sc)};
         PairIndices ix = pair_indices(cv);
         int m, x, rg, qg;
         count_columns(cv, 0, cv.n - 1, &m, &x, &rg, &qg);
@@ -100,7 +100,7 @@ extern "C" int32_t hsq_resolve_multi_probe(hsq_ctx* ctx, const hsq_candidates* c
         int grid = 1;
         if ((rc = persistent_grid(ctx, tie_break_kernel, DP_BLOCK, 2 * nc, &grid))) return rc;
         ScratchPool pool;
-        if ((rc = alloc_scratch(ctx, (int64_t)grid * DP_BLOCK, ctx->p_full.max_len, std::max(w[1], w[2]), &pool))) return rc;
+        if ((rc = alloc_scratch(ctx, (int64_t)grid * DP_BLOCK, 0, ctx->p_full.max_len, std::max(w[1], w[2]), &pool, nullptr))) return rc;
         tie_break_kernel<<<grid, DP_BLOCK, 0, ctx->stream>>>(ctx->r1.view(), ctx->r2.view(), ctx->p_full.view(), ctx->sort_a.as<int64_t>(),
                                                             ctx->sort_b.as<int32_t>(), n, nc, u, v, sp, pool, m2, e2,
                                                             ctx->cells.as<unsigned long long>());

@@ -54,6 +54,14 @@ inline ScoreParams make_score_params(int match, int mismatch, int gap_extend, in
     return s;
 }
 
+// Traceback columns of one thread (the view hsq_emit.cuh works on).
+struct ColStore {
+    uint16_t* cols;
+    int64_t nthreads;
+    int64_t tid;
+    __device__ inline uint16_t& col(int k) const { return cols[(int64_t)k * nthreads + tid]; }
+};
+
 // Per-thread scratch, interleaved by thread so that a warp's accesses coalesce: element e of thread t
 // sits at base[e * nthreads + t].
 struct DpScratch {
@@ -69,11 +77,19 @@ struct DpScratch {
     }
     __device__ inline int32_t& b(int j) const { return brow[(int64_t)j * nthreads + tid]; }
     __device__ inline uint16_t& col(int k) const { return cols[(int64_t)k * nthreads + tid]; }
+    __device__ inline ColStore colstore() const { return ColStore{cols, nthreads, tid}; }
 };
 
 // init score of a border cell k >= 1 (getInitialScore :342-376): gapStart + (k-1)*(gapScore(0)-1)
 __device__ __forceinline__ int border_score(int k, int pen_start, int gap_start) {
     return pen_start ? gap_start - (k - 1) : 0;
+}
+
+// acc * 2 + bit as one IMAD the compiler cannot re-associate (it otherwise rebuilds the bits with extra LOP3s)
+__device__ __forceinline__ uint32_t mad2(uint32_t acc, uint32_t bit) {
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, 2, %2;" : "=r"(r) : "r"(acc), "r"(bit));
+    return r;
 }
 
 // One column of one strip.  State per row r: D4[r], H0[r] (= hout0) of cell (i0+1+r, j-1) on entry, of column j on exit.
@@ -99,8 +115,8 @@ __device__ __forceinline__ int dp_column(int (&D4)[KROWS], int (&H0)[KROWS], con
         const int b0 = x & 1;
         int h0 = b1x2 * sp.c2 + d4;
         int v0 = b0 * sp.c4 + d4;
-        acc_l = acc_l * 2u + (uint32_t)b1x2;
-        acc_u = acc_u * 2u + (uint32_t)b0;
+        acc_l = mad2(acc_l, (uint32_t)b1x2);
+        acc_u = mad2(acc_u, (uint32_t)b0);
         if (HFREE) h0 = (r == rstar) ? d4 + (2 - sp.kh) : h0;  // bottom row, terminal gaps free (:286-300)
         if (VFREE) v0 = d4 + (1 - sp.kv);                       // last column, terminal gaps free (:270-284)
         D4[r] = d4;

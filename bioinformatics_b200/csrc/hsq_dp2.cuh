@@ -1,0 +1,273 @@
+// hsq_dp2.cuh -- the DP fill of hsq_dp.cuh for TWO alignments per thread, packed as the two u16 halves of a register.
+//
+// Same recurrence, same cell encoding (X = 4*S + p, candidates 4*score + {2,1,0}, see hsq_dp.cuh), but each half
+// carries its alignment's X biased by 0x8000 so that it is an unsigned 16-bit number:
+//   - the two maxima of a cell are VIADDMNMX.U16x2 (per-half wrapping add, per-half unsigned max);
+//   - every other step of the cell (mask, multiply by a small constant, add) is ordinary 32-bit integer arithmetic on
+//     the packed word, which is exact per half as long as every half stays inside [0, 65535] -- the host checks the
+//     score range of the scorer / lengths before choosing this kernel (dp2_score_range_ok) and otherwise runs the
+//     32-bit kernel.
+// So one instruction stream fills two matrices: half the instructions per cell of the 32-bit path.
+//
+// The two alignments of a thread have the SAME shape (Q rows, R columns): the bucket sort of hsq_extend.cuh keys read
+// ends by exact (Q, R) and pads every bucket to an even size.
+// Pointer words: per strip column two words, U bits and L bits; row r of the strip sits at bit 15-r of its half.
+#pragma once
+#include "hsq_dp.cuh"
+
+namespace hsq {
+
+static constexpr int DP2_BLOCK = 64;               // threads per block of the packed kernels
+static constexpr int PROF2_INT4_PER_THREAD = 32;   // 2 alignments x 4 one-hot bases x 16 rows x int32
+static constexpr uint32_t DP2_BIAS = 0x8000u;
+static constexpr uint32_t DP2_REP = 0x10001u;
+static constexpr uint32_t DP2_MASK_D4 = 0xFFFCFFFCu, DP2_MASK_B0 = 0x00010001u, DP2_MASK_B1X2 = 0x00020002u;
+
+struct ScoreParams2 {
+    uint32_t kh2, kv2;        // per-half wrapping addends: 4*gapStart + 2, 4*gapStart + 1
+    uint32_t c2, c4;          // 2*(gapExtend-gapStart), 4*(gapExtend-gapStart) as 32-bit multipliers (mod 2^32)
+    uint32_t hfree2, vfree2;  // (2 - kh) and (1 - kv) replicated: turn a D4 into the candidate-neutral free-gap output
+    int ms4, mm4, gap_start;
+};
+
+inline ScoreParams2 make_score_params2(const ScoreParams& s) {
+    ScoreParams2 p;
+    p.kh2 = ((uint32_t)s.kh & 0xFFFFu) * DP2_REP;
+    p.kv2 = ((uint32_t)s.kv & 0xFFFFu) * DP2_REP;
+    p.c2 = (uint32_t)s.c2;
+    p.c4 = (uint32_t)s.c4;
+    p.hfree2 = (uint32_t)(2 - s.kh) * DP2_REP;
+    p.vfree2 = (uint32_t)(1 - s.kv) * DP2_REP;
+    p.ms4 = s.ms4;
+    p.mm4 = s.mm4;
+    p.gap_start = s.gap_start;
+    return p;
+}
+
+// every score the fill can form (cells, candidates, the padding rows of the last strip) stays within +-bound
+inline bool dp2_score_range_ok(int match, int mismatch, int gap_extend, int gap_start, int q_max, int r_max) {
+    int64_t m = 1;
+    for (int v : {match, mismatch, gap_extend, gap_start}) m = std::max<int64_t>(m, v < 0 ? -(int64_t)v : v);
+    const int64_t bound = ((int64_t)q_max + KROWS + r_max + 4) * (m + 1);
+    return 4 * (bound + 2 * m + 2) + 3 < 32768;
+}
+
+struct DpScratch2 {
+    uint2* ptr_words;   // [n_strips_max * (r_max + 1)] per thread: (U word, L word)
+    uint32_t* brow;     // [r_max + 1] per thread: packed X of the row above the current strip
+    uint16_t* cols;     // [q_max + r_max] per thread: traceback columns of the alignment being emitted
+    uint32_t* slow;     // [KROWS] per thread: packed substitution scores of a column with a non-ACGT reference code
+    int4* prof;         // shared memory: [PROF2_INT4_PER_THREAD][DP2_BLOCK]
+    int64_t nthreads;
+    int64_t tid;
+    int r_stride;
+    __device__ inline uint2& word(int strip, int j) const { return ptr_words[((int64_t)strip * r_stride + j) * nthreads + tid]; }
+    __device__ inline uint32_t& b(int j) const { return brow[(int64_t)j * nthreads + tid]; }
+    __device__ inline uint16_t& col(int k) const { return cols[(int64_t)k * nthreads + tid]; }
+    __device__ inline ColStore colstore() const { return ColStore{cols, nthreads, tid}; }
+};
+
+__device__ __forceinline__ uint32_t border2(int k, int pen_start, int gap_start) {  // packed, biased 4*border_score
+    return (uint32_t)(4 * border_score(k, pen_start, gap_start) + (int)DP2_BIAS) * DP2_REP;
+}
+
+// One column of one strip for both alignments.  State per row: D4[r], H0[r] as in dp_column.
+template <bool HFREE, bool VFREE, bool SLOW>
+__device__ __forceinline__ uint32_t dp_column2(uint32_t (&D4)[KROWS], uint32_t (&H0)[KROWS], const int4* __restrict__ pcolA,
+                                               const int4* __restrict__ pcolB, const uint32_t* __restrict__ slow, int64_t nt,
+                                               uint32_t up_v0, uint32_t diag_d4, const ScoreParams2& sp, int rstar, uint2* word_out) {
+    uint32_t acc_l = 0, acc_u = 0;
+    uint32_t vin = up_v0;
+    uint32_t dg = diag_d4;
+    uint32_t x = 0;
+#pragma unroll
+    for (int r = 0; r < KROWS; r++) {
+        uint32_t dsub;
+        if (SLOW) {
+            dsub = dg + slow[r * nt];
+        } else {
+            int4 sa, sb;
+            if ((r & 3) == 0) {
+                sa = pcolA[(r >> 2) * DP2_BLOCK];
+                sb = pcolB[(r >> 2) * DP2_BLOCK];
+            }
+            const int a = (r & 3) == 0 ? sa.x : (r & 3) == 1 ? sa.y : (r & 3) == 2 ? sa.z : sa.w;
+            const int b = (r & 3) == 0 ? sb.x : (r & 3) == 1 ? sb.y : (r & 3) == 2 ? sb.z : sb.w;
+            dsub = dg + (uint32_t)a + (uint32_t)b;
+        }
+        x = __viaddmax_u16x2(H0[r], sp.kh2, __viaddmax_u16x2(vin, sp.kv2, dsub));
+        dg = D4[r];
+        const uint32_t d4 = x & DP2_MASK_D4;
+        const uint32_t b1x2 = x & DP2_MASK_B1X2;
+        const uint32_t b0 = x & DP2_MASK_B0;
+        uint32_t h0 = b1x2 * sp.c2 + d4;
+        uint32_t v0 = b0 * sp.c4 + d4;
+        acc_u = mad2(acc_u, b0);
+        if (r < KROWS - 1) acc_l = mad2(acc_l, b1x2);  // rows 0..14 land at bits 15..1 of their half
+        else acc_l = acc_l + (b1x2 >> 1);              // row 15 at bit 0
+        if (HFREE) h0 = (r == rstar) ? d4 + sp.hfree2 : h0;
+        if (VFREE) v0 = d4 + sp.vfree2;
+        D4[r] = d4;
+        H0[r] = h0;
+        vin = v0;
+    }
+    *word_out = make_uint2(acc_u, acc_l);
+    return x;
+}
+
+// Profile of one strip for both alignments: A's scores as plain int32 (low half), B's scores shifted to the high half,
+// so that  diag + A + B  is the packed diagonal candidate.
+__device__ inline void build_profile2(const uint32_t (&qa)[KROWS], const uint32_t (&qb)[KROWS], const ScoreParams2& sp, int4* prof) {
+#pragma unroll
+    for (int b = 0; b < 4; b++) {
+        const uint32_t code = 1u << b;
+#pragma unroll
+        for (int ch = 0; ch < 4; ch++) {
+            int4 v, w;
+            v.x = (qa[4 * ch + 0] & code) ? sp.ms4 : sp.mm4;
+            v.y = (qa[4 * ch + 1] & code) ? sp.ms4 : sp.mm4;
+            v.z = (qa[4 * ch + 2] & code) ? sp.ms4 : sp.mm4;
+            v.w = (qa[4 * ch + 3] & code) ? sp.ms4 : sp.mm4;
+            w.x = ((qb[4 * ch + 0] & code) ? sp.ms4 : sp.mm4) * 65536;
+            w.y = ((qb[4 * ch + 1] & code) ? sp.ms4 : sp.mm4) * 65536;
+            w.z = ((qb[4 * ch + 2] & code) ? sp.ms4 : sp.mm4) * 65536;
+            w.w = ((qb[4 * ch + 3] & code) ? sp.ms4 : sp.mm4) * 65536;
+            prof[(b * 4 + ch) * DP2_BLOCK + threadIdx.x] = v;
+            prof[(16 + b * 4 + ch) * DP2_BLOCK + threadIdx.x] = w;
+        }
+    }
+}
+
+template <bool HFREE>
+__device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& refB, const SeqView& qryA, const SeqView& qryB,
+                                          const ScoreParams2& sp, int pen_start, bool free_end, const DpScratch2& sc, int s,
+                                          bool last_strip, uint32_t* final_d4) {
+    const int R = refA.len, Q = qryA.len;
+    const int i0 = s * KROWS;
+    const int rstar = last_strip ? (Q - 1 - i0) : -1;
+    uint32_t D4[KROWS], H0[KROWS];
+    {
+        uint32_t qa[KROWS], qb[KROWS];
+#pragma unroll
+        for (int r = 0; r < KROWS; r++) {
+            const int i = i0 + 1 + r;
+            qa[r] = (i <= Q) ? (uint32_t)qryA.get(i - 1) : 0u;
+            qb[r] = (i <= Q) ? (uint32_t)qryB.get(i - 1) : 0u;
+            const uint32_t s0 = border2(i, pen_start, sp.gap_start);
+            D4[r] = s0;
+            H0[r] = (HFREE && r == rstar) ? s0 + sp.hfree2 : s0;
+        }
+        build_profile2(qa, qb, sp, sc.prof);
+    }
+    uint32_t diag_d4 = (i0 == 0) ? DP2_BIAS * DP2_REP : border2(i0, pen_start, sp.gap_start);
+    uint2* wordp = &sc.word(s, 1);
+    uint32_t* browp = &sc.b(1);
+    const uint8_t* rpa = refA.base + refA.start;
+    const uint8_t* rpb = refB.base + refB.start;
+    const int64_t stepa = refA.step, stepb = refB.step;
+    const int64_t nt = sc.nthreads;
+    uint32_t next_a = *rpa, next_b = *rpb;
+    uint32_t next_up = *browp;
+    for (int j = 1; j <= R; j++) {
+        const uint32_t rawa = next_a, rawb = next_b;
+        const uint32_t upx = next_up;
+        if (j < R) {
+            rpa += stepa;
+            rpb += stepb;
+            next_a = *rpa;
+            next_b = *rpb;
+            next_up = browp[nt];
+        }
+        const uint32_t up_d4 = upx & DP2_MASK_D4;
+        const bool vfree = free_end && (j == R);
+        const uint32_t up_v0 = vfree ? up_d4 + sp.vfree2 : (upx & DP2_MASK_B0) * sp.c4 + up_d4;
+        const int ba = prof_slot(rawa, refA.comp), bb = prof_slot(rawb, refB.comp);
+        uint2 w;
+        uint32_t xlast;
+        if (ba != 4 && bb != 4) {
+            const int4* pa = sc.prof + ba * 4 * DP2_BLOCK + threadIdx.x;
+            const int4* pb = sc.prof + (16 + bb * 4) * DP2_BLOCK + threadIdx.x;
+            if (!vfree) xlast = dp_column2<HFREE, false, false>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
+            else xlast = dp_column2<HFREE, true, false>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
+        } else {  // ambiguity code, N, U or gap character in a reference: this column's scores go through global scratch
+            const uint32_t ca = refA.comp ? complement_code((uint8_t)rawa) : rawa;
+            const uint32_t cb = refB.comp ? complement_code((uint8_t)rawb) : rawb;
+            uint32_t* sl = sc.slow + sc.tid;
+#pragma unroll 1
+            for (int r = 0; r < KROWS; r++) {
+                const int i = i0 + 1 + r;
+                const uint32_t qa = (i <= Q) ? (uint32_t)qryA.get(i - 1) : 0u;
+                const uint32_t qb = (i <= Q) ? (uint32_t)qryB.get(i - 1) : 0u;
+                const int va = ((qa & ca & MATCH_MASK) != 0) ? sp.ms4 : sp.mm4;
+                const int vb = ((qb & cb & MATCH_MASK) != 0) ? sp.ms4 : sp.mm4;
+                sl[r * nt] = (uint32_t)va + (uint32_t)vb * 65536u;
+            }
+            if (!vfree) xlast = dp_column2<HFREE, false, true>(D4, H0, nullptr, nullptr, sl, nt, up_v0, diag_d4, sp, rstar, &w);
+            else xlast = dp_column2<HFREE, true, true>(D4, H0, nullptr, nullptr, sl, nt, up_v0, diag_d4, sp, rstar, &w);
+        }
+        *wordp = w;
+        if (!last_strip) *browp = xlast;
+        diag_d4 = up_d4;
+        wordp += nt;
+        browp += nt;
+    }
+    if (last_strip) {
+#pragma unroll
+        for (int r = 0; r < KROWS; r++)
+            if (r == rstar) *final_d4 = D4[r];
+    }
+}
+
+__device__ __forceinline__ int dp2_unpack_score(uint32_t d4, int which) {
+    return ((int)((d4 >> (16 * which)) & 0xFFFFu) - (int)DP2_BIAS) >> 2;
+}
+
+// Fills both matrices (same shape: refA.len == refB.len, qryA.len == qryB.len).  Scores S[Q][R] go to score[0], score[1].
+__device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const SeqView& qryA, const SeqView& qryB,
+                                const ScoreParams2& sp, int pen_start, int pen_end, const DpScratch2& sc, int* score) {
+    const int R = refA.len, Q = qryA.len;
+    if (Q == 0 || R == 0) {
+        const int k = Q == 0 ? R : Q;
+        score[0] = score[1] = (k == 0) ? 0 : border_score(k, pen_start, sp.gap_start);
+        return;
+    }
+    const int n_strips = (Q + KROWS - 1) / KROWS;
+    const bool free_end = !pen_end;
+    {
+        uint32_t* bp = &sc.b(1);
+        for (int j = 1; j <= R; j++, bp += sc.nthreads) *bp = border2(j, pen_start, sp.gap_start) + (uint32_t)P_LEFT * DP2_REP;
+    }
+    uint32_t final_d4 = 0;
+    for (int s = 0; s < n_strips - 1; s++) dp_strip2<false>(refA, refB, qryA, qryB, sp, pen_start, free_end, sc, s, false, &final_d4);
+    if (free_end) dp_strip2<true>(refA, refB, qryA, qryB, sp, pen_start, true, sc, n_strips - 1, true, &final_d4);
+    else dp_strip2<false>(refA, refB, qryA, qryB, sp, pen_start, false, sc, n_strips - 1, true, &final_d4);
+    score[0] = dp2_unpack_score(final_d4, 0);
+    score[1] = dp2_unpack_score(final_d4, 1);
+}
+
+__device__ __forceinline__ uint32_t dp_pointer2(int i, int j, const DpScratch2& sc, int which) {
+    if (i == 0) return P_LEFT;
+    if (j == 0) return P_UP;
+    const int s = (i - 1) / KROWS, r = (i - 1) % KROWS;
+    const uint2 w = sc.word(s, j);
+    const int bit = 15 - r + 16 * which;
+    return (((w.y >> bit) & 1u) << 1) | ((w.x >> bit) & 1u);
+}
+
+// Traceback of alignment `which` of the pair (same output convention as dp_traceback).
+__device__ inline int dp_traceback2(const SeqView& ref, const SeqView& qry, const DpScratch2& sc, int which) {
+    int i = qry.len, j = ref.len, n = 0;
+    while (i > 0 || j > 0) {
+        const uint32_t p = dp_pointer2(i, j, sc, which);
+        uint32_t rc = CODE_GAP, qc = CODE_GAP;
+        if (p != P_UP) { rc = ref.get(j - 1); }
+        if (p != P_LEFT) { qc = qry.get(i - 1); }
+        if (p != P_UP) j--;
+        if (p != P_LEFT) i--;
+        sc.col(n) = (uint16_t)(rc | (qc << 8));
+        n++;
+    }
+    return n;
+}
+
+}  // namespace hsq

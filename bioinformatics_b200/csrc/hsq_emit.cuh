@@ -25,9 +25,9 @@ struct SlotWriter {  // bounded output slot; len keeps counting past cap so over
 };
 
 struct Columns {
-    DpScratch sc;
+    ColStore cs;
     int n;
-    __device__ inline uint32_t fwd(int c) const { return sc.col(n - 1 - c); }
+    __device__ inline uint32_t fwd(int c) const { return cs.col(n - 1 - c); }
 };
 
 __device__ __forceinline__ uint32_t col_ref(uint32_t w) { return w & 0xFFu; }

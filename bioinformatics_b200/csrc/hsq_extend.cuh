@@ -6,6 +6,7 @@
 // Reference: HSQ/process/ExtendReadsToPrimer.java:96-245,286-345.
 #pragma once
 #include "hsq_kernels.cuh"
+#include "hsq_dp2.cuh"
 
 namespace hsq {
 
@@ -68,7 +69,7 @@ __global__ void __launch_bounds__(DP_BLOCK) primer_kernel(DeviceProbes probes, c
         const bool reaches = (e != HSQ_PRIMER_NOT_FOUND && e >= 0 && e < L);  // :206
         if (reaches) {
             const int q = L - (e + 1);
-            keys.key[m] = (uint32_t)(((q + KROWS - 1) / KROWS) * keys.key_stride + v.capture.len);
+            keys.key[m] = (uint32_t)(q * keys.key_stride + v.capture.len);  // exact DP#2 shape (Q rows, R columns)
         } else {
             keys.key[m] = keys.skip_key;
             out.ok[m] = 0;
@@ -100,6 +101,7 @@ __global__ void bucket_hist_kernel(const uint32_t* __restrict__ key, int64_t n, 
 }
 
 // exclusive scan of the histogram into bucket cursors, one block
+// (every bucket is rounded up to an even size so that the packed kernel's pairs never straddle two shapes)
 __global__ void bucket_scan_kernel(uint32_t* __restrict__ hist, int n_keys, uint32_t* __restrict__ cursor) {
     __shared__ uint32_t warp_sums[32];
     __shared__ uint32_t carry;
@@ -108,7 +110,7 @@ __global__ void bucket_scan_kernel(uint32_t* __restrict__ hist, int n_keys, uint
     const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
     for (int base = 0; base < n_keys; base += blockDim.x) {
         const int i = base + threadIdx.x;
-        const uint32_t v = i < n_keys ? hist[i] : 0;
+        const uint32_t v = i < n_keys ? ((hist[i] + 1u) & ~1u) : 0;
         uint32_t x = v;
         for (int o = 1; o < 32; o <<= 1) {
             uint32_t y = __shfl_up_sync(0xffffffffu, x, o);
@@ -150,7 +152,42 @@ __global__ void bucket_scatter_kernel(const uint32_t* __restrict__ key, int64_t 
     }
 }
 
+// What follows DP#2 for one read end (:212-236): acceptance test, traceback, CIGAR / MD / NM / POS, result stores.
+// `traceback` fills the thread's column store and returns the number of alignment columns.
+template <class Traceback>
+__device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqView& rw, int start, int score, const ColStore& cs,
+                                               Traceback traceback, const ExtendDeviceOut& out, int64_t m) {
+    int ok = 0, pos = 0, read_start = 0, read_stop = 0, nm = 0, ref_len = 0;
+    SlotWriter cw{out.cigar + m * out.cigar_cap, out.cigar_cap, 0};
+    SlotWriter mw{out.md + m * out.md_cap, out.md_cap, 0};
+    const int read_length = rw.len - 1;  // :225
+    // score/alignmentLength > 0 (:212): the alignment has max(Q,R) >= 1 columns whenever score != 0
+    if (score > 0 && read_length > LENGTH_THRESHOLD_FOR_EXTENDED_READ) {
+        Columns cv{cs, traceback()};
+        int last_q = cv.n - 1;  // getAlignmentWithoutEndingQueryInserts (:218)
+        while (last_q >= 0 && col_qry(cv.fwd(last_q)) == CODE_GAP) last_q--;
+        emit_cigar_md(cv, 0, last_q, v.is_reversed, &cw, &mw, &nm, &ref_len);  // :220-231
+        pos = v.is_reversed ? v.adjacent - ref_len : v.adjacent + 1;           // :234,:236
+        read_start = start;
+        read_stop = start + read_length;
+        ok = 1;
+    }
+    out.ok[m] = (uint8_t)ok;
+    out.score[m] = score;
+    out.pos[m] = pos;
+    out.read_start[m] = read_start;
+    out.read_stop[m] = read_stop;
+    out.nm[m] = nm;
+    out.ref_len[m] = ref_len;
+    out.cigar_len[m] = cw.len;
+    out.md_len[m] = mw.len;
+    out.overflow[m] = (uint8_t)((cw.len > cw.cap ? 1 : 0) | (mw.len > mw.cap ? 2 : 0));
+}
+
+static constexpr uint32_t ORDER_HOLE = 0xFFFFFFFFu;  // padding entry of an odd-sized bucket
+
 // Stage 2: calculateDetailsForReadExtensionToPrimer (:200-245) for the read ends that reached DP#2, in bucket order.
+// 32-bit cells, one read end per thread: the general kernel (any integer scorer, any length).
 __global__ void __launch_bounds__(DP_BLOCK, 5) capture_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
                                                            DeviceSeqs r2, const uint32_t* __restrict__ order,
                                                            const uint32_t* __restrict__ n_active_ptr, ScoreParams sp_user,
@@ -160,38 +197,66 @@ __global__ void __launch_bounds__(DP_BLOCK, 5) capture_kernel(DeviceProbes probe
     int64_t cells = 0;
     const int64_t n_active = (int64_t)*n_active_ptr;
     for (int64_t t = sc.tid; t < n_active; t += sc.nthreads) {
-        const int64_t m = order[t];
+        const uint32_t mo = order[t];
+        if (mo == ORDER_HOLE) continue;
+        const int64_t m = mo;
         ReadEndViews v = read_end_views(probes, probe_id, r1, r2, m);
-        const int L = v.read.len;
         const int start = out.primer_end[m] + 1;
-        SeqView rw = sub_view(v.read, start, L - start);  // read[e+1 .. L-1] (:210)
-        int ok = 0, pos = 0, read_start = 0, read_stop = 0, nm = 0, ref_len = 0;
-        SlotWriter cw{out.cigar + m * out.cigar_cap, out.cigar_cap, 0};
-        SlotWriter mw{out.md + m * out.md_cap, out.md_cap, 0};
+        SeqView rw = sub_view(v.read, start, v.read.len - start);  // read[e+1 .. L-1] (:210)
         const int score = dp_fill(v.capture, rw, sp_user, 0, 0, sc);  // :211
         cells += (int64_t)v.capture.len * rw.len;
-        const int read_length = rw.len - 1;  // :225
-        // score/alignmentLength > 0 (:212): the alignment has max(Q,R) >= 1 columns whenever score != 0
-        if (score > 0 && read_length > LENGTH_THRESHOLD_FOR_EXTENDED_READ) {
-            Columns cv{sc, dp_traceback(v.capture, rw, sc)};
-            int last_q = cv.n - 1;  // getAlignmentWithoutEndingQueryInserts (:218)
-            while (last_q >= 0 && col_qry(cv.fwd(last_q)) == CODE_GAP) last_q--;
-            emit_cigar_md(cv, 0, last_q, v.is_reversed, &cw, &mw, &nm, &ref_len);  // :220-231
-            pos = v.is_reversed ? v.adjacent - ref_len : v.adjacent + 1;           // :234,:236
-            read_start = start;
-            read_stop = start + read_length;
-            ok = 1;
-        }
-        out.ok[m] = (uint8_t)ok;
-        out.score[m] = score;
-        out.pos[m] = pos;
-        out.read_start[m] = read_start;
-        out.read_stop[m] = read_stop;
-        out.nm[m] = nm;
-        out.ref_len[m] = ref_len;
-        out.cigar_len[m] = cw.len;
-        out.md_len[m] = mw.len;
-        out.overflow[m] = (uint8_t)((cw.len > cw.cap ? 1 : 0) | (mw.len > mw.cap ? 2 : 0));
+        capture_finish(v, rw, start, score, sc.colstore(), [&]() { return dp_traceback(v.capture, rw, sc); }, out, m);
+    }
+    for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
+    if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
+}
+
+struct ScratchPool2 {
+    uint2* ptr_words;
+    uint32_t* brow;
+    uint16_t* cols;
+    uint32_t* slow;
+    int r_stride;
+};
+
+__device__ inline DpScratch2 thread_scratch2(const ScratchPool2& pool, int4* prof) {
+    DpScratch2 sc;
+    sc.prof = prof;
+    sc.ptr_words = pool.ptr_words;
+    sc.brow = pool.brow;
+    sc.cols = pool.cols;
+    sc.slow = pool.slow;
+    sc.nthreads = (int64_t)gridDim.x * blockDim.x;
+    sc.tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    sc.r_stride = pool.r_stride;
+    return sc;
+}
+
+// Stage 2, packed: two read ends of the same DP#2 shape per thread (entries 2t, 2t+1 of the padded bucket order),
+// cells as u16x2 halves (hsq_dp2.cuh).  Chosen by the host when the scorer's score range fits 14 bits.
+__global__ void __launch_bounds__(DP2_BLOCK, 7) capture2_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
+                                                             DeviceSeqs r2, const uint32_t* __restrict__ order,
+                                                             const uint32_t* __restrict__ n_active_ptr, ScoreParams2 sp_user,
+                                                             ScratchPool2 pool, ExtendDeviceOut out, unsigned long long* cells_total) {
+    __shared__ int4 prof[PROF2_INT4_PER_THREAD * DP2_BLOCK];
+    DpScratch2 sc = thread_scratch2(pool, prof);
+    int64_t cells = 0;
+    const int64_t n_slots = (int64_t)*n_active_ptr >> 1;  // bucket sizes are even
+    for (int64_t t = sc.tid; t < n_slots; t += sc.nthreads) {
+        const uint2 mo = reinterpret_cast<const uint2*>(order)[t];
+        const bool has_b = mo.y != ORDER_HOLE;
+        const int64_t ma = mo.x, mb = has_b ? mo.y : mo.x;
+        ReadEndViews va = read_end_views(probes, probe_id, r1, r2, ma);
+        ReadEndViews vb = read_end_views(probes, probe_id, r1, r2, mb);
+        const int start_a = out.primer_end[ma] + 1, start_b = out.primer_end[mb] + 1;
+        SeqView rwa = sub_view(va.read, start_a, va.read.len - start_a);
+        SeqView rwb = sub_view(vb.read, start_b, vb.read.len - start_b);
+        int score[2];
+        dp_fill2(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score);
+        cells += (int64_t)va.capture.len * rwa.len * (has_b ? 2 : 1);
+        capture_finish(va, rwa, start_a, score[0], sc.colstore(), [&]() { return dp_traceback2(va.capture, rwa, sc, 0); }, out, ma);
+        if (has_b)
+            capture_finish(vb, rwb, start_b, score[1], sc.colstore(), [&]() { return dp_traceback2(vb.capture, rwb, sc, 1); }, out, mb);
     }
     for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
     if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);

@@ -6,7 +6,7 @@
 #include <string>
 #include <vector>
 #include <cstdio>
-#include "hsq_kernels.cuh"
+#include "hsq_extend.cuh"
 
 namespace hsq {
 
@@ -61,7 +61,8 @@ struct hsq_ctx {
     hsq::DevBuf q1, q2, probe_id, read_index;
     // scratch + outputs
     hsq::DevBuf ptr_words, brow, cols, status, cells, misc, out_i32, out_u8, out_slots, pair_ok;
-    hsq::DevBuf sort_a, sort_b, sort_c, sort_d, sort_tmp, flags;
+    hsq::DevBuf sort_a, sort_b, sort_c, sort_d, sort_tmp, flags, slow;
+    bool force_dp32 = false;
     int64_t ext_n = -1;  // staged extend batch
     bool ext_ran = false;
     hsq::ExtendDeviceOut ext_out{};

@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(DP_BLOCK) align_kernel(DeviceSeqs refs, Device
         SeqView qry = make_view(qrys.codes + q0, (int)(qrys.offsets[k + 1] - q0), false, false);
         int score = dp_fill(ref, qry, sp, pen_start, pen_end, sc);
         cells += (int64_t)ref.len * qry.len;
-        Columns cv{sc, dp_traceback(ref, qry, sc)};
+        Columns cv{sc.colstore(), dp_traceback(ref, qry, sc)};
         PairIndices ix = pair_indices(cv);
         out.score[k] = score;
         out.n_cols[k] = cv.n;

@@ -102,13 +102,60 @@ def test_extend_adversarial_vs_oracle(ctx):
         r1.append(a)
         r2.append(b)
     pairs = PairBatchHost(pid, r1, r2)
-    for sc in (scorer(), scorer(2, -3, -2, -4)):
+    # the last two scorers exceed the 14-bit score range of the packed kernel and take the 32-bit kernel
+    for sc in (scorer(), scorer(2, -3, -2, -4), scorer(1, -4, 1, 2), scorer(5, -4, 0, -70), scorer(40, -30, -20, -45)):
         ctx.set_probes(probes)
         ctx.set_scorer(sc)
-        got = ctx.extend_batch(pairs, cigar_cap=400, md_cap=600)
-        exp = O.extend_batch(probes, pairs, sc, cigar_cap=400, md_cap=600, nthreads=8)
+        got = ctx.extend_batch(pairs, cigar_cap=1600, md_cap=2400)
+        exp = O.extend_batch(probes, pairs, sc, cigar_cap=1600, md_cap=2400, nthreads=8)
         H.assert_extend_equal(got, exp)
     ctx.set_scorer(scorer())
+
+
+def test_extend_forced_32bit_kernel(monkeypatch):
+    """HSQ_FORCE_DP32=1 routes hsq_extend_batch through the 32-bit capture kernel: same results."""
+    monkeypatch.setenv("HSQ_FORCE_DP32", "1")
+    probes = synth.make_probes(100, seed=5)
+    pairs = synth.make_pairs(probes, 3000, read_len=150, ext_uid_len=10, seed=6, sub_rate=0.02, ins_rate=0.003, del_rate=0.003)
+    with Context(0) as c32:
+        c32.set_probes(probes)
+        got = c32.extend_batch(pairs, cigar_cap=64, md_cap=96)
+    H.assert_extend_equal(got, O.extend_batch(probes, pairs, cigar_cap=64, md_cap=96, nthreads=8))
+
+
+def test_extend_non_acgt_capture_target(ctx):
+    """IUPAC / N codes inside the capture target (the DP reference) take the kernels' slow-column path."""
+    rng = np.random.default_rng(123)
+    n_probes, n = 24, 2000
+    ext = [H.random_seq(rng, 20) for _ in range(n_probes)]
+    lig = [H.random_seq(rng, 21) for _ in range(n_probes)]
+    tgt = []
+    for k in range(n_probes):
+        t = list(H.random_seq(rng, 120))
+        for _ in range(k % 4):
+            t[int(rng.integers(0, 120))] = str(rng.choice(list("NRYKMU")))
+        tgt.append("".join(t))
+    z = np.arange(n_probes, dtype=np.int32) * 500
+    probes = ProbeTableHost(np.arange(n_probes) % 2, z + 10, z + 30, z + 300, z + 320, z + 31, z + 299, ext, lig, tgt)
+    pid = rng.integers(0, n_probes, n)
+    comp = str.maketrans("ACGTNRYKMU", "TGCANYRMKA")
+    r1, r2 = [], []
+    for k in range(n):
+        p = int(pid[k])
+        clean = "".join(c if c in "ACGT" else "A" for c in tgt[p])
+        mol = ext[p] + clean + lig[p]
+        rc = mol[::-1].translate(comp)
+        a = (H.random_seq(rng, 10) + H.mutate(rng, mol, 0.02, 0.005) + H.random_seq(rng, 200))[:150]
+        b = (H.mutate(rng, rc, 0.02, 0.005) + H.random_seq(rng, 200))[:150]
+        r1.append(a)
+        r2.append(b)
+    pairs = PairBatchHost(pid, r1, r2)
+    ctx.set_probes(probes)
+    ctx.set_scorer(scorer())
+    got = ctx.extend_batch(pairs, cigar_cap=200, md_cap=300)
+    exp = O.extend_batch(probes, pairs, cigar_cap=200, md_cap=300, nthreads=8)
+    H.assert_extend_equal(got, exp)
+    assert got.pair_ok.mean() > 0.5
 
 
 def test_dedup_vs_oracle(ctx):
