@@ -67,7 +67,8 @@ int alloc_scratch(hsq_ctx* ctx, int64_t nthreads, int64_t nthreads2, int q_max, 
     const size_t rs = (size_t)r_max + 1, t1 = (size_t)nthreads, t2 = (size_t)nthreads2;
     HSQ_CUDA(ctx, ctx->ptr_words.ensure(std::max(t1 * sizeof(uint32_t), t2 * sizeof(uint2)) * n_strips * rs));
     HSQ_CUDA(ctx, ctx->brow.ensure(std::max(t1, t2) * rs * sizeof(int32_t)));
-    HSQ_CUDA(ctx, ctx->cols.ensure(std::max(t1, t2) * (size_t)(q_max + r_max + 1) * sizeof(uint16_t)));
+    HSQ_CUDA(ctx, ctx->cols.ensure(t1 * (size_t)(q_max + r_max + 1) * sizeof(uint16_t) + 16));
+    HSQ_CUDA(ctx, ctx->colinfo.ensure(t2 * rs * sizeof(uint32_t) + 16));
     HSQ_CUDA(ctx, ctx->slow.ensure(t2 * KROWS * sizeof(uint32_t) + 16));
     pool->r_stride = r_max + 1;
     pool->ptr_words = ctx->ptr_words.as<uint32_t>();
@@ -77,7 +78,7 @@ int alloc_scratch(hsq_ctx* ctx, int64_t nthreads, int64_t nthreads2, int q_max, 
         pool2->r_stride = r_max + 1;
         pool2->ptr_words = ctx->ptr_words.as<uint2>();
         pool2->brow = ctx->brow.as<uint32_t>();
-        pool2->cols = ctx->cols.as<uint16_t>();
+        pool2->colinfo = ctx->colinfo.as<uint32_t>();
         pool2->slow = ctx->slow.as<uint32_t>();
     }
     return HSQ_OK;
@@ -151,7 +152,7 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     hsq::DevBuf* bufs[] = {&ctx->p_rev, &ctx->p_ext_start, &ctx->p_ext_stop, &ctx->p_lig_start, &ctx->p_lig_stop, &ctx->q1, &ctx->q2,
                            &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
                            &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
-                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow};
+                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo};
     for (auto* b : bufs) b->release();
     hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb};
     for (auto* s : seqs) s->release();

@@ -55,34 +55,43 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
     ScoreParams sp_default = make_score_params(1, -4, -1, -6);  // SimpleAlignmentScorer defaults (ExtendReadsToPrimer.java:290-291)
     ScoreParams sp_user = make_score_params(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start);
     // packed u16x2 cells when every score fits 14 bits (always, for HSQUtils' scorers at these lengths), else 32-bit cells
-    const bool packed = !ctx->force_dp32 &&
-                        dp2_score_range_ok(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start, q_max, r_max);
+    const int prefix_max = std::min(read_max, primer_max + PRIMER_ALIGNMENT_BUFFER + 1);
+    const bool packed1 = !ctx->force_dp32 && dp2_score_range_ok(1, -4, -1, -6, primer_max, prefix_max);
+    const bool packed2 = !ctx->force_dp32 &&
+                         dp2_score_range_ok(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start, q_max, r_max);
+    ScoreParams2 sp_default2 = make_score_params2(sp_default);
     ScoreParams2 sp_user2 = make_score_params2(sp_user);
     int grid1 = 1, grid2 = 1;
-    if ((rc = persistent_grid(ctx, primer_kernel, DP_BLOCK, 2 * n, &grid1))) return rc;
-    if (packed) rc = persistent_grid(ctx, capture2_kernel, DP2_BLOCK, n + 1, &grid2);
+    if (packed1) rc = persistent_grid(ctx, primer2_kernel, DP2_BLOCK, n + 1, &grid1);
+    else rc = persistent_grid(ctx, primer_kernel, DP_BLOCK, 2 * n, &grid1);
+    if (rc) return rc;
+    if (packed2) rc = persistent_grid(ctx, capture2_kernel, DP2_BLOCK, n + 1, &grid2);
     else rc = persistent_grid(ctx, capture_kernel, DP_BLOCK, 2 * n, &grid2);
     if (rc) return rc;
     ScratchPool pool;
     ScratchPool2 pool2;
-    if ((rc = alloc_scratch(ctx, (int64_t)std::max(grid1, packed ? 1 : grid2) * DP_BLOCK, packed ? (int64_t)grid2 * DP2_BLOCK : 0, q_max, r_max,
-                            &pool, &pool2)))
-        return rc;
-    // bucket keys: exact DP#2 shape (rows = read remainder, columns = capture-target length); the last key collects the
-    // read ends that stop after DP#1.  Buckets are padded to even sizes (holes = ORDER_HOLE).
-    BucketKeys keys;
+    const int64_t threads32 = (int64_t)std::max(packed1 ? 0 : grid1, packed2 ? 0 : grid2) * DP_BLOCK;
+    const int64_t threads16 = (int64_t)std::max(packed1 ? grid1 : 0, packed2 ? grid2 : 0) * DP2_BLOCK;
+    if ((rc = alloc_scratch(ctx, threads32, threads16, q_max, r_max, &pool, &pool2))) return rc;
+    // Bucket keys = exact DP shape (rows, columns); the last key of the DP#2 sort collects the read ends that stop after
+    // DP#1.  Buckets are padded to even sizes (holes = ORDER_HOLE) so a packed thread's two read ends share one shape.
+    BucketKeys keys1, keys;
+    keys1.key_stride = prefix_max + 1;
+    const int n_keys1 = (primer_max + 1) * keys1.key_stride + 1;
+    keys1.skip_key = (uint32_t)(n_keys1 - 1);
     keys.key_stride = ctx->p_target.max_len + 1;
     const int n_keys = (read_max + 1) * keys.key_stride + 1;
     keys.skip_key = (uint32_t)(n_keys - 1);
-    const size_t order_bytes = (n2 + (size_t)n_keys + 2) * 4;
+    const int n_keys_max = std::max(n_keys, n_keys1);
+    const size_t order_bytes = (n2 + (size_t)n_keys_max + 2) * 4;
     HSQ_CUDA(ctx, ctx->sort_a.ensure(n2 * 4 + 16));
     HSQ_CUDA(ctx, ctx->sort_b.ensure(order_bytes + 16));
-    HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)(2 * n_keys + 4) * 4));
-    keys.key = ctx->sort_a.as<uint32_t>();
+    HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)(2 * n_keys_max + 4) * 4));
+    keys.key = keys1.key = ctx->sort_a.as<uint32_t>();
     uint32_t* order = ctx->sort_b.as<uint32_t>();
     uint32_t* hist = ctx->sort_c.as<uint32_t>();
-    uint32_t* cursor = hist + n_keys;
-    uint32_t* n_active = cursor + n_keys;
+    uint32_t* cursor = hist + n_keys_max;
+    uint32_t* n_active = cursor + n_keys_max;
     HSQ_CUDA(ctx, ctx->out_i32.ensure(10 * n2 * sizeof(int32_t) + 16));
     HSQ_CUDA(ctx, ctx->out_u8.ensure(2 * n2 + 16));
     HSQ_CUDA(ctx, ctx->out_slots.ensure(n2 * ((size_t)cigar_cap + (size_t)md_cap) + 16));
@@ -99,22 +108,33 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
     d.md = d.cigar + n2 * (size_t)cigar_cap;
     if (n > 0) {
         DeviceProbes pv = probe_view(ctx);
-        HSQ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t)n_keys * 4, ctx->stream));
-        HSQ_CUDA(ctx, cudaMemsetAsync(order, 0xFF, order_bytes, ctx->stream));
-        primer_kernel<<<grid1, DP_BLOCK, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), n, sp_default,
-                                                          pool, d, keys, d_status(ctx), ctx->cells.as<unsigned long long>());
+        const int32_t* pid = ctx->probe_id.as<int32_t>();
+        const DeviceSeqs v1 = ctx->r1.view(), v2 = ctx->r2.view();
+        unsigned long long* cells = ctx->cells.as<unsigned long long>();
         const int sblocks = (int)std::min<int64_t>((2 * n + 255) / 256, (int64_t)ctx->sm_count * 8);
-        bucket_hist_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, 2 * n, hist);
-        bucket_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist, n_keys, cursor);
-        HSQ_CUDA(ctx, cudaMemcpyAsync(n_active, cursor + keys.skip_key, 4, cudaMemcpyDeviceToDevice, ctx->stream));
-        bucket_scatter_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, 2 * n, cursor, order);
-        if (packed)
-            capture2_kernel<<<grid2, DP2_BLOCK, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), order,
-                                                                 n_active, sp_user2, pool2, d, ctx->cells.as<unsigned long long>());
-        else
-            capture_kernel<<<grid2, DP_BLOCK, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), ctx->r1.view(), ctx->r2.view(), order,
-                                                               n_active, sp_user, pool, d, ctx->cells.as<unsigned long long>());
-        ctx->launches += 5;
+        // counting sort of the keys in keys.key into `order` (padded buckets); n_active = entries before the skip bucket
+        auto bucket_sort = [&](int nk, uint32_t skip_key) -> int {
+            HSQ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t)nk * 4, ctx->stream));
+            HSQ_CUDA(ctx, cudaMemsetAsync(order, 0xFF, order_bytes, ctx->stream));
+            bucket_hist_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, 2 * n, hist);
+            bucket_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist, nk, cursor);
+            HSQ_CUDA(ctx, cudaMemcpyAsync(n_active, cursor + skip_key, 4, cudaMemcpyDeviceToDevice, ctx->stream));
+            bucket_scatter_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, 2 * n, cursor, order);
+            ctx->launches += 3;
+            return HSQ_OK;
+        };
+        if (packed1) {
+            primer_key_kernel<<<sblocks, 256, 0, ctx->stream>>>(pv, pid, v1, v2, n, keys1);
+            ctx->launches++;
+            if ((rc = bucket_sort(n_keys1, keys1.skip_key))) return rc;
+            primer2_kernel<<<grid1, DP2_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_default2, pool2, d, keys, d_status(ctx), cells);
+        } else {
+            primer_kernel<<<grid1, DP_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, n, sp_default, pool, d, keys, d_status(ctx), cells);
+        }
+        if ((rc = bucket_sort(n_keys, keys.skip_key))) return rc;
+        if (packed2) capture2_kernel<<<grid2, DP2_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_user2, pool2, d, cells);
+        else capture_kernel<<<grid2, DP_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_user, pool, d, cells);
+        ctx->launches += 2;
         HSQ_CUDA(ctx, cudaGetLastError());
         finalize_extend_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), n, d,
                                                                                      ctx->pair_ok.as<uint8_t>(), d_status(ctx));

@@ -1,61 +1,78 @@
 // hsq_dp2.cuh -- the DP fill of hsq_dp.cuh for TWO alignments per thread, packed as the two u16 halves of a register.
 //
 // Same recurrence, same cell encoding (X = 4*S + p, candidates 4*score + {2,1,0}, see hsq_dp.cuh), but each half
-// carries its alignment's X biased by 0x8000 so that it is an unsigned 16-bit number:
+// carries its alignment's X as an unsigned 16-bit number:
+//     X'(i,j) = 4*S(i,j) + p + 0x8000 + (i + j) * SB/2
+//   - 0x8000 makes the half unsigned;
+//   - the position term makes every substitution score non-negative: a diagonal step adds 4*sub + SB >= 0, a gap step
+//     adds its penalty + SB/2 (folded into the constants kh, kv), so all three candidates of a cell carry the same
+//     offset and the max / tie-break is unchanged.  Non-negative profile entries can be merged bit-wise (PRMT) from two
+//     different profile columns -- alignment A's reference base selects the low half, alignment B's the high half.
 //   - the two maxima of a cell are VIADDMNMX.U16x2 (per-half wrapping add, per-half unsigned max);
-//   - every other step of the cell (mask, multiply by a small constant, add) is ordinary 32-bit integer arithmetic on
-//     the packed word, which is exact per half as long as every half stays inside [0, 65535] -- the host checks the
-//     score range of the scorer / lengths before choosing this kernel (dp2_score_range_ok) and otherwise runs the
-//     32-bit kernel.
-// So one instruction stream fills two matrices: half the instructions per cell of the 32-bit path.
+//   - every other step of the cell (mask, multiply by a small constant, add) is ordinary 32-bit integer arithmetic on the
+//     packed word, which is exact per half as long as every half stays inside [0, 65535] -- the host checks the score
+//     range of the scorer / lengths before choosing these kernels (dp2_score_range_ok), else the 32-bit kernels run.
+// One instruction stream fills two matrices: 6 ALU-pipe + 5 FMA-pipe instructions per pair of cells.
 //
-// The two alignments of a thread have the SAME shape (Q rows, R columns): the bucket sort of hsq_extend.cuh keys read
-// ends by exact (Q, R) and pads every bucket to an even size.
+// The two alignments of a thread have the SAME shape (Q rows, R columns): the bucket sorts of hsq_extend.cuh key the
+// read ends by exact (Q, R) and pad every bucket to an even size.
 // Pointer words: per strip column two words, U bits and L bits; row r of the strip sits at bit 15-r of its half.
+// Traceback is streamed (no column store): pointer words are fetched 16 columns at a time into the thread's (by then
+// dead) profile slots, and each column goes straight to a sink (CIGAR/MD state machine or the primer gate).
 #pragma once
+#include <algorithm>
 #include "hsq_dp.cuh"
 
 namespace hsq {
 
-static constexpr int DP2_BLOCK = 64;               // threads per block of the packed kernels
-static constexpr int PROF2_INT4_PER_THREAD = 32;   // 2 alignments x 4 one-hot bases x 16 rows x int32
+static constexpr int DP2_BLOCK = 128;              // threads per block of the packed kernels
+static constexpr int PROF2_INT4_PER_THREAD = 16;   // 4 one-hot bases x 16 rows x (A | B << 16)
+static constexpr int TB_WINDOW = 16;               // traceback window: columns of pointer words staged in shared memory
 static constexpr uint32_t DP2_BIAS = 0x8000u;
 static constexpr uint32_t DP2_REP = 0x10001u;
 static constexpr uint32_t DP2_MASK_D4 = 0xFFFCFFFCu, DP2_MASK_B0 = 0x00010001u, DP2_MASK_B1X2 = 0x00020002u;
 
 struct ScoreParams2 {
-    uint32_t kh2, kv2;        // per-half wrapping addends: 4*gapStart + 2, 4*gapStart + 1
+    uint32_t kh2, kv2;        // per-half wrapping addends: 4*gapStart + 2 + SB/2, 4*gapStart + 1 + SB/2
     uint32_t c2, c4;          // 2*(gapExtend-gapStart), 4*(gapExtend-gapStart) as 32-bit multipliers (mod 2^32)
     uint32_t hfree2, vfree2;  // (2 - kh) and (1 - kv) replicated: turn a D4 into the candidate-neutral free-gap output
-    int ms4, mm4, gap_start;
+    int ms4o, mm4o;           // 4*match + SB, 4*mismatch + SB  (both in [0, 65535])
+    int sb_half;              // SB/2, a multiple of 4
+    int gap_start;
 };
 
 inline ScoreParams2 make_score_params2(const ScoreParams& s) {
     ScoreParams2 p;
-    p.kh2 = ((uint32_t)s.kh & 0xFFFFu) * DP2_REP;
-    p.kv2 = ((uint32_t)s.kv & 0xFFFFu) * DP2_REP;
+    const int lo = std::min(0, std::min(s.ms4, s.mm4));
+    const int sb = ((-lo + 7) / 8) * 8;
+    p.sb_half = sb / 2;
+    p.kh2 = ((uint32_t)(s.kh + p.sb_half) & 0xFFFFu) * DP2_REP;
+    p.kv2 = ((uint32_t)(s.kv + p.sb_half) & 0xFFFFu) * DP2_REP;
     p.c2 = (uint32_t)s.c2;
     p.c4 = (uint32_t)s.c4;
     p.hfree2 = (uint32_t)(2 - s.kh) * DP2_REP;
     p.vfree2 = (uint32_t)(1 - s.kv) * DP2_REP;
-    p.ms4 = s.ms4;
-    p.mm4 = s.mm4;
+    p.ms4o = s.ms4 + sb;
+    p.mm4o = s.mm4 + sb;
     p.gap_start = s.gap_start;
     return p;
 }
 
-// every score the fill can form (cells, candidates, the padding rows of the last strip) stays within +-bound
+// every value the packed fill can form (cells, candidates, the padding rows of the last strip, the position offset)
+// stays inside an unsigned half
 inline bool dp2_score_range_ok(int match, int mismatch, int gap_extend, int gap_start, int q_max, int r_max) {
     int64_t m = 1;
     for (int v : {match, mismatch, gap_extend, gap_start}) m = std::max<int64_t>(m, v < 0 ? -(int64_t)v : v);
-    const int64_t bound = ((int64_t)q_max + KROWS + r_max + 4) * (m + 1);
-    return 4 * (bound + 2 * m + 2) + 3 < 32768;
+    const int64_t span = (int64_t)q_max + KROWS + r_max + 4;
+    const int64_t bound = span * (m + 1);       // |score| of any cell or candidate
+    const int64_t offset = span * (2 * m + 4);  // (i + j) * SB/2 with SB <= 4*m + 7
+    return 4 * (bound + 2 * m + 2) + 3 + offset < 32768;
 }
 
 struct DpScratch2 {
     uint2* ptr_words;   // [n_strips_max * (r_max + 1)] per thread: (U word, L word)
-    uint32_t* brow;     // [r_max + 1] per thread: packed X of the row above the current strip
-    uint16_t* cols;     // [q_max + r_max] per thread: traceback columns of the alignment being emitted
+    uint32_t* brow;     // [r_max + 1] per thread: packed X' of the row above the current strip
+    uint32_t* colinfo;  // [r_max + 1] per thread: profile column of alignment A (byte 0) and B (byte 1); 4 = not A/C/G/T
     uint32_t* slow;     // [KROWS] per thread: packed substitution scores of a column with a non-ACGT reference code
     int4* prof;         // shared memory: [PROF2_INT4_PER_THREAD][DP2_BLOCK]
     int64_t nthreads;
@@ -63,12 +80,12 @@ struct DpScratch2 {
     int r_stride;
     __device__ inline uint2& word(int strip, int j) const { return ptr_words[((int64_t)strip * r_stride + j) * nthreads + tid]; }
     __device__ inline uint32_t& b(int j) const { return brow[(int64_t)j * nthreads + tid]; }
-    __device__ inline uint16_t& col(int k) const { return cols[(int64_t)k * nthreads + tid]; }
-    __device__ inline ColStore colstore() const { return ColStore{cols, nthreads, tid}; }
+    __device__ inline uint32_t& ci(int j) const { return colinfo[(int64_t)j * nthreads + tid]; }
 };
 
-__device__ __forceinline__ uint32_t border2(int k, int pen_start, int gap_start) {  // packed, biased 4*border_score
-    return (uint32_t)(4 * border_score(k, pen_start, gap_start) + (int)DP2_BIAS) * DP2_REP;
+// packed, biased, offset 4*border_score of border cell k (row 0 or column 0)
+__device__ __forceinline__ uint32_t border2(int k, int pen_start, const ScoreParams2& sp) {
+    return (uint32_t)(4 * border_score(k, pen_start, sp.gap_start) + (int)DP2_BIAS + k * sp.sb_half) * DP2_REP;
 }
 
 // One column of one strip for both alignments.  State per row: D4[r], H0[r] as in dp_column.
@@ -82,9 +99,9 @@ __device__ __forceinline__ uint32_t dp_column2(uint32_t (&D4)[KROWS], uint32_t (
     uint32_t x = 0;
 #pragma unroll
     for (int r = 0; r < KROWS; r++) {
-        uint32_t dsub;
+        uint32_t sub;
         if (SLOW) {
-            dsub = dg + slow[r * nt];
+            sub = slow[r * nt];
         } else {
             int4 sa, sb;
             if ((r & 3) == 0) {
@@ -93,8 +110,9 @@ __device__ __forceinline__ uint32_t dp_column2(uint32_t (&D4)[KROWS], uint32_t (
             }
             const int a = (r & 3) == 0 ? sa.x : (r & 3) == 1 ? sa.y : (r & 3) == 2 ? sa.z : sa.w;
             const int b = (r & 3) == 0 ? sb.x : (r & 3) == 1 ? sb.y : (r & 3) == 2 ? sb.z : sb.w;
-            dsub = dg + (uint32_t)a + (uint32_t)b;
+            sub = __byte_perm((uint32_t)a, (uint32_t)b, 0x7610);  // low half from A's column, high half from B's column
         }
+        const uint32_t dsub = dg + sub;
         x = __viaddmax_u16x2(H0[r], sp.kh2, __viaddmax_u16x2(vin, sp.kv2, dsub));
         dg = D4[r];
         const uint32_t d4 = x & DP2_MASK_D4;
@@ -115,25 +133,21 @@ __device__ __forceinline__ uint32_t dp_column2(uint32_t (&D4)[KROWS], uint32_t (
     return x;
 }
 
-// Profile of one strip for both alignments: A's scores as plain int32 (low half), B's scores shifted to the high half,
-// so that  diag + A + B  is the packed diagonal candidate.
+// Profile of one strip: entry [base][row] = A's score in the low half, B's score in the high half (both >= 0).
 __device__ inline void build_profile2(const uint32_t (&qa)[KROWS], const uint32_t (&qb)[KROWS], const ScoreParams2& sp, int4* prof) {
 #pragma unroll
     for (int b = 0; b < 4; b++) {
         const uint32_t code = 1u << b;
 #pragma unroll
         for (int ch = 0; ch < 4; ch++) {
-            int4 v, w;
-            v.x = (qa[4 * ch + 0] & code) ? sp.ms4 : sp.mm4;
-            v.y = (qa[4 * ch + 1] & code) ? sp.ms4 : sp.mm4;
-            v.z = (qa[4 * ch + 2] & code) ? sp.ms4 : sp.mm4;
-            v.w = (qa[4 * ch + 3] & code) ? sp.ms4 : sp.mm4;
-            w.x = ((qb[4 * ch + 0] & code) ? sp.ms4 : sp.mm4) * 65536;
-            w.y = ((qb[4 * ch + 1] & code) ? sp.ms4 : sp.mm4) * 65536;
-            w.z = ((qb[4 * ch + 2] & code) ? sp.ms4 : sp.mm4) * 65536;
-            w.w = ((qb[4 * ch + 3] & code) ? sp.ms4 : sp.mm4) * 65536;
-            prof[(b * 4 + ch) * DP2_BLOCK + threadIdx.x] = v;
-            prof[(16 + b * 4 + ch) * DP2_BLOCK + threadIdx.x] = w;
+            int e[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int va = (qa[4 * ch + k] & code) ? sp.ms4o : sp.mm4o;
+                const int vb = (qb[4 * ch + k] & code) ? sp.ms4o : sp.mm4o;
+                e[k] = va + vb * 65536;
+            }
+            prof[(b * 4 + ch) * DP2_BLOCK + threadIdx.x] = make_int4(e[0], e[1], e[2], e[3]);
         }
     }
 }
@@ -153,53 +167,48 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
             const int i = i0 + 1 + r;
             qa[r] = (i <= Q) ? (uint32_t)qryA.get(i - 1) : 0u;
             qb[r] = (i <= Q) ? (uint32_t)qryB.get(i - 1) : 0u;
-            const uint32_t s0 = border2(i, pen_start, sp.gap_start);
+            const uint32_t s0 = border2(i, pen_start, sp);
             D4[r] = s0;
             H0[r] = (HFREE && r == rstar) ? s0 + sp.hfree2 : s0;
         }
         build_profile2(qa, qb, sp, sc.prof);
     }
-    uint32_t diag_d4 = (i0 == 0) ? DP2_BIAS * DP2_REP : border2(i0, pen_start, sp.gap_start);
+    uint32_t diag_d4 = (i0 == 0) ? DP2_BIAS * DP2_REP : border2(i0, pen_start, sp);
     uint2* wordp = &sc.word(s, 1);
     uint32_t* browp = &sc.b(1);
-    const uint8_t* rpa = refA.base + refA.start;
-    const uint8_t* rpb = refB.base + refB.start;
-    const int64_t stepa = refA.step, stepb = refB.step;
+    const uint32_t* cip = &sc.ci(1);
     const int64_t nt = sc.nthreads;
-    uint32_t next_a = *rpa, next_b = *rpb;
+    const int4* prof_t = sc.prof + threadIdx.x;
+    uint32_t next_ci = *cip;
     uint32_t next_up = *browp;
     for (int j = 1; j <= R; j++) {
-        const uint32_t rawa = next_a, rawb = next_b;
+        const uint32_t ci = next_ci;
         const uint32_t upx = next_up;
         if (j < R) {
-            rpa += stepa;
-            rpb += stepb;
-            next_a = *rpa;
-            next_b = *rpb;
+            cip += nt;
+            next_ci = *cip;
             next_up = browp[nt];
         }
         const uint32_t up_d4 = upx & DP2_MASK_D4;
         const bool vfree = free_end && (j == R);
         const uint32_t up_v0 = vfree ? up_d4 + sp.vfree2 : (upx & DP2_MASK_B0) * sp.c4 + up_d4;
-        const int ba = prof_slot(rawa, refA.comp), bb = prof_slot(rawb, refB.comp);
         uint2 w;
         uint32_t xlast;
-        if (ba != 4 && bb != 4) {
-            const int4* pa = sc.prof + ba * 4 * DP2_BLOCK + threadIdx.x;
-            const int4* pb = sc.prof + (16 + bb * 4) * DP2_BLOCK + threadIdx.x;
+        if ((ci & 0x0404u) == 0) {
+            const int4* pa = prof_t + (ci & 0xFFu) * (4 * DP2_BLOCK);
+            const int4* pb = prof_t + (ci >> 8) * (4 * DP2_BLOCK);
             if (!vfree) xlast = dp_column2<HFREE, false, false>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
             else xlast = dp_column2<HFREE, true, false>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
         } else {  // ambiguity code, N, U or gap character in a reference: this column's scores go through global scratch
-            const uint32_t ca = refA.comp ? complement_code((uint8_t)rawa) : rawa;
-            const uint32_t cb = refB.comp ? complement_code((uint8_t)rawb) : rawb;
+            const uint32_t ca = refA.get(j - 1), cb = refB.get(j - 1);
             uint32_t* sl = sc.slow + sc.tid;
 #pragma unroll 1
             for (int r = 0; r < KROWS; r++) {
                 const int i = i0 + 1 + r;
                 const uint32_t qa = (i <= Q) ? (uint32_t)qryA.get(i - 1) : 0u;
                 const uint32_t qb = (i <= Q) ? (uint32_t)qryB.get(i - 1) : 0u;
-                const int va = ((qa & ca & MATCH_MASK) != 0) ? sp.ms4 : sp.mm4;
-                const int vb = ((qb & cb & MATCH_MASK) != 0) ? sp.ms4 : sp.mm4;
+                const int va = ((qa & ca & MATCH_MASK) != 0) ? sp.ms4o : sp.mm4o;
+                const int vb = ((qb & cb & MATCH_MASK) != 0) ? sp.ms4o : sp.mm4o;
                 sl[r * nt] = (uint32_t)va + (uint32_t)vb * 65536u;
             }
             if (!vfree) xlast = dp_column2<HFREE, false, true>(D4, H0, nullptr, nullptr, sl, nt, up_v0, diag_d4, sp, rstar, &w);
@@ -218,10 +227,6 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
     }
 }
 
-__device__ __forceinline__ int dp2_unpack_score(uint32_t d4, int which) {
-    return ((int)((d4 >> (16 * which)) & 0xFFFFu) - (int)DP2_BIAS) >> 2;
-}
-
 // Fills both matrices (same shape: refA.len == refB.len, qryA.len == qryB.len).  Scores S[Q][R] go to score[0], score[1].
 __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const SeqView& qryA, const SeqView& qryB,
                                 const ScoreParams2& sp, int pen_start, int pen_end, const DpScratch2& sc, int* score) {
@@ -233,41 +238,61 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
     }
     const int n_strips = (Q + KROWS - 1) / KROWS;
     const bool free_end = !pen_end;
-    {
+    {   // matrix row 0 (cells point LEFT: never an UP continuation) and the profile column of every reference position
         uint32_t* bp = &sc.b(1);
-        for (int j = 1; j <= R; j++, bp += sc.nthreads) *bp = border2(j, pen_start, sp.gap_start) + (uint32_t)P_LEFT * DP2_REP;
+        uint32_t* cp = &sc.ci(1);
+        for (int j = 1; j <= R; j++, bp += sc.nthreads, cp += sc.nthreads) {
+            *bp = border2(j, pen_start, sp) + (uint32_t)P_LEFT * DP2_REP;
+            const uint32_t ba = (uint32_t)prof_slot(refA.base[refA.start + (j - 1) * refA.step], refA.comp);
+            const uint32_t bb = (uint32_t)prof_slot(refB.base[refB.start + (j - 1) * refB.step], refB.comp);
+            *cp = ba | (bb << 8);
+        }
     }
     uint32_t final_d4 = 0;
     for (int s = 0; s < n_strips - 1; s++) dp_strip2<false>(refA, refB, qryA, qryB, sp, pen_start, free_end, sc, s, false, &final_d4);
     if (free_end) dp_strip2<true>(refA, refB, qryA, qryB, sp, pen_start, true, sc, n_strips - 1, true, &final_d4);
     else dp_strip2<false>(refA, refB, qryA, qryB, sp, pen_start, false, sc, n_strips - 1, true, &final_d4);
-    score[0] = dp2_unpack_score(final_d4, 0);
-    score[1] = dp2_unpack_score(final_d4, 1);
+    const int off = (int)DP2_BIAS + (Q + R) * sp.sb_half;
+    score[0] = ((int)(final_d4 & 0xFFFFu) - off) >> 2;
+    score[1] = ((int)(final_d4 >> 16) - off) >> 2;
 }
 
-__device__ __forceinline__ uint32_t dp_pointer2(int i, int j, const DpScratch2& sc, int which) {
-    if (i == 0) return P_LEFT;
-    if (j == 0) return P_UP;
-    const int s = (i - 1) / KROWS, r = (i - 1) % KROWS;
-    const uint2 w = sc.word(s, j);
-    const int bit = 15 - r + 16 * which;
-    return (((w.y >> bit) & 1u) << 1) | ((w.x >> bit) & 1u);
-}
-
-// Traceback of alignment `which` of the pair (same output convention as dp_traceback).
-__device__ inline int dp_traceback2(const SeqView& ref, const SeqView& qry, const DpScratch2& sc, int which) {
-    int i = qry.len, j = ref.len, n = 0;
+// Streamed traceback of alignment `which` of the pair (NeedlemanWunschGlobalAlignment.java:85-114): walks from (Q,R) to
+// (0,0) and hands every column, LAST column first, to sink.push(ref code | qry code << 8) (CODE_GAP where the pointer
+// did not consume that sequence).  Pointer words come through a 16-column window in the thread's own profile slots.
+template <class Sink>
+__device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView& qry, const DpScratch2& sc, int which, Sink& sink) {
+    int i = qry.len, j = ref.len;
+    int ws = -1, whi = 0;
+    uint2* win = reinterpret_cast<uint2*>(sc.prof + threadIdx.x);  // slot k at win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)]
+    const int shift = 16 * which;
+    const int64_t nt = sc.nthreads;
     while (i > 0 || j > 0) {
-        const uint32_t p = dp_pointer2(i, j, sc, which);
+        uint32_t p;
+        if (i == 0) p = P_LEFT;
+        else if (j == 0) p = P_UP;
+        else {
+            const int s = (i - 1) / KROWS, r = (i - 1) % KROWS;
+            if (s != ws || j <= whi - TB_WINDOW) {
+                ws = s;
+                whi = j;
+                const uint2* g = &sc.word(s, j);
+                uint2 t[TB_WINDOW];
+#pragma unroll
+                for (int k = 0; k < TB_WINDOW; k++) t[k] = (j - k >= 1) ? g[-(int64_t)k * nt] : make_uint2(0u, 0u);
+#pragma unroll
+                for (int k = 0; k < TB_WINDOW; k++) win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)] = t[k];
+            }
+            const int k = whi - j;
+            const uint2 w = win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)];
+            const int bit = 15 - r + shift;
+            p = (((w.y >> bit) & 1u) << 1) | ((w.x >> bit) & 1u);
+        }
         uint32_t rc = CODE_GAP, qc = CODE_GAP;
-        if (p != P_UP) { rc = ref.get(j - 1); }
-        if (p != P_LEFT) { qc = qry.get(i - 1); }
-        if (p != P_UP) j--;
-        if (p != P_LEFT) i--;
-        sc.col(n) = (uint16_t)(rc | (qc << 8));
-        n++;
+        if (p != P_UP) { rc = ref.get(j - 1); j--; }
+        if (p != P_LEFT) { qc = qry.get(i - 1); i--; }
+        sink.push(rc | (qc << 8));
     }
-    return n;
 }
 
 }  // namespace hsq

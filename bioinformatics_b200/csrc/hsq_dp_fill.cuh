@@ -148,4 +148,18 @@ __device__ inline int dp_traceback(const SeqView& ref, const SeqView& qry, const
     return n;
 }
 
+// Streamed traceback: same walk, but every column (last column first) goes to sink.push(ref code | qry code << 8)
+// instead of the column store.
+template <class Sink>
+__device__ __forceinline__ void dp_traceback_stream(const SeqView& ref, const SeqView& qry, const DpScratch& sc, Sink& sink) {
+    int i = qry.len, j = ref.len;
+    while (i > 0 || j > 0) {
+        const uint32_t p = dp_pointer(i, j, sc);
+        uint32_t rc = CODE_GAP, qc = CODE_GAP;
+        if (p != P_UP) { rc = ref.get(j - 1); j--; }
+        if (p != P_LEFT) { qc = qry.get(i - 1); i--; }
+        sink.push(rc | (qc << 8));
+    }
+}
+
 }  // namespace hsq

@@ -121,6 +121,110 @@ __device__ inline void emit_cigar_md(const Columns& cv, int a, int b, bool rever
     *ref_len_out = ref_len;
 }
 
+// ---- streamed emission (no column store) -------------------------------------------------------------------------
+// The traceback produces columns last-first.  For a read on the reverse strand that IS the emission order of the
+// reference (CIGAR and MD are computed on the reversed alignment, ExtendReadsToPrimer.java:229-231): tokens are appended.
+// For a forward read the emission order is the opposite, so the same state machine runs on the reversed column sequence
+// and writes its tokens right to left ("back" mode: numbers least-significant digit first, a deletion's '^' when the
+// run ends); finish() then moves the string to the start of the slot.  The separator rules of getMismatchDetailsString
+// (a "0" before a leading non-match entry, between adjacent non-match entries, after a trailing one) are symmetric.
+struct StreamWriter {
+    uint8_t* p;
+    int cap;
+    int len;
+    bool back;
+    __device__ inline void put(uint8_t ch) {
+        if (len < cap) p[back ? cap - 1 - len : len] = ch;
+        len++;
+    }
+    __device__ inline void put_int(int v) {  // v >= 0
+        if (back) {
+            do { put((uint8_t)('0' + v % 10)); v /= 10; } while (v > 0);
+        } else {
+            char buf[12];
+            int k = 0;
+            do { buf[k++] = (char)('0' + v % 10); v /= 10; } while (v > 0);
+            while (k > 0) put((uint8_t)buf[--k]);
+        }
+    }
+    __device__ inline void finish() {  // on overflow (len > cap) the slot content is unspecified
+        if (back && len > 0 && len < cap) {
+            const int off = cap - len;
+            for (int k = 0; k < len; k++) p[k] = p[off + k];
+        }
+    }
+};
+
+struct CigarMdStream {
+    StreamWriter cw, mw;
+    bool back;
+    bool started;  // a query base has been seen: trailing query-gap columns are dropped (AlignmentPair.java:95-103)
+    int nm, ref_len;
+    uint8_t run_ch;
+    int run_n;
+    int last_entry;  // 0 none, 1 match, 2 X, 3 D
+    int match_count;
+    uint8_t prev_op;
+    __device__ inline void init(uint8_t* cigar, int cigar_cap, uint8_t* md, int md_cap, bool back_) {
+        back = back_;
+        cw = StreamWriter{cigar, cigar_cap, 0, back_};
+        mw = StreamWriter{md, md_cap, 0, back_};
+        started = false;
+        nm = 0; ref_len = 0; run_ch = 0; run_n = 0; last_entry = 0; match_count = 0; prev_op = 0;
+    }
+    __device__ inline void flush_run() {
+        if (run_n > 0) {
+            if (back) { cw.put(run_ch); cw.put_int(run_n); }
+            else { cw.put_int(run_n); cw.put(run_ch); }
+        }
+    }
+    __device__ inline void sep() {
+        if (last_entry == 1) mw.put_int(match_count);
+        else mw.put('0');
+    }
+    __device__ inline void push(uint32_t w) {
+        if (!started) {
+            if (col_qry(w) == CODE_GAP) return;
+            started = true;
+        }
+        const uint8_t op = column_op(w);
+        if (col_ref(w) != col_qry(w)) nm++;
+        if (op != 'I') ref_len++;
+        const uint8_t sch = (op == '=' || op == 'X') ? (uint8_t)'M' : op;
+        if (sch == run_ch) run_n++;
+        else {
+            flush_run();
+            run_ch = sch;
+            run_n = 1;
+        }
+        if (back && prev_op == 'D' && op != 'D') mw.put('^');
+        if (op == '=') {
+            if (last_entry == 1) match_count++;
+            else { match_count = 1; last_entry = 1; }
+        } else if (op == 'X') {
+            sep();
+            mw.put(decode_code((uint8_t)col_ref(w)));
+            last_entry = 2;
+        } else if (op == 'D') {
+            if (prev_op != 'D') {
+                sep();
+                if (!back) mw.put('^');
+            }
+            mw.put(decode_code((uint8_t)col_ref(w)));
+            last_entry = 3;
+        }
+        prev_op = op;
+    }
+    __device__ inline void finish() {
+        flush_run();
+        if (back && prev_op == 'D') mw.put('^');
+        if (last_entry == 1) mw.put_int(match_count);
+        else if (last_entry >= 2) mw.put('0');
+        cw.finish();
+        mw.finish();
+    }
+};
+
 // counters over forward columns [a..b]
 __device__ inline void count_columns(const Columns& cv, int a, int b, int* matches, int* mismatches, int* ref_gaps,
                                      int* qry_gaps) {

@@ -1,8 +1,9 @@
-// hsq_extend.cuh -- the ExtendReadsToPrimer pipeline on the device, one read end per thread:
-//   primer_kernel   DP#1 (primer x read prefix) + the 0.95^d gate           -> primer end index e, bucket key
-//   bucket sort     counting sort of the read ends by (strips of DP#2, capture-target length)
-//   capture_kernel  DP#2 (capture target x read remainder) + traceback + CIGAR / MD / NM / POS, in bucket order,
-//                   so the 32 lanes of a warp run loops of identical trip counts (no divergence in the fill)
+// hsq_extend.cuh -- the ExtendReadsToPrimer pipeline on the device:
+//   primer stage    DP#1 (primer x read prefix) + the 0.95^d gate           -> primer end index e, DP#2 bucket key
+//   bucket sort     counting sort of the read ends by exact DP shape (rows, columns), buckets padded to even sizes
+//   capture stage   DP#2 (capture target x read remainder) + streamed traceback + CIGAR / MD / NM / POS, in bucket order
+// Each stage exists twice: packed (two read ends of the same DP shape per thread, u16x2 cells, hsq_dp2.cuh) -- the path
+// HSQUtils' scorers take -- and 32-bit (one read end per thread, hsq_dp.cuh) for scorers whose scores do not fit 14 bits.
 // Reference: HSQ/process/ExtendReadsToPrimer.java:96-245,286-345.
 #pragma once
 #include "hsq_kernels.cuh"
@@ -52,7 +53,31 @@ struct BucketKeys {
     uint32_t skip_key;  // read ends that do not reach DP#2
 };
 
-// Stage 1: getPrimerEndIndexInRead for every read end; read ends that stop here get their (all-zero) results now.
+// What follows DP#1 for one read end: primer end index, DP#2 bucket key; read ends that stop here get their (all-zero)
+// results now.
+__device__ __forceinline__ void primer_finish(const ReadEndViews& v, int e, const ExtendDeviceOut& out, const BucketKeys& keys, int64_t m) {
+    const int L = v.read.len;
+    out.primer_end[m] = e;
+    const bool reaches = (e != HSQ_PRIMER_NOT_FOUND && e >= 0 && e < L);  // :206
+    if (reaches) {
+        const int q = L - (e + 1);
+        keys.key[m] = (uint32_t)(q * keys.key_stride + v.capture.len);  // exact DP#2 shape (Q rows, R columns)
+    } else {
+        keys.key[m] = keys.skip_key;
+        out.ok[m] = 0;
+        out.score[m] = 0;
+        out.pos[m] = 0;
+        out.read_start[m] = 0;
+        out.read_stop[m] = 0;
+        out.nm[m] = 0;
+        out.ref_len[m] = 0;
+        out.cigar_len[m] = 0;
+        out.md_len[m] = 0;
+        out.overflow[m] = 0;
+    }
+}
+
+// Stage 1 (32-bit cells, natural order): getPrimerEndIndexInRead for every read end.
 __global__ void __launch_bounds__(DP_BLOCK) primer_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
                                                           DeviceSeqs r2, int64_t n_pairs, ScoreParams sp_default, ScratchPool pool,
                                                           ExtendDeviceOut out, BucketKeys keys, int* status,
@@ -63,29 +88,27 @@ __global__ void __launch_bounds__(DP_BLOCK) primer_kernel(DeviceProbes probes, c
     const int64_t n_tasks = 2 * n_pairs;
     for (int64_t m = sc.tid; m < n_tasks; m += sc.nthreads) {
         ReadEndViews v = read_end_views(probes, probe_id, r1, r2, m);
-        const int L = v.read.len;
         const int e = primer_end_index(v.primer, v.read, sp_default, sc, status, &cells);
-        out.primer_end[m] = e;
-        const bool reaches = (e != HSQ_PRIMER_NOT_FOUND && e >= 0 && e < L);  // :206
-        if (reaches) {
-            const int q = L - (e + 1);
-            keys.key[m] = (uint32_t)(q * keys.key_stride + v.capture.len);  // exact DP#2 shape (Q rows, R columns)
-        } else {
-            keys.key[m] = keys.skip_key;
-            out.ok[m] = 0;
-            out.score[m] = 0;
-            out.pos[m] = 0;
-            out.read_start[m] = 0;
-            out.read_stop[m] = 0;
-            out.nm[m] = 0;
-            out.ref_len[m] = 0;
-            out.cigar_len[m] = 0;
-            out.md_len[m] = 0;
-            out.overflow[m] = 0;
-        }
+        primer_finish(v, e, out, keys, m);
     }
     for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
     if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
+}
+
+// Bucket key of DP#1 (rows = primer length, columns = read prefix length) for the packed primer stage.
+__global__ void primer_key_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1, DeviceSeqs r2, int64_t n_pairs,
+                                  BucketKeys keys) {
+    int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; m < 2 * n_pairs; m += stride) {
+        const int64_t k = m >> 1;
+        const int pid = probe_id[k];
+        const DeviceSeqs& ps = (m & 1) ? probes.lig : probes.ext;
+        const DeviceSeqs& rs = (m & 1) ? r2 : r1;
+        const int p = (int)(ps.offsets[pid + 1] - ps.offsets[pid]);
+        const int L = (int)(rs.offsets[k + 1] - rs.offsets[k]);
+        keys.key[m] = (uint32_t)(p * keys.key_stride + min(L, p + PRIMER_ALIGNMENT_BUFFER + 1));
+    }
 }
 
 // ---- counting sort of read ends by bucket key (order inside a bucket is irrelevant: results are written by id) ----
@@ -152,22 +175,21 @@ __global__ void bucket_scatter_kernel(const uint32_t* __restrict__ key, int64_t 
     }
 }
 
-// What follows DP#2 for one read end (:212-236): acceptance test, traceback, CIGAR / MD / NM / POS, result stores.
-// `traceback` fills the thread's column store and returns the number of alignment columns.
+// What follows DP#2 for one read end (:212-236): acceptance test, streamed traceback into the CIGAR / MD state machine,
+// NM / POS, result stores.  `traceback(sink)` walks the alignment last column first.
 template <class Traceback>
-__device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqView& rw, int start, int score, const ColStore& cs,
-                                               Traceback traceback, const ExtendDeviceOut& out, int64_t m) {
-    int ok = 0, pos = 0, read_start = 0, read_stop = 0, nm = 0, ref_len = 0;
-    SlotWriter cw{out.cigar + m * out.cigar_cap, out.cigar_cap, 0};
-    SlotWriter mw{out.md + m * out.md_cap, out.md_cap, 0};
+__device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqView& rw, int start, int score, Traceback traceback,
+                                               const ExtendDeviceOut& out, int64_t m) {
+    int ok = 0, pos = 0, read_start = 0, read_stop = 0;
+    CigarMdStream st;
+    // a reverse-strand read emits in traceback order; a forward read fills its slots right to left
+    st.init(out.cigar + m * out.cigar_cap, out.cigar_cap, out.md + m * out.md_cap, out.md_cap, !v.is_reversed);
     const int read_length = rw.len - 1;  // :225
     // score/alignmentLength > 0 (:212): the alignment has max(Q,R) >= 1 columns whenever score != 0
     if (score > 0 && read_length > LENGTH_THRESHOLD_FOR_EXTENDED_READ) {
-        Columns cv{cs, traceback()};
-        int last_q = cv.n - 1;  // getAlignmentWithoutEndingQueryInserts (:218)
-        while (last_q >= 0 && col_qry(cv.fwd(last_q)) == CODE_GAP) last_q--;
-        emit_cigar_md(cv, 0, last_q, v.is_reversed, &cw, &mw, &nm, &ref_len);  // :220-231
-        pos = v.is_reversed ? v.adjacent - ref_len : v.adjacent + 1;           // :234,:236
+        traceback(st);  // trailing query-gap columns are dropped by the sink (getAlignmentWithoutEndingQueryInserts :218)
+        st.finish();    // :220-231
+        pos = v.is_reversed ? v.adjacent - st.ref_len : v.adjacent + 1;  // :234,:236
         read_start = start;
         read_stop = start + read_length;
         ok = 1;
@@ -177,11 +199,11 @@ __device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqV
     out.pos[m] = pos;
     out.read_start[m] = read_start;
     out.read_stop[m] = read_stop;
-    out.nm[m] = nm;
-    out.ref_len[m] = ref_len;
-    out.cigar_len[m] = cw.len;
-    out.md_len[m] = mw.len;
-    out.overflow[m] = (uint8_t)((cw.len > cw.cap ? 1 : 0) | (mw.len > mw.cap ? 2 : 0));
+    out.nm[m] = st.nm;
+    out.ref_len[m] = st.ref_len;
+    out.cigar_len[m] = st.cw.len;
+    out.md_len[m] = st.mw.len;
+    out.overflow[m] = (uint8_t)((st.cw.len > st.cw.cap ? 1 : 0) | (st.mw.len > st.mw.cap ? 2 : 0));
 }
 
 static constexpr uint32_t ORDER_HOLE = 0xFFFFFFFFu;  // padding entry of an odd-sized bucket
@@ -205,7 +227,7 @@ __global__ void __launch_bounds__(DP_BLOCK, 5) capture_kernel(DeviceProbes probe
         SeqView rw = sub_view(v.read, start, v.read.len - start);  // read[e+1 .. L-1] (:210)
         const int score = dp_fill(v.capture, rw, sp_user, 0, 0, sc);  // :211
         cells += (int64_t)v.capture.len * rw.len;
-        capture_finish(v, rw, start, score, sc.colstore(), [&]() { return dp_traceback(v.capture, rw, sc); }, out, m);
+        capture_finish(v, rw, start, score, [&](CigarMdStream& st) { dp_traceback_stream(v.capture, rw, sc, st); }, out, m);
     }
     for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
     if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
@@ -214,7 +236,7 @@ __global__ void __launch_bounds__(DP_BLOCK, 5) capture_kernel(DeviceProbes probe
 struct ScratchPool2 {
     uint2* ptr_words;
     uint32_t* brow;
-    uint16_t* cols;
+    uint32_t* colinfo;
     uint32_t* slow;
     int r_stride;
 };
@@ -224,7 +246,7 @@ __device__ inline DpScratch2 thread_scratch2(const ScratchPool2& pool, int4* pro
     sc.prof = prof;
     sc.ptr_words = pool.ptr_words;
     sc.brow = pool.brow;
-    sc.cols = pool.cols;
+    sc.colinfo = pool.colinfo;
     sc.slow = pool.slow;
     sc.nthreads = (int64_t)gridDim.x * blockDim.x;
     sc.tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -232,9 +254,47 @@ __device__ inline DpScratch2 thread_scratch2(const ScratchPool2& pool, int4* pro
     return sc;
 }
 
-// Stage 2, packed: two read ends of the same DP#2 shape per thread (entries 2t, 2t+1 of the padded bucket order),
-// cells as u16x2 halves (hsq_dp2.cuh).  Chosen by the host when the scorer's score range fits 14 bits.
-__global__ void __launch_bounds__(DP2_BLOCK, 7) capture2_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
+// Stage 1, packed: two read ends of the same DP#1 shape per thread (entries 2t, 2t+1 of the padded bucket order).
+__global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
+                                                            DeviceSeqs r2, const uint32_t* __restrict__ order,
+                                                            const uint32_t* __restrict__ n_active_ptr, ScoreParams2 sp_default,
+                                                            ScratchPool2 pool, ExtendDeviceOut out, BucketKeys keys, int* status,
+                                                            unsigned long long* cells_total) {
+    __shared__ int4 prof[PROF2_INT4_PER_THREAD * DP2_BLOCK];
+    DpScratch2 sc = thread_scratch2(pool, prof);
+    int64_t cells = 0;
+    const int64_t n_slots = (int64_t)*n_active_ptr >> 1;  // bucket sizes are even
+    for (int64_t t = sc.tid; t < n_slots; t += sc.nthreads) {
+        const uint2 mo = reinterpret_cast<const uint2*>(order)[t];
+        const int n_here = (mo.y != ORDER_HOLE) ? 2 : 1;
+        const int64_t mm[2] = {(int64_t)mo.x, (int64_t)(n_here == 2 ? mo.y : mo.x)};
+        ReadEndViews va = read_end_views(probes, probe_id, r1, r2, mm[0]);
+        ReadEndViews vb = read_end_views(probes, probe_id, r1, r2, mm[1]);
+        if (va.primer.len == 0) {  // Java: IndexOutOfBounds at :299 (all-gap primer alignment); both have the same shape
+            atomicMin(status, HSQ_ERR_OUT_OF_RANGE);
+            primer_finish(va, HSQ_PRIMER_NOT_FOUND, out, keys, mm[0]);
+            if (n_here == 2) primer_finish(vb, HSQ_PRIMER_NOT_FOUND, out, keys, mm[1]);
+            continue;
+        }
+        SeqView pa = primer_prefix(va.primer, va.read), pb = primer_prefix(vb.primer, vb.read);
+        int score[2];
+        dp_fill2(pa, pb, va.primer, vb.primer, sp_default, /*pen_start=*/1, /*pen_end=*/0, sc, score);  // :290-293
+        cells += (int64_t)pa.len * va.primer.len * n_here;
+#pragma unroll 1
+        for (int which = 0; which < n_here; which++) {
+            const ReadEndViews& v = which ? vb : va;
+            const SeqView& px = which ? pb : pa;
+            PrimerGateSink gate;
+            dp_traceback2(px, v.primer, sc, which, gate);
+            primer_finish(v, gate.result(), out, keys, mm[which]);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
+    if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
+}
+
+// Stage 2, packed: two read ends of the same DP#2 shape per thread, cells as u16x2 halves (hsq_dp2.cuh).
+__global__ void __launch_bounds__(DP2_BLOCK, 5) capture2_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
                                                              DeviceSeqs r2, const uint32_t* __restrict__ order,
                                                              const uint32_t* __restrict__ n_active_ptr, ScoreParams2 sp_user,
                                                              ScratchPool2 pool, ExtendDeviceOut out, unsigned long long* cells_total) {
@@ -244,19 +304,23 @@ __global__ void __launch_bounds__(DP2_BLOCK, 7) capture2_kernel(DeviceProbes pro
     const int64_t n_slots = (int64_t)*n_active_ptr >> 1;  // bucket sizes are even
     for (int64_t t = sc.tid; t < n_slots; t += sc.nthreads) {
         const uint2 mo = reinterpret_cast<const uint2*>(order)[t];
-        const bool has_b = mo.y != ORDER_HOLE;
-        const int64_t ma = mo.x, mb = has_b ? mo.y : mo.x;
-        ReadEndViews va = read_end_views(probes, probe_id, r1, r2, ma);
-        ReadEndViews vb = read_end_views(probes, probe_id, r1, r2, mb);
-        const int start_a = out.primer_end[ma] + 1, start_b = out.primer_end[mb] + 1;
-        SeqView rwa = sub_view(va.read, start_a, va.read.len - start_a);
+        const int n_here = (mo.y != ORDER_HOLE) ? 2 : 1;
+        const int64_t mm[2] = {(int64_t)mo.x, (int64_t)(n_here == 2 ? mo.y : mo.x)};
+        ReadEndViews va = read_end_views(probes, probe_id, r1, r2, mm[0]);
+        ReadEndViews vb = read_end_views(probes, probe_id, r1, r2, mm[1]);
+        const int start_a = out.primer_end[mm[0]] + 1, start_b = out.primer_end[mm[1]] + 1;
+        SeqView rwa = sub_view(va.read, start_a, va.read.len - start_a);  // read[e+1 .. L-1] (:210)
         SeqView rwb = sub_view(vb.read, start_b, vb.read.len - start_b);
         int score[2];
-        dp_fill2(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score);
-        cells += (int64_t)va.capture.len * rwa.len * (has_b ? 2 : 1);
-        capture_finish(va, rwa, start_a, score[0], sc.colstore(), [&]() { return dp_traceback2(va.capture, rwa, sc, 0); }, out, ma);
-        if (has_b)
-            capture_finish(vb, rwb, start_b, score[1], sc.colstore(), [&]() { return dp_traceback2(vb.capture, rwb, sc, 1); }, out, mb);
+        dp_fill2(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score);  // :211
+        cells += (int64_t)va.capture.len * rwa.len * n_here;
+#pragma unroll 1
+        for (int which = 0; which < n_here; which++) {
+            const ReadEndViews& v = which ? vb : va;
+            const SeqView& rw = which ? rwb : rwa;
+            capture_finish(v, rw, which ? start_b : start_a, score[which],
+                           [&](CigarMdStream& st) { dp_traceback2(v.capture, rw, sc, which, st); }, out, mm[which]);
+        }
     }
     for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
     if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);

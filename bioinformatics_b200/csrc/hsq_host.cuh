@@ -61,7 +61,7 @@ struct hsq_ctx {
     hsq::DevBuf q1, q2, probe_id, read_index;
     // scratch + outputs
     hsq::DevBuf ptr_words, brow, cols, status, cells, misc, out_i32, out_u8, out_slots, pair_ok;
-    hsq::DevBuf sort_a, sort_b, sort_c, sort_d, sort_tmp, flags, slow;
+    hsq::DevBuf sort_a, sort_b, sort_c, sort_d, sort_tmp, flags, slow, colinfo;
     bool force_dp32 = false;
     int64_t ext_n = -1;  // staged extend batch
     bool ext_ran = false;

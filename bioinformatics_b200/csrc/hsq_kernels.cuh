@@ -94,32 +94,42 @@ __device__ inline DpScratch thread_scratch(const ScratchPool& pool, int4* prof) 
     return sc;
 }
 
-// getPrimerEndIndexInRead (HSQ/process/ExtendReadsToPrimer.java:286-345)
+// The scan of getPrimerEndIndexInRead (HSQ/process/ExtendReadsToPrimer.java:305-343) as a traceback sink: columns arrive
+// last-first, which is the order of the reversed alignments the reference walks (i = 0 is the last column).
+struct PrimerGateSink {
+    bool passed = false;
+    int pe = 0, first = -1, i = 0;
+    double w = 0.0;
+    __device__ inline void push(uint32_t c) {
+        const uint32_t rc = c & 0xFFu, pc = c >> 8;  // reference = read prefix, query = primer
+        if (!passed && pc != CODE_GAP) { passed = true; first = i; }
+        if (passed && rc != CODE_GAP) {
+            pe++;
+            if ((rc & pc & MATCH_MASK) != 0) w += c_pow95[i - first];  // Math.pow(0.95, i - firstNonGapIndex), summed in this order
+        }
+        i++;
+    }
+    __device__ inline int result() const { return (w < WEIGHTED_ALIGNMENT_SCORE_THRESHOLD) ? HSQ_PRIMER_NOT_FOUND : pe - 1; }
+};
+
+// read[0 .. min(L-1, p+25)] inclusive (:288)
+__device__ inline SeqView primer_prefix(const SeqView& primer, const SeqView& read) {
+    return sub_view(read, 0, min(read.len, primer.len + PRIMER_ALIGNMENT_BUFFER + 1));
+}
+
+// getPrimerEndIndexInRead (HSQ/process/ExtendReadsToPrimer.java:286-345), 32-bit cells
 __device__ inline int primer_end_index(const SeqView& primer, const SeqView& read, const ScoreParams& sp_default,
                                        const DpScratch& sc, int* status, int64_t* cells) {
-    int L = read.len;
-    SeqView prefix = sub_view(read, 0, min(L, primer.len + PRIMER_ALIGNMENT_BUFFER + 1));  // [0 .. min(L-1, p+25)] inclusive (:288)
+    SeqView prefix = primer_prefix(primer, read);
     if (primer.len == 0) {  // Java: IndexOutOfBounds at :299 (all-gap primer alignment)
         atomicMin(status, HSQ_ERR_OUT_OF_RANGE);
         return HSQ_PRIMER_NOT_FOUND;
     }
     dp_fill(prefix, primer, sp_default, /*pen_start=*/1, /*pen_end=*/0, sc);  // ref = read prefix, query = primer (:290-293)
     *cells += (int64_t)prefix.len * primer.len;
-    int n = dp_traceback(prefix, primer, sc);
-    bool passed = false;
-    int pe = 0, first = -1;
-    double w = 0.0;
-    for (int i = 0; i < n; i++) {  // stored order == the reversed alignments of :305-333
-        uint32_t c = sc.col(i);
-        uint32_t rc = col_ref(c), pc = col_qry(c);
-        if (!passed && pc != CODE_GAP) { passed = true; first = i; }
-        if (passed && rc != CODE_GAP) {
-            pe++;
-            if (codes_match(rc, pc)) w += c_pow95[i - first];
-        }
-    }
-    if (w < WEIGHTED_ALIGNMENT_SCORE_THRESHOLD) return HSQ_PRIMER_NOT_FOUND;
-    return pe - 1;
+    PrimerGateSink gate;
+    dp_traceback_stream(prefix, primer, sc, gate);
+    return gate.result();
 }
 
 // The extend pipeline (primer stage, bucketing, capture stage) lives in hsq_extend.cuh.
