@@ -66,13 +66,13 @@ inline bool dp2_score_range_ok(int match, int mismatch, int gap_extend, int gap_
     const int64_t span = (int64_t)q_max + KROWS + r_max + 4;
     const int64_t bound = span * (m + 1);       // |score| of any cell or candidate
     const int64_t offset = span * (2 * m + 4);  // (i + j) * SB/2 with SB <= 4*m + 7
-    return 4 * (bound + 2 * m + 2) + 3 + offset < 32768;
+    return 4 * (bound + 2 * m + 2) + 3 + offset < 32768 && q_max + r_max <= 512;  // 512 = DP2_MAX_COLUMNS (traceback op store)
 }
 
 struct DpScratch2 {
     uint2* ptr_words;   // [n_strips_max * (r_max + 1)] per thread: (U word, L word)
     uint32_t* brow;     // [r_max + 1] per thread: packed X' of the row above the current strip
-    uint32_t* colinfo;  // [r_max + 1] per thread: profile column of alignment A (byte 0) and B (byte 1); 4 = not A/C/G/T
+    uint8_t* colinfo;   // [r_max + 1] per thread: profile column of alignment A (low nibble) and B (high nibble); 4 = not A/C/G/T
     uint32_t* slow;     // [KROWS] per thread: packed substitution scores of a column with a non-ACGT reference code
     int4* prof;         // shared memory: [PROF2_INT4_PER_THREAD][DP2_BLOCK]
     int64_t nthreads;
@@ -80,7 +80,7 @@ struct DpScratch2 {
     int r_stride;
     __device__ inline uint2& word(int strip, int j) const { return ptr_words[((int64_t)strip * r_stride + j) * nthreads + tid]; }
     __device__ inline uint32_t& b(int j) const { return brow[(int64_t)j * nthreads + tid]; }
-    __device__ inline uint32_t& ci(int j) const { return colinfo[(int64_t)j * nthreads + tid]; }
+    __device__ inline uint8_t& ci(int j) const { return colinfo[(int64_t)j * nthreads + tid]; }
 };
 
 // packed, biased, offset 4*border_score of border cell k (row 0 or column 0)
@@ -176,7 +176,7 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
     uint32_t diag_d4 = (i0 == 0) ? DP2_BIAS * DP2_REP : border2(i0, pen_start, sp);
     uint2* wordp = &sc.word(s, 1);
     uint32_t* browp = &sc.b(1);
-    const uint32_t* cip = &sc.ci(1);
+    const uint8_t* cip = &sc.ci(1);
     const int64_t nt = sc.nthreads;
     const int4* prof_t = sc.prof + threadIdx.x;
     uint32_t next_ci = *cip;
@@ -194,9 +194,9 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
         const uint32_t up_v0 = vfree ? up_d4 + sp.vfree2 : (upx & DP2_MASK_B0) * sp.c4 + up_d4;
         uint2 w;
         uint32_t xlast;
-        if ((ci & 0x0404u) == 0) {
-            const int4* pa = prof_t + (ci & 0xFFu) * (4 * DP2_BLOCK);
-            const int4* pb = prof_t + (ci >> 8) * (4 * DP2_BLOCK);
+        if ((ci & 0x44u) == 0) {
+            const int4* pa = prof_t + (ci & 0xFu) * (4 * DP2_BLOCK);
+            const int4* pb = prof_t + (ci >> 4) * (4 * DP2_BLOCK);
             if (!vfree) xlast = dp_column2<HFREE, false, false>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
             else xlast = dp_column2<HFREE, true, false>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
         } else {  // ambiguity code, N, U or gap character in a reference: this column's scores go through global scratch
@@ -214,7 +214,7 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
             if (!vfree) xlast = dp_column2<HFREE, false, true>(D4, H0, nullptr, nullptr, sl, nt, up_v0, diag_d4, sp, rstar, &w);
             else xlast = dp_column2<HFREE, true, true>(D4, H0, nullptr, nullptr, sl, nt, up_v0, diag_d4, sp, rstar, &w);
         }
-        *wordp = w;
+        __stcs(wordp, w);  // streamed: read back once by the traceback, must not evict the boundary rows from L2
         if (!last_strip) *browp = xlast;
         diag_d4 = up_d4;
         wordp += nt;
@@ -240,12 +240,12 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
     const bool free_end = !pen_end;
     {   // matrix row 0 (cells point LEFT: never an UP continuation) and the profile column of every reference position
         uint32_t* bp = &sc.b(1);
-        uint32_t* cp = &sc.ci(1);
+        uint8_t* cp = &sc.ci(1);
         for (int j = 1; j <= R; j++, bp += sc.nthreads, cp += sc.nthreads) {
             *bp = border2(j, pen_start, sp) + (uint32_t)P_LEFT * DP2_REP;
             const uint32_t ba = (uint32_t)prof_slot(refA.base[refA.start + (j - 1) * refA.step], refA.comp);
             const uint32_t bb = (uint32_t)prof_slot(refB.base[refB.start + (j - 1) * refB.step], refB.comp);
-            *cp = ba | (bb << 8);
+            *cp = (uint8_t)(ba | (bb << 4));
         }
     }
     uint32_t final_d4 = 0;
@@ -257,12 +257,30 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
     score[1] = ((int)(final_d4 >> 16) - off) >> 2;
 }
 
-// Streamed traceback of alignment `which` of the pair (NeedlemanWunschGlobalAlignment.java:85-114): walks from (Q,R) to
-// (0,0) and hands every column, LAST column first, to sink.push(ref code | qry code << 8) (CODE_GAP where the pointer
-// did not consume that sequence).  Pointer words come through a 16-column window in the thread's own profile slots.
-template <class Sink>
-__device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView& qry, const DpScratch2& sc, int which, Sink& sink) {
-    int i = qry.len, j = ref.len;
+// ---- traceback in two phases ---------------------------------------------------------------------------------------
+// Phase A walks the pointers from (Q,R) to (0,0) (NeedlemanWunschGlobalAlignment.java:85-114) and only records the
+// pointer of every alignment column, 2 bits each, last column first, in the thread's (by then dead) profile slots 8..15
+// (<= 512 columns; the host guarantees Q + R <= 512 for the packed kernels).  Pointer words come through a 16-column
+// window in profile slots 0..7, one round trip per window instead of one per column.
+// Phase B (walk_ops) replays the columns in whatever order the consumer needs, reading the two sequences sequentially.
+static constexpr int DP2_MAX_COLUMNS = 512;
+
+struct TracebackOps {
+    uint32_t* words;  // this thread's op words: word w at words[((w >> 2) * DP2_BLOCK) * 4 + (w & 3)]
+    int n;            // alignment columns
+    int lead_left;    // columns at the END of the alignment whose query side is a gap (= leading LEFT pointers of the walk)
+    __device__ __forceinline__ uint32_t op(int t) const {
+        const int w = t >> 4;
+        return (words[((w >> 2) * DP2_BLOCK) * 4 + (w & 3)] >> ((t & 15) * 2)) & 3u;
+    }
+};
+
+__device__ __forceinline__ TracebackOps dp_traceback2_ops(int Q, int R, const DpScratch2& sc, int which) {
+    TracebackOps ops;
+    ops.words = reinterpret_cast<uint32_t*>(sc.prof + 8 * DP2_BLOCK + threadIdx.x);
+    int i = Q, j = R, n = 0, lead = 0;
+    bool leading = true;
+    uint32_t acc = 0;
     int ws = -1, whi = 0;
     uint2* win = reinterpret_cast<uint2*>(sc.prof + threadIdx.x);  // slot k at win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)]
     const int shift = 16 * which;
@@ -279,7 +297,7 @@ __device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView&
                 const uint2* g = &sc.word(s, j);
                 uint2 t[TB_WINDOW];
 #pragma unroll
-                for (int k = 0; k < TB_WINDOW; k++) t[k] = (j - k >= 1) ? g[-(int64_t)k * nt] : make_uint2(0u, 0u);
+                for (int k = 0; k < TB_WINDOW; k++) t[k] = (j - k >= 1) ? __ldcs(g - (int64_t)k * nt) : make_uint2(0u, 0u);
 #pragma unroll
                 for (int k = 0; k < TB_WINDOW; k++) win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)] = t[k];
             }
@@ -288,11 +306,63 @@ __device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView&
             const int bit = 15 - r + shift;
             p = (((w.y >> bit) & 1u) << 1) | ((w.x >> bit) & 1u);
         }
-        uint32_t rc = CODE_GAP, qc = CODE_GAP;
-        if (p != P_UP) { rc = ref.get(j - 1); j--; }
-        if (p != P_LEFT) { qc = qry.get(i - 1); i--; }
-        sink.push(rc | (qc << 8));
+        if (leading) {
+            if (p == P_LEFT) lead++;
+            else leading = false;
+        }
+        acc |= p << ((n & 15) * 2);
+        n++;
+        if ((n & 15) == 0) {
+            const int w = (n >> 4) - 1;
+            ops.words[((w >> 2) * DP2_BLOCK) * 4 + (w & 3)] = acc;
+            acc = 0;
+        }
+        if (p != P_UP) j--;
+        if (p != P_LEFT) i--;
     }
+    if (n & 15) {
+        const int w = n >> 4;
+        ops.words[((w >> 2) * DP2_BLOCK) * 4 + (w & 3)] = acc;
+    }
+    ops.n = n;
+    ops.lead_left = lead;
+    return ops;
+}
+
+// Phase B: hands the columns [skip_tail columns dropped from the alignment's end] to sink.push(ref | qry << 8), either
+// first column first (backward == false) or last column first (backward == true).  The codes of the next column are
+// loaded before the current one is consumed.
+template <class Sink>
+__device__ __forceinline__ void walk_ops(const SeqView& ref, const SeqView& qry, const TracebackOps& ops, int skip_tail, bool backward,
+                                         Sink& sink) {
+    const int count = ops.n - skip_tail;
+    if (count <= 0) return;
+    // skipped columns are LEFT pointers: they consume reference positions only
+    int i = backward ? qry.len : 0, j = backward ? ref.len - skip_tail : 0;
+    int t = backward ? skip_tail : ops.n - 1;
+    const int dt = backward ? 1 : -1;
+    auto fetch = [&](int tt, uint32_t* col) {
+        const uint32_t p = ops.op(tt);
+        uint32_t rc = CODE_GAP, qc = CODE_GAP;
+        if (backward) {
+            if (p != P_UP) rc = ref.get(--j);
+            if (p != P_LEFT) qc = qry.get(--i);
+        } else {
+            if (p != P_UP) rc = ref.get(j++);
+            if (p != P_LEFT) qc = qry.get(i++);
+        }
+        *col = rc | (qc << 8);
+    };
+    uint32_t cur;
+    fetch(t, &cur);
+    for (int c = 1; c < count; c++) {
+        t += dt;
+        uint32_t nxt;
+        fetch(t, &nxt);
+        sink.push(cur);
+        cur = nxt;
+    }
+    sink.push(cur);
 }
 
 }  // namespace hsq
