@@ -66,7 +66,7 @@ inline bool dp2_score_range_ok(int match, int mismatch, int gap_extend, int gap_
     const int64_t span = (int64_t)q_max + KROWS + r_max + 4;
     const int64_t bound = span * (m + 1);       // |score| of any cell or candidate
     const int64_t offset = span * (2 * m + 4);  // (i + j) * SB/2 with SB <= 4*m + 7
-    return 4 * (bound + 2 * m + 2) + 3 + offset < 32768 && q_max + r_max <= 512;  // 512 = DP2_MAX_COLUMNS (traceback op store)
+    return 4 * (bound + 2 * m + 2) + 3 + offset < 32768;
 }
 
 struct DpScratch2 {
@@ -257,30 +257,12 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
     score[1] = ((int)(final_d4 >> 16) - off) >> 2;
 }
 
-// ---- traceback in two phases ---------------------------------------------------------------------------------------
-// Phase A walks the pointers from (Q,R) to (0,0) (NeedlemanWunschGlobalAlignment.java:85-114) and only records the
-// pointer of every alignment column, 2 bits each, last column first, in the thread's (by then dead) profile slots 8..15
-// (<= 512 columns; the host guarantees Q + R <= 512 for the packed kernels).  Pointer words come through a 16-column
-// window in profile slots 0..7, one round trip per window instead of one per column.
-// Phase B (walk_ops) replays the columns in whatever order the consumer needs, reading the two sequences sequentially.
-static constexpr int DP2_MAX_COLUMNS = 512;
-
-struct TracebackOps {
-    uint32_t* words;  // this thread's op words: word w at words[((w >> 2) * DP2_BLOCK) * 4 + (w & 3)]
-    int n;            // alignment columns
-    int lead_left;    // columns at the END of the alignment whose query side is a gap (= leading LEFT pointers of the walk)
-    __device__ __forceinline__ uint32_t op(int t) const {
-        const int w = t >> 4;
-        return (words[((w >> 2) * DP2_BLOCK) * 4 + (w & 3)] >> ((t & 15) * 2)) & 3u;
-    }
-};
-
-__device__ __forceinline__ TracebackOps dp_traceback2_ops(int Q, int R, const DpScratch2& sc, int which) {
-    TracebackOps ops;
-    ops.words = reinterpret_cast<uint32_t*>(sc.prof + 8 * DP2_BLOCK + threadIdx.x);
-    int i = Q, j = R, n = 0, lead = 0;
-    bool leading = true;
-    uint32_t acc = 0;
+// Streamed traceback of alignment `which` of the pair (NeedlemanWunschGlobalAlignment.java:85-114): walks from (Q,R) to
+// (0,0) and hands every column, LAST column first, to sink.push(ref code | qry code << 8) (CODE_GAP where the pointer
+// did not consume that sequence).  Pointer words come through a 16-column window in the thread's own profile slots.
+template <class Sink>
+__device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView& qry, const DpScratch2& sc, int which, Sink& sink) {
+    int i = qry.len, j = ref.len;
     int ws = -1, whi = 0;
     uint2* win = reinterpret_cast<uint2*>(sc.prof + threadIdx.x);  // slot k at win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)]
     const int shift = 16 * which;
@@ -306,63 +288,11 @@ __device__ __forceinline__ TracebackOps dp_traceback2_ops(int Q, int R, const Dp
             const int bit = 15 - r + shift;
             p = (((w.y >> bit) & 1u) << 1) | ((w.x >> bit) & 1u);
         }
-        if (leading) {
-            if (p == P_LEFT) lead++;
-            else leading = false;
-        }
-        acc |= p << ((n & 15) * 2);
-        n++;
-        if ((n & 15) == 0) {
-            const int w = (n >> 4) - 1;
-            ops.words[((w >> 2) * DP2_BLOCK) * 4 + (w & 3)] = acc;
-            acc = 0;
-        }
-        if (p != P_UP) j--;
-        if (p != P_LEFT) i--;
-    }
-    if (n & 15) {
-        const int w = n >> 4;
-        ops.words[((w >> 2) * DP2_BLOCK) * 4 + (w & 3)] = acc;
-    }
-    ops.n = n;
-    ops.lead_left = lead;
-    return ops;
-}
-
-// Phase B: hands the columns [skip_tail columns dropped from the alignment's end] to sink.push(ref | qry << 8), either
-// first column first (backward == false) or last column first (backward == true).  The codes of the next column are
-// loaded before the current one is consumed.
-template <class Sink>
-__device__ __forceinline__ void walk_ops(const SeqView& ref, const SeqView& qry, const TracebackOps& ops, int skip_tail, bool backward,
-                                         Sink& sink) {
-    const int count = ops.n - skip_tail;
-    if (count <= 0) return;
-    // skipped columns are LEFT pointers: they consume reference positions only
-    int i = backward ? qry.len : 0, j = backward ? ref.len - skip_tail : 0;
-    int t = backward ? skip_tail : ops.n - 1;
-    const int dt = backward ? 1 : -1;
-    auto fetch = [&](int tt, uint32_t* col) {
-        const uint32_t p = ops.op(tt);
         uint32_t rc = CODE_GAP, qc = CODE_GAP;
-        if (backward) {
-            if (p != P_UP) rc = ref.get(--j);
-            if (p != P_LEFT) qc = qry.get(--i);
-        } else {
-            if (p != P_UP) rc = ref.get(j++);
-            if (p != P_LEFT) qc = qry.get(i++);
-        }
-        *col = rc | (qc << 8);
-    };
-    uint32_t cur;
-    fetch(t, &cur);
-    for (int c = 1; c < count; c++) {
-        t += dt;
-        uint32_t nxt;
-        fetch(t, &nxt);
-        sink.push(cur);
-        cur = nxt;
+        if (p != P_UP) { rc = ref.get(j - 1); j--; }
+        if (p != P_LEFT) { qc = qry.get(i - 1); i--; }
+        sink.push(rc | (qc << 8));
     }
-    sink.push(cur);
 }
 
 }  // namespace hsq

@@ -176,17 +176,14 @@ __global__ void bucket_scatter_kernel(const uint32_t* __restrict__ key, int64_t 
 }
 
 // What follows DP#2 for one read end (:212-236): acceptance test, streamed traceback into the CIGAR / MD state machine,
-// NM / POS, result stores.
-// `traceback(sink)` feeds the alignment columns either in emission order (emission_order == true: first column first for
-// a forward read, last column first for a reverse-strand read, trailing query-gap columns already dropped) or always last
-// column first (the sink then drops the trailing query-gap columns and fills a forward read's slots right to left).
+// NM / POS, result stores.  `traceback(sink)` walks the alignment last column first.
 template <class Traceback>
-__device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqView& rw, int start, int score, bool emission_order,
-                                               Traceback traceback, const ExtendDeviceOut& out, int64_t m) {
+__device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqView& rw, int start, int score, Traceback traceback,
+                                               const ExtendDeviceOut& out, int64_t m) {
     int ok = 0, pos = 0, read_start = 0, read_stop = 0;
     CigarMdStream st;
-    st.init(out.cigar + m * out.cigar_cap, out.cigar_cap, out.md + m * out.md_cap, out.md_cap, !emission_order && !v.is_reversed);
-    st.started = emission_order;
+    // a reverse-strand read emits in traceback order; a forward read fills its slots right to left
+    st.init(out.cigar + m * out.cigar_cap, out.cigar_cap, out.md + m * out.md_cap, out.md_cap, !v.is_reversed);
     const int read_length = rw.len - 1;  // :225
     // score/alignmentLength > 0 (:212): the alignment has max(Q,R) >= 1 columns whenever score != 0
     if (score > 0 && read_length > LENGTH_THRESHOLD_FOR_EXTENDED_READ) {
@@ -230,8 +227,7 @@ __global__ void __launch_bounds__(DP_BLOCK, 5) capture_kernel(DeviceProbes probe
         SeqView rw = sub_view(v.read, start, v.read.len - start);  // read[e+1 .. L-1] (:210)
         const int score = dp_fill(v.capture, rw, sp_user, 0, 0, sc);  // :211
         cells += (int64_t)v.capture.len * rw.len;
-        capture_finish(v, rw, start, score, /*emission_order=*/false,
-                       [&](CigarMdStream& st) { dp_traceback_stream(v.capture, rw, sc, st); }, out, m);
+        capture_finish(v, rw, start, score, [&](CigarMdStream& st) { dp_traceback_stream(v.capture, rw, sc, st); }, out, m);
     }
     for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
     if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
@@ -289,8 +285,7 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes prob
             const ReadEndViews& v = which ? vb : va;
             const SeqView& px = which ? pb : pa;
             PrimerGateSink gate;
-            const TracebackOps ops = dp_traceback2_ops(v.primer.len, px.len, sc, which);
-            walk_ops(px, v.primer, ops, 0, /*backward=*/true, gate);  // the reference scans the alignment from its end (:305-333)
+            dp_traceback2(px, v.primer, sc, which, gate);
             primer_finish(v, gate.result(), out, keys, mm[which]);
         }
     }
@@ -323,14 +318,8 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) capture2_kernel(DeviceProbes pro
         for (int which = 0; which < n_here; which++) {
             const ReadEndViews& v = which ? vb : va;
             const SeqView& rw = which ? rwb : rwa;
-            capture_finish(v, rw, which ? start_b : start_a, score[which], /*emission_order=*/true,
-                           [&](CigarMdStream& st) {
-                               const TracebackOps ops = dp_traceback2_ops(rw.len, v.capture.len, sc, which);
-                               // getAlignmentWithoutEndingQueryInserts (:218) drops the trailing query-gap columns; a
-                               // reverse-strand read emits from the alignment's end (:229-231)
-                               walk_ops(v.capture, rw, ops, ops.lead_left, v.is_reversed, st);
-                           },
-                           out, mm[which]);
+            capture_finish(v, rw, which ? start_b : start_a, score[which],
+                           [&](CigarMdStream& st) { dp_traceback2(v.capture, rw, sc, which, st); }, out, mm[which]);
         }
     }
     for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
