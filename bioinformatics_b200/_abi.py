@@ -1,7 +1,7 @@
 """ctypes mirror of include/hsq_b200.h (struct layouts + small packing helpers).
 
 Only layouts live here; no compute.  Both the product binding (`_lib.py`) and the test-only oracle
-binding (`oracle/oracle.py`) use these definitions so that the same Python objects can be handed to
+binding (the ctypes module next to the CPU restatement) use these definitions so that the same Python objects can be handed to
 either side.
 """
 import ctypes as C

@@ -18,7 +18,7 @@ _lib = None
 EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version", "hsq_pinned_alloc", "hsq_pinned_free",
            "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
-           "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak")
+           "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys")
 
 
 class HsqError(RuntimeError):
@@ -141,6 +141,20 @@ class Context:
         self._check(self.lib.hsq_dedup_batch(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
                                              A.ptr(is_best, A.u8p), A.ptr(group_size, A.i32p), C.byref(sc)))
         return is_best, group_size, stats
+
+    def dedup_keys(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, n_probes, origin_base, d_keys_ptr):
+        """hsq_dedup_keys: key records of this rank's pairs into DEVICE memory at d_keys_ptr (24 B per pair)."""
+        pc = pairs.c()
+        self._check(self.lib.hsq_dedup_keys(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                            C.c_int64(n_probes), C.c_uint32(origin_base), C.c_void_p(d_keys_ptr)))
+
+    def dedup_reduce_keys(self, d_keys_ptr, n, uid_len, d_is_best_ptr, d_group_size_ptr, n_probes):
+        """hsq_dedup_reduce_keys over n DEVICE key records; answers go to DEVICE memory; returns the per-probe counters."""
+        stats = ProbeStatsHost(n_probes)
+        sc = stats.c()
+        self._check(self.lib.hsq_dedup_reduce_keys(self.h, C.c_void_p(d_keys_ptr), C.c_int64(n), C.c_int32(uid_len),
+                                                   C.c_void_p(d_is_best_ptr), C.c_void_p(d_group_size_ptr), C.byref(sc)))
+        return stats
 
     def extend_batch(self, pairs: PairBatchHost, cigar_cap=32, md_cap=48, out=None):
         out = out or ExtendResult(pairs.n, cigar_cap, md_cap)

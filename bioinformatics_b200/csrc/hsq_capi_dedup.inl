@@ -94,6 +94,35 @@ __global__ void dedup_groups_kernel(const uint32_t* __restrict__ idx, const int3
     }
 }
 
+// key columns <-> 24-byte key records (hsq_dedup_key) for the multi-GPU exchange
+__global__ void dedup_pack_keys_kernel(const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank, const int32_t* __restrict__ probe,
+                                       int64_t n, uint32_t origin_base, hsq_dedup_key* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        hsq_dedup_key k;
+        k.uid = uid[i];
+        k.rank = rank[i];
+        k.probe = probe[i];
+        k.origin = origin_base + (uint32_t)i;
+        out[i] = k;
+    }
+}
+
+__global__ void dedup_unpack_keys_kernel(const hsq_dedup_key* __restrict__ in, int64_t n, int64_t n_probes, uint64_t* __restrict__ uid,
+                                         uint64_t* __restrict__ rank, int32_t* __restrict__ probe, uint32_t* __restrict__ idx, int* status) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        const hsq_dedup_key k = in[i];
+        uid[i] = k.uid;
+        rank[i] = k.rank;
+        probe[i] = k.probe;
+        idx[i] = (uint32_t)i;
+        if (k.probe < 0 || k.probe >= n_probes) atomicMin(status, HSQ_ERR_INVALID_ARGUMENT);
+    }
+}
+
 inline int bits_for(uint64_t max_value) {
     int b = 1;
     while (b < 64 && (max_value >> b) != 0) b++;
@@ -113,7 +142,8 @@ int sort_pass(hsq_ctx* ctx, const uint64_t* keys_in, uint64_t* keys_out, const u
     return HSQ_OK;
 }
 
-int run_dedup(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, uint8_t* is_best, int32_t* group_size, hsq_probe_stats* stats) {
+// host -> device copies of one pair batch + key generation: uid -> sort_a, rank -> sort_b, pair index -> sort_d[0..n)
+int dedup_upload_keygen(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, int64_t np) {
     const int64_t n = pb->n;
     const size_t nn = (size_t)n;
     int rc = reset_status(ctx);
@@ -125,67 +155,95 @@ int run_dedup(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, uint8_t* is_
         {&ctx->r1.offsets, pb->r1.offsets, (nn + 1) * 8},         {&ctx->r2.offsets, pb->r2.offsets, (nn + 1) * 8},
         {&ctx->probe_id, pb->probe_id, nn * 4},                   {&ctx->read_index, pb->read_index, nn * 4}};
     for (auto& c : up) {
-        if (c.bytes && !c.h) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_dedup_batch: null input array");
+        if (c.bytes && !c.h) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_dedup: null input array");
         HSQ_CUDA(ctx, c.d->ensure(c.bytes + 16));
         if (c.bytes) HSQ_CUDA(ctx, cudaMemcpyAsync(c.d->p, c.h, c.bytes, cudaMemcpyHostToDevice, ctx->stream));
     }
-    const int64_t np = stats ? stats->n_probes : 0;
     HSQ_CUDA(ctx, ctx->sort_a.ensure(nn * 8 + 16));   // uid per pair
     HSQ_CUDA(ctx, ctx->sort_b.ensure(nn * 8 + 16));   // keys ping
-    HSQ_CUDA(ctx, ctx->sort_c.ensure(nn * 8 + 16));   // keys pong
     HSQ_CUDA(ctx, ctx->sort_d.ensure(nn * 8 + 16));   // idx ping | idx pong (2 x u32)
-    HSQ_CUDA(ctx, ctx->flags.ensure(2 * nn + 32));    // head | is_best
-    HSQ_CUDA(ctx, ctx->out_i32.ensure((nn + 3 * (size_t)np) * 4 + 16));
-    uint64_t* uid = ctx->sort_a.as<uint64_t>();
-    uint64_t* ka = ctx->sort_b.as<uint64_t>();
-    uint64_t* kb = ctx->sort_c.as<uint64_t>();
-    uint32_t* ia = ctx->sort_d.as<uint32_t>();
-    uint32_t* ib = ia + nn;
-    uint8_t* head = ctx->flags.as<uint8_t>();
-    uint8_t* best = head + nn + 16;
-    int32_t* d_gs = ctx->out_i32.as<int32_t>();
-    int32_t* d_stats = d_gs + nn;
-    if (np) HSQ_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 3 * (size_t)np * 4, ctx->stream));
     if (n > 0) {
         const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
         check_probe_ids_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, np > 0 ? np : INT32_MAX, d_status(ctx));
         dedup_keygen_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), ctx->q1.as<uint8_t>(),
                                                             ctx->r2.ascii.as<uint8_t>(), ctx->r2.offsets.as<int64_t>(), ctx->q2.as<uint8_t>(),
-                                                            ctx->read_index.as<int32_t>(), n, u, v, uid, ka, ia, d_status(ctx));
+                                                            ctx->read_index.as<int32_t>(), n, u, v, ctx->sort_a.as<uint64_t>(),
+                                                            ctx->sort_b.as<uint64_t>(), ctx->sort_d.as<uint32_t>(), d_status(ctx));
         ctx->launches += 2;
         int w[1];
         if ((rc = read_status(ctx, w, 1))) return rc;
         if (w[0] != 0)
-            return fail(ctx, w[0], w[0] == HSQ_ERR_UNSUPPORTED ? "hsq_dedup_batch: a UID holds a character other than A,C,G,T (filter N reads first, "
+            return fail(ctx, w[0], w[0] == HSQ_ERR_UNSUPPORTED ? "hsq_dedup: a UID holds a character other than A,C,G,T (filter N reads first, "
                                                                  "PrimerReadExtensionAndPcrDuplicateIdentification.java:815-821)"
-                                   : w[0] == HSQ_ERR_INVALID_ARGUMENT ? "hsq_dedup_batch: probe_id out of range"
-                                                                      : "hsq_dedup_batch: a read is shorter than its UID");
+                                   : w[0] == HSQ_ERR_INVALID_ARGUMENT ? "hsq_dedup: probe_id out of range"
+                                                                      : "hsq_dedup: a read is shorter than its UID");
+    }
+    return HSQ_OK;
+}
+
+// Sort + segmented reduce over key columns that are already on the device: probe -> ctx->probe_id, uid -> sort_a,
+// rank -> sort_b, pair index -> sort_d[0..n).  Results (per pair, in input order) go to d_best / d_gs (device) and the
+// per-probe counters to d_stats[3 * np] (device).
+int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_t* d_best, int32_t* d_gs, int32_t* d_stats) {
+    const size_t nn = (size_t)n;
+    int rc;
+    HSQ_CUDA(ctx, ctx->sort_c.ensure(nn * 8 + 16));   // keys pong
+    HSQ_CUDA(ctx, ctx->flags.ensure(nn + 32));        // head flags
+    uint64_t* uid = ctx->sort_a.as<uint64_t>();
+    uint64_t* ka = ctx->sort_b.as<uint64_t>();
+    uint64_t* kb = ctx->sort_c.as<uint64_t>();
+    uint32_t* ia = ctx->sort_d.as<uint32_t>();
+    uint32_t* ib = ia + nn;
+    uint8_t* head = ctx->flags.as<uint8_t>();
+    if (np) HSQ_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 3 * (size_t)np * 4, ctx->stream));
+    if (n > 0) {
+        const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
         // pass 1: by rank (48 bits) -> ib;  pass 2: by UID -> ia;  pass 3: by probe -> ib
         if ((rc = sort_pass(ctx, ka, kb, ia, ib, n, 48))) return rc;
-        if (u + v > 0) {
+        if (uid_len > 0) {
             gather_u64_kernel<uint64_t><<<gblocks, 256, 0, ctx->stream>>>(uid, ib, n, ka);
             ctx->launches++;
-            if ((rc = sort_pass(ctx, ka, kb, ib, ia, n, 2 * (u + v)))) return rc;
+            if ((rc = sort_pass(ctx, ka, kb, ib, ia, n, 2 * uid_len))) return rc;
         } else {
             HSQ_CUDA(ctx, cudaMemcpyAsync(ia, ib, nn * 4, cudaMemcpyDeviceToDevice, ctx->stream));
         }
         gather_u64_kernel<int32_t><<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), ia, n, ka);
         ctx->launches++;
         if ((rc = sort_pass(ctx, ka, kb, ia, ib, n, bits_for((uint64_t)std::max<int64_t>(np, 1))))) return rc;
-        dedup_heads_kernel<<<gblocks, 256, 0, ctx->stream>>>(ib, ctx->probe_id.as<int32_t>(), uid, n, head, best);
+        dedup_heads_kernel<<<gblocks, 256, 0, ctx->stream>>>(ib, ctx->probe_id.as<int32_t>(), uid, n, head, d_best);
         dedup_groups_kernel<<<gblocks, 256, 0, ctx->stream>>>(ib, ctx->probe_id.as<int32_t>(), head, n, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
         ctx->launches += 2;
         HSQ_CUDA(ctx, cudaGetLastError());
     }
-    if ((rc = d2h(ctx, is_best, best, nn))) return rc;
-    if ((rc = d2h(ctx, group_size, d_gs, nn))) return rc;
+    return HSQ_OK;
+}
+
+int fetch_stats(hsq_ctx* ctx, hsq_probe_stats* stats, const int32_t* d_stats) {
+    int rc;
+    const int64_t np = stats ? stats->n_probes : 0;
     if (stats && np) {
         if ((rc = d2h(ctx, stats->unique_pairs, d_stats, (size_t)np))) return rc;
         if ((rc = d2h(ctx, stats->duplicate_pairs, d_stats + np, (size_t)np))) return rc;
         if ((rc = d2h(ctx, stats->max_pairs_per_uid, d_stats + 2 * np, (size_t)np))) return rc;
     }
     return HSQ_OK;
+}
+
+int run_dedup(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, uint8_t* is_best, int32_t* group_size, hsq_probe_stats* stats) {
+    const size_t nn = (size_t)pb->n;
+    const int64_t np = stats ? stats->n_probes : 0;
+    int rc = dedup_upload_keygen(ctx, pb, u, v, np);
+    if (rc) return rc;
+    HSQ_CUDA(ctx, ctx->out_u8.ensure(nn + 32));
+    HSQ_CUDA(ctx, ctx->out_i32.ensure((nn + 3 * (size_t)np) * 4 + 16));
+    uint8_t* best = ctx->out_u8.as<uint8_t>();
+    int32_t* d_gs = ctx->out_i32.as<int32_t>();
+    int32_t* d_stats = d_gs + nn;
+    if ((rc = dedup_reduce_device(ctx, pb->n, np, u + v, best, d_gs, d_stats))) return rc;
+    if ((rc = d2h(ctx, is_best, best, nn))) return rc;
+    if ((rc = d2h(ctx, group_size, d_gs, nn))) return rc;
+    return fetch_stats(ctx, stats, d_stats);
 }
 
 }  // namespace
@@ -200,6 +258,59 @@ extern "C" int32_t hsq_dedup_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, in
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
     int rc = run_dedup(ctx, pairs, ext_uid_len, lig_uid_len, is_best, group_size, stats);
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}
+
+// ---- sharded dedup: the two halves of hsq_dedup_batch around the caller's all-to-all -----------------
+extern "C" int32_t hsq_dedup_keys(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len, int64_t n_probes,
+                                  uint32_t origin_base, hsq_dedup_key* d_keys_out) {
+    if (!ctx || !pairs) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (pairs->n < 0 || pairs->r1.n != pairs->n || pairs->r2.n != pairs->n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
+    if (pairs->n > 0 && !d_keys_out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null key buffer");
+    if (ext_uid_len < 0 || lig_uid_len < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative UID length");
+    if (ext_uid_len + lig_uid_len > 32) return fail(ctx, HSQ_ERR_UNSUPPORTED, "UID longer than 32 bases in total is outside the accelerated domain");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = dedup_upload_keygen(ctx, pairs, ext_uid_len, lig_uid_len, n_probes);
+    if (!rc && pairs->n > 0) {
+        const int gblocks = (int)std::min<int64_t>((pairs->n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        dedup_pack_keys_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->sort_a.as<uint64_t>(), ctx->sort_b.as<uint64_t>(),
+                                                                ctx->probe_id.as<int32_t>(), pairs->n, origin_base, d_keys_out);
+        ctx->launches++;
+    }
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}
+
+extern "C" int32_t hsq_dedup_reduce_keys(hsq_ctx* ctx, const hsq_dedup_key* d_keys, int64_t n, int32_t uid_len, uint8_t* d_is_best,
+                                         int32_t* d_group_size, hsq_probe_stats* stats) {
+    if (!ctx || n < 0 || (n > 0 && (!d_keys || !d_is_best || !d_group_size))) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (uid_len < 0 || uid_len > 32) return fail(ctx, HSQ_ERR_UNSUPPORTED, "UID longer than 32 bases in total is outside the accelerated domain");
+    if (!stats || stats->n_probes <= 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe stats (with n_probes) are required");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    const size_t nn = (size_t)n;
+    const int64_t np = stats->n_probes;
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    HSQ_CUDA(ctx, ctx->sort_a.ensure(nn * 8 + 16));
+    HSQ_CUDA(ctx, ctx->sort_b.ensure(nn * 8 + 16));
+    HSQ_CUDA(ctx, ctx->sort_d.ensure(nn * 8 + 16));
+    HSQ_CUDA(ctx, ctx->probe_id.ensure(nn * 4 + 16));
+    HSQ_CUDA(ctx, ctx->out_i32.ensure(3 * (size_t)np * 4 + 16));
+    if (n > 0) {
+        const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        dedup_unpack_keys_kernel<<<gblocks, 256, 0, ctx->stream>>>(d_keys, n, np, ctx->sort_a.as<uint64_t>(), ctx->sort_b.as<uint64_t>(),
+                                                                  ctx->probe_id.as<int32_t>(), ctx->sort_d.as<uint32_t>(), d_status(ctx));
+        ctx->launches++;
+        int w[1];
+        if ((rc = read_status(ctx, w, 1))) return rc;
+        if (w[0] != 0) return fail(ctx, w[0], "hsq_dedup_reduce_keys: probe out of range in a key record");
+    }
+    int32_t* d_stats = ctx->out_i32.as<int32_t>();
+    rc = dedup_reduce_device(ctx, n, np, uid_len, d_is_best, d_group_size, d_stats);
+    if (!rc) rc = fetch_stats(ctx, stats, d_stats);
     int rc2 = timer.finish();
     return rc ? rc : rc2;
 }

@@ -143,6 +143,17 @@ typedef struct hsq_candidates {
     const int32_t* cand_probe;
 } hsq_candidates;
 
+/* Key record of the sharded dedup: what one pair contributes to the (probe, UID) grouping.
+ * uid = 2 bit per base of R1[0:u] ++ R2[0:v]; rank orders the pairs of a group best first:
+ * (32767 - (short)qualitySum) << 32 | (readIndex ^ 0x80000000)  (FilterByUid.java:281-297); origin identifies the pair
+ * on the rank that holds its reads. */
+typedef struct hsq_dedup_key {
+    uint64_t uid;
+    uint64_t rank;
+    int32_t probe;
+    uint32_t origin;
+} hsq_dedup_key; /* 24 bytes */
+
 /* ---- context ------------------------------------------------------------------------------ */
 int32_t hsq_ctx_create(int32_t device, hsq_ctx** out);
 void hsq_ctx_destroy(hsq_ctx* ctx);
@@ -184,6 +195,18 @@ int32_t hsq_extend_fetch(hsq_ctx* ctx, hsq_extend_out* out);
 int32_t hsq_resolve_multi_probe(hsq_ctx* ctx, const hsq_candidates* cands, int32_t ext_uid_len, int32_t lig_uid_len,
                                 int32_t* best_probe, int32_t* cand_matches, int32_t* cand_edit);
 
+
+/* ---- sharded dedup: one process per GPU, exchange by the caller ------------------------------------------------------ */
+/* First half of FilterByUid.reduceReadsByProbeAndUid for this rank's pairs (host buffers in): writes pairs->n key
+ * records to DEVICE memory d_keys_out (origin = origin_base + pair index).  The caller routes the records to the rank
+ * that owns each probe (NCCL all-to-all) ... */
+int32_t hsq_dedup_keys(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len, int64_t n_probes,
+                       uint32_t origin_base, hsq_dedup_key* d_keys_out);
+/* ... and the owner groups the n records it received (DEVICE memory) and picks the best pair of every (probe, UID)
+ * group (findBestData, FilterByUid.java:281-297): d_is_best[k], d_group_size[k] (DEVICE memory) answer record k; the
+ * per-probe counters (host arrays) cover the probes this rank owns. */
+int32_t hsq_dedup_reduce_keys(hsq_ctx* ctx, const hsq_dedup_key* d_keys, int64_t n, int32_t uid_len, uint8_t* d_is_best,
+                              int32_t* d_group_size, hsq_probe_stats* stats);
 
 /* ---- measurement helpers ------------------------------------------------------------------- */
 /* CUDA-event stopwatch on the context's stream (the stream every kernel of this library is launched on). */

@@ -128,3 +128,50 @@ def md_trimmed_with_full_cigar(ref, qry, reverse=False):
     buf = C.create_string_buffer(4096)
     lib().hsqo_md_trimmed_with_full_cigar(ref.encode(), qry.encode(), C.c_int32(1 if reverse else 0), buf, 4096)
     return buf.value.decode()
+
+
+# ---- CPU stand-ins for the two device calls of the sharded dedup (tests/test_sharded_gloo.py only) -------------------
+KEY_DTYPE = np.dtype([("uid", "<u8"), ("rank", "<u8"), ("probe", "<i4"), ("origin", "<u4")])  # = hsq_dedup_key, 24 bytes
+
+
+def dedup_keys(pairs, ext_uid_len, lig_uid_len, origin_base=0):
+    """Key records as hsq_dedup_keys writes them (FilterByUid.java:100-101,136-138; findBestData :281-297;
+    BamFileUtil.java:74-85 quality score; ReadPair.java:101-103 short arithmetic)."""
+    code = {ord("A"): 0, ord("C"): 1, ord("G"): 2, ord("T"): 3}
+    out = np.zeros(pairs.n, dtype=KEY_DTYPE)
+    for k in range(pairs.n):
+        a0, a1 = int(pairs.r1.offsets[k]), int(pairs.r1.offsets[k + 1])
+        b0, b1 = int(pairs.r2.offsets[k]), int(pairs.r2.offsets[k + 1])
+        uid = 0
+        for ch in list(pairs.r1.data[a0:a0 + ext_uid_len]) + list(pairs.r2.data[b0:b0 + lig_uid_len]):
+            uid = (uid << 2) | code[int(ch)]
+        total = int(pairs.q1.data[a0:a1].astype(np.int64).sum() - 33 * (a1 - a0) +
+                    pairs.q2.data[b0:b1].astype(np.int64).sum() - 33 * (b1 - b0))
+        qsum = ((total + 32768) % 65536) - 32768  # Java (short)
+        rank = (((32767 - qsum) & 0xFFFF) << 32) | ((int(pairs.read_index[k]) ^ 0x80000000) & 0xFFFFFFFF)
+        out[k] = (uid, rank, int(pairs.probe_id[k]), origin_base + k)
+    return out
+
+
+def dedup_reduce_keys(keys, n_probes):
+    """Best pair per (probe, UID) group over key records: (is_best, group_size) per record + per-probe counters."""
+    n = len(keys)
+    is_best = np.zeros(n, dtype=np.uint8)
+    gsize = np.zeros(n, dtype=np.int32)
+    stats = ProbeStatsHost(n_probes)
+    if n == 0:
+        return is_best, gsize, stats
+    order = np.lexsort((keys["rank"], keys["uid"], keys["probe"]))
+    p, u = keys["probe"][order], keys["uid"][order]
+    head = np.ones(n, dtype=bool)
+    head[1:] = (p[1:] != p[:-1]) | (u[1:] != u[:-1])
+    starts = np.nonzero(head)[0]
+    sizes = np.diff(np.append(starts, n))
+    is_best[order[starts]] = 1
+    gsize[order] = np.repeat(sizes, sizes)
+    for s, sz in zip(starts, sizes):
+        pr = int(p[s])
+        stats.unique_pairs[pr] += 1
+        stats.duplicate_pairs[pr] += sz - 1
+        stats.max_pairs_per_uid[pr] = max(stats.max_pairs_per_uid[pr], sz)
+    return is_best, gsize, stats

@@ -173,6 +173,25 @@ def test_dedup_vs_oracle(ctx):
         assert (st.max_pairs_per_uid == est.max_pairs_per_uid).all()
 
 
+def test_dedup_sharded_entry_points(ctx):
+    """hsq_dedup_keys -> (device records) -> hsq_dedup_reduce_keys equals hsq_dedup_batch; records equal the stand-in."""
+    import torch
+    from bioinformatics_b200 import sharded
+    probes = synth.make_probes(50, seed=3)
+    pairs, _ = synth.drop_n_pairs(synth.make_pairs(probes, 20000, read_len=150, ext_uid_len=6, lig_uid_len=2, seed=4))
+    pairs.q1.data[::7] = ord("5")
+    be = sharded.DeviceBackend(ctx)
+    keys = be.keys(pairs, 6, 2, probes.n, 1000)
+    exp_keys = O.dedup_keys(pairs, 6, 2, 1000)
+    assert (keys.cpu().numpy().reshape(-1) == exp_keys.view(np.uint8)).all()
+    perm = torch.randperm(keys.shape[0], device=keys.device)  # the owner sees records in arbitrary order
+    best, gsize, stats = be.reduce(keys[perm], 8, probes.n)
+    eb, egs, est = O.dedup_batch(pairs, 6, 2, probes.n)
+    p = perm.cpu().numpy()
+    assert (best.cpu().numpy() == eb[p]).all() and (gsize.cpu().numpy() == egs[p]).all()
+    assert (stats.unique_pairs == est.unique_pairs).all() and (stats.max_pairs_per_uid == est.max_pairs_per_uid).all()
+
+
 def test_dedup_int16_wraparound(ctx):
     """2 x 450 bp at Q41+ overflows a Java short: best-pair choice must follow the wrapped sum."""
     rng = np.random.default_rng(9)
