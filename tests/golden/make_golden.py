@@ -34,7 +34,7 @@ def reference_kats():
          "md": "0^TCCCCCCCAGCTTGTGGAGCCT0C127"},
         {"source": T + "CigarStringUtilTest.java:87-96", "reference": T4_REF, "query": T3_QRY, "reverse": False,
          "md": "0^TCCCCCCCAGCTTGTGGAGCCT0C64^CAA63"},
-        {"source": T + "CigarStringUtilTest.java:99-109", "reference": T2_REF, "query": T2_QRY, "reverse": True,
+        {"source": T + "CigarStringUtilTest.java:99-109", "reference": T2_REF[::-1], "query": T2_QRY[::-1], "reverse": True,
          "md": "0^GTCCATCGCCACTGGGATGG11C118"},
     ]
     k["other"] = [

@@ -1,0 +1,97 @@
+"""Committed golden vectors (tests/golden/, generator: make_golden.py).
+
+reference_kats.json : the reference's own known-answer vectors -> pin the oracle (CPU) and the CUDA path (GPU).
+oracle_vectors.json : frozen oracle outputs for the functions no reference test pins -> regression net for both sides.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from bioinformatics_b200 import synth
+from bioinformatics_b200.batches import PairBatchHost
+from oracle import oracle as O
+
+HERE = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+KATS = json.load(open(os.path.join(HERE, "reference_kats.json")))
+VEC = json.load(open(os.path.join(HERE, "oracle_vectors.json")))
+
+
+def _extend_inputs():
+    e = VEC["extend"]
+    probes = synth.make_probes(e["n_probes"], seed=e["probe_seed"])
+    pairs = synth.make_pairs(probes, e["n_pairs"], read_len=e["read_len"], ext_uid_len=e["uid"], seed=e["read_seed"],
+                             sub_rate=e["rates"][0], ins_rate=e["rates"][1], del_rate=e["rates"][2])
+    # the fixture carries the reads themselves: the generator must still produce them, else the fixture is stale
+    assert pairs.r1.strings() == e["r1"] and pairs.r2.strings() == e["r2"] and pairs.probe_id.tolist() == e["probe_id"]
+    return probes, pairs
+
+
+def _check_align(a, flags_key="align"):
+    g = VEC[flags_key]
+    assert a.score.tolist() == g["score"] and a.op_strings() == g["ops"]
+    if "md" in g:
+        assert a.mds() == g["md"] and a.rmds() == g["rmd"]
+        assert a.edit_distance.tolist() == g["edit_distance"] and a.matches.tolist() == g["matches"]
+
+
+def _check_extend(e):
+    g = VEC["extend"]
+    for f in ("ok", "primer_end", "score", "pos", "read_start", "read_stop", "nm", "tlen"):
+        assert getattr(e, f).tolist() == g[f], f
+    assert e.cigars() == g["cigar"] and e.mds() == g["md"] and int(e.cells) == g["cells"]
+
+
+def _check_dedup(b, gs, st):
+    g = VEC["dedup"]
+    assert b.tolist() == g["is_best"] and gs.tolist() == g["group_size"]
+    assert st.unique_pairs.tolist() == g["unique_pairs"] and st.max_pairs_per_uid.tolist() == g["max_pairs_per_uid"]
+
+
+# ---- CPU: the oracle against the committed vectors -------------------------------------------------------------------
+def test_oracle_reference_kats():
+    for k in KATS["md"]:
+        assert O.align_batch([k["reference"]], [k["query"]]).mds()[0] == k["md"], k["source"]
+    for k in KATS["md_trimmed_with_full_cigar"]:
+        assert O.md_trimmed_with_full_cigar(k["reference"], k["query"], k["reverse"]) == k["md"], k["source"]
+    ed, first, trim = KATS["other"]
+    assert O.cigar_edit_distance(ed["reference"], ed["query"]) == ed["expected"]
+    assert O.index_of_first_match_in_reference(first["reference"], first["query"]) == first["expected"]
+    s, q = O.trim_batch([trim["read"]], [trim["qual"]], trim["first"], trim["last"], True)
+    assert len(s.strings()[0]) == trim["expected_length"] == len(q.strings()[0])
+
+
+def test_oracle_frozen_vectors():
+    g = VEC["align"]
+    _check_align(O.align_batch(g["refs"], g["qrys"]))
+    _check_align(O.align_batch(g["refs"], g["qrys"], flags=1), "align_penalize_start")
+    probes, pairs = _extend_inputs()
+    _check_extend(O.extend_batch(probes, pairs, cigar_cap=64, md_cap=96))
+    clean, _ = synth.drop_n_pairs(pairs)
+    _check_dedup(*O.dedup_batch(clean, 10, 0, probes.n))
+    for k in VEC["primer_end"]:
+        end, w = O.primer_end(k["primer"], k["read"])
+        assert end == k["end"] and abs(w - k["weighted"]) < 1e-12
+
+
+# ---- GPU: the CUDA path against the same vectors ---------------------------------------------------------------------
+@pytest.mark.gpu
+def test_cuda_reference_kats_and_frozen_vectors():
+    from bioinformatics_b200._lib import Context
+    with Context(0) as ctx:
+        for k in KATS["md"]:
+            assert ctx.align_batch([k["reference"]], [k["query"]]).mds()[0] == k["md"], k["source"]
+        ed, first, trim = KATS["other"]
+        a = ctx.align_batch([ed["reference"], first["reference"]], [ed["query"], first["query"]])
+        assert int(a.edit_distance[0]) == ed["expected"] and int(a.first_q[1]) == first["expected"]
+        s, q = ctx.trim_batch([trim["read"]], [trim["qual"]], trim["first"], trim["last"], True)
+        assert len(s.strings()[0]) == trim["expected_length"]
+        g = VEC["align"]
+        _check_align(ctx.align_batch(g["refs"], g["qrys"]))
+        _check_align(ctx.align_batch(g["refs"], g["qrys"], flags=1), "align_penalize_start")
+        probes, pairs = _extend_inputs()
+        ctx.set_probes(probes)
+        _check_extend(ctx.extend_batch(pairs, cigar_cap=64, md_cap=96))
+        clean, _ = synth.drop_n_pairs(pairs)
+        _check_dedup(*ctx.dedup_batch(clean, 10, 0, probes.n))
