@@ -30,12 +30,13 @@ struct CallTimer {  // brackets the kernels + copies of one batch call with even
 int reset_status(hsq_ctx* ctx) {
     HSQ_CUDA(ctx, ctx->status.ensure(64));
     HSQ_CUDA(ctx, ctx->cells.ensure(64));
-    HSQ_CUDA(ctx, cudaMemsetAsync(ctx->status.p, 0, 64, ctx->stream));
-    HSQ_CUDA(ctx, cudaMemsetAsync(ctx->cells.p, 0, 64, ctx->stream));
+    // words 0..2 (error, max lengths) always; word 3 (slot overflow) and the cell counter only at the start of a call
+    HSQ_CUDA(ctx, cudaMemsetAsync(ctx->status.p, 0, ctx->keep_counters ? 12 : 64, ctx->stream));
+    if (!ctx->keep_counters) HSQ_CUDA(ctx, cudaMemsetAsync(ctx->cells.p, 0, 64, ctx->stream));
     return HSQ_OK;
 }
 
-// status word 0 = error code, words 1.. = max lengths
+// status word 0 = error code, words 1..2 = max lengths, word 3 = "an output slot was too small"
 int* d_status(hsq_ctx* ctx) { return ctx->status.as<int>(); }
 int* d_maxlen(hsq_ctx* ctx, int slot) { return ctx->status.as<int>() + 1 + slot; }
 
@@ -100,7 +101,7 @@ DeviceProbes probe_view(const hsq_ctx* ctx) {
 template <class T>
 int d2h(hsq_ctx* ctx, T* host, const T* dev, size_t count) {
     if (!host || count == 0) return HSQ_OK;
-    HSQ_CUDA(ctx, cudaMemcpyAsync(host, dev, count * sizeof(T), cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(host, dev, count * sizeof(T), cudaMemcpyDeviceToHost, ctx->io ? ctx->io : ctx->stream));
     return HSQ_OK;
 }
 
@@ -134,6 +135,13 @@ int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) {
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev_user0));
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev_user1));
+    HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
+    HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; k++) {
+        HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_in[k], cudaEventDisableTiming));
+        HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_comp[k], cudaEventDisableTiming));
+        HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_out[k], cudaEventDisableTiming));
+    }
     HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_status, 64));
     HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_cells, 64));
     std::vector<double> tbl(POW95_N);
@@ -152,9 +160,10 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     hsq::DevBuf* bufs[] = {&ctx->p_rev, &ctx->p_ext_start, &ctx->p_ext_stop, &ctx->p_lig_start, &ctx->p_lig_stop, &ctx->q1, &ctx->q2,
                            &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
                            &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
-                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo};
+                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->alt_out_i32,
+                           &ctx->alt_out_u8, &ctx->alt_out_slots, &ctx->alt_pair_ok};
     for (auto* b : bufs) b->release();
-    hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb};
+    hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb, &ctx->alt_r1, &ctx->alt_r2};
     for (auto* s : seqs) s->release();
     cudaFreeHost(ctx->h_status);
     cudaFreeHost(ctx->h_cells);
@@ -162,6 +171,13 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->ev_user0);
     cudaEventDestroy(ctx->ev_user1);
+    for (int k = 0; k < 2; k++) {
+        cudaEventDestroy(ctx->ev_in[k]);
+        cudaEventDestroy(ctx->ev_comp[k]);
+        cudaEventDestroy(ctx->ev_out[k]);
+    }
+    cudaStreamDestroy(ctx->s_in);
+    cudaStreamDestroy(ctx->s_out);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
 }

@@ -14,7 +14,7 @@ int upload_pairs_raw(hsq_ctx* ctx, const hsq_pair_batch* pb) {
     if (pb->r1.n != pb->n || pb->r2.n != pb->n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
     if (n && !pb->probe_id) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe_id is null");
     HSQ_CUDA(ctx, ctx->probe_id.ensure(n * 4 + 16));
-    if (n) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->probe_id.p, pb->probe_id, n * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (n) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->probe_id.p, pb->probe_id, n * 4, cudaMemcpyHostToDevice, ctx->io ? ctx->io : ctx->stream));
     if ((rc = copy_seqs(ctx, &pb->r1, &ctx->r1))) return rc;
     if ((rc = copy_seqs(ctx, &pb->r2, &ctx->r2))) return rc;
     return HSQ_OK;
@@ -145,8 +145,8 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
     return HSQ_OK;
 }
 
-// fetch: device -> host copies of the results of the last run
-int extend_fetch(hsq_ctx* ctx, hsq_extend_out* o) {
+// fetch, part 1: device -> host copies of the results of the last run (asynchronous, on the context's copy stream)
+int extend_fetch_copies(hsq_ctx* ctx, hsq_extend_out* o) {
     if (!ctx->ext_ran || ctx->ext_n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "no results to fetch");
     const int64_t n = ctx->ext_n;
     const size_t n2 = (size_t)(2 * n);
@@ -162,12 +162,110 @@ int extend_fetch(hsq_ctx* ctx, hsq_extend_out* o) {
     if ((rc = d2h(ctx, o->cigar, d.cigar, n2 * (size_t)d.cigar_cap))) return rc;
     if ((rc = d2h(ctx, o->md, d.md, n2 * (size_t)d.md_cap))) return rc;
     if ((rc = d2h(ctx, o->pair_ok, ctx->pair_ok.as<uint8_t>(), (size_t)n))) return rc;
+    return HSQ_OK;
+}
+
+// fetch, part 2: cell counter and status of everything run since the counters were last reset (synchronises)
+int extend_fetch_finish(hsq_ctx* ctx, hsq_extend_out* o) {
+    int rc;
     HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    int w[1];
-    if ((rc = read_status(ctx, w, 1))) return rc;
+    int w[4];
+    if ((rc = read_status(ctx, w, 4))) return rc;
+    if (ctx->io && ctx->io != ctx->stream) HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->io));
     o->cells = (int64_t)ctx->h_cells[0];
     if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend: ") + status_message(w[0]));
+    if (w[3] != 0) return fail(ctx, HSQ_ERR_OVERFLOW, std::string("hsq_extend: ") + status_message(HSQ_ERR_OVERFLOW));
     return HSQ_OK;
+}
+
+int extend_fetch(hsq_ctx* ctx, hsq_extend_out* o) {
+    int rc = extend_fetch_copies(ctx, o);
+    return rc ? rc : extend_fetch_finish(ctx, o);
+}
+
+// The extend-batch buffers exist twice; a chunked call alternates between the two sets.
+void swap_extend_buffers(hsq_ctx* ctx) {
+    std::swap(ctx->r1, ctx->alt_r1);
+    std::swap(ctx->r2, ctx->alt_r2);
+    std::swap(ctx->probe_id, ctx->alt_probe_id);
+    std::swap(ctx->out_i32, ctx->alt_out_i32);
+    std::swap(ctx->out_u8, ctx->alt_out_u8);
+    std::swap(ctx->out_slots, ctx->alt_out_slots);
+    std::swap(ctx->pair_ok, ctx->alt_pair_ok);
+}
+
+hsq_seqs seqs_window(const hsq_seqs& s, int64_t a, int64_t n) {
+    hsq_seqs w;
+    w.data = s.data;
+    w.offsets = s.offsets + a;
+    w.n = n;
+    return w;
+}
+
+// hsq_extend_batch for a large batch: chunks flow through  H2D (s_in) | kernels (stream) | D2H (s_out)  with the two
+// buffer sets, so the copies of chunks c+1 and c-1 hide behind the kernels of chunk c.
+int extend_pipelined(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o, int n_chunks) {
+    const int64_t n = pb->n;
+    const int64_t per = (n + n_chunks - 1) / n_chunks;
+    int rc = HSQ_OK;
+    auto chunk_in = [&](int c) {
+        const int64_t a = (int64_t)c * per, m = std::min(per, n - a);
+        hsq_pair_batch w = *pb;
+        w.n = m;
+        w.probe_id = pb->probe_id + a;
+        w.read_index = pb->read_index ? pb->read_index + a : nullptr;
+        w.r1 = seqs_window(pb->r1, a, m);
+        w.r2 = seqs_window(pb->r2, a, m);
+        return w;
+    };
+    auto chunk_out = [&](int c) {
+        const int64_t a = (int64_t)c * per;
+        hsq_extend_out w = *o;
+        int32_t** f32[9] = {&w.primer_end, &w.score, &w.pos, &w.read_start, &w.read_stop, &w.nm, &w.tlen, &w.cigar_len, &w.md_len};
+        for (auto f : f32) if (*f) *f += 2 * a;
+        if (w.ok) w.ok += 2 * a;
+        if (w.overflow) w.overflow += 2 * a;
+        if (w.cigar) w.cigar += 2 * a * (int64_t)o->cigar_cap;
+        if (w.md) w.md += 2 * a * (int64_t)o->md_cap;
+        if (w.pair_ok) w.pair_ok += a;
+        return w;
+    };
+    ctx->keep_counters = false;
+    ctx->io = ctx->s_in;
+    hsq_pair_batch in0 = chunk_in(0);
+    rc = extend_stage(ctx, &in0);
+    if (!rc) HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_in[0], ctx->s_in));
+    for (int c = 0; c < n_chunks && !rc; c++) {
+        const int slot = c & 1;
+        HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_in[slot], 0));
+        if (c >= 2) HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_out[slot], 0));  // this set's results have left
+        rc = extend_run(ctx, o->cigar_cap, o->md_cap);  // (synchronises once, after the encode kernels)
+        ctx->keep_counters = true;
+        if (rc) break;
+        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_comp[slot], ctx->stream));
+        HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_out, ctx->ev_comp[slot], 0));
+        ctx->io = ctx->s_out;
+        hsq_extend_out wo = chunk_out(c);
+        rc = extend_fetch_copies(ctx, &wo);
+        if (rc) break;
+        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_out[slot], ctx->s_out));
+        swap_extend_buffers(ctx);
+        if (c + 1 < n_chunks) {  // the other set's inputs are free: chunk c-1's kernels finished before run(c) returned
+            ctx->io = ctx->s_in;
+            hsq_pair_batch in = chunk_in(c + 1);
+            rc = extend_stage(ctx, &in);
+            if (!rc) HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_in[slot ^ 1], ctx->s_in));
+        }
+    }
+    ctx->io = ctx->s_out;
+    int rc2 = extend_fetch_finish(ctx, o);
+    cudaStreamSynchronize(ctx->s_in);
+    cudaStreamSynchronize(ctx->s_out);
+    ctx->io = nullptr;
+    ctx->keep_counters = false;
+    ctx->ext_n = -1;  // no single staged batch remains
+    ctx->ext_ran = false;
+    return rc ? rc : rc2;
 }
 
 }  // namespace
@@ -185,9 +283,16 @@ extern "C" int32_t hsq_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, h
     if (pairs->n < 0 || out->cigar_cap < 0 || out->md_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
-    rc = extend_stage(ctx, pairs);
-    if (!rc) rc = extend_run(ctx, out->cigar_cap, out->md_cap);
-    if (!rc || rc == HSQ_ERR_OVERFLOW) { int r2 = extend_fetch(ctx, out); if (!rc) rc = r2; }
+    // chunks of >= 256 k pairs, at most 8 (HSQ_EXTEND_CHUNKS overrides; 1 = no pipelining)
+    int n_chunks = (int)std::min<int64_t>(8, pairs->n / 262144);
+    if (const char* e = getenv("HSQ_EXTEND_CHUNKS")) n_chunks = atoi(e);
+    if (n_chunks > 1 && pairs->n >= n_chunks) {
+        rc = extend_pipelined(ctx, pairs, out, n_chunks);
+    } else {
+        rc = extend_stage(ctx, pairs);
+        if (!rc) rc = extend_run(ctx, out->cigar_cap, out->md_cap);
+        if (!rc) rc = extend_fetch(ctx, out);
+    }
     int rc2 = timer.finish();
     return rc ? rc : rc2;
 }

@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <algorithm>
 #include <string>
 #include <vector>
 #include <cstdio>
@@ -63,6 +64,13 @@ struct hsq_ctx {
     hsq::DevBuf ptr_words, brow, cols, status, cells, misc, out_i32, out_u8, out_slots, pair_ok;
     hsq::DevBuf sort_a, sort_b, sort_c, sort_d, sort_tmp, flags, slow, colinfo;
     bool force_dp32 = false;
+    // second set of extend-batch buffers + copy streams: hsq_extend_batch pipelines chunks (H2D | kernels | D2H)
+    hsq::DevSeqsOwned alt_r1, alt_r2;
+    hsq::DevBuf alt_probe_id, alt_out_i32, alt_out_u8, alt_out_slots, alt_pair_ok;
+    cudaStream_t io = nullptr;      // stream the host<->device copies of the current call go to (default: stream)
+    cudaStream_t s_in = nullptr, s_out = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+    bool keep_counters = false;     // chunks after the first: keep the cell counter and the overflow flag
     int64_t ext_n = -1;  // staged extend batch
     bool ext_ran = false;
     hsq::ExtendDeviceOut ext_out{};
@@ -97,19 +105,33 @@ inline const char* status_message(int st) {
     }
 }
 
-// host -> device copy of a ragged ASCII batch (no kernels)
+__global__ void rebase_offsets_kernel(int64_t* __restrict__ offsets, int64_t n, int64_t base) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) offsets[i] -= base;
+}
+
+// host -> device copy of a ragged ASCII batch on the context's copy stream.  offsets need not start at 0 (a window of a
+// larger batch): the device copy is rebased.
 inline int copy_seqs(hsq_ctx* ctx, const hsq_seqs* s, DevSeqsOwned* d) {
     if (!s || s->n < 0 || !s->offsets) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null sequence batch");
-    if (s->offsets[0] != 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "offsets must start at 0");
+    const int64_t base = s->offsets[0];
+    if (base < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "offsets must not be negative");
     d->n = s->n;
-    d->total = s->offsets[s->n];
+    d->total = s->offsets[s->n] - base;
     if (d->total < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative batch size");
     if (d->total > 0 && !s->data) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null sequence data");
     HSQ_CUDA(ctx, d->ascii.ensure((size_t)d->total + 16));
     HSQ_CUDA(ctx, d->codes.ensure((size_t)d->total + 16));
     HSQ_CUDA(ctx, d->offsets.ensure((size_t)(s->n + 1) * sizeof(int64_t)));
-    if (d->total > 0) HSQ_CUDA(ctx, cudaMemcpyAsync(d->ascii.p, s->data, (size_t)d->total, cudaMemcpyHostToDevice, ctx->stream));
-    HSQ_CUDA(ctx, cudaMemcpyAsync(d->offsets.p, s->offsets, (size_t)(s->n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, ctx->stream));
+    cudaStream_t st = ctx->io ? ctx->io : ctx->stream;
+    if (d->total > 0) HSQ_CUDA(ctx, cudaMemcpyAsync(d->ascii.p, s->data + base, (size_t)d->total, cudaMemcpyHostToDevice, st));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(d->offsets.p, s->offsets, (size_t)(s->n + 1) * sizeof(int64_t), cudaMemcpyHostToDevice, st));
+    if (base != 0) {
+        const int blocks = (int)std::min<int64_t>((s->n + 256) / 256, (int64_t)ctx->sm_count * 4);
+        rebase_offsets_kernel<<<blocks, 256, 0, st>>>(d->offsets.as<int64_t>(), s->n + 1, base);
+        ctx->launches++;
+    }
     return HSQ_OK;
 }
 

@@ -152,7 +152,7 @@ __global__ void finalize_extend_kernel(DeviceProbes probes, const int32_t* __res
         out.pos[2 * k + 1] = (!one_rev) ? adjacent - out.ref_len[2 * k + 1] : adjacent + 1;
     }
     pair_ok[k] = (ok1 && ok2) ? 1 : 0;
-    if ((out.overflow[2 * k] | out.overflow[2 * k + 1]) != 0) atomicMin(status, HSQ_ERR_OVERFLOW);
+    if ((out.overflow[2 * k] | out.overflow[2 * k + 1]) != 0) atomicMin(status + 3, HSQ_ERR_OVERFLOW);  // word 3: not fatal
 }
 
 struct AlignDeviceOut {

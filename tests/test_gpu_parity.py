@@ -123,6 +123,21 @@ def test_extend_forced_32bit_kernel(monkeypatch):
     H.assert_extend_equal(got, O.extend_batch(probes, pairs, cigar_cap=64, md_cap=96, nthreads=8))
 
 
+@pytest.mark.parametrize("chunks", [2, 3, 7])
+def test_extend_chunked_pipeline(ctx, monkeypatch, chunks):
+    """HSQ_EXTEND_CHUNKS forces the H2D | kernels | D2H pipeline of hsq_extend_batch on a small batch: same results."""
+    monkeypatch.setenv("HSQ_EXTEND_CHUNKS", str(chunks))
+    probes = synth.make_probes(80, seed=15)
+    pairs = synth.make_pairs(probes, 5001, read_len=150, ext_uid_len=10, seed=16, sub_rate=0.02, ins_rate=0.003, del_rate=0.003)
+    ctx.set_probes(probes)
+    ctx.set_scorer(scorer())
+    got = ctx.extend_batch(pairs, cigar_cap=64, md_cap=96)
+    H.assert_extend_equal(got, O.extend_batch(probes, pairs, cigar_cap=64, md_cap=96, nthreads=8))
+    with pytest.raises(HsqError) as e:  # a too small slot in some chunk is reported, after all chunks ran
+        ctx.extend_batch(pairs, cigar_cap=3, md_cap=96)
+    assert e.value.status == A.HSQ_ERR_OVERFLOW
+
+
 def test_extend_non_acgt_capture_target(ctx):
     """IUPAC / N codes inside the capture target (the DP reference) take the kernels' slow-column path."""
     rng = np.random.default_rng(123)
