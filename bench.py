@@ -40,6 +40,8 @@ def parse():
     ap.add_argument("--pairs", type=int, default=5_000_000, help="read pairs per GPU (10 M read ends)")
     ap.add_argument("--cpu-sample-pairs", type=int, default=0, help="0 = size the CPU sample for ~15 s")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--stage-pairs", type=int, default=1_000_000, help="pairs per GPU of the trim/dedup side measurements")
+    ap.add_argument("--no-stages", action="store_true", help="skip the trim/dedup side measurements")
     return ap.parse_args()
 
 
@@ -119,6 +121,66 @@ def cpu_baseline(probes, pairs, sample_pairs, threads):
             "sample": "%d read pairs (%d read ends, %.3e cells) of the same synthetic batch, %.1f s" %
                       (sample_pairs, 2 * sample_pairs, r.cells, dt),
             "pairs_per_s": sample_pairs / dt}, dt, r.cells
+
+
+def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
+    """Side measurements of the HBM-bound stages (trim A8, dedup A6/A7), outside the headline's timed region:
+    read-pairs/s through the C ABI with host buffers, on a 1 M pair batch per GPU (2 x 150 bp with qualities).
+    At N > 1 dedup runs sharded: key records -> NCCL all-to-all by probe owner -> reduce -> all-to-all back."""
+    import torch
+    from bioinformatics_b200 import synth, sharded
+    n = args.stage_pairs
+    probes = synth.make_probes(N_PROBES)
+    pairs, _ = synth.drop_n_pairs(synth.make_pairs(probes, n, read_len=READ_LEN, ext_uid_len=UID, seed=synth.SEED_READS + 100 + rank))
+    pairs.read_index = (pairs.read_index.astype(np.int64) + rank * n).astype(np.int32)  # FASTQ ordinals are global
+    out = {"pairs_per_gpu": int(pairs.n), "hbm_peak_gbs": None}
+    # trim: both mates, fixed offsets as HSQUtils trim derives them (UID + primer at 5', 3' clip)
+    first, last = UID + 22, READ_LEN - 23
+    for _ in range(2):
+        ctx.trim_batch(pairs.r1, pairs.q1, first, last, True)
+    barrier()
+    t0 = time.perf_counter()
+    ms_dev = 0.0
+    for sb, qb in ((pairs.r1, pairs.q1), (pairs.r2, pairs.q2)):
+        ctx.trim_batch(sb, qb, first, last, True)
+        ms_dev += ctx.last_timing()[0]
+    barrier()
+    dt = max_over_ranks(time.perf_counter() - t0)
+    out["trim"] = {"read_pairs_per_s": pairs.n * world / dt, "ms_host_to_host": dt * 1e3, "ms_device_incl_copies": ms_dev,
+                   "algorithmic_bytes_per_pair": 8 * READ_LEN}
+    # dedup
+    if world == 1:
+        for _ in range(2):
+            ctx.dedup_batch(pairs, UID, 0, probes.n)
+        barrier()
+        t0 = time.perf_counter()
+        best, gs, st = ctx.dedup_batch(pairs, UID, 0, probes.n)
+        ms_dev = ctx.last_timing()[0]
+        barrier()
+        dt = time.perf_counter() - t0
+        uniq = int(best.sum())
+        mode = "hsq_dedup_batch, one GPU"
+    else:
+        be = sharded.DeviceBackend(ctx)
+        for _ in range(2):
+            sharded.dedup_sharded(be, pairs, UID, 0, probes.n)
+        barrier()
+        t0 = time.perf_counter()
+        best, gs, st = sharded.dedup_sharded(be, pairs, UID, 0, probes.n)
+        barrier()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        ms_dev = None
+        t = torch.tensor([float(best.sum())], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t)
+        uniq = int(t.item())
+        mode = "sharded: hsq_dedup_keys -> NCCL all_to_all by probe owner -> hsq_dedup_reduce_keys -> all_to_all back"
+    out["dedup"] = {"read_pairs_per_s": pairs.n * world / dt, "ms_host_to_host": dt * 1e3, "ms_device_incl_copies": ms_dev,
+                    "unique_pairs": uniq, "mode": mode, "algorithmic_bytes_per_pair": 2 * READ_LEN + 16 + 24 + 48 + 25}
+    try:
+        out["hbm_peak_gbs"] = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+    except Exception:
+        pass
+    return out
 
 
 def run_reference(args):
@@ -250,6 +312,9 @@ def main():
     e2e_s = max_over_ranks(max(e2e_wall, e2e_ms_dev / args.steps * 1e-3))
     e2e_value = total_cells / e2e_s / 1e9
 
+    stages = None
+    if not args.no_stages:
+        stages = stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks)
     line = None
     if rank == 0:
         peak = ctx.int32_peak(2.0)
@@ -268,11 +333,11 @@ def main():
                 "read_pairs_per_s": n * world / (ms_step * 1e-3),
                 "roofline": {"bound": "int32_alu", "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "Tiop/s",
                              "frac": achieved / peak, "traffic": None,
-                             "note": "12 algorithmic INT32 ops per DP cell x cells per launch / CUDA-event time of hsq_extend_run "
-                                     "(extend_kernel is >99%% of it); peak = sustained INT32 issue rate measured in this run by "
+                             "note": "12 algorithmic INT32 ops per DP cell x cells per step / CUDA-event time of hsq_extend_run "
+                                     "(capture2_kernel + primer2_kernel are ~94%% of it, profiles/); peak = sustained INT32 issue rate measured in this run by "
                                      "hsq_int32_peak (IMAD/VIMNMX/LOP3 micro-kernel, 2 s); nominal 148x128x1.965 GHz = %.1f Tiop/s; "
                                      "MEASURED_PEAKS.json holds no INT32 figure" % (nominal / 1e12)},
-                "clocks": clocks}
+                "clocks": clocks, "stages": stages}
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
         base, _, _ = cpu_baseline(probes, pairs, args.cpu_sample_pairs, threads)

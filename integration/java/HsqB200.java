@@ -1,0 +1,158 @@
+/*
+ * HsqB200 -- Panama FFM (JDK 22+) binding of include/hsq_b200.h for nimblegen_heatseq.
+ *
+ * NOT compiled or run in this repository's image (no JVM there); the same ABI is exercised from Python (ctypes) by
+ * tests/.  It shows the reference-side binding a maintainer adds: one context per GPU, pinned staging buffers filled
+ * from the Strings the reference already holds, one downcall per batch.  There is no JVM-side compute fallback: every
+ * failure surfaces as an exception.
+ */
+package com.roche.heatseq.b200;
+
+import java.lang.foreign.*;
+import java.lang.invoke.MethodHandle;
+import java.nio.charset.StandardCharsets;
+
+import static java.lang.foreign.ValueLayout.*;
+
+public final class HsqB200 implements AutoCloseable {
+
+    public static final int HSQ_OK = 0, ERR_INVALID_ARGUMENT = -1, ERR_CUDA = -2, ERR_NO_DEVICE = -3, ERR_BAD_CHARACTER = -4,
+            ERR_UNSUPPORTED = -5, ERR_OUT_OF_RANGE = -6, ERR_OVERFLOW = -7;
+    public static final int PRIMER_NOT_FOUND = -2147483647;
+
+    private static final Linker LINKER = Linker.nativeLinker();
+    private static final SymbolLookup LIB =
+            SymbolLookup.libraryLookup(System.getProperty("hsq.b200.lib", "libhsq_b200.so"), Arena.global());
+
+    private static MethodHandle fn(String name, FunctionDescriptor d) {
+        return LINKER.downcallHandle(LIB.find(name).orElseThrow(() -> new UnsatisfiedLinkError(name)), d);
+    }
+
+    // ---- struct layouts (field order = include/hsq_b200.h) ----------------------------------------------------------
+    static final StructLayout SCORER = MemoryLayout.structLayout(JAVA_INT.withName("match"), JAVA_INT.withName("mismatch"),
+            JAVA_INT.withName("gap_extend"), JAVA_INT.withName("gap_start"));
+    static final StructLayout SEQS = MemoryLayout.structLayout(ADDRESS.withName("data"), ADDRESS.withName("offsets"), JAVA_LONG.withName("n"));
+    static final StructLayout PROBE_TABLE = MemoryLayout.structLayout(JAVA_LONG.withName("n"), ADDRESS.withName("reverse_strand"),
+            ADDRESS.withName("ext_start"), ADDRESS.withName("ext_stop"), ADDRESS.withName("lig_start"), ADDRESS.withName("lig_stop"),
+            ADDRESS.withName("target_start"), ADDRESS.withName("target_stop"), SEQS.withName("ext"), SEQS.withName("lig"),
+            SEQS.withName("target"));
+    static final StructLayout PAIR_BATCH = MemoryLayout.structLayout(JAVA_LONG.withName("n"), ADDRESS.withName("probe_id"),
+            ADDRESS.withName("read_index"), SEQS.withName("r1"), SEQS.withName("r2"), ADDRESS.withName("q1"), ADDRESS.withName("q2"));
+    static final StructLayout EXTEND_OUT = MemoryLayout.structLayout(JAVA_INT.withName("cigar_cap"), JAVA_INT.withName("md_cap"),
+            ADDRESS.withName("ok"), ADDRESS.withName("primer_end"), ADDRESS.withName("score"), ADDRESS.withName("pos"),
+            ADDRESS.withName("read_start"), ADDRESS.withName("read_stop"), ADDRESS.withName("nm"), ADDRESS.withName("tlen"),
+            ADDRESS.withName("cigar_len"), ADDRESS.withName("cigar"), ADDRESS.withName("md_len"), ADDRESS.withName("md"),
+            ADDRESS.withName("overflow"), ADDRESS.withName("pair_ok"), JAVA_LONG.withName("cells"));
+    static final StructLayout PROBE_STATS = MemoryLayout.structLayout(JAVA_LONG.withName("n_probes"), ADDRESS.withName("unique_pairs"),
+            ADDRESS.withName("duplicate_pairs"), ADDRESS.withName("max_pairs_per_uid"));
+
+    // ---- downcall handles --------------------------------------------------------------------------------------------
+    private static final MethodHandle CTX_CREATE = fn("hsq_ctx_create", FunctionDescriptor.of(JAVA_INT, JAVA_INT, ADDRESS));
+    private static final MethodHandle CTX_DESTROY = fn("hsq_ctx_destroy", FunctionDescriptor.ofVoid(ADDRESS));
+    private static final MethodHandle LAST_ERROR = fn("hsq_last_error", FunctionDescriptor.of(ADDRESS, ADDRESS));
+    private static final MethodHandle PINNED_ALLOC = fn("hsq_pinned_alloc", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS));
+    private static final MethodHandle PINNED_FREE = fn("hsq_pinned_free", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle SET_SCORER = fn("hsq_set_scorer", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle SET_PROBES = fn("hsq_set_probes", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle TRIM = fn("hsq_trim_batch", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, JAVA_INT,
+            JAVA_INT, JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle DEDUP = fn("hsq_dedup_batch", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT,
+            ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle EXTEND = fn("hsq_extend_batch", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+
+    private final Arena arena = Arena.ofShared();
+    private final MemorySegment ctx;
+
+    public HsqB200(int device) {
+        MemorySegment out = arena.allocate(ADDRESS);
+        int st = invokeInt(CTX_CREATE, device, out);
+        if (st != HSQ_OK) throw new HsqException(st, lastError(MemorySegment.NULL));  // e.g. ERR_NO_DEVICE: never fall back
+        ctx = out.get(ADDRESS, 0);
+    }
+
+    /** SimpleAlignmentScorer's four numbers (COMMON/alignment/SimpleAlignmentScorer.java:28-31). */
+    public void setScorer(int match, int mismatch, int gapExtend, int gapStart) {
+        MemorySegment s = arena.allocate(SCORER);
+        s.set(JAVA_INT, 0, match);
+        s.set(JAVA_INT, 4, mismatch);
+        s.set(JAVA_INT, 8, gapExtend);
+        s.set(JAVA_INT, 12, gapStart);
+        check(invokeInt(SET_SCORER, ctx, s));
+    }
+
+    /** Pinned host staging memory the caller fills straight from Strings (ISO_8859_1 bytes). */
+    public MemorySegment pinned(long bytes) {
+        MemorySegment out = arena.allocate(ADDRESS);
+        check(invokeInt(PINNED_ALLOC, ctx, bytes, out));
+        return out.get(ADDRESS, 0).reinterpret(bytes);
+    }
+
+    /** Ragged ASCII batch -> hsq_seqs inside `parent` at `offset`. */
+    static void putSeqs(MemorySegment parent, long offset, MemorySegment data, MemorySegment offsets, long n) {
+        parent.set(ADDRESS, offset, data);
+        parent.set(ADDRESS, offset + 8, offsets);
+        parent.set(JAVA_LONG, offset + 16, n);
+    }
+
+    /** ParsedProbeFile -> device resident probe table (fields of COMMON/utils/probeinfo/Probe.java:53-69). */
+    public void setProbes(MemorySegment probeTable) { check(invokeInt(SET_PROBES, ctx, probeTable)); }
+
+    /** FilterByUid.reduceReadsByProbeAndUid + findBestData for a batch spanning probes (HSQ/process/FilterByUid.java:71-297). */
+    public void dedup(MemorySegment pairBatch, int extUidLen, int ligUidLen, MemorySegment isBest, MemorySegment groupSize,
+                      MemorySegment probeStats) {
+        check(invokeInt(DEDUP, ctx, pairBatch, extUidLen, ligUidLen, isBest, groupSize, probeStats));
+    }
+
+    /** ExtendReadsToPrimer.extendReadsToPrimers for a batch spanning probes (HSQ/process/ExtendReadsToPrimer.java:347-380). */
+    public void extend(MemorySegment pairBatch, MemorySegment extendOut) { check(invokeInt(EXTEND, ctx, pairBatch, extendOut)); }
+
+    /** FastqReadTrimmer.trim per read (HSQ/process/FastqReadTrimmer.java:309-328). */
+    public void trim(MemorySegment reads, MemorySegment quals, int firstBaseToKeep, int lastBaseToKeep, boolean threePrime,
+                     MemorySegment outSeq, MemorySegment outQual, MemorySegment outOffsets) {
+        check(invokeInt(TRIM, ctx, reads, quals, firstBaseToKeep, lastBaseToKeep, threePrime ? 1 : 0, outSeq, outQual, outOffsets));
+    }
+
+    private static int invokeInt(MethodHandle h, Object... args) {
+        try {
+            return (int) h.invokeWithArguments(args);
+        } catch (Throwable t) {
+            throw new IllegalStateException(t);
+        }
+    }
+
+    private static String lastError(MemorySegment c) {
+        try {
+            return ((MemorySegment) LAST_ERROR.invoke(c)).reinterpret(4096).getString(0, StandardCharsets.ISO_8859_1);
+        } catch (Throwable t) {
+            return "unknown";
+        }
+    }
+
+    private void check(int status) {
+        if (status == HSQ_OK) return;
+        String msg = lastError(ctx);
+        switch (status) {  // the exceptions the Java implementation throws at the same places
+            case ERR_BAD_CHARACTER: throw new IllegalArgumentException(msg);          // IupacNucleotideCode.getCodesFromString
+            case ERR_OUT_OF_RANGE: throw new IndexOutOfBoundsException(msg);          // FastqReadTrimmer.java:310-312, ExtendReadsToPrimer.java:299
+            case ERR_UNSUPPORTED: throw new UnsupportedOperationException(msg);
+            default: throw new HsqException(status, msg);
+        }
+    }
+
+    @Override
+    public void close() {
+        try {
+            CTX_DESTROY.invoke(ctx);
+        } catch (Throwable ignored) {
+        }
+        arena.close();
+    }
+
+    public static final class HsqException extends RuntimeException {
+        public final int status;
+        public HsqException(int status, String message) {
+            super("hsq status " + status + ": " + message);
+            this.status = status;
+        }
+    }
+}
