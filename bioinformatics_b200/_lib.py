@@ -119,12 +119,16 @@ class Context:
         self._check(st)
         return out
 
-    def trim_batch(self, reads, quals, first, last, three_prime=True):
+    def trim_batch(self, reads, quals, first, last, three_prime=True, out=None):
+        """out: optional (out_seq, out_qual, out_offsets) arrays to write into (e.g. pinned), each large enough."""
         reads = reads if isinstance(reads, A.SeqBatch) else A.SeqBatch.from_strings(reads)
         quals = quals if isinstance(quals, A.SeqBatch) else A.SeqBatch.from_strings(quals)
-        out_seq = np.zeros(max(1, len(reads.data)), dtype=np.uint8)
-        out_qual = np.zeros(max(1, len(reads.data)), dtype=np.uint8)
-        out_off = np.zeros(reads.n + 1, dtype=np.int64)
+        if out is not None:
+            out_seq, out_qual, out_off = out
+        else:
+            out_seq = np.zeros(max(1, len(reads.data)), dtype=np.uint8)
+            out_qual = np.zeros(max(1, len(reads.data)), dtype=np.uint8)
+            out_off = np.zeros(reads.n + 1, dtype=np.int64)
         rc = reads.c()
         self._check(self.lib.hsq_trim_batch(self.h, C.byref(rc), A.ptr(quals.data, A.u8p), C.c_int32(first), C.c_int32(last),
                                             C.c_int32(1 if three_prime else 0), A.ptr(out_seq, A.u8p),
