@@ -102,7 +102,7 @@ def make_workload(n_pairs, rank):
     return probes, pairs
 
 
-def cpu_baseline(probes, pairs, sample_pairs, threads):
+def cpu_baseline(probes, pairs, sample_pairs, threads, keep=None):
     """Oracle (port of the reference algorithm) timed on the host cores on a bounded sample of the workload."""
     from oracle import oracle as O
     O.build()
@@ -117,6 +117,8 @@ def cpu_baseline(probes, pairs, sample_pairs, threads):
     t = time.perf_counter()
     r = O.extend_batch(probes, sub, nthreads=threads)
     dt = time.perf_counter() - t
+    if keep is not None:
+        keep.append(r)
     return {"value": r.cells / dt / 1e9, "unit": "GCUPS", "cores": threads, "kind": "port",
             "sample": "%d read pairs (%d read ends, %.3e cells) of the same synthetic batch, %.1f s" %
                       (sample_pairs, 2 * sample_pairs, r.cells, dt),
@@ -296,6 +298,18 @@ def main():
     ctx.extend_fetch(out)
     cells = out.cells
     assert out.pair_ok.mean() > 0.9, "synthetic batch should extend"
+    CHECK_FIELDS = ExtendResult.FIELDS_I32 + ("ok", "overflow", "pair_ok")
+
+    def digest(o):
+        import hashlib
+        h = hashlib.sha256()
+        for f in CHECK_FIELDS:
+            h.update(np.ascontiguousarray(getattr(o, f)).tobytes())
+        for txt, ln, cap in ((o.cigar, o.cigar_len, CIGAR_CAP), (o.md, o.md_len, MD_CAP)):  # slot bytes up to their length
+            m = np.arange(cap)[None, :] < np.minimum(ln, cap)[:, None]
+            h.update(np.where(m, np.asarray(txt).reshape(-1, cap), 0).astype(np.uint8).tobytes())
+        return h.hexdigest()
+    digest_resident = digest(out)
     sampler = ClockSampler(local)
     barrier()
     sampler.start()
@@ -320,6 +334,10 @@ def main():
         e2e_ms_dev += ctx.last_timing()[0]
     barrier()
     e2e_wall = (time.perf_counter() - t0) / args.steps
+    # size-independent property at the full batch size: the chunked host pipeline returns what the resident run returned
+    parity = {"chunked_e2e_equals_resident": bool(digest(out) == digest_resident and out.cells == cells)}
+    assert parity["chunked_e2e_equals_resident"], "hsq_extend_batch (chunked) differs from stage/run/fetch"
+
     e2e_s = max_over_ranks(max(e2e_wall, e2e_ms_dev / args.steps * 1e-3))
     e2e_value = total_cells / e2e_s / 1e9
 
@@ -348,11 +366,25 @@ def main():
                                      "(capture2_kernel + primer2_kernel are ~94%% of it, profiles/); peak = sustained INT32 issue rate measured in this run by "
                                      "hsq_int32_peak (IMAD/VIMNMX/LOP3 micro-kernel, 2 s); nominal 148x128x1.965 GHz = %.1f Tiop/s; "
                                      "MEASURED_PEAKS.json holds no INT32 figure" % (nominal / 1e12)},
-                "clocks": clocks, "stages": stages}
+                "clocks": clocks, "stages": stages, "parity": parity}
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
-        base, _, _ = cpu_baseline(probes, pairs, args.cpu_sample_pairs, threads)
+        kept = []
+        base, _, _ = cpu_baseline(probes, pairs, args.cpu_sample_pairs, threads, keep=kept)
         line["cpu_baseline"] = base
+        # the oracle's results on the sample against the GPU's results on the same read pairs (bit-exact)
+        exp, k2 = kept[0], 2 * kept[0].n
+        same = all(np.array_equal(getattr(exp, f), getattr(out, f)[:(k2 if f != "pair_ok" else k2 // 2)]) for f in CHECK_FIELDS)
+        for name, cap_g in (("cigar", CIGAR_CAP), ("md", MD_CAP)):
+            ln = getattr(exp, name + "_len")
+            cap_e = getattr(exp, name + "_cap")
+            c = min(cap_e, cap_g)
+            m = np.arange(c)[None, :] < np.minimum(ln, c)[:, None]
+            a_e = np.asarray(getattr(exp, name)).reshape(-1, cap_e)[:, :c]
+            a_g = np.asarray(getattr(out, name)).reshape(-1, cap_g)[:k2, :c]
+            same = same and bool((a_e[m] == a_g[m]).all())
+        parity["gpu_equals_cpu_oracle_on_sample"] = {"read_pairs": int(exp.n), "equal": bool(same)}
+        assert same, "GPU results differ from the CPU oracle on the bench sample"
     elif rank == 0:
         line["cpu_baseline"] = None
     ctx.close()
