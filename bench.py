@@ -365,7 +365,9 @@ def main():
                              "note": "12 algorithmic INT32 ops per DP cell x cells per step / CUDA-event time of hsq_extend_run "
                                      "(capture2_kernel + primer2_kernel are ~94%% of it, profiles/); peak = sustained INT32 issue rate measured in this run by "
                                      "hsq_int32_peak (IMAD/VIMNMX/LOP3 micro-kernel, 2 s); nominal 148x128x1.965 GHz = %.1f Tiop/s; "
-                                     "MEASURED_PEAKS.json holds no INT32 figure" % (nominal / 1e12)},
+                                     "MEASURED_PEAKS.json holds no INT32 figure; the packed kernels do two cells per VIADDMNMX.U16x2 / LOP3 / "
+                                     "IMAD, so the fraction of this scalar-op peak can exceed 1 at long reads (profiles/sweep_lengths_r1.jsonl); "
+                                     "ncu: issue slots 67%% busy, ALU pipe 62%%" % (nominal / 1e12)},
                 "clocks": clocks, "stages": stages, "parity": parity}
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1

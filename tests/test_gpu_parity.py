@@ -207,6 +207,28 @@ def test_dedup_sharded_entry_points(ctx):
     assert (stats.unique_pairs == est.unique_pairs).all() and (stats.max_pairs_per_uid == est.max_pairs_per_uid).all()
 
 
+def test_dedup_config3_shape(ctx):
+    """BASELINE.json configs[2] shape at test size: 14 bp UID, 10 k probes."""
+    probes = synth.make_probes(10000, seed=13)
+    pairs, _ = synth.drop_n_pairs(synth.make_pairs(probes, 150000, read_len=150, ext_uid_len=14, seed=14))
+    ib, gs, st = ctx.dedup_batch(pairs, 14, 0, probes.n)
+    eb, egs, est = O.dedup_batch(pairs, 14, 0, probes.n)
+    assert (ib == eb).all() and (gs == egs).all() and (st.unique_pairs == est.unique_pairs).all()
+    assert (st.duplicate_pairs == est.duplicate_pairs).all() and (st.max_pairs_per_uid == est.max_pairs_per_uid).all()
+
+
+@pytest.mark.parametrize("read_len", [200, 300])
+def test_extend_long_reads(ctx, read_len):
+    """configs[4] lengths: the packed kernels' score range still holds at 2 x 300 bp."""
+    probes = synth.make_probes(100, seed=17, target_len=(read_len - 50, read_len + 10))
+    pairs = synth.make_pairs(probes, 3000, read_len=read_len, ext_uid_len=10, seed=18, sub_rate=0.02, ins_rate=0.003, del_rate=0.003)
+    ctx.set_probes(probes)
+    ctx.set_scorer(scorer())
+    got = ctx.extend_batch(pairs, cigar_cap=64, md_cap=128)
+    H.assert_extend_equal(got, O.extend_batch(probes, pairs, cigar_cap=64, md_cap=128, nthreads=8))
+    assert got.pair_ok.mean() > 0.5
+
+
 def test_dedup_int16_wraparound(ctx):
     """2 x 450 bp at Q41+ overflows a Java short: best-pair choice must follow the wrapped sum."""
     rng = np.random.default_rng(9)
