@@ -138,6 +138,7 @@ int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) {
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
     for (int k = 0; k < 2; k++) {
+        HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_comp[k], cudaStreamNonBlocking));
         HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_in[k], cudaEventDisableTiming));
         HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_comp[k], cudaEventDisableTiming));
         HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_out[k], cudaEventDisableTiming));
@@ -161,7 +162,8 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
                            &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
                            &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
                            &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->alt_out_i32,
-                           &ctx->alt_out_u8, &ctx->alt_out_slots, &ctx->alt_pair_ok};
+                           &ctx->alt_out_u8, &ctx->alt_out_slots, &ctx->alt_pair_ok, &ctx->alt_ptr_words, &ctx->alt_brow, &ctx->alt_cols,
+                           &ctx->alt_colinfo, &ctx->alt_slow, &ctx->alt_sort_a, &ctx->alt_sort_b, &ctx->alt_sort_c};
     for (auto* b : bufs) b->release();
     hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb, &ctx->alt_r1, &ctx->alt_r2};
     for (auto* s : seqs) s->release();
@@ -175,6 +177,7 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
         cudaEventDestroy(ctx->ev_in[k]);
         cudaEventDestroy(ctx->ev_comp[k]);
         cudaEventDestroy(ctx->ev_out[k]);
+        cudaStreamDestroy(ctx->s_comp[k]);
     }
     cudaStreamDestroy(ctx->s_in);
     cudaStreamDestroy(ctx->s_out);

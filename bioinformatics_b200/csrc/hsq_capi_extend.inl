@@ -29,24 +29,32 @@ int extend_stage(hsq_ctx* ctx, const hsq_pair_batch* pb) {
     return HSQ_OK;
 }
 
-// run: encode + DP + finalize on the staged batch; results stay on the device
-int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
+// run: encode + DP + finalize on the staged batch; results stay on the device.
+// host_read_max < 0: the longest read and the probe-id check come from the device (one synchronisation);
+// host_read_max >= 0: the caller measured the reads and validated the probe ids on the host, nothing here blocks.
+int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max = -1) {
     const int64_t n = ctx->ext_n;
     if (n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "no staged batch");
     const size_t n2 = (size_t)(2 * n);
-    int rc = reset_status(ctx);
-    if (rc) return rc;
-    if ((rc = encode_seqs(ctx, &ctx->r1, d_status(ctx), d_maxlen(ctx, 0)))) return rc;
-    if ((rc = encode_seqs(ctx, &ctx->r2, d_status(ctx), d_maxlen(ctx, 1)))) return rc;
-    if (n > 0) {
-        int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
-        check_probe_ids_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, ctx->n_probes, d_status(ctx));
-        ctx->launches++;
+    int rc;
+    int read_max = host_read_max;
+    if (host_read_max < 0) {
+        if ((rc = reset_status(ctx))) return rc;
+        if ((rc = encode_seqs(ctx, &ctx->r1, d_status(ctx), d_maxlen(ctx, 0)))) return rc;
+        if ((rc = encode_seqs(ctx, &ctx->r2, d_status(ctx), d_maxlen(ctx, 1)))) return rc;
+        if (n > 0) {
+            int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
+            check_probe_ids_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, ctx->n_probes, d_status(ctx));
+            ctx->launches++;
+        }
+        int w[3];
+        if ((rc = read_status(ctx, w, 3))) return rc;
+        if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend: ") + (w[0] == HSQ_ERR_INVALID_ARGUMENT ? "probe_id out of range" : status_message(w[0])));
+        read_max = std::max(w[1], w[2]);
+    } else {
+        if ((rc = encode_seqs(ctx, &ctx->r1, d_status(ctx), nullptr))) return rc;
+        if ((rc = encode_seqs(ctx, &ctx->r2, d_status(ctx), nullptr))) return rc;
     }
-    int w[3];
-    if ((rc = read_status(ctx, w, 3))) return rc;
-    if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend: ") + (w[0] == HSQ_ERR_INVALID_ARGUMENT ? "probe_id out of range" : status_message(w[0])));
-    const int read_max = std::max(w[1], w[2]);
     const int primer_max = std::max(ctx->p_ext.max_len, ctx->p_lig.max_len);
     if (2 * primer_max + PRIMER_ALIGNMENT_BUFFER + 2 > POW95_N) return fail(ctx, HSQ_ERR_UNSUPPORTED, "primer longer than the 0.95^d table supports");
     // DP#1: rows = primer, cols = read prefix (<= primer+26); DP#2: rows = read remainder, cols = capture target
@@ -111,6 +119,7 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
         const int32_t* pid = ctx->probe_id.as<int32_t>();
         const DeviceSeqs v1 = ctx->r1.view(), v2 = ctx->r2.view();
         unsigned long long* cells = ctx->cells.as<unsigned long long>();
+        unsigned long long* work = cells + 1 + 2 * ctx->work_slot;
         const int sblocks = (int)std::min<int64_t>((2 * n + 255) / 256, (int64_t)ctx->sm_count * 8);
         // counting sort of the keys in keys.key into `order` (padded buckets); n_active = entries before the skip bucket
         auto bucket_sort = [&](int nk, uint32_t skip_key) -> int {
@@ -127,12 +136,17 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap) {
             primer_key_kernel<<<sblocks, 256, 0, ctx->stream>>>(pv, pid, v1, v2, n, keys1);
             ctx->launches++;
             if ((rc = bucket_sort(n_keys1, keys1.skip_key))) return rc;
-            primer2_kernel<<<grid1, DP2_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_default2, pool2, d, keys, d_status(ctx), cells);
+            HSQ_CUDA(ctx, cudaMemsetAsync(work, 0, 16, ctx->stream));  // work counters of the two packed kernels
+            primer2_kernel<<<grid1, DP2_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_default2, pool2, d, keys, d_status(ctx),
+                                                                cells, work);
         } else {
             primer_kernel<<<grid1, DP_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, n, sp_default, pool, d, keys, d_status(ctx), cells);
         }
         if ((rc = bucket_sort(n_keys, keys.skip_key))) return rc;
-        if (packed2) capture2_kernel<<<grid2, DP2_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_user2, pool2, d, cells);
+        if (packed2) {
+            if (!packed1) HSQ_CUDA(ctx, cudaMemsetAsync(work, 0, 16, ctx->stream));
+            capture2_kernel<<<grid2, DP2_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_user2, pool2, d, cells, work + 1);
+        }
         else capture_kernel<<<grid2, DP_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_user, pool, d, cells);
         ctx->launches += 2;
         HSQ_CUDA(ctx, cudaGetLastError());
@@ -192,6 +206,14 @@ void swap_extend_buffers(hsq_ctx* ctx) {
     std::swap(ctx->out_u8, ctx->alt_out_u8);
     std::swap(ctx->out_slots, ctx->alt_out_slots);
     std::swap(ctx->pair_ok, ctx->alt_pair_ok);
+    std::swap(ctx->ptr_words, ctx->alt_ptr_words);
+    std::swap(ctx->brow, ctx->alt_brow);
+    std::swap(ctx->cols, ctx->alt_cols);
+    std::swap(ctx->colinfo, ctx->alt_colinfo);
+    std::swap(ctx->slow, ctx->alt_slow);
+    std::swap(ctx->sort_a, ctx->alt_sort_a);
+    std::swap(ctx->sort_b, ctx->alt_sort_b);
+    std::swap(ctx->sort_c, ctx->alt_sort_c);
 }
 
 hsq_seqs seqs_window(const hsq_seqs& s, int64_t a, int64_t n) {
@@ -202,8 +224,24 @@ hsq_seqs seqs_window(const hsq_seqs& s, int64_t a, int64_t n) {
     return w;
 }
 
-// hsq_extend_batch for a large batch: chunks flow through  H2D (s_in) | kernels (stream) | D2H (s_out)  with the two
-// buffer sets, so the copies of chunks c+1 and c-1 hide behind the kernels of chunk c.
+// Longest read of a window of a ragged batch and the probe-id range check, on the host (what extend_run otherwise gets
+// from the device at the price of a synchronisation).
+int host_chunk_dims(hsq_ctx* ctx, const hsq_pair_batch& w, int* read_max) {
+    int64_t mx = 0;
+    bool bad = false;
+    for (int64_t k = 0; k < w.n; k++) {
+        mx = std::max(mx, std::max(w.r1.offsets[k + 1] - w.r1.offsets[k], w.r2.offsets[k + 1] - w.r2.offsets[k]));
+        bad |= (w.probe_id[k] < 0) | (w.probe_id[k] >= ctx->n_probes);
+    }
+    if (bad) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_extend: probe_id out of range");
+    if (mx > INT32_MAX) return fail(ctx, HSQ_ERR_UNSUPPORTED, "hsq_extend: read too long");
+    *read_max = (int)mx;
+    return HSQ_OK;
+}
+
+// hsq_extend_batch for a large batch: chunks flow through  H2D (s_in) | kernels (s_comp[chunk & 1]) | D2H (s_out)  with
+// two complete buffer sets.  The host never blocks inside the loop; events order the streams.  Even and odd chunks run
+// their kernels on different streams, so the tail of one chunk's last kernel overlaps the first kernels of the next.
 int extend_pipelined(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o, int n_chunks) {
     const int64_t n = pb->n;
     const int64_t per = (n + n_chunks - 1) / n_chunks;
@@ -230,39 +268,52 @@ int extend_pipelined(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o, 
         if (w.pair_ok) w.pair_ok += a;
         return w;
     };
+    cudaStream_t main_stream = ctx->stream;
     ctx->keep_counters = false;
-    ctx->io = ctx->s_in;
-    hsq_pair_batch in0 = chunk_in(0);
-    rc = extend_stage(ctx, &in0);
-    if (!rc) HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_in[0], ctx->s_in));
+    if ((rc = reset_status(ctx))) return rc;
+    HSQ_CUDA(ctx, cudaStreamSynchronize(main_stream));  // counters are zero before any other stream touches them
+    int n_swaps = 0;
     for (int c = 0; c < n_chunks && !rc; c++) {
         const int slot = c & 1;
-        HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_in[slot], 0));
-        if (c >= 2) HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_out[slot], 0));  // this set's results have left
-        rc = extend_run(ctx, o->cigar_cap, o->md_cap);  // (synchronises once, after the encode kernels)
-        ctx->keep_counters = true;
+        hsq_pair_batch in = chunk_in(c);
+        int read_max = 0;
+        if ((rc = host_chunk_dims(ctx, in, &read_max))) break;
+        // H2D into this slot's inputs once the chunk that used them before (c-2) has run
+        if (c >= 2) HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_in, ctx->ev_comp[slot], 0));
+        ctx->io = ctx->s_in;
+        if ((rc = extend_stage(ctx, &in))) break;
+        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_in[slot], ctx->s_in));
+        // kernels on this slot's stream, after its inputs arrived and its previous results left
+        ctx->stream = ctx->s_comp[slot];
+        ctx->work_slot = slot;
+        cudaError_t e1 = cudaStreamWaitEvent(ctx->stream, ctx->ev_in[slot], 0);
+        cudaError_t e2 = c >= 2 ? cudaStreamWaitEvent(ctx->stream, ctx->ev_out[slot], 0) : cudaSuccess;
+        rc = extend_run(ctx, o->cigar_cap, o->md_cap, read_max);
+        cudaError_t e3 = cudaEventRecord(ctx->ev_comp[slot], ctx->stream);
+        ctx->stream = main_stream;
+        ctx->work_slot = 0;
         if (rc) break;
-        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_comp[slot], ctx->stream));
+        HSQ_CUDA(ctx, e1);
+        HSQ_CUDA(ctx, e2);
+        HSQ_CUDA(ctx, e3);
+        // D2H of this chunk's results
         HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_out, ctx->ev_comp[slot], 0));
         ctx->io = ctx->s_out;
         hsq_extend_out wo = chunk_out(c);
-        rc = extend_fetch_copies(ctx, &wo);
-        if (rc) break;
+        if ((rc = extend_fetch_copies(ctx, &wo))) break;
         HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_out[slot], ctx->s_out));
         swap_extend_buffers(ctx);
-        if (c + 1 < n_chunks) {  // the other set's inputs are free: chunk c-1's kernels finished before run(c) returned
-            ctx->io = ctx->s_in;
-            hsq_pair_batch in = chunk_in(c + 1);
-            rc = extend_stage(ctx, &in);
-            if (!rc) HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_in[slot ^ 1], ctx->s_in));
-        }
+        n_swaps++;
     }
-    ctx->io = ctx->s_out;
-    int rc2 = extend_fetch_finish(ctx, o);
+    // everything joins the main stream, which then reads the counters
+    for (int k = 0; k < 2; k++) {
+        cudaStreamSynchronize(ctx->s_comp[k]);
+    }
     cudaStreamSynchronize(ctx->s_in);
     cudaStreamSynchronize(ctx->s_out);
+    if (n_swaps & 1) swap_extend_buffers(ctx);  // leave the primary set in place
     ctx->io = nullptr;
-    ctx->keep_counters = false;
+    int rc2 = rc ? HSQ_OK : extend_fetch_finish(ctx, o);
     ctx->ext_n = -1;  // no single staged batch remains
     ctx->ext_ran = false;
     return rc ? rc : rc2;

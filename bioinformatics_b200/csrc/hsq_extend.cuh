@@ -208,6 +208,16 @@ __device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqV
 
 static constexpr uint32_t ORDER_HOLE = 0xFFFFFFFFu;  // padding entry of an odd-sized bucket
 
+// Dynamic work distribution of the packed kernels: a warp takes the next 32 pair slots from a device counter, so the
+// last wave of a launch is shared out instead of leaving the threads of a static stride idle (matters for the short
+// launches of the chunked host pipeline: ~3 slots per resident thread).
+__device__ __forceinline__ int64_t next_slot(unsigned long long* counter) {
+    unsigned long long base = 0;
+    if ((threadIdx.x & 31) == 0) base = atomicAdd(counter, 32ull);
+    base = __shfl_sync(0xffffffffu, base, 0);
+    return (int64_t)base + (threadIdx.x & 31);
+}
+
 // Stage 2: calculateDetailsForReadExtensionToPrimer (:200-245) for the read ends that reached DP#2, in bucket order.
 // 32-bit cells, one read end per thread: the general kernel (any integer scorer, any length).
 __global__ void __launch_bounds__(DP_BLOCK, 5) capture_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
@@ -259,12 +269,15 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes prob
                                                             DeviceSeqs r2, const uint32_t* __restrict__ order,
                                                             const uint32_t* __restrict__ n_active_ptr, ScoreParams2 sp_default,
                                                             ScratchPool2 pool, ExtendDeviceOut out, BucketKeys keys, int* status,
-                                                            unsigned long long* cells_total) {
+                                                            unsigned long long* cells_total, unsigned long long* work_counter) {
     __shared__ int4 prof[PROF2_INT4_PER_THREAD * DP2_BLOCK];
     DpScratch2 sc = thread_scratch2(pool, prof);
     int64_t cells = 0;
     const int64_t n_slots = (int64_t)*n_active_ptr >> 1;  // bucket sizes are even
-    for (int64_t t = sc.tid; t < n_slots; t += sc.nthreads) {
+    for (;;) {
+        const int64_t t = next_slot(work_counter);
+        if (t - (threadIdx.x & 31) >= n_slots) break;  // whole warp leaves together
+        if (t >= n_slots) continue;
         const uint2 mo = reinterpret_cast<const uint2*>(order)[t];
         const int n_here = (mo.y != ORDER_HOLE) ? 2 : 1;
         const int64_t mm[2] = {(int64_t)mo.x, (int64_t)(n_here == 2 ? mo.y : mo.x)};
@@ -297,12 +310,16 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes prob
 __global__ void __launch_bounds__(DP2_BLOCK, 5) capture2_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
                                                              DeviceSeqs r2, const uint32_t* __restrict__ order,
                                                              const uint32_t* __restrict__ n_active_ptr, ScoreParams2 sp_user,
-                                                             ScratchPool2 pool, ExtendDeviceOut out, unsigned long long* cells_total) {
+                                                             ScratchPool2 pool, ExtendDeviceOut out, unsigned long long* cells_total,
+                                                             unsigned long long* work_counter) {
     __shared__ int4 prof[PROF2_INT4_PER_THREAD * DP2_BLOCK];
     DpScratch2 sc = thread_scratch2(pool, prof);
     int64_t cells = 0;
     const int64_t n_slots = (int64_t)*n_active_ptr >> 1;  // bucket sizes are even
-    for (int64_t t = sc.tid; t < n_slots; t += sc.nthreads) {
+    for (;;) {
+        const int64_t t = next_slot(work_counter);
+        if (t - (threadIdx.x & 31) >= n_slots) break;  // whole warp leaves together
+        if (t >= n_slots) continue;
         const uint2 mo = reinterpret_cast<const uint2*>(order)[t];
         const int n_here = (mo.y != ORDER_HOLE) ? 2 : 1;
         const int64_t mm[2] = {(int64_t)mo.x, (int64_t)(n_here == 2 ? mo.y : mo.x)};

@@ -67,6 +67,9 @@ struct hsq_ctx {
     // second set of extend-batch buffers + copy streams: hsq_extend_batch pipelines chunks (H2D | kernels | D2H)
     hsq::DevSeqsOwned alt_r1, alt_r2;
     hsq::DevBuf alt_probe_id, alt_out_i32, alt_out_u8, alt_out_slots, alt_pair_ok;
+    hsq::DevBuf alt_ptr_words, alt_brow, alt_cols, alt_colinfo, alt_slow, alt_sort_a, alt_sort_b, alt_sort_c;
+    cudaStream_t s_comp[2] = {nullptr, nullptr};  // kernels of even / odd chunks (their tails overlap the next chunk's start)
+    int work_slot = 0;                            // which pair of work counters the packed kernels of this run use
     cudaStream_t io = nullptr;      // stream the host<->device copies of the current call go to (default: stream)
     cudaStream_t s_in = nullptr, s_out = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
