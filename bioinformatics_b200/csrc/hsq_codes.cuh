@@ -48,11 +48,15 @@ __host__ __device__ inline uint8_t decode_code(uint8_t c) {
     return (uint8_t)tbl[c & 15];
 }
 
-// getComplimentCode (:208-211): swap A<->T, C<->G on the set; U -> A; GAP -> GAP.
+// getComplimentCode (:208-211): swap A<->T, C<->G on the set (= reverse the nibble); U -> A; GAP -> GAP.
 __host__ __device__ inline uint8_t complement_code(uint8_t c) {
+#ifdef __CUDA_ARCH__
+    return (uint8_t)((__brev((uint32_t)c & 15u) >> 28) | (c & CODE_GAP));
+#else
     uint32_t m = c & 15u;
     uint32_t r = ((m & 1u) << 3) | ((m & 2u) << 1) | ((m & 4u) >> 1) | ((m & 8u) >> 3);
     return (uint8_t)(r | (c & CODE_GAP));
+#endif
 }
 
 // A strided, optionally complemented window on a device code array:

@@ -267,7 +267,15 @@ __device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView&
     uint2* win = reinterpret_cast<uint2*>(sc.prof + threadIdx.x);  // slot k at win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)]
     const int shift = 16 * which;
     const int64_t nt = sc.nthreads;
+    // running pointers at ref[j-1] / qry[i-1]: the codes this step may consume are fetched before the pointer is known
+    const uint8_t* rp = ref.base + ref.start + (int64_t)(j - 1) * ref.step;
+    const uint8_t* qp = qry.base + qry.start + (int64_t)(i - 1) * qry.step;
+    const int rstep = ref.step, qstep = qry.step;
+    const bool rcomp = ref.comp != 0, qcomp = qry.comp != 0;
     while (i > 0 || j > 0) {
+        uint32_t rraw = 0, qraw = 0;
+        if (j > 0) rraw = *rp;
+        if (i > 0) qraw = *qp;
         uint32_t p;
         if (i == 0) p = P_LEFT;
         else if (j == 0) p = P_UP;
@@ -289,8 +297,16 @@ __device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView&
             p = (((w.y >> bit) & 1u) << 1) | ((w.x >> bit) & 1u);
         }
         uint32_t rc = CODE_GAP, qc = CODE_GAP;
-        if (p != P_UP) { rc = ref.get(j - 1); j--; }
-        if (p != P_LEFT) { qc = qry.get(i - 1); i--; }
+        if (p != P_UP) {
+            rc = rcomp ? complement_code((uint8_t)rraw) : rraw;
+            rp -= rstep;
+            j--;
+        }
+        if (p != P_LEFT) {
+            qc = qcomp ? complement_code((uint8_t)qraw) : qraw;
+            qp -= qstep;
+            i--;
+        }
         sink.push(rc | (qc << 8));
     }
 }

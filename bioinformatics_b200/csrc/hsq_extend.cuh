@@ -187,8 +187,10 @@ __device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqV
     const int read_length = rw.len - 1;  // :225
     // score/alignmentLength > 0 (:212): the alignment has max(Q,R) >= 1 columns whenever score != 0
     if (score > 0 && read_length > LENGTH_THRESHOLD_FOR_EXTENDED_READ) {
+#ifndef HSQ_EXPERIMENT_NO_TRACEBACK  // (development experiment: upper bound of what the traceback costs)
         traceback(st);  // trailing query-gap columns are dropped by the sink (getAlignmentWithoutEndingQueryInserts :218)
         st.finish();    // :220-231
+#endif
         pos = v.is_reversed ? v.adjacent - st.ref_len : v.adjacent + 1;  // :234,:236
         read_start = start;
         read_stop = start + read_length;
@@ -280,13 +282,13 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes prob
         if (t >= n_slots) continue;
         const uint2 mo = reinterpret_cast<const uint2*>(order)[t];
         const int n_here = (mo.y != ORDER_HOLE) ? 2 : 1;
-        const int64_t mm[2] = {(int64_t)mo.x, (int64_t)(n_here == 2 ? mo.y : mo.x)};
-        ReadEndViews va = read_end_views(probes, probe_id, r1, r2, mm[0]);
-        ReadEndViews vb = read_end_views(probes, probe_id, r1, r2, mm[1]);
+        const int64_t ma = (int64_t)mo.x, mb = (int64_t)(n_here == 2 ? mo.y : mo.x);
+        ReadEndViews va = read_end_views(probes, probe_id, r1, r2, ma);
+        ReadEndViews vb = read_end_views(probes, probe_id, r1, r2, mb);
         if (va.primer.len == 0) {  // Java: IndexOutOfBounds at :299 (all-gap primer alignment); both have the same shape
             atomicMin(status, HSQ_ERR_OUT_OF_RANGE);
-            primer_finish(va, HSQ_PRIMER_NOT_FOUND, out, keys, mm[0]);
-            if (n_here == 2) primer_finish(vb, HSQ_PRIMER_NOT_FOUND, out, keys, mm[1]);
+            primer_finish(va, HSQ_PRIMER_NOT_FOUND, out, keys, ma);
+            if (n_here == 2) primer_finish(vb, HSQ_PRIMER_NOT_FOUND, out, keys, mb);
             continue;
         }
         SeqView pa = primer_prefix(va.primer, va.read), pb = primer_prefix(vb.primer, vb.read);
@@ -299,7 +301,7 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes prob
             const SeqView& px = which ? pb : pa;
             PrimerGateSink gate;
             dp_traceback2(px, v.primer, sc, which, gate);
-            primer_finish(v, gate.result(), out, keys, mm[which]);
+            primer_finish(v, gate.result(), out, keys, which ? mb : ma);
         }
     }
     for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
@@ -322,21 +324,22 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) capture2_kernel(DeviceProbes pro
         if (t >= n_slots) continue;
         const uint2 mo = reinterpret_cast<const uint2*>(order)[t];
         const int n_here = (mo.y != ORDER_HOLE) ? 2 : 1;
-        const int64_t mm[2] = {(int64_t)mo.x, (int64_t)(n_here == 2 ? mo.y : mo.x)};
-        ReadEndViews va = read_end_views(probes, probe_id, r1, r2, mm[0]);
-        ReadEndViews vb = read_end_views(probes, probe_id, r1, r2, mm[1]);
-        const int start_a = out.primer_end[mm[0]] + 1, start_b = out.primer_end[mm[1]] + 1;
+        const int64_t ma = (int64_t)mo.x, mb = (int64_t)(n_here == 2 ? mo.y : mo.x);
+        ReadEndViews va = read_end_views(probes, probe_id, r1, r2, ma);
+        ReadEndViews vb = read_end_views(probes, probe_id, r1, r2, mb);
+        const int start_a = out.primer_end[ma] + 1, start_b = out.primer_end[mb] + 1;
         SeqView rwa = sub_view(va.read, start_a, va.read.len - start_a);  // read[e+1 .. L-1] (:210)
         SeqView rwb = sub_view(vb.read, start_b, vb.read.len - start_b);
         int score[2];
         dp_fill2(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score);  // :211
+        const int score_a = score[0], score_b = score[1];
         cells += (int64_t)va.capture.len * rwa.len * n_here;
 #pragma unroll 1
         for (int which = 0; which < n_here; which++) {
             const ReadEndViews& v = which ? vb : va;
             const SeqView& rw = which ? rwb : rwa;
-            capture_finish(v, rw, which ? start_b : start_a, score[which],
-                           [&](CigarMdStream& st) { dp_traceback2(v.capture, rw, sc, which, st); }, out, mm[which]);
+            capture_finish(v, rw, which ? start_b : start_a, which ? score_b : score_a,
+                           [&](CigarMdStream& st) { dp_traceback2(v.capture, rw, sc, which, st); }, out, which ? mb : ma);
         }
     }
     for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
