@@ -297,8 +297,8 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes prob
         cells += (int64_t)pa.len * va.primer.len * n_here;
 #pragma unroll 1
         for (int which = 0; which < n_here; which++) {
-            const ReadEndViews& v = which ? vb : va;
-            const SeqView& px = which ? pb : pa;
+            const ReadEndViews v = which ? vb : va;  // by value: selected once, not at every use inside the column loop
+            const SeqView px = which ? pb : pa;
             PrimerGateSink gate;
             dp_traceback2(px, v.primer, sc, which, gate);
             primer_finish(v, gate.result(), out, keys, which ? mb : ma);
@@ -336,8 +336,8 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) capture2_kernel(DeviceProbes pro
         cells += (int64_t)va.capture.len * rwa.len * n_here;
 #pragma unroll 1
         for (int which = 0; which < n_here; which++) {
-            const ReadEndViews& v = which ? vb : va;
-            const SeqView& rw = which ? rwb : rwa;
+            const ReadEndViews v = which ? vb : va;  // by value: selected once, not at every use inside the column loop
+            const SeqView rw = which ? rwb : rwa;
             capture_finish(v, rw, which ? start_b : start_a, which ? score_b : score_a,
                            [&](CigarMdStream& st) { dp_traceback2(v.capture, rw, sc, which, st); }, out, which ? mb : ma);
         }
