@@ -62,6 +62,11 @@ class ProbeStats(C.Structure):
     _fields_ = [("n_probes", C.c_int64), ("unique_pairs", i32p), ("duplicate_pairs", i32p), ("max_pairs_per_uid", i32p)]
 
 
+class MergeBatch(C.Structure):
+    _fields_ = [("n", C.c_int64), ("negative_strand", u8p), ("up", Seqs), ("down", Seqs), ("up_qual", u8p), ("down_qual", u8p),
+                ("up_start", i32p), ("down_start", i32p)]
+
+
 class Candidates(C.Structure):
     _fields_ = [("n", C.c_int64), ("r1", Seqs), ("r2", Seqs), ("cand_offsets", i64p), ("cand_probe", i32p)]
 

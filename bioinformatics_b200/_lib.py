@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 from . import _abi as A
-from .batches import AlignResult, ExtendResult, PairBatchHost, ProbeStatsHost, ProbeTableHost, scorer
+from .batches import AlignResult, ExtendResult, PairBatchHost, ProbeStatsHost, ProbeTableHost, merge_args, scorer
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_PKG, "libhsq_b200.so")
@@ -18,7 +18,7 @@ _lib = None
 EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version", "hsq_pinned_alloc", "hsq_pinned_free",
            "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
-           "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys")
+           "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs")
 
 
 class HsqError(RuntimeError):
@@ -145,6 +145,24 @@ class Context:
         self._check(self.lib.hsq_dedup_batch(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
                                              A.ptr(is_best, A.u8p), A.ptr(group_size, A.i32p), C.byref(sc)))
         return is_best, group_size, stats
+
+    def merge_pairs(self, negative, up, down, upq, downq, up_start, down_start, out_cap=None):
+        """hsq_merge_pairs: returns (merged sequences, merged qualities) as SeqBatch; sizes itself with a second call."""
+        mb, keep = merge_args(negative, up, down, upq, downq, up_start, down_start)
+        n = mb.n
+        cap = out_cap if out_cap is not None else int(len(keep[0].data) + len(keep[1].data)) + 16
+        off = np.zeros(n + 1, dtype=np.int64)
+        for _ in range(2):
+            seq = np.zeros(max(1, cap), dtype=np.uint8)
+            qual = np.zeros(max(1, cap), dtype=np.uint8)
+            st = self.lib.hsq_merge_pairs(self.h, C.byref(mb), A.ptr(seq, A.u8p), A.ptr(qual, A.u8p), A.ptr(off, A.i64p), C.c_int64(cap))
+            if st == A.HSQ_ERR_OVERFLOW and out_cap is None:
+                cap = int(off[-1])
+                continue
+            break
+        self._check(st)
+        total = int(off[-1])
+        return A.SeqBatch(seq[:total], off), A.SeqBatch(qual[:total], off.copy())
 
     def dedup_keys(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, n_probes, origin_base, d_keys_ptr):
         """hsq_dedup_keys: key records of this rank's pairs into DEVICE memory at d_keys_ptr (24 B per pair)."""

@@ -170,6 +170,20 @@ class ProbeStatsHost:
                             A.ptr(self.max_pairs_per_uid, A.i32p))
 
 
+def merge_args(negative, up, down, upq, downq, up_start, down_start):
+    up = up if isinstance(up, A.SeqBatch) else A.SeqBatch.from_strings(up)
+    down = down if isinstance(down, A.SeqBatch) else A.SeqBatch.from_strings(down)
+    upq = upq if isinstance(upq, A.SeqBatch) else A.SeqBatch.from_strings(upq)
+    downq = downq if isinstance(downq, A.SeqBatch) else A.SeqBatch.from_strings(downq)
+    assert (upq.offsets == up.offsets).all() and (downq.offsets == down.offsets).all(), "qualities must match the sequences' lengths"
+    neg = np.ascontiguousarray(negative, dtype=np.uint8)
+    us = np.ascontiguousarray(up_start, dtype=np.int32)
+    ds = np.ascontiguousarray(down_start, dtype=np.int32)
+    mb = A.MergeBatch(up.n, A.ptr(neg, A.u8p), up.c(), down.c(), A.ptr(upq.data, A.u8p), A.ptr(downq.data, A.u8p), A.ptr(us, A.i32p),
+                      A.ptr(ds, A.i32p))
+    return mb, (up, down, upq, downq, neg, us, ds)
+
+
 def scorer(match=1, mismatch=-4, gap_extend=-1, gap_start=-6):
     """SimpleAlignmentScorer defaults (COMMON/alignment/SimpleAlignmentScorer.java:23-26)."""
     return A.Scorer(match, mismatch, gap_extend, gap_start)

@@ -219,5 +219,6 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_extend.inl"
 #include "hsq_capi_trim.inl"
 #include "hsq_capi_dedup.inl"
+#include "hsq_capi_merge.inl"
 #include "hsq_capi_resolve.inl"
 #include "hsq_capi_peak.inl"

@@ -154,6 +154,18 @@ typedef struct hsq_dedup_key {
     uint32_t origin;
 } hsq_dedup_key; /* 24 bytes */
 
+/* One mergeSequences call per item (HSQ/process/PrimerReadExtensionAndPcrDuplicateIdentification.java:1362-1552): the
+ * upstream and downstream mate of a pair on the genome's forward strand with their 1-based alignment starts. */
+typedef struct hsq_merge_batch {
+    int64_t n;
+    const uint8_t* negative_strand; /* 1: the merged read is reverse-complemented, its qualities reversed (:1544-1548) */
+    hsq_seqs up, down;              /* upstream / downstream sequences */
+    const uint8_t* up_qual;         /* laid out by up.offsets */
+    const uint8_t* down_qual;       /* laid out by down.offsets */
+    const int32_t* up_start;        /* upstreamAlignmentStart (>= 1) */
+    const int32_t* down_start;      /* downstreamAlignmentStart (>= up_start when the two overlap) */
+} hsq_merge_batch;
+
 /* ---- context ------------------------------------------------------------------------------ */
 int32_t hsq_ctx_create(int32_t device, hsq_ctx** out);
 void hsq_ctx_destroy(hsq_ctx* ctx);
@@ -195,6 +207,13 @@ int32_t hsq_extend_fetch(hsq_ctx* ctx, hsq_extend_out* out);
 int32_t hsq_resolve_multi_probe(hsq_ctx* ctx, const hsq_candidates* cands, int32_t ext_uid_len, int32_t lig_uid_len,
                                 int32_t* best_probe, int32_t* cand_matches, int32_t* cand_edit);
 
+
+/* mergeSequences per item (…Identification.java:1362-1552, behind the unregistered --mergePairs option): lead + overlap
+ * (per position the base with the higher quality wins, ties to upstream; a gap is filled with N / '!') + trail.
+ * out_offsets gets n+1 entries; out_seq/out_qual have out_cap bytes: when the merged total is larger the call returns
+ * HSQ_ERR_OVERFLOW with out_offsets filled, so the caller can size the buffers and call again. */
+int32_t hsq_merge_pairs(hsq_ctx* ctx, const hsq_merge_batch* pairs, uint8_t* out_seq, uint8_t* out_qual, int64_t* out_offsets,
+                        int64_t out_cap);
 
 /* ---- sharded dedup: one process per GPU, exchange by the caller ------------------------------------------------------ */
 /* First half of FilterByUid.reduceReadsByProbeAndUid for this rank's pairs (host buffers in): writes pairs->n key

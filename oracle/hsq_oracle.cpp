@@ -124,6 +124,37 @@ int32_t hsqo_trim_batch(const hsq_seqs* reads, const uint8_t* quals, int32_t fir
     return HSQ_OK;
 }
 
+// mergeSequences per item; out_offsets always filled; HSQ_ERR_OVERFLOW when the total exceeds out_cap
+int32_t hsqo_merge_pairs(const hsq_merge_batch* mb, uint8_t* out_seq, uint8_t* out_qual, int64_t* out_offsets, int64_t out_cap) {
+    try {
+        int64_t pos = 0;
+        out_offsets[0] = 0;
+        bool overflow = false;
+        for (int64_t k = 0; k < mb->n; k++) {
+            std::string ms, mq;
+            merge_sequences(mb->negative_strand[k] != 0, get_str(mb->up.data, mb->up.offsets, k), get_str(mb->down.data, mb->down.offsets, k),
+                            get_str(mb->up_qual, mb->up.offsets, k), get_str(mb->down_qual, mb->down.offsets, k), mb->up_start[k],
+                            mb->down_start[k], &ms, &mq);
+            if (pos + (int64_t)ms.size() <= out_cap) {
+                memcpy(out_seq + pos, ms.data(), ms.size());
+                memcpy(out_qual + pos, mq.data(), mq.size());
+            } else {
+                overflow = true;
+            }
+            pos += (int64_t)ms.size();
+            out_offsets[k + 1] = pos;
+        }
+        if (overflow) return HSQ_ERR_OVERFLOW;
+    } catch (const std::invalid_argument& ex) {
+        g_err = ex.what();
+        return HSQ_ERR_BAD_CHARACTER;
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+        return HSQ_ERR_OUT_OF_RANGE;
+    }
+    return HSQ_OK;
+}
+
 // FilterByUid.reduceReadsByProbeAndUid over all probes (HSQ/process/FilterByUid.java:134-203) + findBestData (:281-297)
 int32_t hsqo_dedup_batch(const hsq_pair_batch* pb, int32_t u, int32_t v, uint8_t* is_best, int32_t* group_size,
                          hsq_probe_stats* stats) {

@@ -197,4 +197,74 @@ inline void tie_break_metrics(const Probe& p, const seq_t& r1, const seq_t& r2, 
     *matches = a1.pair.number_of_matches() + a2.pair.number_of_matches();
 }
 
+// mergeSequences (HSQ/process/PrimerReadExtensionAndPcrDuplicateIdentification.java:1362-1552).  Sequences are ASCII; every
+// output base is the canonical letter of its code (IupacNucleotideCode.toString), as the Java builds the result from codes.
+// Throws std::out_of_range where the Java throws (substring / subSequence bounds).
+inline void merge_sequences(bool negative_strand, const std::string& up, const std::string& down, const std::string& upq,
+                            const std::string& downq, int up_start, int down_start, std::string* out_seq, std::string* out_qual) {
+    if (upq.size() != up.size() || downq.size() != down.size()) throw std::out_of_range("quality length differs from sequence length");
+    const int ul = (int)up.size(), dl = (int)down.size();
+    const int up_end = up_start + ul - 1, down_end = down_start + dl - 1;  // :1371-1374
+    int lead_s = 0, lead_e = 0, lead_len = 0, ov_s = 0, ov_e = 0, ov_len = 0, tr_s = 0, tr_e = 0, tr_len = 0;
+    const int min_end = std::min(up_end, down_end), max_end = std::max(up_end, down_end);  // :1388-1389
+    const bool trail_from_down = (down_end == max_end);                                    // :1394-1402
+    const std::string& tsrc = trail_from_down ? down : up;
+    const std::string& tsrcq = trail_from_down ? downq : upq;
+    const int tsrc_start = trail_from_down ? down_start : up_start;
+    if (down_start <= up_end) {  // :1405-1421
+        ov_s = down_start;
+        ov_e = min_end;
+        ov_len = ov_e - ov_s + 1;
+        if (up_start < ov_s) { lead_s = up_start; lead_e = ov_s - 1; lead_len = lead_e - lead_s + 1; }
+        if (max_end > ov_e) { tr_s = ov_e + 1; tr_e = max_end; tr_len = tr_e - tr_s + 1; }
+    } else {  // :1422-1430
+        lead_s = up_start; lead_e = lead_s + ul - 1; lead_len = lead_e - lead_s + 1;
+        tr_s = down_start; tr_e = tr_s + dl - 1; tr_len = tr_e - tr_s + 1;
+    }
+    auto canon = [](const std::string& x) {
+        std::string r(x.size(), '?');
+        for (size_t k = 0; k < x.size(); k++) {
+            int c = encode_char(x[k]);
+            if (c < 0) throw std::invalid_argument("not an IUPAC code");
+            r[k] = decode_code((code_t)c);
+        }
+        return r;
+    };
+    auto sub = [](const std::string& x, int a, int b_incl) {  // String.substring(a, b+1) / subSequence(a, b) bounds
+        if (a < 0 || b_incl + 1 > (int)x.size() || a > b_incl + 1) throw std::out_of_range("substring out of bounds");
+        return x.substr((size_t)a, (size_t)(b_incl + 1 - a));
+    };
+    std::string lead, leadq, ov, ovq, trail, trailq;
+    if (ov_len == 0) {  // :1449-1468
+        const int gs = lead_e + 1, ge = tr_s - 1;
+        const int fill = ge >= gs ? ge - gs + 1 : 0;
+        if (fill > 0) { ov.assign((size_t)fill, 'N'); ovq.assign((size_t)fill, '!'); ov_len = fill; }
+        lead = canon(up); leadq = upq; trail = canon(down); trailq = downq;
+    } else if (ov_len >= 1) {  // :1469-1521
+        if (lead_len >= 1) { lead = canon(sub(up, lead_s - up_start, lead_e - up_start)); leadq = sub(upq, lead_s - up_start, lead_e - up_start); }
+        const std::string uo = canon(sub(up, ov_s - up_start, ov_e - up_start)), uoq = sub(upq, ov_s - up_start, ov_e - up_start);
+        const std::string dox = canon(sub(down, ov_s - down_start, ov_e - down_start)), doq = sub(downq, ov_s - down_start, ov_e - down_start);
+        for (int i = 0; i < ov_len; i++) {
+            if (i + 1 > (int)downq.size()) throw std::out_of_range("substring out of bounds");
+            const int uqs = (int)(unsigned char)uoq[(size_t)i] - 33;
+            const int dqs = (int)(unsigned char)downq[(size_t)i] - 33;  // :1506 indexes the un-sliced downstream quality
+            if (uqs >= dqs) { ov += uo[(size_t)i]; ovq += uoq[(size_t)i]; }
+            else { ov += dox[(size_t)i]; ovq += doq[(size_t)i]; }
+        }
+        if (tr_len >= 1) { trail = canon(sub(tsrc, tr_s - tsrc_start, tr_e - tsrc_start)); trailq = sub(tsrcq, tr_s - tsrc_start, tr_e - tsrc_start); }
+    } else {
+        throw std::out_of_range("negative overlap");
+    }
+    std::string ms = (lead_len > 0 ? lead : "") + (ov_len > 0 ? ov : "") + (tr_len > 0 ? trail : "");      // :1530-1542
+    std::string mq = (lead_len > 0 ? leadq : "") + (ov_len > 0 ? ovq : "") + (tr_len > 0 ? trailq : "");
+    if (negative_strand) {  // :1544-1548
+        std::string rc(ms.rbegin(), ms.rend());
+        for (auto& ch : rc) ch = decode_code(complement_code((code_t)encode_char(ch)));
+        ms = rc;
+        mq = std::string(mq.rbegin(), mq.rend());
+    }
+    *out_seq = ms;
+    *out_qual = mq;
+}
+
 }  // namespace hsqo

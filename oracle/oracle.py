@@ -11,7 +11,7 @@ import numpy as np
 
 from bioinformatics_b200 import _abi as A
 from bioinformatics_b200.batches import (AlignResult, ExtendResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
-                                         scorer)
+                                         merge_args, scorer)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, "libhsq_oracle.so")
@@ -36,7 +36,7 @@ def lib():
         _lib.hsqo_last_error.restype = C.c_char_p
         for name in ("hsqo_align_batch", "hsqo_trim_batch", "hsqo_dedup_batch", "hsqo_extend_batch",
                      "hsqo_resolve_multi_probe", "hsqo_primer_end", "hsqo_index_of_first_match_in_reference",
-                     "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar"):
+                     "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs"):
             getattr(_lib, name).restype = C.c_int32
     return _lib
 
@@ -75,6 +75,23 @@ def trim_batch(reads, quals, first, last, three_prime=True):
                                  A.ptr(out_off, A.i64p)))
     total = int(out_off[-1])
     return A.SeqBatch(out_seq[:total], out_off), A.SeqBatch(out_qual[:total], out_off)
+
+
+def merge_pairs(negative, up, down, upq, downq, up_start, down_start):
+    mb, keep = merge_args(negative, up, down, upq, downq, up_start, down_start)
+    off = np.zeros(mb.n + 1, dtype=np.int64)
+    cap = 16
+    for _ in range(2):
+        seq = np.zeros(max(1, cap), dtype=np.uint8)
+        qual = np.zeros(max(1, cap), dtype=np.uint8)
+        st = lib().hsqo_merge_pairs(C.byref(mb), A.ptr(seq, A.u8p), A.ptr(qual, A.u8p), A.ptr(off, A.i64p), C.c_int64(cap))
+        if st == A.HSQ_ERR_OVERFLOW:
+            cap = int(off[-1])
+            continue
+        break
+    _check(st)
+    total = int(off[-1])
+    return A.SeqBatch(seq[:total], off), A.SeqBatch(qual[:total], off.copy())
 
 
 def dedup_batch(pairs, ext_uid_len, lig_uid_len, n_probes):
