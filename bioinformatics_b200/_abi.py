@@ -67,6 +67,24 @@ class MergeBatch(C.Structure):
                 ("up_start", i32p), ("down_start", i32p)]
 
 
+class ProbeRanges(C.Structure):
+    _fields_ = [("n", C.c_int64), ("contig", i32p), ("reverse_strand", u8p), ("start", i32p), ("stop", i32p)]
+
+
+class MappedRecords(C.Structure):
+    _fields_ = [("n", C.c_int64), ("contig", i32p), ("negative_strand", u8p), ("second_of_pair", u8p), ("start", i32p), ("end", i32p),
+                ("read_index", i32p), ("alt_offsets", i64p), ("alt_contig", i32p), ("alt_negative", u8p), ("alt_start", i32p),
+                ("alt_stop", i32p)]
+
+
+class AssignOut(C.Structure):
+    _fields_ = [("max_probes", C.c_int32), ("n_probes", i32p), ("probes", i32p), ("mate", i32p), ("n_common", i32p), ("common", i32p),
+                ("overflow", u8p)]
+
+
+ASSIGN_UNPAIRED, ASSIGN_AMBIGUOUS_NAME, ASSIGN_IGNORED = -1, -2, -3
+
+
 class Candidates(C.Structure):
     _fields_ = [("n", C.c_int64), ("r1", Seqs), ("r2", Seqs), ("cand_offsets", i64p), ("cand_probe", i32p)]
 

@@ -9,7 +9,8 @@ import os
 import numpy as np
 
 from . import _abi as A
-from .batches import AlignResult, ExtendResult, PairBatchHost, ProbeStatsHost, ProbeTableHost, merge_args, scorer
+from .batches import (AlignResult, AssignResult, ExtendResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
+                      ProbeTableHost, merge_args, scorer)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_PKG, "libhsq_b200.so")
@@ -18,7 +19,8 @@ _lib = None
 EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version", "hsq_pinned_alloc", "hsq_pinned_free",
            "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
-           "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs")
+           "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
+           "hsq_set_probe_ranges", "hsq_assign_probes")
 
 
 class HsqError(RuntimeError):
@@ -163,6 +165,18 @@ class Context:
         self._check(st)
         total = int(off[-1])
         return A.SeqBatch(seq[:total], off), A.SeqBatch(qual[:total], off.copy())
+
+    def set_probe_ranges(self, ranges: ProbeRangesHost):
+        """hsq_set_probe_ranges: the per (contig, strand) RangeMaps, device resident."""
+        rc = ranges.c()
+        self._check(self.lib.hsq_set_probe_ranges(self.h, C.byref(rc)))
+
+    def assign_probes(self, records: MappedRecordsHost, max_probes=4):
+        """hsq_assign_probes: ReadToProbeAssigner.assignProbesToReads for a batch of mapped records."""
+        out = AssignResult(records.n, max_probes)
+        rc, oc = records.c(), out.c()
+        self._check(self.lib.hsq_assign_probes(self.h, C.byref(rc), C.byref(oc)))
+        return out
 
     def dedup_keys(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, n_probes, origin_base, d_keys_ptr):
         """hsq_dedup_keys: key records of this rank's pairs into DEVICE memory at d_keys_ptr (24 B per pair)."""

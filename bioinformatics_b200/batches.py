@@ -184,6 +184,75 @@ def merge_args(negative, up, down, upq, downq, up_start, down_start):
     return mb, (up, down, upq, downq, neg, us, ds)
 
 
+class ProbeRangesHost:
+    """hsq_probe_ranges: search window, contig and strand of every probe (…Identification.java:285-331)."""
+
+    def __init__(self, contig, reverse_strand, start, stop):
+        self.contig = np.ascontiguousarray(contig, dtype=np.int32)
+        self.reverse_strand = np.ascontiguousarray(reverse_strand, dtype=np.uint8)
+        self.start = np.ascontiguousarray(start, dtype=np.int32)
+        self.stop = np.ascontiguousarray(stop, dtype=np.int32)
+        self.n = len(self.contig)
+        assert len(self.reverse_strand) == len(self.start) == len(self.stop) == self.n
+
+    def c(self):
+        return A.ProbeRanges(self.n, A.ptr(self.contig, A.i32p), A.ptr(self.reverse_strand, A.u8p), A.ptr(self.start, A.i32p),
+                             A.ptr(self.stop, A.i32p))
+
+
+class MappedRecordsHost:
+    """hsq_mapped_records: the fields ReadToProbeAssigner.assignProbesToReads reads off a SAMRecord (…Identification.java:439-576).
+
+    alt = None or (alt_offsets[n+1], alt_contig, alt_negative, alt_start, alt_stop)."""
+
+    def __init__(self, contig, negative_strand, second_of_pair, start, end, read_index, alt=None):
+        self.contig = np.ascontiguousarray(contig, dtype=np.int32)
+        self.negative_strand = np.ascontiguousarray(negative_strand, dtype=np.uint8)
+        self.second_of_pair = np.ascontiguousarray(second_of_pair, dtype=np.uint8)
+        self.start = np.ascontiguousarray(start, dtype=np.int32)
+        self.end = np.ascontiguousarray(end, dtype=np.int32)
+        self.read_index = np.ascontiguousarray(read_index, dtype=np.int32)
+        self.n = len(self.contig)
+        if alt is None:
+            self.alt_offsets = self.alt_contig = self.alt_negative = self.alt_start = self.alt_stop = None
+        else:
+            self.alt_offsets = np.ascontiguousarray(alt[0], dtype=np.int64)
+            self.alt_contig = np.ascontiguousarray(alt[1], dtype=np.int32)
+            self.alt_negative = np.ascontiguousarray(alt[2], dtype=np.uint8)
+            self.alt_start = np.ascontiguousarray(alt[3], dtype=np.int32)
+            self.alt_stop = np.ascontiguousarray(alt[4], dtype=np.int32)
+            assert len(self.alt_offsets) == self.n + 1
+
+    def c(self):
+        return A.MappedRecords(self.n, A.ptr(self.contig, A.i32p), A.ptr(self.negative_strand, A.u8p), A.ptr(self.second_of_pair, A.u8p),
+                               A.ptr(self.start, A.i32p), A.ptr(self.end, A.i32p), A.ptr(self.read_index, A.i32p),
+                               A.ptr(self.alt_offsets, A.i64p), A.ptr(self.alt_contig, A.i32p), A.ptr(self.alt_negative, A.u8p),
+                               A.ptr(self.alt_start, A.i32p), A.ptr(self.alt_stop, A.i32p))
+
+
+class AssignResult:
+    """hsq_assign_out with host arrays."""
+
+    def __init__(self, n, max_probes=4):
+        self.n, self.max_probes = n, max_probes
+        self.n_probes = np.zeros(n, dtype=np.int32)
+        self.probes = np.full((n, max_probes), -1, dtype=np.int32)
+        self.mate = np.zeros(n, dtype=np.int32)
+        self.n_common = np.zeros(n, dtype=np.int32)
+        self.common = np.full((n, max_probes), -1, dtype=np.int32)
+        self.overflow = np.zeros(n, dtype=np.uint8)
+
+    def c(self):
+        return A.AssignOut(self.max_probes, A.ptr(self.n_probes, A.i32p), A.ptr(self.probes, A.i32p), A.ptr(self.mate, A.i32p),
+                           A.ptr(self.n_common, A.i32p), A.ptr(self.common, A.i32p), A.ptr(self.overflow, A.u8p))
+
+    def probe_sets(self):
+        return [tuple(self.probes[k, :self.n_probes[k]]) for k in range(self.n)]
+
+    def common_sets(self):
+        return [tuple(self.common[k, :self.n_common[k]]) for k in range(self.n)]
+
+
 def scorer(match=1, mismatch=-4, gap_extend=-1, gap_start=-6):
     """SimpleAlignmentScorer defaults (COMMON/alignment/SimpleAlignmentScorer.java:23-26)."""
     return A.Scorer(match, mismatch, gap_extend, gap_start)

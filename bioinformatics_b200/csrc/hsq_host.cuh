@@ -64,6 +64,10 @@ struct hsq_ctx {
     hsq::DevBuf ptr_words, brow, cols, status, cells, misc, out_i32, out_u8, out_slots, pair_ok;
     hsq::DevBuf sort_a, sort_b, sort_c, sort_d, sort_tmp, flags, slow, colinfo;
     bool force_dp32 = false;
+    // probe search windows sorted by (contig, strand, start) for hsq_assign_probes
+    hsq::DevBuf rg_start, rg_end, rg_value, rg_off;
+    int64_t rg_n = -1;
+    int32_t rg_contigs = 0;
     // second set of extend-batch buffers + copy streams: hsq_extend_batch pipelines chunks (H2D | kernels | D2H)
     hsq::DevSeqsOwned alt_r1, alt_r2;
     hsq::DevBuf alt_probe_id, alt_out_i32, alt_out_u8, alt_out_slots, alt_pair_ok;

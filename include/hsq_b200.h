@@ -166,6 +166,52 @@ typedef struct hsq_merge_batch {
     const int32_t* down_start;      /* downstreamAlignmentStart (>= up_start when the two overlap) */
 } hsq_merge_batch;
 
+/* ---- coordinate read -> probe assignment ---------------------------------------------------- */
+/* Search window of every probe, in probe-info-file order: what getProbeSearchBoundaries returns
+ * (…Identification.java:285-297) and the contig / strand the probe sits on.  One RangeMap per (contig, strand)
+ * (HSQ/process/RangeMap.java; built at …Identification.java:313-331). */
+typedef struct hsq_probe_ranges {
+    int64_t n;
+    const int32_t* contig;         /* contig id of the probe (caller's numbering, >= 0) */
+    const uint8_t* reverse_strand; /* 1 when probe_strand is '-' */
+    const int32_t* start;          /* queryStart */
+    const int32_t* stop;           /* queryStop */
+} hsq_probe_ranges;
+
+/* Mapped records as ReadToProbeAssigner.assignProbesToReads sees them (…Identification.java:439-545): both mates mapped
+ * (the caller drops records with the unmapped / mate-unmapped flag, :446), read name = FASTQ ordinal. */
+typedef struct hsq_mapped_records {
+    int64_t n;
+    const int32_t* contig;          /* contig id; -1 = a contig without any probe (probeRanges == null, :462): record ignored */
+    const uint8_t* negative_strand; /* getReadNegativeStrandFlag */
+    const uint8_t* second_of_pair;  /* getSecondOfPairFlag (the strand is flipped for read two, :453-455) */
+    const int32_t* start;           /* getAlignmentStart */
+    const int32_t* end;             /* getAlignmentEnd */
+    const int32_t* read_index;      /* Integer.parseInt(readName) */
+    /* alternative hits of record k (XA tag, SAMRecordUtil.getAlternativeHitsFromAttribute): alt_offsets[k] .. alt_offsets[k+1];
+     * alt_offsets may be NULL when no record has any */
+    const int64_t* alt_offsets;
+    const int32_t* alt_contig;      /* -1 = contig without probes */
+    const uint8_t* alt_negative;    /* alternativeHit.getStrand() == REVERSE */
+    const int32_t* alt_start;
+    const int32_t* alt_stop;
+} hsq_mapped_records;
+
+/* Per record results; slot arrays have max_probes entries per record. */
+typedef struct hsq_assign_out {
+    int32_t max_probes;    /* in: slots per record */
+    int32_t* n_probes;     /* probes whose window contains the record or one of its alternative hits (<= max_probes) */
+    int32_t* probes;       /* [n][max_probes] those probes (rows of hsq_probe_ranges), ascending */
+    int32_t* mate;         /* record index of the mate; HSQ_ASSIGN_UNPAIRED / _AMBIGUOUS_NAME / _IGNORED */
+    int32_t* n_common;     /* probes assigned to the PAIR = intersection of the two mates' sets (:478-483); 0 unless paired */
+    int32_t* common;       /* [n][max_probes] ascending; identical for both mates */
+    uint8_t* overflow;     /* 1: a set of this record or of its mate did not fit max_probes: its slots are incomplete, call
+                            * again with more slots */
+} hsq_assign_out;
+#define HSQ_ASSIGN_UNPAIRED (-1)
+#define HSQ_ASSIGN_AMBIGUOUS_NAME (-2) /* the read name occurs on four or more usable records */
+#define HSQ_ASSIGN_IGNORED (-3)        /* the record's contig holds no probe */
+
 /* ---- context ------------------------------------------------------------------------------ */
 int32_t hsq_ctx_create(int32_t device, hsq_ctx** out);
 void hsq_ctx_destroy(hsq_ctx* ctx);
@@ -214,6 +260,18 @@ int32_t hsq_resolve_multi_probe(hsq_ctx* ctx, const hsq_candidates* cands, int32
  * HSQ_ERR_OVERFLOW with out_offsets filled, so the caller can size the buffers and call again. */
 int32_t hsq_merge_pairs(hsq_ctx* ctx, const hsq_merge_batch* pairs, uint8_t* out_seq, uint8_t* out_qual, int64_t* out_offsets,
                         int64_t out_cap);
+
+/* Builds the per (contig, strand) range maps on the device: probes ordered by window start with a stable sort, as
+ * RangeMap.getObjectsThatContainRangeInclusive does on first use (RangeMap.java:98-101). */
+int32_t hsq_set_probe_ranges(hsq_ctx* ctx, const hsq_probe_ranges* ranges);
+/* ReadToProbeAssigner.assignProbesToReads for a batch of records (…Identification.java:439-545) with
+ * RangeMap.getObjectsThatContainRangeInclusive (RangeMap.java:92-153: binary search on the window start, then the leftward
+ * walk that stops at the first window ending before the query -- the "no probe contains another" assumption is kept, as
+ * are the search's landing rules among equal starts).  Records are paired by read name in input order, i.e. the
+ * reference's outcome when one thread feeds the assigner (:470-540): the first two usable records of a name form the pair
+ * (probe set = intersection of the mates' sets, :478-483), a third stays unpaired, and a name seen on four or more records
+ * completes a second pair and is removed from the results altogether (:484-486, :392-400). */
+int32_t hsq_assign_probes(hsq_ctx* ctx, const hsq_mapped_records* records, hsq_assign_out* out);
 
 /* ---- sharded dedup: one process per GPU, exchange by the caller ------------------------------------------------------ */
 /* First half of FilterByUid.reduceReadsByProbeAndUid for this rank's pairs (host buffers in): writes pairs->n key

@@ -1,6 +1,7 @@
 // hsq_oracle.cpp -- TEST INFRASTRUCTURE ONLY (parity oracle / timed CPU baseline); see hsq_oracle_core.hpp.
 // C entry points with the same batch structs as include/hsq_b200.h so tests compare array to array.
 #include "hsq_oracle_heatseq.hpp"
+#include "hsq_oracle_assign.hpp"
 #include "../include/hsq_b200.h"
 #include <cstring>
 #include <thread>
@@ -151,6 +152,17 @@ int32_t hsqo_merge_pairs(const hsq_merge_batch* mb, uint8_t* out_seq, uint8_t* o
     } catch (const std::exception& ex) {
         g_err = ex.what();
         return HSQ_ERR_OUT_OF_RANGE;
+    }
+    return HSQ_OK;
+}
+
+// ReadToProbeAssigner.assignProbesToReads + RangeMap (hsq_oracle_assign.hpp)
+int32_t hsqo_assign_probes(const hsq_probe_ranges* pr, const hsq_mapped_records* rec, hsq_assign_out* o) {
+    try {
+        assign_probes(pr, rec, o);
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+        return HSQ_ERR_INVALID_ARGUMENT;
     }
     return HSQ_OK;
 }

@@ -10,7 +10,7 @@ import subprocess
 import numpy as np
 
 from bioinformatics_b200 import _abi as A
-from bioinformatics_b200.batches import (AlignResult, ExtendResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
+from bioinformatics_b200.batches import (AlignResult, AssignResult, ExtendResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
                                          merge_args, scorer)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -92,6 +92,14 @@ def merge_pairs(negative, up, down, upq, downq, up_start, down_start):
     _check(st)
     total = int(off[-1])
     return A.SeqBatch(seq[:total], off), A.SeqBatch(qual[:total], off.copy())
+
+
+def assign_probes(ranges, records, max_probes=4):
+    """ReadToProbeAssigner.assignProbesToReads + RangeMap on the CPU (hsq_oracle_assign.hpp)."""
+    out = AssignResult(records.n, max_probes)
+    pc, rc, oc = ranges.c(), records.c(), out.c()
+    _check(lib().hsqo_assign_probes(C.byref(pc), C.byref(rc), C.byref(oc)))
+    return out
 
 
 def dedup_batch(pairs, ext_uid_len, lig_uid_len, n_probes):
