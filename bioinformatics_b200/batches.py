@@ -195,6 +195,18 @@ class ProbeRangesHost:
         self.n = len(self.contig)
         assert len(self.reverse_strand) == len(self.start) == len(self.stop) == self.n
 
+    @classmethod
+    def from_probe_table(cls, probes, contig, bases_inside_extension_window=None, bases_inside_ligation_window=None):
+        """getProbeSearchBoundaries (…Identification.java:287-300): Probe.getStart()/getStop() are the min / max of the four
+        primer coordinates (COMMON/utils/probeinfo/Probe.java:75-81); the optional header values shrink the window."""
+        coords = np.stack([probes.lig_start, probes.lig_stop, probes.ext_start, probes.ext_stop]).astype(np.int64)
+        start, stop = coords.min(axis=0), coords.max(axis=0)
+        if bases_inside_extension_window is not None:
+            start = start + int(bases_inside_extension_window)
+        if bases_inside_ligation_window is not None:
+            stop = stop - int(bases_inside_ligation_window)
+        return cls(contig, probes.reverse_strand, start, stop)
+
     def c(self):
         return A.ProbeRanges(self.n, A.ptr(self.contig, A.i32p), A.ptr(self.reverse_strand, A.u8p), A.ptr(self.start, A.i32p),
                              A.ptr(self.stop, A.i32p))

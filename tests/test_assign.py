@@ -50,6 +50,17 @@ def test_oracle_rangemap_nested_window_quirk():
     assert out.probe_sets() == [(2,), (0, 1), (), (0,)]
 
 
+def test_search_windows_from_probe_table():
+    # getProbeSearchBoundaries (…Identification.java:287-300) over Probe.getStart/getStop (Probe.java:75-81)
+    from bioinformatics_b200.batches import ProbeTableHost
+    probes = ProbeTableHost([0, 1], ext_start=[100, 520], ext_stop=[120, 500], lig_start=[280, 330], lig_stop=[300, 310],
+                            target_start=[121, 331], target_stop=[279, 499], ext=["ACGT", "ACGT"], lig=["ACGT", "ACGT"], target=["AC", "AC"])
+    r = ProbeRangesHost.from_probe_table(probes, [0, 1])
+    assert r.start.tolist() == [100, 310] and r.stop.tolist() == [300, 520] and r.reverse_strand.tolist() == [0, 1]
+    r = ProbeRangesHost.from_probe_table(probes, [0, 1], 5, 7)
+    assert r.start.tolist() == [105, 315] and r.stop.tolist() == [293, 513]
+
+
 def _staggered_windows(rng, n, lo=1000):
     """Distinct starts, ends increasing with the starts: no window contains another."""
     starts = lo + np.cumsum(rng.integers(1, 120, n))
