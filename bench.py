@@ -190,6 +190,37 @@ def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
         mode = "sharded: hsq_dedup_keys -> NCCL all_to_all by probe owner -> hsq_dedup_reduce_keys -> all_to_all back"
     out["dedup"] = {"read_pairs_per_s": pairs.n * world / dt, "ms_host_to_host": dt * 1e3, "ms_device_incl_copies": ms_dev,
                     "unique_pairs": uniq, "mode": mode, "algorithmic_bytes_per_pair": 2 * READ_LEN + 16 + 24 + 48 + 25}
+    # dedup + extend: one probe task body per batch (unique pairs only, and with the duplicates as --markDuplicates does)
+    from bioinformatics_b200.batches import DedupExtendResult, ExtendResult
+    ctx.set_probes(probes)
+    res = DedupExtendResult(pairs.n, probes.n, CIGAR_CAP, MD_CAP)
+    for f in ExtendResult.FIELDS_I32 + ("ok", "overflow", "pair_ok", "cigar", "md"):
+        setattr(res.extend, f, pin(getattr(res.extend, f)))
+    for f in ("is_best", "group_size", "extended_pair"):
+        setattr(res, f, pin(getattr(res, f)))
+    for mark in (False, True):
+        if world == 1:
+            def task():
+                r = ctx.dedup_extend_batch(pairs, UID, 0, extend_duplicates=mark, cigar_cap=CIGAR_CAP, md_cap=MD_CAP, out=res)
+                return r.n_extended, int(r.extend.pair_ok[:r.n_extended].sum())
+            mode = "hsq_dedup_extend_batch, one GPU: reads uploaded once, unique pairs compacted on the device"
+        else:
+            def task():
+                b, _, _ = sharded.dedup_sharded(be, pairs, UID, 0, probes.n)
+                idx = np.arange(pairs.n) if mark else np.nonzero(b)[0]
+                sub = pairs if mark else pairs.subset(idx)
+                r = ctx.extend_batch(sub, CIGAR_CAP, MD_CAP, out=res.extend if mark else None)
+                return len(idx), int(r.pair_ok.sum())
+            mode = "sharded dedup over NCCL, then hsq_extend_batch on each rank's own surviving pairs"
+        task()
+        barrier()
+        t0 = time.perf_counter()
+        n_ext, n_ok = task()
+        barrier()
+        dt = max_over_ranks(time.perf_counter() - t0)
+        out["dedup_extend_mark_duplicates" if mark else "dedup_extend"] = {
+            "read_pairs_per_s": pairs.n * world / dt, "ms_host_to_host": dt * 1e3, "pairs_extended_rank0": int(n_ext),
+            "pairs_extended_ok_rank0": n_ok, "mode": mode}
     try:
         out["hbm_peak_gbs"] = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     except Exception:

@@ -62,6 +62,11 @@ class ProbeStats(C.Structure):
     _fields_ = [("n_probes", C.c_int64), ("unique_pairs", i32p), ("duplicate_pairs", i32p), ("max_pairs_per_uid", i32p)]
 
 
+class DedupExtendOut(C.Structure):
+    _fields_ = [("is_best", u8p), ("group_size", i32p), ("stats", C.POINTER(ProbeStats)), ("unique_unable_to_extend", i32p),
+                ("duplicate_unable_to_extend", i32p), ("n_extended", C.c_int64), ("extended_pair", i32p), ("extend", C.POINTER(ExtendOut))]
+
+
 class MergeBatch(C.Structure):
     _fields_ = [("n", C.c_int64), ("negative_strand", u8p), ("up", Seqs), ("down", Seqs), ("up_qual", u8p), ("down_qual", u8p),
                 ("up_start", i32p), ("down_start", i32p)]
@@ -119,6 +124,15 @@ class SeqBatch:
         arr2d = np.ascontiguousarray(arr2d, dtype=np.uint8)
         n, L = arr2d.shape
         return cls(arr2d.reshape(-1), np.arange(n + 1, dtype=np.int64) * L)
+
+    def take(self, idx):
+        """Ragged gather: the strings idx[0], idx[1], ... as a new batch (vectorised)."""
+        idx = np.asarray(idx, dtype=np.int64)
+        lens = (self.offsets[1:] - self.offsets[:-1])[idx]
+        offsets = np.zeros(len(idx) + 1, dtype=np.int64)
+        np.cumsum(lens, out=offsets[1:])
+        src = np.repeat(self.offsets[:-1][idx] - offsets[:-1], lens) + np.arange(offsets[-1], dtype=np.int64)
+        return SeqBatch(self.data[src], offsets)
 
     def string(self, k):
         return self.data[self.offsets[k]:self.offsets[k + 1]].tobytes().decode("ascii")

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 from . import _abi as A
-from .batches import (AlignResult, AssignResult, ExtendResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
+from .batches import (AlignResult, AssignResult, DedupExtendResult, ExtendResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
                       ProbeTableHost, merge_args, scorer)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
@@ -20,7 +20,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
-           "hsq_set_probe_ranges", "hsq_assign_probes")
+           "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch")
 
 
 class HsqError(RuntimeError):
@@ -147,6 +147,17 @@ class Context:
         self._check(self.lib.hsq_dedup_batch(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
                                              A.ptr(is_best, A.u8p), A.ptr(group_size, A.i32p), C.byref(sc)))
         return is_best, group_size, stats
+
+    def dedup_extend_batch(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, extend_duplicates=False, cigar_cap=32, md_cap=48,
+                           n_probes=None, out=None):
+        """hsq_dedup_extend_batch: one probe task body (reduce by UID, extend the unique pairs) for the whole batch."""
+        out = out or DedupExtendResult(pairs.n, n_probes or self.n_probes, cigar_cap, md_cap)
+        pc, oc = pairs.c(), out.c()
+        st = self.lib.hsq_dedup_extend_batch(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                             C.c_int32(1 if extend_duplicates else 0), C.byref(oc))
+        out.finish()
+        self._check(st)
+        return out
 
     def merge_pairs(self, negative, up, down, upq, downq, up_start, down_start, out_cap=None):
         """hsq_merge_pairs: returns (merged sequences, merged qualities) as SeqBatch; sizes itself with a second call."""

@@ -64,12 +64,10 @@ class PairBatchHost:
                              None if self.read_index is None else self.read_index[:k])
 
     def subset(self, idx):
-        idx = np.asarray(idx)
+        idx = np.asarray(idx, dtype=np.int64)
 
         def take(sb):
-            if sb is None:
-                return None
-            return A.SeqBatch.from_strings([sb.data[sb.offsets[k]:sb.offsets[k + 1]].tobytes() for k in idx])
+            return None if sb is None else sb.take(idx)
 
         return PairBatchHost(self.probe_id[idx], take(self.r1), take(self.r2), take(self.q1), take(self.q2),
                              None if self.read_index is None else self.read_index[idx])
@@ -103,6 +101,18 @@ class ExtendResult:
     def finish(self):
         self.cells = int(self._c.cells)
         return self
+
+    def head(self, m):
+        """The first m pair slots as a result of their own (views)."""
+        r = ExtendResult(0, self.cigar_cap, self.md_cap)
+        r.n = m
+        for f in self.FIELDS_I32 + ("ok", "overflow"):
+            setattr(r, f, getattr(self, f)[:2 * m])
+        r.pair_ok = self.pair_ok[:m]
+        r.cigar = self.cigar[:2 * m * self.cigar_cap]
+        r.md = self.md[:2 * m * self.md_cap]
+        r.cells = self.cells
+        return r
 
     def cigars(self):
         return A.slot_strings(self.cigar, self.cigar_len, self.cigar_cap)
@@ -168,6 +178,35 @@ class ProbeStatsHost:
     def c(self):
         return A.ProbeStats(self.n_probes, A.ptr(self.unique_pairs, A.i32p), A.ptr(self.duplicate_pairs, A.i32p),
                             A.ptr(self.max_pairs_per_uid, A.i32p))
+
+
+class DedupExtendResult:
+    """hsq_dedup_extend_out with host arrays for n pairs and n_probes probes."""
+
+    def __init__(self, n, n_probes, cigar_cap=32, md_cap=48):
+        self.n = n
+        self.is_best = np.zeros(n, dtype=np.uint8)
+        self.group_size = np.zeros(n, dtype=np.int32)
+        self.stats = ProbeStatsHost(n_probes)
+        self.unique_unable_to_extend = np.zeros(n_probes, dtype=np.int32)
+        self.duplicate_unable_to_extend = np.zeros(n_probes, dtype=np.int32)
+        self.extended_pair = np.zeros(n, dtype=np.int32)
+        self.extend = ExtendResult(n, cigar_cap, md_cap)
+        self.n_extended = 0
+        self._c = None
+
+    def c(self):
+        self._stats_c = self.stats.c()
+        self._ext_c = self.extend.c()
+        self._c = A.DedupExtendOut(A.ptr(self.is_best, A.u8p), A.ptr(self.group_size, A.i32p), C.pointer(self._stats_c),
+                                   A.ptr(self.unique_unable_to_extend, A.i32p), A.ptr(self.duplicate_unable_to_extend, A.i32p), 0,
+                                   A.ptr(self.extended_pair, A.i32p), C.pointer(self._ext_c))
+        return self._c
+
+    def finish(self):
+        self.n_extended = int(self._c.n_extended)
+        self.extend.cells = int(self._ext_c.cells)
+        return self
 
 
 def merge_args(negative, up, down, upq, downq, up_start, down_start):

@@ -164,7 +164,7 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
                            &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->alt_out_i32,
                            &ctx->alt_out_u8, &ctx->alt_out_slots, &ctx->alt_pair_ok, &ctx->alt_ptr_words, &ctx->alt_brow, &ctx->alt_cols,
                            &ctx->alt_colinfo, &ctx->alt_slow, &ctx->alt_sort_a, &ctx->alt_sort_b, &ctx->alt_sort_c, &ctx->rg_start, &ctx->rg_end,
-                           &ctx->rg_value, &ctx->rg_off};
+                           &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32};
     for (auto* b : bufs) b->release();
     hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb, &ctx->alt_r1, &ctx->alt_r2};
     for (auto* s : seqs) s->release();
@@ -223,4 +223,5 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_merge.inl"
 #include "hsq_capi_resolve.inl"
 #include "hsq_capi_assign.inl"
+#include "hsq_capi_pipeline.inl"
 #include "hsq_capi_peak.inl"

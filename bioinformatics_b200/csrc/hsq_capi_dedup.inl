@@ -149,11 +149,11 @@ int dedup_upload_keygen(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, in
     int rc = reset_status(ctx);
     if (rc) return rc;
     // raw bytes: UID grouping is on the read strings themselves, qualities are summed as chars
+    if ((rc = upload_pairs_raw(ctx, pb))) return rc;  // probe ids + reads (ASCII, offsets rebased to 0)
     struct { hsq::DevBuf* d; const void* h; size_t bytes; } up[] = {
-        {&ctx->r1.ascii, pb->r1.data, (size_t)pb->r1.offsets[n]}, {&ctx->r2.ascii, pb->r2.data, (size_t)pb->r2.offsets[n]},
-        {&ctx->q1, pb->q1, (size_t)pb->r1.offsets[n]},            {&ctx->q2, pb->q2, (size_t)pb->r2.offsets[n]},
-        {&ctx->r1.offsets, pb->r1.offsets, (nn + 1) * 8},         {&ctx->r2.offsets, pb->r2.offsets, (nn + 1) * 8},
-        {&ctx->probe_id, pb->probe_id, nn * 4},                   {&ctx->read_index, pb->read_index, nn * 4}};
+        {&ctx->q1, pb->q1 ? pb->q1 + pb->r1.offsets[0] : nullptr, (size_t)ctx->r1.total},
+        {&ctx->q2, pb->q2 ? pb->q2 + pb->r2.offsets[0] : nullptr, (size_t)ctx->r2.total},
+        {&ctx->read_index, pb->read_index, nn * 4}};
     for (auto& c : up) {
         if (c.bytes && !c.h) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_dedup: null input array");
         HSQ_CUDA(ctx, c.d->ensure(c.bytes + 16));

@@ -1,0 +1,208 @@
+// hsq_capi_pipeline.inl -- hsq_dedup_extend_batch: the body of one probe task for all probes of a batch
+// (HSQ/process/PrimerReadExtensionAndPcrDuplicateIdentification.java:1172-1216): FilterByUid.reduceReadsByProbeAndUid, then
+// ExtendReadsToPrimer.extendReadsToPrimers on the unique pairs (and on the duplicates when they are kept or marked).
+// The reads cross PCIe once.  Without duplicate extension the unique pairs are compacted on the device (flag scan -> list,
+// length scan -> offsets, warp-per-read byte copy) into the second buffer set and the DP kernels see only them.
+namespace {
+
+__global__ void flags_to_i64_kernel(const uint8_t* __restrict__ f, int64_t n, int64_t* __restrict__ out) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride) out[k] = f[k] ? 1 : 0;
+}
+
+// survivors list: list[pos[k]] = k for flagged k; their probe ids and read lengths in list order
+__global__ void survivor_list_kernel(const uint8_t* __restrict__ f, const int64_t* __restrict__ pos, int64_t n, const int32_t* __restrict__ probe_id,
+                                     const int64_t* __restrict__ off1, const int64_t* __restrict__ off2, int32_t* __restrict__ list,
+                                     int32_t* __restrict__ probe_out, int64_t* __restrict__ len1, int64_t* __restrict__ len2) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride) {
+        if (!f[k]) continue;
+        const int64_t j = pos[k];
+        list[j] = (int32_t)k;
+        probe_out[j] = probe_id[k];
+        len1[j] = off1[k + 1] - off1[k];
+        len2[j] = off2[k + 1] - off2[k];
+    }
+}
+
+// one warp per surviving read: raw bytes to their compacted place
+__global__ void survivor_copy_kernel(const uint8_t* __restrict__ src, const int64_t* __restrict__ src_off, const int32_t* __restrict__ list,
+                                     const int64_t* __restrict__ dst_off, int64_t m, uint8_t* __restrict__ dst) {
+    const int lane = threadIdx.x & 31;
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; w < m; w += stride) {
+        const int64_t s = src_off[list[w]], d = dst_off[w];
+        const int len = (int)(dst_off[w + 1] - d);
+        for (int i = lane; i < len; i += 32) dst[d + i] = src[s + i];
+    }
+}
+
+// per-probe "unable to extend" counters (:1189,:1208): slot j holds pair list[j] (or j itself when list is null)
+__global__ void unable_to_extend_kernel(const uint8_t* __restrict__ pair_ok, const int32_t* __restrict__ list, const uint8_t* __restrict__ best,
+                                        const int32_t* __restrict__ probe_of_slot, int64_t m, int32_t* __restrict__ unable_unique,
+                                        int32_t* __restrict__ unable_dup) {
+    int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; j < m; j += stride) {
+        if (pair_ok[j]) continue;
+        const int64_t k = list ? list[j] : j;
+        atomicAdd((best[k] ? unable_unique : unable_dup) + probe_of_slot[j], 1);
+    }
+}
+
+__global__ void iota_kernel(int32_t* __restrict__ out, int64_t n) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride) out[k] = (int32_t)k;
+}
+
+// exclusive scan of in[0..n) into out[0..n] (tile sums in `tiles`)
+int scan_i64(hsq_ctx* ctx, const int64_t* in, int64_t n, int64_t* tiles, int64_t* out) {
+    const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
+    scan_tile_sums_kernel<<<(unsigned)n_tiles, SCAN_BLOCK, 0, ctx->stream>>>(in, n, tiles);
+    scan_sums_kernel<<<1, SCAN_BLOCK, 0, ctx->stream>>>(tiles, n_tiles);
+    scan_apply_kernel<<<(unsigned)n_tiles, SCAN_BLOCK, 0, ctx->stream>>>(in, n, tiles, out);
+    ctx->launches += 3;
+    HSQ_CUDA(ctx, cudaGetLastError());
+    return HSQ_OK;
+}
+
+void swap_read_buffers(hsq_ctx* ctx) {
+    std::swap(ctx->r1, ctx->alt_r1);
+    std::swap(ctx->r2, ctx->alt_r2);
+    std::swap(ctx->probe_id, ctx->alt_probe_id);
+}
+
+// compacts the flagged pairs of the staged batch (ctx->r1/r2/probe_id) into the second buffer set; returns their number
+int compact_survivors(hsq_ctx* ctx, int64_t n, const uint8_t* d_keep, int32_t* d_list, int64_t* m_out) {
+    const size_t nn = (size_t)n;
+    int rc;
+    const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
+    HSQ_CUDA(ctx, ctx->sort_a.ensure((nn + 1) * 8));                     // flags as int64, then lengths of R1
+    HSQ_CUDA(ctx, ctx->sort_b.ensure((nn + 1) * 8));                     // positions, then lengths of R2
+    HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)n_tiles * 8 + 16));         // tile sums
+    int64_t* a = ctx->sort_a.as<int64_t>();
+    int64_t* b = ctx->sort_b.as<int64_t>();
+    int64_t* tiles = ctx->sort_c.as<int64_t>();
+    const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+    flags_to_i64_kernel<<<gblocks, 256, 0, ctx->stream>>>(d_keep, n, a);
+    ctx->launches++;
+    if ((rc = scan_i64(ctx, a, n, tiles, b))) return rc;
+    int64_t* h_m = reinterpret_cast<int64_t*>(ctx->h_cells) + 1;  // pinned
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_m, b + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int64_t m = *h_m;
+    *m_out = m;
+    const size_t mm = (size_t)m;
+    HSQ_CUDA(ctx, ctx->alt_probe_id.ensure(mm * 4 + 16));
+    HSQ_CUDA(ctx, ctx->alt_r1.offsets.ensure((mm + 1) * 8));
+    HSQ_CUDA(ctx, ctx->alt_r2.offsets.ensure((mm + 1) * 8));
+    if (m > 0) {
+        // the length arrays may overwrite the flag array, not the positions: lengths go to a and a second array
+        HSQ_CUDA(ctx, ctx->flags.ensure((mm + 1) * 8 + 16));
+        int64_t* len1 = ctx->flags.as<int64_t>();
+        HSQ_CUDA(ctx, ctx->slow.ensure((mm + 1) * 8 + 16));
+        int64_t* len2 = ctx->slow.as<int64_t>();
+        survivor_list_kernel<<<gblocks, 256, 0, ctx->stream>>>(d_keep, b, n, ctx->probe_id.as<int32_t>(), ctx->r1.offsets.as<int64_t>(),
+                                                              ctx->r2.offsets.as<int64_t>(), d_list, ctx->alt_probe_id.as<int32_t>(), len1, len2);
+        ctx->launches++;
+        if ((rc = scan_i64(ctx, len1, m, tiles, ctx->alt_r1.offsets.as<int64_t>()))) return rc;
+        if ((rc = scan_i64(ctx, len2, m, tiles, ctx->alt_r2.offsets.as<int64_t>()))) return rc;
+    } else {
+        HSQ_CUDA(ctx, cudaMemsetAsync(ctx->alt_r1.offsets.p, 0, 8, ctx->stream));
+        HSQ_CUDA(ctx, cudaMemsetAsync(ctx->alt_r2.offsets.p, 0, 8, ctx->stream));
+    }
+    // the compacted reads are never larger than the batch: size the buffers without a second synchronisation
+    struct { DevSeqsOwned* src; DevSeqsOwned* dst; } sides[2] = {{&ctx->r1, &ctx->alt_r1}, {&ctx->r2, &ctx->alt_r2}};
+    for (auto& s : sides) {
+        HSQ_CUDA(ctx, s.dst->ascii.ensure((size_t)s.src->total + 16));
+        HSQ_CUDA(ctx, s.dst->codes.ensure((size_t)s.src->total + 16));
+        s.dst->n = m;
+        if (m > 0) {
+            const int blocks = (int)std::min<int64_t>((m * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
+            survivor_copy_kernel<<<blocks, 256, 0, ctx->stream>>>(s.src->ascii.as<uint8_t>(), s.src->offsets.as<int64_t>(), d_list,
+                                                                 s.dst->offsets.as<int64_t>(), m, s.dst->ascii.as<uint8_t>());
+            ctx->launches++;
+        }
+    }
+    HSQ_CUDA(ctx, cudaGetLastError());
+    // totals of the compacted sides (needed by the encoder's launch size)
+    int64_t* h_tot = reinterpret_cast<int64_t*>(ctx->h_cells) + 2;
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_tot, ctx->alt_r1.offsets.as<int64_t>() + m, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_tot + 1, ctx->alt_r2.offsets.as<int64_t>() + m, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->alt_r1.total = h_tot[0];
+    ctx->alt_r2.total = h_tot[1];
+    return HSQ_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, int32_t extend_duplicates,
+                                          hsq_dedup_extend_out* out) {
+    if (!ctx || !pairs || !out || !out->is_best || !out->extend || !out->extended_pair) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (pairs->n < 0 || pairs->r1.n != pairs->n || pairs->r2.n != pairs->n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
+    if (pairs->n >= (1ll << 31)) return fail(ctx, HSQ_ERR_UNSUPPORTED, "more than 2^31 pairs in one batch");
+    if (u < 0 || v < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative UID length");
+    if (u + v > 32) return fail(ctx, HSQ_ERR_UNSUPPORTED, "UID longer than 32 bases in total is outside the accelerated domain");
+    if (!out->stats || out->stats->n_probes <= 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe stats (with n_probes) are required");
+    if (out->extend->cigar_cap < 0 || out->extend->md_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
+    int rc = extend_args_ok(ctx);
+    if (rc) return rc;
+    if (out->stats->n_probes != ctx->n_probes) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "stats->n_probes differs from the probe table");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    const int64_t n = pairs->n, np = out->stats->n_probes;
+    const size_t nn = (size_t)n;
+    out->n_extended = 0;
+    auto run = [&]() -> int {
+        int rc;
+        if ((rc = dedup_upload_keygen(ctx, pairs, u, v, np))) return rc;
+        HSQ_CUDA(ctx, ctx->dd_u8.ensure(nn + 32));
+        HSQ_CUDA(ctx, ctx->dd_i32.ensure((2 * nn + 5 * (size_t)np) * 4 + 16));
+        uint8_t* d_best = ctx->dd_u8.as<uint8_t>();
+        int32_t* d_gs = ctx->dd_i32.as<int32_t>();
+        int32_t* d_list = d_gs + nn;
+        int32_t* d_stats = d_list + nn;
+        int32_t* d_unable = d_stats + 3 * np;
+        if ((rc = dedup_reduce_device(ctx, n, np, u + v, d_best, d_gs, d_stats))) return rc;
+        HSQ_CUDA(ctx, cudaMemsetAsync(d_unable, 0, 2 * (size_t)np * 4, ctx->stream));
+        if ((rc = d2h(ctx, out->is_best, d_best, nn))) return rc;
+        if ((rc = d2h(ctx, out->group_size, d_gs, nn))) return rc;
+        if ((rc = fetch_stats(ctx, out->stats, d_stats))) return rc;
+        int64_t m = n;
+        const bool compact = !extend_duplicates && n > 0;
+        if (compact) {
+            if ((rc = compact_survivors(ctx, n, d_best, d_list, &m))) return rc;
+            swap_read_buffers(ctx);  // the compacted pairs are the staged batch now
+        } else if (n > 0) {
+            const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+            iota_kernel<<<gblocks, 256, 0, ctx->stream>>>(d_list, n);
+            ctx->launches++;
+        }
+        if ((rc = d2h(ctx, out->extended_pair, d_list, (size_t)m))) return rc;
+        ctx->ext_n = m;
+        ctx->keep_counters = false;
+        rc = extend_run(ctx, out->extend->cigar_cap, out->extend->md_cap);
+        if (!rc && m > 0) {
+            const int gblocks = (int)std::min<int64_t>((m + 255) / 256, (int64_t)ctx->sm_count * 16);
+            unable_to_extend_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->pair_ok.as<uint8_t>(), d_list, d_best, ctx->probe_id.as<int32_t>(), m,
+                                                                     d_unable, d_unable + np);
+            ctx->launches++;
+        }
+        if (!rc) rc = d2h(ctx, out->unique_unable_to_extend, d_unable, (size_t)np);
+        if (!rc) rc = d2h(ctx, out->duplicate_unable_to_extend, d_unable + np, (size_t)np);
+        if (!rc) rc = extend_fetch(ctx, out->extend);
+        if (compact) swap_read_buffers(ctx);
+        ctx->ext_n = -1;
+        ctx->ext_ran = false;
+        if (!rc) out->n_extended = m;
+        return rc;
+    };
+    rc = run();
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}

@@ -66,6 +66,7 @@ struct hsq_ctx {
     bool force_dp32 = false;
     // probe search windows sorted by (contig, strand, start) for hsq_assign_probes
     hsq::DevBuf rg_start, rg_end, rg_value, rg_off;
+    hsq::DevBuf dd_u8, dd_i32;  // hsq_dedup_extend_batch: dedup answers kept while the extend stage reuses the output buffers
     int64_t rg_n = -1;
     int32_t rg_contigs = 0;
     // second set of extend-batch buffers + copy streams: hsq_extend_batch pipelines chunks (H2D | kernels | D2H)

@@ -212,6 +212,18 @@ typedef struct hsq_assign_out {
 #define HSQ_ASSIGN_AMBIGUOUS_NAME (-2) /* the read name occurs on four or more usable records */
 #define HSQ_ASSIGN_IGNORED (-3)        /* the record's contig holds no probe */
 
+/* ---- one probe task, batched: dedup then extend (…Identification.java:1172-1234) ----------------------------------- */
+typedef struct hsq_dedup_extend_out {
+    uint8_t* is_best;                   /* [n] as hsq_dedup_batch */
+    int32_t* group_size;                /* [n] may be NULL */
+    hsq_probe_stats* stats;             /* per-probe counters of the reduction (required) */
+    int32_t* unique_unable_to_extend;   /* [stats->n_probes] numberOfUniqueReadPairsUnableExtendPrimer (:1189); may be NULL */
+    int32_t* duplicate_unable_to_extend;/* [stats->n_probes] numberOfDuplicateReadPairsUnableExtendPrimer (:1208); may be NULL */
+    int64_t n_extended;                 /* out: pairs handed to the extension = slots used in `extend` */
+    int32_t* extended_pair;             /* [n] out: extended_pair[j] = index of the pair whose results sit in slot j (ascending) */
+    hsq_extend_out* extend;             /* arrays sized for n pairs (2n read ends); slots j < n_extended are written */
+} hsq_dedup_extend_out;
+
 /* ---- context ------------------------------------------------------------------------------ */
 int32_t hsq_ctx_create(int32_t device, hsq_ctx** out);
 void hsq_ctx_destroy(hsq_ctx* ctx);
@@ -253,6 +265,14 @@ int32_t hsq_extend_fetch(hsq_ctx* ctx, hsq_extend_out* out);
 int32_t hsq_resolve_multi_probe(hsq_ctx* ctx, const hsq_candidates* cands, int32_t ext_uid_len, int32_t lig_uid_len,
                                 int32_t* best_probe, int32_t* cand_matches, int32_t* cand_edit);
 
+
+/* The body of PrimerReadExtensionAndFilteringOfUniquePcrProbesTask.run for every probe of the batch at once
+ * (…Identification.java:1172-1216): reduceReadsByProbeAndUid, then extendReadsToPrimers on the unique pairs and -- only when
+ * extend_duplicates != 0 (keepDuplicates or markDuplicates, :1203) -- on the duplicates too.  The reads are uploaded once;
+ * the unique pairs are compacted on the device and the extension runs on them alone.  Results equal hsq_dedup_batch
+ * followed by hsq_extend_batch on the pairs listed in extended_pair. */
+int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len,
+                               int32_t extend_duplicates, hsq_dedup_extend_out* out);
 
 /* mergeSequences per item (…Identification.java:1362-1552, behind the unregistered --mergePairs option): lead + overlap
  * (per position the base with the higher quality wins, ties to upstream; a gap is filled with N / '!') + trail.
