@@ -67,6 +67,10 @@ class DedupExtendOut(C.Structure):
                 ("duplicate_unable_to_extend", i32p), ("n_extended", C.c_int64), ("extended_pair", i32p), ("extend", C.POINTER(ExtendOut))]
 
 
+class RecordOut(C.Structure):
+    _fields_ = [("flag", C.POINTER(C.c_uint16)), ("mate_pos", i32p), ("offsets", i64p), ("seq", u8p), ("qual", u8p)]
+
+
 class MergeBatch(C.Structure):
     _fields_ = [("n", C.c_int64), ("negative_strand", u8p), ("up", Seqs), ("down", Seqs), ("up_qual", u8p), ("down_qual", u8p),
                 ("up_start", i32p), ("down_start", i32p)]

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 from . import _abi as A
-from .batches import (AlignResult, AssignResult, DedupExtendResult, ExtendResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
+from .batches import (AlignResult, AssignResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
                       ProbeTableHost, merge_args, scorer)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
@@ -20,7 +20,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
-           "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch")
+           "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records")
 
 
 class HsqError(RuntimeError):
@@ -157,6 +157,15 @@ class Context:
                                              C.c_int32(1 if extend_duplicates else 0), C.byref(oc))
         out.finish()
         self._check(st)
+        return out
+
+    def extend_records(self, pairs: PairBatchHost, ext: ExtendResult, duplicate=None, out_cap=None):
+        """hsq_extend_records: FLAG / PNEXT / read string / qualities of the records of the pairs `ext` extended."""
+        cap = out_cap if out_cap is not None else int(len(pairs.r1.data) + len(pairs.r2.data))
+        dup = None if duplicate is None else np.ascontiguousarray(duplicate, dtype=np.uint8)
+        out = RecordResult(pairs.n, cap)
+        pc, ec, oc = pairs.c(), ext.c(), out.c()
+        self._check(self.lib.hsq_extend_records(self.h, C.byref(pc), C.byref(ec), A.ptr(dup, A.u8p), C.byref(oc), C.c_int64(cap)))
         return out
 
     def merge_pairs(self, negative, up, down, upq, downq, up_start, down_start, out_cap=None):

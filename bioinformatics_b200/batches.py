@@ -209,6 +209,28 @@ class DedupExtendResult:
         return self
 
 
+class RecordResult:
+    """hsq_record_out with host arrays: FLAG, PNEXT, read string and base qualities of the two records of each pair."""
+
+    def __init__(self, n, cap):
+        self.n, self.cap = n, cap
+        self.flag = np.zeros(2 * n, dtype=np.uint16)
+        self.mate_pos = np.zeros(2 * n, dtype=np.int32)
+        self.offsets = np.zeros(2 * n + 1, dtype=np.int64)
+        self.seq = np.zeros(max(1, cap), dtype=np.uint8)
+        self.qual = np.zeros(max(1, cap), dtype=np.uint8)
+
+    def c(self):
+        return A.RecordOut(C.cast(self.flag.ctypes.data, C.POINTER(C.c_uint16)), A.ptr(self.mate_pos, A.i32p), A.ptr(self.offsets, A.i64p),
+                           A.ptr(self.seq, A.u8p), A.ptr(self.qual, A.u8p))
+
+    def seqs(self):
+        return A.SeqBatch(self.seq[:self.offsets[-1]], self.offsets)
+
+    def quals(self):
+        return A.SeqBatch(self.qual[:self.offsets[-1]], self.offsets)
+
+
 def merge_args(negative, up, down, upq, downq, up_start, down_start):
     up = up if isinstance(up, A.SeqBatch) else A.SeqBatch.from_strings(up)
     down = down if isinstance(down, A.SeqBatch) else A.SeqBatch.from_strings(down)

@@ -224,4 +224,5 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_resolve.inl"
 #include "hsq_capi_assign.inl"
 #include "hsq_capi_pipeline.inl"
+#include "hsq_capi_records.inl"
 #include "hsq_capi_peak.inl"

@@ -224,6 +224,20 @@ typedef struct hsq_dedup_extend_out {
     hsq_extend_out* extend;             /* arrays sized for n pairs (2n read ends); slots j < n_extended are written */
 } hsq_dedup_extend_out;
 
+/* ---- SAM record fields of extended pairs (SURVEY.md 8(a) A5 outputs, 8(f) f4) ---------------------------------------- */
+/* What ExtendReadsToPrimer.extendReadPair / createRecord and SAMRecordUtil.setSAMRecordsAsPair put on the two records of a
+ * pair beyond the fields of hsq_extend_out (ExtendReadsToPrimer.java:131-181,247-284; SAMRecordUtil.java:270-289).
+ * Entry 2k is read one of pair k, 2k+1 read two.  Pairs whose pair_ok is 0 get empty strings, flag 0 and mate_pos 0
+ * (the reference writes only pairs whose two reads extended, ExtendReadsToPrimer.java:364). */
+typedef struct hsq_record_out {
+    uint16_t* flag;     /* [2n] SAM FLAG: 0x1 paired | 0x2 proper pair | 0x10 read on - strand | 0x20 mate on - strand |
+                         * 0x40 first / 0x80 second of pair | 0x400 duplicate */
+    int32_t* mate_pos;  /* [2n] PNEXT: alignment start of the other record */
+    int64_t* offsets;   /* [2n+1] byte range of each record in seq / qual */
+    uint8_t* seq;       /* read strings: read[readStart..readStop], reverse-complemented on the - strand */
+    uint8_t* qual;      /* base qualities of the same range, reversed on the - strand */
+} hsq_record_out;
+
 /* ---- context ------------------------------------------------------------------------------ */
 int32_t hsq_ctx_create(int32_t device, hsq_ctx** out);
 void hsq_ctx_destroy(hsq_ctx* ctx);
@@ -273,6 +287,13 @@ int32_t hsq_resolve_multi_probe(hsq_ctx* ctx, const hsq_candidates* cands, int32
  * followed by hsq_extend_batch on the pairs listed in extended_pair. */
 int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len,
                                int32_t extend_duplicates, hsq_dedup_extend_out* out);
+
+/* Record fields of the pairs of a batch that hsq_extend_batch (or hsq_dedup_extend_batch) extended: `ext` holds that
+ * call's host results for the same pairs (ok, read_start, read_stop, pos, pair_ok are read).  duplicate[k] != 0 sets the
+ * duplicate flag of pair k (isMarkedDuplicate, ExtendReadsToPrimer.java:266); NULL = none.  seq / qual have out_cap bytes;
+ * when more are needed the call returns HSQ_ERR_OVERFLOW with out->offsets filled. */
+int32_t hsq_extend_records(hsq_ctx* ctx, const hsq_pair_batch* pairs, const hsq_extend_out* ext, const uint8_t* duplicate,
+                           hsq_record_out* out, int64_t out_cap);
 
 /* mergeSequences per item (…Identification.java:1362-1552, behind the unregistered --mergePairs option): lead + overlap
  * (per position the base with the higher quality wins, ties to upstream; a gap is filled with N / '!') + trail.

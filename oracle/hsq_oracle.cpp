@@ -156,6 +156,59 @@ int32_t hsqo_merge_pairs(const hsq_merge_batch* mb, uint8_t* out_seq, uint8_t* o
     return HSQ_OK;
 }
 
+// The SAM record fields of extended pairs: runs extendReadPair (ExtendReadsToPrimer.java:96-198) itself and reports what
+// createRecord (:247-284) and SAMRecordUtil.setSAMRecordsAsPair (SAMRecordUtil.java:270-289) put on the two records.
+int32_t hsqo_extend_records(const hsq_probe_table* pt, const hsq_scorer* scorer, const hsq_pair_batch* pb, const uint8_t* duplicate,
+                            hsq_record_out* o, int64_t out_cap) {
+    Scorer sc;
+    sc.match = scorer->match; sc.mismatch = scorer->mismatch; sc.gap_extend = scorer->gap_extend; sc.gap_start = scorer->gap_start;
+    try {
+        std::vector<Probe> probes;
+        for (int64_t k = 0; k < pt->n; k++) probes.push_back(get_probe(*pt, k));
+        NwWorkspace ws;
+        int64_t cells = 0, at = 0;
+        bool overflow = false;
+        o->offsets[0] = 0;
+        for (int64_t k = 0; k < pb->n; k++) {
+            const Probe& p = probes[(size_t)pb->probe_id[k]];
+            seq_t s1 = get_seq(pb->r1, k), s2 = get_seq(pb->r2, k);
+            PairExtension e = extend_read_pair(p, s1, get_str(pb->q1, pb->r1.offsets, k), s2, get_str(pb->q2, pb->r2.offsets, k), sc, &ws, &cells);
+            const std::string* seqs[2] = {&e.seq1, &e.seq2};
+            const std::string* quals[2] = {&e.qual1, &e.qual2};
+            const bool neg[2] = {e.neg1, e.neg2};
+            const int pos[2] = {e.one.pos, e.two.pos};
+            for (int m = 0; m < 2; m++) {
+                const int64_t i = 2 * k + m;
+                o->flag[i] = 0;
+                o->mate_pos[i] = 0;
+                if (e.pair_ok()) {  // only pairs whose two reads extended are written (:364)
+                    // setReadPairedFlag, setProperPairFlag, first/second of pair (SAMRecordUtil.java:271-276); read strand (:257);
+                    // mate strand = the mate's read strand (:283); duplicate (:266)
+                    o->flag[i] = (uint16_t)(0x1 | 0x2 | (m ? 0x80 : 0x40) | (neg[m] ? 0x10 : 0) | (neg[1 - m] ? 0x20 : 0) |
+                                            ((duplicate && duplicate[k]) ? 0x400 : 0));
+                    o->mate_pos[i] = pos[1 - m];
+                    if (at + (int64_t)seqs[m]->size() <= out_cap) {
+                        memcpy(o->seq + at, seqs[m]->data(), seqs[m]->size());
+                        memcpy(o->qual + at, quals[m]->data(), quals[m]->size());
+                    } else {
+                        overflow = true;
+                    }
+                    at += (int64_t)seqs[m]->size();
+                }
+                o->offsets[i + 1] = at;
+            }
+        }
+        if (overflow) return HSQ_ERR_OVERFLOW;
+    } catch (const std::invalid_argument& ex) {
+        g_err = ex.what();
+        return HSQ_ERR_BAD_CHARACTER;
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+        return HSQ_ERR_OUT_OF_RANGE;
+    }
+    return HSQ_OK;
+}
+
 // ReadToProbeAssigner.assignProbesToReads + RangeMap (hsq_oracle_assign.hpp)
 int32_t hsqo_assign_probes(const hsq_probe_ranges* pr, const hsq_mapped_records* rec, hsq_assign_out* o) {
     try {

@@ -10,7 +10,7 @@ import subprocess
 import numpy as np
 
 from bioinformatics_b200 import _abi as A
-from bioinformatics_b200.batches import (AlignResult, AssignResult, ExtendResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
+from bioinformatics_b200.batches import (AlignResult, AssignResult, ExtendResult, RecordResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
                                          merge_args, scorer)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -36,7 +36,8 @@ def lib():
         _lib.hsqo_last_error.restype = C.c_char_p
         for name in ("hsqo_align_batch", "hsqo_trim_batch", "hsqo_dedup_batch", "hsqo_extend_batch",
                      "hsqo_resolve_multi_probe", "hsqo_primer_end", "hsqo_index_of_first_match_in_reference",
-                     "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs"):
+                     "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs", "hsqo_assign_probes",
+                     "hsqo_extend_records"):
             getattr(_lib, name).restype = C.c_int32
     return _lib
 
@@ -92,6 +93,17 @@ def merge_pairs(negative, up, down, upq, downq, up_start, down_start):
     _check(st)
     total = int(off[-1])
     return A.SeqBatch(seq[:total], off), A.SeqBatch(qual[:total], off.copy())
+
+
+def extend_records(probes, pairs, sc=None, duplicate=None):
+    """extendReadPair + createRecord + setSAMRecordsAsPair on the CPU: FLAG, PNEXT, read string, qualities per record."""
+    sc = sc or scorer()
+    cap = int(len(pairs.r1.data) + len(pairs.r2.data))
+    dup = None if duplicate is None else np.ascontiguousarray(duplicate, dtype=np.uint8)
+    out = RecordResult(pairs.n, cap)
+    tc, pc, oc = probes.c(), pairs.c(), out.c()
+    _check(lib().hsqo_extend_records(C.byref(tc), C.byref(sc), C.byref(pc), A.ptr(dup, A.u8p), C.byref(oc), C.c_int64(cap)))
+    return out
 
 
 def assign_probes(ranges, records, max_probes=4):
