@@ -29,7 +29,7 @@ READ_LEN = 150
 UID = 10
 CIGAR_CAP, MD_CAP = 24, 40
 OPS_PER_CELL = 12  # algorithmic INT32 ops per DP cell
-TRAFFIC_PER_PAIR_BYTES = (4.485631e9 + 6.310107e9) / 500000  # measured DRAM traffic of capture2_kernel per read pair (ncu, r1_c)
+TRAFFIC_PER_PAIR_BYTES = (5.109331e9 + 6.514748e9) / 500000  # measured DRAM traffic of capture2_kernel per read pair (ncu, r1_g)
 
 
 def parse():
@@ -396,7 +396,7 @@ def main():
                              "frac": achieved / peak,
                              "traffic": TRAFFIC_PER_PAIR_BYTES * n,
                              "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of capture2_kernel from the ncu --set full capture "
-                                             "at 500 k pairs (profiles/ncu_full_capture2_kernel_r1_c.txt: 4.49 + 6.31 GB) scaled to this "
+                                             "at 500 k pairs (profiles/ncu_full_capture2_kernel_r1_g.txt: 5.11 + 6.51 GB) scaled to this "
                                              "batch: scratch (2-bit pointers, boundary rows), not algorithmic bytes; the kernel is ALU bound",
                              "note": "12 algorithmic INT32 ops per DP cell x cells per step / CUDA-event time of hsq_extend_run "
                                      "(capture2_kernel + primer2_kernel are ~94%% of it, profiles/); peak = sustained INT32 issue rate measured in this run by "

@@ -257,6 +257,53 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
     score[1] = ((int)(final_d4 >> 16) - off) >> 2;
 }
 
+// A sequence view read element by element from its END towards its start through aligned 32-bit words: the word in use
+// and the next one in walking direction sit in registers, so the byte loads of the traceback (which miss L1 while other
+// warps stream their DP scratch through it) become one prefetched word load per four elements.
+struct CodeWalker {
+    const uint32_t* wp;  // aligned word holding the current element
+    uint32_t cur, nxt;
+    int sh;              // 8 * byte index of the current element inside cur
+    int dsh;             // +8 / -8: memory direction of the walk (= -8 * view step)
+    int comp;
+    // elements of the view still to be read after the ones in `cur`: a word is fetched only when it holds one of them
+    // (never touches memory before the first / after the last word of the view)
+    __device__ __forceinline__ bool more_after_cur(int remaining) const {
+        const int in_cur = (dsh > 0 ? (24 - sh) : sh) >> 3;  // further elements in cur, walking direction
+        return remaining - 1 > in_cur;
+    }
+    __device__ __forceinline__ void init(const SeqView& v, int remaining) {
+        comp = v.comp;
+        dsh = -8 * v.step;
+        cur = 0; nxt = 0; sh = 0; wp = nullptr;
+        if (remaining <= 0) return;
+        const uint8_t* p = v.base + v.start + (int64_t)(remaining - 1) * v.step;
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+        wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        sh = (int)(a & 3) * 8;
+        cur = *wp;
+        if (more_after_cur(remaining)) nxt = wp[dsh >> 3];
+    }
+    __device__ __forceinline__ uint32_t peek() const {  // code of the current element (garbage when none remains: unused)
+        const uint32_t c = (cur >> sh) & 0xFFu;
+        return comp ? (uint32_t)complement_code((uint8_t)c) : c;
+    }
+    // `remaining` counts the elements before this step consumes one
+    __device__ __forceinline__ void advance(int remaining) {
+        sh += dsh;
+        if ((uint32_t)sh > 24u) {  // left the word (sh == 32 or -8)
+            sh &= 31;
+            wp += dsh >> 3;
+            cur = nxt;
+            if (more_after_cur(remaining - 1)) nxt = wp[dsh >> 3];
+        }
+    }
+};
+
+// keeps a per-alignment invariant in ONE register (without it ptxas re-selects it from the two alignments at every step)
+__device__ __forceinline__ void pin(int& x) { asm volatile("" : "+r"(x)); }
+__device__ __forceinline__ void pin(uint32_t& x) { asm volatile("" : "+r"(x)); }
+
 // Streamed traceback of alignment `which` of the pair (NeedlemanWunschGlobalAlignment.java:85-114): walks from (Q,R) to
 // (0,0) and hands every column, LAST column first, to sink.push(ref code | qry code << 8) (CODE_GAP where the pointer
 // did not consume that sequence).  Pointer words come through a 16-column window in the thread's own profile slots.
@@ -264,47 +311,71 @@ template <class Sink>
 __device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView& qry, const DpScratch2& sc, int which, Sink& sink) {
     int i = qry.len, j = ref.len;
     int ws = -1, whi = 0;
-    uint2* win = reinterpret_cast<uint2*>(sc.prof + threadIdx.x);  // slot k at win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)]
-    const int shift = 16 * which;
+    // window slot k of this thread: shared address win_s + (k >> 1) * 16 * DP2_BLOCK + (k & 1) * 8
+    uint32_t win_s = (uint32_t)__cvta_generic_to_shared(sc.prof + threadIdx.x);
+    pin(win_s);
+    int shift = 16 * which;
+    pin(shift);
     const int64_t nt = sc.nthreads;
-    // running pointers at ref[j-1] / qry[i-1]: the codes this step may consume are fetched before the pointer is known
-    const uint8_t* rp = ref.base + ref.start + (int64_t)(j - 1) * ref.step;
-    const uint8_t* qp = qry.base + qry.start + (int64_t)(i - 1) * qry.step;
-    const int rstep = ref.step, qstep = qry.step;
-    const bool rcomp = ref.comp != 0, qcomp = qry.comp != 0;
+    CodeWalker rw, qw;
+    rw.init(ref, j);
+    qw.init(qry, i);
+    pin(rw.dsh); pin(rw.comp); pin(qw.dsh); pin(qw.comp);
     while (i > 0 || j > 0) {
-        uint32_t rraw = 0, qraw = 0;
-        if (j > 0) rraw = *rp;
-        if (i > 0) qraw = *qp;
         uint32_t p;
         if (i == 0) p = P_LEFT;
         else if (j == 0) p = P_UP;
         else {
-            const int s = (i - 1) / KROWS, r = (i - 1) % KROWS;
+            const int s = (int)((uint32_t)(i - 1) / KROWS), r = (int)((uint32_t)(i - 1) % KROWS);
             if (s != ws || j <= whi - TB_WINDOW) {
                 ws = s;
                 whi = j;
                 const uint2* g = &sc.word(s, j);
                 uint2 t[TB_WINDOW];
 #pragma unroll
-                for (int k = 0; k < TB_WINDOW; k++) t[k] = (j - k >= 1) ? __ldcs(g - (int64_t)k * nt) : make_uint2(0u, 0u);
+                for (int k = 0; k < TB_WINDOW; k++) {
+                    t[k] = (j - k >= 1) ? __ldcs(g) : make_uint2(0u, 0u);
+                    g -= nt;
+                }
 #pragma unroll
-                for (int k = 0; k < TB_WINDOW; k++) win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)] = t[k];
+                for (int k = 0; k < TB_WINDOW; k++)
+                    asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(win_s + (uint32_t)((k >> 1) * 16 * DP2_BLOCK + (k & 1) * 8)),
+                                 "r"(t[k].x), "r"(t[k].y)
+                                 : "memory");
             }
-            const int k = whi - j;
-            const uint2 w = win[(k >> 1) * 2 * DP2_BLOCK + (k & 1)];
+            const uint32_t k = (uint32_t)(whi - j);
+            uint2 w;
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(w.x), "=r"(w.y) : "r"(win_s + ((k >> 1) * (16 * DP2_BLOCK)) + ((k & 1u) * 8u)) : "memory");
             const int bit = 15 - r + shift;
             p = (((w.y >> bit) & 1u) << 1) | ((w.x >> bit) & 1u);
         }
+        const uint32_t rcc = rw.peek(), qcc = qw.peek();
+        if constexpr (Sink::HAS_FAST) {
+            // the common step: a diagonal move over two equal bases while the sink is inside a run of matches
+            if (p == P_DIAG && rcc == qcc && rcc != CODE_GAP && sink.fast_ready()) {
+                sink.fast_match();
+                rw.advance(j);
+                qw.advance(i);
+                i--;
+                j--;
+                continue;
+            }
+            // columns after the last query base (they come first here) are not part of the reported alignment
+            if (p == P_LEFT && sink.drops_query_gaps()) {
+                rw.advance(j);
+                j--;
+                continue;
+            }
+        }
         uint32_t rc = CODE_GAP, qc = CODE_GAP;
         if (p != P_UP) {
-            rc = rcomp ? complement_code((uint8_t)rraw) : rraw;
-            rp -= rstep;
+            rc = rcc;
+            rw.advance(j);
             j--;
         }
         if (p != P_LEFT) {
-            qc = qcomp ? complement_code((uint8_t)qraw) : qraw;
-            qp -= qstep;
+            qc = qcc;
+            qw.advance(i);
             i--;
         }
         sink.push(rc | (qc << 8));

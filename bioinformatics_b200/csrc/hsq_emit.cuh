@@ -172,6 +172,18 @@ struct CigarMdStream {
         started = false;
         nm = 0; ref_len = 0; run_ch = 0; run_n = 0; last_entry = 0; match_count = 0; prev_op = 0;
     }
+    // fast paths of the packed traceback.  A '=' column that extends an 'M' run (the previous column was '=' or 'X') only
+    // moves counters; a column without a query base before the first query base is dropped (see `started`).
+    static constexpr bool HAS_FAST = true;
+    __device__ inline bool fast_ready() const { return run_ch == 'M'; }
+    __device__ inline void fast_match() {
+        ref_len++;
+        run_n++;
+        match_count = (last_entry == 1) ? match_count + 1 : 1;
+        last_entry = 1;
+        prev_op = '=';
+    }
+    __device__ inline bool drops_query_gaps() const { return !started; }
     __device__ inline void flush_run() {
         if (run_n > 0) {
             if (back) { cw.put(run_ch); cw.put_int(run_n); }

@@ -97,6 +97,7 @@ __device__ inline DpScratch thread_scratch(const ScratchPool& pool, int4* prof) 
 // The scan of getPrimerEndIndexInRead (HSQ/process/ExtendReadsToPrimer.java:305-343) as a traceback sink: columns arrive
 // last-first, which is the order of the reversed alignments the reference walks (i = 0 is the last column).
 struct PrimerGateSink {
+    static constexpr bool HAS_FAST = false;
     bool passed = false;
     int pe = 0, first = -1, i = 0;
     double w = 0.0;
