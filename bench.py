@@ -228,7 +228,7 @@ def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
     return out
 
 
-def run_reference(args):
+def run_reference(args, out_stream):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -258,13 +258,23 @@ def run_reference(args):
                              "sample": "%d read pairs per step; C++ restatement of the reference algorithm (no JVM in the image)" % sub.n},
             "e2e": {"value": v, "unit": "GCUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "read_pairs_per_s": sub.n / dt}
-    print(json.dumps(line))
+    print(json.dumps(line), file=out_stream, flush=True)
+
+
+def claim_stdout():
+    """The contract is ONE JSON line on stdout, but libraries write there too (NCCL prints its version banner to stdout).
+    Everything written to fd 1 from here on goes to stderr; the returned file object is the real stdout."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
 
 
 def main():
     args = parse()
+    out_stream = claim_stdout()
     if args.impl == "reference":
-        return run_reference(args)
+        return run_reference(args, out_stream)
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -430,7 +440,7 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), file=out_stream, flush=True)
 
 
 if __name__ == "__main__":

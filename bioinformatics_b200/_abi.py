@@ -132,6 +132,9 @@ class SeqBatch:
     def take(self, idx):
         """Ragged gather: the strings idx[0], idx[1], ... as a new batch (vectorised)."""
         idx = np.asarray(idx, dtype=np.int64)
+        if self.n > 0 and len(self.data) == self.n * int(self.offsets[1]) and (np.diff(self.offsets) == self.offsets[1]).all():
+            L = int(self.offsets[1])  # equal lengths: a row gather
+            return SeqBatch(self.data.reshape(self.n, L)[idx].reshape(-1), np.arange(len(idx) + 1, dtype=np.int64) * L)
         lens = (self.offsets[1:] - self.offsets[:-1])[idx]
         offsets = np.zeros(len(idx) + 1, dtype=np.int64)
         np.cumsum(lens, out=offsets[1:])
