@@ -207,11 +207,12 @@ def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
         else:
             def task():
                 b, _, _ = sharded.dedup_sharded(be, pairs, UID, 0, probes.n)
-                idx = np.arange(pairs.n) if mark else np.nonzero(b)[0]
-                sub = pairs if mark else pairs.subset(idx)
-                r = ctx.extend_batch(sub, CIGAR_CAP, MD_CAP, out=res.extend if mark else None)
-                return len(idx), int(r.pair_ok.sum())
-            mode = "sharded dedup over NCCL, then hsq_extend_batch on each rank's own surviving pairs"
+                if mark:
+                    r = ctx.extend_batch(pairs, CIGAR_CAP, MD_CAP, out=res.extend)
+                    return pairs.n, int(r.pair_ok.sum())
+                m, _, r = ctx.extend_selected(pairs, b, CIGAR_CAP, MD_CAP, out=res.extend, extended_pair=res.extended_pair)
+                return m, int(r.pair_ok[:m].sum())
+            mode = "sharded dedup over NCCL, then hsq_extend_selected (hsq_extend_batch with duplicates) on each rank's own pairs"
         task()
         barrier()
         t0 = time.perf_counter()

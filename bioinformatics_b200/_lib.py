@@ -20,7 +20,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
-           "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records")
+           "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected")
 
 
 class HsqError(RuntimeError):
@@ -158,6 +158,18 @@ class Context:
         out.finish()
         self._check(st)
         return out
+
+    def extend_selected(self, pairs: PairBatchHost, keep, cigar_cap=32, md_cap=48, out=None, extended_pair=None):
+        """hsq_extend_selected: extend only the pairs with keep[k] != 0; returns (n_extended, extended_pair, ExtendResult)."""
+        out = out or ExtendResult(pairs.n, cigar_cap, md_cap)
+        keep = np.ascontiguousarray(keep, dtype=np.uint8)
+        lst = extended_pair if extended_pair is not None else np.zeros(pairs.n, dtype=np.int32)
+        m = C.c_int64(0)
+        pc, oc = pairs.c(), out.c()
+        st = self.lib.hsq_extend_selected(self.h, C.byref(pc), A.ptr(keep, A.u8p), C.byref(m), A.ptr(lst, A.i32p), C.byref(oc))
+        out.finish()
+        self._check(st)
+        return int(m.value), lst, out
 
     def extend_records(self, pairs: PairBatchHost, ext: ExtendResult, duplicate=None, out_cap=None):
         """hsq_extend_records: FLAG / PNEXT / read string / qualities of the records of the pairs `ext` extended."""

@@ -206,3 +206,55 @@ extern "C" int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pa
     int rc2 = timer.finish();
     return rc ? rc : rc2;
 }
+
+// ExtendReadsToPrimer.extendReadsToPrimers on the pairs the caller flags (keep[k] != 0) -- e.g. the unique pairs of a dedup
+// that ran elsewhere (sharded over several GPUs): same upload-once / compact-on-device path as hsq_dedup_extend_batch.
+extern "C" int32_t hsq_extend_selected(hsq_ctx* ctx, const hsq_pair_batch* pairs, const uint8_t* keep, int64_t* n_extended,
+                                       int32_t* extended_pair, hsq_extend_out* out) {
+    if (!ctx || !pairs || !n_extended || !extended_pair || !out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (pairs->n < 0 || pairs->r1.n != pairs->n || pairs->r2.n != pairs->n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
+    if (pairs->n > 0 && !keep) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null keep flags");
+    if (pairs->n >= (1ll << 31)) return fail(ctx, HSQ_ERR_UNSUPPORTED, "more than 2^31 pairs in one batch");
+    if (out->cigar_cap < 0 || out->md_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
+    int rc = extend_args_ok(ctx);
+    if (rc) return rc;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    const int64_t n = pairs->n;
+    const size_t nn = (size_t)n;
+    *n_extended = 0;
+    auto run = [&]() -> int {
+        int rc;
+        if ((rc = reset_status(ctx))) return rc;
+        if ((rc = upload_pairs_raw(ctx, pairs))) return rc;
+        HSQ_CUDA(ctx, ctx->dd_u8.ensure(nn + 32));
+        HSQ_CUDA(ctx, ctx->dd_i32.ensure(nn * 4 + 16));
+        uint8_t* d_keep = ctx->dd_u8.as<uint8_t>();
+        int32_t* d_list = ctx->dd_i32.as<int32_t>();
+        int64_t m = 0;
+        if (n > 0) {
+            HSQ_CUDA(ctx, cudaMemcpyAsync(d_keep, keep, nn, cudaMemcpyHostToDevice, ctx->stream));
+            const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+            check_probe_ids_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, ctx->n_probes, d_status(ctx));
+            ctx->launches++;
+            if ((rc = compact_survivors(ctx, n, d_keep, d_list, &m))) return rc;  // synchronises: the status word is final
+            int w[1];
+            if ((rc = read_status(ctx, w, 1))) return rc;
+            if (w[0] != 0) return fail(ctx, w[0], "hsq_extend_selected: probe_id out of range");
+            swap_read_buffers(ctx);
+        }
+        if ((rc = d2h(ctx, extended_pair, d_list, (size_t)m))) return rc;
+        ctx->ext_n = m;
+        ctx->keep_counters = false;
+        rc = extend_run(ctx, out->cigar_cap, out->md_cap);
+        if (!rc) rc = extend_fetch(ctx, out);
+        if (n > 0) swap_read_buffers(ctx);
+        ctx->ext_n = -1;
+        ctx->ext_ran = false;
+        if (!rc) *n_extended = m;
+        return rc;
+    };
+    rc = run();
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}

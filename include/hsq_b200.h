@@ -295,6 +295,12 @@ int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_
 int32_t hsq_extend_records(hsq_ctx* ctx, const hsq_pair_batch* pairs, const hsq_extend_out* ext, const uint8_t* duplicate,
                            hsq_record_out* out, int64_t out_cap);
 
+/* ExtendReadsToPrimer.extendReadsToPrimers on the pairs with keep[k] != 0 only (e.g. the unique pairs of a dedup whose
+ * reduction ran sharded over several GPUs): the batch is uploaded once, the flagged pairs are compacted on the device and
+ * extended; slot j of `out` (sized for n pairs) belongs to pair extended_pair[j], j < *n_extended. */
+int32_t hsq_extend_selected(hsq_ctx* ctx, const hsq_pair_batch* pairs, const uint8_t* keep, int64_t* n_extended,
+                            int32_t* extended_pair, hsq_extend_out* out);
+
 /* mergeSequences per item (…Identification.java:1362-1552, behind the unregistered --mergePairs option): lead + overlap
  * (per position the base with the higher quality wins, ties to upstream; a gap is filled with N / '!') + trail.
  * out_offsets gets n+1 entries; out_seq/out_qual have out_cap bytes: when the merged total is larger the call returns

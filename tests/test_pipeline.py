@@ -65,6 +65,31 @@ def test_dedup_extend_vs_oracle(extend_duplicates, n_pairs, read_len, u, v):
 
 
 @pytest.mark.gpu
+def test_extend_selected_vs_oracle():
+    from bioinformatics_b200._lib import Context, HsqError
+    probes = synth.make_probes(80, seed=21)
+    pairs = synth.make_pairs(probes, 4000, read_len=150, ext_uid_len=8, seed=22, sub_rate=0.02, ins_rate=0.003, del_rate=0.003)
+    rng = np.random.default_rng(23)
+    keep = (rng.random(pairs.n) < 0.3).astype(np.uint8)
+    idx = np.nonzero(keep)[0]
+    want = O.extend_batch(probes, pairs.subset(idx), cigar_cap=64, md_cap=96, nthreads=8)
+    with Context(0) as ctx:
+        ctx.set_probes(probes)
+        ctx.set_scorer(scorer())
+        m, lst, got = ctx.extend_selected(pairs, keep, cigar_cap=64, md_cap=96)
+        assert m == len(idx) and (lst[:m] == idx).all()
+        H.assert_extend_equal(got.head(m), want)
+        m, lst, got = ctx.extend_selected(pairs, np.zeros(pairs.n, dtype=np.uint8), cigar_cap=64, md_cap=96)
+        assert m == 0
+        m, lst, got = ctx.extend_selected(pairs, np.ones(pairs.n, dtype=np.uint8), cigar_cap=64, md_cap=96)
+        H.assert_extend_equal(got, O.extend_batch(probes, pairs, cigar_cap=64, md_cap=96, nthreads=8))
+        bad = pairs.subset(np.arange(10))
+        bad.probe_id[3] = 999
+        with pytest.raises(HsqError):
+            ctx.extend_selected(bad, np.ones(10, dtype=np.uint8))
+
+
+@pytest.mark.gpu
 def test_dedup_extend_empty_and_all_duplicates():
     from bioinformatics_b200._lib import Context
     probes = synth.make_probes(10, seed=1)
