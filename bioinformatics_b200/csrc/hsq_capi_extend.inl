@@ -244,10 +244,28 @@ int host_chunk_dims(hsq_ctx* ctx, const hsq_pair_batch& w, int* read_max) {
 // their kernels on different streams, so the tail of one chunk's last kernel overlaps the first kernels of the next.
 int extend_pipelined(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o, int n_chunks) {
     const int64_t n = pb->n;
-    const int64_t per = (n + n_chunks - 1) / n_chunks;
+    // chunk sizes ramp up and down (weights 1,2,4,.. towards the middle): the first H2D and the last D2H are the only copies
+    // that nothing overlaps, so the edge chunks are small and the middle ones large (fewer kernel boundaries)
+    std::vector<int64_t> starts((size_t)n_chunks + 1, 0);
+    {
+        std::vector<double> wgt((size_t)n_chunks);
+        double total = 0;
+        const bool ramp = getenv("HSQ_EXTEND_UNIFORM_CHUNKS") == nullptr;
+        for (int c = 0; c < n_chunks; c++) {
+            const int edge = std::min(c, n_chunks - 1 - c);
+            wgt[(size_t)c] = ramp ? (double)(1 << std::min(edge, 3)) : 1.0;
+            total += wgt[(size_t)c];
+        }
+        double acc = 0;
+        for (int c = 0; c < n_chunks; c++) {
+            acc += wgt[(size_t)c];
+            starts[(size_t)c + 1] = std::min<int64_t>(n, (int64_t)((double)n * acc / total + 0.5));
+        }
+        starts[(size_t)n_chunks] = n;
+    }
     int rc = HSQ_OK;
     auto chunk_in = [&](int c) {
-        const int64_t a = (int64_t)c * per, m = std::min(per, n - a);
+        const int64_t a = starts[(size_t)c], m = starts[(size_t)c + 1] - a;
         hsq_pair_batch w = *pb;
         w.n = m;
         w.probe_id = pb->probe_id + a;
@@ -257,7 +275,7 @@ int extend_pipelined(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o, 
         return w;
     };
     auto chunk_out = [&](int c) {
-        const int64_t a = (int64_t)c * per;
+        const int64_t a = starts[(size_t)c];
         hsq_extend_out w = *o;
         int32_t** f32[9] = {&w.primer_end, &w.score, &w.pos, &w.read_start, &w.read_stop, &w.nm, &w.tlen, &w.cigar_len, &w.md_len};
         for (auto f : f32) if (*f) *f += 2 * a;
