@@ -137,10 +137,16 @@ int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) {
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev_user1));
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
-    for (int k = 0; k < 2; k++) {
-        HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_comp[k], cudaStreamNonBlocking));
+    {   // the prep stream's short kernels should get SM slots ahead of the capture kernels' CTAs
+        int lo = 0, hi = 0;
+        HSQ_CUDA(nullptr, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+        HSQ_CUDA(nullptr, cudaStreamCreateWithPriority(&ctx->s_prep, cudaStreamNonBlocking, hi));
+    }
+    for (int k = 0; k < 2; k++) HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_cap[k], cudaStreamNonBlocking));
+    for (int k = 0; k < hsq_ctx::N_EXTEND_SETS; k++) {
         HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_in[k], cudaEventDisableTiming));
-        HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_comp[k], cudaEventDisableTiming));
+        HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_prep[k], cudaEventDisableTiming));
+        HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_cap[k], cudaEventDisableTiming));
         HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_out[k], cudaEventDisableTiming));
     }
     HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_status, 64));
@@ -161,25 +167,32 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     hsq::DevBuf* bufs[] = {&ctx->p_rev, &ctx->p_ext_start, &ctx->p_ext_stop, &ctx->p_lig_start, &ctx->p_lig_stop, &ctx->q1, &ctx->q2,
                            &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
                            &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
-                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->alt_out_i32,
-                           &ctx->alt_out_u8, &ctx->alt_out_slots, &ctx->alt_pair_ok, &ctx->alt_ptr_words, &ctx->alt_brow, &ctx->alt_cols,
-                           &ctx->alt_colinfo, &ctx->alt_slow, &ctx->alt_sort_a, &ctx->alt_sort_b, &ctx->alt_sort_c, &ctx->rg_start, &ctx->rg_end,
+                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->rg_start, &ctx->rg_end,
                            &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32};
     for (auto* b : bufs) b->release();
     hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb, &ctx->alt_r1, &ctx->alt_r2};
     for (auto* s : seqs) s->release();
+    for (auto& ps : ctx->parked) {
+        hsq::DevBuf* pb[] = {&ps.probe_id, &ps.out_i32, &ps.out_u8, &ps.out_slots, &ps.pair_ok, &ps.ptr_words, &ps.brow, &ps.cols, &ps.colinfo,
+                             &ps.slow, &ps.sort_a, &ps.sort_b, &ps.sort_c};
+        for (auto* b : pb) b->release();
+        ps.r1.release();
+        ps.r2.release();
+    }
     cudaFreeHost(ctx->h_status);
     cudaFreeHost(ctx->h_cells);
     cudaEventDestroy(ctx->ev0);
     cudaEventDestroy(ctx->ev1);
     cudaEventDestroy(ctx->ev_user0);
     cudaEventDestroy(ctx->ev_user1);
-    for (int k = 0; k < 2; k++) {
+    for (int k = 0; k < hsq_ctx::N_EXTEND_SETS; k++) {
         cudaEventDestroy(ctx->ev_in[k]);
-        cudaEventDestroy(ctx->ev_comp[k]);
+        cudaEventDestroy(ctx->ev_prep[k]);
+        cudaEventDestroy(ctx->ev_cap[k]);
         cudaEventDestroy(ctx->ev_out[k]);
-        cudaStreamDestroy(ctx->s_comp[k]);
     }
+    for (int k = 0; k < 2; k++) cudaStreamDestroy(ctx->s_cap[k]);
+    cudaStreamDestroy(ctx->s_prep);
     cudaStreamDestroy(ctx->s_in);
     cudaStreamDestroy(ctx->s_out);
     cudaStreamDestroy(ctx->stream);

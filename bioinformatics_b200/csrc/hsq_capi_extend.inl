@@ -29,10 +29,31 @@ int extend_stage(hsq_ctx* ctx, const hsq_pair_batch* pb) {
     return HSQ_OK;
 }
 
-// run: encode + DP + finalize on the staged batch; results stay on the device.
+// What the capture phase of a staged batch needs from its prep phase (raw device pointers of the buffer set that was active
+// during prep: the capture phase may run while another set is the active one).
+struct ExtendPlan {
+    int64_t n = 0;
+    bool packed2 = false;
+    int grid2 = 1;
+    DeviceProbes pv;
+    const int32_t* pid = nullptr;
+    DeviceSeqs v1, v2;
+    const uint32_t* order = nullptr;
+    const uint32_t* n_active = nullptr;
+    ScoreParams sp_user;
+    ScoreParams2 sp_user2;
+    ScratchPool pool;
+    ScratchPool2 pool2;
+    ExtendDeviceOut d;
+    uint8_t* pair_ok = nullptr;
+    unsigned long long* cells = nullptr;
+    unsigned long long* work = nullptr;
+};
+
+// prep: encode + primer DP + the two bucket sorts of the staged batch, on ctx->stream.
 // host_read_max < 0: the longest read and the probe-id check come from the device (one synchronisation);
 // host_read_max >= 0: the caller measured the reads and validated the probe ids on the host, nothing here blocks.
-int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max = -1) {
+int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, ExtendPlan* plan) {
     const int64_t n = ctx->ext_n;
     if (n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "no staged batch");
     const size_t n2 = (size_t)(2 * n);
@@ -142,21 +163,54 @@ int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max = -1) 
         } else {
             primer_kernel<<<grid1, DP_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, n, sp_default, pool, d, keys, d_status(ctx), cells);
         }
+        ctx->launches++;
         if ((rc = bucket_sort(n_keys, keys.skip_key))) return rc;
-        if (packed2) {
-            if (!packed1) HSQ_CUDA(ctx, cudaMemsetAsync(work, 0, 16, ctx->stream));
-            capture2_kernel<<<grid2, DP2_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_user2, pool2, d, cells, work + 1);
-        }
-        else capture_kernel<<<grid2, DP_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_user, pool, d, cells);
-        ctx->launches += 2;
+        if (packed2 && !packed1) HSQ_CUDA(ctx, cudaMemsetAsync(work, 0, 16, ctx->stream));
         HSQ_CUDA(ctx, cudaGetLastError());
-        finalize_extend_kernel<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(pv, ctx->probe_id.as<int32_t>(), n, d,
-                                                                                     ctx->pair_ok.as<uint8_t>(), d_status(ctx));
+        plan->pv = pv;
+        plan->pid = pid;
+        plan->v1 = v1;
+        plan->v2 = v2;
+        plan->order = order;
+        plan->n_active = n_active;
+        plan->cells = cells;
+        plan->work = work;
+    }
+    plan->n = n;
+    plan->packed2 = packed2;
+    plan->grid2 = grid2;
+    plan->sp_user = sp_user;
+    plan->sp_user2 = sp_user2;
+    plan->pool = pool;
+    plan->pool2 = pool2;
+    plan->d = d;
+    plan->pair_ok = ctx->pair_ok.as<uint8_t>();
+    return HSQ_OK;
+}
+
+// capture: the capture-target DP of the read ends that passed the primer stage + the per-pair finalize, on ctx->stream
+int extend_capture(hsq_ctx* ctx, const ExtendPlan& p) {
+    if (p.n > 0) {
+        if (p.packed2)
+            capture2_kernel<<<p.grid2, DP2_BLOCK, 0, ctx->stream>>>(p.pv, p.pid, p.v1, p.v2, p.order, p.n_active, p.sp_user2, p.pool2, p.d, p.cells, p.work + 1);
+        else
+            capture_kernel<<<p.grid2, DP_BLOCK, 0, ctx->stream>>>(p.pv, p.pid, p.v1, p.v2, p.order, p.n_active, p.sp_user, p.pool, p.d, p.cells);
+        ctx->launches++;
+        HSQ_CUDA(ctx, cudaGetLastError());
+        finalize_extend_kernel<<<(unsigned)((p.n + 255) / 256), 256, 0, ctx->stream>>>(p.pv, p.pid, p.n, p.d, p.pair_ok, d_status(ctx));
         ctx->launches++;
         HSQ_CUDA(ctx, cudaGetLastError());
     }
-    ctx->ext_ran = true;
     return HSQ_OK;
+}
+
+// run: prep + capture of the staged batch on one stream; results stay on the device.
+int extend_run(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max = -1) {
+    ExtendPlan plan;
+    int rc = extend_prep(ctx, cigar_cap, md_cap, host_read_max, &plan);
+    if (!rc) rc = extend_capture(ctx, plan);
+    if (!rc) ctx->ext_ran = true;
+    return rc;
 }
 
 // fetch, part 1: device -> host copies of the results of the last run (asynchronous, on the context's copy stream)
@@ -197,23 +251,32 @@ int extend_fetch(hsq_ctx* ctx, hsq_extend_out* o) {
     return rc ? rc : extend_fetch_finish(ctx, o);
 }
 
-// The extend-batch buffers exist twice; a chunked call alternates between the two sets.
-void swap_extend_buffers(hsq_ctx* ctx) {
-    std::swap(ctx->r1, ctx->alt_r1);
-    std::swap(ctx->r2, ctx->alt_r2);
-    std::swap(ctx->probe_id, ctx->alt_probe_id);
-    std::swap(ctx->out_i32, ctx->alt_out_i32);
-    std::swap(ctx->out_u8, ctx->alt_out_u8);
-    std::swap(ctx->out_slots, ctx->alt_out_slots);
-    std::swap(ctx->pair_ok, ctx->alt_pair_ok);
-    std::swap(ctx->ptr_words, ctx->alt_ptr_words);
-    std::swap(ctx->brow, ctx->alt_brow);
-    std::swap(ctx->cols, ctx->alt_cols);
-    std::swap(ctx->colinfo, ctx->alt_colinfo);
-    std::swap(ctx->slow, ctx->alt_slow);
-    std::swap(ctx->sort_a, ctx->alt_sort_a);
-    std::swap(ctx->sort_b, ctx->alt_sort_b);
-    std::swap(ctx->sort_c, ctx->alt_sort_c);
+// The extend-batch buffers exist three times; the members of hsq_ctx hold the active set, the others are parked.
+void swap_extend_set(hsq_ctx* ctx, hsq_ctx::ExtendSet& st) {
+    std::swap(ctx->r1, st.r1);
+    std::swap(ctx->r2, st.r2);
+    std::swap(ctx->probe_id, st.probe_id);
+    std::swap(ctx->out_i32, st.out_i32);
+    std::swap(ctx->out_u8, st.out_u8);
+    std::swap(ctx->out_slots, st.out_slots);
+    std::swap(ctx->pair_ok, st.pair_ok);
+    std::swap(ctx->ptr_words, st.ptr_words);
+    std::swap(ctx->brow, st.brow);
+    std::swap(ctx->cols, st.cols);
+    std::swap(ctx->colinfo, st.colinfo);
+    std::swap(ctx->slow, st.slow);
+    std::swap(ctx->sort_a, st.sort_a);
+    std::swap(ctx->sort_b, st.sort_b);
+    std::swap(ctx->sort_c, st.sort_c);
+    std::swap(ctx->ext_out, st.ext_out);
+    std::swap(ctx->ext_n, st.ext_n);
+}
+
+void activate_extend_set(hsq_ctx* ctx, int k) {
+    if (ctx->active_set == k) return;
+    swap_extend_set(ctx, ctx->parked[ctx->active_set]);  // park the current members
+    swap_extend_set(ctx, ctx->parked[k]);                // load set k
+    ctx->active_set = k;
 }
 
 hsq_seqs seqs_window(const hsq_seqs& s, int64_t a, int64_t n) {
@@ -239,11 +302,15 @@ int host_chunk_dims(hsq_ctx* ctx, const hsq_pair_batch& w, int* read_max) {
     return HSQ_OK;
 }
 
-// hsq_extend_batch for a large batch: chunks flow through  H2D (s_in) | kernels (s_comp[chunk & 1]) | D2H (s_out)  with
-// two complete buffer sets.  The host never blocks inside the loop; events order the streams.  Even and odd chunks run
-// their kernels on different streams, so the tail of one chunk's last kernel overlaps the first kernels of the next.
+// hsq_extend_batch for a large batch: chunks flow through
+//     H2D (s_in) | prep: encode, primer DP, bucket sorts (s_prep) | capture DP (s_cap[chunk & 1]) | D2H (s_out)
+// with three complete buffer sets, so that three chunks are in flight: while the capture kernel of chunk c runs, the prep
+// of chunk c+1 is already done and chunk c+2 is being copied / prepared.  When a capture kernel drains, the next one is
+// ready to take the freed SMs at once (no chain of small kernels in between), and its tail overlaps that start because
+// consecutive capture kernels sit on different streams.  The host never blocks inside the loop; events order the streams.
 int extend_pipelined(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o, int n_chunks) {
     const int64_t n = pb->n;
+    constexpr int NS = hsq_ctx::N_EXTEND_SETS;
     // chunk sizes ramp up and down (weights 1,2,4,.. towards the middle): the first H2D and the last D2H are the only copies
     // that nothing overlaps, so the edge chunks are small and the middle ones large (fewer kernel boundaries)
     std::vector<int64_t> starts((size_t)n_chunks + 1, 0);
@@ -290,48 +357,64 @@ int extend_pipelined(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o, 
     ctx->keep_counters = false;
     if ((rc = reset_status(ctx))) return rc;
     HSQ_CUDA(ctx, cudaStreamSynchronize(main_stream));  // counters are zero before any other stream touches them
-    int n_swaps = 0;
+    const int home_set = ctx->active_set;
+    // the capture phase of chunk c is issued after the prep of chunk c+1, so that the prep stream always runs one chunk ahead
+    std::vector<ExtendPlan> plans((size_t)n_chunks);
+    auto issue_capture = [&](int c) -> int {
+        const int k = c % NS;
+        cudaStream_t st = ctx->s_cap[c & 1];
+        HSQ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_prep[k], 0));
+        ctx->stream = st;
+        int r = extend_capture(ctx, plans[(size_t)c]);
+        ctx->stream = main_stream;
+        if (r) return r;
+        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_cap[k], st));
+        // D2H of this chunk's results
+        HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_out, ctx->ev_cap[k], 0));
+        activate_extend_set(ctx, k);
+        ctx->ext_ran = true;
+        ctx->io = ctx->s_out;
+        hsq_extend_out wo = chunk_out(c);
+        r = extend_fetch_copies(ctx, &wo);
+        ctx->io = nullptr;
+        if (r) return r;
+        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_out[k], ctx->s_out));
+        return HSQ_OK;
+    };
     for (int c = 0; c < n_chunks && !rc; c++) {
-        const int slot = c & 1;
+        const int k = c % NS;
         hsq_pair_batch in = chunk_in(c);
         int read_max = 0;
         if ((rc = host_chunk_dims(ctx, in, &read_max))) break;
-        // H2D into this slot's inputs once the chunk that used them before (c-2) has run
-        if (c >= 2) HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_in, ctx->ev_comp[slot], 0));
+        activate_extend_set(ctx, k);
+        // H2D into this set once the chunk that used it before (c - NS) has delivered its results
+        if (c >= NS) HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_in, ctx->ev_out[k], 0));
         ctx->io = ctx->s_in;
-        if ((rc = extend_stage(ctx, &in))) break;
-        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_in[slot], ctx->s_in));
-        // kernels on this slot's stream, after its inputs arrived and its previous results left
-        ctx->stream = ctx->s_comp[slot];
-        ctx->work_slot = slot;
-        cudaError_t e1 = cudaStreamWaitEvent(ctx->stream, ctx->ev_in[slot], 0);
-        cudaError_t e2 = c >= 2 ? cudaStreamWaitEvent(ctx->stream, ctx->ev_out[slot], 0) : cudaSuccess;
-        rc = extend_run(ctx, o->cigar_cap, o->md_cap, read_max);
-        cudaError_t e3 = cudaEventRecord(ctx->ev_comp[slot], ctx->stream);
+        rc = extend_stage(ctx, &in);
+        ctx->io = nullptr;
+        if (rc) break;
+        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_in[k], ctx->s_in));
+        // prep on the prep stream
+        HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_prep, ctx->ev_in[k], 0));
+        ctx->stream = ctx->s_prep;
+        ctx->work_slot = k;
+        rc = extend_prep(ctx, o->cigar_cap, o->md_cap, read_max, &plans[(size_t)c]);
         ctx->stream = main_stream;
         ctx->work_slot = 0;
         if (rc) break;
-        HSQ_CUDA(ctx, e1);
-        HSQ_CUDA(ctx, e2);
-        HSQ_CUDA(ctx, e3);
-        // D2H of this chunk's results
-        HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_out, ctx->ev_comp[slot], 0));
-        ctx->io = ctx->s_out;
-        hsq_extend_out wo = chunk_out(c);
-        if ((rc = extend_fetch_copies(ctx, &wo))) break;
-        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_out[slot], ctx->s_out));
-        swap_extend_buffers(ctx);
-        n_swaps++;
+        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_prep[k], ctx->s_prep));
+        if (c >= 1) rc = issue_capture(c - 1);
     }
+    if (!rc) rc = issue_capture(n_chunks - 1);
     // everything joins the main stream, which then reads the counters
-    for (int k = 0; k < 2; k++) {
-        cudaStreamSynchronize(ctx->s_comp[k]);
-    }
+    cudaStreamSynchronize(ctx->s_prep);
+    for (int k = 0; k < 2; k++) cudaStreamSynchronize(ctx->s_cap[k]);
     cudaStreamSynchronize(ctx->s_in);
     cudaStreamSynchronize(ctx->s_out);
-    if (n_swaps & 1) swap_extend_buffers(ctx);  // leave the primary set in place
+    activate_extend_set(ctx, home_set);
     ctx->io = nullptr;
     int rc2 = rc ? HSQ_OK : extend_fetch_finish(ctx, o);
+    for (auto& ps : ctx->parked) ps.ext_n = -1;
     ctx->ext_n = -1;  // no single staged batch remains
     ctx->ext_ran = false;
     return rc ? rc : rc2;
@@ -352,8 +435,8 @@ extern "C" int32_t hsq_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, h
     if (pairs->n < 0 || out->cigar_cap < 0 || out->md_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
-    // chunks of >= 256 k pairs, at most 8 (HSQ_EXTEND_CHUNKS overrides; 1 = no pipelining)
-    int n_chunks = (int)std::min<int64_t>(8, pairs->n / 262144);
+    // chunks of >= 256 k pairs on average, at most 12 (HSQ_EXTEND_CHUNKS overrides; 1 = no pipelining)
+    int n_chunks = (int)std::min<int64_t>(12, pairs->n / 262144);
     if (const char* e = getenv("HSQ_EXTEND_CHUNKS")) n_chunks = atoi(e);
     if (n_chunks > 1 && pairs->n >= n_chunks) {
         rc = extend_pipelined(ctx, pairs, out, n_chunks);

@@ -69,15 +69,25 @@ struct hsq_ctx {
     hsq::DevBuf dd_u8, dd_i32;  // hsq_dedup_extend_batch: dedup answers kept while the extend stage reuses the output buffers
     int64_t rg_n = -1;
     int32_t rg_contigs = 0;
-    // second set of extend-batch buffers + copy streams: hsq_extend_batch pipelines chunks (H2D | kernels | D2H)
-    hsq::DevSeqsOwned alt_r1, alt_r2;
-    hsq::DevBuf alt_probe_id, alt_out_i32, alt_out_u8, alt_out_slots, alt_pair_ok;
-    hsq::DevBuf alt_ptr_words, alt_brow, alt_cols, alt_colinfo, alt_slow, alt_sort_a, alt_sort_b, alt_sort_c;
-    cudaStream_t s_comp[2] = {nullptr, nullptr};  // kernels of even / odd chunks (their tails overlap the next chunk's start)
-    int work_slot = 0;                            // which pair of work counters the packed kernels of this run use
+    // hsq_extend_batch pipelines chunks through  H2D | prep (encode, primer DP, bucket sorts) | capture DP | D2H  with three
+    // complete buffer sets; the two sets not in the members above are parked here (see activate_extend_set)
+    struct ExtendSet {
+        hsq::DevSeqsOwned r1, r2;
+        hsq::DevBuf probe_id, out_i32, out_u8, out_slots, pair_ok, ptr_words, brow, cols, colinfo, slow, sort_a, sort_b, sort_c;
+        hsq::ExtendDeviceOut ext_out{};
+        int64_t ext_n = -1;
+    };
+    static constexpr int N_EXTEND_SETS = 3;
+    ExtendSet parked[N_EXTEND_SETS];
+    int active_set = 0;
+    hsq::DevSeqsOwned alt_r1, alt_r2;  // destination of the device-side compaction (hsq_dedup_extend_batch)
+    hsq::DevBuf alt_probe_id;
+    cudaStream_t s_cap[2] = {nullptr, nullptr};  // capture kernels of even / odd chunks (a tail overlaps the next start)
+    cudaStream_t s_prep = nullptr;               // everything before the capture kernel, one chunk ahead
+    int work_slot = 0;                           // which pair of work counters the packed kernels of this run use
     cudaStream_t io = nullptr;      // stream the host<->device copies of the current call go to (default: stream)
     cudaStream_t s_in = nullptr, s_out = nullptr;
-    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_comp[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+    cudaEvent_t ev_in[N_EXTEND_SETS] = {}, ev_prep[N_EXTEND_SETS] = {}, ev_cap[N_EXTEND_SETS] = {}, ev_out[N_EXTEND_SETS] = {};
     bool keep_counters = false;     // chunks after the first: keep the cell counter and the overflow flag
     int64_t ext_n = -1;  // staged extend batch
     bool ext_ran = false;
