@@ -46,6 +46,24 @@ public final class HsqB200 implements AutoCloseable {
     static final StructLayout PROBE_STATS = MemoryLayout.structLayout(JAVA_LONG.withName("n_probes"), ADDRESS.withName("unique_pairs"),
             ADDRESS.withName("duplicate_pairs"), ADDRESS.withName("max_pairs_per_uid"));
 
+    static final StructLayout PROBE_RANGES = MemoryLayout.structLayout(JAVA_LONG.withName("n"), ADDRESS.withName("contig"),
+            ADDRESS.withName("reverse_strand"), ADDRESS.withName("start"), ADDRESS.withName("stop"));
+    static final StructLayout MAPPED_RECORDS = MemoryLayout.structLayout(JAVA_LONG.withName("n"), ADDRESS.withName("contig"),
+            ADDRESS.withName("negative_strand"), ADDRESS.withName("second_of_pair"), ADDRESS.withName("start"), ADDRESS.withName("end"),
+            ADDRESS.withName("read_index"), ADDRESS.withName("alt_offsets"), ADDRESS.withName("alt_contig"), ADDRESS.withName("alt_negative"),
+            ADDRESS.withName("alt_start"), ADDRESS.withName("alt_stop"));
+    static final StructLayout ASSIGN_OUT = MemoryLayout.structLayout(JAVA_INT.withName("max_probes"), MemoryLayout.paddingLayout(4),
+            ADDRESS.withName("n_probes"), ADDRESS.withName("probes"), ADDRESS.withName("mate"), ADDRESS.withName("n_common"),
+            ADDRESS.withName("common"), ADDRESS.withName("overflow"));
+    static final StructLayout DEDUP_EXTEND_OUT = MemoryLayout.structLayout(ADDRESS.withName("is_best"), ADDRESS.withName("group_size"),
+            ADDRESS.withName("stats"), ADDRESS.withName("unique_unable_to_extend"), ADDRESS.withName("duplicate_unable_to_extend"),
+            JAVA_LONG.withName("n_extended"), ADDRESS.withName("extended_pair"), ADDRESS.withName("extend"));
+    static final StructLayout RECORD_OUT = MemoryLayout.structLayout(ADDRESS.withName("flag"), ADDRESS.withName("mate_pos"),
+            ADDRESS.withName("offsets"), ADDRESS.withName("seq"), ADDRESS.withName("qual"));
+    static final StructLayout MERGE_BATCH = MemoryLayout.structLayout(JAVA_LONG.withName("n"), ADDRESS.withName("negative_strand"),
+            SEQS.withName("up"), SEQS.withName("down"), ADDRESS.withName("up_qual"), ADDRESS.withName("down_qual"),
+            ADDRESS.withName("up_start"), ADDRESS.withName("down_start"));
+
     // ---- downcall handles --------------------------------------------------------------------------------------------
     private static final MethodHandle CTX_CREATE = fn("hsq_ctx_create", FunctionDescriptor.of(JAVA_INT, JAVA_INT, ADDRESS));
     private static final MethodHandle CTX_DESTROY = fn("hsq_ctx_destroy", FunctionDescriptor.ofVoid(ADDRESS));
@@ -59,6 +77,19 @@ public final class HsqB200 implements AutoCloseable {
     private static final MethodHandle DEDUP = fn("hsq_dedup_batch", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT,
             ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle EXTEND = fn("hsq_extend_batch", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+
+    private static final MethodHandle SET_PROBE_RANGES = fn("hsq_set_probe_ranges", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle ASSIGN_PROBES = fn("hsq_assign_probes", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle DEDUP_EXTEND = fn("hsq_dedup_extend_batch", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
+            JAVA_INT, JAVA_INT, ADDRESS));
+    private static final MethodHandle EXTEND_SELECTED = fn("hsq_extend_selected", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
+            ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle EXTEND_RECORDS = fn("hsq_extend_records", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
+            ADDRESS, ADDRESS, JAVA_LONG));
+    private static final MethodHandle MERGE_PAIRS = fn("hsq_merge_pairs", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS,
+            ADDRESS, JAVA_LONG));
+    private static final MethodHandle RESOLVE = fn("hsq_resolve_multi_probe", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
+            JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
 
     private final Arena arena = Arena.ofShared();
     private final MemorySegment ctx;
@@ -105,6 +136,40 @@ public final class HsqB200 implements AutoCloseable {
 
     /** ExtendReadsToPrimer.extendReadsToPrimers for a batch spanning probes (HSQ/process/ExtendReadsToPrimer.java:347-380). */
     public void extend(MemorySegment pairBatch, MemorySegment extendOut) { check(invokeInt(EXTEND, ctx, pairBatch, extendOut)); }
+
+    /** The two range-map tables of getReadToProbeAssignments (HSQ/process/PrimerReadExtensionAndPcrDuplicateIdentification.java:313-331). */
+    public void setProbeRanges(MemorySegment probeRanges) { check(invokeInt(SET_PROBE_RANGES, ctx, probeRanges)); }
+
+    /** ReadToProbeAssigner.assignProbesToReads for a batch of SAM records (…Identification.java:439-576). */
+    public void assignProbes(MemorySegment mappedRecords, MemorySegment assignOut) { check(invokeInt(ASSIGN_PROBES, ctx, mappedRecords, assignOut)); }
+
+    /** The body of PrimerReadExtensionAndFilteringOfUniquePcrProbesTask.run for a batch spanning probes (…Identification.java:1172-1216). */
+    public void dedupExtend(MemorySegment pairBatch, int extUidLen, int ligUidLen, boolean extendDuplicates, MemorySegment dedupExtendOut) {
+        check(invokeInt(DEDUP_EXTEND, ctx, pairBatch, extUidLen, ligUidLen, extendDuplicates ? 1 : 0, dedupExtendOut));
+    }
+
+    /** extendReadsToPrimers on the pairs flagged by the caller (unique pairs of a reduction that ran on another GPU). */
+    public void extendSelected(MemorySegment pairBatch, MemorySegment keep, MemorySegment nExtended, MemorySegment extendedPair,
+                               MemorySegment extendOut) {
+        check(invokeInt(EXTEND_SELECTED, ctx, pairBatch, keep, nExtended, extendedPair, extendOut));
+    }
+
+    /** FLAG / PNEXT / read string / qualities of the records createRecord + setSAMRecordsAsPair build (ExtendReadsToPrimer.java:131-181,247-284). */
+    public void extendRecords(MemorySegment pairBatch, MemorySegment extendOut, MemorySegment duplicate, MemorySegment recordOut, long outCap) {
+        check(invokeInt(EXTEND_RECORDS, ctx, pairBatch, extendOut, duplicate, recordOut, outCap));
+    }
+
+    /** mergeSequences per item (…Identification.java:1362-1552); ERR_OVERFLOW = call again with the sizes in outOffsets. */
+    public int mergePairs(MemorySegment mergeBatch, MemorySegment outSeq, MemorySegment outQual, MemorySegment outOffsets, long outCap) {
+        int st = invokeInt(MERGE_PAIRS, ctx, mergeBatch, outSeq, outQual, outOffsets, outCap);
+        if (st != ERR_OVERFLOW) check(st);
+        return st;
+    }
+
+    /** The multi-probe tie-break (…Identification.java:704-765): bestProbe[k] = winning probe row or -1. */
+    public void resolveMultiProbe(MemorySegment candidates, int extUidLen, int ligUidLen, MemorySegment bestProbe) {
+        check(invokeInt(RESOLVE, ctx, candidates, extUidLen, ligUidLen, bestProbe, MemorySegment.NULL, MemorySegment.NULL));
+    }
 
     /** FastqReadTrimmer.trim per read (HSQ/process/FastqReadTrimmer.java:309-328). */
     public void trim(MemorySegment reads, MemorySegment quals, int firstBaseToKeep, int lastBaseToKeep, boolean threePrime,

@@ -45,6 +45,17 @@ def reference_kats():
         {"source": "nimblegen_heatseq/src/test/java/com/roche/heatseq/process/FastqReadTrimmerTest.java:35-40", "what": "trim",
          "read": "ACGTACGTACGTACGTACGT", "qual": "ABCDEFGHIJKLMNOPQRST", "first": 5, "last": 14, "expected_length": 10},
     ]
+    from tests.test_merge import KATS as MERGE_KATS
+    names = ["standardOneTest :30-39", "gapOneTest :41-50", "disagreementOneTest :52-61", "noOverlapOneTest :63-72", "onlyOverlapOneTest :74-83",
+             "longerUpstreamOneTest :85-93"]
+    k["merge"] = [{"source": "nimblegen_heatseq/src/test/java/com/roche/heatseq/process/PrimerReadExtensionAndPcrDuplicateIdentificationTest.java " + nm,
+                   "negative": c[0], "upstream": c[1], "downstream": c[2], "upstream_quality": c[3], "downstream_quality": c[4],
+                   "upstream_start": c[5], "downstream_start": c[6], "merged": c[7], "merged_quality": c[8]} for c, nm in zip(MERGE_KATS, names)]
+    k["range_map_inputs"] = [  # printed, not asserted, by the reference (RangeMap.java:234-254); answers hand-traced from :92-153
+        {"source": "nimblegen_heatseq/src/main/java/com/roche/heatseq/process/RangeMap.java:234-242 (go3)",
+         "windows": [[2145, 2284], [6462, 6601], [8617, 8756], [8712, 8851]], "query": [8741, 8787], "hand_traced": [3]},
+        {"source": "nimblegen_heatseq/src/main/java/com/roche/heatseq/process/RangeMap.java:244-252 (go4)",
+         "windows": [[1, 10], [2, 11], [3, 12], [4, 13]], "query": [5, 7], "hand_traced": [0, 1, 2, 3]}]
     return k
 
 
@@ -75,6 +86,25 @@ def oracle_vectors():
     quads = [("ACGTTGCATGCAAGTC", "TTACGTTGCATGCAAGTCAGGCTTAACGT"), ("GGCATTACCAGTAGCATT", "ACGGCATTACCAGTAGCATTCCAGGTTAAC"),
              ("ACGTTGCATGCAAGTC", "GGGGGGGGGGGGGGGGGGGGGGGGGGGGG")]
     v["primer_end"] = [{"primer": p, "read": r, "end": O.primer_end(p, r)[0], "weighted": O.primer_end(p, r)[1]} for p, r in quads]
+    # SAM record fields of the extended pairs of 'extend' (first 60 pairs, with qualities; every third pair a duplicate)
+    sub = pairs.head(60)
+    dup = (np.arange(60) % 3 == 0).astype(np.uint8)
+    rec = O.extend_records(probes, sub, duplicate=dup)
+    v["records"] = {"note": "first 60 pairs of 'extend'", "q1": sub.q1.strings(), "q2": sub.q2.strings(), "duplicate": dup.tolist(),
+                    "flag": rec.flag.tolist(), "mate_pos": rec.mate_pos.tolist(), "seq": rec.seqs().strings(), "qual": rec.quals().strings()}
+    # coordinate read -> probe assignment on a seeded problem
+    from tests.test_assign import _random_problem
+    ranges, records = _random_problem(np.random.default_rng(20240504), 40, 300, 4)
+    a = O.assign_probes(ranges, records, max_probes=4)
+    v["assign"] = {"ranges": {"contig": ranges.contig.tolist(), "reverse_strand": ranges.reverse_strand.tolist(), "start": ranges.start.tolist(),
+                              "stop": ranges.stop.tolist()},
+                   "records": {"contig": records.contig.tolist(), "negative_strand": records.negative_strand.tolist(),
+                               "second_of_pair": records.second_of_pair.tolist(), "start": records.start.tolist(), "end": records.end.tolist(),
+                               "read_index": records.read_index.tolist(), "alt_offsets": records.alt_offsets.tolist(),
+                               "alt_contig": records.alt_contig.tolist(), "alt_negative": records.alt_negative.tolist(),
+                               "alt_start": records.alt_start.tolist(), "alt_stop": records.alt_stop.tolist()},
+                   "max_probes": 4, "probes": [list(map(int, t)) for t in a.probe_sets()], "mate": a.mate.tolist(),
+                   "common": [list(map(int, t)) for t in a.common_sets()], "overflow": a.overflow.tolist()}
     return v
 
 

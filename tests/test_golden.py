@@ -9,6 +9,7 @@ import os
 import numpy as np
 import pytest
 
+from bioinformatics_b200 import _abi as A
 from bioinformatics_b200 import synth
 from bioinformatics_b200.batches import PairBatchHost
 from oracle import oracle as O
@@ -73,6 +74,73 @@ def test_oracle_frozen_vectors():
     for k in VEC["primer_end"]:
         end, w = O.primer_end(k["primer"], k["read"])
         assert end == k["end"] and abs(w - k["weighted"]) < 1e-12
+
+
+def _records_inputs():
+    probes, pairs = _extend_inputs()
+    g = VEC["records"]
+    sub = pairs.head(60)
+    sub.q1 = A.SeqBatch.from_strings(g["q1"])
+    sub.q2 = A.SeqBatch.from_strings(g["q2"])
+    return probes, sub, np.array(g["duplicate"], dtype=np.uint8)
+
+
+def _check_records(rec):
+    g = VEC["records"]
+    assert rec.flag.tolist() == g["flag"] and rec.mate_pos.tolist() == g["mate_pos"]
+    assert rec.seqs().strings() == g["seq"] and rec.quals().strings() == g["qual"]
+
+
+def _assign_inputs():
+    from bioinformatics_b200.batches import MappedRecordsHost, ProbeRangesHost
+    g = VEC["assign"]
+    r, m = g["ranges"], g["records"]
+    ranges = ProbeRangesHost(r["contig"], r["reverse_strand"], r["start"], r["stop"])
+    records = MappedRecordsHost(m["contig"], m["negative_strand"], m["second_of_pair"], m["start"], m["end"], m["read_index"],
+                                (m["alt_offsets"], m["alt_contig"], m["alt_negative"], m["alt_start"], m["alt_stop"]))
+    return ranges, records
+
+
+def _check_assign(a):
+    g = VEC["assign"]
+    assert a.overflow.tolist() == g["overflow"] and a.mate.tolist() == g["mate"]
+    ok = [k for k in range(a.n) if not g["overflow"][k]]
+    assert [list(map(int, a.probe_sets()[k])) for k in ok] == [g["probes"][k] for k in ok]
+    assert [list(map(int, a.common_sets()[k])) for k in ok] == [g["common"][k] for k in ok]
+
+
+def test_oracle_frozen_records_assign_and_merge_kats():
+    probes, sub, dup = _records_inputs()
+    _check_records(O.extend_records(probes, sub, duplicate=dup))
+    ranges, records = _assign_inputs()
+    _check_assign(O.assign_probes(ranges, records, max_probes=VEC["assign"]["max_probes"]))
+    for k in KATS["merge"]:
+        s, q = O.merge_pairs([k["negative"]], [k["upstream"]], [k["downstream"]], [k["upstream_quality"]], [k["downstream_quality"]],
+                             [k["upstream_start"]], [k["downstream_start"]])
+        assert s.strings() == [k["merged"]] and q.strings() == [k["merged_quality"]], k["source"]
+    from bioinformatics_b200.batches import MappedRecordsHost, ProbeRangesHost
+    for k in KATS["range_map_inputs"]:
+        n = len(k["windows"])
+        ranges = ProbeRangesHost(np.zeros(n), np.zeros(n), [w[0] for w in k["windows"]], [w[1] for w in k["windows"]])
+        rec = MappedRecordsHost([0], [0], [0], [k["query"][0]], [k["query"][1]], [0])
+        assert list(map(int, O.assign_probes(ranges, rec).probe_sets()[0])) == k["hand_traced"], k["source"]
+
+
+@pytest.mark.gpu
+def test_cuda_frozen_records_assign_and_merge_kats():
+    from bioinformatics_b200._lib import Context
+    with Context(0) as ctx:
+        probes, sub, dup = _records_inputs()
+        ctx.set_probes(probes)
+        ext = ctx.extend_batch(sub, cigar_cap=64, md_cap=96)
+        _check_records(ctx.extend_records(sub, ext, duplicate=dup))
+        ranges, records = _assign_inputs()
+        ctx.set_probe_ranges(ranges)
+        _check_assign(ctx.assign_probes(records, max_probes=VEC["assign"]["max_probes"]))
+        for k in KATS["merge"]:
+            s, q = ctx.merge_pairs([k["negative"]], [k["upstream"]], [k["downstream"]], [k["upstream_quality"]], [k["downstream_quality"]],
+                                   [k["upstream_start"]], [k["downstream_start"]])
+            assert s.strings() == [k["merged"]] and q.strings() == [k["merged_quality"]], k["source"]
 
 
 # ---- GPU: the CUDA path against the same vectors ---------------------------------------------------------------------
