@@ -55,7 +55,7 @@ class AlignOut(C.Structure):
     _fields_ = [("cols_cap", C.c_int32), ("md_cap", C.c_int32), ("score", i32p), ("n_cols", i32p), ("ref_aln", u8p),
                 ("qry_aln", u8p), ("ops", u8p), ("first_q", i32p), ("last_q", i32p), ("first_r", i32p), ("last_r", i32p),
                 ("matches", i32p), ("mismatches", i32p), ("non_terminal_gaps", i32p), ("edit_distance", i32p),
-                ("md_len", i32p), ("md", u8p), ("rmd_len", i32p), ("rmd", u8p), ("overflow", u8p), ("cells", C.c_int64)]
+                ("md_len", i32p), ("md", u8p), ("rmd_len", i32p), ("rmd", u8p), ("overflow", u8p), ("cells", C.c_int64), ("find_counts", i32p)]
 
 
 class ProbeStats(C.Structure):

@@ -135,6 +135,9 @@ class AlignResult:
         self.md = np.zeros(n * md_cap, dtype=np.uint8)
         self.rmd = np.zeros(n * md_cap, dtype=np.uint8)
         self.overflow = np.zeros(n, dtype=np.uint8)
+        # FastqFindAndTrimTool's filter counters over the query-trimmed alignment:
+        # mismatches, insertion gaps, insertion bases, deletion gaps, deletion bases
+        self.find_counts = np.zeros((n, 5), dtype=np.int32)
         self.cells = 0
         self._c = None
 
@@ -145,7 +148,7 @@ class AlignResult:
                              p(self.last_q, A.i32p), p(self.first_r, A.i32p), p(self.last_r, A.i32p),
                              p(self.matches, A.i32p), p(self.mismatches, A.i32p), p(self.non_terminal_gaps, A.i32p),
                              p(self.edit_distance, A.i32p), p(self.md_len, A.i32p), p(self.md, A.u8p),
-                             p(self.rmd_len, A.i32p), p(self.rmd, A.u8p), p(self.overflow, A.u8p), 0)
+                             p(self.rmd_len, A.i32p), p(self.rmd, A.u8p), p(self.overflow, A.u8p), 0, p(self.find_counts, A.i32p))
         return self._c
 
     def finish(self):

@@ -18,7 +18,7 @@ int run_align(hsq_ctx* ctx, const hsq_seqs* refs, const hsq_seqs* qrys, const hs
     ScratchPool pool;
     if ((rc = alloc_scratch(ctx, (int64_t)grid * DP_BLOCK, 0, q_max, r_max, &pool, nullptr))) return rc;
     const size_t nn = (size_t)n;
-    HSQ_CUDA(ctx, ctx->out_i32.ensure(12 * nn * sizeof(int32_t) + 16));
+    HSQ_CUDA(ctx, ctx->out_i32.ensure(17 * nn * sizeof(int32_t) + 16));
     HSQ_CUDA(ctx, ctx->out_u8.ensure(nn + 16));
     HSQ_CUDA(ctx, ctx->out_slots.ensure(nn * (3 * (size_t)o->cols_cap + 2 * (size_t)o->md_cap) + 16));
     int32_t* i32 = ctx->out_i32.as<int32_t>();
@@ -32,6 +32,7 @@ int run_align(hsq_ctx* ctx, const hsq_seqs* refs, const hsq_seqs* qrys, const hs
     d.ref_aln = slots; d.qry_aln = slots + nn * o->cols_cap; d.ops = slots + 2 * nn * o->cols_cap;
     d.md = slots + 3 * nn * o->cols_cap; d.rmd = d.md + nn * o->md_cap;
     d.overflow = ctx->out_u8.as<uint8_t>();
+    d.find_counts = o->find_counts ? i32 + 12 * nn : nullptr;
     const int ps = (flags & HSQ_ALIGN_PENALIZE_START) ? 1 : 0, pe = (flags & HSQ_ALIGN_PENALIZE_END) ? 1 : 0;
     if (n > 0) {
         align_kernel<<<grid, DP_BLOCK, 0, ctx->stream>>>(ctx->sa.view(), ctx->sb.view(), n, sp, ps, pe, pool, d, d_status(ctx),
@@ -49,6 +50,7 @@ int run_align(hsq_ctx* ctx, const hsq_seqs* refs, const hsq_seqs* qrys, const hs
     if ((rc = d2h(ctx, o->md, d.md, nn * o->md_cap))) return rc;
     if ((rc = d2h(ctx, o->rmd, d.rmd, nn * o->md_cap))) return rc;
     if ((rc = d2h(ctx, o->overflow, d.overflow, nn))) return rc;
+    if ((rc = d2h(ctx, o->find_counts, i32 + 12 * nn, 5 * nn))) return rc;
     HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
     if ((rc = read_status(ctx, w, 1))) return rc;
     o->cells = (int64_t)ctx->h_cells[0];

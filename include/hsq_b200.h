@@ -124,6 +124,11 @@ typedef struct hsq_align_out {
     uint8_t* rmd;              /* [n][md_cap] getReverseMismatchDetailsString */
     uint8_t* overflow;         /* bit0 cols, bit1 md, bit2 rmd */
     int64_t cells;             /* out */
+    /* [n][5], may be NULL: the counters FastqFindAndTrimTool filters on (COMMON/fastqtool/FastqFindAndTrimTool.java:932-938),
+     * taken over getAlignmentWithoutEndingAndBeginningQueryInserts (AlignmentPair.java:95-99): getNumberOfMismatches,
+     * getNumberOfInsertionGapsRelativeToReference, getNumberOfInsertionsRelativeToReference,
+     * getNumberOfDeletionGapsRelativeToReference, getNumberOfDeletionsRelativeToReference (AlignmentPair.java:190-256) */
+    int32_t* find_counts;
 } hsq_align_out;
 
 /* Per probe counters of FilterByUid.reduceReadsByProbeAndUid (HSQ/process/FilterByUid.java:149-171,251). */

@@ -96,6 +96,18 @@ int32_t hsqo_align_batch(const hsq_seqs* refs, const hsq_seqs* qrys, const hsq_s
         if (o->edit_distance) o->edit_distance[k] = p.edit_distance();
         put_slot(md_string(p), o->md, o->md_cap, k, o->md_len, o->overflow, 2);
         put_slot(reverse_md_string(p), o->rmd, o->md_cap, k, o->rmd_len, o->overflow, 4);
+        if (o->find_counts) {  // FastqFindAndTrimTool.java:930-938 on getAlignmentWithoutEndingAndBeginningQueryInserts (AlignmentPair.java:95-99)
+            const seq_t ra = seq_sub(p.ref_aln, p.first_q, p.last_q), qa = seq_sub(p.qry_aln, p.first_q, p.last_q);
+            int fx = 0, ig = 0, ib = 0, dg = 0, db = 0;
+            bool in_i = false, in_d = false;
+            for (size_t c = 0; c < ra.size(); c++) {
+                if (ra[c] == GAP) { ib++; if (!in_i) { in_i = true; ig++; } } else in_i = false;      // :190-216
+                if (qa[c] == GAP) { db++; if (!in_d) { in_d = true; dg++; } } else in_d = false;      // :218-244
+                if (ra[c] != GAP && qa[c] != GAP && !code_matches(ra[c], qa[c])) fx++;                  // :246-256
+            }
+            int32_t* fc = o->find_counts + 5 * k;
+            fc[0] = fx; fc[1] = ig; fc[2] = ib; fc[3] = dg; fc[4] = db;
+        }
     });
     o->cells = 0;
     for (auto c : cells) o->cells += c;

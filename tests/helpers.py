@@ -2,7 +2,7 @@
 import numpy as np
 
 ALIGN_FIELDS = ("score", "n_cols", "first_q", "last_q", "first_r", "last_r", "matches", "mismatches", "non_terminal_gaps",
-                "edit_distance", "md_len", "rmd_len")
+                "edit_distance", "md_len", "rmd_len", "find_counts")
 EXTEND_FIELDS = ("ok", "primer_end", "score", "pos", "read_start", "read_stop", "nm", "tlen", "cigar_len", "md_len",
                  "overflow", "pair_ok")
 

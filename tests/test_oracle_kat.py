@@ -56,3 +56,23 @@ def test_trim_kat():  # FastqReadTrimmerTest.java:35-40: 20 bp read, keep [5,14]
     assert seq.strings() == ["CGTACGTACGTACGT"]
     with pytest.raises(O.OracleError):
         O.trim_batch(["ACGT"], ["IIII"], 4, 10, True)
+
+
+def test_find_counters_on_the_query_trimmed_alignment():
+    """FastqFindAndTrimTool.java:930-938: counters over getAlignmentWithoutEndingAndBeginningQueryInserts
+    (AlignmentPair.java:95-99,190-256), hand-derived from the alignment strings the oracle returns."""
+    refs = ["TTTTACGTACGGTACGTAAAA", "ACGTACGTACGT", "ACGTACGT"]
+    qrys = ["ACGTACGTTACGA", "ACGTTTACGTAGGT", "ACGTACGT"]
+    a = O.align_batch(refs, qrys)
+    for k in range(3):
+        ra, qa = a.ref_alns()[k], a.qry_alns()[k]
+        lo, hi = int(a.first_q[k]), int(a.last_q[k])
+        ra, qa = ra[lo:hi + 1], qa[lo:hi + 1]
+        ins_bases = ra.count("_")
+        del_bases = qa.count("_")
+        ins_gaps = len([g for g in ra.replace("A", " ").replace("C", " ").replace("G", " ").replace("T", " ").split() if g])
+        del_gaps = len([g for g in qa.replace("A", " ").replace("C", " ").replace("G", " ").replace("T", " ").split() if g])
+        mism = sum(1 for x, y in zip(ra, qa) if x != "_" and y != "_" and x != y)
+        assert a.find_counts[k].tolist() == [mism, ins_gaps, ins_bases, del_gaps, del_bases], (k, ra, qa)
+    assert a.find_counts[2].tolist() == [0, 0, 0, 0, 0]
+    assert a.find_counts[:2].sum() > 0
