@@ -152,6 +152,100 @@ __device__ inline void build_profile2(const uint32_t (&qa)[KROWS], const uint32_
     }
 }
 
+// A sequence view read element by element from its END towards its start through aligned 32-bit words: the word in use
+// and the next one in walking direction sit in registers, so the byte loads of the traceback (which miss L1 while other
+// warps stream their DP scratch through it) become one prefetched word load per four elements.
+struct CodeWalker {
+    const uint32_t* wp;  // aligned word holding the current element
+    uint32_t cur, nxt;
+    int sh;              // 8 * byte index of the current element inside cur
+    int dsh;             // +8 / -8: memory direction of the walk (= -8 * view step)
+    int comp;
+    // elements of the view still to be read after the ones in `cur`: a word is fetched only when it holds one of them
+    // (never touches memory before the first / after the last word of the view)
+    __device__ __forceinline__ bool more_after_cur(int remaining) const {
+        const int in_cur = (dsh > 0 ? (24 - sh) : sh) >> 3;  // further elements in cur, walking direction
+        return remaining - 1 > in_cur;
+    }
+    __device__ __forceinline__ void init(const SeqView& v, int remaining) {
+        comp = v.comp;
+        dsh = -8 * v.step;
+        cur = 0; nxt = 0; sh = 0; wp = nullptr;
+        if (remaining <= 0) return;
+        const uint8_t* p = v.base + v.start + (int64_t)(remaining - 1) * v.step;
+        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+        wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        sh = (int)(a & 3) * 8;
+        cur = *wp;
+        if (more_after_cur(remaining)) nxt = wp[dsh >> 3];
+    }
+    __device__ __forceinline__ uint32_t peek_raw() const { return (cur >> sh) & 0xFFu; }  // before the complement
+    __device__ __forceinline__ uint32_t peek() const {  // code of the current element (garbage when none remains: unused)
+        const uint32_t c = (cur >> sh) & 0xFFu;
+        return comp ? (uint32_t)complement_code((uint8_t)c) : c;
+    }
+    // `remaining` counts the elements before this step consumes one
+    __device__ __forceinline__ void advance(int remaining) {
+        sh += dsh;
+        if ((uint32_t)sh > 24u) {  // left the word (sh == 32 or -8)
+            sh &= 31;
+            wp += dsh >> 3;
+            cur = nxt;
+            if (more_after_cur(remaining - 1)) nxt = wp[dsh >> 3];
+        }
+    }
+};
+
+// keeps a per-alignment invariant in ONE register (without it ptxas re-selects it from the two alignments at every step)
+__device__ __forceinline__ void pin(int& x) { asm volatile("" : "+r"(x)); }
+__device__ __forceinline__ void pin(uint32_t& x) { asm volatile("" : "+r"(x)); }
+
+// The KROWS query codes of one strip (rows i0+1 .. i0+KROWS; 0 beyond the query).  A forward view is read through five
+// aligned 32-bit words realigned with funnel shifts: sixteen byte loads per lane, each to a different line, kept the LSU
+// busy for longer than the rest of the strip set-up (profiles/README_r1.md).  Reads up to 19 bytes past element i0, which
+// stays inside the slack every code buffer is allocated with.
+__device__ __forceinline__ void load_strip_codes(const SeqView& q, int i0, int Q, uint32_t (&out)[KROWS]) {
+    static_assert(KROWS == 16, "four words per strip");
+    if (q.step == 1) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(q.base + q.start + i0);
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t sh = (uint32_t)(a & 3) * 8u;
+        uint32_t w[5];
+#pragma unroll
+        for (int k = 0; k < 5; k++) w[k] = wp[k];
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const uint32_t v = __funnelshift_r(w[k], w[k + 1], sh);
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const int r = 4 * k + b;
+                uint32_t c = (v >> (8 * b)) & 0xFFu;
+                if (q.comp) c = complement_code((uint8_t)c);
+                out[r] = (i0 + r < Q) ? c : 0u;
+            }
+        }
+    } else if (q.step == -1 && q.start - i0 - (KROWS - 1) >= 0) {  // reversed view, strip inside the sequence: descending addresses
+        const uintptr_t lo = reinterpret_cast<uintptr_t>(q.base + q.start - i0 - (KROWS - 1));
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(lo & ~(uintptr_t)3);
+        const uint32_t sh = (uint32_t)(lo & 3) * 8u;
+        uint32_t w[5], v[4];
+#pragma unroll
+        for (int k = 0; k < 5; k++) w[k] = wp[k];
+#pragma unroll
+        for (int k = 0; k < 4; k++) v[k] = __funnelshift_r(w[k], w[k + 1], sh);
+#pragma unroll
+        for (int r = 0; r < KROWS; r++) {
+            const int byte = KROWS - 1 - r;
+            uint32_t c = (v[byte >> 2] >> (8 * (byte & 3))) & 0xFFu;
+            if (q.comp) c = complement_code((uint8_t)c);
+            out[r] = (i0 + r < Q) ? c : 0u;
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < KROWS; r++) out[r] = (i0 + r < Q) ? (uint32_t)q.get(i0 + r) : 0u;
+    }
+}
+
 template <bool HFREE>
 __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& refB, const SeqView& qryA, const SeqView& qryB,
                                           const ScoreParams2& sp, int pen_start, bool free_end, const DpScratch2& sc, int s,
@@ -162,11 +256,11 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
     uint32_t D4[KROWS], H0[KROWS];
     {
         uint32_t qa[KROWS], qb[KROWS];
+        load_strip_codes(qryA, i0, Q, qa);
+        load_strip_codes(qryB, i0, Q, qb);
 #pragma unroll
         for (int r = 0; r < KROWS; r++) {
             const int i = i0 + 1 + r;
-            qa[r] = (i <= Q) ? (uint32_t)qryA.get(i - 1) : 0u;
-            qb[r] = (i <= Q) ? (uint32_t)qryB.get(i - 1) : 0u;
             const uint32_t s0 = border2(i, pen_start, sp);
             D4[r] = s0;
             H0[r] = (HFREE && r == rstar) ? s0 + sp.hfree2 : s0;
@@ -239,13 +333,18 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
     const int n_strips = (Q + KROWS - 1) / KROWS;
     const bool free_end = !pen_end;
     {   // matrix row 0 (cells point LEFT: never an UP continuation) and the profile column of every reference position
-        uint32_t* bp = &sc.b(1);
-        uint8_t* cp = &sc.ci(1);
-        for (int j = 1; j <= R; j++, bp += sc.nthreads, cp += sc.nthreads) {
+        uint32_t* bp = &sc.b(R);
+        uint8_t* cp = &sc.ci(R);
+        CodeWalker wa, wb;  // last column first: the walkers read from the end of a view
+        wa.init(refA, R);
+        wb.init(refB, R);
+        for (int j = R; j >= 1; j--, bp -= sc.nthreads, cp -= sc.nthreads) {
             *bp = border2(j, pen_start, sp) + (uint32_t)P_LEFT * DP2_REP;
-            const uint32_t ba = (uint32_t)prof_slot(refA.base[refA.start + (j - 1) * refA.step], refA.comp);
-            const uint32_t bb = (uint32_t)prof_slot(refB.base[refB.start + (j - 1) * refB.step], refB.comp);
+            const uint32_t ba = (uint32_t)prof_slot(wa.peek_raw(), refA.comp);
+            const uint32_t bb = (uint32_t)prof_slot(wb.peek_raw(), refB.comp);
             *cp = (uint8_t)(ba | (bb << 4));
+            wa.advance(j);
+            wb.advance(j);
         }
     }
     uint32_t final_d4 = 0;
@@ -256,53 +355,6 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
     score[0] = ((int)(final_d4 & 0xFFFFu) - off) >> 2;
     score[1] = ((int)(final_d4 >> 16) - off) >> 2;
 }
-
-// A sequence view read element by element from its END towards its start through aligned 32-bit words: the word in use
-// and the next one in walking direction sit in registers, so the byte loads of the traceback (which miss L1 while other
-// warps stream their DP scratch through it) become one prefetched word load per four elements.
-struct CodeWalker {
-    const uint32_t* wp;  // aligned word holding the current element
-    uint32_t cur, nxt;
-    int sh;              // 8 * byte index of the current element inside cur
-    int dsh;             // +8 / -8: memory direction of the walk (= -8 * view step)
-    int comp;
-    // elements of the view still to be read after the ones in `cur`: a word is fetched only when it holds one of them
-    // (never touches memory before the first / after the last word of the view)
-    __device__ __forceinline__ bool more_after_cur(int remaining) const {
-        const int in_cur = (dsh > 0 ? (24 - sh) : sh) >> 3;  // further elements in cur, walking direction
-        return remaining - 1 > in_cur;
-    }
-    __device__ __forceinline__ void init(const SeqView& v, int remaining) {
-        comp = v.comp;
-        dsh = -8 * v.step;
-        cur = 0; nxt = 0; sh = 0; wp = nullptr;
-        if (remaining <= 0) return;
-        const uint8_t* p = v.base + v.start + (int64_t)(remaining - 1) * v.step;
-        const uintptr_t a = reinterpret_cast<uintptr_t>(p);
-        wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
-        sh = (int)(a & 3) * 8;
-        cur = *wp;
-        if (more_after_cur(remaining)) nxt = wp[dsh >> 3];
-    }
-    __device__ __forceinline__ uint32_t peek() const {  // code of the current element (garbage when none remains: unused)
-        const uint32_t c = (cur >> sh) & 0xFFu;
-        return comp ? (uint32_t)complement_code((uint8_t)c) : c;
-    }
-    // `remaining` counts the elements before this step consumes one
-    __device__ __forceinline__ void advance(int remaining) {
-        sh += dsh;
-        if ((uint32_t)sh > 24u) {  // left the word (sh == 32 or -8)
-            sh &= 31;
-            wp += dsh >> 3;
-            cur = nxt;
-            if (more_after_cur(remaining - 1)) nxt = wp[dsh >> 3];
-        }
-    }
-};
-
-// keeps a per-alignment invariant in ONE register (without it ptxas re-selects it from the two alignments at every step)
-__device__ __forceinline__ void pin(int& x) { asm volatile("" : "+r"(x)); }
-__device__ __forceinline__ void pin(uint32_t& x) { asm volatile("" : "+r"(x)); }
 
 // Streamed traceback of alignment `which` of the pair (NeedlemanWunschGlobalAlignment.java:85-114): walks from (Q,R) to
 // (0,0) and hands every column, LAST column first, to sink.push(ref code | qry code << 8) (CODE_GAP where the pointer
