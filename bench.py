@@ -29,7 +29,7 @@ READ_LEN = 150
 UID = 10
 CIGAR_CAP, MD_CAP = 24, 40
 OPS_PER_CELL = 12  # algorithmic INT32 ops per DP cell
-TRAFFIC_PER_PAIR_BYTES = (5.109331e9 + 6.514748e9) / 500000  # measured DRAM traffic of capture2_kernel per read pair (ncu, r1_g)
+TRAFFIC_PER_PAIR_BYTES = (4.967699e9 + 6.404992e9) / 500000  # measured DRAM traffic of capture2_kernel per read pair (ncu, r1_j)
 
 
 def parse():
@@ -407,14 +407,14 @@ def main():
                              "frac": achieved / peak,
                              "traffic": TRAFFIC_PER_PAIR_BYTES * n,
                              "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of capture2_kernel from the ncu --set full capture "
-                                             "at 500 k pairs (profiles/ncu_full_capture2_kernel_r1_g.txt: 5.11 + 6.51 GB) scaled to this "
+                                             "at 500 k pairs (profiles/ncu_full_capture2_kernel_r1_j.txt: 4.97 + 6.40 GB) scaled to this "
                                              "batch: scratch (2-bit pointers, boundary rows), not algorithmic bytes; the kernel is ALU bound",
                              "note": "12 algorithmic INT32 ops per DP cell x cells per step / CUDA-event time of hsq_extend_run "
-                                     "(capture2_kernel + primer2_kernel are ~94%% of it, profiles/); peak = sustained INT32 issue rate measured in this run by "
+                                     "(capture2_kernel + primer2_kernel are ~93%% of it, profiles/launches_r1_j.csv); peak = sustained INT32 issue rate measured in this run by "
                                      "hsq_int32_peak (IMAD/VIMNMX/LOP3 micro-kernel, 2 s); nominal 148x128x1.965 GHz = %.1f Tiop/s; "
                                      "MEASURED_PEAKS.json holds no INT32 figure; the packed kernels do two cells per VIADDMNMX.U16x2 / LOP3 / "
                                      "IMAD, so the fraction of this scalar-op peak can exceed 1 at long reads (profiles/sweep_lengths_r1.jsonl); "
-                                     "ncu: issue slots 67%% busy, ALU pipe 62%%" % (nominal / 1e12)},
+                                     "ncu (r1_j): issue slots 71%% busy, ALU pipe 66%%" % (nominal / 1e12)},
                 "clocks": clocks, "stages": stages, "parity": parity}
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1
