@@ -20,7 +20,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
-           "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected")
+           "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs")
 
 
 class HsqError(RuntimeError):
@@ -157,6 +157,13 @@ class Context:
                                              C.c_int32(1 if extend_duplicates else 0), C.byref(oc))
         out.finish()
         self._check(st)
+        return out
+
+    def flag_n_pairs(self, pairs: PairBatchHost):
+        """hsq_flag_n_pairs: 1 where either read of the pair holds an N (…Identification.java:815-821)."""
+        out = np.zeros(pairs.n, dtype=np.uint8)
+        pc = pairs.c()
+        self._check(self.lib.hsq_flag_n_pairs(self.h, C.byref(pc), A.ptr(out, A.u8p)))
         return out
 
     def extend_selected(self, pairs: PairBatchHost, keep, cigar_cap=32, md_cap=48, out=None, extended_pair=None):

@@ -258,3 +258,42 @@ extern "C" int32_t hsq_extend_selected(hsq_ctx* ctx, const hsq_pair_batch* pairs
     int rc2 = timer.finish();
     return rc ? rc : rc2;
 }
+
+namespace {
+// one warp per pair: any 'N' / 'n' in either read
+__global__ void flag_n_kernel(const uint8_t* __restrict__ r1, const int64_t* __restrict__ off1, const uint8_t* __restrict__ r2,
+                              const int64_t* __restrict__ off2, int64_t n, uint8_t* __restrict__ has_n) {
+    const int lane = threadIdx.x & 31;
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; w < n; w += stride) {
+        bool hit = false;
+        for (int64_t i = off1[w] + lane; i < off1[w + 1]; i += 32) hit |= ((r1[i] | 0x20) == 'n');
+        for (int64_t i = off2[w] + lane; i < off2[w + 1]; i += 32) hit |= ((r2[i] | 0x20) == 'n');
+        hit = __any_sync(0xffffffffu, hit);
+        if (lane == 0) has_n[w] = hit ? 1 : 0;
+    }
+}
+}  // namespace
+
+extern "C" int32_t hsq_flag_n_pairs(hsq_ctx* ctx, const hsq_pair_batch* pairs, uint8_t* has_n) {
+    if (!ctx || !pairs) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    const int64_t n = pairs->n;
+    if (n < 0 || pairs->r1.n != n || pairs->r2.n != n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
+    if (n > 0 && !has_n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null output");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc;
+    if ((rc = copy_seqs(ctx, &pairs->r1, &ctx->r1))) return rc;
+    if ((rc = copy_seqs(ctx, &pairs->r2, &ctx->r2))) return rc;
+    HSQ_CUDA(ctx, ctx->out_u8.ensure((size_t)n + 16));
+    if (n > 0) {
+        const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
+        flag_n_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), ctx->r2.ascii.as<uint8_t>(),
+                                                      ctx->r2.offsets.as<int64_t>(), n, ctx->out_u8.as<uint8_t>());
+        ctx->launches++;
+        HSQ_CUDA(ctx, cudaGetLastError());
+        if ((rc = d2h(ctx, has_n, ctx->out_u8.as<uint8_t>(), (size_t)n))) return rc;
+    }
+    return timer.finish();
+}

@@ -173,6 +173,62 @@ def drop_n_pairs(pairs):
                          pairs.read_index[keep]), keep
 
 
+def make_mapped_records(probes, pairs, seed=5, alt_rate=0.05, lone_rate=0.02, off_panel_rate=0.02, repeat_names=3):
+    """Mapped records (what a mapper would report for `pairs`) for the read -> probe assignment, in shuffled order.
+
+    Each pair gives a read-one record on the probe's strand and a read-two record on the other one
+    (…Identification.java:452-455), both inside the probe's window.  alt_rate of the pairs carry an alternative hit (XA) inside
+    another probe's window on both mates, so the pair has two candidate probes; lone_rate lose their read two; off_panel_rate map
+    to a contig without probes; repeat_names read names occur on four records.  Returns (ProbeRangesHost, MappedRecordsHost)."""
+    from .batches import MappedRecordsHost, ProbeRangesHost
+    rng = np.random.default_rng(seed)
+    names = sorted(set(probes.chromosomes), key=lambda c: int(c[3:]))
+    contig_of = {c: k for k, c in enumerate(names)}
+    pcontig = np.array([contig_of[c] for c in probes.chromosomes], dtype=np.int32)
+    ranges = ProbeRangesHost.from_probe_table(probes, pcontig)
+    n = pairs.n
+    p = pairs.probe_id.astype(np.int64)
+    rev = probes.reverse_strand[p].astype(np.uint8)
+
+    def inside(pid, m):
+        a = ranges.start[pid] + rng.integers(0, 6, m)
+        b = ranges.stop[pid] - rng.integers(0, 6, m)
+        return a.astype(np.int32), b.astype(np.int32)
+
+    a1, b1 = inside(p, n)
+    a2, b2 = inside(p, n)
+    contig = np.concatenate([pcontig[p], pcontig[p]])
+    neg = np.concatenate([rev, 1 - rev]).astype(np.uint8)
+    second = np.concatenate([np.zeros(n, np.uint8), np.ones(n, np.uint8)])
+    start, end = np.concatenate([a1, a2]), np.concatenate([b1, b2])
+    ridx = np.concatenate([pairs.read_index, pairs.read_index]).astype(np.int32)
+    has_alt = rng.random(n) < alt_rate
+    other = (p + 1 + rng.integers(0, max(1, probes.n - 1), n)) % probes.n
+    alt_count = np.concatenate([has_alt, has_alt]).astype(np.int64)
+    oa, ob = inside(other, n)
+    orev = probes.reverse_strand[other].astype(np.uint8)
+    alt_contig_full = np.concatenate([pcontig[other], pcontig[other]])
+    alt_neg_full = np.concatenate([orev, 1 - orev]).astype(np.uint8)
+    alt_a_full, alt_b_full = np.concatenate([oa, oa]), np.concatenate([ob, ob])
+    off = np.concatenate([rng.random(n) < off_panel_rate] * 2)
+    contig = np.where(off, -1, contig).astype(np.int32)
+    keep = np.ones(2 * n, dtype=bool)
+    keep[n:] = rng.random(n) >= lone_rate
+    if repeat_names and n > 2 * repeat_names:  # a read name on four records: removed from every probe (:392-400)
+        twice = rng.choice(n, repeat_names, replace=False)
+        extra = np.concatenate([twice, twice + n])
+        order = np.concatenate([np.nonzero(keep)[0], extra])
+    else:
+        order = np.nonzero(keep)[0]
+    order = order[rng.permutation(len(order))]
+    cnt = alt_count[order]
+    alt_off = np.zeros(len(order) + 1, dtype=np.int64)
+    alt_off[1:] = np.cumsum(cnt)
+    src = order[cnt > 0]
+    alt = (alt_off, alt_contig_full[src], alt_neg_full[src], alt_a_full[src], alt_b_full[src])
+    return ranges, MappedRecordsHost(contig[order], neg[order], second[order], start[order], end[order], ridx[order], alt)
+
+
 def write_probe_info_file(probes, path, ext_uid_len=10, lig_uid_len=0):
     """Probe-info TSV with the 13 named columns the reference parses (ProbeFileUtil.java:45-46) and its #key=value header."""
     cols = ["probe_id", "chromosome", "probe_strand", "ext_start", "ext_stop", "ext_sequence", "lig_start", "lig_stop",

@@ -306,6 +306,10 @@ int32_t hsq_extend_records(hsq_ctx* ctx, const hsq_pair_batch* pairs, const hsq_
 int32_t hsq_extend_selected(hsq_ctx* ctx, const hsq_pair_batch* pairs, const uint8_t* keep, int64_t* n_extended,
                             int32_t* extended_pair, hsq_extend_out* out);
 
+/* has_n[k] = 1 when read one or read two of pair k holds an 'N' or 'n': such pairs are not handed to the probe tasks
+ * (readString.toLowerCase().contains("n"), …Identification.java:815-821). */
+int32_t hsq_flag_n_pairs(hsq_ctx* ctx, const hsq_pair_batch* pairs, uint8_t* has_n);
+
 /* mergeSequences per item (…Identification.java:1362-1552, behind the unregistered --mergePairs option): lead + overlap
  * (per position the base with the higher quality wins, ties to upstream; a gap is filled with N / '!') + trail.
  * out_offsets gets n+1 entries; out_seq/out_qual have out_cap bytes: when the merged total is larger the call returns

@@ -86,6 +86,7 @@ public final class HsqB200 implements AutoCloseable {
             ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle EXTEND_RECORDS = fn("hsq_extend_records", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
             ADDRESS, ADDRESS, JAVA_LONG));
+    private static final MethodHandle FLAG_N = fn("hsq_flag_n_pairs", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle MERGE_PAIRS = fn("hsq_merge_pairs", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS,
             ADDRESS, JAVA_LONG));
     private static final MethodHandle RESOLVE = fn("hsq_resolve_multi_probe", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
@@ -158,6 +159,9 @@ public final class HsqB200 implements AutoCloseable {
     public void extendRecords(MemorySegment pairBatch, MemorySegment extendOut, MemorySegment duplicate, MemorySegment recordOut, long outCap) {
         check(invokeInt(EXTEND_RECORDS, ctx, pairBatch, extendOut, duplicate, recordOut, outCap));
     }
+
+    /** hasN[k] = 1 when either read of pair k holds an N (…Identification.java:815-821): such pairs skip the probe tasks. */
+    public void flagNPairs(MemorySegment pairBatch, MemorySegment hasN) { check(invokeInt(FLAG_N, ctx, pairBatch, hasN)); }
 
     /** mergeSequences per item (…Identification.java:1362-1552); ERR_OVERFLOW = call again with the sizes in outOffsets. */
     public int mergePairs(MemorySegment mergeBatch, MemorySegment outSeq, MemorySegment outQual, MemorySegment outOffsets, long outCap) {
