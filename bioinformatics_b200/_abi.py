@@ -91,6 +91,11 @@ class AssignOut(C.Structure):
                 ("overflow", u8p)]
 
 
+class FindOut(C.Structure):
+    _fields_ = [("max_candidates", C.c_int32), ("lead_trimmed", i32p), ("trail_trimmed", i32p), ("has_n", u8p), ("n_candidates", i32p),
+                ("candidates", i32p), ("hits", i32p), ("overflow", u8p), ("order_dependent", u8p)]
+
+
 ASSIGN_UNPAIRED, ASSIGN_AMBIGUOUS_NAME, ASSIGN_IGNORED = -1, -2, -3
 
 

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 from . import _abi as A
-from .batches import (AlignResult, AssignResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
+from .batches import (AlignResult, AssignResult, FindResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
                       ProbeTableHost, merge_args, scorer)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
@@ -20,7 +20,8 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_scorer", "hsq_set_probes", "hsq_last_timing", "hsq_align_batch", "hsq_trim_batch", "hsq_dedup_batch",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
-           "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs")
+           "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs",
+           "hsq_set_find_sequences", "hsq_find_candidates")
 
 
 class HsqError(RuntimeError):
@@ -215,6 +216,23 @@ class Context:
         out = AssignResult(records.n, max_probes)
         rc, oc = records.c(), out.c()
         self._check(self.lib.hsq_assign_probes(self.h, C.byref(rc), C.byref(oc)))
+        return out
+
+    def set_find_sequences(self, seqs, kmer=5, max_refs_per_kmer=15000):
+        """hsq_set_find_sequences: SimpleMapper index of the sequences to find (FastqFindAndTrimTool.java:231-237)."""
+        seqs = seqs if isinstance(seqs, A.SeqBatch) else A.SeqBatch.from_strings(seqs)
+        sc = seqs.c()
+        self._check(self.lib.hsq_set_find_sequences(self.h, C.byref(sc), C.c_int32(kmer), C.c_int32(max_refs_per_kmer)))
+
+    def find_candidates(self, reads, quals, leading_quality=0, trailing_quality=0, candidate_limit=10, min_hit_ratio=0.5, max_candidates=16):
+        """hsq_find_candidates: quality trim, N test and SimpleMapper.getBestCandidateReferences per read."""
+        reads = reads if isinstance(reads, A.SeqBatch) else A.SeqBatch.from_strings(reads)
+        quals = quals if isinstance(quals, A.SeqBatch) else A.SeqBatch.from_strings(quals)
+        assert (quals.offsets == reads.offsets).all(), "qualities must match the reads' lengths"
+        out = FindResult(reads.n, max_candidates)
+        rc, oc = reads.c(), out.c()
+        self._check(self.lib.hsq_find_candidates(self.h, C.byref(rc), A.ptr(quals.data, A.u8p), C.c_int32(leading_quality),
+                                                 C.c_int32(trailing_quality), C.c_int32(candidate_limit), C.c_double(min_hit_ratio), C.byref(oc)))
         return out
 
     def dedup_keys(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, n_probes, origin_base, d_keys_ptr):

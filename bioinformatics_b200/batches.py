@@ -329,6 +329,29 @@ class AssignResult:
         return [tuple(self.common[k, :self.n_common[k]]) for k in range(self.n)]
 
 
+class FindResult:
+    """hsq_find_out with host arrays."""
+
+    def __init__(self, n, max_candidates=16):
+        self.n, self.max_candidates = n, max_candidates
+        self.lead_trimmed = np.zeros(n, dtype=np.int32)
+        self.trail_trimmed = np.zeros(n, dtype=np.int32)
+        self.has_n = np.zeros(n, dtype=np.uint8)
+        self.n_candidates = np.zeros(n, dtype=np.int32)
+        self.candidates = np.full((n, max_candidates), -1, dtype=np.int32)
+        self.hits = np.zeros((n, max_candidates), dtype=np.int32)
+        self.overflow = np.zeros(n, dtype=np.uint8)
+        self.order_dependent = np.zeros(n, dtype=np.uint8)
+
+    def c(self):
+        return A.FindOut(self.max_candidates, A.ptr(self.lead_trimmed, A.i32p), A.ptr(self.trail_trimmed, A.i32p), A.ptr(self.has_n, A.u8p),
+                         A.ptr(self.n_candidates, A.i32p), A.ptr(self.candidates, A.i32p), A.ptr(self.hits, A.i32p),
+                         A.ptr(self.overflow, A.u8p), A.ptr(self.order_dependent, A.u8p))
+
+    def candidate_lists(self):
+        return [[(int(self.candidates[k, j]), int(self.hits[k, j])) for j in range(self.n_candidates[k])] for k in range(self.n)]
+
+
 def scorer(match=1, mismatch=-4, gap_extend=-1, gap_start=-6):
     """SimpleAlignmentScorer defaults (COMMON/alignment/SimpleAlignmentScorer.java:23-26)."""
     return A.Scorer(match, mismatch, gap_extend, gap_start)

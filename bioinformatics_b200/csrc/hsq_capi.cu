@@ -168,9 +168,9 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
                            &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
                            &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
                            &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->rg_start, &ctx->rg_end,
-                           &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32};
+                           &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32, &ctx->fi_start, &ctx->fi_len, &ctx->fi_refs, &ctx->fi_size};
     for (auto* b : bufs) b->release();
-    hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb, &ctx->alt_r1, &ctx->alt_r2};
+    hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb, &ctx->alt_r1, &ctx->alt_r2, &ctx->fs};
     for (auto* s : seqs) s->release();
     for (auto& ps : ctx->parked) {
         hsq::DevBuf* pb[] = {&ps.probe_id, &ps.out_i32, &ps.out_u8, &ps.out_slots, &ps.pair_ok, &ps.ptr_words, &ps.brow, &ps.cols, &ps.colinfo,
@@ -238,4 +238,5 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_assign.inl"
 #include "hsq_capi_pipeline.inl"
 #include "hsq_capi_records.inl"
+#include "hsq_capi_find.inl"
 #include "hsq_capi_peak.inl"

@@ -1,0 +1,339 @@
+// hsq_capi_find.inl -- candidate stage of FastqFindAndTrimTool:
+//   trimReadBasedOnQuality                     COMMON/fastqtool/FastqFindAndTrimTool.java:1188-1219
+//   the N test on the trimmed read             :920
+//   SimpleMapper (index, tallies, candidates)  COMMON/mapping/SimpleMapper.java:90-143,154-217
+// Device plan.  Index: every (k-mer, sequence) occurrence becomes a 64-bit key kmer * R + row; radix sort, drop repeats
+// (a k-mer counts once per sequence: the reference keeps a Set), count per k-mer, scan -> CSR; k-mers over the per-k-mer cap
+// get length 0.  Query: one warp per read; tallies of all R sequences live in shared memory (global scratch when R is
+// large), filled with one atomicAdd per (query position, sequence holding that k-mer); the candidate walk then takes the
+// groups of equal tallies from the largest down, each group in ascending row order, exactly as the reference's loop does
+// when equal tallies come out of its sort in that order.
+namespace {
+
+constexpr int FIND_MAX_K = 10;  // 4^10 CSR rows
+
+__device__ __forceinline__ bool is_acgt(uint8_t c) {
+    const uint8_t u = c & 0xDF;  // NucleotideCode.getNucleotidesFromString upper-cases first
+    return u == 'A' || u == 'C' || u == 'G' || u == 'T';
+}
+__device__ __forceinline__ uint32_t base2(uint8_t c) { return (c >> 1) & 3u; }  // A/a 0, C/c 1, T/t 2, G/g 3
+
+__device__ __forceinline__ uint32_t kmer_at(const uint8_t* s, int k) {
+    uint32_t v = 0;
+    for (int j = 0; j < k; j++) v = (v << 2) | base2(s[j]);
+    return v;
+}
+
+// one thread per sequence to find: checks, size, number of indexed k-mers (start positions 0 .. size-k-1, SimpleMapper.java:93)
+__global__ void find_seq_check_kernel(const uint8_t* __restrict__ data, const int64_t* __restrict__ off, int64_t R, int k, int32_t* __restrict__ size,
+                                      int64_t* __restrict__ count, int* __restrict__ status) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < R; r += stride) {
+        const int64_t a = off[r];
+        const int len = (int)(off[r + 1] - a);
+        bool ok = true;
+        for (int i = 0; i < len; i++) ok &= is_acgt(data[a + i]);
+        if (!ok) atomicCAS(status, 0, HSQ_ERR_BAD_CHARACTER);
+        else if (len < k) atomicCAS(status, 0, HSQ_ERR_OUT_OF_RANGE);
+        size[r] = len;
+        count[r] = (ok && len > k) ? (len - k) : 0;
+    }
+}
+
+__global__ void find_emit_keys_kernel(const uint8_t* __restrict__ data, const int64_t* __restrict__ off, const int64_t* __restrict__ pos, int64_t R,
+                                      int k, uint64_t* __restrict__ keys) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < R; r += stride) {
+        const int64_t a = off[r];
+        const int m = (int)(pos[r + 1] - pos[r]);
+        for (int i = 0; i < m; i++) keys[pos[r] + i] = (uint64_t)kmer_at(data + a + i, k) * (uint64_t)R + (uint64_t)r;
+    }
+}
+
+// first occurrence of every (k-mer, sequence) key in the sorted list: flag + per-k-mer count
+__global__ void find_heads_kernel(const uint64_t* __restrict__ keys, int64_t M, uint64_t R, int64_t* __restrict__ head, int64_t* __restrict__ per_kmer) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < M; i += stride) {
+        const bool h = (i == 0) || keys[i] != keys[i - 1];
+        head[i] = h ? 1 : 0;
+        if (h) atomicAdd(reinterpret_cast<unsigned long long*>(per_kmer + keys[i] / R), 1ull);
+    }
+}
+
+__global__ void find_compact_kernel(const uint64_t* __restrict__ keys, const int64_t* __restrict__ head, const int64_t* __restrict__ upos, int64_t M,
+                                    uint64_t R, int32_t* __restrict__ refs) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < M; i += stride)
+        if (head[i]) refs[upos[i]] = (int32_t)(keys[i] % R);
+}
+
+// length of every CSR row; a k-mer held by more than max_refs sequences is not in the index (SimpleMapper.java:135-138)
+__global__ void find_row_len_kernel(const int64_t* __restrict__ per_kmer, int64_t rows, int max_refs, int32_t* __restrict__ len) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < rows; i += stride) len[i] = (max_refs > 0 && per_kmer[i] > max_refs) ? 0 : (int32_t)per_kmer[i];
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_set_find_sequences(hsq_ctx* ctx, const hsq_seqs* seqs, int32_t kmer, int32_t max_refs_per_kmer) {
+    if (!ctx || !seqs) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (kmer < 1 || kmer > FIND_MAX_K) return fail(ctx, HSQ_ERR_UNSUPPORTED, "k-mer size must be 1..10");
+    if (seqs->n < 1 || seqs->n >= (1ll << 31)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "need between 1 and 2^31-1 sequences to find");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    ctx->fi_n = -1;
+    int rc;
+    if ((rc = reset_status(ctx))) return rc;
+    if ((rc = copy_seqs(ctx, seqs, &ctx->fs))) return rc;
+    const int64_t R = seqs->n, rows = 1ll << (2 * kmer);
+    HSQ_CUDA(ctx, ctx->fi_size.ensure((size_t)R * 4 + 16));
+    HSQ_CUDA(ctx, ctx->cols.ensure((size_t)(R + 1) * 8));
+    HSQ_CUDA(ctx, ctx->brow.ensure((size_t)(R + 1) * 8));
+    HSQ_CUDA(ctx, ctx->misc.ensure((size_t)((std::max(R, rows) + 1 + SCAN_TILE) / SCAN_TILE + 1) * 8 + 64));
+    int64_t* cnt = ctx->cols.as<int64_t>();
+    int64_t* pos = ctx->brow.as<int64_t>();
+    int64_t* tiles = ctx->misc.as<int64_t>();
+    const uint8_t* data = ctx->fs.ascii.as<uint8_t>();
+    const int64_t* off = ctx->fs.offsets.as<int64_t>();
+    const int rblocks = (int)std::min<int64_t>((R + 127) / 128, (int64_t)ctx->sm_count * 16);
+    find_seq_check_kernel<<<rblocks, 128, 0, ctx->stream>>>(data, off, R, kmer, ctx->fi_size.as<int32_t>(), cnt, ctx->status.as<int>());
+    ctx->launches++;
+    if ((rc = scan_i64(ctx, cnt, R, tiles, pos))) return rc;
+    int64_t* h_m = reinterpret_cast<int64_t*>(ctx->h_cells) + 1;  // pinned
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_m, pos + R, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_status, ctx->status.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->h_status[0] != 0) return fail(ctx, ctx->h_status[0], ctx->h_status[0] == HSQ_ERR_BAD_CHARACTER
+                                                                      ? "a sequence to find holds a character other than A, C, G, T"
+                                                                      : "a sequence to find is shorter than the k-mer size");
+    const int64_t M = *h_m;
+    const size_t mm = (size_t)M;
+    HSQ_CUDA(ctx, ctx->fi_start.ensure((size_t)(rows + 1) * 8));
+    HSQ_CUDA(ctx, ctx->fi_len.ensure((size_t)rows * 4 + 16));
+    HSQ_CUDA(ctx, ctx->fi_refs.ensure(mm * 4 + 16));
+    HSQ_CUDA(ctx, ctx->sort_a.ensure(mm * 8 + 16));
+    HSQ_CUDA(ctx, ctx->sort_b.ensure(mm * 8 + 16));
+    HSQ_CUDA(ctx, ctx->sort_c.ensure(mm * 4 + 16));
+    HSQ_CUDA(ctx, ctx->sort_d.ensure(mm * 4 + 16));
+    HSQ_CUDA(ctx, ctx->flags.ensure((mm + 1) * 8 + 16));
+    HSQ_CUDA(ctx, ctx->slow.ensure((std::max<size_t>(mm, (size_t)rows) + 1) * 8 + 16));
+    HSQ_CUDA(ctx, ctx->colinfo.ensure((size_t)(rows + 1) * 8));
+    int64_t* per_kmer = ctx->colinfo.as<int64_t>();
+    HSQ_CUDA(ctx, cudaMemsetAsync(per_kmer, 0, (size_t)(rows + 1) * 8, ctx->stream));
+    const int kblocks = (int)std::min<int64_t>((rows + 255) / 256, (int64_t)ctx->sm_count * 16);
+    if (M > 0) {
+        uint64_t* ka = ctx->sort_a.as<uint64_t>();
+        uint64_t* kb = ctx->sort_b.as<uint64_t>();
+        find_emit_keys_kernel<<<rblocks, 128, 0, ctx->stream>>>(data, off, pos, R, kmer, ka);
+        ctx->launches++;
+        if ((rc = sort_pass(ctx, ka, kb, ctx->sort_c.as<uint32_t>(), ctx->sort_d.as<uint32_t>(), M, 2 * kmer + bits_for((uint64_t)R)))) return rc;
+        const int mblocks = (int)std::min<int64_t>((M + 255) / 256, (int64_t)ctx->sm_count * 16);
+        int64_t* head = ctx->flags.as<int64_t>();
+        int64_t* upos = ctx->slow.as<int64_t>();
+        find_heads_kernel<<<mblocks, 256, 0, ctx->stream>>>(kb, M, (uint64_t)R, head, per_kmer);
+        ctx->launches++;
+        if ((rc = scan_i64(ctx, head, M, tiles, upos))) return rc;
+        find_compact_kernel<<<mblocks, 256, 0, ctx->stream>>>(kb, head, upos, M, (uint64_t)R, ctx->fi_refs.as<int32_t>());
+        ctx->launches++;
+    }
+    if ((rc = scan_i64(ctx, per_kmer, rows, tiles, ctx->fi_start.as<int64_t>()))) return rc;
+    find_row_len_kernel<<<kblocks, 256, 0, ctx->stream>>>(per_kmer, rows, max_refs_per_kmer, ctx->fi_len.as<int32_t>());
+    ctx->launches++;
+    HSQ_CUDA(ctx, cudaGetLastError());
+    if ((rc = timer.finish())) return rc;
+    ctx->fi_n = R;
+    ctx->fi_k = kmer;
+    return HSQ_OK;
+}
+
+namespace {
+
+struct FindIndex {
+    const int64_t* start;  // [4^k + 1]
+    const int32_t* len;    // [4^k] 0 = k-mer not indexed
+    const int32_t* refs;
+    const int32_t* size;   // [R] referenceAddressesToSizeMap
+    int32_t R, k;
+};
+
+struct FindDeviceOut {
+    int32_t K;
+    int32_t *lead, *trail, *n_cand, *cand, *hits;
+    uint8_t *has_n, *overflow, *order_dep;
+};
+
+// One warp per read.  `tally_global` != null: the warps' tallies live there (R too large for shared memory).
+__global__ void find_candidates_kernel(const uint8_t* __restrict__ reads, const uint8_t* __restrict__ quals, const int64_t* __restrict__ off, int64_t n,
+                                       FindIndex ix, int lead_q, int trail_q, int limit, double min_ratio, FindDeviceOut o,
+                                       uint32_t* __restrict__ tally_global, int* __restrict__ status) {
+    extern __shared__ uint32_t find_smem[];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    uint32_t* tally = tally_global ? tally_global + warp0 * ix.R : find_smem + (size_t)wib * ix.R;
+    const int R = ix.R, k = ix.k;
+    for (int64_t r = warp0; r < n; r += n_warps) {
+        const int64_t a = off[r];
+        const int len = (int)(off[r + 1] - a);
+        const uint8_t* q = quals + a;
+        // trimReadBasedOnQuality (:1194-1214): first position from each end whose quality reaches the threshold
+        int lead = len;
+        for (int b = 0; b < len; b += 32) {
+            const int i = b + lane;
+            const unsigned m = __ballot_sync(0xffffffffu, i < len && ((int)q[i] - 33) >= lead_q);
+            if (m) { lead = b + __ffs(m) - 1; break; }
+        }
+        const int rest = len - lead;
+        int trail = rest;
+        for (int b = 0; b < rest; b += 32) {
+            const int t = b + lane;  // candidate number of trailing bases already trimmed
+            const unsigned m = __ballot_sync(0xffffffffu, t < rest && ((int)q[len - t - 1] - 33) >= trail_q);
+            if (m) { trail = b + __ffs(m) - 1; break; }
+        }
+        const uint8_t* s = reads + a + lead;
+        const int tlen = len - lead - trail;
+        bool has_n = false, bad = false;
+        for (int i = lane; i < tlen; i += 32) {
+            const uint8_t c = s[i];
+            has_n |= ((c | 0x20) == 'n');
+            bad |= !is_acgt(c);
+        }
+        has_n = __any_sync(0xffffffffu, has_n);
+        bad = __any_sync(0xffffffffu, bad);
+        int count = 0;
+        bool od = false;
+        if (!has_n && bad && lane == 0) atomicCAS(status, 0, HSQ_ERR_BAD_CHARACTER);
+        if (!has_n && !bad && tlen > k) {
+            for (int i = lane; i < R; i += 32) tally[i] = 0;
+            __syncwarp();
+            // getReferenceTallyMap (SimpleMapper.java:205-217): query positions 0 .. size-k-1
+            for (int i = lane; i < tlen - k; i += 32) {
+                const uint32_t code = kmer_at(s + i, k);
+                const int32_t m = ix.len[code];
+                const int32_t* row = ix.refs + ix.start[code];
+                for (int j = 0; j < m; j++) atomicAdd(&tally[row[j]], 1u);
+            }
+            __syncwarp();
+            // getBestCandidateReferences (:154-187), groups of equal tallies from the largest down
+            const double limit_q = min_ratio * (double)(tlen - k);
+            uint32_t prev = 0xffffffffu;
+            while (true) {
+                uint32_t h = 0;
+                for (int i = lane; i < R; i += 32) {
+                    const uint32_t t = tally[i];
+                    if (t < prev && t > h) h = t;
+                }
+                for (int d = 16; d > 0; d >>= 1) h = max(h, __shfl_xor_sync(0xffffffffu, h, d));
+                if (h == 0) break;
+                if (count > limit) break;  // candidate limit reached and this group is not tied with the last one added
+                const bool below_q = (double)h < limit_q;
+                bool stopped = false;
+                for (int b = 0; b < R; b += 32) {
+                    const int ref = b + lane;
+                    const bool in = ref < R && tally[ref] == h;
+                    const bool failing = in && below_q && ((double)h < min_ratio * (double)(ix.size[ref] - k));
+                    const unsigned m_in = __ballot_sync(0xffffffffu, in), m_fail = __ballot_sync(0xffffffffu, failing);
+                    const unsigned take = m_fail ? (m_in & ((1u << (__ffs(m_fail) - 1)) - 1u)) : m_in;
+                    if (take & (1u << lane)) {
+                        const int slot = count + __popc(take & ((1u << lane) - 1u));
+                        if (slot < o.K) {
+                            o.cand[r * o.K + slot] = ref;
+                            o.hits[r * o.K + slot] = (int32_t)h;
+                        }
+                    }
+                    count += __popc(take);
+                    if (m_fail) { stopped = true; break; }
+                }
+                if (stopped) {  // would an entry of this tally have passed had it come first?
+                    bool pass = false;
+                    for (int ref = lane; ref < R; ref += 32)
+                        pass |= (tally[ref] == h) && !((double)h < min_ratio * (double)(ix.size[ref] - k));
+                    od = __any_sync(0xffffffffu, pass);
+                    break;
+                }
+                prev = h;
+            }
+        }
+        if (lane == 0) {
+            o.lead[r] = lead;
+            o.trail[r] = trail;
+            o.has_n[r] = has_n ? 1 : 0;
+            o.n_cand[r] = min(count, o.K);
+            o.overflow[r] = count > o.K ? 1 : 0;
+            o.order_dep[r] = od ? 1 : 0;
+        }
+        __syncwarp();
+    }
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_find_candidates(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int32_t leading_quality,
+                                       int32_t trailing_quality, int32_t candidate_limit, double min_hit_ratio, hsq_find_out* out) {
+    if (!ctx || !reads || !out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (ctx->fi_n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_set_find_sequences first");
+    if (out->max_candidates < 1) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "max_candidates must be positive");
+    const int64_t n = reads->n;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc;
+    if ((rc = reset_status(ctx))) return rc;
+    if ((rc = copy_seqs(ctx, reads, &ctx->r1))) return rc;
+    const size_t total = (size_t)ctx->r1.total, nn = (size_t)n, K = (size_t)out->max_candidates;
+    if (total > 0 && !quals) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null qualities");
+    HSQ_CUDA(ctx, ctx->q1.ensure(total + 16));
+    if (total > 0) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q1.p, quals + reads->offsets[0], total, cudaMemcpyHostToDevice, ctx->stream));
+    HSQ_CUDA(ctx, ctx->out_i32.ensure((3 * nn + 2 * nn * K) * 4 + 16));
+    HSQ_CUDA(ctx, ctx->out_u8.ensure(3 * nn + 16));
+    FindDeviceOut o;
+    o.K = (int32_t)K;
+    o.lead = ctx->out_i32.as<int32_t>();
+    o.trail = o.lead + nn;
+    o.n_cand = o.trail + nn;
+    o.cand = o.n_cand + nn;
+    o.hits = o.cand + nn * K;
+    o.has_n = ctx->out_u8.as<uint8_t>();
+    o.overflow = o.has_n + nn;
+    o.order_dep = o.overflow + nn;
+    if (n > 0) {
+        FindIndex ix{ctx->fi_start.as<int64_t>(), ctx->fi_len.as<int32_t>(), ctx->fi_refs.as<int32_t>(), ctx->fi_size.as<int32_t>(), (int32_t)ctx->fi_n,
+                     ctx->fi_k};
+        const size_t per_warp = (size_t)ctx->fi_n * 4;
+        int warps = 8;
+        while (warps > 1 && per_warp * warps > 96 * 1024) warps >>= 1;
+        uint32_t* tally_global = nullptr;
+        size_t smem = per_warp * warps;
+        int blocks = (int)std::min<int64_t>((n + warps - 1) / warps, (int64_t)ctx->sm_count * (warps >= 4 ? 2 : 4));
+        if (smem > 200 * 1024) {  // tallies in global memory, one slice per resident warp
+            warps = 4;
+            smem = 0;
+            blocks = (int)std::min<int64_t>((n + warps - 1) / warps, (int64_t)ctx->sm_count * 4);
+            HSQ_CUDA(ctx, ctx->slow.ensure(per_warp * (size_t)blocks * warps + 16));
+            tally_global = ctx->slow.as<uint32_t>();
+        } else if (smem > 48 * 1024) {
+            HSQ_CUDA(ctx, cudaFuncSetAttribute(find_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        }
+        find_candidates_kernel<<<blocks, warps * 32, smem, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->q1.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), n, ix,
+                                                                         leading_quality, trailing_quality, candidate_limit, min_hit_ratio, o,
+                                                                         tally_global, ctx->status.as<int>());
+        ctx->launches++;
+        HSQ_CUDA(ctx, cudaGetLastError());
+        if ((rc = d2h(ctx, out->lead_trimmed, o.lead, nn))) return rc;
+        if ((rc = d2h(ctx, out->trail_trimmed, o.trail, nn))) return rc;
+        if ((rc = d2h(ctx, out->n_candidates, o.n_cand, nn))) return rc;
+        if ((rc = d2h(ctx, out->candidates, o.cand, nn * K))) return rc;
+        if ((rc = d2h(ctx, out->hits, o.hits, nn * K))) return rc;
+        if ((rc = d2h(ctx, out->has_n, o.has_n, nn))) return rc;
+        if ((rc = d2h(ctx, out->overflow, o.overflow, nn))) return rc;
+        if ((rc = d2h(ctx, out->order_dependent, o.order_dep, nn))) return rc;
+        HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_status, ctx->status.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if ((rc = timer.finish())) return rc;
+    if (n > 0 && ctx->h_status[0] != 0) return fail(ctx, ctx->h_status[0], "a read without N holds a character other than A, C, G, T");
+    return HSQ_OK;
+}

@@ -69,6 +69,11 @@ struct hsq_ctx {
     hsq::DevBuf dd_u8, dd_i32;  // hsq_dedup_extend_batch: dedup answers kept while the extend stage reuses the output buffers
     int64_t rg_n = -1;
     int32_t rg_contigs = 0;
+    // k-mer index of the sequences to find (hsq_set_find_sequences): refs of k-mer c are fi_refs[fi_start[c] .. + fi_len[c])
+    hsq::DevSeqsOwned fs;
+    hsq::DevBuf fi_start, fi_len, fi_refs, fi_size;
+    int64_t fi_n = -1;
+    int32_t fi_k = 0;
     // hsq_extend_batch pipelines chunks through  H2D | prep (encode, primer DP, bucket sorts) | capture DP | D2H  with three
     // complete buffer sets; the two sets not in the members above are parked here (see activate_extend_set)
     struct ExtendSet {

@@ -59,3 +59,34 @@ def dedup_flow(be, records, fastq, ext_uid_len, lig_uid_len, mark_duplicates=Fal
     ext = res.extend.head(m)
     rec = be.extend_records(written, ext, duplicate=duplicate)
     return {"pairs": pairs, "info": info, "dedup": res, "extended_pairs": written, "extend": ext, "records": rec}
+
+
+def find_flow(be, seqs, reads, quals, leading_quality=0, trailing_quality=0, allowed_mismatches=0, allowed_insertion_gaps=0,
+              allowed_insertion_bases=0, allowed_deletion_gaps=0, allowed_deletion_bases=0, max_candidates=16, cols_cap=640, md_cap=640):
+    """The per-entry decision of FastqFindAndTrimTool.findAndTrim (COMMON/fastqtool/FastqFindAndTrimTool.java:904-951):
+    quality trim -> N test -> SimpleMapper candidates (find_candidates) -> one alignment of the trimmed read (reference) with
+    every candidate sequence (query) under the default scorer -> the five count thresholds of the find settings.
+
+    `be` must have had set_find_sequences(seqs, ...) called.  Returns the candidate stage's result, the (read, candidate) list,
+    their alignments and `accepted` (one flag per listed alignment); matches of read k = the accepted rows with item_read == k,
+    in candidate order (1 row: single match, more: multiple matches, none: no match :953-985)."""
+    from ._abi import SeqBatch
+    cand = be.find_candidates(reads, quals, leading_quality, trailing_quality, max_candidates=max_candidates)
+    if cand.overflow.any():
+        raise OverflowError("a read has more candidates than max_candidates: call again with more slots")
+    item_read = np.repeat(np.arange(reads.n), cand.n_candidates)
+    mask = np.arange(cand.max_candidates)[None, :] < cand.n_candidates[:, None]
+    item_seq = cand.candidates[mask]
+    # the trimmed reads: rows of `reads` cut to [lead, len - trail)
+    a = reads.offsets[:-1] + cand.lead_trimmed
+    b = reads.offsets[1:] - cand.trail_trimmed
+    lens = (b - a)[item_read]
+    off = np.zeros(len(item_read) + 1, dtype=np.int64)
+    off[1:] = np.cumsum(lens)
+    src = np.repeat(a[item_read] - off[:-1], lens) + np.arange(int(off[-1]))
+    refs = SeqBatch(reads.data[src], off)
+    aln = be.align_batch(refs, seqs.take(item_seq), flags=0, cols_cap=cols_cap, md_cap=md_cap)
+    limits = np.array([allowed_mismatches, allowed_insertion_gaps, allowed_insertion_bases, allowed_deletion_gaps, allowed_deletion_bases])
+    accepted = (aln.find_counts <= limits[None, :]).all(axis=1) if len(item_read) else np.zeros(0, dtype=bool)
+    n_matches = np.bincount(item_read[accepted], minlength=reads.n)
+    return {"candidates": cand, "item_read": item_read, "item_seq": item_seq, "alignments": aln, "accepted": accepted, "n_matches": n_matches}

@@ -148,6 +148,21 @@ typedef struct hsq_candidates {
     const int32_t* cand_probe;
 } hsq_candidates;
 
+/* Per read results of hsq_find_candidates; slot arrays have max_candidates entries per read. */
+typedef struct hsq_find_out {
+    int32_t max_candidates;  /* in: slots per read */
+    int32_t* lead_trimmed;   /* trimReadBasedOnQuality: leading bases with quality < leading threshold */
+    int32_t* trail_trimmed;  /* ... trailing bases with quality < trailing threshold, never past the leading trim */
+    uint8_t* has_n;          /* 1: the trimmed read holds an N / n: the tool skips the entry (no candidates) */
+    int32_t* n_candidates;   /* candidates of the read (<= max_candidates) */
+    int32_t* candidates;     /* [n][max_candidates] rows of the sequences-to-find table, most hits first, ties by ascending row */
+    int32_t* hits;           /* [n][max_candidates] tally of each candidate */
+    uint8_t* overflow;       /* 1: more candidates than slots, call again with more slots */
+    uint8_t* order_dependent;/* 1: the walk stopped on the min-ratio test inside a group of equal tallies that also holds
+                              * passing entries, so the reference's list depends on its HashMap iteration order; the list
+                              * here is the one for ascending-row order */
+} hsq_find_out;
+
 /* Key record of the sharded dedup: what one pair contributes to the (probe, UID) grouping.
  * uid = 2 bit per base of R1[0:u] ++ R2[0:v]; rank orders the pairs of a group best first:
  * (32767 - (short)qualitySum) << 32 | (readIndex ^ 0x80000000)  (FilterByUid.java:281-297); origin identifies the pair
@@ -309,6 +324,22 @@ int32_t hsq_extend_selected(hsq_ctx* ctx, const hsq_pair_batch* pairs, const uin
 /* has_n[k] = 1 when read one or read two of pair k holds an 'N' or 'n': such pairs are not handed to the probe tasks
  * (readString.toLowerCase().contains("n"), …Identification.java:815-821). */
 int32_t hsq_flag_n_pairs(hsq_ctx* ctx, const hsq_pair_batch* pairs, uint8_t* has_n);
+
+/* SimpleMapper as FastqFindAndTrimTool builds it (COMMON/mapping/SimpleMapper.java:90-143,
+ * COMMON/fastqtool/FastqFindAndTrimTool.java:231-237): every k-mer of every sequence to find at start positions
+ * 0 .. size-k-1 (the last k-mer is not indexed, :93), reference and query spacing 1; a k-mer held by more than
+ * max_refs_per_kmer sequences is dropped from the index (:135-138; <= 0 = no cap).  Sequences must hold A/C/G/T only
+ * (NucleotideCode.getNucleotidesFromString throws otherwise: HSQ_ERR_BAD_CHARACTER) and be at least k long
+ * (IllegalStateException :98: HSQ_ERR_OUT_OF_RANGE).  1 <= k <= 12. */
+int32_t hsq_set_find_sequences(hsq_ctx* ctx, const hsq_seqs* seqs, int32_t kmer, int32_t max_refs_per_kmer);
+/* The per-read front half of FastqFindAndTrimTool.findAndTrim (FastqFindAndTrimTool.java:904-926): quality trim
+ * (trimReadBasedOnQuality :1188-1219, Phred+33), the N test on the trimmed read (:920) and
+ * SimpleMapper.getBestCandidateReferences (SimpleMapper.java:154-217) with the given candidate limit and hit ratio
+ * (10 and 0.5 in the tool).  The caller aligns each (trimmed read, candidate) with hsq_align_batch and applies the
+ * find_counts thresholds (:930-951).  A trimmed read without N that holds anything but A/C/G/T fails the call with
+ * HSQ_ERR_BAD_CHARACTER (the reference throws IllegalArgumentException on it). */
+int32_t hsq_find_candidates(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int32_t leading_quality,
+                            int32_t trailing_quality, int32_t candidate_limit, double min_hit_ratio, hsq_find_out* out);
 
 /* mergeSequences per item (…Identification.java:1362-1552, behind the unregistered --mergePairs option): lead + overlap
  * (per position the base with the higher quality wins, ties to upstream; a gap is filled with N / '!') + trail.

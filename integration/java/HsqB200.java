@@ -87,6 +87,9 @@ public final class HsqB200 implements AutoCloseable {
     private static final MethodHandle EXTEND_RECORDS = fn("hsq_extend_records", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
             ADDRESS, ADDRESS, JAVA_LONG));
     private static final MethodHandle FLAG_N = fn("hsq_flag_n_pairs", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle SET_FIND_SEQUENCES = fn("hsq_set_find_sequences", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT));
+    private static final MethodHandle FIND_CANDIDATES = fn("hsq_find_candidates", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, JAVA_INT,
+            JAVA_INT, JAVA_INT, JAVA_DOUBLE, ADDRESS));
     private static final MethodHandle MERGE_PAIRS = fn("hsq_merge_pairs", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS,
             ADDRESS, JAVA_LONG));
     private static final MethodHandle RESOLVE = fn("hsq_resolve_multi_probe", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
@@ -162,6 +165,15 @@ public final class HsqB200 implements AutoCloseable {
 
     /** hasN[k] = 1 when either read of pair k holds an N (…Identification.java:815-821): such pairs skip the probe tasks. */
     public void flagNPairs(MemorySegment pairBatch, MemorySegment hasN) { check(invokeInt(FLAG_N, ctx, pairBatch, hasN)); }
+
+    /** The SimpleMapper index of FastqFindAndTrimTool (FastqFindAndTrimTool.java:231-237): k = 5, at most 15000 sequences per k-mer. */
+    public void setFindSequences(MemorySegment seqs, int kmer, int maxRefsPerKmer) { check(invokeInt(SET_FIND_SEQUENCES, ctx, seqs, kmer, maxRefsPerKmer)); }
+
+    /** Quality trim, N test and getBestCandidateReferences per read (FastqFindAndTrimTool.java:904-926); findOut = hsq_find_out. */
+    public void findCandidates(MemorySegment reads, MemorySegment quals, int leadingQuality, int trailingQuality, int candidateLimit,
+                               double minHitRatio, MemorySegment findOut) {
+        check(invokeInt(FIND_CANDIDATES, ctx, reads, quals, leadingQuality, trailingQuality, candidateLimit, minHitRatio, findOut));
+    }
 
     /** mergeSequences per item (…Identification.java:1362-1552); ERR_OVERFLOW = call again with the sizes in outOffsets. */
     public int mergePairs(MemorySegment mergeBatch, MemorySegment outSeq, MemorySegment outQual, MemorySegment outOffsets, long outCap) {

@@ -2,6 +2,7 @@
 // C entry points with the same batch structs as include/hsq_b200.h so tests compare array to array.
 #include "hsq_oracle_heatseq.hpp"
 #include "hsq_oracle_assign.hpp"
+#include "hsq_oracle_find.hpp"
 #include "../include/hsq_b200.h"
 #include <cstring>
 #include <thread>
@@ -230,6 +231,19 @@ int32_t hsqo_assign_probes(const hsq_probe_ranges* pr, const hsq_mapped_records*
         return HSQ_ERR_INVALID_ARGUMENT;
     }
     return HSQ_OK;
+}
+
+// trimReadBasedOnQuality + SimpleMapper.getBestCandidateReferences per read (hsq_oracle_find.hpp)
+int32_t hsqo_find_candidates(const hsq_seqs* seqs, int32_t kmer, int32_t max_refs_per_kmer, const hsq_seqs* reads, const uint8_t* quals,
+                             int32_t leading_quality, int32_t trailing_quality, int32_t candidate_limit, double min_hit_ratio,
+                             hsq_find_out* out) {
+    try {
+        return find_candidates(seqs, kmer, max_refs_per_kmer, reads, quals, leading_quality, trailing_quality, candidate_limit,
+                               min_hit_ratio, out);
+    } catch (const std::exception& ex) {
+        g_err = ex.what();
+        return HSQ_ERR_INVALID_ARGUMENT;
+    }
 }
 
 // FilterByUid.reduceReadsByProbeAndUid over all probes (HSQ/process/FilterByUid.java:134-203) + findBestData (:281-297)

@@ -10,7 +10,7 @@ import subprocess
 import numpy as np
 
 from bioinformatics_b200 import _abi as A
-from bioinformatics_b200.batches import (AlignResult, AssignResult, ExtendResult, RecordResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
+from bioinformatics_b200.batches import (AlignResult, AssignResult, ExtendResult, FindResult, RecordResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
                                          merge_args, scorer)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -37,7 +37,7 @@ def lib():
         for name in ("hsqo_align_batch", "hsqo_trim_batch", "hsqo_dedup_batch", "hsqo_extend_batch",
                      "hsqo_resolve_multi_probe", "hsqo_primer_end", "hsqo_index_of_first_match_in_reference",
                      "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs", "hsqo_assign_probes",
-                     "hsqo_extend_records"):
+                     "hsqo_extend_records", "hsqo_find_candidates"):
             getattr(_lib, name).restype = C.c_int32
     return _lib
 
@@ -111,6 +111,20 @@ def assign_probes(ranges, records, max_probes=4):
     out = AssignResult(records.n, max_probes)
     pc, rc, oc = ranges.c(), records.c(), out.c()
     _check(lib().hsqo_assign_probes(C.byref(pc), C.byref(rc), C.byref(oc)))
+    return out
+
+
+def find_candidates(seqs, reads, quals, kmer=5, max_refs_per_kmer=15000, leading_quality=0, trailing_quality=0, candidate_limit=10,
+                    min_hit_ratio=0.5, max_candidates=16):
+    """trimReadBasedOnQuality + the N test + SimpleMapper.getBestCandidateReferences per read (hsq_oracle_find.hpp)."""
+    seqs = seqs if isinstance(seqs, A.SeqBatch) else A.SeqBatch.from_strings(seqs)
+    reads = reads if isinstance(reads, A.SeqBatch) else A.SeqBatch.from_strings(reads)
+    quals = quals if isinstance(quals, A.SeqBatch) else A.SeqBatch.from_strings(quals)
+    out = FindResult(reads.n, max_candidates)
+    sc, rc, oc = seqs.c(), reads.c(), out.c()
+    _check(lib().hsqo_find_candidates(C.byref(sc), C.c_int32(kmer), C.c_int32(max_refs_per_kmer), C.byref(rc), A.ptr(quals.data, A.u8p),
+                                      C.c_int32(leading_quality), C.c_int32(trailing_quality), C.c_int32(candidate_limit),
+                                      C.c_double(min_hit_ratio), C.byref(oc)))
     return out
 
 
