@@ -222,10 +222,108 @@ def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
         out["dedup_extend_mark_duplicates" if mark else "dedup_extend"] = {
             "read_pairs_per_s": pairs.n * world / dt, "ms_host_to_host": dt * 1e3, "pairs_extended_rank0": int(n_ext),
             "pairs_extended_ok_rank0": n_ok, "mode": mode}
+    if world == 1:
+        out.update(next_row_numbers(ctx, probes, pairs, res))
     try:
         out["hbm_peak_gbs"] = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
     except Exception:
         pass
+    return out
+
+
+def next_row_numbers(ctx, probes, pairs, res):
+    """SURVEY 8(f) rows at N = 1, host buffers in, host buffers out, each with the CPU oracle timed on a bounded sample beside it:
+    f1 read->probe assignment, f4 record fields, f3 candidate stage (+ the alignment filter of the listed candidates)."""
+    from bioinformatics_b200 import synth, flow
+    from bioinformatics_b200 import _abi as A
+    from oracle import oracle as O
+    O.build()
+    out = {}
+
+    def timed(fn, reps=2):
+        fn()
+        best = 1e30
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            r = fn()
+            best = min(best, time.perf_counter() - t0)
+        return best, r
+
+    # f1: two records per pair, 5 % with an alternative hit on both mates
+    ranges, records = synth.make_mapped_records(probes, pairs, seed=9)
+    ctx.set_probe_ranges(ranges)
+    dt, a = timed(lambda: ctx.assign_probes(records, 4))
+    sub = 200000
+    from bioinformatics_b200.batches import MappedRecordsHost
+    ao = records.alt_offsets
+    head = MappedRecordsHost(records.contig[:sub], records.negative_strand[:sub], records.second_of_pair[:sub], records.start[:sub],
+                             records.end[:sub], records.read_index[:sub],
+                             (ao[:sub + 1], records.alt_contig[:ao[sub]], records.alt_negative[:ao[sub]], records.alt_start[:ao[sub]],
+                              records.alt_stop[:ao[sub]]))
+    t0 = time.perf_counter()
+    O.assign_probes(ranges, head, 4)
+    dt_cpu = time.perf_counter() - t0
+    out["assign_probes"] = {"records_per_s": records.n / dt, "ms_host_to_host": dt * 1e3, "records": int(records.n),
+                            "paired_records": int((a.mate >= 0).sum()), "cpu_port_records_per_s": sub / dt_cpu,
+                            "cpu_sample": "%d records, 1 thread" % sub,
+                            "algorithmic_bytes_per_record": 22 + 8 + 4 * 4 * 2 + 13}
+    # f4: record fields of the pairs the fused call extended (res still holds the mark-duplicates run: every pair)
+    m = res.n_extended
+    written = pairs if m == pairs.n else pairs.subset(res.extended_pair[:m])
+    ext = res.extend.head(m)
+    dup = (1 - res.is_best[res.extended_pair[:m]]).astype(np.uint8)
+    from bioinformatics_b200.batches import RecordResult
+    rec = RecordResult(m, int(len(written.r1.data) + len(written.r2.data)))
+    for f in ("flag", "mate_pos", "offsets", "seq", "qual"):
+        q = ctx.pinned_array(getattr(rec, f).nbytes).view(getattr(rec, f).dtype)
+        setattr(rec, f, q)
+    dt, rec = timed(lambda: ctx.extend_records(written, ext, duplicate=dup, out=rec))
+    ms_dev = ctx.last_timing()[0]
+    sub = min(m, 100000)
+    t0 = time.perf_counter()
+    O.extend_records(probes, written.head(sub), duplicate=dup[:sub])
+    dt_cpu = time.perf_counter() - t0
+    out["extend_records"] = {"read_pairs_per_s": m / dt, "ms_host_to_host": dt * 1e3, "ms_device_incl_copies": ms_dev, "pairs": int(m),
+                             "record_bytes": int(rec.offsets[-1]), "cpu_port_read_pairs_per_s": sub / dt_cpu,
+                             "cpu_sample": "%d pairs, 1 thread; the port re-runs the extension to get the record fields" % sub}
+    # f3: the primers of the panel as sequences to find, read one of every pair as the FASTQ entries
+    seqs = A.SeqBatch.from_strings(probes.ext.strings() + probes.lig.strings())
+    ctx.set_find_sequences(seqs, 5, 15000)
+    dt, c = timed(lambda: ctx.find_candidates(pairs.r1, pairs.q1, 20, 20, max_candidates=16))
+    sub = 4000
+    t0 = time.perf_counter()
+    O.find_candidates(seqs, A.SeqBatch(pairs.r1.data, pairs.r1.offsets[:sub + 1]), A.SeqBatch(pairs.q1.data, pairs.q1.offsets[:sub + 1]),
+                      leading_quality=20, trailing_quality=20, max_candidates=16)
+    dt_cpu = time.perf_counter() - t0
+    out["find_candidates"] = {"reads_per_s": pairs.n / dt, "ms_host_to_host": dt * 1e3, "reads": int(pairs.n), "sequences_to_find": int(seqs.n),
+                              "candidates": int(c.n_candidates.sum()), "overflowed_reads": int(c.overflow.sum()),
+                              "cpu_port_reads_per_s": sub / dt_cpu, "cpu_sample": "%d reads, 1 thread" % sub}
+    sub = 250000
+    rs, qs = A.SeqBatch(pairs.r1.data, pairs.r1.offsets[:sub + 1]), A.SeqBatch(pairs.q1.data, pairs.q1.offsets[:sub + 1])
+    limits = (2, 1, 1, 1, 1)
+    dt, f = timed(lambda: ctx.find_matches(rs, qs, 20, 20, limits, max_candidates=64), reps=1)
+    ms_dev = ctx.last_timing()[0]
+    sub_cpu = 1500
+    rc_, qc_ = A.SeqBatch(pairs.r1.data, pairs.r1.offsets[:sub_cpu + 1]), A.SeqBatch(pairs.q1.data, pairs.q1.offsets[:sub_cpu + 1])
+
+    class _Port:  # the same decision over the CPU port: candidates, then one alignment per candidate
+        def find_candidates(self, reads, quals, lq, tq, max_candidates=16):
+            return O.find_candidates(seqs, reads, quals, leading_quality=lq, trailing_quality=tq, max_candidates=max_candidates)
+
+        def align_batch(self, refs, qrys, flags=0, cols_cap=640, md_cap=640):
+            return O.align_batch(refs, qrys, flags=flags, cols_cap=cols_cap, md_cap=md_cap, nthreads=1)
+
+    t0 = time.perf_counter()
+    fo = flow.find_flow(_Port(), seqs, rc_, qc_, 20, 20, *limits, max_candidates=64)
+    dt_cpu = time.perf_counter() - t0
+    same = bool((fo["n_matches"] == f.n_matches[:sub_cpu]).all())
+    out["find_matches"] = {"reads_per_s": sub / dt, "ms_host_to_host": dt * 1e3, "ms_device_incl_copies": ms_dev, "reads": sub,
+                           "alignments": int(f.cand.n_candidates.sum()), "gcups": f.cells / dt / 1e9,
+                           "single_match_reads": int((f.n_matches == 1).sum()), "multiple_match_reads": int((f.n_matches > 1).sum()),
+                           "cpu_port_reads_per_s": sub_cpu / dt_cpu, "cpu_sample": "%d reads, 1 thread" % sub_cpu,
+                           "equals_cpu_port_on_sample": same,
+                           "note": "hsq_find_matches: candidates + one alignment per candidate + the five limits in one call; slot arrays "
+                                   "(64 per read) returned to pageable host memory"}
     return out
 
 

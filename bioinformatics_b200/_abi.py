@@ -96,6 +96,15 @@ class FindOut(C.Structure):
                 ("candidates", i32p), ("hits", i32p), ("overflow", u8p), ("order_dependent", u8p)]
 
 
+class FindLimits(C.Structure):
+    _fields_ = [("mismatches", C.c_int32), ("insertion_gaps", C.c_int32), ("insertion_bases", C.c_int32), ("deletion_gaps", C.c_int32),
+                ("deletion_bases", C.c_int32)]
+
+
+class FindMatchOut(C.Structure):
+    _fields_ = [("cand", FindOut), ("counts", i32p), ("accepted", u8p), ("n_matches", i32p), ("cells", C.c_int64)]
+
+
 ASSIGN_UNPAIRED, ASSIGN_AMBIGUOUS_NAME, ASSIGN_IGNORED = -1, -2, -3
 
 

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 from . import _abi as A
-from .batches import (AlignResult, AssignResult, FindResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
+from .batches import (AlignResult, AssignResult, FindResult, FindMatchResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
                       ProbeTableHost, merge_args, scorer)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
@@ -21,7 +21,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
            "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs",
-           "hsq_set_find_sequences", "hsq_find_candidates")
+           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches")
 
 
 class HsqError(RuntimeError):
@@ -179,11 +179,12 @@ class Context:
         self._check(st)
         return int(m.value), lst, out
 
-    def extend_records(self, pairs: PairBatchHost, ext: ExtendResult, duplicate=None, out_cap=None):
-        """hsq_extend_records: FLAG / PNEXT / read string / qualities of the records of the pairs `ext` extended."""
-        cap = out_cap if out_cap is not None else int(len(pairs.r1.data) + len(pairs.r2.data))
+    def extend_records(self, pairs: PairBatchHost, ext: ExtendResult, duplicate=None, out_cap=None, out=None):
+        """hsq_extend_records: FLAG / PNEXT / read string / qualities of the records of the pairs `ext` extended.
+        out: optional RecordResult to write into (e.g. with pinned arrays)."""
+        cap = out.cap if out is not None else out_cap if out_cap is not None else int(len(pairs.r1.data) + len(pairs.r2.data))
         dup = None if duplicate is None else np.ascontiguousarray(duplicate, dtype=np.uint8)
-        out = RecordResult(pairs.n, cap)
+        out = out if out is not None else RecordResult(pairs.n, cap)
         pc, ec, oc = pairs.c(), ext.c(), out.c()
         self._check(self.lib.hsq_extend_records(self.h, C.byref(pc), C.byref(ec), A.ptr(dup, A.u8p), C.byref(oc), C.c_int64(cap)))
         return out
@@ -233,6 +234,21 @@ class Context:
         rc, oc = reads.c(), out.c()
         self._check(self.lib.hsq_find_candidates(self.h, C.byref(rc), A.ptr(quals.data, A.u8p), C.c_int32(leading_quality),
                                                  C.c_int32(trailing_quality), C.c_int32(candidate_limit), C.c_double(min_hit_ratio), C.byref(oc)))
+        return out
+
+    def find_matches(self, reads, quals, leading_quality=0, trailing_quality=0, limits=(0, 0, 0, 0, 0), candidate_limit=10, min_hit_ratio=0.5,
+                     max_candidates=16):
+        """hsq_find_matches: candidates, one alignment per candidate and the five-limit test, all on the device.
+        limits = (mismatches, insertion gaps, insertion bases, deletion gaps, deletion bases)."""
+        reads = reads if isinstance(reads, A.SeqBatch) else A.SeqBatch.from_strings(reads)
+        quals = quals if isinstance(quals, A.SeqBatch) else A.SeqBatch.from_strings(quals)
+        assert (quals.offsets == reads.offsets).all(), "qualities must match the reads' lengths"
+        out = FindMatchResult(reads.n, max_candidates)
+        rc, oc, lc = reads.c(), out.c(), A.FindLimits(*[int(v) for v in limits])
+        st = self.lib.hsq_find_matches(self.h, C.byref(rc), A.ptr(quals.data, A.u8p), C.c_int32(leading_quality), C.c_int32(trailing_quality),
+                                       C.c_int32(candidate_limit), C.c_double(min_hit_ratio), C.byref(lc), C.byref(oc))
+        out.finish()
+        self._check(st)
         return out
 
     def dedup_keys(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, n_probes, origin_base, d_keys_ptr):

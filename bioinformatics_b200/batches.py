@@ -352,6 +352,27 @@ class FindResult:
         return [[(int(self.candidates[k, j]), int(self.hits[k, j])) for j in range(self.n_candidates[k])] for k in range(self.n)]
 
 
+class FindMatchResult:
+    """hsq_find_match_out with host arrays."""
+
+    def __init__(self, n, max_candidates=16):
+        self.n, self.max_candidates = n, max_candidates
+        self.cand = FindResult(n, max_candidates)
+        self.counts = np.zeros((n, max_candidates, 5), dtype=np.int32)
+        self.accepted = np.zeros((n, max_candidates), dtype=np.uint8)
+        self.n_matches = np.zeros(n, dtype=np.int32)
+        self.cells = 0
+        self._c = None
+
+    def c(self):
+        self._c = A.FindMatchOut(self.cand.c(), A.ptr(self.counts, A.i32p), A.ptr(self.accepted, A.u8p), A.ptr(self.n_matches, A.i32p), 0)
+        return self._c
+
+    def finish(self):
+        self.cells = int(self._c.cells)
+        return self
+
+
 def scorer(match=1, mismatch=-4, gap_extend=-1, gap_start=-6):
     """SimpleAlignmentScorer defaults (COMMON/alignment/SimpleAlignmentScorer.java:23-26)."""
     return A.Scorer(match, mismatch, gap_extend, gap_start)

@@ -145,9 +145,13 @@ extern "C" int32_t hsq_set_find_sequences(hsq_ctx* ctx, const hsq_seqs* seqs, in
     find_row_len_kernel<<<kblocks, 256, 0, ctx->stream>>>(per_kmer, rows, max_refs_per_kmer, ctx->fi_len.as<int32_t>());
     ctx->launches++;
     HSQ_CUDA(ctx, cudaGetLastError());
+    if ((rc = encode_seqs(ctx, &ctx->fs, d_status(ctx), d_maxlen(ctx, 1)))) return rc;  // codes for hsq_find_matches' alignments
+    int w[3];
+    if ((rc = read_status(ctx, w, 3))) return rc;
     if ((rc = timer.finish())) return rc;
     ctx->fi_n = R;
     ctx->fi_k = kmer;
+    ctx->fi_max_len = w[2];
     return HSQ_OK;
 }
 
@@ -271,6 +275,115 @@ __global__ void find_candidates_kernel(const uint8_t* __restrict__ reads, const 
     }
 }
 
+// per item (read r, candidate slot j): NeedlemanWunschGlobalAlignment(trimmed read, candidate) with the default scorer, the five
+// counters over the query-trimmed alignment and the limit test (FastqFindAndTrimTool.java:930-951)
+__global__ void __launch_bounds__(DP_BLOCK) find_align_kernel(DeviceSeqs reads, DeviceSeqs seqs, const int32_t* __restrict__ item_read,
+                                                         const int64_t* __restrict__ item_off, int64_t n_items, FindDeviceOut o, ScoreParams sp,
+                                                         hsq_find_limits lim, ScratchPool pool, int32_t* __restrict__ counts,
+                                                         uint8_t* __restrict__ accepted, int32_t* __restrict__ n_matches,
+                                                         unsigned long long* cells_total) {
+    __shared__ int4 prof[PROF_INT4_PER_THREAD * DP_BLOCK];
+    DpScratch sc = thread_scratch(pool, prof);
+    int64_t cells = 0;
+    for (int64_t i = sc.tid; i < n_items; i += sc.nthreads) {
+        const int64_t r = item_read[i];
+        const int64_t slot = r * o.K + (i - item_off[r]);
+        const int32_t cand = o.cand[slot];
+        const int64_t r0 = reads.offsets[r] + o.lead[r], q0 = seqs.offsets[cand];
+        SeqView ref = make_view(reads.codes + r0, (int)(reads.offsets[r + 1] - reads.offsets[r]) - o.lead[r] - o.trail[r], false, false);
+        SeqView qry = make_view(seqs.codes + q0, (int)(seqs.offsets[cand + 1] - q0), false, false);
+        dp_fill(ref, qry, sp, 0, 0, sc);
+        cells += (int64_t)ref.len * qry.len;
+        Columns cv{sc.colstore(), dp_traceback(ref, qry, sc)};
+        PairIndices ix = pair_indices(cv);
+        int32_t fc[5];
+        find_counters(cv, ix, fc);
+        for (int f = 0; f < 5; f++) counts[slot * 5 + f] = fc[f];
+        const bool ok = fc[0] <= lim.mismatches && fc[1] <= lim.insertion_gaps && fc[2] <= lim.insertion_bases && fc[3] <= lim.deletion_gaps &&
+                        fc[4] <= lim.deletion_bases;
+        accepted[slot] = ok ? 1 : 0;
+        if (ok) atomicAdd(&n_matches[r], 1);
+    }
+    for (int d = 16; d > 0; d >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, d);
+    if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
+}
+
+__global__ void find_item_counts_kernel(const int32_t* __restrict__ n_cand, int64_t n, int64_t* __restrict__ out) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride) out[k] = n_cand[k];
+}
+
+__global__ void find_items_kernel(const int64_t* __restrict__ item_off, int64_t n, int32_t* __restrict__ item_read) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n; r += stride)
+        for (int64_t i = item_off[r]; i < item_off[r + 1]; i++) item_read[i] = (int32_t)r;
+}
+
+// uploads the reads, runs the candidate kernel (results stay on the device in `o`) and the encoder: new
+// IupacNucleotideCodeSequence(readString) (:906) throws on a byte that is no IUPAC code, wherever it sits in the read
+int find_run_candidates(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int lead_q, int trail_q, int limit, double ratio, int32_t K,
+                        bool encode, FindDeviceOut* o) {
+    const int64_t n = reads->n;
+    int rc;
+    if ((rc = reset_status(ctx))) return rc;
+    if ((rc = copy_seqs(ctx, reads, &ctx->r1))) return rc;
+    const size_t total = (size_t)ctx->r1.total, nn = (size_t)n, kk = (size_t)K;
+    if (total > 0 && !quals) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null qualities");
+    HSQ_CUDA(ctx, ctx->q1.ensure(total + 16));
+    if (total > 0) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q1.p, quals + reads->offsets[0], total, cudaMemcpyHostToDevice, ctx->stream));
+    HSQ_CUDA(ctx, ctx->out_i32.ensure((3 * nn + 2 * nn * kk) * 4 + 16));
+    HSQ_CUDA(ctx, ctx->out_u8.ensure(3 * nn + 16));
+    o->K = K;
+    o->lead = ctx->out_i32.as<int32_t>();
+    o->trail = o->lead + nn;
+    o->n_cand = o->trail + nn;
+    o->cand = o->n_cand + nn;
+    o->hits = o->cand + nn * kk;
+    o->has_n = ctx->out_u8.as<uint8_t>();
+    o->overflow = o->has_n + nn;
+    o->order_dep = o->overflow + nn;
+    if (n == 0) return HSQ_OK;
+    FindIndex ix{ctx->fi_start.as<int64_t>(), ctx->fi_len.as<int32_t>(), ctx->fi_refs.as<int32_t>(), ctx->fi_size.as<int32_t>(), (int32_t)ctx->fi_n,
+                 ctx->fi_k};
+    const size_t per_warp = (size_t)ctx->fi_n * 4;
+    int warps = 8;
+    while (warps > 1 && per_warp * warps > 96 * 1024) warps >>= 1;
+    uint32_t* tally_global = nullptr;
+    size_t smem = per_warp * warps;
+    int blocks = (int)std::min<int64_t>((n + warps - 1) / warps, (int64_t)ctx->sm_count * (warps >= 4 ? 2 : 4));
+    if (smem > 200 * 1024) {  // tallies in global memory, one slice per resident warp
+        warps = 4;
+        smem = 0;
+        blocks = (int)std::min<int64_t>((n + warps - 1) / warps, (int64_t)ctx->sm_count * 4);
+        HSQ_CUDA(ctx, ctx->slow.ensure(per_warp * (size_t)blocks * warps + 16));
+        tally_global = ctx->slow.as<uint32_t>();
+    } else if (smem > 48 * 1024) {
+        HSQ_CUDA(ctx, cudaFuncSetAttribute(find_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    }
+    find_candidates_kernel<<<blocks, warps * 32, smem, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->q1.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), n, ix,
+                                                                     lead_q, trail_q, limit, ratio, *o, tally_global, ctx->status.as<int>());
+    ctx->launches++;
+    HSQ_CUDA(ctx, cudaGetLastError());
+    if (encode && (rc = encode_seqs(ctx, &ctx->r1, d_status(ctx), d_maxlen(ctx, 0)))) return rc;
+    return HSQ_OK;
+}
+
+int find_fetch_candidates(hsq_ctx* ctx, const FindDeviceOut& o, int64_t n, hsq_find_out* out) {
+    const size_t nn = (size_t)n, kk = (size_t)o.K;
+    int rc;
+    if ((rc = d2h(ctx, out->lead_trimmed, o.lead, nn))) return rc;
+    if ((rc = d2h(ctx, out->trail_trimmed, o.trail, nn))) return rc;
+    if ((rc = d2h(ctx, out->n_candidates, o.n_cand, nn))) return rc;
+    if ((rc = d2h(ctx, out->candidates, o.cand, nn * kk))) return rc;
+    if ((rc = d2h(ctx, out->hits, o.hits, nn * kk))) return rc;
+    if ((rc = d2h(ctx, out->has_n, o.has_n, nn))) return rc;
+    if ((rc = d2h(ctx, out->overflow, o.overflow, nn))) return rc;
+    if ((rc = d2h(ctx, out->order_dependent, o.order_dep, nn))) return rc;
+    return HSQ_OK;
+}
+
 }  // namespace
 
 extern "C" int32_t hsq_find_candidates(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int32_t leading_quality,
@@ -278,62 +391,85 @@ extern "C" int32_t hsq_find_candidates(hsq_ctx* ctx, const hsq_seqs* reads, cons
     if (!ctx || !reads || !out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
     if (ctx->fi_n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_set_find_sequences first");
     if (out->max_candidates < 1) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "max_candidates must be positive");
-    const int64_t n = reads->n;
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
-    int rc;
-    if ((rc = reset_status(ctx))) return rc;
-    if ((rc = copy_seqs(ctx, reads, &ctx->r1))) return rc;
-    const size_t total = (size_t)ctx->r1.total, nn = (size_t)n, K = (size_t)out->max_candidates;
-    if (total > 0 && !quals) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null qualities");
-    HSQ_CUDA(ctx, ctx->q1.ensure(total + 16));
-    if (total > 0) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q1.p, quals + reads->offsets[0], total, cudaMemcpyHostToDevice, ctx->stream));
-    HSQ_CUDA(ctx, ctx->out_i32.ensure((3 * nn + 2 * nn * K) * 4 + 16));
-    HSQ_CUDA(ctx, ctx->out_u8.ensure(3 * nn + 16));
     FindDeviceOut o;
-    o.K = (int32_t)K;
-    o.lead = ctx->out_i32.as<int32_t>();
-    o.trail = o.lead + nn;
-    o.n_cand = o.trail + nn;
-    o.cand = o.n_cand + nn;
-    o.hits = o.cand + nn * K;
-    o.has_n = ctx->out_u8.as<uint8_t>();
-    o.overflow = o.has_n + nn;
-    o.order_dep = o.overflow + nn;
-    if (n > 0) {
-        FindIndex ix{ctx->fi_start.as<int64_t>(), ctx->fi_len.as<int32_t>(), ctx->fi_refs.as<int32_t>(), ctx->fi_size.as<int32_t>(), (int32_t)ctx->fi_n,
-                     ctx->fi_k};
-        const size_t per_warp = (size_t)ctx->fi_n * 4;
-        int warps = 8;
-        while (warps > 1 && per_warp * warps > 96 * 1024) warps >>= 1;
-        uint32_t* tally_global = nullptr;
-        size_t smem = per_warp * warps;
-        int blocks = (int)std::min<int64_t>((n + warps - 1) / warps, (int64_t)ctx->sm_count * (warps >= 4 ? 2 : 4));
-        if (smem > 200 * 1024) {  // tallies in global memory, one slice per resident warp
-            warps = 4;
-            smem = 0;
-            blocks = (int)std::min<int64_t>((n + warps - 1) / warps, (int64_t)ctx->sm_count * 4);
-            HSQ_CUDA(ctx, ctx->slow.ensure(per_warp * (size_t)blocks * warps + 16));
-            tally_global = ctx->slow.as<uint32_t>();
-        } else if (smem > 48 * 1024) {
-            HSQ_CUDA(ctx, cudaFuncSetAttribute(find_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        }
-        find_candidates_kernel<<<blocks, warps * 32, smem, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->q1.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), n, ix,
-                                                                         leading_quality, trailing_quality, candidate_limit, min_hit_ratio, o,
-                                                                         tally_global, ctx->status.as<int>());
-        ctx->launches++;
-        HSQ_CUDA(ctx, cudaGetLastError());
-        if ((rc = d2h(ctx, out->lead_trimmed, o.lead, nn))) return rc;
-        if ((rc = d2h(ctx, out->trail_trimmed, o.trail, nn))) return rc;
-        if ((rc = d2h(ctx, out->n_candidates, o.n_cand, nn))) return rc;
-        if ((rc = d2h(ctx, out->candidates, o.cand, nn * K))) return rc;
-        if ((rc = d2h(ctx, out->hits, o.hits, nn * K))) return rc;
-        if ((rc = d2h(ctx, out->has_n, o.has_n, nn))) return rc;
-        if ((rc = d2h(ctx, out->overflow, o.overflow, nn))) return rc;
-        if ((rc = d2h(ctx, out->order_dependent, o.order_dep, nn))) return rc;
-        HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_status, ctx->status.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    int rc;
+    if ((rc = find_run_candidates(ctx, reads, quals, leading_quality, trailing_quality, candidate_limit, min_hit_ratio, out->max_candidates, true, &o)))
+        return rc;
+    int w[1] = {0};
+    if (reads->n > 0) {
+        if ((rc = find_fetch_candidates(ctx, o, reads->n, out))) return rc;
+        if ((rc = read_status(ctx, w, 1))) return rc;
     }
     if ((rc = timer.finish())) return rc;
-    if (n > 0 && ctx->h_status[0] != 0) return fail(ctx, ctx->h_status[0], "a read without N holds a character other than A, C, G, T");
+    if (w[0] != 0) return fail(ctx, w[0], "a read without N holds a character other than A, C, G, T");
+    return HSQ_OK;
+}
+
+extern "C" int32_t hsq_find_matches(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int32_t leading_quality, int32_t trailing_quality,
+                                    int32_t candidate_limit, double min_hit_ratio, const hsq_find_limits* limits, hsq_find_match_out* out) {
+    if (!ctx || !reads || !out || !limits) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (ctx->fi_n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_set_find_sequences first");
+    const int32_t K = out->cand.max_candidates;
+    if (K < 1) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "max_candidates must be positive");
+    const int64_t n = reads->n;
+    const size_t nn = (size_t)n, kk = (size_t)K;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    FindDeviceOut o;
+    int rc;
+    out->cells = 0;
+    if ((rc = find_run_candidates(ctx, reads, quals, leading_quality, trailing_quality, candidate_limit, min_hit_ratio, K, true, &o))) return rc;
+    if (n == 0) return timer.finish();
+    // item list: candidate slots of all reads in read order
+    const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
+    HSQ_CUDA(ctx, ctx->sort_a.ensure((nn + 1) * 8));
+    HSQ_CUDA(ctx, ctx->sort_b.ensure((nn + 1) * 8));
+    HSQ_CUDA(ctx, ctx->misc.ensure((size_t)n_tiles * 8 + 64));
+    HSQ_CUDA(ctx, ctx->dd_i32.ensure((nn * kk * 5 + nn) * 4 + 16));
+    HSQ_CUDA(ctx, ctx->dd_u8.ensure(nn * kk + 16));
+    int64_t* cnt = ctx->sort_a.as<int64_t>();
+    int64_t* item_off = ctx->sort_b.as<int64_t>();
+    int32_t* counts = ctx->dd_i32.as<int32_t>();
+    int32_t* n_matches = counts + nn * kk * 5;
+    uint8_t* accepted = ctx->dd_u8.as<uint8_t>();
+    const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+    find_item_counts_kernel<<<gblocks, 256, 0, ctx->stream>>>(o.n_cand, n, cnt);
+    ctx->launches++;
+    if ((rc = scan_i64(ctx, cnt, n, ctx->misc.as<int64_t>(), item_off))) return rc;
+    HSQ_CUDA(ctx, cudaMemsetAsync(counts, 0, (nn * kk * 5 + nn) * 4, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemsetAsync(accepted, 0, nn * kk, ctx->stream));
+    int64_t* h_m = reinterpret_cast<int64_t*>(ctx->h_cells) + 1;  // pinned
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_m, item_off + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    int w[4];
+    if ((rc = read_status(ctx, w, 2))) return rc;
+    if (w[0] != 0) return fail(ctx, w[0], "a read without N holds a character other than A, C, G, T");
+    const int64_t n_items = *h_m;
+    const int r_max = w[1];
+    if (n_items > 0) {
+        HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)n_items * 4 + 16));
+        int32_t* item_read = ctx->sort_c.as<int32_t>();
+        find_items_kernel<<<gblocks, 256, 0, ctx->stream>>>(item_off, n, item_read);
+        ctx->launches++;
+        int grid = 1;
+        if ((rc = persistent_grid(ctx, find_align_kernel, DP_BLOCK, n_items, &grid))) return rc;
+        ScratchPool pool;
+        if ((rc = alloc_scratch(ctx, (int64_t)grid * DP_BLOCK, 0, ctx->fi_max_len, r_max, &pool, nullptr))) return rc;
+        ScoreParams sp = make_score_params(1, -4, -1, -6);  // new SimpleAlignmentScorer() (SimpleAlignmentScorer.java:23-26,35-43)
+        find_align_kernel<<<grid, DP_BLOCK, 0, ctx->stream>>>(ctx->r1.view(), ctx->fs.view(), item_read, item_off, n_items, o, sp, *limits, pool, counts,
+                                                             accepted, n_matches, ctx->cells.as<unsigned long long>());
+        ctx->launches++;
+        HSQ_CUDA(ctx, cudaGetLastError());
+    }
+    if ((rc = find_fetch_candidates(ctx, o, n, &out->cand))) return rc;
+    if ((rc = d2h(ctx, out->counts, counts, nn * kk * 5))) return rc;
+    if ((rc = d2h(ctx, out->accepted, accepted, nn * kk))) return rc;
+    if ((rc = d2h(ctx, out->n_matches, n_matches, nn))) return rc;
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if ((rc = timer.finish())) return rc;
+    out->cells = (int64_t)ctx->h_cells[0];
+    for (size_t k = 0; k < nn; k++)
+        if (out->cand.overflow[k]) return fail(ctx, HSQ_ERR_OVERFLOW, "a read has more candidates than slots; see the overflow flags");
     return HSQ_OK;
 }

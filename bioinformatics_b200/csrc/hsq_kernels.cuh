@@ -164,6 +164,22 @@ struct AlignDeviceOut {
     int32_t* find_counts;  // [n][5] or null
 };
 
+// The five counters FastqFindAndTrimTool filters on (FastqFindAndTrimTool.java:932-938) over the columns [first_q .. last_q] of
+// getAlignmentWithoutEndingAndBeginningQueryInserts (AlignmentPair.java:95-99; empty when the query has no base: subSequence
+// clamps): mismatches, insertion gaps / bases, deletion gaps / bases relative to the reference (AlignmentPair.java:190-256).
+__device__ inline void find_counters(const Columns& cv, const PairIndices& ix, int32_t* fc) {
+    int fx = 0, ig = 0, ib = 0, dg = 0, db = 0;
+    bool in_i = false, in_d = false;
+    for (int c = max(ix.first_q, 0); c <= ix.last_q && c < cv.n; c++) {
+        const uint32_t w = cv.fwd(c);
+        const uint32_t r = col_ref(w), q = col_qry(w);
+        if (r == CODE_GAP) { ib++; if (!in_i) ig++; in_i = true; } else in_i = false;
+        if (q == CODE_GAP) { db++; if (!in_d) dg++; in_d = true; } else in_d = false;
+        if (r != CODE_GAP && q != CODE_GAP && !codes_match(r, q)) fx++;
+    }
+    fc[0] = fx; fc[1] = ig; fc[2] = ib; fc[3] = dg; fc[4] = db;
+}
+
 // Operator seam: NeedlemanWunschGlobalAlignment + AlignmentPair getters, one alignment per thread.
 __global__ void __launch_bounds__(DP_BLOCK) align_kernel(DeviceSeqs refs, DeviceSeqs qrys, int64_t n, ScoreParams sp, int pen_start,
                                                     int pen_end, ScratchPool pool, AlignDeviceOut out, int* status,
@@ -190,19 +206,7 @@ __global__ void __launch_bounds__(DP_BLOCK) align_kernel(DeviceSeqs refs, Device
         out.matches[k] = m;
         out.mismatches[k] = x;
         out.non_terminal_gaps[k] = non_terminal_gaps(cv, ix);
-        if (out.find_counts) {  // over columns [first_q .. last_q] (empty when the query has no base: subSequence clamps)
-            int fx = 0, ig = 0, ib = 0, dg = 0, db = 0;
-            bool in_i = false, in_d = false;
-            for (int c = max(ix.first_q, 0); c <= ix.last_q && c < cv.n; c++) {
-                const uint32_t w = cv.fwd(c);
-                const uint32_t r = col_ref(w), q = col_qry(w);
-                if (r == CODE_GAP) { ib++; if (!in_i) ig++; in_i = true; } else in_i = false;
-                if (q == CODE_GAP) { db++; if (!in_d) dg++; in_d = true; } else in_d = false;
-                if (r != CODE_GAP && q != CODE_GAP && !codes_match(r, q)) fx++;
-            }
-            int32_t* fc = out.find_counts + 5 * k;
-            fc[0] = fx; fc[1] = ig; fc[2] = ib; fc[3] = dg; fc[4] = db;
-        }
+        if (out.find_counts) find_counters(cv, ix, out.find_counts + 5 * k);
         uint8_t ovf = cv.n > out.cols_cap ? 1 : 0;
         for (int c = 0; c < cv.n && c < out.cols_cap; c++) {
             uint32_t w = cv.fwd(c);

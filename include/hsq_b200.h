@@ -163,6 +163,21 @@ typedef struct hsq_find_out {
                               * here is the one for ascending-row order */
 } hsq_find_out;
 
+/* The five limits of the find settings (FastqToolFindSettings: allowed mismatch bases, insertion gaps / bases, deletion
+ * gaps / bases; COMMON/fastqtool/FastqFindAndTrimTool.java:940-949). */
+typedef struct hsq_find_limits {
+    int32_t mismatches, insertion_gaps, insertion_bases, deletion_gaps, deletion_bases;
+} hsq_find_limits;
+
+/* Results of hsq_find_matches: the candidate stage's arrays plus, per candidate slot, the alignment's counters and verdict. */
+typedef struct hsq_find_match_out {
+    hsq_find_out cand;
+    int32_t* counts;     /* [n][max_candidates][5]: mismatches, insertion gaps, insertion bases, deletion gaps, deletion bases */
+    uint8_t* accepted;   /* [n][max_candidates] 1: all five counters within the limits (isAcceptable :947) */
+    int32_t* n_matches;  /* matches.size() of the read: 0 no match, 1 single match, > 1 multiple matches (:953-985) */
+    int64_t cells;       /* out: DP cells computed */
+} hsq_find_match_out;
+
 /* Key record of the sharded dedup: what one pair contributes to the (probe, UID) grouping.
  * uid = 2 bit per base of R1[0:u] ++ R2[0:v]; rank orders the pairs of a group best first:
  * (32767 - (short)qualitySum) << 32 | (readIndex ^ 0x80000000)  (FilterByUid.java:281-297); origin identifies the pair
@@ -340,6 +355,13 @@ int32_t hsq_set_find_sequences(hsq_ctx* ctx, const hsq_seqs* seqs, int32_t kmer,
  * HSQ_ERR_BAD_CHARACTER (the reference throws IllegalArgumentException on it). */
 int32_t hsq_find_candidates(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int32_t leading_quality,
                             int32_t trailing_quality, int32_t candidate_limit, double min_hit_ratio, hsq_find_out* out);
+
+/* hsq_find_candidates followed, on the device, by one NeedlemanWunschGlobalAlignment(trimmed read, candidate) under the
+ * default SimpleAlignmentScorer for every listed candidate and the five-limit test (FastqFindAndTrimTool.java:926-951):
+ * the whole per-entry decision of findAndTrim in one call.  A read with more candidates than slots makes the call return
+ * HSQ_ERR_OVERFLOW (its overflow flag is set; the listed candidates are still evaluated). */
+int32_t hsq_find_matches(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int32_t leading_quality, int32_t trailing_quality,
+                         int32_t candidate_limit, double min_hit_ratio, const hsq_find_limits* limits, hsq_find_match_out* out);
 
 /* mergeSequences per item (…Identification.java:1362-1552, behind the unregistered --mergePairs option): lead + overlap
  * (per position the base with the higher quality wins, ties to upstream; a gap is filled with N / '!') + trail.

@@ -90,6 +90,8 @@ public final class HsqB200 implements AutoCloseable {
     private static final MethodHandle SET_FIND_SEQUENCES = fn("hsq_set_find_sequences", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT));
     private static final MethodHandle FIND_CANDIDATES = fn("hsq_find_candidates", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, JAVA_INT,
             JAVA_INT, JAVA_INT, JAVA_DOUBLE, ADDRESS));
+    private static final MethodHandle FIND_MATCHES = fn("hsq_find_matches", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, JAVA_INT,
+            JAVA_INT, JAVA_INT, JAVA_DOUBLE, ADDRESS, ADDRESS));
     private static final MethodHandle MERGE_PAIRS = fn("hsq_merge_pairs", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS,
             ADDRESS, JAVA_LONG));
     private static final MethodHandle RESOLVE = fn("hsq_resolve_multi_probe", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
@@ -173,6 +175,12 @@ public final class HsqB200 implements AutoCloseable {
     public void findCandidates(MemorySegment reads, MemorySegment quals, int leadingQuality, int trailingQuality, int candidateLimit,
                                double minHitRatio, MemorySegment findOut) {
         check(invokeInt(FIND_CANDIDATES, ctx, reads, quals, leadingQuality, trailingQuality, candidateLimit, minHitRatio, findOut));
+    }
+
+    /** findCandidates + one alignment per candidate + the five limits (FastqFindAndTrimTool.java:926-951); limits = hsq_find_limits. */
+    public void findMatches(MemorySegment reads, MemorySegment quals, int leadingQuality, int trailingQuality, int candidateLimit,
+                            double minHitRatio, MemorySegment limits, MemorySegment findMatchOut) {
+        check(invokeInt(FIND_MATCHES, ctx, reads, quals, leadingQuality, trailingQuality, candidateLimit, minHitRatio, limits, findMatchOut));
     }
 
     /** mergeSequences per item (…Identification.java:1362-1552); ERR_OVERFLOW = call again with the sizes in outOffsets. */

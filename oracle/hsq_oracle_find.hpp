@@ -15,6 +15,7 @@
 #include <string>
 #include <vector>
 #include "../include/hsq_b200.h"
+#include "hsq_oracle_core.hpp"
 
 namespace hsqo {
 
@@ -108,6 +109,8 @@ inline int32_t find_candidates(const hsq_seqs* seqs, int k, int max_refs, const 
         const int64_t a = reads->offsets[r], len = reads->offsets[r + 1] - a;
         const std::string read((const char*)reads->data + a, (size_t)len);
         const uint8_t* q = quals + a;
+        for (char c : read)  // new IupacNucleotideCodeSequence(record.getReadString()) :906
+            if (encode_char(c) < 0) status = HSQ_ERR_BAD_CHARACTER;
         // trimReadBasedOnQuality (FastqFindAndTrimTool.java:1194-1214)
         int lead = 0;
         while (lead < len && ((int)q[lead] - 33) < lead_q) lead++;

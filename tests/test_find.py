@@ -242,3 +242,25 @@ def test_find_flow_gpu_matches_oracle():
     assert (got["item_read"] == want["item_read"]).all() and (got["item_seq"] == want["item_seq"]).all()
     H.assert_align_equal(got["alignments"], want["alignments"])
     assert (got["accepted"] == want["accepted"]).all() and (got["n_matches"] == want["n_matches"]).all()
+
+
+@pytest.mark.gpu
+def test_find_matches_fused_equals_the_two_call_flow_on_the_oracle():
+    from bioinformatics_b200._lib import Context, HsqError
+    seqs, reads, quals = _find_flow_problem()
+    limits = (2, 1, 1, 1, 1)
+    K = 32
+    want = flow.find_flow(_OracleFind(seqs, 5, 15000), seqs, reads, quals, 10, 15, *limits, max_candidates=K)
+    with Context(0) as ctx:
+        ctx.set_find_sequences(seqs, 5, 15000)
+        got = ctx.find_matches(reads, quals, 10, 15, limits, max_candidates=K)
+        _assert_find_equal(got.cand, want["candidates"])
+        assert (got.n_matches == want["n_matches"]).all()
+        mask = np.arange(K)[None, :] < got.cand.n_candidates[:, None]
+        assert (got.counts[mask] == want["alignments"].find_counts).all()
+        assert (got.accepted[mask].astype(bool) == want["accepted"]).all()
+        assert not got.accepted[~mask].any() and got.cells == want["alignments"].cells
+        with pytest.raises(HsqError) as e:  # too few slots: an error, never a silently shorter candidate list
+            ctx.find_matches(reads, quals, 10, 15, limits, max_candidates=2)
+        assert e.value.status == A.HSQ_ERR_OVERFLOW
+        assert ctx.find_matches([], [], 10, 15, limits).n == 0
