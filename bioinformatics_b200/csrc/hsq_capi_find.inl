@@ -171,16 +171,28 @@ struct FindDeviceOut {
     uint8_t *has_n, *overflow, *order_dep;
 };
 
-// One warp per read.  `tally_global` != null: the warps' tallies live there (R too large for shared memory).
+// One warp per read.  Shared memory per warp: tallies of all R sequences, two 16-bit counters per word (or `tally_global`
+// when R is too large; a tally never exceeds the read length, which the launcher keeps below 65536) and five
+// arrays indexed by tally value (H = longest read - k + 1 entries): how many sequences hold that tally, how many of them
+// fail the hit-ratio test, the smallest failing row, the output slot of the group's first entry, entries already placed.
 __global__ void find_candidates_kernel(const uint8_t* __restrict__ reads, const uint8_t* __restrict__ quals, const int64_t* __restrict__ off, int64_t n,
-                                       FindIndex ix, int lead_q, int trail_q, int limit, double min_ratio, FindDeviceOut o,
+                                       FindIndex ix, int lead_q, int trail_q, int limit, double min_ratio, FindDeviceOut o, int H,
                                        uint32_t* __restrict__ tally_global, int* __restrict__ status) {
     extern __shared__ uint32_t find_smem[];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const unsigned lt_mask = (1u << lane) - 1u;
     const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t n_warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    uint32_t* tally = tally_global ? tally_global + warp0 * ix.R : find_smem + (size_t)wib * ix.R;
     const int R = ix.R, k = ix.k;
+    const int W = (R + 1) >> 1;  // tally words
+    const size_t per_warp = (size_t)(tally_global ? 0 : W) + 5 * (size_t)H;
+    uint32_t* base_smem = find_smem + (size_t)wib * per_warp;
+    uint32_t* tally = tally_global ? tally_global + warp0 * W : base_smem;
+    uint32_t* hist = base_smem + (tally_global ? 0 : W);
+    uint32_t* failcnt = hist + H;
+    uint32_t* failmin = failcnt + H;
+    uint32_t* slot0 = failmin + H;
+    uint32_t* placed = slot0 + H;
     for (int64_t r = warp0; r < n; r += n_warps) {
         const int64_t a = off[r];
         const int len = (int)(off[r + 1] - a);
@@ -213,54 +225,81 @@ __global__ void find_candidates_kernel(const uint8_t* __restrict__ reads, const 
         bool od = false;
         if (!has_n && bad && lane == 0) atomicCAS(status, 0, HSQ_ERR_BAD_CHARACTER);
         if (!has_n && !bad && tlen > k) {
-            for (int i = lane; i < R; i += 32) tally[i] = 0;
+            const int nlev = tlen - k;  // largest possible tally (< H)
+            for (int i = lane; i < W; i += 32) tally[i] = 0;
+            for (int i = lane; i <= nlev; i += 32) { hist[i] = 0; failcnt[i] = 0; failmin[i] = 0xffffffffu; placed[i] = 0; }
             __syncwarp();
             // getReferenceTallyMap (SimpleMapper.java:205-217): query positions 0 .. size-k-1
-            for (int i = lane; i < tlen - k; i += 32) {
+            for (int i = lane; i < nlev; i += 32) {
                 const uint32_t code = kmer_at(s + i, k);
                 const int32_t m = ix.len[code];
                 const int32_t* row = ix.refs + ix.start[code];
-                for (int j = 0; j < m; j++) atomicAdd(&tally[row[j]], 1u);
+                int j = 0;
+                for (; j + 4 <= m; j += 4) {  // the four row loads are issued before the first atomic waits on one
+                    const int32_t r0 = __ldg(row + j), r1 = __ldg(row + j + 1), r2 = __ldg(row + j + 2), r3 = __ldg(row + j + 3);
+                    atomicAdd(&tally[r0 >> 1], (r0 & 1) ? 0x10000u : 1u);
+                    atomicAdd(&tally[r1 >> 1], (r1 & 1) ? 0x10000u : 1u);
+                    atomicAdd(&tally[r2 >> 1], (r2 & 1) ? 0x10000u : 1u);
+                    atomicAdd(&tally[r3 >> 1], (r3 & 1) ? 0x10000u : 1u);
+                }
+                for (; j < m; j++) {
+                    const int32_t r0 = __ldg(row + j);
+                    atomicAdd(&tally[r0 >> 1], (r0 & 1) ? 0x10000u : 1u);
+                }
             }
             __syncwarp();
-            // getBestCandidateReferences (:154-187), groups of equal tallies from the largest down
-            const double limit_q = min_ratio * (double)(tlen - k);
-            uint32_t prev = 0xffffffffu;
-            while (true) {
-                uint32_t h = 0;
-                for (int i = lane; i < R; i += 32) {
-                    const uint32_t t = tally[i];
-                    if (t < prev && t > h) h = t;
+            // one pass over the tallies: group sizes and, per group, the entries the ratio test rejects (:171)
+            const double limit_q = min_ratio * (double)nlev;
+            uint32_t top = 0;
+            for (int ref = lane; ref < R; ref += 32) {
+                const uint32_t t = (tally[ref >> 1] >> ((ref & 1) * 16)) & 0xffffu;
+                if (t == 0) continue;
+                top = max(top, t);
+                atomicAdd(&hist[t], 1u);
+                if ((double)t < limit_q && (double)t < min_ratio * (double)(ix.size[ref] - k)) {
+                    atomicAdd(&failcnt[t], 1u);
+                    atomicMin(&failmin[t], (uint32_t)ref);
                 }
-                for (int d = 16; d > 0; d >>= 1) h = max(h, __shfl_xor_sync(0xffffffffu, h, d));
-                if (h == 0) break;
-                if (count > limit) break;  // candidate limit reached and this group is not tied with the last one added
-                const bool below_q = (double)h < limit_q;
-                bool stopped = false;
-                for (int b = 0; b < R; b += 32) {
-                    const int ref = b + lane;
-                    const bool in = ref < R && tally[ref] == h;
-                    const bool failing = in && below_q && ((double)h < min_ratio * (double)(ix.size[ref] - k));
-                    const unsigned m_in = __ballot_sync(0xffffffffu, in), m_fail = __ballot_sync(0xffffffffu, failing);
-                    const unsigned take = m_fail ? (m_in & ((1u << (__ffs(m_fail) - 1)) - 1u)) : m_in;
-                    if (take & (1u << lane)) {
-                        const int slot = count + __popc(take & ((1u << lane) - 1u));
-                        if (slot < o.K) {
-                            o.cand[r * o.K + slot] = ref;
-                            o.hits[r * o.K + slot] = (int32_t)h;
-                        }
-                    }
-                    count += __popc(take);
-                    if (m_fail) { stopped = true; break; }
-                }
-                if (stopped) {  // would an entry of this tally have passed had it come first?
-                    bool pass = false;
-                    for (int ref = lane; ref < R; ref += 32)
-                        pass |= (tally[ref] == h) && !((double)h < min_ratio * (double)(ix.size[ref] - k));
-                    od = __any_sync(0xffffffffu, pass);
+            }
+            for (int d = 16; d > 0; d >>= 1) top = max(top, __shfl_xor_sync(0xffffffffu, top, d));
+            __syncwarp();
+            // getBestCandidateReferences (:154-187): groups of equal tallies from the largest down (every lane walks the same path)
+            uint32_t cut = 0xffffffffu, stop_h = 0, stop_ref = 0;
+            for (uint32_t h = top; h >= 1; h--) {
+                const uint32_t c = hist[h];
+                if (c == 0) continue;
+                if (count > limit) break;  // candidate limit reached and this group is not tied with the last one added (:172)
+                if (lane == 0) slot0[h] = (uint32_t)count;
+                if (failcnt[h] > 0) {  // the walk ends at the first rejected entry: rows before it (all accepted) still get in
+                    stop_h = h;
+                    stop_ref = failmin[h];
+                    od = c > failcnt[h];
                     break;
                 }
-                prev = h;
+                count += (int)c;
+                cut = h;
+            }
+            __syncwarp();
+            // placement: slot = first slot of the tally group + rank inside it in ascending row order
+            for (int b = 0; b < R; b += 32) {
+                const int ref = b + lane;
+                const uint32_t t = ref < R ? (tally[ref >> 1] >> ((ref & 1) * 16)) & 0xffffu : 0;
+                const bool part = stop_h != 0 && t == stop_h && (uint32_t)ref < stop_ref;
+                const bool take = (t != 0 && t >= cut) || part;
+                const unsigned m_take = __ballot_sync(0xffffffffu, take);
+                if (m_take == 0) continue;
+                count += __popc(__ballot_sync(0xffffffffu, part));
+                if (take) {
+                    const unsigned peers = __match_any_sync(m_take, t);
+                    const int slot = (int)(slot0[t] + placed[t]) + __popc(peers & lt_mask);
+                    if (slot < o.K) {
+                        o.cand[r * o.K + slot] = ref;
+                        o.hits[r * o.K + slot] = (int32_t)t;
+                    }
+                    __syncwarp(m_take);
+                    if ((peers & lt_mask) == 0) placed[t] += (uint32_t)__popc(peers);
+                    __syncwarp(m_take);
+                }
             }
         }
         if (lane == 0) {
@@ -324,7 +363,7 @@ __global__ void find_items_kernel(const int64_t* __restrict__ item_off, int64_t 
 // uploads the reads, runs the candidate kernel (results stay on the device in `o`) and the encoder: new
 // IupacNucleotideCodeSequence(readString) (:906) throws on a byte that is no IUPAC code, wherever it sits in the read
 int find_run_candidates(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int lead_q, int trail_q, int limit, double ratio, int32_t K,
-                        bool encode, FindDeviceOut* o) {
+                        FindDeviceOut* o, int* r_max) {
     const int64_t n = reads->n;
     int rc;
     if ((rc = reset_status(ctx))) return rc;
@@ -345,28 +384,39 @@ int find_run_candidates(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* qual
     o->overflow = o->has_n + nn;
     o->order_dep = o->overflow + nn;
     if (n == 0) return HSQ_OK;
+    if ((rc = encode_seqs(ctx, &ctx->r1, d_status(ctx), d_maxlen(ctx, 0)))) return rc;
+    int w[2];
+    if ((rc = read_status(ctx, w, 2))) return rc;
+    if (w[0] != 0) return fail(ctx, w[0], "a read holds a byte that is not an IUPAC code");
+    *r_max = w[1];
+    const int H = std::max(1, w[1] - ctx->fi_k + 1);  // tallies run from 0 to read length - k
     FindIndex ix{ctx->fi_start.as<int64_t>(), ctx->fi_len.as<int32_t>(), ctx->fi_refs.as<int32_t>(), ctx->fi_size.as<int32_t>(), (int32_t)ctx->fi_n,
                  ctx->fi_k};
-    const size_t per_warp = (size_t)ctx->fi_n * 4;
-    int warps = 8;
-    while (warps > 1 && per_warp * warps > 96 * 1024) warps >>= 1;
+    if (H > 65535) return fail(ctx, HSQ_ERR_UNSUPPORTED, "reads of 65 535 bases or more are not supported");
+    const size_t levels = 5 * (size_t)H * 4, words = ((size_t)ctx->fi_n + 1) / 2 * 4;
+    size_t per_warp = words + levels;
+    int warps = 4;
+    while (warps > 1 && per_warp * warps > 100 * 1024) warps >>= 1;
     uint32_t* tally_global = nullptr;
-    size_t smem = per_warp * warps;
-    int blocks = (int)std::min<int64_t>((n + warps - 1) / warps, (int64_t)ctx->sm_count * (warps >= 4 ? 2 : 4));
-    if (smem > 200 * 1024) {  // tallies in global memory, one slice per resident warp
+    if (per_warp * warps > 200 * 1024) {  // tallies in global memory, one slice per resident warp
         warps = 4;
-        smem = 0;
-        blocks = (int)std::min<int64_t>((n + warps - 1) / warps, (int64_t)ctx->sm_count * 4);
-        HSQ_CUDA(ctx, ctx->slow.ensure(per_warp * (size_t)blocks * warps + 16));
-        tally_global = ctx->slow.as<uint32_t>();
-    } else if (smem > 48 * 1024) {
-        HSQ_CUDA(ctx, cudaFuncSetAttribute(find_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        while (warps > 1 && levels * warps > 100 * 1024) warps >>= 1;
+        if (levels * warps > 200 * 1024) return fail(ctx, HSQ_ERR_UNSUPPORTED, "reads longer than 10 000 bases are not supported");
+        per_warp = levels;
     }
+    // persistent grid: as many blocks per SM as the shared memory lets in (the kernel waits on L2 loads of the index rows)
+    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(std::min<size_t>(64 / warps, 16), (220 * 1024) / (per_warp * warps + 1024)));
+    const int blocks = (int)std::min<int64_t>((n + warps - 1) / warps, (int64_t)ctx->sm_count * per_sm);
+    if (per_warp == levels) {
+        HSQ_CUDA(ctx, ctx->slow.ensure(words * (size_t)blocks * warps + 16));
+        tally_global = ctx->slow.as<uint32_t>();
+    }
+    const size_t smem = per_warp * warps;
+    if (smem > 48 * 1024) HSQ_CUDA(ctx, cudaFuncSetAttribute(find_candidates_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     find_candidates_kernel<<<blocks, warps * 32, smem, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->q1.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), n, ix,
-                                                                     lead_q, trail_q, limit, ratio, *o, tally_global, ctx->status.as<int>());
+                                                                     lead_q, trail_q, limit, ratio, *o, H, tally_global, ctx->status.as<int>());
     ctx->launches++;
     HSQ_CUDA(ctx, cudaGetLastError());
-    if (encode && (rc = encode_seqs(ctx, &ctx->r1, d_status(ctx), d_maxlen(ctx, 0)))) return rc;
     return HSQ_OK;
 }
 
@@ -394,8 +444,8 @@ extern "C" int32_t hsq_find_candidates(hsq_ctx* ctx, const hsq_seqs* reads, cons
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
     FindDeviceOut o;
-    int rc;
-    if ((rc = find_run_candidates(ctx, reads, quals, leading_quality, trailing_quality, candidate_limit, min_hit_ratio, out->max_candidates, true, &o)))
+    int rc, r_max = 0;
+    if ((rc = find_run_candidates(ctx, reads, quals, leading_quality, trailing_quality, candidate_limit, min_hit_ratio, out->max_candidates, &o, &r_max)))
         return rc;
     int w[1] = {0};
     if (reads->n > 0) {
@@ -418,9 +468,9 @@ extern "C" int32_t hsq_find_matches(hsq_ctx* ctx, const hsq_seqs* reads, const u
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
     FindDeviceOut o;
-    int rc;
+    int rc, r_max = 0;
     out->cells = 0;
-    if ((rc = find_run_candidates(ctx, reads, quals, leading_quality, trailing_quality, candidate_limit, min_hit_ratio, K, true, &o))) return rc;
+    if ((rc = find_run_candidates(ctx, reads, quals, leading_quality, trailing_quality, candidate_limit, min_hit_ratio, K, &o, &r_max))) return rc;
     if (n == 0) return timer.finish();
     // item list: candidate slots of all reads in read order
     const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
@@ -442,11 +492,10 @@ extern "C" int32_t hsq_find_matches(hsq_ctx* ctx, const hsq_seqs* reads, const u
     HSQ_CUDA(ctx, cudaMemsetAsync(accepted, 0, nn * kk, ctx->stream));
     int64_t* h_m = reinterpret_cast<int64_t*>(ctx->h_cells) + 1;  // pinned
     HSQ_CUDA(ctx, cudaMemcpyAsync(h_m, item_off + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    int w[4];
-    if ((rc = read_status(ctx, w, 2))) return rc;
+    int w[1];
+    if ((rc = read_status(ctx, w, 1))) return rc;
     if (w[0] != 0) return fail(ctx, w[0], "a read without N holds a character other than A, C, G, T");
     const int64_t n_items = *h_m;
-    const int r_max = w[1];
     if (n_items > 0) {
         HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)n_items * 4 + 16));
         int32_t* item_read = ctx->sort_c.as<int32_t>();

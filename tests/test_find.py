@@ -197,6 +197,32 @@ def test_find_errors_gpu():
             ctx.find_candidates(["ACGTRCGTAA"], ["I" * 10])
         assert e.value.status == A.HSQ_ERR_BAD_CHARACTER
         assert ctx.find_candidates(["ACGTNCGTAA"], ["I" * 10]).has_n[0] == 1  # an N is a skip, not an error
+        with pytest.raises(HsqError) as e:  # new IupacNucleotideCodeSequence(readString) throws before the N test is reached
+            ctx.find_candidates(["ACGTN*GTAA"], ["I" * 10])
+        assert e.value.status == A.HSQ_ERR_BAD_CHARACTER
+
+
+@pytest.mark.gpu
+def test_find_candidates_long_and_mixed_length_reads_gpu():
+    from bioinformatics_b200._lib import Context
+    rng = np.random.default_rng(5)
+    seqs = [H.random_seq(rng, int(rng.integers(20, 60))) for _ in range(500)]
+    reads, quals = [], []
+    for k in range(400):
+        L = int(rng.choice([30, 150, 300, 1200, 3000]))
+        body = list(H.random_seq(rng, L))
+        for _ in range(L // 60):  # several sequences to find planted per read: many tally groups, long candidate walks
+            s_ = seqs[int(rng.integers(0, 500))]
+            at = int(rng.integers(0, max(1, L - len(s_))))
+            body[at:at + len(s_)] = list(s_[:max(0, L - at)])
+        reads.append("".join(body)[:L])
+        quals.append("I" * L)
+    for limit, ratio in ((10, 0.5), (3, 0.2), (40, 0.05)):
+        want = O.find_candidates(seqs, reads, quals, candidate_limit=limit, min_hit_ratio=ratio, max_candidates=64)
+        with Context(0) as ctx:
+            ctx.set_find_sequences(seqs, 5, 15000)
+            _assert_find_equal(ctx.find_candidates(reads, quals, 0, 0, limit, ratio, max_candidates=64), want)
+        assert want.n_candidates.max() > 3
 
 
 class _OracleFind:
