@@ -16,6 +16,10 @@ HSQ_ERR_BAD_CHARACTER = -4
 HSQ_ERR_UNSUPPORTED = -5
 HSQ_ERR_OUT_OF_RANGE = -6
 HSQ_ERR_OVERFLOW = -7
+HSQ_ERR_NAME_MISMATCH = -8
+HSQ_ERR_NOT_TRIMMED = -9
+HSQ_ERR_NO_MATCHES = -10
+HSQ_ERR_MALFORMED = -11
 HSQ_PRIMER_NOT_FOUND = -2147483647
 HSQ_ALIGN_PENALIZE_START = 1
 HSQ_ALIGN_PENALIZE_END = 2
@@ -103,6 +107,23 @@ class FindLimits(C.Structure):
 
 class FindMatchOut(C.Structure):
     _fields_ = [("cand", FindOut), ("counts", i32p), ("accepted", u8p), ("n_matches", i32p), ("cells", C.c_int64)]
+
+
+class FastqIndex(C.Structure):
+    _fields_ = [("cap", C.c_int64), ("n", C.c_int64), ("header_off", i64p), ("header_len", i32p), ("seq_off", i64p), ("seq_len", i32p),
+                ("qual_off", i64p), ("qual_len", i32p)]
+
+
+class NameJoin(C.Structure):
+    _fields_ = [("sam_names", Seqs), ("sam_flags", i32p), ("sam_seq_len", i32p), ("sam_qual_len", i32p), ("fq1_headers", Seqs),
+                ("fq2_headers", Seqs), ("fq1_seq_len", i32p), ("fq2_seq_len", i32p), ("by_index", C.c_int32), ("trimming_skipped", C.c_int32),
+                ("check_trim", C.c_int32), ("three_prime", C.c_int32), ("r1_first", C.c_int32), ("r1_stop", C.c_int32),
+                ("r2_first", C.c_int32), ("r2_stop", C.c_int32)]
+
+
+class NameJoinOut(C.Structure):
+    _fields_ = [("n_emitted", C.c_int64), ("total_matching_pairs", C.c_int64), ("sam_record", i32p), ("fastq_record", i32p),
+                ("name_len", i32p), ("status", u8p)]
 
 
 ASSIGN_UNPAIRED, ASSIGN_AMBIGUOUS_NAME, ASSIGN_IGNORED = -1, -2, -3

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 from . import _abi as A
-from .batches import (AlignResult, AssignResult, FindResult, FindMatchResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
+from .batches import (FastqIndexResult, NameJoinHost, NameJoinResult, AlignResult, AssignResult, FindResult, FindMatchResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
                       ProbeTableHost, merge_args, scorer)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
@@ -21,7 +21,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
            "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs",
-           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches")
+           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_join_names", "hsq_gather_rows")
 
 
 class HsqError(RuntimeError):
@@ -218,6 +218,38 @@ class Context:
         rc, oc = records.c(), out.c()
         self._check(self.lib.hsq_assign_probes(self.h, C.byref(rc), C.byref(oc)))
         return out
+
+    def index_fastq(self, text, cap=None):
+        """hsq_index_fastq: record index of FASTQ text (htsjdk FastqReader grammar)."""
+        text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+        if cap is None:
+            cap = len(text) // 8 + 1  # a record is at least "@x\nA\n+\nI\n"
+        out = FastqIndexResult(cap)
+        oc = out.c()
+        self._check(self.lib.hsq_index_fastq(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(oc)))
+        out.n = int(oc.n)
+        return out
+
+    def join_names(self, join: NameJoinHost):
+        """hsq_join_names: both sorts and the merge loop of FastqAndBamFileMerger's MergedSamIterator."""
+        out = NameJoinResult(join.n)
+        jc, oc = join.c(), out.c()
+        self._check(self.lib.hsq_join_names(self.h, C.byref(jc), C.byref(oc)))
+        return out.take(oc)
+
+    def gather_rows(self, text, off, length, out_cap=None):
+        """hsq_gather_rows: rows text[off[e] : off[e] + length[e]] as a ragged batch."""
+        text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+        off = np.ascontiguousarray(off, dtype=np.int64)
+        length = np.ascontiguousarray(length, dtype=np.int32)
+        n = len(off)
+        if out_cap is None:
+            out_cap = int(length.astype(np.int64).sum())
+        data = np.zeros(max(out_cap, 1), dtype=np.uint8)
+        offsets = np.zeros(n + 1, dtype=np.int64)
+        self._check(self.lib.hsq_gather_rows(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), A.ptr(off, A.i64p), A.ptr(length, A.i32p),
+                                             C.c_int64(n), A.ptr(data, A.u8p), A.ptr(offsets, A.i64p), C.c_int64(out_cap)))
+        return A.SeqBatch(data[:offsets[-1]], offsets)
 
     def set_find_sequences(self, seqs, kmer=5, max_refs_per_kmer=15000):
         """hsq_set_find_sequences: SimpleMapper index of the sequences to find (FastqFindAndTrimTool.java:231-237)."""

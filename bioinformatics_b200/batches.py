@@ -373,6 +373,75 @@ class FindMatchResult:
         return self
 
 
+class FastqIndexResult:
+    """hsq_fastq_index with host arrays: where header, bases and qualities of every record sit in the FASTQ text."""
+
+    def __init__(self, cap):
+        self.cap, self.n = int(cap), 0
+        self.header_off = np.zeros(cap, dtype=np.int64)
+        self.header_len = np.zeros(cap, dtype=np.int32)
+        self.seq_off = np.zeros(cap, dtype=np.int64)
+        self.seq_len = np.zeros(cap, dtype=np.int32)
+        self.qual_off = np.zeros(cap, dtype=np.int64)
+        self.qual_len = np.zeros(cap, dtype=np.int32)
+
+    def c(self):
+        return A.FastqIndex(self.cap, 0, A.ptr(self.header_off, A.i64p), A.ptr(self.header_len, A.i32p), A.ptr(self.seq_off, A.i64p),
+                            A.ptr(self.seq_len, A.i32p), A.ptr(self.qual_off, A.i64p), A.ptr(self.qual_len, A.i32p))
+
+    FIELDS = ("header_off", "header_len", "seq_off", "seq_len", "qual_off", "qual_len")
+
+    def head(self):
+        return {f: getattr(self, f)[:self.n] for f in self.FIELDS}
+
+
+class NameJoinHost:
+    """hsq_name_join: what FastqAndBamFileMerger reads off the SAM records and the two FASTQ files
+    (HSQ/process/FastqAndBamFileMerger.java:107-158,213-345)."""
+
+    def __init__(self, sam_names, sam_flags, sam_seq_len, fq1_headers, fq2_headers, fq1_seq_len=None, fq2_seq_len=None, sam_qual_len=None,
+                 by_index=False, trimming_skipped=False, check_trim=True, three_prime=False, r1_first=0, r1_stop=0, r2_first=0, r2_stop=0):
+        sb = lambda x: x if isinstance(x, A.SeqBatch) else A.SeqBatch.from_strings(x)
+        i32 = lambda x: None if x is None else np.ascontiguousarray(x, dtype=np.int32)
+        self.sam_names, self.fq1_headers, self.fq2_headers = sb(sam_names), sb(fq1_headers), sb(fq2_headers)
+        self.sam_flags, self.sam_seq_len, self.sam_qual_len = i32(sam_flags), i32(sam_seq_len), i32(sam_qual_len)
+        self.fq1_seq_len, self.fq2_seq_len = i32(fq1_seq_len), i32(fq2_seq_len)
+        self.params = (int(by_index), int(trimming_skipped), int(check_trim), int(three_prime), int(r1_first), int(r1_stop), int(r2_first),
+                       int(r2_stop))
+        self.n = self.sam_names.n
+        assert len(self.sam_flags) == self.n and len(self.sam_seq_len) == self.n
+
+    def c(self):
+        return A.NameJoin(self.sam_names.c(), A.ptr(self.sam_flags, A.i32p), A.ptr(self.sam_seq_len, A.i32p), A.ptr(self.sam_qual_len, A.i32p),
+                          self.fq1_headers.c(), self.fq2_headers.c(), A.ptr(self.fq1_seq_len, A.i32p), A.ptr(self.fq2_seq_len, A.i32p),
+                          *self.params)
+
+
+class NameJoinResult:
+    """hsq_name_join_out with host arrays."""
+
+    def __init__(self, n):
+        self.n = n
+        self.n_emitted = 0
+        self.total_matching_pairs = 0
+        self.sam_record = np.full(n, -1, dtype=np.int32)
+        self.fastq_record = np.full(n, -1, dtype=np.int32)
+        self.name_len = np.full(n, -1, dtype=np.int32)
+        self.status = np.zeros(n, dtype=np.uint8)
+
+    def c(self):
+        return A.NameJoinOut(0, 0, A.ptr(self.sam_record, A.i32p), A.ptr(self.fastq_record, A.i32p), A.ptr(self.name_len, A.i32p),
+                             A.ptr(self.status, A.u8p))
+
+    def take(self, oc):
+        self.n_emitted, self.total_matching_pairs = int(oc.n_emitted), int(oc.total_matching_pairs)
+        return self
+
+    def emitted(self):
+        m = self.n_emitted
+        return self.sam_record[:m], self.fastq_record[:m], self.name_len[:m]
+
+
 def scorer(match=1, mismatch=-4, gap_extend=-1, gap_start=-6):
     """SimpleAlignmentScorer defaults (COMMON/alignment/SimpleAlignmentScorer.java:23-26)."""
     return A.Scorer(match, mismatch, gap_extend, gap_start)

@@ -170,6 +170,7 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
                            &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->rg_start, &ctx->rg_end,
                            &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32, &ctx->fi_start, &ctx->fi_len, &ctx->fi_refs, &ctx->fi_size};
     for (auto* b : bufs) b->release();
+    for (auto& b : ctx->ing) b.release();
     hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb, &ctx->alt_r1, &ctx->alt_r2, &ctx->fs};
     for (auto* s : seqs) s->release();
     for (auto& ps : ctx->parked) {
@@ -239,4 +240,5 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_pipeline.inl"
 #include "hsq_capi_records.inl"
 #include "hsq_capi_find.inl"
+#include "hsq_capi_ingest.inl"
 #include "hsq_capi_peak.inl"

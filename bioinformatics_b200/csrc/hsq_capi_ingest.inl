@@ -1,0 +1,758 @@
+// hsq_capi_ingest.inl -- SURVEY §8(f) row f2: FASTQ ingest and the FASTQ <-> SAM name join in front of the dedup path.
+//   hsq_index_fastq : record index of FASTQ text (htsjdk FastqReader grammar; call sites HSQ/utils/FastqSorter.java:77,98)
+//   hsq_join_names  : FastqAndBamFileMerger.createBamFileWithDataFromRawFastqFiles without the codecs
+//                     (HSQ/process/FastqAndBamFileMerger.java:107-158, MergedSamIterator :213-345, trim check :65-94,366-373)
+//   hsq_gather_rows : the raw read / quality strings the merged records take (:386-396)
+// The reference's merge is a sequential two-cursor loop over two sorted iterators.  Here both sides are sorted on the device
+// (LSD radix over big-endian 8-byte chunks of the zero-padded keys = String.compareTo for ASCII), and the loop becomes, for
+// the j-th primary SAM record in sorted order with unique id s:  c = number of earlier not-first-of-pair records with the
+// same id (each of them, once matched, moves the FASTQ cursor on, :304-309);  p = first sorted FASTQ position whose id is >= s;
+// the record is returned iff FASTQ position p + c exists and carries id s.  That equals the loop whenever ids ascend along both
+// sorted sides; if they do not (a sort key orders differently from the id it contains) the call fails with HSQ_ERR_UNSUPPORTED.
+#include <cub/device/device_scan.cuh>
+#include <climits>
+namespace hsq {
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// FASTQ text -> line starts -> records
+static constexpr int NL_BLOCK = 256, NL_BYTES = 16, NL_TILE = NL_BLOCK * NL_BYTES;
+
+__device__ inline uint32_t newline_mask16(const uint8_t* __restrict__ text, int64_t base, int64_t n, int* lone_cr) {
+    __align__(16) uint8_t b[2 * NL_BYTES];
+    if (base + NL_BYTES <= n) {
+        const uint4 v = *reinterpret_cast<const uint4*>(text + base);  // base is a multiple of 16, text is cudaMalloc aligned
+        *reinterpret_cast<uint4*>(b) = v;
+        b[NL_BYTES] = base + NL_BYTES < n ? text[base + NL_BYTES] : (uint8_t)'\n';
+    } else {
+        for (int k = 0; k <= NL_BYTES; k++) b[k] = base + k < n ? text[base + k] : (uint8_t)'\n';
+    }
+    uint32_t m = 0;
+    for (int k = 0; k < NL_BYTES; k++) {
+        if (base + k >= n) break;
+        if (b[k] == '\n') m |= 1u << k;
+        if (b[k] == '\r' && b[k + 1] != '\n') *lone_cr = 1;  // end of text after '\r' counts as a terminator too
+    }
+    return m;
+}
+
+__global__ void nl_count_kernel(const uint8_t* __restrict__ text, int64_t n, int64_t* __restrict__ tile_counts, int* status) {
+    const int64_t base = (int64_t)blockIdx.x * NL_TILE + (int64_t)threadIdx.x * NL_BYTES;
+    int lone = 0;
+    const uint32_t m = base < n ? newline_mask16(text, base, n, &lone) : 0u;
+    if (lone) atomicMin(status, HSQ_ERR_UNSUPPORTED);
+    int64_t total;
+    block_exclusive_scan((int64_t)__popc(m), &total);
+    if (threadIdx.x == 0) tile_counts[blockIdx.x] = total;
+}
+
+// line_start[0] = 0; line_start[k] = byte after the k-th newline
+__global__ void nl_write_kernel(const uint8_t* __restrict__ text, int64_t n, const int64_t* __restrict__ tile_excl, int64_t* __restrict__ line_start) {
+    const int64_t base = (int64_t)blockIdx.x * NL_TILE + (int64_t)threadIdx.x * NL_BYTES;
+    int lone = 0;
+    uint32_t m = base < n ? newline_mask16(text, base, n, &lone) : 0u;
+    int64_t total;
+    int64_t rank = tile_excl[blockIdx.x] + block_exclusive_scan((int64_t)__popc(m), &total) + 1;
+    if (blockIdx.x == 0 && threadIdx.x == 0) line_start[0] = 0;
+    while (m) {
+        const int k = __ffs(m) - 1;
+        m &= m - 1;
+        line_start[rank++] = base + k + 1;
+    }
+}
+
+__global__ void set_i64_kernel(int64_t* p, int64_t v) { *p = v; }
+
+__global__ void fastq_record_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ line_start, int64_t n_rec,
+                                    int64_t* __restrict__ h_off, int32_t* __restrict__ h_len, int64_t* __restrict__ s_off, int32_t* __restrict__ s_len,
+                                    int64_t* __restrict__ q_off, int32_t* __restrict__ q_len, int* status, unsigned long long* first_bad) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n_rec; r += stride) {
+        int64_t off[4];
+        int32_t len[4];
+        bool bad = false;
+        for (int k = 0; k < 4; k++) {
+            off[k] = line_start[4 * r + k];
+            int64_t l = line_start[4 * r + k + 1] - 1 - off[k];
+            if (l > 0 && text[off[k] + l - 1] == '\r') l--;
+            len[k] = (int32_t)l;
+            bool blank = true;  // StringUtil.isBlank: FastqReader rejects such a line
+            for (int64_t i = 0; i < l && blank; i++) blank = text[off[k] + i] <= ' ';
+            bad |= blank;
+        }
+        if (!bad) bad = text[off[0]] != '@' || text[off[2]] != '+' || len[1] != len[3];
+        if (bad) {
+            atomicMin(status, HSQ_ERR_MALFORMED);
+            atomicMin(first_bad, (unsigned long long)r);
+        }
+        h_off[r] = off[0] + 1; h_len[r] = len[0] - 1;
+        s_off[r] = off[1]; s_len[r] = len[1];
+        q_off[r] = off[3]; q_len[r] = len[3];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// ragged row gather
+__global__ void rows_len_kernel(const int64_t* __restrict__ off, const int32_t* __restrict__ len, int64_t n, int64_t n_bytes,
+                                int64_t* __restrict__ len64, int* status) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride) {
+        int64_t l = len[k];
+        if (l < 0 || off[k] < 0 || off[k] + l > n_bytes) { atomicMin(status, HSQ_ERR_OUT_OF_RANGE); l = 0; }
+        len64[k] = l;
+    }
+}
+
+__global__ void rows_copy_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, const int64_t* __restrict__ dst_off, int64_t n,
+                                 int64_t cap, uint8_t* __restrict__ dst) {
+    const int lane = threadIdx.x & 31;
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; w < n; w += stride) {
+        const int64_t s = off[w], d = dst_off[w];
+        const int len = (int)(dst_off[w + 1] - d);
+        if (d + len > cap) continue;
+        for (int i = lane; i < len; i += 32) dst[d + i] = text[s + i];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// name join
+enum { JC_ORDER = 0, JC_MISMATCH = 1, JC_KMAX = 2, JC_TRIM = 3, JC_EMITTED = 4, JC_PAIRS = 5, JC_PARSE = 6, JC_NONPRIMARY = 7,
+       JC_MAX_SAM = 8, JC_MAX_FQ1 = 9, JC_MAX_FQ2 = 10, JC_WORDS = 16 };
+
+__device__ inline int unique_id_len(const uint8_t* __restrict__ p, int len) {  // IlluminaFastQReadNameUtil.java:40-58
+    for (int i = 0; i < len; i++)
+        if (p[i] == ' ' || p[i] == '/') return i;
+    return len;
+}
+// String.compareTo for ASCII: first differing byte, else the shorter string first
+__device__ inline int str_cmp(const uint8_t* __restrict__ a, int la, const uint8_t* __restrict__ b, int lb) {
+    const int m = la < lb ? la : lb;
+    for (int i = 0; i < m; i++) {
+        const int d = (int)a[i] - (int)b[i];
+        if (d) return d;
+    }
+    return la - lb;
+}
+
+// FASTQ sort keys: header [+ " _ " + ordinal] (FastqSorter.java:298-302), zero padded, as big-endian 8-byte chunks, chunk-major
+__global__ void fq_keys_kernel(const uint8_t* __restrict__ data, const int64_t* __restrict__ off, int64_t n, int n_chunks, int append_index,
+                               uint64_t* __restrict__ keys, int32_t* __restrict__ uid_len) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n; r += stride) {
+        const uint8_t* p = data + off[r];
+        const int len = (int)(off[r + 1] - off[r]);
+        uid_len[r] = unique_id_len(p, len);
+        if (!keys) continue;
+        uint8_t suf[16];
+        int sl = 0;
+        if (append_index) {
+            suf[0] = ' '; suf[1] = '_'; suf[2] = ' ';
+            uint8_t dig[12];
+            int nd = 0;
+            int64_t v = r;
+            do { dig[nd++] = (uint8_t)('0' + v % 10); v /= 10; } while (v);
+            sl = 3;
+            while (nd) suf[sl++] = dig[--nd];
+        }
+        const int total = len + sl;
+        for (int c = 0; c < n_chunks; c++) {
+            uint64_t w = 0;
+            for (int b = 0; b < 8; b++) {
+                const int pos = c * 8 + b;
+                const uint8_t byte = pos < len ? p[pos] : (pos < total ? suf[pos - len] : (uint8_t)0);
+                w = (w << 8) | byte;
+            }
+            keys[(int64_t)c * n + r] = w;
+        }
+    }
+}
+
+// SAM sort keys by name (BamSorter.java:348-361): name chunks, a first-of-pair-first key, a primary-records-first key
+__global__ void sam_keys_kernel(const uint8_t* __restrict__ data, const int64_t* __restrict__ off, const int32_t* __restrict__ flags, int64_t n,
+                                int n_chunks, uint64_t* __restrict__ keys, uint64_t* __restrict__ k_nonfirst, uint64_t* __restrict__ k_nonprimary,
+                                int32_t* __restrict__ uid_len, int* ctr) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n; r += stride) {
+        const uint8_t* p = data + off[r];
+        const int len = (int)(off[r + 1] - off[r]);
+        uid_len[r] = unique_id_len(p, len);
+        const int f = flags[r];
+        k_nonfirst[r] = (f & 0x40) ? 0 : 1;
+        k_nonprimary[r] = (f & 0x100) ? 1 : 0;
+        if (f & 0x100) atomicAdd(ctr + JC_NONPRIMARY, 1);
+        for (int c = 0; c < n_chunks; c++) {
+            uint64_t w = 0;
+            for (int b = 0; b < 8; b++) {
+                const int pos = c * 8 + b;
+                w = (w << 8) | (pos < len ? p[pos] : (uint8_t)0);
+            }
+            keys[(int64_t)c * n + r] = w;
+        }
+    }
+}
+
+// SAM sort key by index (BamSorter.java:322-346): Integer.parseInt(name), first of pair first, primary records first
+__global__ void sam_intkeys_kernel(const uint8_t* __restrict__ data, const int64_t* __restrict__ off, const int32_t* __restrict__ flags, int64_t n,
+                                   uint64_t* __restrict__ key, int32_t* __restrict__ val, int32_t* __restrict__ uid_len, int* ctr) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n; r += stride) {
+        const uint8_t* p = data + off[r];
+        const int len = (int)(off[r + 1] - off[r]);
+        int i = 0;
+        bool neg = false, ok = true;
+        if (len > 0 && (p[0] == '-' || p[0] == '+')) { neg = p[0] == '-'; i = 1; }
+        if (i >= len) ok = false;
+        int64_t v = 0;
+        for (; i < len && ok; i++) {
+            if (p[i] < '0' || p[i] > '9') ok = false;
+            else {
+                v = v * 10 + (p[i] - '0');
+                if (v > (int64_t)INT_MAX + 1) ok = false;
+            }
+        }
+        if (neg) v = -v;
+        if (v > INT_MAX || v < INT_MIN) ok = false;
+        if (!ok) { atomicExch(ctr + JC_PARSE, 1); v = 0; }
+        const int f = flags[r];
+        val[r] = (int32_t)v;
+        uid_len[r] = len;
+        if (f & 0x100) atomicAdd(ctr + JC_NONPRIMARY, 1);
+        key[r] = ((uint64_t)((f & 0x100) ? 1 : 0) << 33) | ((uint64_t)(uint32_t)((int32_t)v ^ INT_MIN) << 1) | ((f & 0x40) ? 0u : 1u);
+    }
+}
+
+// live[c] = 1 when chunk c differs between records (a chunk all records share needs no sort pass)
+__global__ void chunk_live_kernel(const uint64_t* __restrict__ keys, int64_t n, int n_chunks, int* __restrict__ live) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t total = n * n_chunks;
+    for (; i < total; i += stride) {
+        const int64_t c = i / n;
+        if (keys[i] != keys[c * n] && !live[c]) live[c] = 1;
+    }
+}
+
+__global__ void iota_u32_kernel(uint32_t* __restrict__ out, int64_t n) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride) out[k] = (uint32_t)k;
+}
+
+// sorted view of one FASTQ file: where the unique id of sorted position q sits
+__global__ void fq_sorted_view_kernel(const uint32_t* __restrict__ perm, const int64_t* __restrict__ off, const int32_t* __restrict__ uid_len, int64_t n,
+                                      int64_t* __restrict__ s_off, int32_t* __restrict__ s_len) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; q < n; q += stride) {
+        const int64_t r = perm ? perm[q] : q;
+        s_off[q] = off[r];
+        s_len[q] = uid_len[r];
+    }
+}
+
+struct SortedIds {
+    const uint8_t* data;
+    const int64_t* off;  // by sorted position
+    const int32_t* len;
+};
+
+// ids must ascend along the sorted FASTQ-one side; FASTQ one / two ids must agree position by position (:266-273)
+__global__ void fq_check_kernel(SortedIds a, SortedIds b, int64_t n1, int64_t nf, int by_index, int* ctr) {
+    int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; q < n1; q += stride) {
+        if (!by_index && q > 0 && str_cmp(a.data + a.off[q - 1], a.len[q - 1], a.data + a.off[q], a.len[q]) > 0) atomicExch(ctr + JC_ORDER, 1);
+        if (q < nf && str_cmp(a.data + a.off[q], a.len[q], b.data + b.off[q], b.len[q]) != 0) atomicMin(ctr + JC_MISMATCH, (int)q);
+    }
+}
+
+// per primary SAM record in sorted order: start of its id group and whether it is a not-first-of-pair record
+__global__ void sam_heads_kernel(const uint8_t* __restrict__ data, const int64_t* __restrict__ off, const int32_t* __restrict__ uid_len,
+                                 const int32_t* __restrict__ flags, const uint32_t* __restrict__ perm, int64_t np, const int32_t* __restrict__ val,
+                                 int32_t* __restrict__ headpos, int32_t* __restrict__ nonfirst, int* ctr) {
+    int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; j < np; j += stride) {
+        const uint32_t s = perm[j];
+        int cmp = 1;
+        if (j > 0) {
+            const uint32_t t = perm[j - 1];
+            if (val) cmp = val[s] > val[t] ? 1 : (val[s] < val[t] ? -1 : 0);
+            else cmp = str_cmp(data + off[s], uid_len[s], data + off[t], uid_len[t]);
+            if (cmp < 0) atomicExch(ctr + JC_ORDER, 1);
+        }
+        headpos[j] = cmp != 0 ? (int32_t)j : 0;
+        nonfirst[j] = (flags[s] & 0x40) ? 0 : 1;
+    }
+}
+
+struct TrimParams {
+    int check, three_prime, r1_first, r1_stop, r2_first, r2_stop;
+};
+
+__device__ inline int64_t fq_lower_bound(const SortedIds& f, int64_t nf, const uint8_t* s, int ls, bool upper) {
+    int64_t lo = 0, hi = nf;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        const int c = str_cmp(f.data + f.off[mid], f.len[mid], s, ls);
+        if (c < 0 || (upper && c == 0)) lo = mid + 1;
+        else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void join_match_kernel(const uint8_t* __restrict__ data, const int64_t* __restrict__ off, const int32_t* __restrict__ uid_len,
+                                  const int32_t* __restrict__ flags, const int32_t* __restrict__ seq_len, const int32_t* __restrict__ qual_len,
+                                  const uint32_t* __restrict__ perm, int64_t np, const int32_t* __restrict__ val, const int32_t* __restrict__ headpos,
+                                  const int32_t* __restrict__ excl_nonfirst, SortedIds f1, int64_t nf, const uint32_t* __restrict__ perm1,
+                                  const uint32_t* __restrict__ perm2, const int32_t* __restrict__ fq1_len, const int32_t* __restrict__ fq2_len,
+                                  TrimParams tp, int32_t* __restrict__ emit, int32_t* __restrict__ used, int32_t* __restrict__ nlen,
+                                  int32_t* __restrict__ target_of, int* ctr) {
+    int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; j < np; j += stride) {
+        const uint32_t s = perm[j];
+        const uint8_t* id = data + off[s];
+        const int ls = uid_len[s];
+        const int64_t cnt = (int64_t)excl_nonfirst[j] - excl_nonfirst[headpos[j]];
+        const bool first = (flags[s] & 0x40) != 0;
+        int64_t p0, target;
+        bool matched;
+        if (val) {  // FASTQ key of position k is k itself (:274-277)
+            p0 = val[s] < 0 ? 0 : val[s];
+            target = p0 + cnt;
+            matched = val[s] >= 0 && cnt == 0 && target < nf;
+        } else {
+            p0 = fq_lower_bound(f1, nf, id, ls, false);
+            target = p0 + cnt;
+            matched = target < nf && str_cmp(f1.data + f1.off[target], f1.len[target], id, ls) == 0;
+        }
+        int e = 0, u = -1, nl = -1;
+        if (matched) {
+            e = 1;
+            u = (int32_t)(first ? (perm1 ? perm1[target] : target) : (perm2 ? perm2[target] : target));
+            nl = f1.len[target];
+            if (!first) atomicAdd(ctr + JC_PAIRS, 1);
+            if (tp.check) {  // isTrimAmountCorrect (:65-94) over FastqReadTrimmer.trim (FastqReadTrimmer.java:309-328)
+                const int len = first ? fq1_len[u] : fq2_len[u];
+                const int t_first = first ? tp.r1_first : tp.r2_first, t_stop = first ? tp.r1_stop : tp.r2_stop;
+                int last_base = len - 1;
+                if (tp.three_prime) last_base = min(t_stop, len - 1);
+                const int expected = last_base + 1 - t_first;
+                if (t_first >= len || expected < 0) atomicMin((unsigned*)(ctr + JC_TRIM), (unsigned)j * 2u);
+                else if (seq_len[s] > expected || qual_len[s] > expected) atomicMin((unsigned*)(ctr + JC_TRIM), (unsigned)j * 2u + 1u);
+            }
+        }
+        emit[j] = e;
+        used[j] = u;
+        nlen[j] = nl;
+        target_of[j] = (int32_t)(target < nf ? target : nf);
+        if (j == np - 1) {  // last FASTQ position the loop fetches: where the cursor stands at the last primary record
+            int64_t cur = target;
+            if (!matched) {
+                if (val) cur = val[s] < 0 ? 0 : (cnt == 0 ? target : p0 + 1);
+                else {
+                    const int64_t ub = fq_lower_bound(f1, nf, id, ls, true);
+                    cur = target < ub ? target : ub;
+                }
+            }
+            ctr[JC_KMAX] = (int)(cur < nf ? cur : nf - 1);
+        }
+    }
+}
+
+__global__ void join_scatter_kernel(const uint32_t* __restrict__ perm, int64_t n, int64_t np, const int32_t* __restrict__ emit,
+                                    const int32_t* __restrict__ epos, const int32_t* __restrict__ used, const int32_t* __restrict__ nlen,
+                                    int32_t* __restrict__ sam_record, int32_t* __restrict__ fastq_record, int32_t* __restrict__ name_len,
+                                    uint8_t* __restrict__ status, int* ctr) {
+    int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; j < n; j += stride) {
+        const uint32_t s = perm[j];
+        if (j >= np) { status[s] = 0; continue; }
+        if (emit[j]) {
+            const int32_t e = epos[j];
+            sam_record[e] = (int32_t)s;
+            fastq_record[e] = used[j];
+            name_len[e] = nlen[j];
+            status[s] = 1;
+        } else {
+            status[s] = 2;
+        }
+        if (j == np - 1) ctr[JC_EMITTED] = epos[j] + emit[j];
+    }
+}
+
+}  // namespace hsq
+
+using namespace hsq;
+
+namespace {
+
+inline int grid_for(hsq_ctx* ctx, int64_t n, int block, int per_sm) {
+    return (int)std::max<int64_t>(1, std::min<int64_t>((n + block - 1) / block, (int64_t)ctx->sm_count * per_sm));
+}
+
+// LSD radix sort of chunk-major keys: `perm` (sorted position -> record) ends up in *result (one of pa / pb)
+int lsd_chunk_sort(hsq_ctx* ctx, const uint64_t* keys, int n_chunks, const int* live, int64_t n, uint32_t** cur, uint32_t** other, uint64_t* ka,
+                   uint64_t* kb) {
+    const int g = grid_for(ctx, n, 256, 16);
+    for (int c = n_chunks - 1; c >= 0; c--) {
+        if (!live[c]) continue;
+        gather_u64_kernel<uint64_t><<<g, 256, 0, ctx->stream>>>(keys + (int64_t)c * n, *cur, n, ka);
+        ctx->launches++;
+        int rc = sort_pass(ctx, ka, kb, *cur, *other, n, 64);
+        if (rc) return rc;
+        std::swap(*cur, *other);
+    }
+    return HSQ_OK;
+}
+
+int bit_sort(hsq_ctx* ctx, const uint64_t* key, int64_t n, uint32_t** cur, uint32_t** other, uint64_t* ka, uint64_t* kb) {
+    gather_u64_kernel<uint64_t><<<grid_for(ctx, n, 256, 16), 256, 0, ctx->stream>>>(key, *cur, n, ka);
+    ctx->launches++;
+    int rc = sort_pass(ctx, ka, kb, *cur, *other, n, 1);
+    if (rc) return rc;
+    std::swap(*cur, *other);
+    return HSQ_OK;
+}
+
+struct Arena {  // bump allocator over one DevBuf, sized up front
+    size_t need = 0;
+    uint8_t* base = nullptr;
+    size_t reserve(size_t bytes) {
+        const size_t o = need;
+        need += (bytes + 255) & ~(size_t)255;
+        return o;
+    }
+    template <class T> T* at(size_t o) const { return reinterpret_cast<T*>(base + o); }
+};
+
+int upload_strings(hsq_ctx* ctx, const hsq_seqs* s, DevBuf* data, DevBuf* off, const char* what) {
+    if (s->n < 0 || s->n >= (1ll << 31) || !s->offsets) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, std::string("hsq_join_names: bad batch: ") + what);
+    if (s->offsets[0] != 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, std::string("hsq_join_names: offsets must start at 0: ") + what);
+    const int64_t total = s->offsets[s->n];
+    if (total < 0 || (total > 0 && !s->data)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, std::string("hsq_join_names: null data: ") + what);
+    HSQ_CUDA(ctx, data->ensure((size_t)total + 16));
+    HSQ_CUDA(ctx, off->ensure((size_t)(s->n + 1) * 8));
+    if (total) HSQ_CUDA(ctx, cudaMemcpyAsync(data->p, s->data, (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(off->p, s->offsets, (size_t)(s->n + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+    return HSQ_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_fastq_index* out) {
+    if (!ctx || !out || n_bytes < 0 || (n_bytes > 0 && !text)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_fastq: null argument");
+    out->n = 0;
+    if (n_bytes == 0) return HSQ_OK;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    const int64_t n_tiles = (n_bytes + NL_TILE - 1) / NL_TILE;
+    HSQ_CUDA(ctx, ctx->r1.ascii.ensure((size_t)n_bytes + 32));
+    HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)(n_tiles + 1) * 8 + 16));
+    uint8_t* d_text = ctx->r1.ascii.as<uint8_t>();
+    int64_t* d_tiles = ctx->sort_c.as<int64_t>();
+    HSQ_CUDA(ctx, cudaMemcpyAsync(d_text, text, (size_t)n_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemsetAsync(d_tiles + n_tiles, 0, 8, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemsetAsync(ctx->cells.p, 0xff, 8, ctx->stream));  // first malformed record
+    nl_count_kernel<<<(unsigned)n_tiles, NL_BLOCK, 0, ctx->stream>>>(d_text, n_bytes, d_tiles, d_status(ctx));
+    scan_sums_kernel<<<1, SCAN_BLOCK, 0, ctx->stream>>>(d_tiles, n_tiles + 1);  // in place: exclusive; entry n_tiles = total
+    ctx->launches += 2;
+    HSQ_CUDA(ctx, cudaGetLastError());
+    int64_t n_newlines = 0;
+    HSQ_CUDA(ctx, cudaMemcpyAsync(&n_newlines, d_tiles + n_tiles, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const bool open_tail = text[n_bytes - 1] != '\n';  // a last line without terminator is still a line (BufferedReader.readLine)
+    const int64_t n_lines = n_newlines + (open_tail ? 1 : 0);
+    HSQ_CUDA(ctx, ctx->sort_a.ensure((size_t)(n_lines + 2) * 8));
+    int64_t* d_lines = ctx->sort_a.as<int64_t>();
+    nl_write_kernel<<<(unsigned)n_tiles, NL_BLOCK, 0, ctx->stream>>>(d_text, n_bytes, d_tiles, d_lines);
+    ctx->launches++;
+    if (open_tail) {
+        set_i64_kernel<<<1, 1, 0, ctx->stream>>>(d_lines + n_lines, n_bytes + 1);
+        ctx->launches++;
+    }
+    const int64_t n_rec = n_lines / 4;
+    out->n = n_rec;
+    int st[4];
+    if (n_lines % 4 != 0) {
+        if ((rc = read_status(ctx, st, 1))) return rc;
+        if (st[0] == HSQ_ERR_UNSUPPORTED) return fail(ctx, st[0], "hsq_index_fastq: a carriage return that is not followed by a line feed");
+        return fail(ctx, HSQ_ERR_MALFORMED, "hsq_index_fastq: File is too short: the last record has fewer than four lines");
+    }
+    if (n_rec > out->cap) return fail(ctx, HSQ_ERR_OVERFLOW, "hsq_index_fastq: more records than out->cap");
+    if (n_rec > 0 && (!out->header_off || !out->header_len || !out->seq_off || !out->seq_len || !out->qual_off || !out->qual_len))
+        return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_fastq: null output array");
+    const size_t nr = (size_t)n_rec;
+    HSQ_CUDA(ctx, ctx->out_i32.ensure(nr * 12 + 64));
+    HSQ_CUDA(ctx, ctx->sort_b.ensure(nr * 24 + 64));
+    int64_t* d_o64 = ctx->sort_b.as<int64_t>();
+    int32_t* d_o32 = ctx->out_i32.as<int32_t>();
+    if (n_rec > 0) {
+        fastq_record_kernel<<<grid_for(ctx, n_rec, 128, 16), 128, 0, ctx->stream>>>(d_text, d_lines, n_rec, d_o64, d_o32, d_o64 + nr, d_o32 + nr,
+                                                                                 d_o64 + 2 * nr, d_o32 + 2 * nr, d_status(ctx),
+                                                                                 ctx->cells.as<unsigned long long>());
+        ctx->launches++;
+    }
+    HSQ_CUDA(ctx, cudaGetLastError());
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if ((rc = read_status(ctx, st, 1))) return rc;
+    if (st[0] == HSQ_ERR_UNSUPPORTED) return fail(ctx, st[0], "hsq_index_fastq: a carriage return that is not followed by a line feed");
+    if (st[0]) return fail(ctx, st[0], "hsq_index_fastq: record " + std::to_string(ctx->h_cells[0]) +
+                                           " is not '@' header / bases / '+' header / qualities of the same length (or holds a blank line)");
+    struct { void* h; const void* d; size_t bytes; } down[] = {{out->header_off, d_o64, nr * 8}, {out->seq_off, d_o64 + nr, nr * 8},
+                                                               {out->qual_off, d_o64 + 2 * nr, nr * 8}, {out->header_len, d_o32, nr * 4},
+                                                               {out->seq_len, d_o32 + nr, nr * 4}, {out->qual_len, d_o32 + 2 * nr, nr * 4}};
+    for (auto& c : down)
+        if (c.bytes) HSQ_CUDA(ctx, cudaMemcpyAsync(c.h, c.d, c.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return timer.finish();
+}
+
+extern "C" int32_t hsq_gather_rows(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, const int64_t* off, const int32_t* len, int64_t n,
+                                   uint8_t* out_data, int64_t* out_offsets, int64_t out_cap) {
+    if (!ctx || n < 0 || n_bytes < 0 || !out_offsets || out_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_gather_rows: bad argument");
+    if (n > 0 && (!off || !len)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_gather_rows: null row array");
+    if (n_bytes > 0 && !text) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_gather_rows: null text");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    const size_t nn = (size_t)n;
+    const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
+    HSQ_CUDA(ctx, ctx->r1.ascii.ensure((size_t)n_bytes + 32));
+    HSQ_CUDA(ctx, ctx->sort_a.ensure((nn + 1) * 8));  // row offsets in
+    HSQ_CUDA(ctx, ctx->sort_b.ensure((nn + 1) * 8));  // lengths (int64)
+    HSQ_CUDA(ctx, ctx->sort_d.ensure((nn + 1) * 8));  // offsets out
+    HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)n_tiles * 8 + 16));
+    HSQ_CUDA(ctx, ctx->out_i32.ensure(nn * 4 + 16));
+    HSQ_CUDA(ctx, ctx->out_u8.ensure((size_t)out_cap + 16));
+    if (n_bytes) HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->r1.ascii.p, text, (size_t)n_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (n) {
+        HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->sort_a.p, off, nn * 8, cudaMemcpyHostToDevice, ctx->stream));
+        HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->out_i32.p, len, nn * 4, cudaMemcpyHostToDevice, ctx->stream));
+        rows_len_kernel<<<grid_for(ctx, n, 256, 16), 256, 0, ctx->stream>>>(ctx->sort_a.as<int64_t>(), ctx->out_i32.as<int32_t>(), n, n_bytes,
+                                                                             ctx->sort_b.as<int64_t>(), d_status(ctx));
+        ctx->launches++;
+    }
+    if ((rc = scan_i64(ctx, ctx->sort_b.as<int64_t>(), n, ctx->sort_c.as<int64_t>(), ctx->sort_d.as<int64_t>()))) return rc;
+    if (n) {
+        rows_copy_kernel<<<grid_for(ctx, n * 32, 256, 16), 256, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->sort_a.as<int64_t>(),
+                                                                                  ctx->sort_d.as<int64_t>(), n, out_cap, ctx->out_u8.as<uint8_t>());
+        ctx->launches++;
+    }
+    HSQ_CUDA(ctx, cudaGetLastError());
+    HSQ_CUDA(ctx, cudaMemcpyAsync(out_offsets, ctx->sort_d.p, (nn + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    int st[1];
+    if ((rc = read_status(ctx, st, 1))) return rc;
+    if (st[0]) return fail(ctx, st[0], "hsq_gather_rows: a row reaches outside the text");
+    const int64_t total = out_offsets[n];
+    if (total > out_cap) return fail(ctx, HSQ_ERR_OVERFLOW, "hsq_gather_rows: out_cap too small; out_offsets holds the sizes");
+    if (total > 0) {
+        if (!out_data) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_gather_rows: null out_data");
+        HSQ_CUDA(ctx, cudaMemcpyAsync(out_data, ctx->out_u8.p, (size_t)total, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    return timer.finish();
+}
+
+extern "C" int32_t hsq_join_names(hsq_ctx* ctx, const hsq_name_join* in, hsq_name_join_out* out) {
+    if (!ctx || !in || !out) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_join_names: null argument");
+    const int64_t ns = in->sam_names.n, n1 = in->fq1_headers.n, n2 = in->fq2_headers.n;
+    const int64_t nf = std::min(n1, n2);  // the loop ends when either FASTQ iterator runs out (:214-215)
+    out->n_emitted = 0;
+    out->total_matching_pairs = 0;
+    const bool by_index = in->by_index != 0;
+    const bool check = !in->trimming_skipped && in->check_trim;
+    if (ns > 0 && (!in->sam_flags || !in->sam_seq_len || !out->sam_record || !out->fastq_record || !out->name_len || !out->status))
+        return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_join_names: null array");
+    if (check && ((n1 > 0 && !in->fq1_seq_len) || (n2 > 0 && !in->fq2_seq_len)))
+        return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_join_names: the trim check needs the FASTQ read lengths");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc;
+    DevBuf* ib = ctx->ing;
+    // inputs
+    if ((rc = upload_strings(ctx, &in->sam_names, &ib[0], &ib[1], "sam_names"))) return rc;
+    if ((rc = upload_strings(ctx, &in->fq1_headers, &ib[2], &ib[3], "fq1_headers"))) return rc;
+    if ((rc = upload_strings(ctx, &in->fq2_headers, &ib[4], &ib[5], "fq2_headers"))) return rc;
+    const size_t nss = (size_t)ns, n1s = (size_t)n1, n2s = (size_t)n2;
+    HSQ_CUDA(ctx, ib[6].ensure((nss * 3 + n1s + n2s) * 4 + 64));
+    int32_t* d_flags = ib[6].as<int32_t>();
+    int32_t* d_seq_len = d_flags + nss;
+    int32_t* d_qual_len = d_seq_len + nss;
+    int32_t* d_fq1_len = d_qual_len + nss;
+    int32_t* d_fq2_len = d_fq1_len + n1s;
+    if (ns) {
+        HSQ_CUDA(ctx, cudaMemcpyAsync(d_flags, in->sam_flags, nss * 4, cudaMemcpyHostToDevice, ctx->stream));
+        HSQ_CUDA(ctx, cudaMemcpyAsync(d_seq_len, in->sam_seq_len, nss * 4, cudaMemcpyHostToDevice, ctx->stream));
+        HSQ_CUDA(ctx, cudaMemcpyAsync(d_qual_len, in->sam_qual_len ? in->sam_qual_len : in->sam_seq_len, nss * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (check && n1) HSQ_CUDA(ctx, cudaMemcpyAsync(d_fq1_len, in->fq1_seq_len, n1s * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (check && n2) HSQ_CUDA(ctx, cudaMemcpyAsync(d_fq2_len, in->fq2_seq_len, n2s * 4, cudaMemcpyHostToDevice, ctx->stream));
+    // counters
+    HSQ_CUDA(ctx, ib[7].ensure(JC_WORDS * 4 + 64 * 4 * 3));
+    int* d_ctr = ib[7].as<int>();
+    int* d_live = d_ctr + JC_WORDS;  // up to 64 chunks per key set, three key sets
+    HSQ_CUDA(ctx, cudaMemsetAsync(d_ctr, 0, JC_WORDS * 4 + 64 * 4 * 3, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemsetAsync(d_ctr + JC_MISMATCH, 0x7f, 4, ctx->stream));  // 0x7f7f7f7f: larger than any position
+    HSQ_CUDA(ctx, cudaMemsetAsync(d_ctr + JC_TRIM, 0xff, 4, ctx->stream));
+    const int64_t* off_s = ib[1].as<int64_t>();
+    const int64_t* off_1 = ib[3].as<int64_t>();
+    const int64_t* off_2 = ib[5].as<int64_t>();
+    if (ns) max_len_kernel<<<grid_for(ctx, ns, 256, 8), 256, 0, ctx->stream>>>(off_s, ns, d_ctr + JC_MAX_SAM);
+    if (n1) max_len_kernel<<<grid_for(ctx, n1, 256, 8), 256, 0, ctx->stream>>>(off_1, n1, d_ctr + JC_MAX_FQ1);
+    if (n2) max_len_kernel<<<grid_for(ctx, n2, 256, 8), 256, 0, ctx->stream>>>(off_2, n2, d_ctr + JC_MAX_FQ2);
+    ctx->launches += 3;
+    int h_ctr[JC_WORDS + 64 * 3];
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_ctr, d_ctr, JC_WORDS * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    auto digits = [](int64_t v) { int d = 1; while (v >= 10) { v /= 10; d++; } return d; };
+    const int ch_s = by_index ? 0 : std::max(1, (h_ctr[JC_MAX_SAM] + 7) / 8);
+    const int ch_1 = by_index ? 0 : (h_ctr[JC_MAX_FQ1] + 3 + digits(std::max<int64_t>(n1 - 1, 0)) + 7) / 8;
+    const int ch_2 = by_index ? 0 : (h_ctr[JC_MAX_FQ2] + 3 + digits(std::max<int64_t>(n2 - 1, 0)) + 7) / 8;
+    if (ch_s > 64 || ch_1 > 64 || ch_2 > 64) return fail(ctx, HSQ_ERR_UNSUPPORTED, "hsq_join_names: read names longer than 490 bytes");
+    // working set
+    const size_t nmax = std::max(nss, std::max(n1s, n2s));
+    Arena ar;
+    const size_t o_keys_s = ar.reserve(nss * 8 * (size_t)std::max(ch_s, 1)), o_keys_1 = ar.reserve(n1s * 8 * (size_t)ch_1), o_keys_2 = ar.reserve(n2s * 8 * (size_t)ch_2);
+    const size_t o_kf = ar.reserve(nss * 8), o_kp = ar.reserve(nss * 8), o_ka = ar.reserve(nmax * 8), o_kb = ar.reserve(nmax * 8);
+    const size_t o_ps_a = ar.reserve(nss * 4), o_ps_b = ar.reserve(nss * 4), o_p1_a = ar.reserve(n1s * 4), o_p1_b = ar.reserve(n1s * 4);
+    const size_t o_p2_a = ar.reserve(n2s * 4), o_p2_b = ar.reserve(n2s * 4);
+    const size_t o_uid_s = ar.reserve(nss * 4), o_uid_1 = ar.reserve(n1s * 4), o_uid_2 = ar.reserve(n2s * 4), o_val = ar.reserve(nss * 4);
+    const size_t o_so1 = ar.reserve(n1s * 8), o_sl1 = ar.reserve(n1s * 4), o_so2 = ar.reserve(n2s * 8), o_sl2 = ar.reserve(n2s * 4);
+    const size_t o_head = ar.reserve(nss * 4), o_headmax = ar.reserve(nss * 4), o_nf = ar.reserve(nss * 4), o_excl = ar.reserve(nss * 4);
+    const size_t o_emit = ar.reserve(nss * 4), o_epos = ar.reserve(nss * 4), o_used = ar.reserve(nss * 4), o_nlen = ar.reserve(nss * 4), o_tgt = ar.reserve(nss * 4);
+    const size_t o_out = ar.reserve(nss * 13 + 64);
+    HSQ_CUDA(ctx, ib[8].ensure(ar.need + 256));
+    ar.base = ib[8].as<uint8_t>();
+    uint64_t *ka = ar.at<uint64_t>(o_ka), *kb = ar.at<uint64_t>(o_kb);
+    uint32_t *ps = ar.at<uint32_t>(o_ps_a), *ps_o = ar.at<uint32_t>(o_ps_b);
+    uint32_t *p1 = ar.at<uint32_t>(o_p1_a), *p1_o = ar.at<uint32_t>(o_p1_b), *p2 = ar.at<uint32_t>(o_p2_a), *p2_o = ar.at<uint32_t>(o_p2_b);
+    int32_t *uid_s = ar.at<int32_t>(o_uid_s), *uid_1 = ar.at<int32_t>(o_uid_1), *uid_2 = ar.at<int32_t>(o_uid_2), *val = ar.at<int32_t>(o_val);
+    // keys
+    if (n1) fq_keys_kernel<<<grid_for(ctx, n1, 128, 16), 128, 0, ctx->stream>>>(ib[2].as<uint8_t>(), off_1, n1, ch_1, 1, by_index ? nullptr : ar.at<uint64_t>(o_keys_1), uid_1);
+    if (n2) fq_keys_kernel<<<grid_for(ctx, n2, 128, 16), 128, 0, ctx->stream>>>(ib[4].as<uint8_t>(), off_2, n2, ch_2, 1, by_index ? nullptr : ar.at<uint64_t>(o_keys_2), uid_2);
+    ctx->launches += 2;
+    if (ns) {
+        if (by_index)
+            sam_intkeys_kernel<<<grid_for(ctx, ns, 128, 16), 128, 0, ctx->stream>>>(ib[0].as<uint8_t>(), off_s, d_flags, ns, ar.at<uint64_t>(o_keys_s), val, uid_s, d_ctr);
+        else
+            sam_keys_kernel<<<grid_for(ctx, ns, 128, 16), 128, 0, ctx->stream>>>(ib[0].as<uint8_t>(), off_s, d_flags, ns, ch_s, ar.at<uint64_t>(o_keys_s),
+                                                                                 ar.at<uint64_t>(o_kf), ar.at<uint64_t>(o_kp), uid_s, d_ctr);
+        ctx->launches++;
+    }
+    if (!by_index) {
+        if (ns) chunk_live_kernel<<<grid_for(ctx, ns * ch_s, 256, 16), 256, 0, ctx->stream>>>(ar.at<uint64_t>(o_keys_s), ns, ch_s, d_live);
+        if (n1) chunk_live_kernel<<<grid_for(ctx, n1 * ch_1, 256, 16), 256, 0, ctx->stream>>>(ar.at<uint64_t>(o_keys_1), n1, ch_1, d_live + 64);
+        if (n2) chunk_live_kernel<<<grid_for(ctx, n2 * ch_2, 256, 16), 256, 0, ctx->stream>>>(ar.at<uint64_t>(o_keys_2), n2, ch_2, d_live + 128);
+        ctx->launches += 3;
+    }
+    HSQ_CUDA(ctx, cudaGetLastError());
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_ctr, d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (h_ctr[JC_PARSE])
+        return fail(ctx, HSQ_ERR_UNSUPPORTED, "hsq_join_names: by_index needs integer read names (Integer.parseInt would throw NumberFormatException)");
+    const int64_t np = ns - h_ctr[JC_NONPRIMARY];
+    const int* live = h_ctr + JC_WORDS;
+    // sorts
+    if (ns) iota_u32_kernel<<<grid_for(ctx, ns, 256, 16), 256, 0, ctx->stream>>>(ps, ns);
+    ctx->launches++;
+    if (by_index) {
+        if (ns) {
+            if ((rc = sort_pass(ctx, ar.at<uint64_t>(o_keys_s), kb, ps, ps_o, ns, 34))) return rc;
+            std::swap(ps, ps_o);
+        }
+    } else {
+        if (ns) {
+            if ((rc = bit_sort(ctx, ar.at<uint64_t>(o_kf), ns, &ps, &ps_o, ka, kb))) return rc;
+            if ((rc = lsd_chunk_sort(ctx, ar.at<uint64_t>(o_keys_s), ch_s, live, ns, &ps, &ps_o, ka, kb))) return rc;
+            if (np < ns && (rc = bit_sort(ctx, ar.at<uint64_t>(o_kp), ns, &ps, &ps_o, ka, kb))) return rc;
+        }
+        if (n1) {
+            iota_u32_kernel<<<grid_for(ctx, n1, 256, 16), 256, 0, ctx->stream>>>(p1, n1);
+            ctx->launches++;
+            if ((rc = lsd_chunk_sort(ctx, ar.at<uint64_t>(o_keys_1), ch_1, live + 64, n1, &p1, &p1_o, ka, kb))) return rc;
+        }
+        if (n2) {
+            iota_u32_kernel<<<grid_for(ctx, n2, 256, 16), 256, 0, ctx->stream>>>(p2, n2);
+            ctx->launches++;
+            if ((rc = lsd_chunk_sort(ctx, ar.at<uint64_t>(o_keys_2), ch_2, live + 128, n2, &p2, &p2_o, ka, kb))) return rc;
+        }
+    }
+    // sorted FASTQ views and their checks
+    SortedIds f1{ib[2].as<uint8_t>(), ar.at<int64_t>(o_so1), ar.at<int32_t>(o_sl1)};
+    SortedIds f2{ib[4].as<uint8_t>(), ar.at<int64_t>(o_so2), ar.at<int32_t>(o_sl2)};
+    if (n1) fq_sorted_view_kernel<<<grid_for(ctx, n1, 256, 16), 256, 0, ctx->stream>>>(by_index ? nullptr : p1, off_1, uid_1, n1, ar.at<int64_t>(o_so1), ar.at<int32_t>(o_sl1));
+    if (n2) fq_sorted_view_kernel<<<grid_for(ctx, n2, 256, 16), 256, 0, ctx->stream>>>(by_index ? nullptr : p2, off_2, uid_2, n2, ar.at<int64_t>(o_so2), ar.at<int32_t>(o_sl2));
+    if (n1) fq_check_kernel<<<grid_for(ctx, n1, 256, 16), 256, 0, ctx->stream>>>(f1, f2, n1, nf, by_index ? 1 : 0, d_ctr);
+    ctx->launches += 3;
+    // the SAM side
+    int32_t* d_sam_record = ar.at<int32_t>(o_out);
+    int32_t* d_fastq_record = d_sam_record + nss;
+    int32_t* d_name_len = d_fastq_record + nss;
+    uint8_t* d_rec_status = reinterpret_cast<uint8_t*>(d_name_len + nss);
+    if (np > 0) {
+        const int g = grid_for(ctx, np, 128, 16);
+        sam_heads_kernel<<<g, 128, 0, ctx->stream>>>(ib[0].as<uint8_t>(), off_s, uid_s, d_flags, ps, np, by_index ? val : nullptr, ar.at<int32_t>(o_head),
+                                                     ar.at<int32_t>(o_nf), d_ctr);
+        ctx->launches++;
+        size_t tb1 = 0, tb2 = 0;
+        HSQ_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, tb1, ar.at<int32_t>(o_nf), ar.at<int32_t>(o_excl), (int)np, ctx->stream));
+        HSQ_CUDA(ctx, cub::DeviceScan::InclusiveScan(nullptr, tb2, ar.at<int32_t>(o_head), ar.at<int32_t>(o_headmax), cub::Max(), (int)np, ctx->stream));
+        HSQ_CUDA(ctx, ctx->sort_tmp.ensure(std::max(tb1, tb2) + 16));
+        HSQ_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->sort_tmp.p, tb1, ar.at<int32_t>(o_nf), ar.at<int32_t>(o_excl), (int)np, ctx->stream));
+        HSQ_CUDA(ctx, cub::DeviceScan::InclusiveScan(ctx->sort_tmp.p, tb2, ar.at<int32_t>(o_head), ar.at<int32_t>(o_headmax), cub::Max(), (int)np, ctx->stream));
+        TrimParams tp{check ? 1 : 0, in->three_prime, in->r1_first, in->r1_stop, in->r2_first, in->r2_stop};
+        join_match_kernel<<<g, 128, 0, ctx->stream>>>(ib[0].as<uint8_t>(), off_s, uid_s, d_flags, d_seq_len, d_qual_len, ps, np, by_index ? val : nullptr,
+                                                      ar.at<int32_t>(o_headmax), ar.at<int32_t>(o_excl), f1, nf, by_index ? nullptr : p1,
+                                                      by_index ? nullptr : p2, d_fq1_len, d_fq2_len, tp, ar.at<int32_t>(o_emit), ar.at<int32_t>(o_used),
+                                                      ar.at<int32_t>(o_nlen), ar.at<int32_t>(o_tgt), d_ctr);
+        ctx->launches++;
+        HSQ_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->sort_tmp.p, tb1, ar.at<int32_t>(o_emit), ar.at<int32_t>(o_epos), (int)np, ctx->stream));
+        ctx->launches += 3;  // library scans (approximate)
+    }
+    if (ns) {
+        join_scatter_kernel<<<grid_for(ctx, ns, 256, 16), 256, 0, ctx->stream>>>(ps, ns, np, ar.at<int32_t>(o_emit), ar.at<int32_t>(o_epos), ar.at<int32_t>(o_used),
+                                                                                 ar.at<int32_t>(o_nlen), d_sam_record, d_fastq_record, d_name_len, d_rec_status, d_ctr);
+        ctx->launches++;
+    }
+    HSQ_CUDA(ctx, cudaGetLastError());
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_ctr, d_ctr, JC_WORDS * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (h_ctr[JC_ORDER])
+        return fail(ctx, HSQ_ERR_UNSUPPORTED, "hsq_join_names: unique ids do not ascend along a sorted side; the reference's result depends on its merge order here");
+    // which exception the sequential loop meets first
+    const bool have_mismatch = np > 0 && nf > 0 && h_ctr[JC_MISMATCH] <= h_ctr[JC_KMAX];
+    const unsigned trim_key = (unsigned)h_ctr[JC_TRIM];
+    if (trim_key != 0xffffffffu) {
+        int32_t tgt = 0;
+        HSQ_CUDA(ctx, cudaMemcpyAsync(&tgt, ar.at<int32_t>(o_tgt) + (trim_key >> 1), 4, cudaMemcpyDeviceToHost, ctx->stream));
+        HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (!(have_mismatch && h_ctr[JC_MISMATCH] <= tgt)) {
+            if (trim_key & 1u) return fail(ctx, HSQ_ERR_NOT_TRIMMED, "hsq_join_names: a SAM read is longer than its FASTQ read after trimming (sorted primary record " + std::to_string(trim_key >> 1) + ")");
+            return fail(ctx, HSQ_ERR_OUT_OF_RANGE, "hsq_join_names: Unable to trim: first base to keep is not inside a FASTQ read");
+        }
+    }
+    if (have_mismatch)
+        return fail(ctx, HSQ_ERR_NAME_MISMATCH, "hsq_join_names: The read names within the Fastq files do not match at sorted position " + std::to_string(h_ctr[JC_MISMATCH]));
+    if (h_ctr[JC_PAIRS] == 0)
+        return fail(ctx, HSQ_ERR_NO_MATCHES, "hsq_join_names: The read names in the input Fastq files do not match the reads names in the provided bam/sam file");
+    out->n_emitted = h_ctr[JC_EMITTED];
+    out->total_matching_pairs = h_ctr[JC_PAIRS];
+    const size_t ne = (size_t)out->n_emitted;
+    if (ne) {
+        HSQ_CUDA(ctx, cudaMemcpyAsync(out->sam_record, d_sam_record, ne * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        HSQ_CUDA(ctx, cudaMemcpyAsync(out->fastq_record, d_fastq_record, ne * 4, cudaMemcpyDeviceToHost, ctx->stream));
+        HSQ_CUDA(ctx, cudaMemcpyAsync(out->name_len, d_name_len, ne * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    if (ns) HSQ_CUDA(ctx, cudaMemcpyAsync(out->status, d_rec_status, nss, cudaMemcpyDeviceToHost, ctx->stream));
+    return timer.finish();
+}

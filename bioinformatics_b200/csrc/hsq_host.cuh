@@ -73,6 +73,7 @@ struct hsq_ctx {
     hsq::DevSeqsOwned fs;
     hsq::DevBuf fi_start, fi_len, fi_refs, fi_size;
     int64_t fi_n = -1;
+    hsq::DevBuf ing[9];  // hsq_join_names: inputs, counters and one working arena
     int32_t fi_k = 0, fi_max_len = 0;
     // hsq_extend_batch pipelines chunks through  H2D | prep (encode, primer DP, bucket sorts) | capture DP | D2H  with three
     // complete buffer sets; the two sets not in the members above are parked here (see activate_extend_set)

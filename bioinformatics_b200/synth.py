@@ -241,3 +241,60 @@ def write_probe_info_file(probes, path, ext_uid_len=10, lig_uid_len=0):
                                str(probes.ext_start[k]), str(probes.ext_stop[k]), probes.ext.string(k),
                                str(probes.lig_start[k]), str(probes.lig_stop[k]), probes.lig.string(k),
                                str(probes.target_start[k]), str(probes.target_stop[k]), probes.target.string(k), ""]) + "\n")
+
+
+def make_ingest_case(n_pairs, read_len=150, seed=7, mapped_frac=0.9, lone_frac=0.03, nonprimary_frac=0.02, repeat_frac=0.01, orphan_frac=0.01,
+                     old_style=False, trim=(10, 139, 0, 139), three_prime=False, shuffle=True, crlf=False, final_newline=True):
+    """Synthetic input of `HSQutils dedup` as files hold it: two FASTQ texts in one (random) file order and the
+    SAM-side columns FastqAndBamFileMerger reads (QNAME, FLAG, read length), for the records a mapper would emit from the
+    trimmed reads: both mates of most pairs, some lone mates, not-primary lines, repeated lines and names the FASTQ files
+    do not hold.  Names follow Casava 1.8 ("<id> 1:N:0:1") or the older "<id>#0/1" style
+    (COMMON/utils/IlluminaFastQReadNameUtil.java:30-33).  Returns a dict."""
+    rng = np.random.default_rng(seed)
+    xy = rng.choice(100_000_000, size=n_pairs, replace=False)
+    tile = 1101 + (xy % 16)
+    ids = ["M01077:35:000000000-A3J96:1:%d:%d:%d" % (t, v // 10000, v % 10000) for t, v in zip(tile.tolist(), xy.tolist())]
+    if old_style:
+        ids = [s + "#0" for s in ids]
+        h1 = [s + "/1" for s in ids]
+        h2 = [s + "/2" for s in ids]
+    else:
+        h1 = [s + " 1:N:0:1" for s in ids]
+        h2 = [s + " 2:N:0:1" for s in ids]
+    lens = np.full(n_pairs, read_len, dtype=np.int32)
+    bases = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=(2, n_pairs, read_len))]
+    quals = (33 + rng.integers(2, 42, size=(2, n_pairs, read_len))).astype(np.uint8)
+    eol = b"\r\n" if crlf else b"\n"
+
+    def text(headers, b, q):
+        parts = []
+        for k, h in enumerate(headers):
+            parts += [b"@", h.encode(), eol, b[k].tobytes(), eol, b"+", eol, q[k].tobytes(), eol]
+        t = b"".join(parts)
+        return t if final_newline or not t else t[:-len(eol)]
+
+    fq1_text, fq2_text = text(h1, bases[0], quals[0]), text(h2, bases[1], quals[1])
+    # SAM side: names as a mapper writes them (the unique id), trimmed lengths
+    f1, s1, f2, s2 = trim
+    exp1 = (min(s1, read_len - 1) if three_prime else read_len - 1) + 1 - f1
+    exp2 = (min(s2, read_len - 1) if three_prime else read_len - 1) + 1 - f2
+    names, flags, slen = [], [], []
+    u = rng.random(n_pairs)
+    for k in range(n_pairs):
+        if u[k] >= mapped_frac:
+            continue
+        lone = rng.random() < lone_frac
+        which = (1, 2) if not lone else ((1,) if rng.random() < 0.5 else (2,))
+        for m in which:
+            fl = (0x41 if m == 1 else 0x81) | (0x10 if rng.random() < 0.5 else 0)
+            names.append(ids[k]); flags.append(fl); slen.append(exp1 if m == 1 else exp2)
+            if rng.random() < nonprimary_frac:
+                names.append(ids[k]); flags.append(fl | 0x100); slen.append(exp1 if m == 1 else exp2)
+            if rng.random() < repeat_frac:
+                names.append(ids[k]); flags.append(fl | 0x800); slen.append(exp1 if m == 1 else exp2)
+    for k in range(int(orphan_frac * n_pairs)):
+        names.append(("A00000:%d" if k % 2 else "Z99999:%d") % k); flags.append(0x41 if k % 3 else 0x81); slen.append(exp1)
+    order = rng.permutation(len(names)) if shuffle else np.arange(len(names))
+    return dict(n_pairs=n_pairs, ids=ids, fq1_headers=h1, fq2_headers=h2, fq1_text=fq1_text, fq2_text=fq2_text, fq_seq_len=lens,
+                bases=bases, quals=quals, sam_names=[names[i] for i in order], sam_flags=np.asarray(flags, dtype=np.int32)[order],
+                sam_seq_len=np.asarray(slen, dtype=np.int32)[order], trim=trim, three_prime=three_prime)

@@ -34,6 +34,10 @@ extern "C" {
 #define HSQ_ERR_UNSUPPORTED (-5)   /* input outside the accelerated domain (e.g. UID longer than 32 bases) */
 #define HSQ_ERR_OUT_OF_RANGE (-6)  /* Java would throw IndexOutOfBounds / IllegalArgument (e.g. trim start >= read length) */
 #define HSQ_ERR_OVERFLOW (-7)      /* an output slot was too small; the per-item overflow flags say which */
+#define HSQ_ERR_NAME_MISMATCH (-8) /* FASTQ one / two read names differ at a visited position (IllegalStateException, FastqAndBamFileMerger.java:270-273) */
+#define HSQ_ERR_NOT_TRIMMED (-9)   /* a SAM read is longer than its trimmed FASTQ read (UnableToMergeFastqAndBamFilesException, :366-371) */
+#define HSQ_ERR_NO_MATCHES (-10)   /* no FASTQ pair matched any SAM record (IllegalStateException, :143-148) */
+#define HSQ_ERR_MALFORMED (-11)    /* FASTQ text is not a sequence of 4-line records (htsjdk FastqReader throws SAMException) */
 
 #define HSQ_PRIMER_NOT_FOUND (-2147483647) /* Java `null` from getPrimerEndIndexInRead */
 
@@ -381,6 +385,62 @@ int32_t hsq_set_probe_ranges(hsq_ctx* ctx, const hsq_probe_ranges* ranges);
  * (probe set = intersection of the mates' sets, :478-483), a third stays unpaired, and a name seen on four or more records
  * completes a second pair and is removed from the results altogether (:484-486, :392-400). */
 int32_t hsq_assign_probes(hsq_ctx* ctx, const hsq_mapped_records* records, hsq_assign_out* out);
+
+/* ---- f2: FASTQ ingest and the FASTQ <-> SAM name join in front of the dedup path ------------------------------------- */
+/* Record index of FASTQ text as htsjdk's FastqReader reads it (htsjdk 2.9.0, git_superpom/pom.xml:72-75; the reference's call
+ * sites: HSQ/utils/FastqSorter.java:77,98): four lines per record ('\n' or '\r\n'), '@' header, '+' quality header, equal
+ * sequence / quality length, no blank line -- anything else fails the call with HSQ_ERR_MALFORMED.  Offsets are byte offsets
+ * into `text`; header_off/len exclude the '@'.  Record k is the k-th record of the file: the index FastqSorter appends to
+ * the header (FastqSorter.java:298-302) and the read index the dedup path breaks quality ties with.  More than `cap`
+ * records: HSQ_ERR_OVERFLOW with `n` set. */
+typedef struct hsq_fastq_index {
+    int64_t cap; /* in: entries available in each array */
+    int64_t n;   /* out: records in the text */
+    int64_t* header_off;
+    int32_t* header_len;
+    int64_t* seq_off;
+    int32_t* seq_len;
+    int64_t* qual_off;
+    int32_t* qual_len;
+} hsq_fastq_index;
+int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_fastq_index* out);
+
+/* FastqAndBamFileMerger.createBamFileWithDataFromRawFastqFiles (HSQ/process/FastqAndBamFileMerger.java:107-158) without the
+ * file codecs: both sorts and the merge loop of MergedSamIterator (:213-345) for the two configurations the dedup command
+ * uses.  by_index = 0 (…Identification.java:150-160): FASTQ records sorted by header + " _ " + ordinal
+ * (FastqSorter.java:298-302,334-339), SAM records by (read name, first of pair first) (BamSorter.java:348-361), joined on
+ * IlluminaFastQReadNameUtil.getUniqueIdForReadHeader (COMMON/utils/IlluminaFastQReadNameUtil.java:40-58).  by_index = 1
+ * (…Identification.java:871-881): FASTQ in file order, SAM names are integers (BamSorter.java:322-346), joined on the
+ * ordinal.  Records that compare equal keep input order.  A result that would depend on the merge loop meeting names out
+ * of order (unique ids not ascending along a sorted side) fails with HSQ_ERR_UNSUPPORTED. */
+typedef struct hsq_name_join {
+    hsq_seqs sam_names;          /* QNAME per SAM record, input order */
+    const int32_t* sam_flags;    /* FLAG: 0x40 first of pair, 0x100 not primary (dropped, :222-225) */
+    const int32_t* sam_seq_len;  /* record.getReadString().length() */
+    const int32_t* sam_qual_len; /* record.getBaseQualityString().length(); NULL = same as sam_seq_len */
+    hsq_seqs fq1_headers, fq2_headers; /* read headers without '@', file order */
+    const int32_t* fq1_seq_len;  /* read lengths (trim check); may be NULL when the check is off */
+    const int32_t* fq2_seq_len;
+    int32_t by_index;
+    int32_t trimming_skipped, check_trim;                     /* :366-368 */
+    int32_t three_prime, r1_first, r1_stop, r2_first, r2_stop; /* ProbeTrimmingInformation (FastqReadTrimmer.java:153-190) */
+} hsq_name_join;
+typedef struct hsq_name_join_out {
+    int64_t n_emitted;            /* out: records the merged iterator returns, in its order */
+    int64_t total_matching_pairs; /* out: getTotalMatches() (:343) */
+    int32_t* sam_record;   /* [sam n] e-th returned record = input record sam_record[e] */
+    int32_t* fastq_record; /* [sam n] ordinal, in FASTQ one (first of pair) or FASTQ two (otherwise), of the record whose
+                            *         sequence, qualities and appended index the returned record takes (:303-325) */
+    int32_t* name_len;     /* [sam n] length of the unique id of that position's FASTQ-one header (FASTQ_READ_NAME, :317) */
+    uint8_t* status;       /* [sam n] by INPUT record: 0 not primary, 1 returned, 2 dropped */
+} hsq_name_join_out;
+int32_t hsq_join_names(hsq_ctx* ctx, const hsq_name_join* in, hsq_name_join_out* out);
+
+/* out row e = text[off[e] .. off[e]+len[e]) for n rows (the raw read / quality strings storeFastqInfoInRecord puts into the
+ * merged records, FastqAndBamFileMerger.java:386-396): out_offsets gets n+1 entries; more than out_cap bytes:
+ * HSQ_ERR_OVERFLOW with out_offsets filled. */
+int32_t hsq_gather_rows(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, const int64_t* off, const int32_t* len, int64_t n,
+                        uint8_t* out_data, int64_t* out_offsets, int64_t out_cap);
 
 /* ---- sharded dedup: one process per GPU, exchange by the caller ------------------------------------------------------ */
 /* First half of FilterByUid.reduceReadsByProbeAndUid for this rank's pairs (host buffers in): writes pairs->n key

@@ -3,6 +3,7 @@
 #include "hsq_oracle_heatseq.hpp"
 #include "hsq_oracle_assign.hpp"
 #include "hsq_oracle_find.hpp"
+#include "hsq_oracle_ingest.hpp"
 #include "../include/hsq_b200.h"
 #include <cstring>
 #include <thread>
@@ -354,6 +355,60 @@ int32_t hsqo_resolve_multi_probe(const hsq_probe_table* pt, const hsq_candidates
 }
 
 // single-call helpers for the KAT tests
+// f2: FastqReader record index of FASTQ text (hsq_oracle_ingest.hpp)
+int32_t hsqo_index_fastq(const uint8_t* text, int64_t n_bytes, hsq_fastq_index* o) {
+    try {
+        FastqIndex ix = index_fastq(text, n_bytes);
+        o->n = (int64_t)ix.header_off.size();
+        if (o->n > o->cap) { g_err = "more records than cap"; return HSQ_ERR_OVERFLOW; }
+        for (int64_t k = 0; k < o->n; k++) {
+            o->header_off[k] = ix.header_off[(size_t)k]; o->header_len[k] = ix.header_len[(size_t)k];
+            o->seq_off[k] = ix.seq_off[(size_t)k]; o->seq_len[k] = ix.seq_len[(size_t)k];
+            o->qual_off[k] = ix.qual_off[(size_t)k]; o->qual_len[k] = ix.qual_len[(size_t)k];
+        }
+        return HSQ_OK;
+    } catch (const FastqMalformed& e) { g_err = e.what(); return HSQ_ERR_MALFORMED; }
+}
+
+// f2: the two sorts and the merge loop of FastqAndBamFileMerger (hsq_oracle_ingest.hpp)
+int32_t hsqo_join_names(const hsq_name_join* in, hsq_name_join_out* o) {
+    JoinInput ji;
+    JoinParams jp;
+    const int64_t ns = in->sam_names.n;
+    for (int64_t k = 0; k < ns; k++) ji.sam_names.push_back(get_str(in->sam_names.data, in->sam_names.offsets, k));
+    ji.sam_flags.assign(in->sam_flags, in->sam_flags + ns);
+    ji.sam_seq_len.assign(in->sam_seq_len, in->sam_seq_len + ns);
+    const int32_t* ql = in->sam_qual_len ? in->sam_qual_len : in->sam_seq_len;
+    ji.sam_qual_len.assign(ql, ql + ns);
+    for (int64_t k = 0; k < in->fq1_headers.n; k++) ji.fq1_headers.push_back(get_str(in->fq1_headers.data, in->fq1_headers.offsets, k));
+    for (int64_t k = 0; k < in->fq2_headers.n; k++) ji.fq2_headers.push_back(get_str(in->fq2_headers.data, in->fq2_headers.offsets, k));
+    if (in->fq1_seq_len) ji.fq1_seq_len.assign(in->fq1_seq_len, in->fq1_seq_len + in->fq1_headers.n);
+    else ji.fq1_seq_len.assign((size_t)in->fq1_headers.n, 0);
+    if (in->fq2_seq_len) ji.fq2_seq_len.assign(in->fq2_seq_len, in->fq2_seq_len + in->fq2_headers.n);
+    else ji.fq2_seq_len.assign((size_t)in->fq2_headers.n, 0);
+    jp.by_index = in->by_index != 0;
+    jp.trimming_skipped = in->trimming_skipped != 0; jp.check_trim = in->check_trim != 0; jp.three_prime = in->three_prime != 0;
+    jp.r1_first = in->r1_first; jp.r1_stop = in->r1_stop; jp.r2_first = in->r2_first; jp.r2_stop = in->r2_stop;
+    o->n_emitted = 0;
+    o->total_matching_pairs = 0;
+    try {
+        JoinOutput jo = join_names(ji, jp);
+        o->n_emitted = (int64_t)jo.sam_record.size();
+        o->total_matching_pairs = jo.total_matching_pairs;
+        for (size_t e = 0; e < jo.sam_record.size(); e++) {
+            o->sam_record[e] = jo.sam_record[e];
+            o->fastq_record[e] = jo.fastq_record[e];
+            o->name_len[e] = jo.name_len[e];
+        }
+        for (int64_t k = 0; k < ns; k++) o->status[k] = jo.status[(size_t)k];
+        return HSQ_OK;
+    } catch (const JoinNameMismatch& e) { g_err = e.what(); return HSQ_ERR_NAME_MISMATCH;
+    } catch (const JoinNotTrimmed& e) { g_err = e.what(); return HSQ_ERR_NOT_TRIMMED;
+    } catch (const JoinNoMatches& e) { g_err = e.what(); return HSQ_ERR_NO_MATCHES;
+    } catch (const JoinBadNumber& e) { g_err = e.what(); return HSQ_ERR_UNSUPPORTED;
+    } catch (const std::out_of_range& e) { g_err = e.what(); return HSQ_ERR_OUT_OF_RANGE; }
+}
+
 int32_t hsqo_primer_end(const char* primer, const char* read, double* weighted) {
     int64_t cells = 0;
     NwWorkspace ws;

@@ -1,0 +1,238 @@
+// hsq_oracle_ingest.hpp -- TEST INFRASTRUCTURE ONLY (parity oracle / timed CPU baseline).
+// CPU restatement of the FASTQ <-> SAM name join in front of the dedup path:
+//   HSQ/process/FastqAndBamFileMerger.java:65-94 (isTrimAmountCorrect), :107-158 (driver), :213-345 (the merge loop of
+//   MergedSamIterator), :386-396 (storeFastqInfoInRecord); HSQ/utils/FastqSorter.java:90-124,291-318 (index appended to the
+//   header with " _ "), :334-339 (FastqRecordNameComparator); HSQ/utils/BamSorter.java:322-361 (the two SAM comparators);
+//   COMMON/utils/IlluminaFastQReadNameUtil.java:40-58 (getUniqueIdForReadHeader); HSQ/process/FastqReadTrimmer.java:309-328.
+// The FASTQ text grammar is htsjdk's FastqReader (htsjdk 2.9.0, pinned in git_superpom/pom.xml:72-75, source absent from
+// /root/reference): four lines per record, '@' header, '+' quality header, equal sequence / quality length, no blank lines.
+// Parity: unpinned by the reference (its tests hold nothing for FastqAndBamFileMerger); pinned here on hand traces
+// (tests/test_ingest.py) and on a second, dictionary-based statement of the same join.
+// Sorting: the chunked external sorts (FastqSorter.java:291-318 + the TreeSet merge :136-141, BamSorter) are restated as one
+// stable in-memory sort by the same comparator.  With the index appended every FASTQ key is distinct, so the TreeSet merge
+// loses nothing; SAM records that compare equal (same name, same first-of-pair flag) keep input order.
+#pragma once
+#include <algorithm>
+#include <climits>
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace hsqo {
+
+static const char* const FASTQ_NAME_AND_INDEX_DELIMITER = " _ ";  // FastqSorter.java:50
+
+struct JoinNameMismatch : std::runtime_error { using std::runtime_error::runtime_error; };   // IllegalStateException :270-273
+struct JoinNotTrimmed : std::runtime_error { using std::runtime_error::runtime_error; };     // UnableToMergeFastqAndBamFilesException :370
+struct JoinNoMatches : std::runtime_error { using std::runtime_error::runtime_error; };      // IllegalStateException :143-148
+struct JoinBadNumber : std::runtime_error { using std::runtime_error::runtime_error; };      // NumberFormatException :276
+
+// IlluminaFastQReadNameUtil.getUniqueIdForReadHeader (:40-58)
+inline std::string unique_id_for_read_header(const std::string& h) {
+    size_t sp = h.find(' '), sl = h.find('/');
+    size_t end = std::min(std::min(sp, sl), h.size());  // npos is the largest value, as Integer.MAX_VALUE is there
+    return h.substr(0, end);
+}
+
+// the name both FASTQ headers go through before they are compared (:252-263)
+inline std::string fastq_join_name(std::string h) {
+    size_t us = h.rfind(FASTQ_NAME_AND_INDEX_DELIMITER);
+    if (us != std::string::npos) h = h.substr(0, us);
+    return unique_id_for_read_header(h);
+}
+
+// Integer.parseInt: optional sign, decimal digits, int32 range
+inline int32_t java_parse_int(const std::string& s) {
+    size_t i = 0;
+    bool neg = false;
+    if (!s.empty() && (s[0] == '-' || s[0] == '+')) { neg = s[0] == '-'; i = 1; }
+    if (i >= s.size()) throw JoinBadNumber("For input string: \"" + s + "\"");
+    int64_t v = 0;
+    for (; i < s.size(); i++) {
+        if (s[i] < '0' || s[i] > '9') throw JoinBadNumber("For input string: \"" + s + "\"");
+        v = v * 10 + (s[i] - '0');
+        if (v > (int64_t)INT32_MAX + 1) throw JoinBadNumber("For input string: \"" + s + "\"");
+    }
+    if (neg) v = -v;
+    if (v > INT32_MAX || v < INT32_MIN) throw JoinBadNumber("For input string: \"" + s + "\"");
+    return (int32_t)v;
+}
+
+// length FastqReadTrimmer.trim would keep (FastqReadTrimmer.java:309-328); throws as it does
+inline int trimmed_length(int len, int first, int last, bool three_prime) {
+    if (first >= len) throw std::out_of_range("Unable to trim bases from the beginning of a sequence");  // :310-312
+    int last_base = len - 1;
+    if (three_prime) last_base = std::min(last, len - 1);
+    if (last_base + 1 < first) throw std::out_of_range("substring end before begin");  // String.substring
+    return last_base + 1 - first;
+}
+
+struct JoinParams {
+    bool by_index = false;          // useFastqIndexesAsFastqReadNamesWhenMerging; also: FASTQ not sorted, no index appended
+    bool trimming_skipped = false, check_trim = true, three_prime = false;
+    int r1_first = 0, r1_stop = 0, r2_first = 0, r2_stop = 0;
+};
+
+struct JoinInput {
+    std::vector<std::string> sam_names;
+    std::vector<int32_t> sam_flags, sam_seq_len, sam_qual_len;
+    std::vector<std::string> fq1_headers, fq2_headers;  // without '@'
+    std::vector<int32_t> fq1_seq_len, fq2_seq_len;
+};
+
+struct JoinOutput {
+    std::vector<int32_t> sam_record, fastq_record, name_len;
+    std::vector<uint8_t> status;  // by input record: 0 not primary, 1 emitted, 2 dropped
+    int64_t total_matching_pairs = 0;
+};
+
+inline JoinOutput join_names(const JoinInput& in, const JoinParams& p) {
+    const size_t ns = in.sam_names.size();
+    JoinOutput out;
+    out.status.assign(ns, 2);
+    // FASTQ iterators: (header as the iterator returns it, ordinal in the file)
+    struct Fq { std::string header; int32_t ordinal; };
+    auto make_fastq = [&](const std::vector<std::string>& hs) {
+        std::vector<Fq> v(hs.size());
+        for (size_t k = 0; k < hs.size(); k++) {
+            v[k].ordinal = (int32_t)k;
+            v[k].header = p.by_index ? hs[k] : hs[k] + FASTQ_NAME_AND_INDEX_DELIMITER + std::to_string(k);  // FastqSorter.java:298-302
+        }
+        if (!p.by_index)  // FastqRecordNameComparator :334-339 (String.compareTo == unsigned byte order for ASCII)
+            std::stable_sort(v.begin(), v.end(), [](const Fq& a, const Fq& b) { return a.header < b.header; });
+        return v;
+    };
+    const std::vector<Fq> f1 = make_fastq(in.fq1_headers), f2 = make_fastq(in.fq2_headers);
+    // SAM iterator
+    std::vector<int32_t> order(ns);
+    for (size_t k = 0; k < ns; k++) order[k] = (int32_t)k;
+    auto first_of_pair = [&](int32_t r) { return (in.sam_flags[(size_t)r] & 0x40) != 0; };
+    if (p.by_index) {  // SamRecordNameAsIndexComparator, BamSorter.java:322-346 (names that are not integers: outside this statement)
+        std::vector<int32_t> key(ns);
+        for (size_t k = 0; k < ns; k++) key[k] = java_parse_int(in.sam_names[k]);
+        std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
+            if (key[(size_t)a] != key[(size_t)b]) return key[(size_t)a] < key[(size_t)b];
+            return first_of_pair(a) && !first_of_pair(b);
+        });
+    } else {  // SamRecordNameComparator, BamSorter.java:348-361
+        std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) {
+            int c = in.sam_names[(size_t)a].compare(in.sam_names[(size_t)b]);
+            if (c != 0) return c < 0;
+            return first_of_pair(a) && !first_of_pair(b);
+        });
+    }
+    // MergedSamIterator.getNextRecordToReturn (:213-345), run to exhaustion
+    size_t si = 0, fi1 = 0, fi2 = 0;
+    int32_t sam = -1;
+    const Fq *one = nullptr, *two = nullptr;
+    int32_t fastq_index = -1;
+    while (((sam < 0 && si < ns) || sam >= 0) && ((!one && fi1 < f1.size() && !two && fi2 < f2.size()) || (one && two))) {
+        if (sam < 0) {
+            sam = order[si++];
+            if (in.sam_flags[(size_t)sam] & 0x100) {  // :222-225
+                out.status[(size_t)sam] = 0;
+                sam = -1;
+                continue;
+            }
+        }
+        if (!one && !two) {
+            fastq_index++;
+            one = &f1[fi1++];
+            two = &f2[fi2++];
+        }
+        const std::string sam_name = unique_id_for_read_header(in.sam_names[(size_t)sam]);
+        const std::string one_name = fastq_join_name(one->header), two_name = fastq_join_name(two->header);
+        if (one_name != two_name)
+            throw JoinNameMismatch("The read names within the Fastq files do not match, Fastq1 has read name [" + one_name + "] whereas Fastq2 has read name [" + two_name + "]");
+        int cmp;
+        if (p.by_index) {
+            int32_t v = java_parse_int(sam_name);
+            cmp = v < fastq_index ? -1 : (v > fastq_index ? 1 : 0);
+        } else {
+            cmp = sam_name.compare(one_name);
+        }
+        if (cmp < 0) {
+            sam = -1;  // skipped with a warning (:282-297)
+        } else if (cmp > 0) {
+            one = two = nullptr;
+        } else {
+            const bool first = first_of_pair(sam);
+            const Fq* used = first ? one : two;
+            const int32_t fq_len = first ? in.fq1_seq_len[(size_t)used->ordinal] : in.fq2_seq_len[(size_t)used->ordinal];
+            if (!first) {
+                one = two = nullptr;
+                out.total_matching_pairs++;
+            }
+            // checkAndStoreFastqInfoInRecord :366-373, isTrimAmountCorrect :65-94 (the !trimmingSkipped branch is the only one reached)
+            if (!p.trimming_skipped && p.check_trim) {
+                const int expected = first ? trimmed_length(fq_len, p.r1_first, p.r1_stop, p.three_prime)
+                                           : trimmed_length(fq_len, p.r2_first, p.r2_stop, p.three_prime);
+                if (in.sam_seq_len[(size_t)sam] > expected || in.sam_qual_len[(size_t)sam] > expected)
+                    throw JoinNotTrimmed("Readname:" + in.sam_names[(size_t)sam] + " is not trimmed appropriately");
+            }
+            out.status[(size_t)sam] = 1;
+            out.sam_record.push_back(sam);
+            out.fastq_record.push_back(used->ordinal);
+            out.name_len.push_back((int32_t)one_name.size());
+            sam = -1;
+        }
+    }
+    // records the loop never reached stay "dropped"; non-primary ones among them are reported as such
+    for (size_t k = 0; k < ns; k++)
+        if (in.sam_flags[k] & 0x100) out.status[k] = 0;
+    if (out.total_matching_pairs == 0)
+        throw JoinNoMatches("The read names in the input Fastq files do not match the reads names in the provided bam/sam file");
+    return out;
+}
+
+// ---- FASTQ text -> record index (htsjdk FastqReader grammar, see the header) -------------------------------------------
+struct FastqIndex {
+    std::vector<int64_t> header_off, seq_off, qual_off;
+    std::vector<int32_t> header_len, seq_len, qual_len;
+};
+struct FastqMalformed : std::runtime_error { using std::runtime_error::runtime_error; };
+
+inline FastqIndex index_fastq(const uint8_t* text, int64_t n) {
+    FastqIndex ix;
+    int64_t pos = 0;
+    auto read_line = [&](int64_t* off, int32_t* len) -> bool {  // BufferedReader.readLine for \n and \r\n
+        if (pos >= n) return false;
+        int64_t e = pos;
+        while (e < n && text[e] != '\n') e++;
+        int64_t stop = e;
+        if (stop > pos && text[stop - 1] == '\r') stop--;
+        for (int64_t k = pos; k < stop; k++)
+            if (text[k] == '\r') throw FastqMalformed("lone carriage return");  // a third terminator readLine knows: not restated
+        *off = pos;
+        *len = (int32_t)(stop - pos);
+        pos = e < n ? e + 1 : n;
+        return true;
+    };
+    auto blank = [&](int64_t off, int32_t len) {  // StringUtil.isBlank
+        for (int32_t k = 0; k < len; k++)
+            if (text[off + k] > ' ') return false;
+        return true;
+    };
+    while (true) {
+        int64_t o[4];
+        int32_t l[4];
+        if (!read_line(&o[0], &l[0])) break;
+        for (int k = 1; k < 4; k++)
+            if (!read_line(&o[k], &l[k])) throw FastqMalformed("File is too short");
+        for (int k = 0; k < 4; k++)
+            if (blank(o[k], l[k])) throw FastqMalformed("Missing line");
+        if (text[o[0]] != '@') throw FastqMalformed("Sequence header must start with @");
+        if (text[o[2]] != '+') throw FastqMalformed("Quality header must start with +");
+        if (l[1] != l[3]) throw FastqMalformed("Sequence and quality line must be the same length");
+        ix.header_off.push_back(o[0] + 1);
+        ix.header_len.push_back(l[0] - 1);
+        ix.seq_off.push_back(o[1]);
+        ix.seq_len.push_back(l[1]);
+        ix.qual_off.push_back(o[3]);
+        ix.qual_len.push_back(l[3]);
+    }
+    return ix;
+}
+
+}  // namespace hsqo

@@ -10,7 +10,7 @@ import subprocess
 import numpy as np
 
 from bioinformatics_b200 import _abi as A
-from bioinformatics_b200.batches import (AlignResult, AssignResult, ExtendResult, FindResult, RecordResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
+from bioinformatics_b200.batches import (FastqIndexResult, NameJoinResult, AlignResult, AssignResult, ExtendResult, FindResult, RecordResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
                                          merge_args, scorer)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -37,7 +37,7 @@ def lib():
         for name in ("hsqo_align_batch", "hsqo_trim_batch", "hsqo_dedup_batch", "hsqo_extend_batch",
                      "hsqo_resolve_multi_probe", "hsqo_primer_end", "hsqo_index_of_first_match_in_reference",
                      "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs", "hsqo_assign_probes",
-                     "hsqo_extend_records", "hsqo_find_candidates"):
+                     "hsqo_extend_records", "hsqo_find_candidates", "hsqo_index_fastq", "hsqo_join_names"):
             getattr(_lib, name).restype = C.c_int32
     return _lib
 
@@ -112,6 +112,26 @@ def assign_probes(ranges, records, max_probes=4):
     pc, rc, oc = ranges.c(), records.c(), out.c()
     _check(lib().hsqo_assign_probes(C.byref(pc), C.byref(rc), C.byref(oc)))
     return out
+
+
+def index_fastq(text, cap=None):
+    """FastqReader record index of FASTQ text on the CPU (hsq_oracle_ingest.hpp)."""
+    text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+    if cap is None:
+        cap = len(text) // 8 + 1
+    out = FastqIndexResult(cap)
+    oc = out.c()
+    _check(lib().hsqo_index_fastq(A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(oc)))
+    out.n = int(oc.n)
+    return out
+
+
+def join_names(join):
+    """The two sorts and the merge loop of FastqAndBamFileMerger on the CPU, sequential as in the reference."""
+    out = NameJoinResult(join.n)
+    jc, oc = join.c(), out.c()
+    _check(lib().hsqo_join_names(C.byref(jc), C.byref(oc)))
+    return out.take(oc)
 
 
 def find_candidates(seqs, reads, quals, kmer=5, max_refs_per_kmer=15000, leading_quality=0, trailing_quality=0, candidate_limit=10,

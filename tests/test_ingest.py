@@ -1,0 +1,384 @@
+"""FASTQ ingest and the FASTQ <-> SAM name join (HSQ/process/FastqAndBamFileMerger.java:65-94,107-158,213-345,
+386-396; HSQ/utils/FastqSorter.java:90-124,291-339; HSQ/utils/BamSorter.java:322-361;
+COMMON/utils/IlluminaFastQReadNameUtil.java:40-58).
+
+The reference's tests hold nothing for FastqAndBamFileMerger (parity unpinned by the reference).  The oracle is the sequential
+two-cursor loop restated line by line; it is pinned here on hand traces of that loop and cross-checked against a second,
+dictionary-based statement of the join; the CUDA path is then compared with the oracle array by array."""
+import re
+from collections import defaultdict
+
+import numpy as np
+import pytest
+
+from bioinformatics_b200 import _abi as A
+from bioinformatics_b200 import synth
+from bioinformatics_b200.batches import NameJoinHost
+from oracle import oracle as O
+
+
+def join_of(case, **kw):
+    f1, s1, f2, s2 = case["trim"]
+    args = dict(fq1_seq_len=case["fq_seq_len"], fq2_seq_len=case["fq_seq_len"], r1_first=f1, r1_stop=s1, r2_first=f2, r2_stop=s2,
+                three_prime=case["three_prime"])
+    args.update(kw)
+    return NameJoinHost(case["sam_names"], case["sam_flags"], case["sam_seq_len"], case["fq1_headers"], case["fq2_headers"], **args)
+
+
+def second_statement(join, by_index=False):
+    """The join without cursors: FASTQ positions of every unique id in a dictionary, a per-id count of consumed positions."""
+    uid = lambda h: re.split("[ /]", h, maxsplit=1)[0]
+    h1, h2, names = join.fq1_headers.strings(), join.fq2_headers.strings(), join.sam_names.strings()
+    nf = min(len(h1), len(h2))
+    flags = join.sam_flags
+    if by_index:
+        o1, o2 = list(range(len(h1))), list(range(len(h2)))
+        sam_order = sorted(range(len(names)), key=lambda r: (int(names[r]), 0 if flags[r] & 0x40 else 1))
+        key_of = lambda r: int(names[r])
+        positions = {k: [k] for k in range(nf)}
+    else:
+        o1 = sorted(range(len(h1)), key=lambda k: (h1[k] + " _ %d" % k).encode())
+        o2 = sorted(range(len(h2)), key=lambda k: (h2[k] + " _ %d" % k).encode())
+        sam_order = sorted(range(len(names)), key=lambda r: (names[r].encode(), 0 if flags[r] & 0x40 else 1))
+        key_of = lambda r: uid(names[r])
+        positions = defaultdict(list)
+        for q in range(nf):
+            positions[uid(h1[o1[q]])].append(q)
+    used = defaultdict(int)
+    status = np.full(len(names), 2, dtype=np.uint8)
+    sam_record, fastq_record, name_len = [], [], []
+    pairs = 0
+    for r in sam_order:
+        if flags[r] & 0x100:
+            status[r] = 0
+            continue
+        k = key_of(r)
+        pos = positions.get(k, [])
+        c = used[k]
+        first = bool(flags[r] & 0x40)
+        if not first:
+            used[k] += 1
+        if c < len(pos):
+            q = pos[c]
+            status[r] = 1
+            sam_record.append(r)
+            fastq_record.append(o1[q] if first else o2[q])
+            name_len.append(len(uid(h1[o1[q]])))
+            pairs += 0 if first else 1
+    return sam_record, fastq_record, name_len, status, pairs
+
+
+def assert_same(got, exp):
+    assert got.n_emitted == exp.n_emitted and got.total_matching_pairs == exp.total_matching_pairs
+    for a, b in zip(got.emitted(), exp.emitted()):
+        assert (a == b).all()
+    assert (got.status == exp.status).all()
+
+
+KAT_BY_NAME = dict(
+    sam_names=["r3", "r1", "r1", "r2", "r2", "zz", "r1"], sam_flags=[0x81, 0x41, 0x81, 0x141, 0x41, 0x41, 0x81], sam_seq_len=[5] * 7,
+    fq1=["r2 1:N", "r1 1:N", "r3 1:N"], fq2=["r2 2:N", "r1 2:N", "r3 2:N"],
+    # hand trace of MergedSamIterator: FASTQ sorted = r1 (file ordinal 1), r2 (0), r3 (2); SAM sorted = r1/1 [1], r1/2 [2], r1/2 [6],
+    # r2 not primary [3], r2/1 [4], r3/2 [0], zz [5].  [1] takes FASTQ one of r1; [2] takes FASTQ two of r1 and moves the FASTQ
+    # cursor to r2, so [6] compares r1 < r2 and is skipped; [3] is dropped as not primary; [4] takes r2; the cursor moves to r3 for
+    # [0], which is a read two: matched, cursor past the end, loop over, [5] is never looked at.
+    sam_record=[1, 2, 4, 0], fastq_record=[1, 1, 0, 2], name_len=[2, 2, 2, 2], status=[1, 1, 1, 0, 1, 2, 2], pairs=2)
+
+KAT_BY_INDEX = dict(
+    sam_names=["2", "0", "0", "10", "-1", "1"], sam_flags=[0x81, 0x41, 0x81, 0x41, 0x41, 0x41], sam_seq_len=[5] * 6,
+    fq1=["a:1 1:N", "b:22/1", "c"], fq2=["a:1 2:N", "b:22/2", "c"],
+    # sorted by Integer.parseInt: -1 [4], 0/1 [1], 0/2 [2], 1 [5], 2 [0], 10 [3]; FASTQ position k has key k.  -1 < 0: skipped; [1] and
+    # [2] take position 0; [5] takes position 1 (FASTQ one); [0] is a read two at position 2: matched, FASTQ exhausted; [3] unreached.
+    sam_record=[1, 2, 5, 0], fastq_record=[0, 0, 1, 2], name_len=[3, 3, 4, 1], status=[1, 1, 1, 2, 2, 1], pairs=2)
+
+
+def kat_join(k, by_index):
+    return NameJoinHost(k["sam_names"], k["sam_flags"], k["sam_seq_len"], k["fq1"], k["fq2"], [9, 9, 9], [9, 9, 9], by_index=by_index, check_trim=False)
+
+
+def check_kat(res, k):
+    s, f, n = res.emitted()
+    assert list(s) == k["sam_record"] and list(f) == k["fastq_record"] and list(n) == k["name_len"]
+    assert list(res.status) == k["status"] and res.total_matching_pairs == k["pairs"]
+
+
+def error_cases():
+    """(join, expected status) for every exception of the path."""
+    base = dict(sam_names=["r1", "r1", "r2", "r2"], sam_flags=[0x41, 0x81, 0x41, 0x81], sam_seq_len=[8, 8, 8, 8])
+    fq1, fq2 = ["r1 1", "r2 1"], ["r1 2", "r2 2"]
+    cases = []
+    # FASTQ two holds another read at the second position: IllegalStateException :270-273
+    cases.append((NameJoinHost(fq1_headers=fq1, fq2_headers=["r1 2", "rX 2"], fq1_seq_len=[10, 10], fq2_seq_len=[10, 10], check_trim=False, **base),
+                  A.HSQ_ERR_NAME_MISMATCH))
+    # ... but a mismatch behind the last position the loop fetches is never seen
+    cases.append((NameJoinHost(["r1", "r1"], [0x41, 0x81], [8, 8], fq1, ["r1 2", "rX 2"], [10, 10], [10, 10], check_trim=False), A.HSQ_OK))
+    # SAM read longer than the trimmed FASTQ read: UnableToMergeFastqAndBamFilesException :366-371 (10 - 3 = 7 < 8)
+    cases.append((NameJoinHost(fq1_headers=fq1, fq2_headers=fq2, fq1_seq_len=[10, 10], fq2_seq_len=[10, 10], r1_first=3, **base), A.HSQ_ERR_NOT_TRIMMED))
+    # same lengths with the check switched off by --trimmingSkipped
+    cases.append((NameJoinHost(fq1_headers=fq1, fq2_headers=fq2, fq1_seq_len=[10, 10], fq2_seq_len=[10, 10], r1_first=3, trimming_skipped=True, **base),
+                  A.HSQ_OK))
+    # three prime trimming: kept [0, 6] = 7 bases < 8
+    cases.append((NameJoinHost(fq1_headers=fq1, fq2_headers=fq2, fq1_seq_len=[10, 10], fq2_seq_len=[10, 10], three_prime=True, r1_stop=9, r2_stop=6, **base),
+                  A.HSQ_ERR_NOT_TRIMMED))
+    # qualities longer than the trimmed read although the bases fit
+    cases.append((NameJoinHost(fq1_headers=fq1, fq2_headers=fq2, fq1_seq_len=[10, 10], fq2_seq_len=[10, 10], sam_qual_len=[8, 8, 11, 8], **base),
+                  A.HSQ_ERR_NOT_TRIMMED))
+    # first base to keep outside the FASTQ read: FastqReadTrimmer.trim throws (FastqReadTrimmer.java:310-312)
+    cases.append((NameJoinHost(fq1_headers=fq1, fq2_headers=fq2, fq1_seq_len=[10, 10], fq2_seq_len=[10, 10], r2_first=10, **base), A.HSQ_ERR_OUT_OF_RANGE))
+    # the trim failure of r1 comes before the name mismatch at r2 ...
+    cases.append((NameJoinHost(fq1_headers=fq1, fq2_headers=["r1 2", "rX 2"], fq1_seq_len=[10, 10], fq2_seq_len=[10, 10], r1_first=3, **base),
+                  A.HSQ_ERR_NOT_TRIMMED))
+    # ... and the other way round
+    cases.append((NameJoinHost(fq1_headers=fq1, fq2_headers=["rX 2", "r2 2"], fq1_seq_len=[10, 10], fq2_seq_len=[10, 8], r2_first=1, **base),
+                  A.HSQ_ERR_NAME_MISMATCH))
+    # nothing matches: IllegalStateException :143-148 (only read ones match -> getTotalMatches() is still 0)
+    cases.append((NameJoinHost(["q1", "q2"], [0x41, 0x81], [8, 8], fq1, fq2, [10, 10], [10, 10], check_trim=False), A.HSQ_ERR_NO_MATCHES))
+    cases.append((NameJoinHost(["r1", "r2"], [0x41, 0x41], [8, 8], fq1, fq2, [10, 10], [10, 10], check_trim=False), A.HSQ_ERR_NO_MATCHES))
+    cases.append((NameJoinHost(["r1"], [0x181], [8], fq1, fq2, [10, 10], [10, 10], check_trim=False), A.HSQ_ERR_NO_MATCHES))
+    cases.append((NameJoinHost(["r1"], [0x81], [8], [], [], [], [], check_trim=False), A.HSQ_ERR_NO_MATCHES))
+    # by index with a name that is not an integer: NumberFormatException
+    cases.append((NameJoinHost(["0", "x1"], [0x81, 0x81], [8, 8], fq1, fq2, [10, 10], [10, 10], by_index=True, check_trim=False), A.HSQ_ERR_UNSUPPORTED))
+    cases.append((NameJoinHost(["0", "99999999999"], [0x81, 0x81], [8, 8], fq1, fq2, [10, 10], [10, 10], by_index=True, check_trim=False),
+                  A.HSQ_ERR_UNSUPPORTED))
+    # unequal FASTQ files: the loop stops with the shorter one
+    cases.append((NameJoinHost(fq1_headers=fq1, fq2_headers=["r1 2"], fq1_seq_len=[10, 10], fq2_seq_len=[10], check_trim=False, **base), A.HSQ_OK))
+    return cases
+
+
+def run_status(fn, join):
+    try:
+        return A.HSQ_OK, fn(join)
+    except Exception as e:  # OracleError / HsqError both carry .status
+        return e.status, None
+
+
+FASTQ_BAD = [
+    (b"@r1\nACGT\n+\nIII\n", A.HSQ_ERR_MALFORMED),           # lengths differ
+    (b"r1\nACGT\n+\nIIII\n", A.HSQ_ERR_MALFORMED),           # no '@'
+    (b"@r1\nACGT\n-\nIIII\n", A.HSQ_ERR_MALFORMED),          # no '+'
+    (b"@r1\nACGT\n+\nIIII\n@r2\nAC\n+\n", A.HSQ_ERR_MALFORMED),  # too short
+    (b"@r1\nACGT\n+\nIIII\n\n", A.HSQ_ERR_MALFORMED),        # blank line at the end
+    (b"@r1\n\n+\n\n", A.HSQ_ERR_MALFORMED),                  # empty read
+    (b"@r1\nACGT\n+\nIIII\n   \nAC\n+\nII\n", A.HSQ_ERR_MALFORMED),  # blank header
+]
+FASTQ_GOOD = [b"", b"@r1 x/1\nACGT\n+\nIIII\n", b"@r1\nACGT\n+r1\nIIII", b"@r1\r\nACGT\r\n+\r\nIIII\r\n@r2\r\nA\r\n+\r\n#\r\n", b"@a\nA\n+\n@\n@b\n@\n+\n+\n",
+              b"@r1\r\nACGT\r\n+\r\nIIII\r"]
+
+
+def split_statement(text):
+    """FASTQ records by str.splitlines-style reading (second statement of the index for well-formed text)."""
+    lines, pos = [], 0
+    while pos < len(text):
+        e = text.find(b"\n", pos)
+        e = len(text) if e < 0 else e
+        stop = e - 1 if e > pos and text[e - 1:e] == b"\r" else e
+        lines.append((pos, stop - pos))
+        pos = e + 1
+    recs = [lines[k:k + 4] for k in range(0, len(lines), 4)]
+    return dict(header_off=[r[0][0] + 1 for r in recs], header_len=[r[0][1] - 1 for r in recs], seq_off=[r[1][0] for r in recs],
+                seq_len=[r[1][1] for r in recs], qual_off=[r[3][0] for r in recs], qual_len=[r[3][1] for r in recs])
+
+
+# ---------------------------------------------------------------------------------------------------------------- CPU: the oracle
+def test_oracle_hand_traces():
+    check_kat(O.join_names(kat_join(KAT_BY_NAME, False)), KAT_BY_NAME)
+    check_kat(O.join_names(kat_join(KAT_BY_INDEX, True)), KAT_BY_INDEX)
+
+
+def test_oracle_unique_id():
+    """IlluminaFastQReadNameUtil.getUniqueIdForReadHeader on the two sample headers of its source (:30-33), through the join."""
+    j = NameJoinHost(["MS5_15454:1:1110:12527:26507#26", "M01077:35:000000000-A3J96:1:1102:13646:7860"], [0x81, 0x81], [5, 5],
+                     ["M01077:35:000000000-A3J96:1:1102:13646:7860 1:N:0:1", "MS5_15454:1:1110:12527:26507#26/1"],
+                     ["M01077:35:000000000-A3J96:1:1102:13646:7860 2:N:0:1", "MS5_15454:1:1110:12527:26507#26/2"], check_trim=False)
+    r = O.join_names(j)
+    s, f, n = r.emitted()
+    assert list(s) == [1, 0] and list(f) == [0, 1] and list(n) == [43, 31]
+
+
+@pytest.mark.parametrize("old_style", [False, True])
+def test_oracle_equals_second_statement(old_style):
+    case = synth.make_ingest_case(3000, read_len=40, seed=11 + old_style, old_style=old_style, trim=(3, 30, 0, 30))
+    j = join_of(case)
+    exp = second_statement(j)
+    got = O.join_names(j)
+    s, f, n = got.emitted()
+    assert list(s) == exp[0] and list(f) == exp[1] and list(n) == exp[2] and (got.status == exp[3]).all() and got.total_matching_pairs == exp[4]
+    assert got.n_emitted > 4000 and (got.status == 0).sum() > 10 and (got.status == 2).sum() > 10
+
+
+def by_index_case(case, seed=3):
+    """The second configuration: the records of the first join renamed to the FASTQ ordinal they took (:319-321)."""
+    first = O.join_names(join_of(case))
+    s, f, _ = first.emitted()
+    rng = np.random.default_rng(seed)
+    names = [str(int(v)) for v in f] + ["-5", str(case["n_pairs"] + 7), str(int(f[0]))]
+    flags = np.concatenate([case["sam_flags"][s], [0x41, 0x81, 0x81]]).astype(np.int32)
+    order = rng.permutation(len(names))
+    return NameJoinHost([names[i] for i in order], flags[order], np.full(len(names), 30, dtype=np.int32), case["fq1_headers"], case["fq2_headers"],
+                        by_index=True, check_trim=False)
+
+
+def test_oracle_by_index_equals_second_statement():
+    case = synth.make_ingest_case(2000, read_len=40, seed=5, trim=(3, 30, 0, 30))
+    j = by_index_case(case)
+    exp = second_statement(j, by_index=True)
+    got = O.join_names(j)
+    s, f, n = got.emitted()
+    assert list(s) == exp[0] and list(f) == exp[1] and list(n) == exp[2] and (got.status == exp[3]).all() and got.total_matching_pairs == exp[4]
+
+
+def test_oracle_errors():
+    for j, want in error_cases():
+        st, _ = run_status(O.join_names, j)
+        assert st == want
+
+
+def test_oracle_fastq_index():
+    for text in FASTQ_GOOD:
+        ix = O.index_fastq(text)
+        exp = split_statement(text)
+        assert ix.n == len(exp["header_off"])
+        for f in ix.FIELDS:
+            assert list(ix.head()[f]) == exp[f], f
+    for text, want in FASTQ_BAD:
+        with pytest.raises(O.OracleError) as e:
+            O.index_fastq(text)
+        assert e.value.status == want
+    case = synth.make_ingest_case(500, read_len=30, seed=2, final_newline=False)
+    ix = O.index_fastq(case["fq1_text"])
+    t = np.frombuffer(case["fq1_text"], dtype=np.uint8)
+    assert ix.n == 500 and (ix.seq_len[:500] == 30).all()
+    for k in (0, 17, 499):
+        assert t[ix.header_off[k]:ix.header_off[k] + ix.header_len[k]].tobytes().decode() == case["fq1_headers"][k]
+        assert (t[ix.seq_off[k]:ix.seq_off[k] + 30] == case["bases"][0][k]).all() and (t[ix.qual_off[k]:ix.qual_off[k] + 30] == case["quals"][0][k]).all()
+
+
+# ---------------------------------------------------------------------------------------------------------------- GPU: parity
+@pytest.fixture(scope="module")
+def ctx():
+    from bioinformatics_b200._lib import Context
+    with Context(0) as c:
+        yield c
+
+
+@pytest.mark.gpu
+def test_gpu_hand_traces(ctx):
+    check_kat(ctx.join_names(kat_join(KAT_BY_NAME, False)), KAT_BY_NAME)
+    check_kat(ctx.join_names(kat_join(KAT_BY_INDEX, True)), KAT_BY_INDEX)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("n_pairs,old_style,three_prime,seed", [(1, False, False, 1), (2, True, False, 2), (700, False, True, 3), (700, True, False, 4),
+                                                                  (60000, False, False, 5), (60000, True, True, 6)])
+def test_gpu_join_by_name_equals_oracle(ctx, n_pairs, old_style, three_prime, seed):
+    case = synth.make_ingest_case(n_pairs, read_len=50, seed=seed, old_style=old_style, trim=(4, 40, 2, 44), three_prime=three_prime,
+                                  mapped_frac=1.0 if n_pairs < 10 else 0.9)
+    j = join_of(case)
+    assert_same(ctx.join_names(j), O.join_names(j))
+
+
+@pytest.mark.gpu
+def test_gpu_join_repeated_fastq_names_and_heavy_repeats(ctx):
+    """FASTQ files that hold a name more than once, SAM names with many records each, '/1' '/2' names kept by the mapper."""
+    rng = np.random.default_rng(9)
+    ids = ["n%02d" % k for k in range(40)]
+    h = [ids[int(k)] for k in rng.integers(0, 40, size=300)]
+    fq1 = [x + " 1:N:0:1" for x in h]
+    fq2 = [x + " 2:N:0:1" for x in h]
+    picks = rng.integers(0, 44, size=2500)
+    names = [("n%02d" % k) + ("" if k % 3 else ("/1" if k % 2 else "/2")) for k in picks]
+    flags = rng.choice([0x41, 0x81, 0x141, 0x181, 0x841, 0x1], size=2500).astype(np.int32)
+    j = NameJoinHost(names, flags, np.full(2500, 9, dtype=np.int32), fq1, fq2, check_trim=False)
+    exp = O.join_names(j)
+    assert exp.n_emitted > 200
+    assert_same(ctx.join_names(j), exp)
+
+
+@pytest.mark.gpu
+def test_gpu_join_by_index_equals_oracle(ctx):
+    for n, seed in ((300, 1), (40000, 2)):
+        case = synth.make_ingest_case(n, read_len=40, seed=seed, trim=(3, 30, 0, 30))
+        j = by_index_case(case)
+        assert_same(ctx.join_names(j), O.join_names(j))
+
+
+@pytest.mark.gpu
+def test_gpu_join_errors(ctx):
+    from bioinformatics_b200._lib import HsqError
+    for j, want in error_cases():
+        st, got = run_status(ctx.join_names, j)
+        assert st == want, ctx.lib.hsq_last_error(ctx.h)
+        if want == A.HSQ_OK:
+            assert_same(got, O.join_names(j))
+    # ids that do not ascend along the sorted FASTQ side ("a/1" sorts after "a-b/1", the id "a" before "a-b"): refused
+    j = NameJoinHost(["a", "a-b"], [0x81, 0x81], [5, 5], ["a/1", "a-b/1"], ["a/2", "a-b/2"], check_trim=False)
+    with pytest.raises(HsqError) as e:
+        ctx.join_names(j)
+    assert e.value.status == A.HSQ_ERR_UNSUPPORTED
+
+
+@pytest.mark.gpu
+def test_gpu_fastq_index_equals_oracle(ctx):
+    from bioinformatics_b200._lib import HsqError
+    for text in FASTQ_GOOD:
+        got, exp = ctx.index_fastq(text), O.index_fastq(text)
+        assert got.n == exp.n
+        for f in got.FIELDS:
+            assert (got.head()[f] == exp.head()[f]).all(), f
+    for text, want in FASTQ_BAD:
+        with pytest.raises(HsqError) as e:
+            ctx.index_fastq(text)
+        assert e.value.status == want
+    with pytest.raises(HsqError) as e:
+        ctx.index_fastq(b"@r1\rACGT\n+\nIIII\n")
+    assert e.value.status == A.HSQ_ERR_UNSUPPORTED
+    for n, kw in ((1, {}), (4097, dict(crlf=True)), (30000, dict(final_newline=False)), (30000, dict(old_style=True))):
+        case = synth.make_ingest_case(n, read_len=75, seed=n % 7, **kw)
+        for text in (case["fq1_text"], case["fq2_text"]):
+            got, exp = ctx.index_fastq(text), O.index_fastq(text)
+            assert got.n == exp.n == n
+            for f in got.FIELDS:
+                assert (got.head()[f] == exp.head()[f]).all(), f
+    with pytest.raises(HsqError) as e:
+        ctx.index_fastq(case["fq1_text"], cap=10)
+    assert e.value.status == A.HSQ_ERR_OVERFLOW
+
+
+@pytest.mark.gpu
+def test_gpu_files_to_merged_records(ctx):
+    """FASTQ texts + SAM columns -> the merged records' read index, raw bases and raw qualities, device path against the oracle's."""
+    case = synth.make_ingest_case(20000, read_len=60, seed=21, trim=(5, 50, 0, 50))
+    t1, t2 = case["fq1_text"], case["fq2_text"]
+    out = {}
+    for name, index_fastq, join_names in (("gpu", ctx.index_fastq, ctx.join_names), ("cpu", O.index_fastq, O.join_names)):
+        i1, i2 = index_fastq(t1), index_fastq(t2)
+        a1, a2 = np.frombuffer(t1, dtype=np.uint8), np.frombuffer(t2, dtype=np.uint8)
+        heads = []
+        for ix, arr in ((i1, a1), (i2, a2)):
+            off, ln = ix.header_off[:ix.n], ix.header_len[:ix.n]
+            offsets = np.zeros(ix.n + 1, dtype=np.int64)
+            np.cumsum(ln, out=offsets[1:])
+            src = np.repeat(off - offsets[:-1], ln) + np.arange(offsets[-1], dtype=np.int64)
+            heads.append(A.SeqBatch(arr[src], offsets))
+        j = NameJoinHost(case["sam_names"], case["sam_flags"], case["sam_seq_len"], heads[0], heads[1], i1.seq_len[:i1.n], i2.seq_len[:i2.n],
+                         r1_first=5, r1_stop=50, r2_first=0, r2_stop=50)
+        out[name] = (i1, i2, join_names(j))
+    assert_same(out["gpu"][2], out["cpu"][2])
+    i1, i2, res = out["gpu"]
+    s, f, _ = res.emitted()
+    first = (case["sam_flags"][s] & 0x40) != 0
+    # raw bases / qualities of the merged records (storeFastqInfoInRecord): FASTQ one rows for read ones, FASTQ two rows otherwise
+    for text, ix, sel, mate in ((t1, i1, first, 0), (t2, i2, ~first, 1)):
+        rows = f[sel]
+        seqs = ctx.gather_rows(text, ix.seq_off[rows], ix.seq_len[rows])
+        quals = ctx.gather_rows(text, ix.qual_off[rows], ix.qual_len[rows])
+        assert (seqs.data.reshape(-1, 60) == case["bases"][mate][rows]).all()
+        assert (quals.data.reshape(-1, 60) == case["quals"][mate][rows]).all()
+        assert (np.diff(seqs.offsets) == 60).all()
+    # the read index a record is renamed to is the FASTQ ordinal of its own name
+    ids = case["ids"]
+    assert all(case["sam_names"][int(r)] == ids[int(k)] for r, k in zip(s[:2000], f[:2000]))
+    from bioinformatics_b200._lib import HsqError
+    with pytest.raises(HsqError) as e:
+        ctx.gather_rows(t1, [len(t1) - 2], [5])
+    assert e.value.status == A.HSQ_ERR_OUT_OF_RANGE
