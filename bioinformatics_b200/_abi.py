@@ -114,6 +114,14 @@ class FastqIndex(C.Structure):
                 ("qual_off", i64p), ("qual_len", i32p)]
 
 
+class SamIndex(C.Structure):
+    _fields_ = [("cap", C.c_int64), ("n", C.c_int64), ("n_header_lines", C.c_int64), ("off", i64p), ("val", i32p)]
+
+
+SAM_FIELDS = ("qname", "rname", "cigar", "seq", "qual", "tags", "xa")
+SAM_VALUES = ("flag", "pos", "mapq", "pnext", "tlen", "ref_len")
+
+
 class NameJoin(C.Structure):
     _fields_ = [("sam_names", Seqs), ("sam_flags", i32p), ("sam_seq_len", i32p), ("sam_qual_len", i32p), ("fq1_headers", Seqs),
                 ("fq2_headers", Seqs), ("fq1_seq_len", i32p), ("fq2_seq_len", i32p), ("by_index", C.c_int32), ("trimming_skipped", C.c_int32),

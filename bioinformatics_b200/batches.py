@@ -395,6 +395,30 @@ class FastqIndexResult:
         return {f: getattr(self, f)[:self.n] for f in self.FIELDS}
 
 
+class SamIndexResult:
+    """hsq_sam_index with host planes; `<field>_off`, `<field>_len` and the numeric columns as attributes after take()."""
+
+    def __init__(self, cap):
+        self.cap, self.n, self.n_header_lines = int(cap), 0, 0
+        self.off = np.zeros((len(A.SAM_FIELDS), self.cap), dtype=np.int64)
+        self.val = np.zeros((len(A.SAM_FIELDS) + len(A.SAM_VALUES), self.cap), dtype=np.int32)
+
+    def c(self):
+        return A.SamIndex(self.cap, 0, 0, A.ptr(self.off, A.i64p), A.ptr(self.val, A.i32p))
+
+    def take(self, oc):
+        self.n, self.n_header_lines = int(oc.n), int(oc.n_header_lines)
+        for f, name in enumerate(A.SAM_FIELDS):
+            setattr(self, name + "_off", self.off[f, :self.n])
+            setattr(self, name + "_len", self.val[f, :self.n])
+        for v, name in enumerate(A.SAM_VALUES):
+            setattr(self, name, self.val[len(A.SAM_FIELDS) + v, :self.n])
+        return self
+
+    def columns(self):
+        return [n + "_off" for n in A.SAM_FIELDS] + [n + "_len" for n in A.SAM_FIELDS] + list(A.SAM_VALUES)
+
+
 class NameJoinHost:
     """hsq_name_join: what FastqAndBamFileMerger reads off the SAM records and the two FASTQ files
     (HSQ/process/FastqAndBamFileMerger.java:107-158,213-345)."""

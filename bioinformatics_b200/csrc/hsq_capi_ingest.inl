@@ -92,6 +92,128 @@ __global__ void fastq_record_kernel(const uint8_t* __restrict__ text, const int6
 }
 
 // ---------------------------------------------------------------------------------------------------------------------------
+// SAM text: header lines are the leading '@' lines; one warp per alignment line finds the tabs with ballots
+__global__ void sam_first_line_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ line_start, int64_t n_lines,
+                                      unsigned long long* first_alignment_line) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n_lines; i += stride) {
+        const int64_t s = line_start[i];
+        if (!(s < line_start[i + 1] - 1 && text[s] == '@')) atomicMin(first_alignment_line, (unsigned long long)i);
+    }
+}
+
+__device__ inline bool parse_i32_field(const uint8_t* __restrict__ p, int len, int32_t* out) {  // Integer.parseInt
+    int i = 0;
+    bool neg = false;
+    if (len > 0 && (p[0] == '-' || p[0] == '+')) { neg = p[0] == '-'; i = 1; }
+    if (i >= len) return false;
+    int64_t v = 0;
+    for (; i < len; i++) {
+        if (p[i] < '0' || p[i] > '9') return false;
+        v = v * 10 + (p[i] - '0');
+        if (v > (int64_t)INT_MAX + 1) return false;
+    }
+    if (neg) v = -v;
+    if (v > INT_MAX || v < INT_MIN) return false;
+    *out = (int32_t)v;
+    return true;
+}
+
+__device__ inline bool cigar_reference_length(const uint8_t* __restrict__ p, int len, int32_t* out) {  // Cigar.getReferenceLength
+    if (len == 1 && p[0] == '*') { *out = 0; return true; }
+    if (len == 0) return false;
+    int64_t rl = 0, count = 0;
+    bool digits = false;
+    for (int k = 0; k < len; k++) {
+        const uint8_t c = p[k];
+        if (c >= '0' && c <= '9') {
+            count = count * 10 + (c - '0');
+            digits = true;
+            if (count > INT_MAX) return false;
+            continue;
+        }
+        if (!digits) return false;
+        if (c == 'M' || c == 'D' || c == 'N' || c == '=' || c == 'X') rl += count;
+        else if (!(c == 'I' || c == 'S' || c == 'H' || c == 'P')) return false;
+        count = 0;
+        digits = false;
+    }
+    if (digits || rl > INT_MAX) return false;
+    *out = (int32_t)rl;
+    return true;
+}
+
+__global__ void sam_line_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ line_start, int64_t first_line, int64_t n_rec,
+                                int64_t* __restrict__ off, int32_t* __restrict__ val, int* status, unsigned long long* first_bad) {
+    const int lane = threadIdx.x & 31;
+    int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; r < n_rec; r += stride) {
+        const int64_t s = line_start[first_line + r];
+        int64_t e = line_start[first_line + r + 1] - 1;
+        if (e > s && text[e - 1] == '\r') e--;
+        int64_t tab[11];
+        int ntab = 0, total_tabs = 0;
+        int64_t xa_s = -1, xa_e = -1;
+        for (int64_t base = s; base < e; base += 32) {
+            const int64_t pos = base + lane;
+            const uint8_t c = pos < e ? text[pos] : (uint8_t)0;
+            const unsigned mask = __ballot_sync(0xffffffffu, c == '\t');
+            const int ordinal = total_tabs + __popc(mask & ((1u << lane) - 1u));  // tabs before this byte
+            const bool is_xa = c == '\t' && ordinal >= 10 && pos + 6 <= e && text[pos + 1] == 'X' && text[pos + 2] == 'A' && text[pos + 3] == ':' &&
+                               text[pos + 4] == 'Z' && text[pos + 5] == ':';
+            const unsigned xmask = __ballot_sync(0xffffffffu, is_xa);
+            if (xa_s < 0 && xmask) xa_s = base + (__ffs(xmask) - 1) + 6;
+            if (xa_s >= 0 && xa_e < 0) {
+                unsigned m2 = mask;
+                if (xa_s > base) m2 = xa_s - base >= 32 ? 0u : (mask & ~((1u << (int)(xa_s - base)) - 1u));
+                if (m2) xa_e = base + (__ffs(m2) - 1);
+            }
+            unsigned m = mask;
+            while (m && ntab < 11) {
+                tab[ntab++] = base + (__ffs(m) - 1);
+                m &= m - 1;
+            }
+            total_tabs += __popc(mask);
+        }
+        bool bad = e == s || text[s] == '@' || ntab < 10;
+        int64_t f_off[HSQ_SAM_N_FIELDS] = {0, 0, 0, 0, 0, 0, 0};
+        int32_t f_len[HSQ_SAM_N_FIELDS] = {0, 0, 0, 0, 0, 0, 0};
+        int32_t num = 0;
+        if (!bad) {
+            auto fs = [&](int k) { return k == 0 ? s : tab[k - 1] + 1; };
+            auto fe = [&](int k) { return k < ntab ? tab[k] : e; };
+            const int col[5] = {0, 2, 5, 9, 10};  // QNAME, RNAME, CIGAR, SEQ, QUAL
+            for (int f = 0; f < 5; f++) { f_off[f] = fs(col[f]); f_len[f] = (int32_t)(fe(col[f]) - fs(col[f])); }
+            f_off[HSQ_SAM_TAGS] = ntab >= 11 ? tab[10] + 1 : e;
+            f_len[HSQ_SAM_TAGS] = (int32_t)(e - f_off[HSQ_SAM_TAGS]);
+            if (xa_s >= 0) {
+                if (xa_e < 0) xa_e = e;
+                if (xa_e > xa_s) { f_off[HSQ_SAM_XA] = xa_s; f_len[HSQ_SAM_XA] = (int32_t)(xa_e - xa_s); }
+            }
+            const int ncol[5] = {1, 3, 4, 7, 8};  // FLAG, POS, MAPQ, PNEXT, TLEN
+            bool ok = true;
+            if (lane < 5) ok = parse_i32_field(text + fs(ncol[lane]), (int)(fe(ncol[lane]) - fs(ncol[lane])), &num);
+            else if (lane == 5) ok = cigar_reference_length(text + f_off[HSQ_SAM_CIGAR], f_len[HSQ_SAM_CIGAR], &num);
+            bad = __any_sync(0xffffffffu, !ok);
+        }
+        if (bad) {
+            if (lane == 0) {
+                atomicMin(status, HSQ_ERR_MALFORMED);
+                atomicMin(first_bad, (unsigned long long)r);
+            }
+            continue;
+        }
+        if (lane < HSQ_SAM_N_FIELDS) {
+            off[(int64_t)lane * n_rec + r] = f_off[lane];
+            val[(int64_t)lane * n_rec + r] = f_len[lane];
+        }
+        if (lane < 6) val[(int64_t)(HSQ_SAM_N_FIELDS + lane) * n_rec + r] = num;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
 // ragged row gather
 __global__ void rows_len_kernel(const int64_t* __restrict__ off, const int32_t* __restrict__ len, int64_t n, int64_t n_bytes,
                                 int64_t* __restrict__ len64, int* status) {
@@ -446,16 +568,8 @@ int upload_strings(hsq_ctx* ctx, const hsq_seqs* s, DevBuf* data, DevBuf* off, c
     return HSQ_OK;
 }
 
-}  // namespace
-
-extern "C" int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_fastq_index* out) {
-    if (!ctx || !out || n_bytes < 0 || (n_bytes > 0 && !text)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_fastq: null argument");
-    out->n = 0;
-    if (n_bytes == 0) return HSQ_OK;
-    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
-    CallTimer timer(ctx);
-    int rc = reset_status(ctx);
-    if (rc) return rc;
+// text -> device copy + line starts (line i = [lines[i], lines[i+1] - 1), '\n' excluded; a last line without terminator counts)
+int build_line_index(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, uint8_t** d_text_out, int64_t** d_lines_out, int64_t* n_lines_out) {
     const int64_t n_tiles = (n_bytes + NL_TILE - 1) / NL_TILE;
     HSQ_CUDA(ctx, ctx->r1.ascii.ensure((size_t)n_bytes + 32));
     HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)(n_tiles + 1) * 8 + 16));
@@ -463,7 +577,7 @@ extern "C" int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_
     int64_t* d_tiles = ctx->sort_c.as<int64_t>();
     HSQ_CUDA(ctx, cudaMemcpyAsync(d_text, text, (size_t)n_bytes, cudaMemcpyHostToDevice, ctx->stream));
     HSQ_CUDA(ctx, cudaMemsetAsync(d_tiles + n_tiles, 0, 8, ctx->stream));
-    HSQ_CUDA(ctx, cudaMemsetAsync(ctx->cells.p, 0xff, 8, ctx->stream));  // first malformed record
+    HSQ_CUDA(ctx, cudaMemsetAsync(ctx->cells.p, 0xff, 16, ctx->stream));  // first malformed record | first alignment line
     nl_count_kernel<<<(unsigned)n_tiles, NL_BLOCK, 0, ctx->stream>>>(d_text, n_bytes, d_tiles, d_status(ctx));
     scan_sums_kernel<<<1, SCAN_BLOCK, 0, ctx->stream>>>(d_tiles, n_tiles + 1);  // in place: exclusive; entry n_tiles = total
     ctx->launches += 2;
@@ -481,6 +595,26 @@ extern "C" int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_
         set_i64_kernel<<<1, 1, 0, ctx->stream>>>(d_lines + n_lines, n_bytes + 1);
         ctx->launches++;
     }
+    *d_text_out = d_text;
+    *d_lines_out = d_lines;
+    *n_lines_out = n_lines;
+    return HSQ_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_fastq_index* out) {
+    if (!ctx || !out || n_bytes < 0 || (n_bytes > 0 && !text)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_fastq: null argument");
+    out->n = 0;
+    if (n_bytes == 0) return HSQ_OK;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    uint8_t* d_text;
+    int64_t* d_lines;
+    int64_t n_lines;
+    if ((rc = build_line_index(ctx, text, n_bytes, &d_text, &d_lines, &n_lines))) return rc;
     const int64_t n_rec = n_lines / 4;
     out->n = n_rec;
     int st[4];
@@ -514,6 +648,54 @@ extern "C" int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_
                                                                {out->seq_len, d_o32 + nr, nr * 4}, {out->qual_len, d_o32 + 2 * nr, nr * 4}};
     for (auto& c : down)
         if (c.bytes) HSQ_CUDA(ctx, cudaMemcpyAsync(c.h, c.d, c.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return timer.finish();
+}
+
+extern "C" int32_t hsq_index_sam(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_sam_index* out) {
+    if (!ctx || !out || n_bytes < 0 || (n_bytes > 0 && !text)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_sam: null argument");
+    out->n = 0;
+    out->n_header_lines = 0;
+    if (n_bytes == 0) return HSQ_OK;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    uint8_t* d_text;
+    int64_t* d_lines;
+    int64_t n_lines;
+    if ((rc = build_line_index(ctx, text, n_bytes, &d_text, &d_lines, &n_lines))) return rc;
+    unsigned long long* d_first = ctx->cells.as<unsigned long long>() + 1;
+    sam_first_line_kernel<<<grid_for(ctx, n_lines, 256, 16), 256, 0, ctx->stream>>>(d_text, d_lines, n_lines, d_first);
+    ctx->launches++;
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int64_t n_header = ctx->h_cells[1] == ~0ull ? n_lines : (int64_t)ctx->h_cells[1];
+    const int64_t n_rec = n_lines - n_header;
+    out->n = n_rec;
+    out->n_header_lines = n_header;
+    if (n_rec > out->cap) return fail(ctx, HSQ_ERR_OVERFLOW, "hsq_index_sam: more alignment lines than out->cap");
+    if (n_rec > 0 && (!out->off || !out->val)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_sam: null output plane");
+    const size_t nr = (size_t)n_rec;
+    HSQ_CUDA(ctx, ctx->sort_b.ensure(nr * 8 * HSQ_SAM_N_FIELDS + 64));
+    HSQ_CUDA(ctx, ctx->out_i32.ensure(nr * 4 * HSQ_SAM_N_VALUES + 64));
+    int64_t* d_off = ctx->sort_b.as<int64_t>();
+    int32_t* d_val = ctx->out_i32.as<int32_t>();
+    if (n_rec > 0) {
+        sam_line_kernel<<<grid_for(ctx, n_rec * 32, 256, 16), 256, 0, ctx->stream>>>(d_text, d_lines, n_header, n_rec, d_off, d_val, d_status(ctx),
+                                                                                     ctx->cells.as<unsigned long long>());
+        ctx->launches++;
+    }
+    HSQ_CUDA(ctx, cudaGetLastError());
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    int st[1];
+    if ((rc = read_status(ctx, st, 1))) return rc;
+    if (st[0] == HSQ_ERR_UNSUPPORTED) return fail(ctx, st[0], "hsq_index_sam: a carriage return that is not followed by a line feed");
+    if (st[0]) return fail(ctx, st[0], "hsq_index_sam: alignment line " + std::to_string(ctx->h_cells[0]) +
+                                           " is empty, a header line, has fewer than 11 columns, a non-numeric FLAG/POS/MAPQ/PNEXT/TLEN or a bad CIGAR");
+    for (int f = 0; f < HSQ_SAM_N_FIELDS && nr; f++)
+        HSQ_CUDA(ctx, cudaMemcpyAsync(out->off + (int64_t)f * out->cap, d_off + (size_t)f * nr, nr * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    for (int v = 0; v < HSQ_SAM_N_VALUES && nr; v++)
+        HSQ_CUDA(ctx, cudaMemcpyAsync(out->val + (int64_t)v * out->cap, d_val + (size_t)v * nr, nr * 4, cudaMemcpyDeviceToHost, ctx->stream));
     return timer.finish();
 }
 

@@ -90,3 +90,31 @@ def find_flow(be, seqs, reads, quals, leading_quality=0, trailing_quality=0, all
     accepted = (aln.find_counts <= limits[None, :]).all(axis=1) if len(item_read) else np.zeros(0, dtype=bool)
     n_matches = np.bincount(item_read[accepted], minlength=reads.n)
     return {"candidates": cand, "item_read": item_read, "item_seq": item_seq, "alignments": aln, "accepted": accepted, "n_matches": n_matches}
+
+
+def ingest_flow(be, fq1_text, fq2_text, sam_text, trim=(0, 0, 0, 0), three_prime=False, trimming_skipped=False):
+    """FASTQ texts + SAM text -> the merged records createBamFileWithDataFromRawFastqFiles writes
+    (HSQ/process/FastqAndBamFileMerger.java:107-158, first configuration …Identification.java:150-160), as index glue over
+    hsq_index_fastq, hsq_index_sam, hsq_gather_rows and hsq_join_names.  `be` needs index_fastq, index_sam, gather_rows and
+    join_names (a Context, or the tests' adapter of the CPU oracle).  Returns a dict: per returned record the SAM line it came
+    from, its new read name (= FASTQ ordinal, FastqSorter.java:298-302), the ML tag (mapped read length,
+    FastqAndBamFileMerger.java:390-391), first-of-pair, the raw bases / qualities it now carries, and the SAM columns the
+    read->probe assignment reads next."""
+    from .batches import NameJoinHost
+    i1, i2, sam = be.index_fastq(fq1_text), be.index_fastq(fq2_text), be.index_sam(sam_text)
+    heads = [be.gather_rows(t, ix.header_off[:ix.n], ix.header_len[:ix.n]) for t, ix in ((fq1_text, i1), (fq2_text, i2))]
+    names = be.gather_rows(sam_text, sam.qname_off, sam.qname_len)
+    f1, s1, f2, s2 = trim
+    j = NameJoinHost(names, sam.flag, sam.seq_len, heads[0], heads[1], i1.seq_len[:i1.n], i2.seq_len[:i2.n], sam_qual_len=sam.qual_len,
+                     trimming_skipped=trimming_skipped, three_prime=three_prime, r1_first=f1, r1_stop=s1, r2_first=f2, r2_stop=s2)
+    res = be.join_names(j)
+    rec, fq, _ = res.emitted()
+    first = (sam.flag[rec] & 0x40) != 0
+    out = dict(sam_line=rec, read_index=fq, first_of_pair=first, mapped_read_length=sam.seq_len[rec], status=res.status,
+               total_matching_pairs=res.total_matching_pairs, flag=sam.flag[rec], pos=sam.pos[rec], ref_len=sam.ref_len[rec],
+               rname_off=sam.rname_off[rec], rname_len=sam.rname_len[rec], xa_off=sam.xa_off[rec], xa_len=sam.xa_len[rec])
+    for key, text, ix, sel in (("one", fq1_text, i1, first), ("two", fq2_text, i2, ~first)):
+        rows = fq[sel]
+        out["seq_" + key] = be.gather_rows(text, ix.seq_off[rows], ix.seq_len[rows])
+        out["qual_" + key] = be.gather_rows(text, ix.qual_off[rows], ix.qual_len[rows])
+    return out

@@ -298,3 +298,42 @@ def make_ingest_case(n_pairs, read_len=150, seed=7, mapped_frac=0.9, lone_frac=0
     return dict(n_pairs=n_pairs, ids=ids, fq1_headers=h1, fq2_headers=h2, fq1_text=fq1_text, fq2_text=fq2_text, fq_seq_len=lens,
                 bases=bases, quals=quals, sam_names=[names[i] for i in order], sam_flags=np.asarray(flags, dtype=np.int32)[order],
                 sam_seq_len=np.asarray(slen, dtype=np.int32)[order], trim=trim, three_prime=three_prime)
+
+
+def sam_text_of(case, seed=3, n_contigs=22, xa_rate=0.05, crlf=False, final_newline=True):
+    """SAM text for the records of make_ingest_case: header lines, then one alignment line per record with the trimmed read, a CIGAR
+    with an occasional insertion / deletion / soft clip, mate columns and NM / MD / XA tags (as `bwa mem` writes them)."""
+    rng = np.random.default_rng(seed)
+    eol = "\r\n" if crlf else "\n"
+    f1, _, f2, _ = case["trim"]
+    row_of = {s: k for k, s in enumerate(case["ids"])}
+    lines = ["@HD\tVN:1.5\tSO:unsorted"] + ["@SQ\tSN:chr%d\tLN:%d" % (c + 1, 50_000_000) for c in range(n_contigs)] + ["@PG\tID:bwa\tPN:bwa"]
+    n = len(case["sam_names"])
+    kind = rng.integers(0, 8, size=n)
+    pos = rng.integers(1, 40_000_000, size=n)
+    contig = rng.integers(1, n_contigs + 1, size=n)
+    for k in range(n):
+        name, fl, ln = case["sam_names"][k], int(case["sam_flags"][k]), int(case["sam_seq_len"][k])
+        row = row_of.get(name)
+        mate = 0 if fl & 0x40 else 1
+        if row is None:
+            seq, qual = "A" * ln, "I" * ln
+        else:
+            first = f1 if mate == 0 else f2
+            seq = case["bases"][mate][row][first:first + ln].tobytes().decode()
+            qual = case["quals"][mate][row][first:first + ln].tobytes().decode()
+        if kind[k] == 0 and ln > 20:
+            cigar = "%dM1I%dM" % (10, ln - 11)
+        elif kind[k] == 1 and ln > 20:
+            cigar = "%dM2D%dM" % (12, ln - 12)
+        elif kind[k] == 2 and ln > 20:
+            cigar = "5S%dM" % (ln - 5)
+        else:
+            cigar = "%dM" % ln
+        tags = ["NM:i:%d" % (kind[k] % 3), "MD:Z:%d" % ln, "AS:i:%d" % ln]
+        if rng.random() < xa_rate:
+            tags.insert(int(rng.integers(0, 4)), "XA:Z:chr%d,%s%d,%dM,1;" % (int(rng.integers(1, n_contigs + 1)), "+-"[k % 2], int(pos[k]) + 7, ln))
+        lines.append("\t".join([name, str(fl), "chr%d" % contig[k], str(int(pos[k])), str(int(rng.integers(0, 61))), cigar, "=",
+                                str(int(pos[k]) + 100), str(int(rng.integers(-400, 400))), seq, qual] + tags))
+    t = eol.join(lines) + (eol if final_newline else "")
+    return t.encode()

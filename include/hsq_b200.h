@@ -405,6 +405,24 @@ typedef struct hsq_fastq_index {
 } hsq_fastq_index;
 int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_fastq_index* out);
 
+/* Field index of SAM text for the columns the dedup path reads off a SAMRecord (QNAME, FLAG, SEQ and QUAL lengths:
+ * FastqAndBamFileMerger.java:222-330; RNAME, POS, strand, alignment end = POS + reference length of the CIGAR - 1 and the XA
+ * tag: …Identification.java:439-576).  Grammar as htsjdk's SAMLineParser: '@' header lines first (counted, skipped), then
+ * lines of at least 11 tab separated columns; FLAG, POS, MAPQ, PNEXT, TLEN are integers; CIGAR is '*' or <count><op> runs
+ * (HSQ_ERR_MALFORMED otherwise).  Planes: off[f * cap + k], val[f * cap + k] = offset / length of string field f of
+ * alignment line k (XA: the value of the first XA:Z: tag, length 0 when absent); val[v * cap + k] for the numeric columns. */
+enum { HSQ_SAM_QNAME = 0, HSQ_SAM_RNAME = 1, HSQ_SAM_CIGAR = 2, HSQ_SAM_SEQ = 3, HSQ_SAM_QUAL = 4, HSQ_SAM_TAGS = 5, HSQ_SAM_XA = 6,
+       HSQ_SAM_N_FIELDS = 7 };
+enum { HSQ_SAM_FLAG = 7, HSQ_SAM_POS = 8, HSQ_SAM_MAPQ = 9, HSQ_SAM_PNEXT = 10, HSQ_SAM_TLEN = 11, HSQ_SAM_REF_LEN = 12, HSQ_SAM_N_VALUES = 13 };
+typedef struct hsq_sam_index {
+    int64_t cap;            /* in: alignment lines the planes can hold */
+    int64_t n;              /* out: alignment lines */
+    int64_t n_header_lines; /* out */
+    int64_t* off;           /* [HSQ_SAM_N_FIELDS][cap] */
+    int32_t* val;           /* [HSQ_SAM_N_VALUES][cap] */
+} hsq_sam_index;
+int32_t hsq_index_sam(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_sam_index* out);
+
 /* FastqAndBamFileMerger.createBamFileWithDataFromRawFastqFiles (HSQ/process/FastqAndBamFileMerger.java:107-158) without the
  * file codecs: both sorts and the merge loop of MergedSamIterator (:213-345) for the two configurations the dedup command
  * uses.  by_index = 0 (…Identification.java:150-160): FASTQ records sorted by header + " _ " + ordinal

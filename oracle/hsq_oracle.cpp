@@ -370,6 +370,24 @@ int32_t hsqo_index_fastq(const uint8_t* text, int64_t n_bytes, hsq_fastq_index* 
     } catch (const FastqMalformed& e) { g_err = e.what(); return HSQ_ERR_MALFORMED; }
 }
 
+// f2: SAM text field index (hsq_oracle_ingest.hpp)
+int32_t hsqo_index_sam(const uint8_t* text, int64_t n_bytes, hsq_sam_index* o) {
+    try {
+        SamIndex ix = index_sam(text, n_bytes);
+        o->n = (int64_t)ix.flag.size();
+        o->n_header_lines = ix.n_header_lines;
+        if (o->n > o->cap) { g_err = "more alignment lines than cap"; return HSQ_ERR_OVERFLOW; }
+        const std::vector<int64_t>* offs[HSQ_SAM_N_FIELDS] = {&ix.qname_off, &ix.rname_off, &ix.cigar_off, &ix.seq_off, &ix.qual_off, &ix.tags_off, &ix.xa_off};
+        const std::vector<int32_t>* vals[HSQ_SAM_N_VALUES] = {&ix.qname_len, &ix.rname_len, &ix.cigar_len, &ix.seq_len, &ix.qual_len, &ix.tags_len, &ix.xa_len,
+                                                              &ix.flag, &ix.pos, &ix.mapq, &ix.pnext, &ix.tlen, &ix.ref_len};
+        for (int f = 0; f < HSQ_SAM_N_FIELDS; f++)
+            for (int64_t k = 0; k < o->n; k++) o->off[(int64_t)f * o->cap + k] = (*offs[f])[(size_t)k];
+        for (int v = 0; v < HSQ_SAM_N_VALUES; v++)
+            for (int64_t k = 0; k < o->n; k++) o->val[(int64_t)v * o->cap + k] = (*vals[v])[(size_t)k];
+        return HSQ_OK;
+    } catch (const FastqMalformed& e) { g_err = e.what(); return HSQ_ERR_MALFORMED; }
+}
+
 // f2: the two sorts and the merge loop of FastqAndBamFileMerger (hsq_oracle_ingest.hpp)
 int32_t hsqo_join_names(const hsq_name_join* in, hsq_name_join_out* o) {
     JoinInput ji;

@@ -235,4 +235,92 @@ inline FastqIndex index_fastq(const uint8_t* text, int64_t n) {
     return ix;
 }
 
+// ---- SAM text -> field index ------------------------------------------------------------------------------------------------
+// The columns the dedup path reads off a SAMRecord: QNAME / FLAG / SEQ / QUAL lengths (FastqAndBamFileMerger.java:222-330),
+// RNAME, POS, strand and alignment end = POS + reference length of the CIGAR - 1, and the XA tag
+// (...Identification.java:439-576).  Line grammar as htsjdk's SAMLineParser (2.9.0, absent): '@' header lines first, then lines of
+// at least 11 tab separated columns; FLAG, POS, MAPQ, PNEXT, TLEN decimal integers; CIGAR '*' or <count><op> runs.
+struct SamIndex {
+    int64_t n_header_lines = 0;
+    std::vector<int64_t> qname_off, rname_off, cigar_off, seq_off, qual_off, tags_off, xa_off;
+    std::vector<int32_t> qname_len, rname_len, cigar_len, seq_len, qual_len, tags_len, xa_len, flag, pos, mapq, pnext, tlen, ref_len;
+};
+
+inline SamIndex index_sam(const uint8_t* text, int64_t n) {
+    SamIndex ix;
+    int64_t p = 0;
+    bool in_header = true;
+    auto parse_int = [&](int64_t off, int32_t len) -> int32_t {
+        try {
+            return java_parse_int(std::string((const char*)text + off, (size_t)len));
+        } catch (const JoinBadNumber&) { throw FastqMalformed("a numeric SAM column is not an integer"); }
+    };
+    while (p < n) {
+        int64_t e = p;
+        while (e < n && text[e] != '\n') e++;
+        int64_t stop = e;
+        if (stop > p && text[stop - 1] == '\r') stop--;
+        const int64_t start = p;
+        p = e < n ? e + 1 : n;
+        if (stop == start) throw FastqMalformed("empty line");
+        if (text[start] == '@') {
+            if (!in_header) throw FastqMalformed("header line after the first alignment line");
+            ix.n_header_lines++;
+            continue;
+        }
+        in_header = false;
+        int64_t off[12];
+        int32_t len[12];
+        int nf = 0;
+        int64_t fs = start;
+        for (int64_t k = start; k <= stop && nf < 11; k++)
+            if (k == stop || text[k] == '\t') { off[nf] = fs; len[nf] = (int32_t)(k - fs); nf++; fs = k + 1; }
+        if (nf < 11) throw FastqMalformed("fewer than 11 columns");
+        off[11] = std::min(fs, stop);
+        len[11] = (int32_t)(stop - off[11]);
+        ix.qname_off.push_back(off[0]); ix.qname_len.push_back(len[0]);
+        ix.flag.push_back(parse_int(off[1], len[1]));
+        ix.rname_off.push_back(off[2]); ix.rname_len.push_back(len[2]);
+        ix.pos.push_back(parse_int(off[3], len[3]));
+        ix.mapq.push_back(parse_int(off[4], len[4]));
+        ix.cigar_off.push_back(off[5]); ix.cigar_len.push_back(len[5]);
+        ix.pnext.push_back(parse_int(off[7], len[7]));
+        ix.tlen.push_back(parse_int(off[8], len[8]));
+        ix.seq_off.push_back(off[9]); ix.seq_len.push_back(len[9]);
+        ix.qual_off.push_back(off[10]); ix.qual_len.push_back(len[10]);
+        ix.tags_off.push_back(off[11]); ix.tags_len.push_back(len[11]);
+        int64_t rl = 0;  // Cigar.getReferenceLength: M, D, N, =, X consume the reference
+        if (!(len[5] == 1 && text[off[5]] == '*')) {
+            int64_t count = 0;
+            bool digits = false;
+            for (int32_t k = 0; k < len[5]; k++) {
+                const uint8_t c = text[off[5] + k];
+                if (c >= '0' && c <= '9') { count = count * 10 + (c - '0'); digits = true; if (count > INT32_MAX) throw FastqMalformed("CIGAR count"); continue; }
+                if (!digits) throw FastqMalformed("CIGAR operator without a count");
+                if (c == 'M' || c == 'D' || c == 'N' || c == '=' || c == 'X') rl += count;
+                else if (!(c == 'I' || c == 'S' || c == 'H' || c == 'P')) throw FastqMalformed("unknown CIGAR operator");
+                count = 0;
+                digits = false;
+            }
+            if (digits || len[5] == 0) throw FastqMalformed("CIGAR ends inside a count");
+            if (rl > INT32_MAX) throw FastqMalformed("CIGAR reference length");
+        }
+        ix.ref_len.push_back((int32_t)rl);
+        int64_t xo = off[11];
+        int32_t xl = 0;  // first XA:Z: tag
+        for (int64_t k = off[11]; k < stop;) {
+            int64_t t = k;
+            while (t < stop && text[t] != '\t') t++;
+            if (t - k >= 5 && text[k] == 'X' && text[k + 1] == 'A' && text[k + 2] == ':' && text[k + 3] == 'Z' && text[k + 4] == ':') {
+                xo = k + 5;
+                xl = (int32_t)(t - xo);
+                break;
+            }
+            k = t + 1;
+        }
+        ix.xa_off.push_back(xl ? xo : 0); ix.xa_len.push_back(xl);
+    }
+    return ix;
+}
+
 }  // namespace hsqo

@@ -179,6 +179,74 @@ def split_statement(text):
                 seq_len=[r[1][1] for r in recs], qual_off=[r[3][0] for r in recs], qual_len=[r[3][1] for r in recs])
 
 
+def sam_split_statement(text):
+    """SAM columns by bytes.split: the second statement of the field index for well-formed text."""
+    cols = defaultdict(list)
+    pos, header = 0, 0
+    ref_ops = set("MDN=X")
+    for raw in text.split(b"\n"):
+        line = raw[:-1] if raw.endswith(b"\r") else raw
+        start = pos
+        pos += len(raw) + 1
+        if not line:
+            continue
+        if line.startswith(b"@"):
+            header += 1
+            continue
+        f = line.split(b"\t")
+        offs = [start]
+        for x in f[:-1]:
+            offs.append(offs[-1] + len(x) + 1)
+        for name, c in (("qname", 0), ("rname", 2), ("cigar", 5), ("seq", 9), ("qual", 10)):
+            cols[name + "_off"].append(offs[c])
+            cols[name + "_len"].append(len(f[c]))
+        cols["tags_off"].append(offs[11] if len(f) > 11 else start + len(line))
+        cols["tags_len"].append(start + len(line) - cols["tags_off"][-1])
+        xa = [(offs[i] + 5, len(f[i]) - 5) for i in range(11, len(f)) if f[i].startswith(b"XA:Z:")]
+        xo, xl = xa[0] if xa and xa[0][1] > 0 else (0, 0)
+        cols["xa_off"].append(xo)
+        cols["xa_len"].append(xl)
+        for name, c in (("flag", 1), ("pos", 3), ("mapq", 4), ("pnext", 7), ("tlen", 8)):
+            cols[name].append(int(f[c]))
+        cig = f[5].decode()
+        cols["ref_len"].append(0 if cig == "*" else sum(int(n) for n, op in re.findall(r"(\d+)([A-Z=])", cig) if op in ref_ops))
+    return header, cols
+
+
+SAM_SMALL = (b"@HD\tVN:1.0\n@SQ\tSN:chr1\tLN:100\nr1\t99\tchr1\t10\t60\t5M1I3M2D4M\t=\t50\t60\tACGTACGTACGTA\tIIIIIIIIIIIII\tNM:i:1\tXA:Z:chr2,+5,13M,1;\tMD:Z:3\n"
+             b"r2\t4\t*\t0\t0\t*\t*\t0\t0\t*\t*\nr3\t-1\tc\t+7\t0\t3=1X2N\t=\t1\t-9\tAC\t##\tXA:Z:\tXA:Z:q\nr4\t0\tc\t7\t0\t2H3M\t=\t1\t0\tAC\t##\t")
+SAM_BAD = [b"r1\t99\tchr1\t10\t60\t5M\t=\t50\t60\tACGTA\n",                        # ten columns
+           b"r1\t99\tchr1\t1x\t60\t5M\t=\t50\t60\tACGTA\tIIIII\n",                  # POS is not a number
+           b"r1\t99\tchr1\t10\t60\t5M3\t=\t50\t60\tACGTA\tIIIII\n",                 # CIGAR ends inside a count
+           b"r1\t99\tchr1\t10\t60\t5Q\t=\t50\t60\tACGTA\tIIIII\n",                  # unknown operator
+           b"r1\t99\tchr1\t10\t60\tM\t=\t50\t60\tACGTA\tIIIII\n",                   # operator without count
+           b"r1\t99\tchr1\t10\t60\t5M\t=\t50\t60\tACGTA\tIIIII\n@CO\tlate header\n",  # header line after an alignment line
+           b"@HD\tVN:1.0\n\nr1\t99\tchr1\t10\t60\t5M\t=\t50\t60\tACGTA\tIIIII\n",      # empty line
+           b"r1\t99999999999\tchr1\t10\t60\t5M\t=\t50\t60\tACGTA\tIIIII\n"]          # FLAG outside int
+
+
+def check_sam_index(ix, text):
+    header, cols = sam_split_statement(text)
+    assert ix.n_header_lines == header and ix.n == len(cols["flag"])
+    for c in ix.columns():
+        assert list(getattr(ix, c)) == cols[c], c
+
+
+def test_oracle_sam_index():
+    check_sam_index(O.index_sam(SAM_SMALL), SAM_SMALL)
+    ix = O.index_sam(SAM_SMALL)
+    assert list(ix.ref_len) == [14, 0, 6, 3] and list(ix.flag) == [99, 4, -1, 0] and list(ix.xa_len) == [14, 0, 0, 0] and list(ix.tags_len) == [33, 0, 12, 0]
+    for text in SAM_BAD:
+        with pytest.raises(O.OracleError) as e:
+            O.index_sam(text)
+        assert e.value.status == A.HSQ_ERR_MALFORMED
+    assert O.index_sam(b"").n == 0 and O.index_sam(b"@HD\tVN:1.0\n").n_header_lines == 1
+    case = synth.make_ingest_case(800, read_len=40, seed=4, trim=(3, 30, 0, 30))
+    for kw in ({}, dict(crlf=True), dict(final_newline=False)):
+        text = synth.sam_text_of(case, **kw)
+        check_sam_index(O.index_sam(text), text)
+
+
 # ---------------------------------------------------------------------------------------------------------------- CPU: the oracle
 def test_oracle_hand_traces():
     check_kat(O.join_names(kat_join(KAT_BY_NAME, False)), KAT_BY_NAME)
@@ -345,40 +413,80 @@ def test_gpu_fastq_index_equals_oracle(ctx):
 
 
 @pytest.mark.gpu
-def test_gpu_files_to_merged_records(ctx):
-    """FASTQ texts + SAM columns -> the merged records' read index, raw bases and raw qualities, device path against the oracle's."""
-    case = synth.make_ingest_case(20000, read_len=60, seed=21, trim=(5, 50, 0, 50))
-    t1, t2 = case["fq1_text"], case["fq2_text"]
-    out = {}
-    for name, index_fastq, join_names in (("gpu", ctx.index_fastq, ctx.join_names), ("cpu", O.index_fastq, O.join_names)):
-        i1, i2 = index_fastq(t1), index_fastq(t2)
-        a1, a2 = np.frombuffer(t1, dtype=np.uint8), np.frombuffer(t2, dtype=np.uint8)
-        heads = []
-        for ix, arr in ((i1, a1), (i2, a2)):
-            off, ln = ix.header_off[:ix.n], ix.header_len[:ix.n]
-            offsets = np.zeros(ix.n + 1, dtype=np.int64)
-            np.cumsum(ln, out=offsets[1:])
-            src = np.repeat(off - offsets[:-1], ln) + np.arange(offsets[-1], dtype=np.int64)
-            heads.append(A.SeqBatch(arr[src], offsets))
-        j = NameJoinHost(case["sam_names"], case["sam_flags"], case["sam_seq_len"], heads[0], heads[1], i1.seq_len[:i1.n], i2.seq_len[:i2.n],
-                         r1_first=5, r1_stop=50, r2_first=0, r2_stop=50)
-        out[name] = (i1, i2, join_names(j))
-    assert_same(out["gpu"][2], out["cpu"][2])
-    i1, i2, res = out["gpu"]
-    s, f, _ = res.emitted()
-    first = (case["sam_flags"][s] & 0x40) != 0
-    # raw bases / qualities of the merged records (storeFastqInfoInRecord): FASTQ one rows for read ones, FASTQ two rows otherwise
-    for text, ix, sel, mate in ((t1, i1, first, 0), (t2, i2, ~first, 1)):
-        rows = f[sel]
-        seqs = ctx.gather_rows(text, ix.seq_off[rows], ix.seq_len[rows])
-        quals = ctx.gather_rows(text, ix.qual_off[rows], ix.qual_len[rows])
-        assert (seqs.data.reshape(-1, 60) == case["bases"][mate][rows]).all()
-        assert (quals.data.reshape(-1, 60) == case["quals"][mate][rows]).all()
-        assert (np.diff(seqs.offsets) == 60).all()
-    # the read index a record is renamed to is the FASTQ ordinal of its own name
-    ids = case["ids"]
-    assert all(case["sam_names"][int(r)] == ids[int(k)] for r, k in zip(s[:2000], f[:2000]))
+def test_gpu_sam_index_equals_oracle(ctx):
     from bioinformatics_b200._lib import HsqError
+    check_sam_index(ctx.index_sam(SAM_SMALL), SAM_SMALL)
+    for text in SAM_BAD:
+        with pytest.raises(HsqError) as e:
+            ctx.index_sam(text)
+        assert e.value.status == A.HSQ_ERR_MALFORMED
+    assert ctx.index_sam(b"").n == 0 and ctx.index_sam(b"@HD\tVN:1.0\n").n_header_lines == 1
+    for n, kw in ((800, {}), (800, dict(crlf=True)), (25000, dict(final_newline=False, xa_rate=0.3))):
+        case = synth.make_ingest_case(n, read_len=70, seed=n % 5, trim=(3, 60, 0, 60))
+        text = synth.sam_text_of(case, **kw)
+        got, exp = ctx.index_sam(text), O.index_sam(text)
+        assert got.n == exp.n == len(case["sam_names"]) and got.n_header_lines == exp.n_header_lines == 24
+        for c in got.columns():
+            assert (getattr(got, c) == getattr(exp, c)).all(), c
+    with pytest.raises(HsqError) as e:
+        ctx.index_sam(text, cap=10)
+    assert e.value.status == A.HSQ_ERR_OVERFLOW
+
+
+class OraclePort:
+    """The oracle behind the calls flow.ingest_flow makes (gather_rows: numpy fancy indexing)."""
+    index_fastq = staticmethod(O.index_fastq)
+    index_sam = staticmethod(O.index_sam)
+    join_names = staticmethod(O.join_names)
+
+    @staticmethod
+    def gather_rows(text, off, length):
+        t = np.frombuffer(text, dtype=np.uint8)
+        off, length = np.asarray(off, dtype=np.int64), np.asarray(length, dtype=np.int64)
+        offsets = np.zeros(len(off) + 1, dtype=np.int64)
+        np.cumsum(length, out=offsets[1:])
+        src = np.repeat(off - offsets[:-1], length) + np.arange(offsets[-1], dtype=np.int64)
+        return A.SeqBatch(t[src], offsets)
+
+
+def test_flow_over_oracle_against_generator():
+    """flow.ingest_flow over the oracle: every returned record carries the FASTQ ordinal of its own name and the raw rows."""
+    from bioinformatics_b200 import flow
+    case = synth.make_ingest_case(3000, read_len=60, seed=22, trim=(5, 50, 0, 50), old_style=True)
+    ts = synth.sam_text_of(case, seed=9, crlf=True)
+    got = flow.ingest_flow(OraclePort, case["fq1_text"], case["fq2_text"], ts, trim=case["trim"])
+    ids, first, fq = case["ids"], got["first_of_pair"], got["read_index"]
+    assert len(fq) > 4000 and all(case["sam_names"][int(r)] == ids[int(k)] for r, k in zip(got["sam_line"], fq))
+    assert (got["seq_one"].data.reshape(-1, 60) == case["bases"][0][fq[first]]).all()
+    assert (got["qual_two"].data.reshape(-1, 60) == case["quals"][1][fq[~first]]).all()
+    assert (got["mapped_read_length"] == np.where(first, 55, 60)).all()
+
+
+@pytest.mark.gpu
+def test_gpu_files_to_merged_records(ctx):
+    """FASTQ texts + SAM text -> the merged records' read index, ML tag, raw bases and raw qualities: flow.ingest_flow over the
+    C ABI against the same flow over the oracle, and against what the generator put into the files."""
+    from bioinformatics_b200 import flow
+    from bioinformatics_b200._lib import HsqError
+    case = synth.make_ingest_case(20000, read_len=60, seed=21, trim=(5, 50, 0, 50))
+    t1, t2, ts = case["fq1_text"], case["fq2_text"], synth.sam_text_of(case, seed=8)
+    got = flow.ingest_flow(ctx, t1, t2, ts, trim=case["trim"])
+    exp = flow.ingest_flow(OraclePort, t1, t2, ts, trim=case["trim"])
+    assert set(got) == set(exp) and len(got["sam_line"]) > 30000
+    for k in got:
+        if isinstance(got[k], A.SeqBatch):
+            assert (got[k].data == exp[k].data).all() and (got[k].offsets == exp[k].offsets).all(), k
+        else:
+            assert np.array_equal(got[k], exp[k]), k
+    # against the generator: record -> its own name's FASTQ ordinal, raw (untrimmed) rows of the right file
+    ids, first, fq = case["ids"], got["first_of_pair"], got["read_index"]
+    assert all(case["sam_names"][int(r)] == ids[int(k)] for r, k in zip(got["sam_line"][:3000], fq[:3000]))
+    assert (got["seq_one"].data.reshape(-1, 60) == case["bases"][0][fq[first]]).all()
+    assert (got["qual_two"].data.reshape(-1, 60) == case["quals"][1][fq[~first]]).all()
+    assert (got["mapped_read_length"] == np.where(first, 55, 60)).all()
     with pytest.raises(HsqError) as e:
         ctx.gather_rows(t1, [len(t1) - 2], [5])
     assert e.value.status == A.HSQ_ERR_OUT_OF_RANGE
+    with pytest.raises(HsqError) as e:  # the BAM was made from untrimmed reads but the caller says trimmed
+        flow.ingest_flow(ctx, t1, t2, ts, trim=(9, 50, 0, 50))
+    assert e.value.status == A.HSQ_ERR_NOT_TRIMMED
