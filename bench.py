@@ -233,7 +233,7 @@ def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
 
 def next_row_numbers(ctx, probes, pairs, res):
     """SURVEY 8(f) rows at N = 1, host buffers in, host buffers out, each with the CPU oracle timed on a bounded sample beside it:
-    f1 read->probe assignment, f4 record fields, f3 candidate stage (+ the alignment filter of the listed candidates)."""
+    f1 read->probe assignment, f4 record fields, f3 candidate stage (+ the alignment filter of the listed candidates), f2 text ingest + name join."""
     from bioinformatics_b200 import synth, flow
     from bioinformatics_b200 import _abi as A
     from oracle import oracle as O
@@ -324,6 +324,48 @@ def next_row_numbers(ctx, probes, pairs, res):
                            "equals_cpu_port_on_sample": same,
                            "note": "hsq_find_matches: candidates + one alignment per candidate + the five limits in one call; slot arrays "
                                    "(64 per read) returned to pageable host memory"}
+    # f2: FASTQ / SAM text -> record indexes -> the FASTQ <-> SAM name join (first dedup configuration), pageable host buffers
+    n_ing = 250000
+    case = synth.make_ingest_case(n_ing, read_len=150, seed=31)
+    sam_text = synth.sam_text_of(case, seed=32)
+    from bioinformatics_b200.batches import NameJoinHost
+    f1_, s1_, f2_, s2_ = case["trim"]
+    join = NameJoinHost(case["sam_names"], case["sam_flags"], case["sam_seq_len"], case["fq1_headers"], case["fq2_headers"], case["fq_seq_len"],
+                        case["fq_seq_len"], r1_first=f1_, r1_stop=s1_, r2_first=f2_, r2_stop=s2_)
+    ing = {"read_pairs": n_ing, "sam_lines": int(join.n), "host_buffers": "text in pinned memory, index arrays pageable"}
+
+    def pinned_text(t):
+        a = ctx.pinned_array(len(t))
+        a[:] = np.frombuffer(t, dtype=np.uint8)
+        return a
+
+    for key, gpu_fn, cpu_fn, text in (("index_fastq", ctx.index_fastq, O.index_fastq, case["fq1_text"]), ("index_sam", ctx.index_sam, O.index_sam, sam_text)):
+        ptext = pinned_text(text)
+        dt, g = timed(lambda: gpu_fn(ptext))
+        ms_dev = ctx.last_timing()[0]
+        t0 = time.perf_counter()
+        c = cpu_fn(text)
+        dt_cpu = time.perf_counter() - t0
+        cols = g.FIELDS if key == "index_fastq" else g.columns()
+        same = g.n == c.n and all(np.array_equal(getattr(g, f)[:g.n], getattr(c, f)[:c.n]) for f in cols)
+        ing[key] = {"records_per_s": g.n / dt, "text_gb_per_s_host_to_host": len(text) / dt / 1e9, "ms_host_to_host": dt * 1e3,
+                    "ms_device_incl_copies": ms_dev, "text_bytes": len(text), "records": int(g.n), "cpu_port_records_per_s": c.n / dt_cpu,
+                    "cpu_sample": "the same text, 1 thread", "equals_cpu_port": bool(same),
+                    "algorithmic_bytes_per_record": len(text) / max(g.n, 1) + (36 if key == "index_fastq" else 108)}
+    for f in ("sam_names", "fq1_headers", "fq2_headers"):  # name bytes from pinned memory
+        b = getattr(join, f)
+        setattr(join, f, A.SeqBatch(pinned_text(b.data.tobytes()), b.offsets))
+    dt, g = timed(lambda: ctx.join_names(join))
+    ms_dev = ctx.last_timing()[0]
+    t0 = time.perf_counter()
+    c = O.join_names(join)
+    dt_cpu = time.perf_counter() - t0
+    same = g.n_emitted == c.n_emitted and all(np.array_equal(a, b) for a, b in zip(g.emitted(), c.emitted())) and np.array_equal(g.status, c.status)
+    ing["join_names"] = {"sam_records_per_s": join.n / dt, "ms_host_to_host": dt * 1e3, "ms_device_incl_copies": ms_dev,
+                         "returned_records": int(g.n_emitted), "matching_pairs": int(g.total_matching_pairs),
+                         "cpu_port_sam_records_per_s": join.n / dt_cpu, "cpu_sample": "the same records, 1 thread (two std::stable_sort + the merge loop)",
+                         "equals_cpu_port": bool(same)}
+    out["ingest"] = ing
     return out
 
 

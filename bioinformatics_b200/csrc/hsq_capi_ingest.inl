@@ -146,24 +146,27 @@ __device__ inline bool cigar_reference_length(const uint8_t* __restrict__ p, int
 
 __global__ void sam_line_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ line_start, int64_t first_line, int64_t n_rec,
                                 int64_t* __restrict__ off, int32_t* __restrict__ val, int* status, unsigned long long* first_bad) {
+    const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
+    // column this lane extracts: lanes 0-4 the string columns QNAME, RNAME, CIGAR, SEQ, QUAL; lanes 8-12 FLAG, POS, MAPQ, PNEXT, TLEN
+    const int col = lane == 1 ? 2 : lane == 2 ? 5 : lane == 3 ? 9 : lane == 4 ? 10 : lane == 8 ? 1 : lane == 9 ? 3 : lane == 10 ? 4 : lane == 11 ? 7 : lane == 12 ? 8 : 0;
     int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (; r < n_rec; r += stride) {
         const int64_t s = line_start[first_line + r];
         int64_t e = line_start[first_line + r + 1] - 1;
         if (e > s && text[e - 1] == '\r') e--;
-        int64_t tab[11];
+        int64_t my_tab = e;  // lane k keeps the position of tab k (k < 11): no per-thread array
         int ntab = 0, total_tabs = 0;
         int64_t xa_s = -1, xa_e = -1;
         for (int64_t base = s; base < e; base += 32) {
             const int64_t pos = base + lane;
             const uint8_t c = pos < e ? text[pos] : (uint8_t)0;
-            const unsigned mask = __ballot_sync(0xffffffffu, c == '\t');
+            const unsigned mask = __ballot_sync(full, c == '\t');
             const int ordinal = total_tabs + __popc(mask & ((1u << lane) - 1u));  // tabs before this byte
             const bool is_xa = c == '\t' && ordinal >= 10 && pos + 6 <= e && text[pos + 1] == 'X' && text[pos + 2] == 'A' && text[pos + 3] == ':' &&
                                text[pos + 4] == 'Z' && text[pos + 5] == ':';
-            const unsigned xmask = __ballot_sync(0xffffffffu, is_xa);
+            const unsigned xmask = __ballot_sync(full, is_xa);
             if (xa_s < 0 && xmask) xa_s = base + (__ffs(xmask) - 1) + 6;
             if (xa_s >= 0 && xa_e < 0) {
                 unsigned m2 = mask;
@@ -172,31 +175,32 @@ __global__ void sam_line_kernel(const uint8_t* __restrict__ text, const int64_t*
             }
             unsigned m = mask;
             while (m && ntab < 11) {
-                tab[ntab++] = base + (__ffs(m) - 1);
+                if (lane == ntab) my_tab = base + (__ffs(m) - 1);
+                ntab++;
                 m &= m - 1;
             }
             total_tabs += __popc(mask);
+            if (ntab >= 11 && xa_e >= 0) break;  // nothing left to find on this line
         }
+        const int64_t t_prev = __shfl_sync(full, my_tab, col > 0 ? col - 1 : 0), t_cur = __shfl_sync(full, my_tab, col), t10 = __shfl_sync(full, my_tab, 10);
         bool bad = e == s || text[s] == '@' || ntab < 10;
-        int64_t f_off[HSQ_SAM_N_FIELDS] = {0, 0, 0, 0, 0, 0, 0};
-        int32_t f_len[HSQ_SAM_N_FIELDS] = {0, 0, 0, 0, 0, 0, 0};
-        int32_t num = 0;
+        int64_t f_off = col == 0 ? s : t_prev + 1;
+        int32_t f_len = (int32_t)((col < ntab ? t_cur : e) - f_off);
+        if (lane == HSQ_SAM_TAGS) {
+            f_off = ntab >= 11 ? t10 + 1 : e;
+            f_len = (int32_t)(e - f_off);
+        } else if (lane == HSQ_SAM_XA) {
+            if (xa_s >= 0 && xa_e < 0) xa_e = e;
+            const bool have = xa_s >= 0 && xa_e > xa_s;
+            f_off = have ? xa_s : 0;
+            f_len = have ? (int32_t)(xa_e - xa_s) : 0;
+        }
+        int32_t num = 0, ref_len = 0;
         if (!bad) {
-            auto fs = [&](int k) { return k == 0 ? s : tab[k - 1] + 1; };
-            auto fe = [&](int k) { return k < ntab ? tab[k] : e; };
-            const int col[5] = {0, 2, 5, 9, 10};  // QNAME, RNAME, CIGAR, SEQ, QUAL
-            for (int f = 0; f < 5; f++) { f_off[f] = fs(col[f]); f_len[f] = (int32_t)(fe(col[f]) - fs(col[f])); }
-            f_off[HSQ_SAM_TAGS] = ntab >= 11 ? tab[10] + 1 : e;
-            f_len[HSQ_SAM_TAGS] = (int32_t)(e - f_off[HSQ_SAM_TAGS]);
-            if (xa_s >= 0) {
-                if (xa_e < 0) xa_e = e;
-                if (xa_e > xa_s) { f_off[HSQ_SAM_XA] = xa_s; f_len[HSQ_SAM_XA] = (int32_t)(xa_e - xa_s); }
-            }
-            const int ncol[5] = {1, 3, 4, 7, 8};  // FLAG, POS, MAPQ, PNEXT, TLEN
             bool ok = true;
-            if (lane < 5) ok = parse_i32_field(text + fs(ncol[lane]), (int)(fe(ncol[lane]) - fs(ncol[lane])), &num);
-            else if (lane == 5) ok = cigar_reference_length(text + f_off[HSQ_SAM_CIGAR], f_len[HSQ_SAM_CIGAR], &num);
-            bad = __any_sync(0xffffffffu, !ok);
+            if (lane >= 8 && lane <= 12) ok = parse_i32_field(text + f_off, f_len, &num);
+            else if (lane == HSQ_SAM_CIGAR) ok = cigar_reference_length(text + f_off, f_len, &ref_len);
+            bad = __any_sync(full, !ok);
         }
         if (bad) {
             if (lane == 0) {
@@ -206,10 +210,11 @@ __global__ void sam_line_kernel(const uint8_t* __restrict__ text, const int64_t*
             continue;
         }
         if (lane < HSQ_SAM_N_FIELDS) {
-            off[(int64_t)lane * n_rec + r] = f_off[lane];
-            val[(int64_t)lane * n_rec + r] = f_len[lane];
+            off[(int64_t)lane * n_rec + r] = f_off;
+            val[(int64_t)lane * n_rec + r] = f_len;
         }
-        if (lane < 6) val[(int64_t)(HSQ_SAM_N_FIELDS + lane) * n_rec + r] = num;
+        if (lane >= 8 && lane <= 12) val[(int64_t)(HSQ_SAM_FLAG + lane - 8) * n_rec + r] = num;
+        if (lane == HSQ_SAM_CIGAR) val[(int64_t)HSQ_SAM_REF_LEN * n_rec + r] = ref_len;
     }
 }
 
