@@ -122,6 +122,12 @@ SAM_FIELDS = ("qname", "rname", "cigar", "seq", "qual", "tags", "xa")
 SAM_VALUES = ("flag", "pos", "mapq", "pnext", "tlen", "ref_len")
 
 
+class SamRecordsOut(C.Structure):
+    _fields_ = [("cap", C.c_int64), ("alt_cap", C.c_int64), ("n", C.c_int64), ("n_alt", C.c_int64), ("sam_line", i32p), ("contig", i32p),
+                ("negative_strand", u8p), ("second_of_pair", u8p), ("start", i32p), ("end", i32p), ("read_index", i32p), ("alt_offsets", i64p),
+                ("alt_contig", i32p), ("alt_negative", u8p), ("alt_start", i32p), ("alt_stop", i32p)]
+
+
 class NameJoin(C.Structure):
     _fields_ = [("sam_names", Seqs), ("sam_flags", i32p), ("sam_seq_len", i32p), ("sam_qual_len", i32p), ("fq1_headers", Seqs),
                 ("fq2_headers", Seqs), ("fq1_seq_len", i32p), ("fq2_seq_len", i32p), ("by_index", C.c_int32), ("trimming_skipped", C.c_int32),

@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 from . import _abi as A
-from .batches import (SamIndexResult, FastqIndexResult, NameJoinHost, NameJoinResult, AlignResult, AssignResult, FindResult, FindMatchResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
+from .batches import (SamRecordsResult, SamIndexResult, FastqIndexResult, NameJoinHost, NameJoinResult, AlignResult, AssignResult, FindResult, FindMatchResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
                       ProbeTableHost, merge_args, scorer)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
@@ -21,7 +21,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
            "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs",
-           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_index_sam", "hsq_join_names", "hsq_gather_rows")
+           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows")
 
 
 class HsqError(RuntimeError):
@@ -238,6 +238,19 @@ class Context:
         out = SamIndexResult(cap)
         oc = out.c()
         self._check(self.lib.hsq_index_sam(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(oc)))
+        return out.take(oc)
+
+    def sam_mapped_records(self, text, contig_names, cap=None, alt_cap=None):
+        """hsq_sam_mapped_records: SAM text -> the columns hsq_assign_probes takes (records().n may be smaller than the line count)."""
+        text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+        names = contig_names if isinstance(contig_names, A.SeqBatch) else A.SeqBatch.from_strings(contig_names)
+        if cap is None:
+            cap = len(text) // 22 + 1
+        if alt_cap is None:
+            alt_cap = len(text) // 8 + 1  # an XA entry is at least "c,1,*,0;"
+        out = SamRecordsResult(cap, alt_cap)
+        nc, oc = names.c(), out.c()
+        self._check(self.lib.hsq_sam_mapped_records(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(nc), C.byref(oc)))
         return out.take(oc)
 
     def join_names(self, join: NameJoinHost):

@@ -419,6 +419,36 @@ class SamIndexResult:
         return [n + "_off" for n in A.SAM_FIELDS] + [n + "_len" for n in A.SAM_FIELDS] + list(A.SAM_VALUES)
 
 
+class SamRecordsResult:
+    """hsq_sam_records_out with host arrays; records() gives the MappedRecordsHost hsq_assign_probes takes."""
+
+    def __init__(self, cap, alt_cap):
+        self.cap, self.alt_cap, self.n, self.n_alt = int(cap), int(alt_cap), 0, 0
+        i32, u8 = (lambda m: np.zeros(m, dtype=np.int32)), (lambda m: np.zeros(m, dtype=np.uint8))
+        self.sam_line, self.contig, self.start, self.end, self.read_index = i32(cap), i32(cap), i32(cap), i32(cap), i32(cap)
+        self.negative_strand, self.second_of_pair = u8(cap), u8(cap)
+        self.alt_offsets = np.zeros(cap + 1, dtype=np.int64)
+        self.alt_contig, self.alt_start, self.alt_stop, self.alt_negative = i32(alt_cap), i32(alt_cap), i32(alt_cap), u8(alt_cap)
+
+    def c(self):
+        return A.SamRecordsOut(self.cap, self.alt_cap, 0, 0, A.ptr(self.sam_line, A.i32p), A.ptr(self.contig, A.i32p), A.ptr(self.negative_strand, A.u8p),
+                               A.ptr(self.second_of_pair, A.u8p), A.ptr(self.start, A.i32p), A.ptr(self.end, A.i32p), A.ptr(self.read_index, A.i32p),
+                               A.ptr(self.alt_offsets, A.i64p), A.ptr(self.alt_contig, A.i32p), A.ptr(self.alt_negative, A.u8p),
+                               A.ptr(self.alt_start, A.i32p), A.ptr(self.alt_stop, A.i32p))
+
+    def take(self, oc):
+        self.n, self.n_alt = int(oc.n), int(oc.n_alt)
+        return self
+
+    COLUMNS = ("sam_line", "contig", "negative_strand", "second_of_pair", "start", "end", "read_index")
+    ALT_COLUMNS = ("alt_contig", "alt_negative", "alt_start", "alt_stop")
+
+    def records(self):
+        n, m = self.n, self.n_alt
+        return MappedRecordsHost(self.contig[:n], self.negative_strand[:n], self.second_of_pair[:n], self.start[:n], self.end[:n], self.read_index[:n],
+                                 (self.alt_offsets[:n + 1], self.alt_contig[:m], self.alt_negative[:m], self.alt_start[:m], self.alt_stop[:m]))
+
+
 class NameJoinHost:
     """hsq_name_join: what FastqAndBamFileMerger reads off the SAM records and the two FASTQ files
     (HSQ/process/FastqAndBamFileMerger.java:107-158,213-345)."""

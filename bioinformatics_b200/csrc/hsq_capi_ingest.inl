@@ -219,6 +219,127 @@ __global__ void sam_line_kernel(const uint8_t* __restrict__ text, const int64_t*
 }
 
 // ---------------------------------------------------------------------------------------------------------------------------
+// SAM columns -> mapped records (hsq_sam_mapped_records)
+struct NameDict {  // contig names in the caller's numbering
+    const uint8_t* data;
+    const int64_t* off;
+    int n;
+};
+__device__ inline int dict_lookup(const NameDict& d, const uint8_t* __restrict__ p, int len) {
+    for (int c = 0; c < d.n; c++) {
+        const int64_t o = d.off[c];
+        if ((int)(d.off[c + 1] - o) != len) continue;
+        int i = 0;
+        while (i < len && d.data[o + i] == p[i]) i++;
+        if (i == len) return c;
+    }
+    return -1;
+}
+
+struct AltSink {
+    int32_t* contig;
+    uint8_t* negative;
+    int32_t* start;
+    int32_t* stop;
+};
+
+// AlternativeHit.fromAttributeText (HSQ/utils/SAMRecordUtil.java:440-468) over the XA value; returns the number of hits kept and
+// writes them from slot `at` on when sink.contig is not null
+__device__ inline int xa_hits(const uint8_t* __restrict__ p, int len, const NameDict& dict, const AltSink& sink, int64_t at, bool* bad_cigar) {
+    int count = 0;
+    int es = 0;
+    while (es < len) {
+        int ee = es;
+        while (ee < len && p[ee] != ';') ee++;
+        int f_start[4] = {0, 0, 0, 0}, f_len[4] = {0, 0, 0, 0};
+        int nf = 0, last_nonempty = -1, fs = es;
+        for (int k = es; k <= ee; k++) {
+            if (k == ee || p[k] == ',') {
+                if (nf < 4) { f_start[nf] = fs; f_len[nf] = k - fs; }
+                if (k > fs) last_nonempty = nf;
+                nf++;
+                fs = k + 1;
+            }
+        }
+        if (last_nonempty == 3) {  // String.split drops trailing empty strings: exactly four fields remain
+            int32_t start_and_strand = 0, rl = 0;
+            if (parse_i32_field(p + f_start[1], f_len[1], &start_and_strand)) {
+                if (!cigar_reference_length(p + f_start[2], f_len[2], &rl)) *bad_cigar = true;
+                else {
+                    if (sink.contig) {
+                        const int32_t st = start_and_strand < 0 ? -start_and_strand : start_and_strand;
+                        sink.contig[at + count] = dict_lookup(dict, p + f_start[0], f_len[0]);
+                        sink.negative[at + count] = start_and_strand < 0 ? 1 : 0;
+                        sink.start[at + count] = st;
+                        sink.stop[at + count] = st + rl - 1;
+                    }
+                    count++;
+                }
+            }
+        }
+        es = ee + 1;
+    }
+    return count;
+}
+
+// per alignment line: kept (both mates mapped, ...Identification.java:446) and its number of alternative hits
+__global__ void samrec_count_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, const int32_t* __restrict__ val, int64_t n_rec,
+                                    NameDict dict, int64_t* __restrict__ keep, int64_t* __restrict__ n_alt, int* status) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n_rec; r += stride) {
+        const int f = val[(int64_t)HSQ_SAM_FLAG * n_rec + r];
+        if (!(f & 0x1)) atomicMin(status, HSQ_ERR_UNSUPPORTED);  // getMateUnmappedFlag on an unpaired record throws
+        const bool k = !(f & 0x4) && !(f & 0x8);
+        int c = 0;
+        const int xl = val[(int64_t)HSQ_SAM_XA * n_rec + r];
+        if (k && xl > 0) {
+            bool bad = false;
+            c = xa_hits(text + off[(int64_t)HSQ_SAM_XA * n_rec + r], xl, dict, AltSink{nullptr, nullptr, nullptr, nullptr}, 0, &bad);
+            if (bad) atomicMin(status, HSQ_ERR_MALFORMED);
+        }
+        keep[r] = k ? 1 : 0;
+        n_alt[r] = c;
+    }
+}
+
+__global__ void samrec_fill_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ off, const int32_t* __restrict__ val, int64_t n_rec,
+                                   NameDict dict, const int64_t* __restrict__ keep_pos, const int64_t* __restrict__ alt_pos, int64_t cap, int64_t alt_cap,
+                                   int32_t* __restrict__ sam_line, int32_t* __restrict__ contig, uint8_t* __restrict__ negative,
+                                   uint8_t* __restrict__ second, int32_t* __restrict__ start, int32_t* __restrict__ end, int32_t* __restrict__ read_index,
+                                   int64_t* __restrict__ alt_offsets, AltSink sink, int* status) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r <= n_rec; r += stride) {
+        const int64_t j = keep_pos[r];
+        if (r == n_rec) {
+            if (j <= cap) alt_offsets[j] = alt_pos[r];
+            continue;
+        }
+        if (keep_pos[r + 1] == j || j >= cap) continue;
+        const int f = val[(int64_t)HSQ_SAM_FLAG * n_rec + r];
+        const int c = dict_lookup(dict, text + off[(int64_t)HSQ_SAM_RNAME * n_rec + r], val[(int64_t)HSQ_SAM_RNAME * n_rec + r]);
+        int32_t ri = 0;
+        if (c >= 0 && !parse_i32_field(text + off[(int64_t)HSQ_SAM_QNAME * n_rec + r], val[(int64_t)HSQ_SAM_QNAME * n_rec + r], &ri))
+            atomicMin(status, HSQ_ERR_BAD_CHARACTER);  // "Expecting all read names to be numbers" (:471-474)
+        const int32_t pos = val[(int64_t)HSQ_SAM_POS * n_rec + r];
+        sam_line[j] = (int32_t)r;
+        contig[j] = c;
+        negative[j] = (f & 0x10) ? 1 : 0;
+        second[j] = (f & 0x80) ? 1 : 0;
+        start[j] = pos;
+        end[j] = pos + val[(int64_t)HSQ_SAM_REF_LEN * n_rec + r] - 1;
+        read_index[j] = ri;
+        alt_offsets[j] = alt_pos[r];
+        const int xl = val[(int64_t)HSQ_SAM_XA * n_rec + r];
+        if (xl > 0 && alt_pos[r + 1] <= alt_cap) {
+            bool bad = false;
+            xa_hits(text + off[(int64_t)HSQ_SAM_XA * n_rec + r], xl, dict, sink, alt_pos[r], &bad);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
 // ragged row gather
 __global__ void rows_len_kernel(const int64_t* __restrict__ off, const int32_t* __restrict__ len, int64_t n, int64_t n_bytes,
                                 int64_t* __restrict__ len64, int* status) {
@@ -656,13 +777,12 @@ extern "C" int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_
     return timer.finish();
 }
 
-extern "C" int32_t hsq_index_sam(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_sam_index* out) {
-    if (!ctx || !out || n_bytes < 0 || (n_bytes > 0 && !text)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_sam: null argument");
-    out->n = 0;
-    out->n_header_lines = 0;
-    if (n_bytes == 0) return HSQ_OK;
-    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
-    CallTimer timer(ctx);
+namespace {
+
+// text -> device-resident column planes (stride n_rec): d_off [HSQ_SAM_N_FIELDS][n_rec] in ctx->sort_b, d_val [HSQ_SAM_N_VALUES][n_rec] in
+// ctx->out_i32; the text stays in ctx->r1.ascii
+int sam_index_device(hsq_ctx* ctx, const char* who, const uint8_t* text, int64_t n_bytes, uint8_t** d_text_out, int64_t** d_off_out, int32_t** d_val_out,
+                     int64_t* n_rec_out, int64_t* n_header_out) {
     int rc = reset_status(ctx);
     if (rc) return rc;
     uint8_t* d_text;
@@ -676,10 +796,7 @@ extern "C" int32_t hsq_index_sam(hsq_ctx* ctx, const uint8_t* text, int64_t n_by
     HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     const int64_t n_header = ctx->h_cells[1] == ~0ull ? n_lines : (int64_t)ctx->h_cells[1];
     const int64_t n_rec = n_lines - n_header;
-    out->n = n_rec;
-    out->n_header_lines = n_header;
-    if (n_rec > out->cap) return fail(ctx, HSQ_ERR_OVERFLOW, "hsq_index_sam: more alignment lines than out->cap");
-    if (n_rec > 0 && (!out->off || !out->val)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_sam: null output plane");
+    if (n_rec >= (1ll << 31)) return fail(ctx, HSQ_ERR_UNSUPPORTED, std::string(who) + ": more than 2^31 alignment lines in one call");
     const size_t nr = (size_t)n_rec;
     HSQ_CUDA(ctx, ctx->sort_b.ensure(nr * 8 * HSQ_SAM_N_FIELDS + 64));
     HSQ_CUDA(ctx, ctx->out_i32.ensure(nr * 4 * HSQ_SAM_N_VALUES + 64));
@@ -694,13 +811,116 @@ extern "C" int32_t hsq_index_sam(hsq_ctx* ctx, const uint8_t* text, int64_t n_by
     HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
     int st[1];
     if ((rc = read_status(ctx, st, 1))) return rc;
-    if (st[0] == HSQ_ERR_UNSUPPORTED) return fail(ctx, st[0], "hsq_index_sam: a carriage return that is not followed by a line feed");
-    if (st[0]) return fail(ctx, st[0], "hsq_index_sam: alignment line " + std::to_string(ctx->h_cells[0]) +
+    if (st[0] == HSQ_ERR_UNSUPPORTED) return fail(ctx, st[0], std::string(who) + ": a carriage return that is not followed by a line feed");
+    if (st[0]) return fail(ctx, st[0], std::string(who) + ": alignment line " + std::to_string(ctx->h_cells[0]) +
                                            " is empty, a header line, has fewer than 11 columns, a non-numeric FLAG/POS/MAPQ/PNEXT/TLEN or a bad CIGAR");
+    *d_text_out = d_text;
+    *d_off_out = d_off;
+    *d_val_out = d_val;
+    *n_rec_out = n_rec;
+    *n_header_out = n_header;
+    return HSQ_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_index_sam(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_sam_index* out) {
+    if (!ctx || !out || n_bytes < 0 || (n_bytes > 0 && !text)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_sam: null argument");
+    out->n = 0;
+    out->n_header_lines = 0;
+    if (n_bytes == 0) return HSQ_OK;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    uint8_t* d_text;
+    int64_t* d_off;
+    int32_t* d_val;
+    int64_t n_rec, n_header;
+    int rc = sam_index_device(ctx, "hsq_index_sam", text, n_bytes, &d_text, &d_off, &d_val, &n_rec, &n_header);
+    if (rc) return rc;
+    out->n = n_rec;
+    out->n_header_lines = n_header;
+    if (n_rec > out->cap) return fail(ctx, HSQ_ERR_OVERFLOW, "hsq_index_sam: more alignment lines than out->cap");
+    if (n_rec > 0 && (!out->off || !out->val)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_index_sam: null output plane");
+    const size_t nr = (size_t)n_rec;
     for (int f = 0; f < HSQ_SAM_N_FIELDS && nr; f++)
         HSQ_CUDA(ctx, cudaMemcpyAsync(out->off + (int64_t)f * out->cap, d_off + (size_t)f * nr, nr * 8, cudaMemcpyDeviceToHost, ctx->stream));
     for (int v = 0; v < HSQ_SAM_N_VALUES && nr; v++)
         HSQ_CUDA(ctx, cudaMemcpyAsync(out->val + (int64_t)v * out->cap, d_val + (size_t)v * nr, nr * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    return timer.finish();
+}
+
+extern "C" int32_t hsq_sam_mapped_records(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, const hsq_seqs* contig_names, hsq_sam_records_out* out) {
+    if (!ctx || !out || !contig_names || n_bytes < 0 || (n_bytes > 0 && !text)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_sam_mapped_records: null argument");
+    out->n = 0;
+    out->n_alt = 0;
+    if (contig_names->n < 0 || contig_names->n > 100000 || !contig_names->offsets || contig_names->offsets[0] != 0)
+        return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_sam_mapped_records: bad contig_names");
+    if (out->cap >= 0 && out->alt_offsets) out->alt_offsets[0] = 0;
+    if (n_bytes == 0) return HSQ_OK;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    uint8_t* d_text;
+    int64_t* d_off;
+    int32_t* d_val;
+    int64_t n_rec, n_header;
+    int rc = sam_index_device(ctx, "hsq_sam_mapped_records", text, n_bytes, &d_text, &d_off, &d_val, &n_rec, &n_header);
+    if (rc) return rc;
+    if (n_rec == 0) return timer.finish();
+    DevBuf* ib = ctx->ing;
+    const int64_t dict_bytes = contig_names->offsets[contig_names->n];
+    HSQ_CUDA(ctx, ib[0].ensure((size_t)dict_bytes + 16));
+    HSQ_CUDA(ctx, ib[1].ensure((size_t)(contig_names->n + 1) * 8));
+    if (dict_bytes) HSQ_CUDA(ctx, cudaMemcpyAsync(ib[0].p, contig_names->data, (size_t)dict_bytes, cudaMemcpyHostToDevice, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ib[1].p, contig_names->offsets, (size_t)(contig_names->n + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
+    NameDict dict{ib[0].as<uint8_t>(), ib[1].as<int64_t>(), (int)contig_names->n};
+    const size_t nr = (size_t)n_rec;
+    const int64_t n_tiles = (n_rec + 1 + SCAN_TILE - 1) / SCAN_TILE;
+    HSQ_CUDA(ctx, ib[2].ensure((nr + 1) * 8 * 4 + 64));
+    HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)n_tiles * 8 + 16));
+    int64_t* d_keep = ib[2].as<int64_t>();
+    int64_t* d_nalt = d_keep + nr + 1;
+    int64_t* d_keep_pos = d_nalt + nr + 1;
+    int64_t* d_alt_pos = d_keep_pos + nr + 1;
+    const int g = grid_for(ctx, n_rec + 1, 128, 16);
+    samrec_count_kernel<<<g, 128, 0, ctx->stream>>>(d_text, d_off, d_val, n_rec, dict, d_keep, d_nalt, d_status(ctx));
+    ctx->launches++;
+    if ((rc = scan_i64(ctx, d_keep, n_rec, ctx->sort_c.as<int64_t>(), d_keep_pos))) return rc;
+    if ((rc = scan_i64(ctx, d_nalt, n_rec, ctx->sort_c.as<int64_t>(), d_alt_pos))) return rc;
+    int64_t totals[2] = {0, 0};
+    HSQ_CUDA(ctx, cudaMemcpyAsync(&totals[0], d_keep_pos + nr, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(&totals[1], d_alt_pos + nr, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    int st[1];
+    if ((rc = read_status(ctx, st, 1))) return rc;
+    if (st[0] == HSQ_ERR_UNSUPPORTED) return fail(ctx, st[0], "hsq_sam_mapped_records: a record without the paired flag (htsjdk: Inappropriate call if not paired read)");
+    if (st[0]) return fail(ctx, st[0], "hsq_sam_mapped_records: malformed CIGAR in an XA entry");
+    out->n = totals[0];
+    out->n_alt = totals[1];
+    if (out->n > out->cap || out->n_alt > out->alt_cap) return fail(ctx, HSQ_ERR_OVERFLOW, "hsq_sam_mapped_records: more records or alternative hits than cap / alt_cap");
+    const size_t nk = (size_t)out->n, na = (size_t)out->n_alt;
+    if (nk && (!out->sam_line || !out->contig || !out->negative_strand || !out->second_of_pair || !out->start || !out->end || !out->read_index || !out->alt_offsets))
+        return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_sam_mapped_records: null output array");
+    if (na && (!out->alt_contig || !out->alt_negative || !out->alt_start || !out->alt_stop))
+        return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_sam_mapped_records: null alternative-hit array");
+    // outputs: 5 int32 columns + 2 byte columns + offsets; 3 int32 + 1 byte per hit
+    HSQ_CUDA(ctx, ib[3].ensure(nk * 4 * 5 + (nk + 1) * 8 + nk * 2 + na * 13 + 256));
+    uint8_t* ob = ib[3].as<uint8_t>();
+    int64_t* o_altoff = reinterpret_cast<int64_t*>(ob);
+    int32_t* o_line = reinterpret_cast<int32_t*>(o_altoff + nk + 1);
+    int32_t *o_contig = o_line + nk, *o_start = o_contig + nk, *o_end = o_start + nk, *o_ri = o_end + nk;
+    int32_t *o_ac = o_ri + nk, *o_as = o_ac + na, *o_ae = o_as + na;
+    uint8_t *o_neg = reinterpret_cast<uint8_t*>(o_ae + na), *o_sec = o_neg + nk, *o_an = o_sec + nk;
+    samrec_fill_kernel<<<g, 128, 0, ctx->stream>>>(d_text, d_off, d_val, n_rec, dict, d_keep_pos, d_alt_pos, (int64_t)nk, (int64_t)na, o_line, o_contig, o_neg,
+                                                   o_sec, o_start, o_end, o_ri, o_altoff, AltSink{o_ac, o_an, o_as, o_ae}, d_status(ctx));
+    ctx->launches++;
+    HSQ_CUDA(ctx, cudaGetLastError());
+    if ((rc = read_status(ctx, st, 1))) return rc;
+    if (st[0]) return fail(ctx, st[0], "hsq_sam_mapped_records: Expecting all read names to be numbers (the merged BAM names its records by FASTQ ordinal)");
+    struct { void* h; const void* d; size_t bytes; } down[] = {
+        {out->sam_line, o_line, nk * 4}, {out->contig, o_contig, nk * 4}, {out->start, o_start, nk * 4}, {out->end, o_end, nk * 4},
+        {out->read_index, o_ri, nk * 4}, {out->negative_strand, o_neg, nk}, {out->second_of_pair, o_sec, nk}, {out->alt_offsets, o_altoff, (nk + 1) * 8},
+        {out->alt_contig, o_ac, na * 4}, {out->alt_start, o_as, na * 4}, {out->alt_stop, o_ae, na * 4}, {out->alt_negative, o_an, na}};
+    for (auto& c : down)
+        if (c.bytes && c.h) HSQ_CUDA(ctx, cudaMemcpyAsync(c.h, c.d, c.bytes, cudaMemcpyDeviceToHost, ctx->stream));
     return timer.finish();
 }
 

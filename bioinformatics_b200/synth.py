@@ -300,9 +300,10 @@ def make_ingest_case(n_pairs, read_len=150, seed=7, mapped_frac=0.9, lone_frac=0
                 sam_seq_len=np.asarray(slen, dtype=np.int32)[order], trim=trim, three_prime=three_prime)
 
 
-def sam_text_of(case, seed=3, n_contigs=22, xa_rate=0.05, crlf=False, final_newline=True):
+def sam_text_of(case, seed=3, n_contigs=22, xa_rate=0.05, crlf=False, final_newline=True, index_names=False):
     """SAM text for the records of make_ingest_case: header lines, then one alignment line per record with the trimmed read, a CIGAR
-    with an occasional insertion / deletion / soft clip, mate columns and NM / MD / XA tags (as `bwa mem` writes them)."""
+    with an occasional insertion / deletion / soft clip, mate columns and NM / MD / XA tags (as `bwa mem` writes them).
+    index_names: QNAME = the FASTQ ordinal of the read, as in the merged BAM the dedup path works on (FastqSorter.java:298-302)."""
     rng = np.random.default_rng(seed)
     eol = "\r\n" if crlf else "\n"
     f1, _, f2, _ = case["trim"]
@@ -332,7 +333,11 @@ def sam_text_of(case, seed=3, n_contigs=22, xa_rate=0.05, crlf=False, final_newl
             cigar = "%dM" % ln
         tags = ["NM:i:%d" % (kind[k] % 3), "MD:Z:%d" % ln, "AS:i:%d" % ln]
         if rng.random() < xa_rate:
-            tags.insert(int(rng.integers(0, 4)), "XA:Z:chr%d,%s%d,%dM,1;" % (int(rng.integers(1, n_contigs + 1)), "+-"[k % 2], int(pos[k]) + 7, ln))
+            hits = ["chr%d,%s%d,%dM,1;" % (int(rng.integers(1, n_contigs + 3)), "+-"[(k + h) % 2], int(pos[k]) + 7 * h, ln - h)
+                    for h in range(int(rng.integers(1, 4)))]
+            tags.insert(int(rng.integers(0, 4)), "XA:Z:" + "".join(hits))
+        if index_names:
+            name = str(row if row is not None else case["n_pairs"] + k)
         lines.append("\t".join([name, str(fl), "chr%d" % contig[k], str(int(pos[k])), str(int(rng.integers(0, 61))), cigar, "=",
                                 str(int(pos[k]) + 100), str(int(rng.integers(-400, 400))), seq, qual] + tags))
     t = eol.join(lines) + (eol if final_newline else "")

@@ -423,6 +423,32 @@ typedef struct hsq_sam_index {
 } hsq_sam_index;
 int32_t hsq_index_sam(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_sam_index* out);
 
+/* SAM text -> the columns hsq_assign_probes takes (hsq_mapped_records), as ReadToProbeAssigner.assignProbesToReads reads
+ * them off the merged BAM's records (…Identification.java:439-474): records with the unmapped or mate-unmapped flag are dropped
+ * (:446; a record that is not paired makes htsjdk throw there: HSQ_ERR_UNSUPPORTED), contig = index of RNAME in contig_names
+ * (-1: not listed), end = POS + reference length of the CIGAR - 1, read_index = Integer.parseInt(QNAME) for records on a listed
+ * contig (not a number: HSQ_ERR_BAD_CHARACTER, the IllegalStateException of :471-474).  Alternative hits are the XA entries as
+ * AlternativeHit.fromAttributeText keeps them (HSQ/utils/SAMRecordUtil.java:440-468): four comma separated fields, the second
+ * an integer (else the entry is skipped), stop = start + reference length of the entry's CIGAR - 1.  More records / hits than
+ * cap / alt_cap: HSQ_ERR_OVERFLOW with n / n_alt set. */
+typedef struct hsq_sam_records_out {
+    int64_t cap, alt_cap; /* in */
+    int64_t n, n_alt;     /* out */
+    int32_t* sam_line;    /* [cap] alignment line (0-based, header lines not counted) of kept record k */
+    int32_t* contig;
+    uint8_t* negative_strand;
+    uint8_t* second_of_pair;
+    int32_t* start;
+    int32_t* end;
+    int32_t* read_index;
+    int64_t* alt_offsets; /* [cap + 1] */
+    int32_t* alt_contig;  /* [alt_cap] */
+    uint8_t* alt_negative;
+    int32_t* alt_start;
+    int32_t* alt_stop;
+} hsq_sam_records_out;
+int32_t hsq_sam_mapped_records(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, const hsq_seqs* contig_names, hsq_sam_records_out* out);
+
 /* FastqAndBamFileMerger.createBamFileWithDataFromRawFastqFiles (HSQ/process/FastqAndBamFileMerger.java:107-158) without the
  * file codecs: both sorts and the merge loop of MergedSamIterator (:213-345) for the two configurations the dedup command
  * uses.  by_index = 0 (…Identification.java:150-160): FASTQ records sorted by header + " _ " + ordinal

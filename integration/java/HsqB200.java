@@ -94,6 +94,11 @@ public final class HsqB200 implements AutoCloseable {
             JAVA_INT, JAVA_INT, JAVA_DOUBLE, ADDRESS, ADDRESS));
     private static final MethodHandle MERGE_PAIRS = fn("hsq_merge_pairs", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS,
             ADDRESS, JAVA_LONG));
+    private static final MethodHandle INDEX_FASTQ = fn("hsq_index_fastq", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
+    private static final MethodHandle INDEX_SAM = fn("hsq_index_sam", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
+    private static final MethodHandle JOIN_NAMES = fn("hsq_join_names", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle GATHER_ROWS = fn("hsq_gather_rows", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS,
+            ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG));
     private static final MethodHandle RESOLVE = fn("hsq_resolve_multi_probe", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
             JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
 
@@ -181,6 +186,25 @@ public final class HsqB200 implements AutoCloseable {
     public void findMatches(MemorySegment reads, MemorySegment quals, int leadingQuality, int trailingQuality, int candidateLimit,
                             double minHitRatio, MemorySegment limits, MemorySegment findMatchOut) {
         check(invokeInt(FIND_MATCHES, ctx, reads, quals, leadingQuality, trailingQuality, candidateLimit, minHitRatio, limits, findMatchOut));
+    }
+
+    /** Record index of FASTQ text as FastqReader reads it (call sites FastqSorter.java:77,98); fastqIndex = hsq_fastq_index. */
+    public void indexFastq(MemorySegment text, long nBytes, MemorySegment fastqIndex) { check(invokeInt(INDEX_FASTQ, ctx, text, nBytes, fastqIndex)); }
+
+    /** Column index of SAM text (QNAME, FLAG, RNAME, POS, CIGAR reference length, SEQ, QUAL, XA); samIndex = hsq_sam_index. */
+    public void indexSam(MemorySegment text, long nBytes, MemorySegment samIndex) { check(invokeInt(INDEX_SAM, ctx, text, nBytes, samIndex)); }
+
+    /** Both sorts and the merge loop of FastqAndBamFileMerger.createBamFileWithDataFromRawFastqFiles (FastqAndBamFileMerger.java:107-158,
+     *  213-345); nameJoin = hsq_name_join, nameJoinOut = hsq_name_join_out.  The status codes map back to the exceptions of the loop:
+     *  ERR_NAME_MISMATCH / ERR_NO_MATCHES -> IllegalStateException, ERR_NOT_TRIMMED -> UnableToMergeFastqAndBamFilesException. */
+    public void joinNames(MemorySegment nameJoin, MemorySegment nameJoinOut) { check(invokeInt(JOIN_NAMES, ctx, nameJoin, nameJoinOut)); }
+
+    /** Rows text[off[k] .. off[k] + len[k]) as a ragged batch: the raw reads / qualities storeFastqInfoInRecord copies (:386-396). */
+    public int gatherRows(MemorySegment text, long nBytes, MemorySegment off, MemorySegment len, long n, MemorySegment outData,
+                          MemorySegment outOffsets, long outCap) {
+        int st = invokeInt(GATHER_ROWS, ctx, text, nBytes, off, len, n, outData, outOffsets, outCap);
+        if (st != ERR_OVERFLOW) check(st);
+        return st;
     }
 
     /** mergeSequences per item (…Identification.java:1362-1552); ERR_OVERFLOW = call again with the sizes in outOffsets. */

@@ -388,6 +388,31 @@ int32_t hsqo_index_sam(const uint8_t* text, int64_t n_bytes, hsq_sam_index* o) {
     } catch (const FastqMalformed& e) { g_err = e.what(); return HSQ_ERR_MALFORMED; }
 }
 
+// f2 -> f1: SAM text -> mapped records (hsq_oracle_ingest.hpp)
+int32_t hsqo_sam_mapped_records(const uint8_t* text, int64_t n_bytes, const hsq_seqs* contig_names, hsq_sam_records_out* o) {
+    try {
+        std::vector<std::string> names;
+        for (int64_t k = 0; k < contig_names->n; k++) names.push_back(get_str(contig_names->data, contig_names->offsets, k));
+        SamRecords r = sam_mapped_records(text, n_bytes, names);
+        o->n = (int64_t)r.contig.size();
+        o->n_alt = (int64_t)r.alt_contig.size();
+        if (o->n > o->cap || o->n_alt > o->alt_cap) { g_err = "more records or hits than cap"; return HSQ_ERR_OVERFLOW; }
+        for (int64_t k = 0; k < o->n; k++) {
+            const size_t i = (size_t)k;
+            o->sam_line[k] = r.sam_line[i]; o->contig[k] = r.contig[i]; o->negative_strand[k] = r.negative_strand[i];
+            o->second_of_pair[k] = r.second_of_pair[i]; o->start[k] = r.start[i]; o->end[k] = r.end[i]; o->read_index[k] = r.read_index[i];
+        }
+        for (int64_t k = 0; k <= o->n; k++) o->alt_offsets[k] = r.alt_offsets[(size_t)k];
+        for (int64_t k = 0; k < o->n_alt; k++) {
+            const size_t i = (size_t)k;
+            o->alt_contig[k] = r.alt_contig[i]; o->alt_negative[k] = r.alt_negative[i]; o->alt_start[k] = r.alt_start[i]; o->alt_stop[k] = r.alt_stop[i];
+        }
+        return HSQ_OK;
+    } catch (const SamUnpaired& e) { g_err = e.what(); return HSQ_ERR_UNSUPPORTED;
+    } catch (const SamNameNotANumber& e) { g_err = e.what(); return HSQ_ERR_BAD_CHARACTER;
+    } catch (const FastqMalformed& e) { g_err = e.what(); return HSQ_ERR_MALFORMED; }
+}
+
 // f2: the two sorts and the merge loop of FastqAndBamFileMerger (hsq_oracle_ingest.hpp)
 int32_t hsqo_join_names(const hsq_name_join* in, hsq_name_join_out* o) {
     JoinInput ji;

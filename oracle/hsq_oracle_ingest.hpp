@@ -323,4 +323,98 @@ inline SamIndex index_sam(const uint8_t* text, int64_t n) {
     return ix;
 }
 
+// ---- SAM text -> the records ReadToProbeAssigner.assignProbesToReads works on ------------------------------------------------
+// ...Identification.java:439-470: records with the unmapped or mate-unmapped flag are dropped (:446; htsjdk's getMateUnmappedFlag
+// throws IllegalStateException on a record that is not paired), strand / second-of-pair flags, getAlignmentStart / getAlignmentEnd,
+// Integer.parseInt(readName) for records on a contig that has probes (:469-474).  Alternative hits:
+// SAMRecordUtil.getAlternativeHitsFromAttribute -> AlternativeHit.fromAttributeText (HSQ/utils/SAMRecordUtil.java:362-375,440-468):
+// entries split on ';', fields on ',' (String.split: trailing empty strings dropped), exactly four fields, Integer.parseInt of the
+// second (sign = strand, abs = start; NumberFormatException: entry skipped), stop = getAlignmentEnd of the copy = start +
+// reference length of the entry's CIGAR - 1 (the `stop` computed at :457 is handed to a constructor that ignores it, :399-406).
+struct SamUnpaired : std::runtime_error { using std::runtime_error::runtime_error; };
+struct SamNameNotANumber : std::runtime_error { using std::runtime_error::runtime_error; };
+
+inline std::vector<std::string> java_split(const std::string& s, char sep) {
+    std::vector<std::string> out;
+    size_t b = 0;
+    for (size_t k = 0; k <= s.size(); k++)
+        if (k == s.size() || s[k] == sep) { out.push_back(s.substr(b, k - b)); b = k + 1; }
+    while (!out.empty() && out.back().empty()) out.pop_back();
+    if (out.empty() && s.empty()) out.push_back("");  // "".split(x) is [""]
+    return out;
+}
+
+inline bool cigar_ref_len(const std::string& c, int64_t* out) {
+    if (c == "*") { *out = 0; return true; }
+    if (c.empty()) return false;
+    int64_t rl = 0, count = 0;
+    bool digits = false;
+    for (char ch : c) {
+        if (ch >= '0' && ch <= '9') { count = count * 10 + (ch - '0'); digits = true; if (count > INT32_MAX) return false; continue; }
+        if (!digits) return false;
+        if (ch == 'M' || ch == 'D' || ch == 'N' || ch == '=' || ch == 'X') rl += count;
+        else if (!(ch == 'I' || ch == 'S' || ch == 'H' || ch == 'P')) return false;
+        count = 0;
+        digits = false;
+    }
+    if (digits || rl > INT32_MAX) return false;
+    *out = rl;
+    return true;
+}
+
+struct SamRecords {
+    std::vector<int32_t> sam_line, contig, start, end, read_index, alt_contig, alt_start, alt_stop;
+    std::vector<uint8_t> negative_strand, second_of_pair, alt_negative;
+    std::vector<int64_t> alt_offsets{0};
+};
+
+inline SamRecords sam_mapped_records(const uint8_t* text, int64_t n, const std::vector<std::string>& contig_names) {
+    const SamIndex ix = index_sam(text, n);
+    SamRecords out;
+    auto contig_of = [&](const std::string& name) {
+        for (size_t c = 0; c < contig_names.size(); c++)
+            if (contig_names[c] == name) return (int32_t)c;
+        return (int32_t)-1;
+    };
+    auto str = [&](int64_t off, int32_t len) { return std::string((const char*)text + off, (size_t)len); };
+    for (size_t k = 0; k < ix.flag.size(); k++) {
+        const int32_t f = ix.flag[k];
+        if (!(f & 0x1)) throw SamUnpaired("Inappropriate call if not paired read");
+        if ((f & 0x8) || (f & 0x4)) continue;
+        const int32_t contig = contig_of(str(ix.rname_off[k], ix.rname_len[k]));
+        int32_t read_index = 0;
+        if (contig >= 0) {
+            try {
+                read_index = java_parse_int(str(ix.qname_off[k], ix.qname_len[k]));
+            } catch (const JoinBadNumber&) { throw SamNameNotANumber("Expecting all read names to be numbers because the trim step also replaces names with the read index"); }
+        }
+        out.sam_line.push_back((int32_t)k);
+        out.contig.push_back(contig);
+        out.negative_strand.push_back((f & 0x10) ? 1 : 0);
+        out.second_of_pair.push_back((f & 0x80) ? 1 : 0);
+        out.start.push_back(ix.pos[k]);
+        out.end.push_back(ix.pos[k] + ix.ref_len[k] - 1);
+        out.read_index.push_back(read_index);
+        if (ix.xa_len[k] > 0) {
+            for (const std::string& entry : java_split(str(ix.xa_off[k], ix.xa_len[k]), ';')) {
+                const std::vector<std::string> fields = java_split(entry, ',');
+                if (fields.size() != 4) continue;
+                int32_t start_and_strand;
+                try {
+                    start_and_strand = java_parse_int(fields[1]);
+                } catch (const JoinBadNumber&) { continue; }  // warning, hit not used (:462-464)
+                int64_t rl;
+                if (!cigar_ref_len(fields[2], &rl)) throw FastqMalformed("CIGAR of an alternative hit");
+                const int32_t start = start_and_strand < 0 ? -start_and_strand : start_and_strand;
+                out.alt_contig.push_back(contig_of(fields[0]));
+                out.alt_negative.push_back(start_and_strand < 0 ? 1 : 0);
+                out.alt_start.push_back(start);
+                out.alt_stop.push_back((int32_t)(start + rl - 1));
+            }
+        }
+        out.alt_offsets.push_back((int64_t)out.alt_contig.size());
+    }
+    return out;
+}
+
 }  // namespace hsqo

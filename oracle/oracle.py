@@ -10,7 +10,7 @@ import subprocess
 import numpy as np
 
 from bioinformatics_b200 import _abi as A
-from bioinformatics_b200.batches import (SamIndexResult, FastqIndexResult, NameJoinResult, AlignResult, AssignResult, ExtendResult, FindResult, RecordResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
+from bioinformatics_b200.batches import (SamRecordsResult, SamIndexResult, FastqIndexResult, NameJoinResult, AlignResult, AssignResult, ExtendResult, FindResult, RecordResult, PairBatchHost, ProbeStatsHost, ProbeTableHost,
                                          merge_args, scorer)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
@@ -37,7 +37,7 @@ def lib():
         for name in ("hsqo_align_batch", "hsqo_trim_batch", "hsqo_dedup_batch", "hsqo_extend_batch",
                      "hsqo_resolve_multi_probe", "hsqo_primer_end", "hsqo_index_of_first_match_in_reference",
                      "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs", "hsqo_assign_probes",
-                     "hsqo_extend_records", "hsqo_find_candidates", "hsqo_index_fastq", "hsqo_index_sam", "hsqo_join_names"):
+                     "hsqo_extend_records", "hsqo_find_candidates", "hsqo_index_fastq", "hsqo_index_sam", "hsqo_sam_mapped_records", "hsqo_join_names"):
             getattr(_lib, name).restype = C.c_int32
     return _lib
 
@@ -134,6 +134,16 @@ def index_sam(text, cap=None):
     out = SamIndexResult(cap)
     oc = out.c()
     _check(lib().hsqo_index_sam(A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(oc)))
+    return out.take(oc)
+
+
+def sam_mapped_records(text, contig_names, cap=None, alt_cap=None):
+    """SAM text -> mapped records + alternative hits on the CPU (hsq_oracle_ingest.hpp)."""
+    text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+    names = contig_names if isinstance(contig_names, A.SeqBatch) else A.SeqBatch.from_strings(contig_names)
+    out = SamRecordsResult(len(text) // 22 + 1 if cap is None else cap, len(text) // 8 + 1 if alt_cap is None else alt_cap)
+    nc, oc = names.c(), out.c()
+    _check(lib().hsqo_sam_mapped_records(A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(nc), C.byref(oc)))
     return out.take(oc)
 
 

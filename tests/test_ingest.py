@@ -247,6 +247,88 @@ def test_oracle_sam_index():
         check_sam_index(O.index_sam(text), text)
 
 
+SAM_RECORDS_KAT = (b"@HD\tVN:1.0\n"
+                   b"7\t99\tchr1\t10\t60\t5M1I3M2D4M\t=\t50\t60\tACGTACGTACGTA\tIIIIIIIIIIIII\tNM:i:1\t"
+                   b"XA:Z:chr2,+5,13M,1;chrX,-77,3M2D3M,0;chr1,x,3M,1;chr1,+9,3M;chr2,-4,2S3M,0,;;\n"
+                   b"8\t77\t*\t0\t0\t*\t*\t0\t0\tAC\t##\n"
+                   b"9\t147\tchrU\t20\t0\t4M\t=\t1\t0\tACGT\t####\n")
+# by hand: line 0 (flag 99: paired, first, forward) chr1 -> 0, end = 10 + (5+3+2+4) - 1 = 23; XA keeps chr2,+5,13M (stop 17), chrX,-77,3M2D3M
+# (contig -1, reverse, stop 77+8-1 = 84) and chr2,-4,2S3M,0, (String.split drops the trailing empty field; stop 4+3-1 = 6); "chr1,x,..." is not a
+# number, "chr1,+9,3M" has three fields.  Line 1 (flag 77) is unmapped: dropped.  Line 2 (flag 147: reverse, second) sits on a contig without
+# probes: -1, its name is never parsed.
+SAM_RECORDS_KAT_EXPECTED = dict(sam_line=[0, 2], contig=[0, -1], negative_strand=[0, 1], second_of_pair=[0, 1], start=[10, 20], end=[23, 23],
+                                read_index=[7, 0], alt_offsets=[0, 3, 3], alt_contig=[1, -1, 1], alt_negative=[0, 1, 1], alt_start=[5, 77, 4],
+                                alt_stop=[17, 84, 6])
+SAM_RECORDS_BAD = [(b"7\t0\tchr1\t10\t60\t5M\t=\t50\t60\tACGTA\tIIIII\n", A.HSQ_ERR_UNSUPPORTED),            # not paired
+                   (b"r7\t99\tchr1\t10\t60\t5M\t=\t50\t60\tACGTA\tIIIII\n", A.HSQ_ERR_BAD_CHARACTER),        # name is not a number
+                   (b"7\t99\tchr1\t10\t60\t5M\t=\t50\t60\tACGTA\tIIIII\tXA:Z:chr1,+5,3Q,0;\n", A.HSQ_ERR_MALFORMED)]  # CIGAR of a hit
+
+
+def check_sam_records(r, exp):
+    n, m = len(exp["contig"]), len(exp["alt_contig"])
+    assert r.n == n and r.n_alt == m
+    for c in r.COLUMNS:
+        assert list(getattr(r, c)[:n]) == list(exp[c]), c
+    assert list(r.alt_offsets[:n + 1]) == list(exp["alt_offsets"])
+    for c in r.ALT_COLUMNS:
+        assert list(getattr(r, c)[:m]) == list(exp[c]), c
+
+
+def sam_records_statement(text, contig_names):
+    """Second statement with str.split and re (String.split semantics: trailing empty strings dropped)."""
+    def jsplit(s, sep):
+        f = s.split(sep)
+        while f and f[-1] == "":
+            f.pop()
+        return f
+    exp = defaultdict(list)
+    exp["alt_offsets"].append(0)
+    cid = {c: i for i, c in enumerate(contig_names)}
+    k = -1
+    for raw in text.decode().split("\n"):
+        line = raw.rstrip("\r")
+        if not line or line.startswith("@"):
+            continue
+        k += 1
+        f = line.split("\t")
+        fl = int(f[1])
+        if fl & 0xC:
+            continue
+        ref = sum(int(n) for n, op in re.findall(r"(\d+)([A-Z=])", f[5]) if op in "MDN=X")
+        contig = cid.get(f[2], -1)
+        for name, v in (("sam_line", k), ("contig", contig), ("negative_strand", 1 if fl & 0x10 else 0), ("second_of_pair", 1 if fl & 0x80 else 0),
+                        ("start", int(f[3])), ("end", int(f[3]) + ref - 1), ("read_index", int(f[0]) if contig >= 0 else 0)):
+            exp[name].append(v)
+        xa = [t[5:] for t in f[11:] if t.startswith("XA:Z:")]
+        for entry in (jsplit(xa[0], ";") if xa else []):
+            g = jsplit(entry, ",")
+            if len(g) != 4 or not re.fullmatch(r"[+-]?\d+", g[1]):
+                continue
+            v = int(g[1])
+            rl = sum(int(n) for n, op in re.findall(r"(\d+)([A-Z=])", g[2]) if op in "MDN=X")
+            exp["alt_contig"].append(cid.get(g[0], -1)); exp["alt_negative"].append(1 if v < 0 else 0)
+            exp["alt_start"].append(abs(v)); exp["alt_stop"].append(abs(v) + rl - 1)
+        exp["alt_offsets"].append(len(exp["alt_contig"]))
+    return exp
+
+
+CONTIGS = ["chr%d" % c for c in range(1, 23)]
+
+
+def test_oracle_sam_mapped_records():
+    check_sam_records(O.sam_mapped_records(SAM_RECORDS_KAT, ["chr1", "chr2"]), SAM_RECORDS_KAT_EXPECTED)
+    check_sam_records(O.sam_mapped_records(SAM_RECORDS_KAT, ["chr1", "chr2"]), sam_records_statement(SAM_RECORDS_KAT, ["chr1", "chr2"]))
+    for text, want in SAM_RECORDS_BAD:
+        with pytest.raises(O.OracleError) as e:
+            O.sam_mapped_records(text, ["chr1"])
+        assert e.value.status == want
+    case = synth.make_ingest_case(1500, read_len=40, seed=6, trim=(3, 30, 0, 30))
+    text = synth.sam_text_of(case, xa_rate=0.4, index_names=True)
+    r = O.sam_mapped_records(text, CONTIGS)
+    check_sam_records(r, sam_records_statement(text, CONTIGS))
+    assert r.n_alt > 1000 and (r.alt_contig[:r.n_alt] == -1).sum() > 20
+
+
 # ---------------------------------------------------------------------------------------------------------------- CPU: the oracle
 def test_oracle_hand_traces():
     check_kat(O.join_names(kat_join(KAT_BY_NAME, False)), KAT_BY_NAME)
@@ -431,6 +513,43 @@ def test_gpu_sam_index_equals_oracle(ctx):
     with pytest.raises(HsqError) as e:
         ctx.index_sam(text, cap=10)
     assert e.value.status == A.HSQ_ERR_OVERFLOW
+
+
+@pytest.mark.gpu
+def test_gpu_sam_mapped_records_equals_oracle(ctx):
+    from bioinformatics_b200._lib import HsqError
+    check_sam_records(ctx.sam_mapped_records(SAM_RECORDS_KAT, ["chr1", "chr2"]), SAM_RECORDS_KAT_EXPECTED)
+    for text, want in SAM_RECORDS_BAD:
+        with pytest.raises(HsqError) as e:
+            ctx.sam_mapped_records(text, ["chr1"])
+        assert e.value.status == want
+    assert ctx.sam_mapped_records(b"", CONTIGS).n == 0 and ctx.sam_mapped_records(b"@HD\tVN:1.0\n", CONTIGS).n == 0
+    for n, kw in ((600, dict(crlf=True)), (30000, dict(xa_rate=0.3))):
+        case = synth.make_ingest_case(n, read_len=70, seed=n % 5, trim=(3, 60, 0, 60))
+        text = synth.sam_text_of(case, index_names=True, **kw)
+        got, exp = ctx.sam_mapped_records(text, CONTIGS), O.sam_mapped_records(text, CONTIGS)
+        assert got.n == exp.n and got.n_alt == exp.n_alt and got.n_alt > 20
+        for c in got.COLUMNS:
+            assert (getattr(got, c)[:got.n] == getattr(exp, c)[:exp.n]).all(), c
+        assert (got.alt_offsets[:got.n + 1] == exp.alt_offsets[:exp.n + 1]).all()
+        for c in got.ALT_COLUMNS:
+            assert (getattr(got, c)[:got.n_alt] == getattr(exp, c)[:exp.n_alt]).all(), c
+    with pytest.raises(HsqError) as e:
+        ctx.sam_mapped_records(text, CONTIGS, cap=100)
+    assert e.value.status == A.HSQ_ERR_OVERFLOW
+    with pytest.raises(HsqError) as e:
+        ctx.sam_mapped_records(text, CONTIGS, alt_cap=3)
+    assert e.value.status == A.HSQ_ERR_OVERFLOW
+    # straight into the read -> probe assignment: the records built on the device give the assignment the oracle's records give
+    from bioinformatics_b200.batches import ProbeRangesHost
+    rng = np.random.default_rng(3)
+    starts = rng.integers(1, 40_000_000, size=4000)
+    ranges = ProbeRangesHost(rng.integers(0, 22, size=4000), rng.integers(0, 2, size=4000), starts, starts + 2_000_000)
+    ctx.set_probe_ranges(ranges)
+    a, b = ctx.assign_probes(got.records(), 8), O.assign_probes(ranges, exp.records(), 8)
+    for f in ("n_probes", "probes", "mate", "n_common", "common", "overflow"):
+        assert (getattr(a, f) == getattr(b, f)).all(), f
+    assert (a.n_probes > 0).sum() > 1000
 
 
 class OraclePort:
