@@ -352,6 +352,18 @@ def next_row_numbers(ctx, probes, pairs, res):
                     "ms_device_incl_copies": ms_dev, "text_bytes": len(text), "records": int(g.n), "cpu_port_records_per_s": c.n / dt_cpu,
                     "cpu_sample": "the same text, 1 thread", "equals_cpu_port": bool(same),
                     "algorithmic_bytes_per_record": len(text) / max(g.n, 1) + (36 if key == "index_fastq" else 108)}
+    contigs = ["chr%d" % c for c in range(1, 23)]
+    merged_text = pinned_text(synth.sam_text_of(case, seed=32, index_names=True))  # the merged BAM's records: names are FASTQ ordinals
+    dt, g = timed(lambda: ctx.sam_mapped_records(merged_text, contigs))
+    ms_dev = ctx.last_timing()[0]
+    t0 = time.perf_counter()
+    c = O.sam_mapped_records(merged_text, contigs)
+    dt_cpu = time.perf_counter() - t0
+    same = g.n == c.n and g.n_alt == c.n_alt and all(np.array_equal(getattr(g, f)[:g.n], getattr(c, f)[:c.n]) for f in g.COLUMNS) and \
+        all(np.array_equal(getattr(g, f)[:g.n_alt], getattr(c, f)[:c.n_alt]) for f in g.ALT_COLUMNS)
+    ing["sam_mapped_records"] = {"records_per_s": g.n / dt, "text_gb_per_s_host_to_host": len(merged_text) / dt / 1e9, "ms_host_to_host": dt * 1e3,
+                                 "ms_device_incl_copies": ms_dev, "records": int(g.n), "alternative_hits": int(g.n_alt),
+                                 "cpu_port_records_per_s": c.n / dt_cpu, "cpu_sample": "the same text, 1 thread", "equals_cpu_port": bool(same)}
     for f in ("sam_names", "fq1_headers", "fq2_headers"):  # name bytes from pinned memory
         b = getattr(join, f)
         setattr(join, f, A.SeqBatch(pinned_text(b.data.tobytes()), b.offsets))

@@ -96,6 +96,7 @@ public final class HsqB200 implements AutoCloseable {
             ADDRESS, JAVA_LONG));
     private static final MethodHandle INDEX_FASTQ = fn("hsq_index_fastq", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
     private static final MethodHandle INDEX_SAM = fn("hsq_index_sam", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
+    private static final MethodHandle SAM_MAPPED_RECORDS = fn("hsq_sam_mapped_records", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS));
     private static final MethodHandle JOIN_NAMES = fn("hsq_join_names", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle GATHER_ROWS = fn("hsq_gather_rows", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS,
             ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG));
@@ -193,6 +194,12 @@ public final class HsqB200 implements AutoCloseable {
 
     /** Column index of SAM text (QNAME, FLAG, RNAME, POS, CIGAR reference length, SEQ, QUAL, XA); samIndex = hsq_sam_index. */
     public void indexSam(MemorySegment text, long nBytes, MemorySegment samIndex) { check(invokeInt(INDEX_SAM, ctx, text, nBytes, samIndex)); }
+
+    /** SAM text -> the columns of hsq_mapped_records + the XA hits (…Identification.java:439-474, SAMRecordUtil.java:440-468);
+     *  contigNames = hsq_seqs in the numbering of setProbeRanges, samRecordsOut = hsq_sam_records_out. */
+    public void samMappedRecords(MemorySegment text, long nBytes, MemorySegment contigNames, MemorySegment samRecordsOut) {
+        check(invokeInt(SAM_MAPPED_RECORDS, ctx, text, nBytes, contigNames, samRecordsOut));
+    }
 
     /** Both sorts and the merge loop of FastqAndBamFileMerger.createBamFileWithDataFromRawFastqFiles (FastqAndBamFileMerger.java:107-158,
      *  213-345); nameJoin = hsq_name_join, nameJoinOut = hsq_name_join_out.  The status codes map back to the exceptions of the loop:
