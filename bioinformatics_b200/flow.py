@@ -118,3 +118,24 @@ def ingest_flow(be, fq1_text, fq2_text, sam_text, trim=(0, 0, 0, 0), three_prime
         out["seq_" + key] = be.gather_rows(text, ix.seq_off[rows], ix.seq_len[rows])
         out["qual_" + key] = be.gather_rows(text, ix.qual_off[rows], ix.qual_len[rows])
     return out
+
+
+def fastq_pair_table(be, fq1_text, fq2_text):
+    """The raw reads of both FASTQ files as the pair batch dedup_flow indexes by read index (pair k = FASTQ ordinal k)."""
+    i1, i2 = be.index_fastq(fq1_text), be.index_fastq(fq2_text)
+    n = min(i1.n, i2.n)
+    rows = lambda t, off, ln: be.gather_rows(t, off[:n], ln[:n])
+    return PairBatchHost(np.zeros(n, dtype=np.int32), rows(fq1_text, i1.seq_off, i1.seq_len), rows(fq2_text, i2.seq_off, i2.seq_len),
+                         rows(fq1_text, i1.qual_off, i1.qual_len), rows(fq2_text, i2.qual_off, i2.qual_len), np.arange(n, dtype=np.int32))
+
+
+def dedup_from_files(be, fq1_text, fq2_text, sam_text, contig_names, ext_uid_len, lig_uid_len, write_merged, **kw):
+    """`HSQutils dedup` from its three input files to the output record fields: ingest_flow (merge the raw FASTQ data into the
+    mapper's records, …Identification.java:150-160), the caller's writer (`write_merged(sam_text, merged) -> merged SAM text`, the
+    htsjdk side: records renamed to their FASTQ ordinal), hsq_sam_mapped_records, then dedup_flow."""
+    merged = ingest_flow(be, fq1_text, fq2_text, sam_text, trimming_skipped=True)
+    merged_text = write_merged(sam_text, merged)
+    records = be.sam_mapped_records(merged_text, contig_names).records()
+    out = dedup_flow(be, records, fastq_pair_table(be, fq1_text, fq2_text), ext_uid_len, lig_uid_len, **kw)
+    out["merged"], out["mapped_records"] = merged, records
+    return out

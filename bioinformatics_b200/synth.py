@@ -342,3 +342,42 @@ def sam_text_of(case, seed=3, n_contigs=22, xa_rate=0.05, crlf=False, final_newl
                                 str(int(pos[k]) + 100), str(int(rng.integers(-400, 400))), seq, qual] + tags))
     t = eol.join(lines) + (eol if final_newline else "")
     return t.encode()
+
+
+def dedup_input_files(probes, fastq, records, seed=11):
+    """The three inputs of `HSQutils dedup` as text for a synthetic run: FASTQ one / two (ordinal k = pair k of `fastq`) and the
+    mapper's SAM text for `records` (make_mapped_records), read names = Illumina-style ids instead of ordinals, unsorted.
+    Returns (fq1_text, fq2_text, sam_text, contig_names) with contig_names in the numbering of the probe ranges."""
+    rng = np.random.default_rng(seed)
+    n = fastq.n
+    xy = rng.choice(90_000_000, size=n, replace=False)
+    ids = ["M01077:35:000000000-A3J96:1:%d:%d:%d" % (1101 + v % 16, v // 10000, v % 10000) for v in xy.tolist()]
+
+    def fq_text(reads, quals, tag):
+        parts = []
+        for k in range(n):
+            parts += [b"@", ids[k].encode(), tag, b"\n", reads.data[reads.offsets[k]:reads.offsets[k + 1]].tobytes(), b"\n+\n",
+                      quals.data[quals.offsets[k]:quals.offsets[k + 1]].tobytes(), b"\n"]
+        return b"".join(parts)
+
+    fq1, fq2 = fq_text(fastq.r1, fastq.q1, b" 1:N:0:1"), fq_text(fastq.r2, fastq.q2, b" 2:N:0:1")
+    contigs = sorted(set(probes.chromosomes), key=lambda c: int(c[3:]))
+    cname = lambda c: contigs[c] if c >= 0 else "chrUn_random"
+    lines = ["@HD\tVN:1.5\tSO:unsorted"] + ["@SQ\tSN:%s\tLN:250000000" % c for c in contigs + ["chrUn_random"]]
+    ao = records.alt_offsets
+    for r in range(records.n):
+        k = int(records.read_index[r])
+        second = bool(records.second_of_pair[r])
+        flag = 0x1 | 0x2 | (0x10 if records.negative_strand[r] else 0x20) | (0x80 if second else 0x40)
+        reads, quals = (fastq.r2, fastq.q2) if second else (fastq.r1, fastq.q1)
+        seq = reads.data[reads.offsets[k]:reads.offsets[k + 1]].tobytes().decode()
+        qual = quals.data[quals.offsets[k]:quals.offsets[k + 1]].tobytes().decode()
+        span = int(records.end[r]) - int(records.start[r]) + 1
+        tags = ["NM:i:0"]
+        if ao is not None and ao[r + 1] > ao[r]:
+            tags.append("XA:Z:" + "".join("%s,%s%d,%dM,0;" % (cname(int(records.alt_contig[a])), "-" if records.alt_negative[a] else "+",
+                                                            int(records.alt_start[a]), int(records.alt_stop[a]) - int(records.alt_start[a]) + 1)
+                                          for a in range(int(ao[r]), int(ao[r + 1]))))
+        lines.append("\t".join([ids[k], str(flag), cname(int(records.contig[r])), str(int(records.start[r])), "60", "%dM" % span, "=",
+                                str(int(records.start[r])), "0", seq, qual] + tags))
+    return fq1, fq2, ("\n".join(lines) + "\n").encode(), contigs

@@ -613,3 +613,78 @@ def test_gpu_files_to_merged_records(ctx):
     with pytest.raises(HsqError) as e:  # the BAM was made from untrimmed reads but the caller says trimmed
         flow.ingest_flow(ctx, t1, t2, ts, trim=(9, 50, 0, 50))
     assert e.value.status == A.HSQ_ERR_NOT_TRIMMED
+
+
+def write_merged(sam_text, merged):
+    """The writer of createBamFileWithDataFromRawFastqFiles, as text: header kept, the returned records in the iterator's order, QNAME
+    replaced by the FASTQ ordinal (storeFastqInfoInRecord, FastqAndBamFileMerger.java:386-396; SEQ / QUAL already equal the raw reads here)."""
+    lines = sam_text.decode().split("\n")
+    header = [x for x in lines if x.startswith("@")]
+    body = [x for x in lines if x and not x.startswith("@")]
+    out = list(header)
+    for line, idx in zip(merged["sam_line"], merged["read_index"]):
+        f = body[int(line)].split("\t")
+        f[0] = str(int(idx))
+        out.append("\t".join(f))
+    return ("\n".join(out) + "\n").encode()
+
+
+def _files_problem(repeat_names):
+    from tests.test_flow import U, V
+    probes = synth.make_probes(50, seed=4)
+    fastq = synth.make_pairs(probes, 2500, read_len=150, ext_uid_len=U, lig_uid_len=V, seed=5, sub_rate=0.01, n_rate=0.01)
+    ranges, records = synth.make_mapped_records(probes, fastq, seed=6, repeat_names=repeat_names)
+    return probes, fastq, ranges, records, synth.dedup_input_files(probes, fastq, records)
+
+
+def _same_flow_outputs(a, b):
+    from tests import helpers as H
+    assert (a["merged"]["sam_line"] == b["merged"]["sam_line"]).all() and (a["merged"]["read_index"] == b["merged"]["read_index"]).all()
+    for f in ("contig", "negative_strand", "second_of_pair", "start", "end", "read_index", "alt_offsets", "alt_contig", "alt_negative", "alt_start", "alt_stop"):
+        assert (getattr(a["mapped_records"], f) == getattr(b["mapped_records"], f)).all(), f
+    assert (a["pairs"].probe_id == b["pairs"].probe_id).all() and (a["pairs"].read_index == b["pairs"].read_index).all()
+    assert (a["dedup"].is_best == b["dedup"].is_best).all() and (a["dedup"].group_size == b["dedup"].group_size).all()
+    for f in H.EXTEND_FIELDS:
+        assert (getattr(a["extend"], f) == getattr(b["extend"], f)).all(), f
+    assert a["extend"].cigars() == b["extend"].cigars() and a["extend"].mds() == b["extend"].mds()
+    ra, rb = a["records"], b["records"]
+    assert (ra.flag == rb.flag).all() and (ra.mate_pos == rb.mate_pos).all() and (ra.offsets == rb.offsets).all()
+    assert (ra.seq[:ra.offsets[-1]] == rb.seq[:rb.offsets[-1]]).all() and (ra.qual[:ra.offsets[-1]] == rb.qual[:rb.offsets[-1]]).all()
+
+
+def test_dedup_from_files_on_oracle_equals_dedup_from_tables():
+    """Files -> merge -> mapped records -> dedup gives what dedup_flow gives on the tables the files were written from."""
+    from bioinformatics_b200 import flow
+    from tests.test_flow import OracleBackend, U, V
+    probes, fastq, ranges, records, (fq1, fq2, sam, contigs) = _files_problem(repeat_names=0)
+
+    class Backend(OracleBackend, OraclePort):
+        sam_mapped_records = staticmethod(O.sam_mapped_records)
+
+    be = Backend(probes, ranges)
+    out = flow.dedup_from_files(be, fq1, fq2, sam, contigs, U, V, write_merged)
+    direct = flow.dedup_flow(be, records, fastq, U, V)
+    assert out["mapped_records"].n == records.n and len(out["merged"]["sam_line"]) == records.n
+    key = lambda o: sorted(zip(o["pairs"].read_index.tolist(), o["pairs"].probe_id.tolist(), o["dedup"].is_best.tolist()))
+    assert key(out) == key(direct) and out["records"].n == direct["records"].n > 300
+    pos = lambda o: sorted(zip(o["extended_pairs"].read_index.tolist(), o["extend"].pos[0::2].tolist(), o["extend"].cigars()[0::2]))
+    assert pos(out) == pos(direct)
+
+
+@pytest.mark.gpu
+def test_gpu_dedup_from_files_equals_oracle(ctx):
+    """The whole dedup data path from the three input files on the device against the same flow over the oracle (names that sit on
+    four records included: the merge keeps three of them, FastqAndBamFileMerger.java:304-309)."""
+    from bioinformatics_b200 import flow
+    from tests.test_flow import OracleBackend, U, V
+    probes, fastq, ranges, records, (fq1, fq2, sam, contigs) = _files_problem(repeat_names=3)
+
+    class Backend(OracleBackend, OraclePort):
+        sam_mapped_records = staticmethod(O.sam_mapped_records)
+
+    ctx.set_probes(probes)
+    ctx.set_probe_ranges(ranges)
+    got = flow.dedup_from_files(ctx, fq1, fq2, sam, contigs, U, V, write_merged)
+    exp = flow.dedup_from_files(Backend(probes, ranges), fq1, fq2, sam, contigs, U, V, write_merged)
+    _same_flow_outputs(got, exp)
+    assert len(got["merged"]["sam_line"]) == records.n - 3 and got["records"].n > 300
