@@ -156,6 +156,8 @@ int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) {
     HSQ_CUDA(nullptr, cudaMemcpyToSymbol(c_pow95, tbl.data(), sizeof(double) * POW95_N));
     const char* f32 = getenv("HSQ_FORCE_DP32");  // development / test switch: always use the 32-bit DP kernels
     ctx->force_dp32 = f32 && f32[0] == '1';
+    const char* fdc = getenv("HSQ_DEDUP_CUB");
+    ctx->force_dedup_cub = fdc && fdc[0] == '1';
     *out = ctx;
     return HSQ_OK;
 }
@@ -171,6 +173,7 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
                            &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32, &ctx->fi_start, &ctx->fi_len, &ctx->fi_refs, &ctx->fi_size};
     for (auto* b : bufs) b->release();
     for (auto& b : ctx->ing) b.release();
+    ctx->dd_seg.release();
     hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb, &ctx->alt_r1, &ctx->alt_r2, &ctx->fs};
     for (auto* s : seqs) s->release();
     for (auto& ps : ctx->parked) {

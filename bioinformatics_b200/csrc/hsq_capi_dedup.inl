@@ -7,6 +7,7 @@
 // (so each group is contiguous with its best pair first) -> head flags -> per-group sizes and per-probe counters.
 // Round 1 uses cub::DeviceRadixSort for the sort passes; the surrounding kernels are hand-written.
 #include <cub/device/device_radix_sort.cuh>
+#include "hsq_scan.cuh"
 namespace hsq {
 
 __global__ void dedup_keygen_kernel(const uint8_t* __restrict__ r1, const int64_t* __restrict__ off1, const uint8_t* __restrict__ q1,
@@ -94,6 +95,135 @@ __global__ void dedup_groups_kernel(const uint32_t* __restrict__ idx, const int3
     }
 }
 
+// ---- segment path: counting sort by probe, then one block per probe sorts its pairs by (UID, rank, pair) in shared memory and
+// reduces them in the same kernel (heads = best pairs, group sizes, the probe's counters).  Keys are read once and never move in
+// global memory; the cub path below stays for batches in which one probe holds more pairs than a block can sort.
+static constexpr int DEDUP_SEG_BLOCK = 256;     // = SCAN_BLOCK: block_exclusive_scan is used inside
+static constexpr int DEDUP_SEG_MAX = 8192;      // pairs per probe the segment kernel takes (28 B of shared memory each)
+
+__global__ void dedup_probe_hist_kernel(const int32_t* __restrict__ probe, int64_t n, int32_t* __restrict__ cnt) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int lane = threadIdx.x & 31;
+    for (; i < n; i += stride) {
+        const int p = probe[i];
+        const unsigned peers = __match_any_sync(__activemask(), p);  // one atomic per distinct probe in the warp
+        if (lane == __ffs(peers) - 1) atomicAdd(&cnt[p], __popc(peers));
+    }
+}
+
+__global__ void dedup_seg_prepare_kernel(const int32_t* __restrict__ cnt, int64_t np, int64_t* __restrict__ cnt64, int* __restrict__ max_count) {
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int mx = 0;
+    for (; p < np; p += stride) {
+        cnt64[p] = cnt[p];
+        mx = max(mx, cnt[p]);
+    }
+    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((threadIdx.x & 31) == 0 && mx > 0) atomicMax(max_count, mx);
+}
+
+__global__ void dedup_scatter_kernel(const int32_t* __restrict__ probe, int64_t n, const int64_t* __restrict__ start, int32_t* __restrict__ cursor,
+                                     uint32_t* __restrict__ seg) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int lane = threadIdx.x & 31;
+    for (; i < n; i += stride) {
+        const int p = probe[i];
+        const unsigned peers = __match_any_sync(__activemask(), p);
+        const int leader = __ffs(peers) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(&cursor[p], __popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        seg[start[p] + base + __popc(peers & ((1u << lane) - 1u))] = (uint32_t)i;  // order inside a segment is settled by the sort
+    }
+}
+
+__global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_segment_kernel(const uint32_t* __restrict__ seg, const int64_t* __restrict__ start, int64_t np, int cap,
+                                                                        const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank,
+                                                                        uint8_t* __restrict__ is_best, int32_t* __restrict__ group_size,
+                                                                        int32_t* __restrict__ unique_pairs, int32_t* __restrict__ duplicate_pairs,
+                                                                        int32_t* __restrict__ max_pairs) {
+    extern __shared__ __align__(16) unsigned char dedup_smem[];
+    uint64_t* s_uid = reinterpret_cast<uint64_t*>(dedup_smem);
+    uint64_t* s_rank = s_uid + cap;
+    uint32_t* s_idx = reinterpret_cast<uint32_t*>(s_rank + cap);
+    int32_t* s_gid = reinterpret_cast<int32_t*>(s_idx + cap);
+    int32_t* s_hp = s_gid + cap;  // cap + 1 entries
+    __shared__ int s_max;
+    const int tid = threadIdx.x;
+    for (int64_t p = blockIdx.x; p < np; p += gridDim.x) {
+        const int64_t b = start[p];
+        const int m = (int)(start[p + 1] - b);
+        if (m == 0) continue;  // block-uniform
+        int pm = 1;
+        while (pm < m) pm <<= 1;
+        for (int j = tid; j < pm; j += DEDUP_SEG_BLOCK) {
+            if (j < m) {
+                const uint32_t i = seg[b + j];
+                s_uid[j] = uid[i];
+                s_rank[j] = rank[i];
+                s_idx[j] = i;
+            } else {  // padding sorts behind every pair
+                s_uid[j] = ~0ull;
+                s_rank[j] = ~0ull;
+                s_idx[j] = ~0u;
+            }
+        }
+        if (tid == 0) s_max = 0;
+        __syncthreads();
+        for (int k = 2; k <= pm; k <<= 1) {  // bitonic network on (UID, rank, pair index)
+            for (int j = k >> 1; j > 0; j >>= 1) {
+                for (int t = tid; t < (pm >> 1); t += DEDUP_SEG_BLOCK) {
+                    const int a = ((t / j) * 2 * j) + (t % j), c = a + j;
+                    const uint64_t ua = s_uid[a], uc = s_uid[c], ra = s_rank[a], rc = s_rank[c];
+                    const uint32_t ia = s_idx[a], ic = s_idx[c];
+                    const bool greater = ua != uc ? ua > uc : (ra != rc ? ra > rc : ia > ic);
+                    if (greater == ((a & k) == 0)) {
+                        s_uid[a] = uc; s_uid[c] = ua;
+                        s_rank[a] = rc; s_rank[c] = ra;
+                        s_idx[a] = ic; s_idx[c] = ia;
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        // group ids: a head opens a (probe, UID) group and is its best pair (smallest rank, then smallest pair index)
+        const int per = (pm + DEDUP_SEG_BLOCK - 1) / DEDUP_SEG_BLOCK;
+        const int lo = tid * per, hi = min(lo + per, m);
+        int heads = 0;
+        for (int j = lo; j < hi; j++) heads += (j == 0 || s_uid[j] != s_uid[j - 1]) ? 1 : 0;
+        int64_t total;
+        int g = (int)block_exclusive_scan((int64_t)heads, &total);
+        for (int j = lo; j < hi; j++) {
+            if (j == 0 || s_uid[j] != s_uid[j - 1]) s_hp[g++] = j;
+            s_gid[j] = g - 1;
+        }
+        const int n_groups = (int)total;
+        if (tid == 0) s_hp[n_groups] = m;
+        __syncthreads();
+        int mx = 0;
+        for (int j = tid; j < m; j += DEDUP_SEG_BLOCK) {
+            const int gid = s_gid[j];
+            const int size = s_hp[gid + 1] - s_hp[gid];
+            const uint32_t i = s_idx[j];
+            is_best[i] = s_hp[gid] == j ? 1 : 0;
+            group_size[i] = size;
+            mx = max(mx, size);
+        }
+        for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        if ((tid & 31) == 0) atomicMax(&s_max, mx);
+        __syncthreads();
+        if (tid == 0) {  // FilterByUid.java:149-171,251
+            unique_pairs[p] = n_groups;
+            duplicate_pairs[p] = m - n_groups;
+            max_pairs[p] = s_max;
+        }
+        __syncthreads();
+    }
+}
+
 // key columns <-> 24-byte key records (hsq_dedup_key) for the multi-GPU exchange
 __global__ void dedup_pack_keys_kernel(const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank, const int32_t* __restrict__ probe,
                                        int64_t n, uint32_t origin_base, hsq_dedup_key* __restrict__ out) {
@@ -139,6 +269,17 @@ int sort_pass(hsq_ctx* ctx, const uint64_t* keys_in, uint64_t* keys_out, const u
     HSQ_CUDA(ctx, ctx->sort_tmp.ensure(tmp_bytes + 16));
     HSQ_CUDA(ctx, cub::DeviceRadixSort::SortPairs(ctx->sort_tmp.p, tmp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, end_bit, ctx->stream));
     ctx->launches += (end_bit + 7) / 8 + 2;  // library kernels (approximate; they are not counted as ours in bench.py)
+    return HSQ_OK;
+}
+
+// exclusive scan of in[0..n) into out[0..n] (tile sums in `tiles`)
+int scan_i64(hsq_ctx* ctx, const int64_t* in, int64_t n, int64_t* tiles, int64_t* out) {
+    const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
+    scan_tile_sums_kernel<<<(unsigned)n_tiles, SCAN_BLOCK, 0, ctx->stream>>>(in, n, tiles);
+    scan_sums_kernel<<<1, SCAN_BLOCK, 0, ctx->stream>>>(tiles, n_tiles);
+    scan_apply_kernel<<<(unsigned)n_tiles, SCAN_BLOCK, 0, ctx->stream>>>(in, n, tiles, out);
+    ctx->launches += 3;
+    HSQ_CUDA(ctx, cudaGetLastError());
     return HSQ_OK;
 }
 
@@ -197,6 +338,44 @@ int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_
     uint32_t* ib = ia + nn;
     uint8_t* head = ctx->flags.as<uint8_t>();
     if (np) HSQ_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 3 * (size_t)np * 4, ctx->stream));
+    if (n > 0 && np > 0 && !ctx->force_dedup_cub) {
+        // segment path: counting sort by probe + one block per probe (sort and reduce fused)
+        const size_t nps = (size_t)np;
+        const int64_t n_tiles = (np + 1 + SCAN_TILE - 1) / SCAN_TILE;
+        HSQ_CUDA(ctx, ctx->dd_seg.ensure(nps * 8 + (nps + 1) * 16 + (size_t)n_tiles * 8 + 64));
+        int64_t* cnt64 = ctx->dd_seg.as<int64_t>();
+        int64_t* start = cnt64 + nps + 1;
+        int64_t* tiles = start + nps + 1;
+        int32_t* cnt = reinterpret_cast<int32_t*>(tiles + n_tiles);
+        int32_t* cursor = cnt + nps;
+        HSQ_CUDA(ctx, cudaMemsetAsync(cnt, 0, nps * 8, ctx->stream));
+        int* d_max = d_status(ctx) + 8;  // a status word nothing else uses
+        const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        const int pblocks = (int)std::max<int64_t>(1, std::min<int64_t>((np + 255) / 256, (int64_t)ctx->sm_count * 8));
+        HSQ_CUDA(ctx, cudaMemsetAsync(d_max, 0, 4, ctx->stream));
+        dedup_probe_hist_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, cnt);
+        dedup_seg_prepare_kernel<<<pblocks, 256, 0, ctx->stream>>>(cnt, np, cnt64, d_max);
+        ctx->launches += 2;
+        if ((rc = scan_i64(ctx, cnt64, np, tiles, start))) return rc;
+        int w[9];
+        if ((rc = read_status(ctx, w, 9))) return rc;
+        const int max_count = w[8];
+        if (max_count <= DEDUP_SEG_MAX) {
+            int cap = 32;
+            while (cap < max_count) cap <<= 1;
+            const size_t smem = (size_t)cap * 28 + 16;
+            HSQ_CUDA(ctx, cudaFuncSetAttribute(dedup_segment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            int per_sm = 1;
+            HSQ_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dedup_segment_kernel, DEDUP_SEG_BLOCK, smem));
+            const int sblocks = (int)std::max<int64_t>(1, std::min<int64_t>(np, (int64_t)ctx->sm_count * std::max(per_sm, 1)));
+            dedup_scatter_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, start, cursor, ib);
+            dedup_segment_kernel<<<sblocks, DEDUP_SEG_BLOCK, smem, ctx->stream>>>(ib, start, np, cap, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
+            ctx->launches += 2;
+            HSQ_CUDA(ctx, cudaGetLastError());
+            return HSQ_OK;
+        }
+        // a probe with more pairs than a block sorts: the whole batch takes the radix path below
+    }
     if (n > 0) {
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
         // pass 1: by rank (48 bits) -> ib;  pass 2: by UID -> ia;  pass 3: by probe -> ib

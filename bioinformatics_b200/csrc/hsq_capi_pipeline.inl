@@ -59,17 +59,6 @@ __global__ void iota_kernel(int32_t* __restrict__ out, int64_t n) {
     for (; k < n; k += stride) out[k] = (int32_t)k;
 }
 
-// exclusive scan of in[0..n) into out[0..n] (tile sums in `tiles`)
-int scan_i64(hsq_ctx* ctx, const int64_t* in, int64_t n, int64_t* tiles, int64_t* out) {
-    const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
-    scan_tile_sums_kernel<<<(unsigned)n_tiles, SCAN_BLOCK, 0, ctx->stream>>>(in, n, tiles);
-    scan_sums_kernel<<<1, SCAN_BLOCK, 0, ctx->stream>>>(tiles, n_tiles);
-    scan_apply_kernel<<<(unsigned)n_tiles, SCAN_BLOCK, 0, ctx->stream>>>(in, n, tiles, out);
-    ctx->launches += 3;
-    HSQ_CUDA(ctx, cudaGetLastError());
-    return HSQ_OK;
-}
-
 void swap_read_buffers(hsq_ctx* ctx) {
     std::swap(ctx->r1, ctx->alt_r1);
     std::swap(ctx->r2, ctx->alt_r2);

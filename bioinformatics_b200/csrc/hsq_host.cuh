@@ -66,6 +66,8 @@ struct hsq_ctx {
     bool force_dp32 = false;
     // probe search windows sorted by (contig, strand, start) for hsq_assign_probes
     hsq::DevBuf rg_start, rg_end, rg_value, rg_off;
+    hsq::DevBuf dd_seg;         // dedup segment path: per-probe counters, offsets
+    bool force_dedup_cub = false;  // development / test switch (HSQ_DEDUP_CUB=1): always take the radix-sort path
     hsq::DevBuf dd_u8, dd_i32;  // hsq_dedup_extend_batch: dedup answers kept while the extend stage reuses the output buffers
     int64_t rg_n = -1;
     int32_t rg_contigs = 0;

@@ -188,6 +188,48 @@ def test_dedup_vs_oracle(ctx):
         assert (st.max_pairs_per_uid == est.max_pairs_per_uid).all()
 
 
+def _dedup_equal(got, exp):
+    (ib, gs, st), (eb, egs, est) = got, exp
+    assert (ib == eb).all() and (gs == egs).all()
+    assert (st.unique_pairs == est.unique_pairs).all() and (st.duplicate_pairs == est.duplicate_pairs).all()
+    assert (st.max_pairs_per_uid == est.max_pairs_per_uid).all()
+
+
+def test_dedup_segment_and_radix_paths(ctx, monkeypatch):
+    """The per-probe segment path (counting sort by probe + one block sorting and reducing each probe) and the radix-sort path give
+    the oracle's answer: skewed panels, a probe larger than a block takes (whole batch falls back), probes without pairs, a sparse
+    200 k-probe table, repeated read indexes (ties go to the earlier pair)."""
+    from bioinformatics_b200._lib import Context
+    rng = np.random.default_rng(5)
+    probes = synth.make_probes(60, seed=23)
+    base, _ = synth.drop_n_pairs(synth.make_pairs(probes, 30000, read_len=100, ext_uid_len=5, lig_uid_len=1, seed=24))
+    base.q1.data[::5] = ord("5")
+    cases = []
+    skew = base.subset(np.arange(base.n))
+    skew.probe_id[:] = np.minimum(rng.geometric(0.15, size=base.n) - 1, 59)  # probe 0 holds ~4500 pairs, the tail almost none
+    cases.append(("skewed", skew, 60, 5, 1))
+    hot = base.subset(np.arange(base.n))
+    hot.probe_id[:] = np.where(rng.random(base.n) < 0.5, 7, hot.probe_id)  # ~15 k pairs on one probe: more than a block sorts
+    cases.append(("hot probe", hot, 60, 5, 1))
+    sparse = base.subset(np.arange(5000))
+    sparse.probe_id[:] = rng.integers(0, 200000, size=5000)
+    cases.append(("sparse", sparse, 200000, 5, 1))
+    ties = base.subset(np.arange(8000))
+    ties.read_index[:] = rng.integers(0, 50, size=8000)
+    ties.q1.data[:] = ord("I")
+    ties.q2.data[:] = ord("I")
+    cases.append(("ties", ties, 60, 3, 0))
+    cases.append(("no uid", base.head(3000), 60, 0, 0))
+    cases.append(("one pair", base.head(1), 60, 5, 1))
+    expected = {name: O.dedup_batch(pb, u, v, npr) for name, pb, npr, u, v in cases}
+    for name, pb, npr, u, v in cases:
+        _dedup_equal(ctx.dedup_batch(pb, u, v, npr), expected[name])
+    monkeypatch.setenv("HSQ_DEDUP_CUB", "1")
+    with Context(0) as radix:
+        for name, pb, npr, u, v in cases:
+            _dedup_equal(radix.dedup_batch(pb, u, v, npr), expected[name])
+
+
 def test_dedup_sharded_entry_points(ctx):
     """hsq_dedup_keys -> (device records) -> hsq_dedup_reduce_keys equals hsq_dedup_batch; records equal the stand-in."""
     import torch
