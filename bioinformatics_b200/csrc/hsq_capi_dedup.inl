@@ -3,9 +3,10 @@
 //   group key   = (probe, UID)                              :134-147 (one HashMap per probe task)
 //   best pair   = max (short)(sum(q1-33)+sum(q2-33)), tie -> smaller Integer.parseInt(readName)   :281-297,
 //                 HSQ/utils/BamFileUtil.java:74-85, HSQ/objects/ReadPair.java:101-103 (Java short wrap-around)
-// Device plan: key generation (HBM-bound, one warp per pair) -> stable LSD radix sorts by rank, UID, probe
-// (so each group is contiguous with its best pair first) -> head flags -> per-group sizes and per-probe counters.
-// Round 1 uses cub::DeviceRadixSort for the sort passes; the surrounding kernels are hand-written.
+// Device plan: key generation (HBM-bound, one warp per pair) -> counting sort of the pair indexes by probe -> one block per probe
+// sorts its pairs by (UID, rank, pair) in shared memory and reduces them in the same kernel (heads = best pairs, group sizes,
+// per-probe counters).  A batch in which one probe holds more pairs than a block can sort takes the radix path instead: stable
+// LSD radix sorts by rank, UID, probe (cub::DeviceRadixSort) -> head flags -> group walk.
 #include <cub/device/device_radix_sort.cuh>
 #include "hsq_scan.cuh"
 namespace hsq {
@@ -95,20 +96,27 @@ __global__ void dedup_groups_kernel(const uint32_t* __restrict__ idx, const int3
     }
 }
 
-// ---- segment path: counting sort by probe, then one block per probe sorts its pairs by (UID, rank, pair) in shared memory and
-// reduces them in the same kernel (heads = best pairs, group sizes, the probe's counters).  Keys are read once and never move in
-// global memory; the cub path below stays for batches in which one probe holds more pairs than a block can sort.
-static constexpr int DEDUP_SEG_BLOCK = 256;     // = SCAN_BLOCK: block_exclusive_scan is used inside
-static constexpr int DEDUP_SEG_MAX = 8192;      // pairs per probe the segment kernel takes (28 B of shared memory each)
+// ---- segment path: counting sort of the pair indexes by probe, then one block per probe groups its pairs by UID in a shared-memory
+// hash table and reduces them in the same kernel (best pair = smallest rank, then smallest pair index; group sizes; the probe's
+// counters).  No sort: FilterByUid groups with a HashMap per probe too (FilterByUid.java:134-147), and the result does not depend on
+// any order.  Keys are read from HBM once and never move; the radix path below stays for batches in which one probe holds more
+// pairs than a block's table takes.
+static constexpr int DEDUP_SEG_BLOCK = 256;
+static constexpr int DEDUP_SEG_MAX = 4096;      // pairs per probe the group kernel takes (52 B of shared memory each)
 
-__global__ void dedup_probe_hist_kernel(const int32_t* __restrict__ probe, int64_t n, int32_t* __restrict__ cnt) {
+// cnt[p] = pairs of probe p; within[i] = arrival number of pair i inside its probe (any order: the group kernel is order free)
+__global__ void dedup_probe_hist_kernel(const int32_t* __restrict__ probe, int64_t n, int32_t* __restrict__ cnt, uint32_t* __restrict__ within) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     const int lane = threadIdx.x & 31;
     for (; i < n; i += stride) {
         const int p = probe[i];
         const unsigned peers = __match_any_sync(__activemask(), p);  // one atomic per distinct probe in the warp
-        if (lane == __ffs(peers) - 1) atomicAdd(&cnt[p], __popc(peers));
+        const int leader = __ffs(peers) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(&cnt[p], __popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        within[i] = (uint32_t)(base + __popc(peers & ((1u << lane) - 1u)));
     }
 }
 
@@ -124,100 +132,96 @@ __global__ void dedup_seg_prepare_kernel(const int32_t* __restrict__ cnt, int64_
     if ((threadIdx.x & 31) == 0 && mx > 0) atomicMax(max_count, mx);
 }
 
-__global__ void dedup_scatter_kernel(const int32_t* __restrict__ probe, int64_t n, const int64_t* __restrict__ start, int32_t* __restrict__ cursor,
+__global__ void dedup_scatter_kernel(const int32_t* __restrict__ probe, int64_t n, const int64_t* __restrict__ start, const uint32_t* __restrict__ within,
                                      uint32_t* __restrict__ seg) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
-    const int lane = threadIdx.x & 31;
-    for (; i < n; i += stride) {
-        const int p = probe[i];
-        const unsigned peers = __match_any_sync(__activemask(), p);
-        const int leader = __ffs(peers) - 1;
-        int base = 0;
-        if (lane == leader) base = atomicAdd(&cursor[p], __popc(peers));
-        base = __shfl_sync(peers, base, leader);
-        seg[start[p] + base + __popc(peers & ((1u << lane) - 1u))] = (uint32_t)i;  // order inside a segment is settled by the sort
-    }
+    for (; i < n; i += stride) seg[start[probe[i]] + within[i]] = (uint32_t)i;
 }
 
-__global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_segment_kernel(const uint32_t* __restrict__ seg, const int64_t* __restrict__ start, int64_t np, int cap,
-                                                                        const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank,
-                                                                        uint8_t* __restrict__ is_best, int32_t* __restrict__ group_size,
-                                                                        int32_t* __restrict__ unique_pairs, int32_t* __restrict__ duplicate_pairs,
-                                                                        int32_t* __restrict__ max_pairs) {
+__global__ void dedup_iota_kernel(uint32_t* __restrict__ out, int64_t n) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) out[i] = (uint32_t)i;
+}
+
+__global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_kernel(const uint32_t* __restrict__ seg, const int64_t* __restrict__ start, int64_t np, int cap,
+                                                                      const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank,
+                                                                      uint8_t* __restrict__ is_best, int32_t* __restrict__ group_size,
+                                                                      int32_t* __restrict__ unique_pairs, int32_t* __restrict__ duplicate_pairs,
+                                                                      int32_t* __restrict__ max_pairs) {
     extern __shared__ __align__(16) unsigned char dedup_smem[];
+    // per pair: its UID and its table slot; per table slot (2 x cap of them): claiming pair + 1, best rank, best pair, pairs
     uint64_t* s_uid = reinterpret_cast<uint64_t*>(dedup_smem);
-    uint64_t* s_rank = s_uid + cap;
-    uint32_t* s_idx = reinterpret_cast<uint32_t*>(s_rank + cap);
-    int32_t* s_gid = reinterpret_cast<int32_t*>(s_idx + cap);
-    int32_t* s_hp = s_gid + cap;  // cap + 1 entries
-    __shared__ int s_max;
+    unsigned long long* t_best = reinterpret_cast<unsigned long long*>(s_uid + cap);
+    int* s_slot = reinterpret_cast<int*>(t_best + 2 * cap);
+    int* t_tag = s_slot + cap;
+    unsigned* t_bidx = reinterpret_cast<unsigned*>(t_tag + 2 * cap);
+    int* t_cnt = reinterpret_cast<int*>(t_bidx + 2 * cap);
+    __shared__ int s_groups, s_max;
     const int tid = threadIdx.x;
     for (int64_t p = blockIdx.x; p < np; p += gridDim.x) {
         const int64_t b = start[p];
         const int m = (int)(start[p + 1] - b);
         if (m == 0) continue;  // block-uniform
-        int pm = 1;
-        while (pm < m) pm <<= 1;
-        for (int j = tid; j < pm; j += DEDUP_SEG_BLOCK) {
-            if (j < m) {
-                const uint32_t i = seg[b + j];
-                s_uid[j] = uid[i];
-                s_rank[j] = rank[i];
-                s_idx[j] = i;
-            } else {  // padding sorts behind every pair
-                s_uid[j] = ~0ull;
-                s_rank[j] = ~0ull;
-                s_idx[j] = ~0u;
-            }
+        int table = 64;
+        while (table < 2 * m) table <<= 1;
+        const unsigned mask = (unsigned)table - 1u;
+        for (int h = tid; h < table; h += DEDUP_SEG_BLOCK) {
+            t_tag[h] = 0;
+            t_best[h] = ~0ull;
+            t_bidx[h] = ~0u;
+            t_cnt[h] = 0;
         }
-        if (tid == 0) s_max = 0;
+        for (int j = tid; j < m; j += DEDUP_SEG_BLOCK) s_uid[j] = uid[seg[b + j]];
+        if (tid == 0) { s_groups = 0; s_max = 0; }
         __syncthreads();
-        for (int k = 2; k <= pm; k <<= 1) {  // bitonic network on (UID, rank, pair index)
-            for (int j = k >> 1; j > 0; j >>= 1) {
-                for (int t = tid; t < (pm >> 1); t += DEDUP_SEG_BLOCK) {
-                    const int a = ((t / j) * 2 * j) + (t % j), c = a + j;
-                    const uint64_t ua = s_uid[a], uc = s_uid[c], ra = s_rank[a], rc = s_rank[c];
-                    const uint32_t ia = s_idx[a], ic = s_idx[c];
-                    const bool greater = ua != uc ? ua > uc : (ra != rc ? ra > rc : ia > ic);
-                    if (greater == ((a & k) == 0)) {
-                        s_uid[a] = uc; s_uid[c] = ua;
-                        s_rank[a] = rc; s_rank[c] = ra;
-                        s_idx[a] = ic; s_idx[c] = ia;
-                    }
+        int claimed = 0;
+        for (int j = tid; j < m; j += DEDUP_SEG_BLOCK) {  // find or claim the slot of this pair's UID
+            const uint64_t u = s_uid[j];
+            unsigned h = (unsigned)((u ^ (u >> 29)) * 0x9E3779B97F4A7C15ull >> 40) & mask;
+            int slot;
+            while (true) {
+                int tag = t_tag[h];
+                if (tag == 0) {
+                    tag = atomicCAS(&t_tag[h], 0, j + 1);
+                    if (tag == 0) { slot = (int)h; claimed++; break; }
                 }
-                __syncthreads();
+                if (s_uid[tag - 1] == u) { slot = (int)h; break; }
+                h = (h + 1u) & mask;
             }
+            s_slot[j] = slot;
+            atomicMin(&t_best[slot], (unsigned long long)rank[seg[b + j]]);
+            atomicAdd(&t_cnt[slot], 1);
         }
-        // group ids: a head opens a (probe, UID) group and is its best pair (smallest rank, then smallest pair index)
-        const int per = (pm + DEDUP_SEG_BLOCK - 1) / DEDUP_SEG_BLOCK;
-        const int lo = tid * per, hi = min(lo + per, m);
-        int heads = 0;
-        for (int j = lo; j < hi; j++) heads += (j == 0 || s_uid[j] != s_uid[j - 1]) ? 1 : 0;
-        int64_t total;
-        int g = (int)block_exclusive_scan((int64_t)heads, &total);
-        for (int j = lo; j < hi; j++) {
-            if (j == 0 || s_uid[j] != s_uid[j - 1]) s_hp[g++] = j;
-            s_gid[j] = g - 1;
+        __syncthreads();
+        for (int j = tid; j < m; j += DEDUP_SEG_BLOCK) {  // among the pairs with the best rank the earliest pair wins
+            const uint32_t i = seg[b + j];
+            const int slot = s_slot[j];
+            if ((unsigned long long)rank[i] == t_best[slot]) atomicMin(&t_bidx[slot], i);
         }
-        const int n_groups = (int)total;
-        if (tid == 0) s_hp[n_groups] = m;
         __syncthreads();
         int mx = 0;
         for (int j = tid; j < m; j += DEDUP_SEG_BLOCK) {
-            const int gid = s_gid[j];
-            const int size = s_hp[gid + 1] - s_hp[gid];
-            const uint32_t i = s_idx[j];
-            is_best[i] = s_hp[gid] == j ? 1 : 0;
+            const uint32_t i = seg[b + j];
+            const int slot = s_slot[j];
+            const int size = t_cnt[slot];
+            is_best[i] = t_bidx[slot] == i ? 1 : 0;
             group_size[i] = size;
             mx = max(mx, size);
         }
-        for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-        if ((tid & 31) == 0) atomicMax(&s_max, mx);
+        for (int o = 16; o > 0; o >>= 1) {
+            mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            claimed += __shfl_xor_sync(0xffffffffu, claimed, o);
+        }
+        if ((tid & 31) == 0) {
+            atomicMax(&s_max, mx);
+            atomicAdd(&s_groups, claimed);
+        }
         __syncthreads();
         if (tid == 0) {  // FilterByUid.java:149-171,251
-            unique_pairs[p] = n_groups;
-            duplicate_pairs[p] = m - n_groups;
+            unique_pairs[p] = s_groups;
+            duplicate_pairs[p] = m - s_groups;
             max_pairs[p] = s_max;
         }
         __syncthreads();
@@ -339,7 +343,7 @@ int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_
     uint8_t* head = ctx->flags.as<uint8_t>();
     if (np) HSQ_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 3 * (size_t)np * 4, ctx->stream));
     if (n > 0 && np > 0 && !ctx->force_dedup_cub) {
-        // segment path: counting sort by probe + one block per probe (sort and reduce fused)
+        // segment path: counting sort by probe + one block per probe (hash group-by and reduce fused)
         const size_t nps = (size_t)np;
         const int64_t n_tiles = (np + 1 + SCAN_TILE - 1) / SCAN_TILE;
         HSQ_CUDA(ctx, ctx->dd_seg.ensure(nps * 8 + (nps + 1) * 16 + (size_t)n_tiles * 8 + 64));
@@ -353,7 +357,7 @@ int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
         const int pblocks = (int)std::max<int64_t>(1, std::min<int64_t>((np + 255) / 256, (int64_t)ctx->sm_count * 8));
         HSQ_CUDA(ctx, cudaMemsetAsync(d_max, 0, 4, ctx->stream));
-        dedup_probe_hist_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, cnt);
+        dedup_probe_hist_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, cnt, ia);  // ia: arrival numbers from here on
         dedup_seg_prepare_kernel<<<pblocks, 256, 0, ctx->stream>>>(cnt, np, cnt64, d_max);
         ctx->launches += 2;
         if ((rc = scan_i64(ctx, cnt64, np, tiles, start))) return rc;
@@ -363,18 +367,20 @@ int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_
         if (max_count <= DEDUP_SEG_MAX) {
             int cap = 32;
             while (cap < max_count) cap <<= 1;
-            const size_t smem = (size_t)cap * 28 + 16;
-            HSQ_CUDA(ctx, cudaFuncSetAttribute(dedup_segment_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            const size_t smem = (size_t)cap * 52 + 16;
+            HSQ_CUDA(ctx, cudaFuncSetAttribute(dedup_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int per_sm = 1;
-            HSQ_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dedup_segment_kernel, DEDUP_SEG_BLOCK, smem));
+            HSQ_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dedup_group_kernel, DEDUP_SEG_BLOCK, smem));
             const int sblocks = (int)std::max<int64_t>(1, std::min<int64_t>(np, (int64_t)ctx->sm_count * std::max(per_sm, 1)));
-            dedup_scatter_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, start, cursor, ib);
-            dedup_segment_kernel<<<sblocks, DEDUP_SEG_BLOCK, smem, ctx->stream>>>(ib, start, np, cap, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
+            dedup_scatter_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, start, ia, ib);
+            dedup_group_kernel<<<sblocks, DEDUP_SEG_BLOCK, smem, ctx->stream>>>(ib, start, np, cap, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
             ctx->launches += 2;
             HSQ_CUDA(ctx, cudaGetLastError());
             return HSQ_OK;
         }
-        // a probe with more pairs than a block sorts: the whole batch takes the radix path below
+        dedup_iota_kernel<<<gblocks, 256, 0, ctx->stream>>>(ia, n);  // the radix path wants the pair indexes back in ia
+        ctx->launches++;
+        // a probe with more pairs than a block's table takes: the whole batch goes down the radix path below
     }
     if (n > 0) {
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
