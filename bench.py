@@ -357,6 +357,18 @@ def next_row_numbers(ctx, probes, pairs, res):
                     "ms_device_incl_copies": ms_dev, "text_bytes": len(text), "records": int(g.n), "cpu_port_records_per_s": c.n / dt_cpu,
                     "cpu_sample": "the same text, 1 thread", "equals_cpu_port": bool(same),
                     "algorithmic_bytes_per_record": len(text) / max(g.n, 1) + (36 if key == "index_fastq" else 108)}
+    # config 1 file to file: FastqReadTrimmer.trimReads on FASTQ text (both buffers pinned)
+    ptext = pinned_text(case["fq1_text"])
+    pout = ctx.pinned_array(len(ptext))
+    dt, (g, nrec) = timed(lambda: ctx.trim_fastq(ptext, 32, 127, True, out=pout))
+    ms_dev = ctx.last_timing()[0]
+    t0 = time.perf_counter()
+    c, _ = O.trim_fastq(ptext, 32, 127, True)
+    dt_cpu = time.perf_counter() - t0
+    ing["trim_fastq"] = {"records_per_s": nrec / dt, "text_gb_per_s_host_to_host": len(ptext) / dt / 1e9, "ms_host_to_host": dt * 1e3,
+                         "ms_device_incl_copies": ms_dev, "text_bytes_in": len(ptext), "text_bytes_out": int(len(g)), "records": int(nrec),
+                         "cpu_port_records_per_s": nrec / dt_cpu, "cpu_sample": "the same text, 1 thread", "equals_cpu_port": bool(np.array_equal(g, c)),
+                         "algorithmic_bytes_per_record": (len(ptext) + len(g)) / max(nrec, 1)}
     contigs = ["chr%d" % c for c in range(1, 23)]
     merged_text = pinned_text(synth.sam_text_of(case, seed=32, index_names=True))  # the merged BAM's records: names are FASTQ ordinals
     dt, g = timed(lambda: ctx.sam_mapped_records(merged_text, contigs))

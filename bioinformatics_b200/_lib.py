@@ -21,7 +21,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
            "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs",
-           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows")
+           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows")
 
 
 class HsqError(RuntimeError):
@@ -229,6 +229,15 @@ class Context:
         self._check(self.lib.hsq_index_fastq(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(oc)))
         out.n = int(oc.n)
         return out
+
+    def trim_fastq(self, text, first, last, three_prime=True, out=None):
+        """hsq_trim_fastq: FastqReadTrimmer.trimReads, FASTQ text in, trimmed FASTQ text out (uint8 array) and the record count."""
+        text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+        out = np.zeros(max(1, len(text)), dtype=np.uint8) if out is None else out  # trimming never grows a record
+        nb, nrec = C.c_int64(0), C.c_int64(0)
+        self._check(self.lib.hsq_trim_fastq(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), C.c_int32(first), C.c_int32(last),
+                                            C.c_int32(1 if three_prime else 0), A.ptr(out, A.u8p), C.c_int64(len(out)), C.byref(nb), C.byref(nrec)))
+        return out[:nb.value], int(nrec.value)
 
     def index_sam(self, text, cap=None):
         """hsq_index_sam: field index of SAM text (the columns the dedup path reads off a SAMRecord)."""

@@ -64,7 +64,8 @@ __global__ void set_i64_kernel(int64_t* p, int64_t v) { *p = v; }
 
 __global__ void fastq_record_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ line_start, int64_t n_rec,
                                     int64_t* __restrict__ h_off, int32_t* __restrict__ h_len, int64_t* __restrict__ s_off, int32_t* __restrict__ s_len,
-                                    int64_t* __restrict__ q_off, int32_t* __restrict__ q_len, int* status, unsigned long long* first_bad) {
+                                    int64_t* __restrict__ q_off, int32_t* __restrict__ q_len, int* status, unsigned long long* first_bad,
+                                    int64_t* __restrict__ p_off = nullptr, int32_t* __restrict__ p_len = nullptr) {
     int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; r < n_rec; r += stride) {
@@ -88,6 +89,55 @@ __global__ void fastq_record_kernel(const uint8_t* __restrict__ text, const int6
         h_off[r] = off[0] + 1; h_len[r] = len[0] - 1;
         s_off[r] = off[1]; s_len[r] = len[1];
         q_off[r] = off[3]; q_len[r] = len[3];
+        if (p_off) { p_off[r] = off[2] + 1; p_len[r] = len[2] - 1; }  // quality header without the '+'
+    }
+}
+
+// FastqReadTrimmer.trimReads: output bytes per record, flags the reads Java throws on (FastqReadTrimmer.java:310-312)
+__global__ void trimfq_len_kernel(const int32_t* __restrict__ h_len, const int32_t* __restrict__ s_len, const int32_t* __restrict__ p_len, int64_t n,
+                                  int first, int last, int three_prime, int64_t* __restrict__ out_len, int32_t* __restrict__ keep, int* status) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n; r += stride) {
+        const int len = s_len[r];
+        int lb = len - 1;
+        if (three_prime) lb = min(last, len - 1);
+        int kp = lb + 1 - first;
+        if (first >= len || kp < 0) { atomicMin(status, HSQ_ERR_OUT_OF_RANGE); kp = 0; }
+        keep[r] = kp;
+        out_len[r] = (int64_t)h_len[r] + p_len[r] + 2 * (int64_t)kp + 6;
+    }
+}
+
+// one warp per record: "@" header "\n" bases "\n+" quality header "\n" qualities "\n"
+__global__ void trimfq_write_kernel(const uint8_t* __restrict__ text, const int64_t* __restrict__ h_off, const int32_t* __restrict__ h_len,
+                                    const int64_t* __restrict__ s_off, const int64_t* __restrict__ q_off, const int64_t* __restrict__ p_off,
+                                    const int32_t* __restrict__ p_len, const int32_t* __restrict__ keep, const int64_t* __restrict__ out_off, int64_t n,
+                                    int first, int64_t cap, uint8_t* __restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; r < n; r += stride) {
+        const int64_t d = out_off[r];
+        const int total = (int)(out_off[r + 1] - d);
+        if (d + total > cap) continue;
+        const int hl = h_len[r], pl = p_len[r], kp = keep[r];
+        const int64_t ho = h_off[r] - 1, so = s_off[r] + first - (hl + 2), po = p_off[r] - (hl + kp + 4), qo = q_off[r] + first - (hl + kp + pl + 5);
+        const int e_head = hl + 1, e_seq = e_head + 1 + kp, e_plus = e_seq + 2 + pl, e_qual = e_plus + 1 + kp;
+        for (int k = lane; k < total; k += 32) {
+            uint8_t c;
+            if (k == 0) c = '@';
+            else if (k < e_head) c = text[ho + k];
+            else if (k == e_head) c = '\n';
+            else if (k < e_seq) c = text[so + k];
+            else if (k == e_seq) c = '\n';
+            else if (k == e_seq + 1) c = '+';
+            else if (k < e_plus) c = text[po + k];
+            else if (k == e_plus) c = '\n';
+            else if (k < e_qual) c = text[qo + k];
+            else c = '\n';
+            out[d + k] = c;
+        }
     }
 }
 
@@ -774,6 +824,64 @@ extern "C" int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_
                                                                {out->seq_len, d_o32 + nr, nr * 4}, {out->qual_len, d_o32 + 2 * nr, nr * 4}};
     for (auto& c : down)
         if (c.bytes) HSQ_CUDA(ctx, cudaMemcpyAsync(c.h, c.d, c.bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return timer.finish();
+}
+
+extern "C" int32_t hsq_trim_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, int32_t first, int32_t last, int32_t three_prime,
+                                  uint8_t* out_text, int64_t out_cap, int64_t* out_bytes, int64_t* n_records) {
+    if (!ctx || !out_bytes || n_bytes < 0 || out_cap < 0 || (n_bytes > 0 && !text)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_trim_fastq: null argument");
+    if (first < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_trim_fastq: First base to keep must be greater than zero");  // FastqReadTrimmer.java:264-266
+    if (last <= first) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_trim_fastq: Last base to keep must be greater than the first base to keep");  // :268-270
+    *out_bytes = 0;
+    if (n_records) *n_records = 0;
+    if (n_bytes == 0) return HSQ_OK;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    uint8_t* d_text;
+    int64_t* d_lines;
+    int64_t n_lines;
+    if ((rc = build_line_index(ctx, text, n_bytes, &d_text, &d_lines, &n_lines))) return rc;
+    int st[1];
+    if (n_lines % 4 != 0) {
+        if ((rc = read_status(ctx, st, 1))) return rc;
+        if (st[0] == HSQ_ERR_UNSUPPORTED) return fail(ctx, st[0], "hsq_trim_fastq: a carriage return that is not followed by a line feed");
+        return fail(ctx, HSQ_ERR_MALFORMED, "hsq_trim_fastq: File is too short: the last record has fewer than four lines");
+    }
+    const int64_t n_rec = n_lines / 4;
+    const size_t nr = (size_t)n_rec;
+    if (n_records) *n_records = n_rec;
+    const int64_t n_tiles = (n_rec + 1 + SCAN_TILE - 1) / SCAN_TILE;
+    DevBuf* ib = ctx->ing;
+    HSQ_CUDA(ctx, ib[4].ensure(nr * 8 * 4 + (nr + 1) * 16 + 64));  // four offset columns, output lengths, output offsets
+    HSQ_CUDA(ctx, ib[5].ensure(nr * 4 * 5 + 64));                  // four length columns, kept bases
+    HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)n_tiles * 8 + 16));
+    HSQ_CUDA(ctx, ctx->out_u8.ensure((size_t)out_cap + 16));
+    int64_t* o64 = ib[4].as<int64_t>();
+    int32_t* o32 = ib[5].as<int32_t>();
+    int64_t *h_off = o64, *s_off = o64 + nr, *q_off = o64 + 2 * nr, *p_off = o64 + 3 * nr, *out_len = o64 + 4 * nr, *out_off = out_len + nr + 1;
+    int32_t *h_len = o32, *s_len = o32 + nr, *q_len = o32 + 2 * nr, *p_len = o32 + 3 * nr, *keep = o32 + 4 * nr;
+    fastq_record_kernel<<<grid_for(ctx, n_rec, 128, 16), 128, 0, ctx->stream>>>(d_text, d_lines, n_rec, h_off, h_len, s_off, s_len, q_off, q_len, d_status(ctx),
+                                                                             ctx->cells.as<unsigned long long>(), p_off, p_len);
+    trimfq_len_kernel<<<grid_for(ctx, n_rec, 256, 16), 256, 0, ctx->stream>>>(h_len, s_len, p_len, n_rec, first, last, three_prime, out_len, keep, d_status(ctx));
+    ctx->launches += 2;
+    if ((rc = scan_i64(ctx, out_len, n_rec, ctx->sort_c.as<int64_t>(), out_off))) return rc;
+    trimfq_write_kernel<<<grid_for(ctx, n_rec * 32, 256, 16), 256, 0, ctx->stream>>>(d_text, h_off, h_len, s_off, q_off, p_off, p_len, keep, out_off, n_rec, first,
+                                                                                     out_cap, ctx->out_u8.as<uint8_t>());
+    ctx->launches++;
+    HSQ_CUDA(ctx, cudaGetLastError());
+    HSQ_CUDA(ctx, cudaMemcpyAsync(out_bytes, out_off + nr, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if ((rc = read_status(ctx, st, 1))) return rc;
+    if (st[0] == HSQ_ERR_UNSUPPORTED) return fail(ctx, st[0], "hsq_trim_fastq: a carriage return that is not followed by a line feed");
+    if (st[0] == HSQ_ERR_MALFORMED) return fail(ctx, st[0], "hsq_trim_fastq: record " + std::to_string(ctx->h_cells[0]) + " is not a FASTQ record");
+    if (st[0]) return fail(ctx, st[0], "hsq_trim_fastq: Unable to trim: a read is not longer than the first base to keep");
+    if (*out_bytes > out_cap) return fail(ctx, HSQ_ERR_OVERFLOW, "hsq_trim_fastq: out_cap too small; *out_bytes holds the size");
+    if (*out_bytes > 0) {
+        if (!out_text) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_trim_fastq: null out_text");
+        HSQ_CUDA(ctx, cudaMemcpyAsync(out_text, ctx->out_u8.p, (size_t)*out_bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    }
     return timer.finish();
 }
 

@@ -139,3 +139,23 @@ def dedup_from_files(be, fq1_text, fq2_text, sam_text, contig_names, ext_uid_len
     out = dedup_flow(be, records, fastq_pair_table(be, fq1_text, fq2_text), ext_uid_len, lig_uid_len, **kw)
     out["merged"], out["mapped_records"] = merged, records
     return out
+
+
+def probe_trimming_information(probes, ext_uid_len, lig_uid_len, trim_primers=True, additional_ext_trim=0, additional_lig_trim=0):
+    """FastqReadTrimmer.getProbeTrimmingInformation (HSQ/process/FastqReadTrimmer.java:78-127) from the probe table's primer and
+    capture-target lengths (collectStatsFromProbeInformation :129-151): (r1_first, r1_stop, r2_first, r2_stop)."""
+    ext, lig, target = probes.ext.lengths(), probes.lig.lengths(), probes.target.lengths()
+    r1_first = additional_ext_trim + ext_uid_len + (int(ext.max()) if trim_primers else 0)
+    r1_stop = int(target.min()) + (int(lig.min()) if trim_primers else 0)
+    r2_first = additional_lig_trim + lig_uid_len + (int(lig.max()) if trim_primers else 0)
+    r2_stop = int(target.min()) + (int(ext.min()) if trim_primers else 0)
+    return r1_first, r1_stop, r2_first, r2_stop
+
+
+def trim_flow(be, probes, fq1_text, fq2_text, ext_uid_len, lig_uid_len, three_prime=True, trim_primers=True):
+    """`HSQutils trim` file to file (FastqReadTrimmer.trimReads :263-307 on both FASTQ files): returns (trimmed FASTQ one text, trimmed
+    FASTQ two text, trimming information).  `be` needs trim_fastq (a Context, or the tests' adapter of the CPU oracle)."""
+    info = probe_trimming_information(probes, ext_uid_len, lig_uid_len, trim_primers)
+    t1, n1 = be.trim_fastq(fq1_text, info[0], info[1], three_prime)
+    t2, n2 = be.trim_fastq(fq2_text, info[2], info[3], three_prime)
+    return t1, t2, info

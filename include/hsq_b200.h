@@ -405,6 +405,14 @@ typedef struct hsq_fastq_index {
 } hsq_fastq_index;
 int32_t hsq_index_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_fastq_index* out);
 
+/* FastqReadTrimmer.trimReads (HSQ/process/FastqReadTrimmer.java:263-307), the file loop of `HSQutils trim`, text to text: every
+ * record of the FASTQ text keeps its header and quality header, bases and qualities are cut as hsq_trim_batch cuts them (:309-328),
+ * and records are written the way htsjdk's BasicFastqWriter writes them ("@" header "\n" bases "\n+" quality header "\n"
+ * qualities "\n").  first < 0 or last <= first: HSQ_ERR_INVALID_ARGUMENT (:264-270); a read not longer than `first`:
+ * HSQ_ERR_OUT_OF_RANGE (:310-312); more than out_cap bytes: HSQ_ERR_OVERFLOW with *out_bytes set. */
+int32_t hsq_trim_fastq(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, int32_t first, int32_t last, int32_t three_prime,
+                       uint8_t* out_text, int64_t out_cap, int64_t* out_bytes, int64_t* n_records);
+
 /* Field index of SAM text for the columns the dedup path reads off a SAMRecord (QNAME, FLAG, SEQ and QUAL lengths:
  * FastqAndBamFileMerger.java:222-330; RNAME, POS, strand, alignment end = POS + reference length of the CIGAR - 1 and the XA
  * tag: …Identification.java:439-576).  Grammar as htsjdk's SAMLineParser: '@' header lines first (counted, skipped), then

@@ -355,6 +355,21 @@ int32_t hsqo_resolve_multi_probe(const hsq_probe_table* pt, const hsq_candidates
 }
 
 // single-call helpers for the KAT tests
+// config 1 file to file: FastqReadTrimmer.trimReads on FASTQ text (hsq_oracle_ingest.hpp)
+int32_t hsqo_trim_fastq(const uint8_t* text, int64_t n_bytes, int32_t first, int32_t last, int32_t three_prime, uint8_t* out_text, int64_t out_cap,
+                        int64_t* out_bytes, int64_t* n_records) {
+    try {
+        const std::string t = trim_fastq_text(text, n_bytes, first, last, three_prime != 0);
+        *out_bytes = (int64_t)t.size();
+        if (n_records) { int64_t c = 0; for (char ch : t) c += ch == '\n'; *n_records = c / 4; }
+        if ((int64_t)t.size() > out_cap) { g_err = "out_cap too small"; return HSQ_ERR_OVERFLOW; }
+        memcpy(out_text, t.data(), t.size());
+        return HSQ_OK;
+    } catch (const FastqMalformed& e) { g_err = e.what(); return HSQ_ERR_MALFORMED;
+    } catch (const std::invalid_argument& e) { g_err = e.what(); return HSQ_ERR_INVALID_ARGUMENT;
+    } catch (const std::out_of_range& e) { g_err = e.what(); return HSQ_ERR_OUT_OF_RANGE; }
+}
+
 // f2: FastqReader record index of FASTQ text (hsq_oracle_ingest.hpp)
 int32_t hsqo_index_fastq(const uint8_t* text, int64_t n_bytes, hsq_fastq_index* o) {
     try {

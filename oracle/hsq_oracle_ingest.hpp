@@ -235,6 +235,34 @@ inline FastqIndex index_fastq(const uint8_t* text, int64_t n) {
     return ix;
 }
 
+// ---- FASTQ text -> trimmed FASTQ text: FastqReadTrimmer.trimReads (HSQ/process/FastqReadTrimmer.java:263-307) ---------------------
+// every record keeps its header and quality header; bases and qualities are cut by trim(String, String, int, int, boolean) (:309-328);
+// records are written as htsjdk's BasicFastqWriter does: "@" header "\n" bases "\n+" quality-header "\n" qualities "\n".
+inline std::string trim_fastq_text(const uint8_t* text, int64_t n, int first, int last, bool three_prime) {
+    if (first < 0) throw std::invalid_argument("First base to keep must be greater than zero");                       // :264-266
+    if (last <= first) throw std::invalid_argument("Last base to keep must be greater than the first base to keep");  // :268-270
+    const FastqIndex ix = index_fastq(text, n);
+    std::string out;
+    for (size_t k = 0; k < ix.header_off.size(); k++) {
+        const int keep = trimmed_length(ix.seq_len[k], first, last, three_prime);
+        const int64_t plus = ix.seq_off[k] + ix.seq_len[k];  // line terminator of the bases, then the '+' line up to the qualities
+        int64_t p0 = plus;
+        while (text[p0] != '+') p0++;
+        int64_t p1 = p0;
+        while (text[p1] != '\n' && text[p1] != '\r') p1++;
+        out += '@';
+        out.append((const char*)text + ix.header_off[k], (size_t)ix.header_len[k]);
+        out += '\n';
+        out.append((const char*)text + ix.seq_off[k] + first, (size_t)keep);
+        out += "\n+";
+        out.append((const char*)text + p0 + 1, (size_t)(p1 - p0 - 1));
+        out += '\n';
+        out.append((const char*)text + ix.qual_off[k] + first, (size_t)keep);
+        out += '\n';
+    }
+    return out;
+}
+
 // ---- SAM text -> field index ------------------------------------------------------------------------------------------------
 // The columns the dedup path reads off a SAMRecord: QNAME / FLAG / SEQ / QUAL lengths (FastqAndBamFileMerger.java:222-330),
 // RNAME, POS, strand and alignment end = POS + reference length of the CIGAR - 1, and the XA tag

@@ -37,7 +37,7 @@ def lib():
         for name in ("hsqo_align_batch", "hsqo_trim_batch", "hsqo_dedup_batch", "hsqo_extend_batch",
                      "hsqo_resolve_multi_probe", "hsqo_primer_end", "hsqo_index_of_first_match_in_reference",
                      "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs", "hsqo_assign_probes",
-                     "hsqo_extend_records", "hsqo_find_candidates", "hsqo_index_fastq", "hsqo_index_sam", "hsqo_sam_mapped_records", "hsqo_join_names"):
+                     "hsqo_extend_records", "hsqo_find_candidates", "hsqo_index_fastq", "hsqo_trim_fastq", "hsqo_index_sam", "hsqo_sam_mapped_records", "hsqo_join_names"):
             getattr(_lib, name).restype = C.c_int32
     return _lib
 
@@ -124,6 +124,16 @@ def index_fastq(text, cap=None):
     _check(lib().hsqo_index_fastq(A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(oc)))
     out.n = int(oc.n)
     return out
+
+
+def trim_fastq(text, first, last, three_prime=True):
+    """FastqReadTrimmer.trimReads on FASTQ text on the CPU (hsq_oracle_ingest.hpp)."""
+    text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
+    out = np.zeros(max(1, len(text)), dtype=np.uint8)
+    nb, nrec = C.c_int64(0), C.c_int64(0)
+    _check(lib().hsqo_trim_fastq(A.ptr(text, A.u8p), C.c_int64(len(text)), C.c_int32(first), C.c_int32(last), C.c_int32(1 if three_prime else 0),
+                                 A.ptr(out, A.u8p), C.c_int64(len(out)), C.byref(nb), C.byref(nrec)))
+    return out[:nb.value], int(nrec.value)
 
 
 def index_sam(text, cap=None):

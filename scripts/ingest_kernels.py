@@ -18,6 +18,7 @@ with Context(0) as ctx:
         print("%-22s %8.3f ms (%d launches)" % ((name,) + ctx.last_timing()))
     for rep in range(2):  # first pass allocates
         ix = ctx.index_fastq(case["fq1_text"]); show("index_fastq (%d MB)" % (len(case["fq1_text"]) >> 20))
+        ctx.trim_fastq(case["fq1_text"], 32, 127, True); show("trim_fastq")
         sx = ctx.index_sam(sam_text); show("index_sam (%d MB)" % (len(sam_text) >> 20))
         r = ctx.join_names(join); show("join_names (%d SAM records)" % join.n)
         ctx.gather_rows(case["fq1_text"], ix.seq_off[:ix.n], ix.seq_len[:ix.n]); show("gather_rows")

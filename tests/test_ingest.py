@@ -559,6 +559,7 @@ def test_gpu_sam_mapped_records_equals_oracle(ctx):
 class OraclePort:
     """The oracle behind the calls flow.ingest_flow makes (gather_rows: numpy fancy indexing)."""
     index_fastq = staticmethod(O.index_fastq)
+    trim_fastq = staticmethod(O.trim_fastq)
     index_sam = staticmethod(O.index_sam)
     join_names = staticmethod(O.join_names)
 
@@ -688,3 +689,77 @@ def test_gpu_dedup_from_files_equals_oracle(ctx):
     exp = flow.dedup_from_files(Backend(probes, ranges), fq1, fq2, sam, contigs, U, V, write_merged)
     _same_flow_outputs(got, exp)
     assert len(got["merged"]["sam_line"]) == records.n - 3 and got["records"].n > 300
+
+
+# -------------------------------------------------------------------------------------------------- `HSQutils trim`, file to file
+def trim_statement(text, first, last, three_prime):
+    """FastqReadTrimmer.trimReads with str.splitlines (second statement)."""
+    lines = text.decode().splitlines()
+    out = []
+    for k in range(0, len(lines), 4):
+        h, s_, p, q = lines[k:k + 4]
+        lb = min(last, len(s_) - 1) if three_prime else len(s_) - 1
+        out += [h, s_[first:lb + 1], p, q[first:lb + 1]]
+    return ("\n".join(out) + "\n").encode() if out else b""
+
+
+TRIM_TEXT = b"@r1 x\nACGTACGTACGTACGTACGT\n+r1 x\nABCDEFGHIJKLMNOPQRST\n@r2\r\nACGTACGTAC\r\n+\r\n0123456789"
+# FastqReadTrimmerTest.java:35-40: a 20 base read, first base to keep 5, last 14 -> 10 bases; the second read is shorter than the stop
+TRIM_EXPECTED = b"@r1 x\nCGTACGTACG\n+r1 x\nFGHIJKLMNO\n@r2\nCGTAC\n+\n56789\n"
+TRIM_BAD = [((b"@r\nACGT\n+\nIIII\n", 4, 9, True), A.HSQ_ERR_OUT_OF_RANGE),      # first base to keep behind the read (:310-312)
+            ((b"@r\nACGT\n+\nIIII\n", -1, 9, True), A.HSQ_ERR_INVALID_ARGUMENT),  # :264-266
+            ((b"@r\nACGT\n+\nIIII\n", 3, 3, True), A.HSQ_ERR_INVALID_ARGUMENT),   # :268-270
+            ((b"@r\nACGT\n+\nIII\n", 1, 3, True), A.HSQ_ERR_MALFORMED)]
+
+
+def test_oracle_trim_fastq():
+    t, n = O.trim_fastq(TRIM_TEXT, 5, 14, True)
+    assert n == 2 and t.tobytes() == TRIM_EXPECTED
+    assert O.trim_fastq(TRIM_TEXT, 5, 14, False)[0].tobytes() == b"@r1 x\nCGTACGTACGTACGT\n+r1 x\nFGHIJKLMNOPQRST\n@r2\nCGTAC\n+\n56789\n"
+    for args, want in TRIM_BAD:
+        with pytest.raises(O.OracleError) as e:
+            O.trim_fastq(*args)
+        assert e.value.status == want
+    case = synth.make_ingest_case(700, read_len=60, seed=8)
+    for first, last, tp in ((12, 47, True), (0, 200, True), (7, 8, False)):
+        assert O.trim_fastq(case["fq2_text"], first, last, tp)[0].tobytes() == trim_statement(case["fq2_text"], first, last, tp)
+
+
+def test_trim_flow_over_oracle():
+    """`HSQutils trim` file to file: the offsets of getProbeTrimmingInformation, then every output record is its input record cut."""
+    from bioinformatics_b200 import flow
+    probes = synth.make_probes(30, seed=2)
+    fastq = synth.make_pairs(probes, 400, read_len=150, ext_uid_len=10, seed=3)
+    fq1, fq2, _, _ = synth.dedup_input_files(probes, fastq, synth.make_mapped_records(probes, fastq, seed=4)[1])
+    t1, t2, info = flow.trim_flow(OraclePort, probes, fq1, fq2, 10, 0)
+    ext, lig, tgt = probes.ext.lengths(), probes.lig.lengths(), probes.target.lengths()
+    assert info == (10 + ext.max(), tgt.min() + lig.min(), lig.max(), tgt.min() + ext.min())
+    i1 = O.index_fastq(t1.tobytes())
+    assert i1.n == 400 and (i1.seq_len[:400] == min(info[1], 149) + 1 - info[0]).all()
+    assert t2.tobytes() == trim_statement(fq2, info[2], info[3], True)
+
+
+@pytest.mark.gpu
+def test_gpu_trim_fastq_equals_oracle(ctx):
+    from bioinformatics_b200._lib import HsqError
+    from bioinformatics_b200 import flow
+    t, n = ctx.trim_fastq(TRIM_TEXT, 5, 14, True)
+    assert n == 2 and t.tobytes() == TRIM_EXPECTED
+    for args, want in TRIM_BAD:
+        with pytest.raises(HsqError) as e:
+            ctx.trim_fastq(*args)
+        assert e.value.status == want
+    assert ctx.trim_fastq(b"", 1, 5)[1] == 0
+    for n_pairs, kw in ((1, {}), (3000, dict(crlf=True)), (40000, dict(final_newline=False, old_style=True))):
+        case = synth.make_ingest_case(n_pairs, read_len=101, seed=n_pairs % 9, **kw)
+        for first, last, tp in ((12, 88, True), (0, 300, True), (30, 31, False)):
+            got, exp = ctx.trim_fastq(case["fq1_text"], first, last, tp), O.trim_fastq(case["fq1_text"], first, last, tp)
+            assert got[1] == exp[1] == n_pairs and got[0].tobytes() == exp[0].tobytes()
+    with pytest.raises(HsqError) as e:
+        ctx.trim_fastq(case["fq1_text"], 12, 88, True, out=np.zeros(1000, dtype=np.uint8))
+    assert e.value.status == A.HSQ_ERR_OVERFLOW
+    probes = synth.make_probes(30, seed=2)
+    fastq = synth.make_pairs(probes, 2000, read_len=150, ext_uid_len=10, seed=3)
+    fq1, fq2, _, _ = synth.dedup_input_files(probes, fastq, synth.make_mapped_records(probes, fastq, seed=4)[1])
+    g, o = flow.trim_flow(ctx, probes, fq1, fq2, 10, 0), flow.trim_flow(OraclePort, probes, fq1, fq2, 10, 0)
+    assert g[0].tobytes() == o[0].tobytes() and g[1].tobytes() == o[1].tobytes() and g[2] == o[2]
