@@ -359,7 +359,7 @@ def next_row_numbers(ctx, probes, pairs, res):
                     "algorithmic_bytes_per_record": len(text) / max(g.n, 1) + (36 if key == "index_fastq" else 108)}
     # config 1 file to file: FastqReadTrimmer.trimReads on FASTQ text (both buffers pinned)
     ptext = pinned_text(case["fq1_text"])
-    pout = ctx.pinned_array(len(ptext))
+    pout = ctx.pinned_array(len(ptext) + 2)
     dt, (g, nrec) = timed(lambda: ctx.trim_fastq(ptext, 32, 127, True, out=pout))
     ms_dev = ctx.last_timing()[0]
     t0 = time.perf_counter()

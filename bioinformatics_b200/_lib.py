@@ -233,7 +233,7 @@ class Context:
     def trim_fastq(self, text, first, last, three_prime=True, out=None):
         """hsq_trim_fastq: FastqReadTrimmer.trimReads, FASTQ text in, trimmed FASTQ text out (uint8 array) and the record count."""
         text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
-        out = np.zeros(max(1, len(text)), dtype=np.uint8) if out is None else out  # trimming never grows a record
+        out = np.zeros(len(text) + 2, dtype=np.uint8) if out is None else out  # a record only shrinks; a missing last line feed is added
         nb, nrec = C.c_int64(0), C.c_int64(0)
         self._check(self.lib.hsq_trim_fastq(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), C.c_int32(first), C.c_int32(last),
                                             C.c_int32(1 if three_prime else 0), A.ptr(out, A.u8p), C.c_int64(len(out)), C.byref(nb), C.byref(nrec)))

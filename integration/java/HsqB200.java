@@ -95,6 +95,8 @@ public final class HsqB200 implements AutoCloseable {
     private static final MethodHandle MERGE_PAIRS = fn("hsq_merge_pairs", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS,
             ADDRESS, JAVA_LONG));
     private static final MethodHandle INDEX_FASTQ = fn("hsq_index_fastq", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
+    private static final MethodHandle TRIM_FASTQ = fn("hsq_trim_fastq", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, JAVA_INT, JAVA_INT,
+            JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS));
     private static final MethodHandle INDEX_SAM = fn("hsq_index_sam", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
     private static final MethodHandle SAM_MAPPED_RECORDS = fn("hsq_sam_mapped_records", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS));
     private static final MethodHandle JOIN_NAMES = fn("hsq_join_names", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
@@ -191,6 +193,13 @@ public final class HsqB200 implements AutoCloseable {
 
     /** Record index of FASTQ text as FastqReader reads it (call sites FastqSorter.java:77,98); fastqIndex = hsq_fastq_index. */
     public void indexFastq(MemorySegment text, long nBytes, MemorySegment fastqIndex) { check(invokeInt(INDEX_FASTQ, ctx, text, nBytes, fastqIndex)); }
+
+    /** FastqReadTrimmer.trimReads (FastqReadTrimmer.java:263-307), FASTQ text in, trimmed FASTQ text out; returns the bytes written. */
+    public long trimFastq(MemorySegment text, long nBytes, int firstBaseToKeep, int lastBaseToKeep, boolean threePrime, MemorySegment outText, long outCap) {
+        MemorySegment outBytes = arena.allocate(JAVA_LONG), nRecords = arena.allocate(JAVA_LONG);
+        check(invokeInt(TRIM_FASTQ, ctx, text, nBytes, firstBaseToKeep, lastBaseToKeep, threePrime ? 1 : 0, outText, outCap, outBytes, nRecords));
+        return outBytes.get(JAVA_LONG, 0);
+    }
 
     /** Column index of SAM text (QNAME, FLAG, RNAME, POS, CIGAR reference length, SEQ, QUAL, XA); samIndex = hsq_sam_index. */
     public void indexSam(MemorySegment text, long nBytes, MemorySegment samIndex) { check(invokeInt(INDEX_SAM, ctx, text, nBytes, samIndex)); }

@@ -129,7 +129,7 @@ def index_fastq(text, cap=None):
 def trim_fastq(text, first, last, three_prime=True):
     """FastqReadTrimmer.trimReads on FASTQ text on the CPU (hsq_oracle_ingest.hpp)."""
     text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
-    out = np.zeros(max(1, len(text)), dtype=np.uint8)
+    out = np.zeros(len(text) + 2, dtype=np.uint8)
     nb, nrec = C.c_int64(0), C.c_int64(0)
     _check(lib().hsqo_trim_fastq(A.ptr(text, A.u8p), C.c_int64(len(text)), C.c_int32(first), C.c_int32(last), C.c_int32(1 if three_prime else 0),
                                  A.ptr(out, A.u8p), C.c_int64(len(out)), C.byref(nb), C.byref(nrec)))
