@@ -128,6 +128,11 @@ class SamRecordsOut(C.Structure):
                 ("alt_contig", i32p), ("alt_negative", u8p), ("alt_start", i32p), ("alt_stop", i32p)]
 
 
+class CoordSortIn(C.Structure):
+    _fields_ = [("n", C.c_int64), ("ref_index", i32p), ("pos", i32p), ("flags", i32p), ("mapq", i32p), ("mate_ref_index", i32p), ("mate_pos", i32p),
+                ("tlen", i32p), ("names", Seqs)]
+
+
 class NameJoin(C.Structure):
     _fields_ = [("sam_names", Seqs), ("sam_flags", i32p), ("sam_seq_len", i32p), ("sam_qual_len", i32p), ("fq1_headers", Seqs),
                 ("fq2_headers", Seqs), ("fq1_seq_len", i32p), ("fq2_seq_len", i32p), ("by_index", C.c_int32), ("trimming_skipped", C.c_int32),

@@ -21,7 +21,13 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
            "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs",
-           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows")
+           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order")
+
+
+def _coord_args(ref_index, pos, flags, mapq, mate_ref_index, mate_pos, tlen, names):
+    cols = [np.ascontiguousarray(x, dtype=np.int32) for x in (ref_index, pos, flags, mapq, mate_ref_index, mate_pos, tlen)]
+    names = names if isinstance(names, A.SeqBatch) else A.SeqBatch.from_strings(names)
+    return cols, names, A.CoordSortIn(len(cols[0]), *[A.ptr(c, A.i32p) for c in cols], names.c())
 
 
 class HsqError(RuntimeError):
@@ -261,6 +267,13 @@ class Context:
         nc, oc = names.c(), out.c()
         self._check(self.lib.hsq_sam_mapped_records(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(nc), C.byref(oc)))
         return out.take(oc)
+
+    def coordinate_order(self, ref_index, pos, flags, mapq, mate_ref_index, mate_pos, tlen, names):
+        """hsq_coordinate_order: order of the final coordinate sort (SAMRecordCoordinateComparator)."""
+        keep = _coord_args(ref_index, pos, flags, mapq, mate_ref_index, mate_pos, tlen, names)
+        order = np.zeros(len(keep[0][0]), dtype=np.int32)
+        self._check(self.lib.hsq_coordinate_order(self.h, C.byref(keep[2]), A.ptr(order, A.i32p)))
+        return order
 
     def join_names(self, join: NameJoinHost):
         """hsq_join_names: both sorts and the merge loop of FastqAndBamFileMerger's MergedSamIterator."""

@@ -390,6 +390,25 @@ __global__ void samrec_fill_kernel(const uint8_t* __restrict__ text, const int64
 }
 
 // ---------------------------------------------------------------------------------------------------------------------------
+// keys of the final coordinate sort (htsjdk SAMRecordCoordinateComparator): signed integers biased to unsigned order
+__global__ void coord_keys_kernel(const int32_t* __restrict__ ref, const int32_t* __restrict__ pos, const int32_t* __restrict__ flags,
+                                  const int32_t* __restrict__ mapq, const int32_t* __restrict__ mate_ref, const int32_t* __restrict__ mate_pos,
+                                  const int32_t* __restrict__ tlen, int64_t n, uint64_t* __restrict__ k_place, uint64_t* __restrict__ k_strand,
+                                  uint64_t* __restrict__ k_flags, uint64_t* __restrict__ k_mapq_mref, uint64_t* __restrict__ k_mpos_tlen) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    auto b = [](int32_t v) { return (uint64_t)((uint32_t)v ^ 0x80000000u); };
+    for (; i < n; i += stride) {
+        const uint64_t rk = ref[i] == -1 ? 0xFFFFFFFFull : b(ref[i]);           // records without a reference go last
+        k_place[i] = (rk << 32) | (ref[i] == -1 ? 0ull : b(pos[i]));              // ... and are not ordered by position
+        k_strand[i] = (flags[i] & 0x10) ? 1 : 0;
+        k_flags[i] = b(flags[i]);
+        k_mapq_mref[i] = (b(mapq[i]) << 32) | b(mate_ref[i]);
+        k_mpos_tlen[i] = (b(mate_pos[i]) << 32) | b(tlen[i]);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------------
 // ragged row gather
 __global__ void rows_len_kernel(const int64_t* __restrict__ off, const int32_t* __restrict__ len, int64_t n, int64_t n_bytes,
                                 int64_t* __restrict__ len64, int* status) {
@@ -712,10 +731,10 @@ int lsd_chunk_sort(hsq_ctx* ctx, const uint64_t* keys, int n_chunks, const int* 
     return HSQ_OK;
 }
 
-int bit_sort(hsq_ctx* ctx, const uint64_t* key, int64_t n, uint32_t** cur, uint32_t** other, uint64_t* ka, uint64_t* kb) {
+int bit_sort(hsq_ctx* ctx, const uint64_t* key, int64_t n, uint32_t** cur, uint32_t** other, uint64_t* ka, uint64_t* kb, int end_bit = 1) {
     gather_u64_kernel<uint64_t><<<grid_for(ctx, n, 256, 16), 256, 0, ctx->stream>>>(key, *cur, n, ka);
     ctx->launches++;
-    int rc = sort_pass(ctx, ka, kb, *cur, *other, n, 1);
+    int rc = sort_pass(ctx, ka, kb, *cur, *other, n, end_bit);
     if (rc) return rc;
     std::swap(*cur, *other);
     return HSQ_OK;
@@ -1269,5 +1288,61 @@ extern "C" int32_t hsq_join_names(hsq_ctx* ctx, const hsq_name_join* in, hsq_nam
         HSQ_CUDA(ctx, cudaMemcpyAsync(out->name_len, d_name_len, ne * 4, cudaMemcpyDeviceToHost, ctx->stream));
     }
     if (ns) HSQ_CUDA(ctx, cudaMemcpyAsync(out->status, d_rec_status, nss, cudaMemcpyDeviceToHost, ctx->stream));
+    return timer.finish();
+}
+
+extern "C" int32_t hsq_coordinate_order(hsq_ctx* ctx, const hsq_coord_sort_in* in, int32_t* order) {
+    if (!ctx || !in) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_coordinate_order: null argument");
+    const int64_t n = in->n;
+    if (n < 0 || n >= (1ll << 31) || in->names.n != n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_coordinate_order: bad n");
+    if (n == 0) return HSQ_OK;
+    if (!order || !in->ref_index || !in->pos || !in->flags || !in->mapq || !in->mate_ref_index || !in->mate_pos || !in->tlen)
+        return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_coordinate_order: null array");
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    int rc;
+    DevBuf* ib = ctx->ing;
+    if ((rc = upload_strings(ctx, &in->names, &ib[0], &ib[1], "names"))) return rc;
+    const size_t nn = (size_t)n;
+    HSQ_CUDA(ctx, ib[6].ensure(nn * 4 * 7 + 64));
+    int32_t* d_cols = ib[6].as<int32_t>();
+    const int32_t* cols[7] = {in->ref_index, in->pos, in->flags, in->mapq, in->mate_ref_index, in->mate_pos, in->tlen};
+    for (int c = 0; c < 7; c++) HSQ_CUDA(ctx, cudaMemcpyAsync(d_cols + (size_t)c * nn, cols[c], nn * 4, cudaMemcpyHostToDevice, ctx->stream));
+    HSQ_CUDA(ctx, ib[7].ensure(JC_WORDS * 4 + 64 * 4 * 3));
+    int* d_ctr = ib[7].as<int>();
+    int* d_live = d_ctr + JC_WORDS;
+    HSQ_CUDA(ctx, cudaMemsetAsync(d_ctr, 0, JC_WORDS * 4 + 64 * 4 * 3, ctx->stream));
+    max_len_kernel<<<grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>(ib[1].as<int64_t>(), n, d_ctr + JC_MAX_SAM);
+    ctx->launches++;
+    int h_ctr[JC_WORDS + 64];
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_ctr, d_ctr, JC_WORDS * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const int ch = std::max(1, (h_ctr[JC_MAX_SAM] + 7) / 8);
+    if (ch > 64) return fail(ctx, HSQ_ERR_UNSUPPORTED, "hsq_coordinate_order: read names longer than 512 bytes");
+    Arena ar;
+    const size_t o_keys = ar.reserve(nn * 8 * (size_t)ch), o_k = ar.reserve(nn * 8 * 5), o_ka = ar.reserve(nn * 8), o_kb = ar.reserve(nn * 8);
+    const size_t o_pa = ar.reserve(nn * 4), o_pb = ar.reserve(nn * 4), o_uid = ar.reserve(nn * 4);
+    HSQ_CUDA(ctx, ib[8].ensure(ar.need + 256));
+    ar.base = ib[8].as<uint8_t>();
+    uint64_t *keys = ar.at<uint64_t>(o_keys), *k5 = ar.at<uint64_t>(o_k), *ka = ar.at<uint64_t>(o_ka), *kb = ar.at<uint64_t>(o_kb);
+    uint32_t *pa = ar.at<uint32_t>(o_pa), *pb = ar.at<uint32_t>(o_pb);
+    const int g = grid_for(ctx, n, 256, 16);
+    coord_keys_kernel<<<g, 256, 0, ctx->stream>>>(d_cols, d_cols + nn, d_cols + 2 * nn, d_cols + 3 * nn, d_cols + 4 * nn, d_cols + 5 * nn, d_cols + 6 * nn, n, k5,
+                                                  k5 + nn, k5 + 2 * nn, k5 + 3 * nn, k5 + 4 * nn);
+    fq_keys_kernel<<<grid_for(ctx, n, 128, 16), 128, 0, ctx->stream>>>(ib[0].as<uint8_t>(), ib[1].as<int64_t>(), n, ch, 0, keys, ar.at<int32_t>(o_uid));
+    chunk_live_kernel<<<grid_for(ctx, n * ch, 256, 16), 256, 0, ctx->stream>>>(keys, n, ch, d_live);
+    iota_u32_kernel<<<g, 256, 0, ctx->stream>>>(pa, n);
+    ctx->launches += 4;
+    HSQ_CUDA(ctx, cudaGetLastError());
+    HSQ_CUDA(ctx, cudaMemcpyAsync(h_ctr, d_ctr, sizeof(h_ctr), cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    // least significant key first, every pass stable
+    if ((rc = bit_sort(ctx, k5 + 4 * nn, n, &pa, &pb, ka, kb, 64))) return rc;  // mate start, insert size
+    if ((rc = bit_sort(ctx, k5 + 3 * nn, n, &pa, &pb, ka, kb, 64))) return rc;  // mapping quality, mate reference
+    if ((rc = bit_sort(ctx, k5 + 2 * nn, n, &pa, &pb, ka, kb, 32))) return rc;  // flags
+    if ((rc = lsd_chunk_sort(ctx, keys, ch, h_ctr + JC_WORDS, n, &pa, &pb, ka, kb))) return rc;  // read name
+    if ((rc = bit_sort(ctx, k5 + nn, n, &pa, &pb, ka, kb, 1))) return rc;       // strand
+    if ((rc = bit_sort(ctx, k5, n, &pa, &pb, ka, kb, 64))) return rc;           // reference, start
+    HSQ_CUDA(ctx, cudaMemcpyAsync(order, pa, nn * 4, cudaMemcpyDeviceToHost, ctx->stream));
     return timer.finish();
 }

@@ -494,6 +494,24 @@ int32_t hsq_join_names(hsq_ctx* ctx, const hsq_name_join* in, hsq_name_join_out*
 int32_t hsq_gather_rows(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, const int64_t* off, const int32_t* len, int64_t n,
                         uint8_t* out_data, int64_t* out_offsets, int64_t out_cap);
 
+/* Order of the final coordinate sort of the output records (BamSorter.sortBamFile(..., new SAMRecordCoordinateComparator()),
+ * …Identification.java:897; htsjdk 2.9.0's comparator, source absent from /root/reference: reference index with -1 last, alignment
+ * start, forward strand before reverse, then read name (String.compareTo), FLAG, MAPQ, mate reference index, mate alignment
+ * start, inferred insert size as signed integers).  order[k] = input record at sorted position k; records that compare equal
+ * keep input order (the reference's chunk merge refuses such records when they meet, BamSorter.java:153-165). */
+typedef struct hsq_coord_sort_in {
+    int64_t n;
+    const int32_t* ref_index;
+    const int32_t* pos;
+    const int32_t* flags;
+    const int32_t* mapq;
+    const int32_t* mate_ref_index;
+    const int32_t* mate_pos;
+    const int32_t* tlen;
+    hsq_seqs names;
+} hsq_coord_sort_in;
+int32_t hsq_coordinate_order(hsq_ctx* ctx, const hsq_coord_sort_in* in, int32_t* order);
+
 /* ---- sharded dedup: one process per GPU, exchange by the caller ------------------------------------------------------ */
 /* First half of FilterByUid.reduceReadsByProbeAndUid for this rank's pairs (host buffers in): writes pairs->n key
  * records to DEVICE memory d_keys_out (origin = origin_base + pair index).  The caller routes the records to the rank

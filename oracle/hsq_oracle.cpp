@@ -370,6 +370,20 @@ int32_t hsqo_trim_fastq(const uint8_t* text, int64_t n_bytes, int32_t first, int
     } catch (const std::out_of_range& e) { g_err = e.what(); return HSQ_ERR_OUT_OF_RANGE; }
 }
 
+// f4: order of the final coordinate sort (hsq_oracle_ingest.hpp)
+int32_t hsqo_coordinate_order(const hsq_coord_sort_in* in, int32_t* order) {
+    std::vector<CoordRecord> r((size_t)in->n);
+    for (int64_t k = 0; k < in->n; k++) {
+        CoordRecord& c = r[(size_t)k];
+        c.ref = in->ref_index[k]; c.pos = in->pos[k]; c.flags = in->flags[k]; c.mapq = in->mapq[k];
+        c.mate_ref = in->mate_ref_index[k]; c.mate_pos = in->mate_pos[k]; c.tlen = in->tlen[k];
+        c.name = get_str(in->names.data, in->names.offsets, k);
+    }
+    const std::vector<int32_t> o = coordinate_order(r);
+    for (int64_t k = 0; k < in->n; k++) order[k] = o[(size_t)k];
+    return HSQ_OK;
+}
+
 // f2: FastqReader record index of FASTQ text (hsq_oracle_ingest.hpp)
 int32_t hsqo_index_fastq(const uint8_t* text, int64_t n_bytes, hsq_fastq_index* o) {
     try {

@@ -445,4 +445,34 @@ inline SamRecords sam_mapped_records(const uint8_t* text, int64_t n, const std::
     return out;
 }
 
+// ---- the final coordinate sort (...Identification.java:897): htsjdk 2.9.0 SAMRecordCoordinateComparator, restated from its published
+// source (absent from /root/reference): fileOrderCompare (reference index, -1 last; alignment start), then, for equal strands, read name,
+// flags, mapping quality, mate reference index, mate alignment start, inferred insert size; for unequal strands the reverse strand last.
+struct CoordRecord {
+    int32_t ref, pos, flags, mapq, mate_ref, mate_pos, tlen;
+    std::string name;
+};
+inline std::vector<int32_t> coordinate_order(const std::vector<CoordRecord>& r) {
+    std::vector<int32_t> order(r.size());
+    for (size_t k = 0; k < r.size(); k++) order[k] = (int32_t)k;
+    auto cmp = [](int64_t x, int64_t y) { return x < y ? -1 : (x > y ? 1 : 0); };
+    std::stable_sort(order.begin(), order.end(), [&](int32_t x, int32_t y) {
+        const CoordRecord &a = r[(size_t)x], &b = r[(size_t)y];
+        int c;
+        if (a.ref == -1) c = b.ref == -1 ? 0 : 1;
+        else if (b.ref == -1) c = -1;
+        else if ((c = cmp(a.ref, b.ref)) == 0) c = cmp(a.pos, b.pos);
+        if (c != 0) return c < 0;
+        const bool na = (a.flags & 0x10) != 0, nb = (b.flags & 0x10) != 0;
+        if (na != nb) return !na;  // the record on the reverse strand goes last
+        if ((c = a.name.compare(b.name)) != 0) return c < 0;
+        if ((c = cmp(a.flags, b.flags)) != 0) return c < 0;
+        if ((c = cmp(a.mapq, b.mapq)) != 0) return c < 0;
+        if ((c = cmp(a.mate_ref, b.mate_ref)) != 0) return c < 0;
+        if ((c = cmp(a.mate_pos, b.mate_pos)) != 0) return c < 0;
+        return cmp(a.tlen, b.tlen) < 0;
+    });
+    return order;
+}
+
 }  // namespace hsqo

@@ -37,7 +37,7 @@ def lib():
         for name in ("hsqo_align_batch", "hsqo_trim_batch", "hsqo_dedup_batch", "hsqo_extend_batch",
                      "hsqo_resolve_multi_probe", "hsqo_primer_end", "hsqo_index_of_first_match_in_reference",
                      "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs", "hsqo_assign_probes",
-                     "hsqo_extend_records", "hsqo_find_candidates", "hsqo_index_fastq", "hsqo_trim_fastq", "hsqo_index_sam", "hsqo_sam_mapped_records", "hsqo_join_names"):
+                     "hsqo_extend_records", "hsqo_find_candidates", "hsqo_index_fastq", "hsqo_trim_fastq", "hsqo_index_sam", "hsqo_coordinate_order", "hsqo_sam_mapped_records", "hsqo_join_names"):
             getattr(_lib, name).restype = C.c_int32
     return _lib
 
@@ -155,6 +155,15 @@ def sam_mapped_records(text, contig_names, cap=None, alt_cap=None):
     nc, oc = names.c(), out.c()
     _check(lib().hsqo_sam_mapped_records(A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(nc), C.byref(oc)))
     return out.take(oc)
+
+
+def coordinate_order(ref_index, pos, flags, mapq, mate_ref_index, mate_pos, tlen, names):
+    """Order of the final coordinate sort on the CPU: std::stable_sort with htsjdk's SAMRecordCoordinateComparator restated."""
+    from bioinformatics_b200._lib import _coord_args
+    keep = _coord_args(ref_index, pos, flags, mapq, mate_ref_index, mate_pos, tlen, names)
+    order = np.zeros(len(keep[0][0]), dtype=np.int32)
+    _check(lib().hsqo_coordinate_order(C.byref(keep[2]), A.ptr(order, A.i32p)))
+    return order
 
 
 def join_names(join):

@@ -763,3 +763,54 @@ def test_gpu_trim_fastq_equals_oracle(ctx):
     fq1, fq2, _, _ = synth.dedup_input_files(probes, fastq, synth.make_mapped_records(probes, fastq, seed=4)[1])
     g, o = flow.trim_flow(ctx, probes, fq1, fq2, 10, 0), flow.trim_flow(OraclePort, probes, fq1, fq2, 10, 0)
     assert g[0].tobytes() == o[0].tobytes() and g[1].tobytes() == o[1].tobytes() and g[2] == o[2]
+
+
+# ------------------------------------------------------------------------------------- the final coordinate sort (f4, output side)
+def coord_problem(n, seed, n_names=None):
+    rng = np.random.default_rng(seed)
+    ref = rng.integers(-1, 4, size=n)
+    pos = rng.integers(1, 60, size=n)
+    flags = rng.choice([99, 147, 83, 163, 1123, 1171, 65, 129, 81, 161], size=n)
+    mapq = rng.choice([0, 60, 37], size=n)
+    mate_ref = rng.integers(-1, 3, size=n)
+    mate_pos = rng.integers(0, 5, size=n)
+    tlen = rng.integers(-3, 4, size=n)
+    names = ["M0:%d:%s" % (int(k), "x" * int(k % 5)) for k in rng.integers(0, n_names or max(2, n // 3), size=n)]
+    return ref, pos, flags, mapq, mate_ref, mate_pos, tlen, names
+
+
+def coord_statement(ref, pos, flags, mapq, mate_ref, mate_pos, tlen, names):
+    """sorted() with the comparator as a key tuple (Python's sort is stable)."""
+    key = lambda k: ((1, 0) if ref[k] == -1 else (0, int(ref[k]), int(pos[k])), 1 if flags[k] & 0x10 else 0, names[k].encode(), int(flags[k]), int(mapq[k]),
+                     int(mate_ref[k]), int(mate_pos[k]), int(tlen[k]))
+    return sorted(range(len(ref)), key=key)
+
+
+# by hand: reference 0 before reference 2, unplaced (-1) last; inside reference 0: start 5 before 9; at (0, 5) the forward record [3] before the
+# reverse ones; the two reverse records at (0, 5) by name "a" < "b"; at (2, 7) same strand and name: flags 99 before 163
+COORD_KAT = ([2, -1, 0, 0, 0, 2, 0], [7, 3, 5, 5, 9, 7, 5], [163, 77, 83, 99, 99, 99, 83], [60] * 7, [0] * 7, [1] * 7, [0] * 7, ["q", "u", "b", "z", "c", "q", "a"])
+COORD_KAT_ORDER = [3, 6, 2, 4, 5, 0, 1]
+
+
+def test_oracle_coordinate_order():
+    assert list(O.coordinate_order(*COORD_KAT)) == COORD_KAT_ORDER
+    for n, seed in ((1, 1), (50, 2), (3000, 3)):
+        p = coord_problem(n, seed)
+        assert list(O.coordinate_order(*p)) == coord_statement(*p)
+
+
+@pytest.mark.gpu
+def test_gpu_coordinate_order_equals_oracle(ctx):
+    assert list(ctx.coordinate_order(*COORD_KAT)) == COORD_KAT_ORDER
+    for n, seed, names in ((1, 1, None), (2, 2, None), (700, 3, 5), (50000, 4, None), (50000, 5, 40)):
+        p = coord_problem(n, seed, names)
+        assert (ctx.coordinate_order(*p) == O.coordinate_order(*p)).all()
+    # the records dedup_flow writes, ordered for the output BAM: positions from the extension, names = read indexes as strings
+    rng = np.random.default_rng(9)
+    n = 20000
+    p = (rng.integers(0, 22, size=n), rng.integers(1, 10 ** 8, size=n), rng.choice([99, 147, 83, 163], size=n), np.full(n, 60), rng.integers(0, 22, size=n),
+         rng.integers(1, 10 ** 8, size=n), rng.integers(-400, 400, size=n), [str(int(k)) for k in rng.integers(0, 10 ** 7, size=n)])
+    got = ctx.coordinate_order(*p)
+    assert (got == O.coordinate_order(*p)).all()
+    key = p[0][got].astype(np.int64) * 10 ** 9 + p[1][got]
+    assert (np.diff(key) >= 0).all()
