@@ -394,6 +394,21 @@ def next_row_numbers(ctx, probes, pairs, res):
                          "returned_records": int(g.n_emitted), "matching_pairs": int(g.total_matching_pairs),
                          "cpu_port_sam_records_per_s": join.n / dt_cpu, "cpu_sample": "the same records, 1 thread (two std::stable_sort + the merge loop)",
                          "equals_cpu_port": bool(same)}
+    # f4 output side: order of the final coordinate sort for the records of the extended pairs (names = read indexes as strings)
+    rng = np.random.default_rng(5)
+    n_out = 1000000
+    cols = (rng.integers(0, 22, size=n_out), rng.integers(1, 10 ** 8, size=n_out), rng.choice([99, 147, 83, 163], size=n_out), np.full(n_out, 60),
+            rng.integers(0, 22, size=n_out), rng.integers(1, 10 ** 8, size=n_out), rng.integers(-400, 400, size=n_out))
+    names = A.SeqBatch.from_strings(["%d" % k for k in rng.integers(0, 10 ** 7, size=n_out).tolist()])
+    dt, g = timed(lambda: ctx.coordinate_order(*cols, names))
+    ms_dev = ctx.last_timing()[0]
+    sub = 200000
+    t0 = time.perf_counter()
+    c = O.coordinate_order(*[x[:sub] for x in cols], A.SeqBatch(names.data, names.offsets[:sub + 1]))
+    dt_cpu = time.perf_counter() - t0
+    out["coordinate_order"] = {"records_per_s": n_out / dt, "ms_host_to_host": dt * 1e3, "ms_device_incl_copies": ms_dev, "records": n_out,
+                               "cpu_port_records_per_s": sub / dt_cpu, "cpu_sample": "%d records, 1 thread (std::stable_sort)" % sub,
+                               "sorted": bool((np.diff(cols[0][g].astype(np.int64) * 10 ** 9 + cols[1][g]) >= 0).all())}
     out["ingest"] = ing
     return out
 

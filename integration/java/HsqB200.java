@@ -99,6 +99,7 @@ public final class HsqB200 implements AutoCloseable {
             JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS));
     private static final MethodHandle INDEX_SAM = fn("hsq_index_sam", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
     private static final MethodHandle SAM_MAPPED_RECORDS = fn("hsq_sam_mapped_records", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS));
+    private static final MethodHandle COORDINATE_ORDER = fn("hsq_coordinate_order", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle JOIN_NAMES = fn("hsq_join_names", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle GATHER_ROWS = fn("hsq_gather_rows", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS,
             ADDRESS, JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG));
@@ -209,6 +210,9 @@ public final class HsqB200 implements AutoCloseable {
     public void samMappedRecords(MemorySegment text, long nBytes, MemorySegment contigNames, MemorySegment samRecordsOut) {
         check(invokeInt(SAM_MAPPED_RECORDS, ctx, text, nBytes, contigNames, samRecordsOut));
     }
+
+    /** Order of the final coordinate sort (…Identification.java:897, SAMRecordCoordinateComparator); coordSortIn = hsq_coord_sort_in, order = int32[n]. */
+    public void coordinateOrder(MemorySegment coordSortIn, MemorySegment order) { check(invokeInt(COORDINATE_ORDER, ctx, coordSortIn, order)); }
 
     /** Both sorts and the merge loop of FastqAndBamFileMerger.createBamFileWithDataFromRawFastqFiles (FastqAndBamFileMerger.java:107-158,
      *  213-345); nameJoin = hsq_name_join, nameJoinOut = hsq_name_join_out.  The status codes map back to the exceptions of the loop:
