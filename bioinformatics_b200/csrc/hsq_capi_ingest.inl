@@ -3,6 +3,10 @@
 //   hsq_join_names  : FastqAndBamFileMerger.createBamFileWithDataFromRawFastqFiles without the codecs
 //                     (HSQ/process/FastqAndBamFileMerger.java:107-158, MergedSamIterator :213-345, trim check :65-94,366-373)
 //   hsq_gather_rows : the raw read / quality strings the merged records take (:386-396)
+//   hsq_index_sam / hsq_sam_mapped_records : the SAMRecord getters of the merge and of ReadToProbeAssigner.assignProbesToReads over SAM
+//                     text (...Identification.java:439-474; XA entries as HSQ/utils/SAMRecordUtil.java:440-468 keeps them)
+//   hsq_trim_fastq  : FastqReadTrimmer.trimReads, the file loop of `HSQutils trim`, text to text (HSQ/process/FastqReadTrimmer.java:262-307)
+//   hsq_coordinate_order : order of the final coordinate sort (...Identification.java:897, htsjdk SAMRecordCoordinateComparator)
 // The reference's merge is a sequential two-cursor loop over two sorted iterators.  Here both sides are sorted on the device
 // (LSD radix over big-endian 8-byte chunks of the zero-padded keys = String.compareTo for ASCII), and the loop becomes, for
 // the j-th primary SAM record in sorted order with unique id s:  c = number of earlier not-first-of-pair records with the

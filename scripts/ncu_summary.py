@@ -3,9 +3,10 @@ import collections, csv, subprocess, sys
 
 def launches(path):
     rows = [r for r in csv.reader(open(path)) if len(r) > 10]
-    h = rows[0]; ki = h.index('Kernel Name'); vi = h.index('Metric Value')
+    h = rows[0]; ki = h.index('Kernel Name'); vi = h.index('Metric Value'); mi = h.index('Metric Name')
     agg = collections.defaultdict(lambda: [0, 0.0])
     for r in rows[1:]:
+        if r[mi] != 'gpu__time_duration.sum': continue  # lists taken with several metrics: time only
         try: v = float(r[vi].replace(',', ''))
         except ValueError: continue
         k = r[ki].split('(')[0][-48:]

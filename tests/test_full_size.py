@@ -114,3 +114,36 @@ def test_trim_full_size_config1():
             # trimming the result with a window that covers it is the identity
             seq2, _ = ctx.trim_batch(seq, qual, 0, keep - 1, True)
             assert (seq2.data == seq.data).all()
+
+
+@pytest.mark.gpu
+def test_ingest_full_size():
+    """f2 at a size where every scan spans many tiles and the string sorts run over > 2^19 records: 400 k read pairs, both FASTQ texts indexed,
+    ~730 k SAM lines indexed and joined, all equal to the CPU oracle; then size-independent properties of the join."""
+    from bioinformatics_b200 import synth
+    from bioinformatics_b200._lib import Context
+    from bioinformatics_b200.batches import NameJoinHost
+    from oracle import oracle as O
+    case = synth.make_ingest_case(400000, read_len=100, seed=41, trim=(10, 89, 0, 89))
+    sam_text = synth.sam_text_of(case, seed=42, xa_rate=0.1)
+    with Context(0) as ctx:
+        for text in (case["fq1_text"], case["fq2_text"]):
+            g, e = ctx.index_fastq(text), O.index_fastq(text)
+            assert g.n == e.n == 400000 and all((g.head()[f] == e.head()[f]).all() for f in g.FIELDS)
+        gs, es = ctx.index_sam(sam_text), O.index_sam(sam_text)
+        assert gs.n == es.n == len(case["sam_names"]) and all((getattr(gs, c) == getattr(es, c)).all() for c in gs.columns())
+        join = NameJoinHost(case["sam_names"], gs.flag, gs.seq_len, case["fq1_headers"], case["fq2_headers"], case["fq_seq_len"], case["fq_seq_len"],
+                            sam_qual_len=gs.qual_len, r1_first=10, r1_stop=89, r2_first=0, r2_stop=89)
+        g, e = ctx.join_names(join), O.join_names(join)
+        assert g.n_emitted == e.n_emitted and g.total_matching_pairs == e.total_matching_pairs
+        assert all((a == b).all() for a, b in zip(g.emitted(), e.emitted())) and (g.status == e.status).all()
+        rec, fq, _ = g.emitted()
+        # every returned record carries the FASTQ ordinal of its own name; the iterator's order is the order of the names
+        ids = np.array(case["ids"])
+        names = np.array(case["sam_names"])
+        assert (names[rec] == ids[fq]).all()
+        assert (names[rec][1:] >= names[rec][:-1]).all()
+        # idempotence: joining only the returned records returns all of them, in the same order
+        again = NameJoinHost(list(names[rec]), gs.flag[rec], gs.seq_len[rec], case["fq1_headers"], case["fq2_headers"], check_trim=False)
+        g2 = ctx.join_names(again)
+        assert g2.n_emitted == len(rec) and (g2.emitted()[0] == np.arange(len(rec))).all() and (g2.emitted()[1] == fq).all()
