@@ -337,7 +337,7 @@ def next_row_numbers(ctx, probes, pairs, res):
     f1_, s1_, f2_, s2_ = case["trim"]
     join = NameJoinHost(case["sam_names"], case["sam_flags"], case["sam_seq_len"], case["fq1_headers"], case["fq2_headers"], case["fq_seq_len"],
                         case["fq_seq_len"], r1_first=f1_, r1_stop=s1_, r2_first=f2_, r2_stop=s2_)
-    ing = {"read_pairs": n_ing, "sam_lines": int(join.n), "host_buffers": "text in pinned memory, index arrays pageable"}
+    ing = {"read_pairs": n_ing, "sam_lines": int(join.n), "host_buffers": "text and index arrays in pinned memory"}
 
     def pinned_text(t):
         a = ctx.pinned_array(len(t))
@@ -346,7 +346,9 @@ def next_row_numbers(ctx, probes, pairs, res):
 
     for key, gpu_fn, cpu_fn, text in (("index_fastq", ctx.index_fastq, O.index_fastq, case["fq1_text"]), ("index_sam", ctx.index_sam, O.index_sam, sam_text)):
         ptext = pinned_text(text)
-        dt, g = timed(lambda: gpu_fn(ptext))
+        from bioinformatics_b200.batches import FastqIndexResult, SamIndexResult
+        res_out = (FastqIndexResult(n_ing + 8, ctx.pinned_array) if key == "index_fastq" else SamIndexResult(join.n + 8, ctx.pinned_array))
+        dt, g = timed(lambda: gpu_fn(ptext, out=res_out))
         ms_dev = ctx.last_timing()[0]
         t0 = time.perf_counter()
         c = cpu_fn(text)

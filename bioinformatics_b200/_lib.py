@@ -225,12 +225,12 @@ class Context:
         self._check(self.lib.hsq_assign_probes(self.h, C.byref(rc), C.byref(oc)))
         return out
 
-    def index_fastq(self, text, cap=None):
-        """hsq_index_fastq: record index of FASTQ text (htsjdk FastqReader grammar)."""
+    def index_fastq(self, text, cap=None, out=None):
+        """hsq_index_fastq: record index of FASTQ text (htsjdk FastqReader grammar).  out: a FastqIndexResult to fill (e.g. pinned)."""
         text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
         if cap is None:
             cap = len(text) // 8 + 1  # a record is at least "@x\nA\n+\nI\n"
-        out = FastqIndexResult(cap)
+        out = out or FastqIndexResult(cap)
         oc = out.c()
         self._check(self.lib.hsq_index_fastq(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(oc)))
         out.n = int(oc.n)
@@ -245,12 +245,12 @@ class Context:
                                             C.c_int32(1 if three_prime else 0), A.ptr(out, A.u8p), C.c_int64(len(out)), C.byref(nb), C.byref(nrec)))
         return out[:nb.value], int(nrec.value)
 
-    def index_sam(self, text, cap=None):
-        """hsq_index_sam: field index of SAM text (the columns the dedup path reads off a SAMRecord)."""
+    def index_sam(self, text, cap=None, out=None):
+        """hsq_index_sam: field index of SAM text (the columns the dedup path reads off a SAMRecord).  out: a SamIndexResult to fill."""
         text = np.frombuffer(text, dtype=np.uint8) if isinstance(text, (bytes, bytearray)) else np.ascontiguousarray(text, dtype=np.uint8)
         if cap is None:
             cap = len(text) // 22 + 1  # an alignment line is at least 11 one-byte columns, 10 tabs and a line feed
-        out = SamIndexResult(cap)
+        out = out or SamIndexResult(cap)
         oc = out.c()
         self._check(self.lib.hsq_index_sam(self.h, A.ptr(text, A.u8p), C.c_int64(len(text)), C.byref(oc)))
         return out.take(oc)

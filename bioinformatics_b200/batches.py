@@ -376,14 +376,13 @@ class FindMatchResult:
 class FastqIndexResult:
     """hsq_fastq_index with host arrays: where header, bases and qualities of every record sit in the FASTQ text."""
 
-    def __init__(self, cap):
+    def __init__(self, cap, alloc=None):
+        """alloc(nbytes) -> uint8 array, e.g. Context.pinned_array (default: pageable numpy memory)."""
         self.cap, self.n = int(cap), 0
-        self.header_off = np.zeros(cap, dtype=np.int64)
-        self.header_len = np.zeros(cap, dtype=np.int32)
-        self.seq_off = np.zeros(cap, dtype=np.int64)
-        self.seq_len = np.zeros(cap, dtype=np.int32)
-        self.qual_off = np.zeros(cap, dtype=np.int64)
-        self.qual_len = np.zeros(cap, dtype=np.int32)
+        new = lambda dt: (np.zeros(cap, dtype=dt) if alloc is None else alloc(cap * np.dtype(dt).itemsize).view(dt))
+        self.header_off, self.header_len = new(np.int64), new(np.int32)
+        self.seq_off, self.seq_len = new(np.int64), new(np.int32)
+        self.qual_off, self.qual_len = new(np.int64), new(np.int32)
 
     def c(self):
         return A.FastqIndex(self.cap, 0, A.ptr(self.header_off, A.i64p), A.ptr(self.header_len, A.i32p), A.ptr(self.seq_off, A.i64p),
@@ -398,10 +397,16 @@ class FastqIndexResult:
 class SamIndexResult:
     """hsq_sam_index with host planes; `<field>_off`, `<field>_len` and the numeric columns as attributes after take()."""
 
-    def __init__(self, cap):
+    def __init__(self, cap, alloc=None):
+        """alloc(nbytes) -> uint8 array, e.g. Context.pinned_array (default: pageable numpy memory)."""
         self.cap, self.n, self.n_header_lines = int(cap), 0, 0
-        self.off = np.zeros((len(A.SAM_FIELDS), self.cap), dtype=np.int64)
-        self.val = np.zeros((len(A.SAM_FIELDS) + len(A.SAM_VALUES), self.cap), dtype=np.int32)
+        nf, nv = len(A.SAM_FIELDS), len(A.SAM_FIELDS) + len(A.SAM_VALUES)
+        if alloc is None:
+            self.off = np.zeros((nf, self.cap), dtype=np.int64)
+            self.val = np.zeros((nv, self.cap), dtype=np.int32)
+        else:
+            self.off = alloc(nf * self.cap * 8).view(np.int64).reshape(nf, self.cap)
+            self.val = alloc(nv * self.cap * 4).view(np.int32).reshape(nv, self.cap)
 
     def c(self):
         return A.SamIndex(self.cap, 0, 0, A.ptr(self.off, A.i64p), A.ptr(self.val, A.i32p))
