@@ -54,12 +54,13 @@ class ClockSampler:
     def __init__(self, index):
         self.index = index
         self.proc = None
-        self.lines = []
+        self.lines = []   # (arrival time, line)
+        self.t_mark = None
 
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
         except Exception:
@@ -67,11 +68,26 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
+
+    def wait_first(self, timeout=5.0):
+        """nvidia-smi needs a few hundred ms to come up (more on an 8-GPU box): start it before the warm-up and wait for a sample."""
+        t0 = time.perf_counter()
+        while self.proc and not self.lines and time.perf_counter() - t0 < timeout:
+            time.sleep(0.02)
+
+    def mark(self):
+        """The timed region starts now: samples that arrive from here on are the ones reported."""
+        self.t_mark = time.perf_counter()
 
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        if self.t_mark is not None and not any(t >= self.t_mark for t, _ in self.lines):
+            t0 = time.perf_counter()  # region shorter than one sampling period: take the sample that is about to arrive as well
+            n0 = len(self.lines)
+            while len(self.lines) == n0 and time.perf_counter() - t0 < 0.3:
+                time.sleep(0.01)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
@@ -79,7 +95,12 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        inside = [ln for t, ln in self.lines if self.t_mark is None or t >= self.t_mark]
+        note = None
+        if self.t_mark is not None and len(inside) <= 1 and len(self.lines) >= 2 and not any(t >= self.t_mark for t, _ in self.lines[:-1]):
+            inside = [ln for _, ln in self.lines[-2:]]  # region shorter than the 50 ms sampling period: the samples on either side of it
+            note = "timed region shorter than the sampling period: the samples just before and just after it"
+        for ln in inside:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -91,8 +112,11 @@ class ClockSampler:
             for k, nm in enumerate(names):
                 if f[3 + k].lower().startswith("active"):
                     reasons.add(nm)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        out = {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+               "reasons": sorted(reasons), "samples": len(sm)}
+        if note:
+            out["note"] = note
+        return out
 
 
 def make_workload(n_pairs, rank):
@@ -521,6 +545,9 @@ def main():
     # ---- resident leg: batch staged once, K timed passes of the kernels --------------------------------------
     ctx.extend_stage(pairs)
     launches_per_step = 0
+    sampler = ClockSampler(local)
+    sampler.start()
+    sampler.wait_first()
     for _ in range(max(3, args.warmup)):
         ctx.extend_run(CIGAR_CAP, MD_CAP)
         launches_per_step = ctx.last_timing()[1]
@@ -539,9 +566,8 @@ def main():
             h.update(np.where(m, np.asarray(txt).reshape(-1, cap), 0).astype(np.uint8).tobytes())
         return h.hexdigest()
     digest_resident = digest(out)
-    sampler = ClockSampler(local)
     barrier()
-    sampler.start()
+    sampler.mark()
     ctx.timer_start()
     for _ in range(args.steps):
         ctx.extend_run(CIGAR_CAP, MD_CAP)
