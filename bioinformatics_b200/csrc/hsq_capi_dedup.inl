@@ -11,22 +11,6 @@
 #include "hsq_scan.cuh"
 namespace hsq {
 
-// this lane's share of the sum of the bytes [b, b + len) of a cudaMalloc'ed buffer: aligned 32-bit words (the bytes outside the range are
-// masked off the first and last word), four bytes per __vsadu4 instead of one byte per load (the buffers end with >= 16 spare bytes)
-__device__ inline int warp_byte_sum(const uint8_t* __restrict__ buf, int64_t b, int len, int lane) {
-    const uint32_t* __restrict__ words = reinterpret_cast<const uint32_t*>(buf);
-    const int64_t end = b + len, w1 = (end + 3) >> 2;
-    int sum = 0;
-    for (int64_t w = (b >> 2) + lane; w < w1; w += 32) {
-        uint32_t v = words[w];
-        const int64_t byte0 = w << 2;
-        if (byte0 < b) v &= 0xFFFFFFFFu << (8 * (int)(b - byte0));             // little endian: the low bytes come first
-        if (byte0 + 4 > end) v &= (1u << (8 * (int)(end - byte0))) - 1u;       // 1 .. 3 bytes of the last word
-        sum += (int)__vsadu4(v, 0u);
-    }
-    return sum;
-}
-
 __global__ void dedup_keygen_kernel(const uint8_t* __restrict__ r1, const int64_t* __restrict__ off1, const uint8_t* __restrict__ q1,
                                     const uint8_t* __restrict__ r2, const int64_t* __restrict__ off2, const uint8_t* __restrict__ q2,
                                     const int32_t* __restrict__ read_index, int64_t n, int u, int v, uint64_t* __restrict__ uid_out,
@@ -37,9 +21,10 @@ __global__ void dedup_keygen_kernel(const uint8_t* __restrict__ r1, const int64_
     for (; w < n; w += stride) {
         const int64_t b1 = off1[w], b2 = off2[w];
         const int l1 = (int)(off1[w + 1] - b1), l2 = (int)(off2[w + 1] - b2);
-        int sum = warp_byte_sum(q1, b1, l1, lane) + warp_byte_sum(q2, b2, l2, lane);
+        int sum = 0;  // byte loads: an aligned-word + __vsadu4 variant of these two loops measured 300 us against 178 us (r1_o)
+        for (int i = lane; i < l1; i += 32) sum += (int)q1[b1 + i] - 33;
+        for (int i = lane; i < l2; i += 32) sum += (int)q2[b2 + i] - 33;
         for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        sum -= 33 * (l1 + l2);
         // UID bases: lane i < u reads R1[i], lane u <= i < u+v reads R2[i-u]   (u + v <= 32)
         uint64_t code = 0;
         bool bad = false, short_read = false;
