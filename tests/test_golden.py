@@ -163,3 +163,43 @@ def test_cuda_reference_kats_and_frozen_vectors():
         _check_extend(ctx.extend_batch(pairs, cigar_cap=64, md_cap=96))
         clean, _ = synth.drop_n_pairs(pairs)
         _check_dedup(*ctx.dedup_batch(clean, 10, 0, probes.n))
+
+
+# ---- f2 / f4 frozen vectors (tests/golden/ingest_vectors.json, generator: tests/golden/make_golden_ingest.py) ------------------------------
+def _ingest_checks(be):
+    import json
+    import os
+    from bioinformatics_b200.batches import NameJoinHost
+    v = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ingest_vectors.json")))
+    fq1, sam, merged = v["fq1_text"].encode(), v["sam_text"].encode(), v["merged_sam_text"].encode()
+    ix = be.index_fastq(fq1)
+    assert all(ix.head()[f].tolist() == v["fastq_index"][f] for f in ix.FIELDS)
+    t, n = be.trim_fastq(fq1, v["trim_fastq"]["first"], v["trim_fastq"]["last"], v["trim_fastq"]["three_prime"])
+    assert n == v["trim_fastq"]["records"] and t.tobytes().decode() == v["trim_fastq"]["text"]
+    sx = be.index_sam(sam)
+    assert sx.n_header_lines == v["sam_index"]["n_header_lines"] and all(getattr(sx, c).tolist() == v["sam_index"][c] for c in sx.columns())
+    r = be.sam_mapped_records(merged, v["contigs"])
+    want = v["sam_mapped_records"]
+    assert all(getattr(r, c)[:r.n].tolist() == want[c] for c in r.COLUMNS) and r.alt_offsets[:r.n + 1].tolist() == want["alt_offsets"]
+    assert all(getattr(r, c)[:r.n_alt].tolist() == want[c] for c in r.ALT_COLUMNS)
+    j = v["join"]
+    f1, s1, f2, s2 = v["trim"]
+    res = be.join_names(NameJoinHost(j["sam_names"], j["sam_flags"], j["sam_seq_len"], j["fq1_headers"], j["fq2_headers"], j["fq_seq_len"], j["fq_seq_len"],
+                                     r1_first=f1, r1_stop=s1, r2_first=f2, r2_stop=s2))
+    assert [x.tolist() for x in res.emitted()] == [j["sam_record"], j["fastq_record"], j["name_len"]]
+    assert res.status.tolist() == j["status"] and res.total_matching_pairs == j["total_matching_pairs"]
+    c = v["coordinate_order"]
+    assert be.coordinate_order(*c["columns"], c["names"]).tolist() == c["order"]
+
+
+def test_oracle_frozen_ingest_vectors():
+    import types
+    _ingest_checks(types.SimpleNamespace(index_fastq=O.index_fastq, trim_fastq=O.trim_fastq, index_sam=O.index_sam, sam_mapped_records=O.sam_mapped_records,
+                                         join_names=O.join_names, coordinate_order=O.coordinate_order))
+
+
+@pytest.mark.gpu
+def test_cuda_frozen_ingest_vectors():
+    from bioinformatics_b200._lib import Context
+    with Context(0) as ctx:
+        _ingest_checks(ctx)
