@@ -150,7 +150,7 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_kernel(const uint
                                                                       const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank,
                                                                       uint8_t* __restrict__ is_best, int32_t* __restrict__ group_size,
                                                                       int32_t* __restrict__ unique_pairs, int32_t* __restrict__ duplicate_pairs,
-                                                                      int32_t* __restrict__ max_pairs) {
+                                                                      int32_t* __restrict__ max_pairs, int skip_up_to) {
     extern __shared__ __align__(16) unsigned char dedup_smem[];
     // per pair: its UID and its table slot; per table slot (2 x cap of them): claiming pair + 1, best rank, best pair, pairs
     uint64_t* s_uid = reinterpret_cast<uint64_t*>(dedup_smem);
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_kernel(const uint
     for (int64_t p = blockIdx.x; p < np; p += gridDim.x) {
         const int64_t b = start[p];
         const int m = (int)(start[p + 1] - b);
-        if (m == 0) continue;  // block-uniform
+        if (m <= skip_up_to) continue;  // block-uniform: empty probes, and the small ones dedup_group_small_kernel takes
         int table = 64;
         while (table < 2 * m) table <<= 1;
         const unsigned mask = (unsigned)table - 1u;
@@ -226,6 +226,61 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_kernel(const uint
             max_pairs[p] = s_max;
         }
         __syncthreads();
+    }
+}
+
+// probes with at most 32 pairs: one warp per probe, one pair per lane; the pairs of a UID find each other with __match_any_sync, the
+// (rank, pair) columns of the warp sit in shared memory so every lane can look at its peers
+static constexpr int DEDUP_SMALL_MAX = 32;
+__global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_small_kernel(const uint32_t* __restrict__ seg, const int64_t* __restrict__ start, int64_t np,
+                                                                            const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank,
+                                                                            uint8_t* __restrict__ is_best, int32_t* __restrict__ group_size,
+                                                                            int32_t* __restrict__ unique_pairs, int32_t* __restrict__ duplicate_pairs,
+                                                                            int32_t* __restrict__ max_pairs) {
+    __shared__ uint64_t s_rank[DEDUP_SEG_BLOCK / 32][32];
+    __shared__ uint32_t s_idx[DEDUP_SEG_BLOCK / 32][32];
+    const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    int64_t p = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; p < np; p += stride) {
+        const int64_t b = start[p];
+        const int m = (int)(start[p + 1] - b);
+        if (m == 0 || m > DEDUP_SMALL_MAX) continue;  // warp-uniform; larger probes belong to dedup_group_kernel
+        const bool active = lane < m;
+        const unsigned amask = __ballot_sync(0xffffffffu, active);
+        uint32_t i = 0;
+        uint64_t u = 0, r = 0;
+        if (active) {
+            i = seg[b + lane];
+            u = uid[i];
+            r = rank[i];
+            s_rank[wib][lane] = r;
+            s_idx[wib][lane] = i;
+        }
+        __syncwarp();
+        int size = 0;
+        bool leader = false;
+        if (active) {
+            const unsigned peers = __match_any_sync(amask, u);
+            size = __popc(peers);
+            leader = lane == __ffs(peers) - 1;
+            bool best = true;  // smallest rank, then smallest pair index, among the pairs of this UID
+            for (unsigned q = peers & ~(1u << lane); q; q &= q - 1) {
+                const int o = __ffs(q) - 1;
+                const uint64_t ro = s_rank[wib][o];
+                if (ro < r || (ro == r && s_idx[wib][o] < i)) best = false;
+            }
+            is_best[i] = best ? 1 : 0;
+            group_size[i] = size;
+        }
+        const int groups = __popc(__ballot_sync(0xffffffffu, leader));
+        for (int o = 16; o > 0; o >>= 1) size = max(size, __shfl_xor_sync(0xffffffffu, size, o));
+        if (lane == 0) {  // FilterByUid.java:149-171,251
+            unique_pairs[p] = groups;
+            duplicate_pairs[p] = m - groups;
+            max_pairs[p] = size;
+        }
+        __syncwarp();  // the shared rows are rewritten by the next probe
     }
 }
 
@@ -374,8 +429,14 @@ int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_
             HSQ_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dedup_group_kernel, DEDUP_SEG_BLOCK, smem));
             const int sblocks = (int)std::max<int64_t>(1, std::min<int64_t>(np, (int64_t)ctx->sm_count * std::max(per_sm, 1)));
             dedup_scatter_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, start, ia, ib);
-            dedup_group_kernel<<<sblocks, DEDUP_SEG_BLOCK, smem, ctx->stream>>>(ib, start, np, cap, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
+            const int wblocks = (int)std::max<int64_t>(1, std::min<int64_t>((np + 7) / 8, (int64_t)ctx->sm_count * 8));
+            dedup_group_small_kernel<<<wblocks, DEDUP_SEG_BLOCK, 0, ctx->stream>>>(ib, start, np, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
             ctx->launches += 2;
+            if (max_count > DEDUP_SMALL_MAX) {
+                dedup_group_kernel<<<sblocks, DEDUP_SEG_BLOCK, smem, ctx->stream>>>(ib, start, np, cap, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np,
+                                                                                   DEDUP_SMALL_MAX);
+                ctx->launches++;
+            }
             HSQ_CUDA(ctx, cudaGetLastError());
             return HSQ_OK;
         }
