@@ -62,6 +62,35 @@ class AlignOut(C.Structure):
                 ("md_len", i32p), ("md", u8p), ("rmd_len", i32p), ("rmd", u8p), ("overflow", u8p), ("cells", C.c_int64), ("find_counts", i32p)]
 
 
+u32p = C.POINTER(C.c_uint32)
+i16p = C.POINTER(C.c_int16)
+
+
+class PackedReads(C.Structure):
+    _fields_ = [("bits", C.c_int32), ("n", C.c_int64), ("data", u8p), ("len", i32p), ("n_exceptions", C.c_int64), ("exc_read", u32p),
+                ("exc_pos", u32p), ("exc_char", u8p)]
+
+
+class PackedPairs(C.Structure):
+    _fields_ = [("n", C.c_int64), ("probe_id", i32p), ("read_index", i32p), ("r1", PackedReads), ("r2", PackedReads), ("q1", u8p), ("q2", u8p),
+                ("qsum1", i16p), ("qsum2", i16p)]
+
+
+class ExtendPooledOut(C.Structure):
+    _fields_ = [("cigar_cap", C.c_int32), ("md_cap", C.c_int32), ("ok", u8p), ("primer_end", i32p), ("score", i32p), ("pos", i32p),
+                ("read_start", i32p), ("read_stop", i32p), ("nm", i32p), ("tlen", i32p), ("cigar_len", i32p), ("md_len", i32p),
+                ("str_off", i64p), ("pool", u8p), ("pool_cap", C.c_int64), ("pool_bytes", C.c_int64), ("pair_ok", u8p), ("cells", C.c_int64)]
+
+
+class Config(C.Structure):
+    _fields_ = [("struct_bytes", C.c_int32), ("force_dp32", C.c_int32), ("force_dedup_radix", C.c_int32), ("extend_chunks", C.c_int32),
+                ("uniform_chunks", C.c_int32), ("band", C.c_int32)]
+
+    def __init__(self, **kw):
+        super().__init__(**kw)
+        self.struct_bytes = C.sizeof(Config)
+
+
 class ProbeStats(C.Structure):
     _fields_ = [("n_probes", C.c_int64), ("unique_pairs", i32p), ("duplicate_pairs", i32p), ("max_pairs_per_uid", i32p)]
 

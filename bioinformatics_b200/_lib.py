@@ -9,7 +9,7 @@ import os
 import numpy as np
 
 from . import _abi as A
-from .batches import (SamRecordsResult, SamIndexResult, FastqIndexResult, NameJoinHost, NameJoinResult, AlignResult, AssignResult, FindResult, FindMatchResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
+from .batches import (PackedReadsHost, PackedPairsHost, PooledExtendResult, SamRecordsResult, SamIndexResult, FastqIndexResult, NameJoinHost, NameJoinResult, AlignResult, AssignResult, FindResult, FindMatchResult, DedupExtendResult, ExtendResult, RecordResult, MappedRecordsHost, PairBatchHost, ProbeRangesHost, ProbeStatsHost,
                       ProbeTableHost, merge_args, scorer)
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
@@ -21,7 +21,10 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_extend_batch", "hsq_resolve_multi_probe", "hsq_extend_stage", "hsq_extend_run", "hsq_extend_fetch",
            "hsq_timer_start", "hsq_timer_stop", "hsq_int32_peak", "hsq_dedup_keys", "hsq_dedup_reduce_keys", "hsq_merge_pairs",
            "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs",
-           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order")
+           "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order",
+           "hsq_ctx_create_ex", "hsq_ctx_configure", "hsq_packed_bytes", "hsq_pack_reads", "hsq_quality_sums", "hsq_unpack_reads",
+           "hsq_extend_packed")
+_NOT_STATUS = {"hsq_last_error": C.c_char_p, "hsq_version": C.c_char_p, "hsq_ctx_destroy": None, "hsq_packed_bytes": C.c_int64}
 
 
 def _coord_args(ref_index, pos, flags, mapq, mate_ref_index, mate_pos, tlen, names):
@@ -49,19 +52,61 @@ def load():
         lib.hsq_ctx_destroy.restype = None
         lib.hsq_ctx_destroy.argtypes = [C.c_void_p]
         for name in EXPORTS:
-            if name not in ("hsq_last_error", "hsq_version", "hsq_ctx_destroy"):
-                getattr(lib, name).restype = C.c_int32
+            getattr(lib, name).restype = _NOT_STATUS.get(name, C.c_int32)
         _lib = lib
     return _lib
+
+
+def pack_reads(reads, bits=2, alloc=None, threads=0):
+    """hsq_pack_reads (host helper of the library, no device): SeqBatch -> PackedReadsHost.  alloc(nbytes) -> uint8 array (e.g. pinned)."""
+    lib = load()
+    reads = reads if isinstance(reads, A.SeqBatch) else A.SeqBatch.from_strings(reads)
+    alloc = alloc or (lambda nbytes: np.zeros(nbytes, dtype=np.uint8))
+    nbytes = int(lib.hsq_packed_bytes(A.ptr(reads.offsets, A.i64p), C.c_int64(reads.n), C.c_int32(bits)))
+    if nbytes < 0:
+        raise HsqError(A.HSQ_ERR_INVALID_ARGUMENT, "hsq_packed_bytes: bad arguments")
+    data = alloc(max(nbytes, 4))[:max(nbytes, 4)]
+    lens = alloc(4 * max(reads.n, 1)).view(np.int32)[:reads.n]
+    n_exc = C.c_int64(0)
+    rc_ = reads.c()
+    cap = 0
+    exc = (None, None, None)
+    while True:
+        st = lib.hsq_pack_reads(C.byref(rc_), C.c_int32(bits), A.ptr(data, A.u8p), A.ptr(lens, A.i32p), C.c_int64(cap), C.byref(n_exc),
+                                A.ptr(exc[0], A.u32p), A.ptr(exc[1], A.u32p), A.ptr(exc[2], A.u8p), C.c_int32(threads))
+        if st == A.HSQ_ERR_OVERFLOW and n_exc.value > cap:  # size the exception arrays and pack again
+            cap = int(n_exc.value)
+            exc = (alloc(4 * cap).view(np.uint32)[:cap], alloc(4 * cap).view(np.uint32)[:cap], alloc(cap)[:cap])
+            continue
+        if st != 0:
+            raise HsqError(st, lib.hsq_last_error(None).decode())
+        break
+    k = int(n_exc.value)
+    return PackedReadsHost(bits, data[:nbytes], lens, *(None if e is None else e[:k] for e in exc))
+
+
+def quality_sums(quals, threads=0):
+    """hsq_quality_sums (host helper): (short) sum(q - 33) per read of a quality SeqBatch."""
+    lib = load()
+    out = np.zeros(quals.n, dtype=np.int16)
+    st = lib.hsq_quality_sums(A.ptr(quals.data, A.u8p), A.ptr(quals.offsets, A.i64p), C.c_int64(quals.n), A.ptr(out, A.i16p), C.c_int32(threads))
+    if st != 0:
+        raise HsqError(st, lib.hsq_last_error(None).decode())
+    return out
 
 
 class Context:
     """One hsq_ctx (one GPU)."""
 
-    def __init__(self, device=0, scorer_=None):
+    def __init__(self, device=0, scorer_=None, config=None):
+        """config: dict of hsq_config fields (force_dp32, force_dedup_radix, extend_chunks, uniform_chunks, band)."""
         self.lib = load()
         h = C.c_void_p()
-        st = self.lib.hsq_ctx_create(C.c_int32(device), C.byref(h))
+        if config:
+            cfg = A.Config(**config)
+            st = self.lib.hsq_ctx_create_ex(C.c_int32(device), C.byref(cfg), C.byref(h))
+        else:
+            st = self.lib.hsq_ctx_create(C.c_int32(device), C.byref(h))
         if st != 0:
             raise HsqError(st, self.lib.hsq_last_error(None).decode())
         self.h = h
@@ -93,6 +138,31 @@ class Context:
     def _check(self, st):
         if st != 0:
             raise HsqError(st, self.lib.hsq_last_error(self.h).decode())
+
+    def configure(self, **config):
+        cfg = A.Config(**config)
+        self._check(self.lib.hsq_ctx_configure(self.h, C.byref(cfg)))
+
+    def pack_reads(self, reads, bits=2, pinned=False, threads=0):
+        return pack_reads(reads, bits, alloc=self.pinned_array if pinned else None, threads=threads)
+
+    def unpack_reads(self, packed):
+        """hsq_unpack_reads: packed words -> upper-case ASCII on the device (round-trip check of the packed layout)."""
+        total = int(packed.len.sum())
+        data = np.zeros(max(total, 1), dtype=np.uint8)
+        off = np.zeros(packed.n + 1, dtype=np.int64)
+        pc = packed.c()
+        self._check(self.lib.hsq_unpack_reads(self.h, C.byref(pc), A.ptr(data, A.u8p), A.ptr(off, A.i64p)))
+        return A.SeqBatch(data[:total], off)
+
+    def extend_packed(self, pairs, out=None, pool_cap=None, fields=None, cigar_cap=0, md_cap=0):
+        """hsq_extend_packed: packed reads in, integer columns + CIGAR / MD pool out."""
+        out = out or PooledExtendResult(pairs.n, pool_cap if pool_cap is not None else 2 * pairs.n * 48, fields, cigar_cap=cigar_cap, md_cap=md_cap)
+        pc, oc = pairs.c(), out.c()
+        st = self.lib.hsq_extend_packed(self.h, C.byref(pc), C.byref(oc))
+        out.finish()
+        self._check(st)
+        return out
 
     def last_timing(self):
         ms, n = C.c_float(0), C.c_int32(0)

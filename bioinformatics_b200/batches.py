@@ -121,6 +121,92 @@ class ExtendResult:
         return A.slot_strings(self.md, self.md_len, self.md_cap)
 
 
+class PackedReadsHost:
+    """hsq_packed_reads: 2 / 4 bit words, lengths and (2 bit) the exception list.  Built by `_lib.pack_reads`."""
+
+    def __init__(self, bits, data, lens, exc_read=None, exc_pos=None, exc_char=None):
+        self.bits = bits
+        self.data = data
+        self.len = np.ascontiguousarray(lens, dtype=np.int32) if not isinstance(lens, np.ndarray) or lens.dtype != np.int32 else lens
+        self.n = len(self.len)
+        self.exc_read = np.zeros(0, dtype=np.uint32) if exc_read is None else exc_read
+        self.exc_pos = np.zeros(0, dtype=np.uint32) if exc_pos is None else exc_pos
+        self.exc_char = np.zeros(0, dtype=np.uint8) if exc_char is None else exc_char
+
+    @property
+    def nbytes(self):
+        return self.data.nbytes + self.len.nbytes + self.exc_read.nbytes + self.exc_pos.nbytes + self.exc_char.nbytes
+
+    def c(self):
+        ne = len(self.exc_read)
+        return A.PackedReads(self.bits, self.n, A.ptr(self.data, A.u8p), A.ptr(self.len, A.i32p), ne,
+                             A.ptr(self.exc_read if ne else None, A.u32p), A.ptr(self.exc_pos if ne else None, A.u32p),
+                             A.ptr(self.exc_char if ne else None, A.u8p))
+
+
+class PackedPairsHost:
+    """hsq_packed_pairs.  q1 / q2: quality bytes back to back in read order (numpy uint8) or None; qsum1 / qsum2: int16 or None."""
+
+    def __init__(self, probe_id, r1, r2, q1=None, q2=None, read_index=None, qsum1=None, qsum2=None):
+        self.probe_id = probe_id if isinstance(probe_id, np.ndarray) and probe_id.dtype == np.int32 else np.ascontiguousarray(probe_id, dtype=np.int32)
+        self.n = len(self.probe_id)
+        self.r1, self.r2, self.q1, self.q2, self.qsum1, self.qsum2 = r1, r2, q1, q2, qsum1, qsum2
+        self.read_index = None if read_index is None else np.ascontiguousarray(read_index, dtype=np.int32)
+
+    def c(self):
+        return A.PackedPairs(self.n, A.ptr(self.probe_id, A.i32p), A.ptr(self.read_index, A.i32p), self.r1.c(), self.r2.c(),
+                             A.ptr(self.q1, A.u8p), A.ptr(self.q2, A.u8p), A.ptr(self.qsum1, A.i16p), A.ptr(self.qsum2, A.i16p))
+
+
+class PooledExtendResult:
+    """hsq_extend_pooled_out for n pairs: integer columns (those named in `fields`; the others are not fetched) + the CIGAR / MD pool."""
+    FIELDS_I32 = ExtendResult.FIELDS_I32
+
+    def __init__(self, n, pool_cap, fields=None, alloc=None, cigar_cap=0, md_cap=0):
+        alloc = alloc or (lambda nbytes: np.zeros(nbytes, dtype=np.uint8))
+        self.n, self.pool_cap, self.cigar_cap, self.md_cap = n, pool_cap, cigar_cap, md_cap
+        want = set(fields) if fields is not None else set(self.FIELDS_I32) | {"ok", "pair_ok", "str_off"}
+        for f in self.FIELDS_I32:
+            setattr(self, f, alloc(8 * n).view(np.int32) if f in want else None)
+        self.ok = alloc(2 * n) if "ok" in want else None
+        self.pair_ok = alloc(n) if "pair_ok" in want else None
+        self.str_off = alloc(16 * n).view(np.int64) if "str_off" in want else None
+        self.pool = alloc(max(pool_cap, 1))
+        self.pool_bytes = 0
+        self.cells = 0
+        self._c = None
+
+    def nbytes(self):
+        """Bytes that cross PCIe towards the host per call (columns fetched + pool bytes used)."""
+        cols = [getattr(self, f) for f in self.FIELDS_I32 + ("ok", "pair_ok", "str_off")]
+        return sum(a.nbytes for a in cols if a is not None) + int(self.pool_bytes)
+
+    def c(self):
+        p = A.ptr
+        self._c = A.ExtendPooledOut(self.cigar_cap, self.md_cap, p(self.ok, A.u8p), p(self.primer_end, A.i32p), p(self.score, A.i32p),
+                                    p(self.pos, A.i32p), p(self.read_start, A.i32p), p(self.read_stop, A.i32p), p(self.nm, A.i32p),
+                                    p(self.tlen, A.i32p), p(self.cigar_len, A.i32p), p(self.md_len, A.i32p), p(self.str_off, A.i64p),
+                                    p(self.pool, A.u8p), self.pool_cap, 0, p(self.pair_ok, A.u8p), 0)
+        return self._c
+
+    def finish(self):
+        self.cells = int(self._c.cells)
+        self.pool_bytes = int(self._c.pool_bytes)
+        return self
+
+    def _strings(self, which):
+        off = self.str_off + (self.cigar_len if which == "md" else 0)
+        ln = self.md_len if which == "md" else self.cigar_len
+        buf = self.pool.tobytes()
+        return [buf[o:o + l].decode("ascii") for o, l in zip(off.tolist(), ln.tolist())]
+
+    def cigars(self):
+        return self._strings("cigar")
+
+    def mds(self):
+        return self._strings("md")
+
+
 class AlignResult:
     FIELDS_I32 = ("score", "n_cols", "first_q", "last_q", "first_r", "last_r", "matches", "mismatches",
                   "non_terminal_gaps", "edit_distance", "md_len", "rmd_len")

@@ -113,22 +113,7 @@ const char* hsq_version(void) { return "hsq-b200 0.1 (sm_100a)"; }
 
 const char* hsq_last_error(const hsq_ctx* ctx) { return ctx ? ctx->error.c_str() : g_create_error.c_str(); }
 
-int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) {
-    if (!out) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "out is null");
-    *out = nullptr;
-    int count = 0;
-    cudaError_t e = cudaGetDeviceCount(&count);
-    if (e != cudaSuccess || count == 0)
-        return fail(nullptr, HSQ_ERR_NO_DEVICE, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count is 0") +
-                                                    " (this library has no CPU fallback)");
-    if (device < 0 || device >= count) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "device index out of range");
-    cudaDeviceProp prop;
-    HSQ_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
-    if (prop.major < 10)
-        return fail(nullptr, HSQ_ERR_NO_DEVICE, std::string("device ") + prop.name + " is not sm_100 class; kernels are built for sm_100a only");
-    HSQ_CUDA(nullptr, cudaSetDevice(device));
-    hsq_ctx* ctx = new hsq_ctx();
-    ctx->device = device;
+static int ctx_init(hsq_ctx* ctx, const cudaDeviceProp& prop) {
     ctx->sm_count = prop.multiProcessorCount;
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
@@ -154,23 +139,63 @@ int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) {
     std::vector<double> tbl(POW95_N);
     for (int d = 0; d < POW95_N; d++) tbl[(size_t)d] = std::pow(0.95, (double)d);
     HSQ_CUDA(nullptr, cudaMemcpyToSymbol(c_pow95, tbl.data(), sizeof(double) * POW95_N));
-    const char* f32 = getenv("HSQ_FORCE_DP32");  // development / test switch: always use the 32-bit DP kernels
-    ctx->force_dp32 = f32 && f32[0] == '1';
-    const char* fdc = getenv("HSQ_DEDUP_CUB");
-    ctx->force_dedup_cub = fdc && fdc[0] == '1';
+    return HSQ_OK;
+}
+
+static int apply_config(hsq_ctx* ctx, const hsq_config* config) {
+    hsq_config c{};
+    if (config) {
+        if (config->struct_bytes <= 0 || config->struct_bytes > (int32_t)sizeof(hsq_config))
+            return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_config.struct_bytes must be sizeof(hsq_config) of the caller's header");
+        std::memcpy(&c, config, (size_t)config->struct_bytes);  // an older, shorter struct leaves the newer fields at their defaults
+    }
+    if (c.extend_chunks < 0 || c.band < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative value in hsq_config");
+    ctx->cfg = c;
+    return HSQ_OK;
+}
+
+int32_t hsq_ctx_create_ex(int32_t device, const hsq_config* config, hsq_ctx** out) {
+    if (!out) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "out is null");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail(nullptr, HSQ_ERR_NO_DEVICE, std::string("no CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "count is 0") +
+                                                    " (this library has no CPU fallback)");
+    if (device < 0 || device >= count) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "device index out of range");
+    cudaDeviceProp prop;
+    HSQ_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail(nullptr, HSQ_ERR_NO_DEVICE, std::string("device ") + prop.name + " is not sm_100 class; kernels are built for sm_100a only");
+    HSQ_CUDA(nullptr, cudaSetDevice(device));
+    hsq_ctx* ctx = new hsq_ctx();
+    ctx->device = device;
+    int rc = ctx_init(ctx, prop);
+    if (!rc && (rc = apply_config(ctx, config))) g_create_error = ctx->error;
+    if (rc) {  // nothing created so far may leak
+        hsq_ctx_destroy(ctx);
+        return rc;
+    }
     *out = ctx;
     return HSQ_OK;
+}
+
+int32_t hsq_ctx_create(int32_t device, hsq_ctx** out) { return hsq_ctx_create_ex(device, nullptr, out); }
+
+int32_t hsq_ctx_configure(hsq_ctx* ctx, const hsq_config* config) {
+    if (!ctx) return HSQ_ERR_INVALID_ARGUMENT;
+    return apply_config(ctx, config);
 }
 
 void hsq_ctx_destroy(hsq_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
-    cudaStreamSynchronize(ctx->stream);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     hsq::DevBuf* bufs[] = {&ctx->p_rev, &ctx->p_ext_start, &ctx->p_ext_stop, &ctx->p_lig_start, &ctx->p_lig_stop, &ctx->q1, &ctx->q2,
                            &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
                            &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
                            &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->rg_start, &ctx->rg_end,
-                           &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32, &ctx->fi_start, &ctx->fi_len, &ctx->fi_refs, &ctx->fi_size};
+                           &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32, &ctx->fi_start, &ctx->fi_len, &ctx->fi_refs, &ctx->fi_size, &ctx->pool_tmp, &ctx->pool_cursor, &ctx->pool_dev};
     for (auto* b : bufs) b->release();
     for (auto& b : ctx->ing) b.release();
     ctx->dd_seg.release();
@@ -183,23 +208,15 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
         ps.r1.release();
         ps.r2.release();
     }
-    cudaFreeHost(ctx->h_status);
-    cudaFreeHost(ctx->h_cells);
-    cudaEventDestroy(ctx->ev0);
-    cudaEventDestroy(ctx->ev1);
-    cudaEventDestroy(ctx->ev_user0);
-    cudaEventDestroy(ctx->ev_user1);
-    for (int k = 0; k < hsq_ctx::N_EXTEND_SETS; k++) {
-        cudaEventDestroy(ctx->ev_in[k]);
-        cudaEventDestroy(ctx->ev_prep[k]);
-        cudaEventDestroy(ctx->ev_cap[k]);
-        cudaEventDestroy(ctx->ev_out[k]);
-    }
-    for (int k = 0; k < 2; k++) cudaStreamDestroy(ctx->s_cap[k]);
-    cudaStreamDestroy(ctx->s_prep);
-    cudaStreamDestroy(ctx->s_in);
-    cudaStreamDestroy(ctx->s_out);
-    cudaStreamDestroy(ctx->stream);
+    if (ctx->h_status) cudaFreeHost(ctx->h_status);
+    if (ctx->h_cells) cudaFreeHost(ctx->h_cells);
+    for (cudaEvent_t ev : {ctx->ev0, ctx->ev1, ctx->ev_user0, ctx->ev_user1})
+        if (ev) cudaEventDestroy(ev);
+    for (int k = 0; k < hsq_ctx::N_EXTEND_SETS; k++)
+        for (cudaEvent_t ev : {ctx->ev_in[k], ctx->ev_prep[k], ctx->ev_cap[k], ctx->ev_out[k]})
+            if (ev) cudaEventDestroy(ev);
+    for (cudaStream_t st : {ctx->s_cap[0], ctx->s_cap[1], ctx->s_prep, ctx->s_in, ctx->s_out, ctx->stream})
+        if (st) cudaStreamDestroy(st);
     delete ctx;
 }
 
@@ -240,6 +257,7 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_merge.inl"
 #include "hsq_capi_resolve.inl"
 #include "hsq_capi_assign.inl"
+#include "hsq_capi_packed.inl"
 #include "hsq_capi_pipeline.inl"
 #include "hsq_capi_records.inl"
 #include "hsq_capi_find.inl"

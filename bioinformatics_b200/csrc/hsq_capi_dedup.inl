@@ -398,7 +398,7 @@ int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_
     uint32_t* ib = ia + nn;
     uint8_t* head = ctx->flags.as<uint8_t>();
     if (np) HSQ_CUDA(ctx, cudaMemsetAsync(d_stats, 0, 3 * (size_t)np * 4, ctx->stream));
-    if (n > 0 && np > 0 && !ctx->force_dedup_cub) {
+    if (n > 0 && np > 0 && !ctx->cfg.force_dedup_radix) {
         // segment path: counting sort by probe + one block per probe (hash group-by and reduce fused)
         const size_t nps = (size_t)np;
         const int64_t n_tiles = (np + 1 + SCAN_TILE - 1) / SCAN_TILE;

@@ -8,6 +8,9 @@ __global__ void check_probe_ids_kernel(const int32_t* __restrict__ probe_id, int
         if (probe_id[k] < 0 || probe_id[k] >= n_probes) atomicMin(status, HSQ_ERR_INVALID_ARGUMENT);
 }
 
+// ASCII -> codes, or packed words -> codes (hsq_capi_packed.inl), or nothing when the codes of the staged batch are already valid
+int prepare_codes(hsq_ctx* ctx, DevSeqsOwned* d, int* d_maxlen);
+
 int upload_pairs_raw(hsq_ctx* ctx, const hsq_pair_batch* pb) {
     int rc;
     const size_t n = (size_t)pb->n;
@@ -61,8 +64,8 @@ int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, Exte
     int read_max = host_read_max;
     if (host_read_max < 0) {
         if ((rc = reset_status(ctx))) return rc;
-        if ((rc = encode_seqs(ctx, &ctx->r1, d_status(ctx), d_maxlen(ctx, 0)))) return rc;
-        if ((rc = encode_seqs(ctx, &ctx->r2, d_status(ctx), d_maxlen(ctx, 1)))) return rc;
+        if ((rc = prepare_codes(ctx, &ctx->r1, d_maxlen(ctx, 0)))) return rc;
+        if ((rc = prepare_codes(ctx, &ctx->r2, d_maxlen(ctx, 1)))) return rc;
         if (n > 0) {
             int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
             check_probe_ids_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, ctx->n_probes, d_status(ctx));
@@ -73,8 +76,8 @@ int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, Exte
         if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend: ") + (w[0] == HSQ_ERR_INVALID_ARGUMENT ? "probe_id out of range" : status_message(w[0])));
         read_max = std::max(w[1], w[2]);
     } else {
-        if ((rc = encode_seqs(ctx, &ctx->r1, d_status(ctx), nullptr))) return rc;
-        if ((rc = encode_seqs(ctx, &ctx->r2, d_status(ctx), nullptr))) return rc;
+        if ((rc = prepare_codes(ctx, &ctx->r1, nullptr))) return rc;
+        if ((rc = prepare_codes(ctx, &ctx->r2, nullptr))) return rc;
     }
     const int primer_max = std::max(ctx->p_ext.max_len, ctx->p_lig.max_len);
     if (2 * primer_max + PRIMER_ALIGNMENT_BUFFER + 2 > POW95_N) return fail(ctx, HSQ_ERR_UNSUPPORTED, "primer longer than the 0.95^d table supports");
@@ -85,8 +88,8 @@ int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, Exte
     ScoreParams sp_user = make_score_params(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start);
     // packed u16x2 cells when every score fits 14 bits (always, for HSQUtils' scorers at these lengths), else 32-bit cells
     const int prefix_max = std::min(read_max, primer_max + PRIMER_ALIGNMENT_BUFFER + 1);
-    const bool packed1 = !ctx->force_dp32 && dp2_score_range_ok(1, -4, -1, -6, primer_max, prefix_max);
-    const bool packed2 = !ctx->force_dp32 &&
+    const bool packed1 = !ctx->cfg.force_dp32 && dp2_score_range_ok(1, -4, -1, -6, primer_max, prefix_max);
+    const bool packed2 = !ctx->cfg.force_dp32 &&
                          dp2_score_range_ok(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start, q_max, r_max);
     ScoreParams2 sp_default2 = make_score_params2(sp_default);
     ScoreParams2 sp_user2 = make_score_params2(sp_user);
@@ -234,17 +237,19 @@ int extend_fetch_copies(hsq_ctx* ctx, hsq_extend_out* o) {
 }
 
 // fetch, part 2: cell counter and status of everything run since the counters were last reset (synchronises)
-int extend_fetch_finish(hsq_ctx* ctx, hsq_extend_out* o) {
+int extend_counters(hsq_ctx* ctx, int64_t* cells_out) {
     int rc;
     HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
     int w[4];
     if ((rc = read_status(ctx, w, 4))) return rc;
     if (ctx->io && ctx->io != ctx->stream) HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->io));
-    o->cells = (int64_t)ctx->h_cells[0];
+    *cells_out = (int64_t)ctx->h_cells[0];
     if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend: ") + status_message(w[0]));
     if (w[3] != 0) return fail(ctx, HSQ_ERR_OVERFLOW, std::string("hsq_extend: ") + status_message(HSQ_ERR_OVERFLOW));
     return HSQ_OK;
 }
+
+int extend_fetch_finish(hsq_ctx* ctx, hsq_extend_out* o) { return extend_counters(ctx, &o->cells); }
 
 int extend_fetch(hsq_ctx* ctx, hsq_extend_out* o) {
     int rc = extend_fetch_copies(ctx, o);
@@ -291,68 +296,71 @@ hsq_seqs seqs_window(const hsq_seqs& s, int64_t a, int64_t n) {
 // from the device at the price of a synchronisation).
 int host_chunk_dims(hsq_ctx* ctx, const hsq_pair_batch& w, int* read_max) {
     int64_t mx = 0;
-    bool bad = false;
+    bool bad = false, order = false;
     for (int64_t k = 0; k < w.n; k++) {
-        mx = std::max(mx, std::max(w.r1.offsets[k + 1] - w.r1.offsets[k], w.r2.offsets[k + 1] - w.r2.offsets[k]));
+        const int64_t l1 = w.r1.offsets[k + 1] - w.r1.offsets[k], l2 = w.r2.offsets[k + 1] - w.r2.offsets[k];
+        order |= (l1 < 0) | (l2 < 0);
+        mx = std::max(mx, std::max(l1, l2));
         bad |= (w.probe_id[k] < 0) | (w.probe_id[k] >= ctx->n_probes);
     }
+    if (order) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_extend: offsets must not decrease");
     if (bad) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_extend: probe_id out of range");
     if (mx > INT32_MAX) return fail(ctx, HSQ_ERR_UNSUPPORTED, "hsq_extend: read too long");
     *read_max = (int)mx;
     return HSQ_OK;
 }
 
-// hsq_extend_batch for a large batch: chunks flow through
+// Chunk boundaries of the host pipeline: sizes ramp up and down (weights 1,2,4,8 towards the middle) because the first H2D
+// and the last D2H are the only copies nothing overlaps, so the edge chunks are small and the middle ones large.
+std::vector<int64_t> chunk_starts(const hsq_ctx* ctx, int64_t n, int n_chunks) {
+    std::vector<int64_t> starts((size_t)n_chunks + 1, 0);
+    std::vector<double> wgt((size_t)n_chunks);
+    double total = 0;
+    const bool ramp = !ctx->cfg.uniform_chunks;
+    for (int c = 0; c < n_chunks; c++) {
+        const int edge = std::min(c, n_chunks - 1 - c);
+        wgt[(size_t)c] = ramp ? (double)(1 << std::min(edge, 3)) : 1.0;
+        total += wgt[(size_t)c];
+    }
+    double acc = 0;
+    for (int c = 0; c < n_chunks; c++) {
+        acc += wgt[(size_t)c];
+        starts[(size_t)c + 1] = std::min<int64_t>(n, (int64_t)((double)n * acc / total + 0.5));
+    }
+    starts[(size_t)n_chunks] = n;
+    return starts;
+}
+
+// chunks of >= 256 k pairs on average, at most 12 (hsq_config.extend_chunks overrides; 1 = no pipelining)
+int pick_chunks(const hsq_ctx* ctx, int64_t n) {
+    int n_chunks = (int)std::min<int64_t>(12, n / 262144);
+    if (ctx->cfg.extend_chunks > 0) n_chunks = ctx->cfg.extend_chunks;
+    if (n_chunks < 1) n_chunks = 1;
+    if (n < n_chunks) n_chunks = (int)std::max<int64_t>(1, n);
+    return n_chunks;
+}
+
+// What differs between the callers of the host pipeline (ASCII batches with slot output, packed batches with pooled output).
+struct ExtendChunkIO {
+    // host-side size / range checks of chunk [a, a+m): longest read
+    std::function<int(int64_t a, int64_t m, int* read_max)> dims;
+    // host -> device copies of the chunk into the active buffer set, on ctx->io
+    std::function<int(int64_t a, int64_t m)> stage;
+    // device -> host delivery of the active set's results for the chunk, on ctx->io (the set's capture kernels have finished)
+    std::function<int(int64_t a, int64_t m)> fetch;
+};
+
+// A large batch flows through
 //     H2D (s_in) | prep: encode, primer DP, bucket sorts (s_prep) | capture DP (s_cap[chunk & 1]) | D2H (s_out)
 // with three complete buffer sets, so that three chunks are in flight: while the capture kernel of chunk c runs, the prep
 // of chunk c+1 is already done and chunk c+2 is being copied / prepared.  When a capture kernel drains, the next one is
 // ready to take the freed SMs at once (no chain of small kernels in between), and its tail overlaps that start because
 // consecutive capture kernels sit on different streams.  The host never blocks inside the loop; events order the streams.
-int extend_pipelined(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o, int n_chunks) {
-    const int64_t n = pb->n;
+// Every exit goes through the join at the end: no copy is in flight and the home buffer set is active when this returns.
+int extend_pipelined(hsq_ctx* ctx, int64_t n, int cigar_cap, int md_cap, int n_chunks, const ExtendChunkIO& io, int64_t* cells_out) {
     constexpr int NS = hsq_ctx::N_EXTEND_SETS;
-    // chunk sizes ramp up and down (weights 1,2,4,.. towards the middle): the first H2D and the last D2H are the only copies
-    // that nothing overlaps, so the edge chunks are small and the middle ones large (fewer kernel boundaries)
-    std::vector<int64_t> starts((size_t)n_chunks + 1, 0);
-    {
-        std::vector<double> wgt((size_t)n_chunks);
-        double total = 0;
-        const bool ramp = getenv("HSQ_EXTEND_UNIFORM_CHUNKS") == nullptr;
-        for (int c = 0; c < n_chunks; c++) {
-            const int edge = std::min(c, n_chunks - 1 - c);
-            wgt[(size_t)c] = ramp ? (double)(1 << std::min(edge, 3)) : 1.0;
-            total += wgt[(size_t)c];
-        }
-        double acc = 0;
-        for (int c = 0; c < n_chunks; c++) {
-            acc += wgt[(size_t)c];
-            starts[(size_t)c + 1] = std::min<int64_t>(n, (int64_t)((double)n * acc / total + 0.5));
-        }
-        starts[(size_t)n_chunks] = n;
-    }
+    const std::vector<int64_t> starts = chunk_starts(ctx, n, n_chunks);
     int rc = HSQ_OK;
-    auto chunk_in = [&](int c) {
-        const int64_t a = starts[(size_t)c], m = starts[(size_t)c + 1] - a;
-        hsq_pair_batch w = *pb;
-        w.n = m;
-        w.probe_id = pb->probe_id + a;
-        w.read_index = pb->read_index ? pb->read_index + a : nullptr;
-        w.r1 = seqs_window(pb->r1, a, m);
-        w.r2 = seqs_window(pb->r2, a, m);
-        return w;
-    };
-    auto chunk_out = [&](int c) {
-        const int64_t a = starts[(size_t)c];
-        hsq_extend_out w = *o;
-        int32_t** f32[9] = {&w.primer_end, &w.score, &w.pos, &w.read_start, &w.read_stop, &w.nm, &w.tlen, &w.cigar_len, &w.md_len};
-        for (auto f : f32) if (*f) *f += 2 * a;
-        if (w.ok) w.ok += 2 * a;
-        if (w.overflow) w.overflow += 2 * a;
-        if (w.cigar) w.cigar += 2 * a * (int64_t)o->cigar_cap;
-        if (w.md) w.md += 2 * a * (int64_t)o->md_cap;
-        if (w.pair_ok) w.pair_ok += a;
-        return w;
-    };
     cudaStream_t main_stream = ctx->stream;
     ctx->keep_counters = false;
     if ((rc = reset_status(ctx))) return rc;
@@ -360,60 +368,72 @@ int extend_pipelined(hsq_ctx* ctx, const hsq_pair_batch* pb, hsq_extend_out* o, 
     const int home_set = ctx->active_set;
     // the capture phase of chunk c is issued after the prep of chunk c+1, so that the prep stream always runs one chunk ahead
     std::vector<ExtendPlan> plans((size_t)n_chunks);
+#define HSQ_STEP(expr)                                                                              \
+    do {                                                                                            \
+        cudaError_t _e = (expr);                                                                    \
+        if (_e != cudaSuccess) return hsq::fail(ctx, HSQ_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); \
+    } while (0)
     auto issue_capture = [&](int c) -> int {
         const int k = c % NS;
         cudaStream_t st = ctx->s_cap[c & 1];
-        HSQ_CUDA(ctx, cudaStreamWaitEvent(st, ctx->ev_prep[k], 0));
+        HSQ_STEP(cudaStreamWaitEvent(st, ctx->ev_prep[k], 0));
         ctx->stream = st;
         int r = extend_capture(ctx, plans[(size_t)c]);
         ctx->stream = main_stream;
         if (r) return r;
-        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_cap[k], st));
-        // D2H of this chunk's results
-        HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_out, ctx->ev_cap[k], 0));
+        HSQ_STEP(cudaEventRecord(ctx->ev_cap[k], st));
+        // delivery of this chunk's results
+        HSQ_STEP(cudaStreamWaitEvent(ctx->s_out, ctx->ev_cap[k], 0));
         activate_extend_set(ctx, k);
         ctx->ext_ran = true;
         ctx->io = ctx->s_out;
-        hsq_extend_out wo = chunk_out(c);
-        r = extend_fetch_copies(ctx, &wo);
+        r = io.fetch(starts[(size_t)c], starts[(size_t)c + 1] - starts[(size_t)c]);
         ctx->io = nullptr;
         if (r) return r;
-        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_out[k], ctx->s_out));
+        HSQ_STEP(cudaEventRecord(ctx->ev_out[k], ctx->s_out));
         return HSQ_OK;
     };
-    for (int c = 0; c < n_chunks && !rc; c++) {
+    auto issue_front = [&](int c) -> int {  // H2D + prep of chunk c
         const int k = c % NS;
-        hsq_pair_batch in = chunk_in(c);
-        int read_max = 0;
-        if ((rc = host_chunk_dims(ctx, in, &read_max))) break;
+        const int64_t a = starts[(size_t)c], m = starts[(size_t)c + 1] - a;
+        int read_max = 0, r;
+        if ((r = io.dims(a, m, &read_max))) return r;
         activate_extend_set(ctx, k);
         // H2D into this set once the chunk that used it before (c - NS) has delivered its results
-        if (c >= NS) HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_in, ctx->ev_out[k], 0));
+        if (c >= NS) HSQ_STEP(cudaStreamWaitEvent(ctx->s_in, ctx->ev_out[k], 0));
         ctx->io = ctx->s_in;
-        rc = extend_stage(ctx, &in);
+        ctx->ext_n = -1;
+        r = io.stage(a, m);
         ctx->io = nullptr;
-        if (rc) break;
-        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_in[k], ctx->s_in));
-        // prep on the prep stream
-        HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->s_prep, ctx->ev_in[k], 0));
+        if (r) return r;
+        ctx->ext_n = m;
+        HSQ_STEP(cudaEventRecord(ctx->ev_in[k], ctx->s_in));
+        HSQ_STEP(cudaStreamWaitEvent(ctx->s_prep, ctx->ev_in[k], 0));
         ctx->stream = ctx->s_prep;
         ctx->work_slot = k;
-        rc = extend_prep(ctx, o->cigar_cap, o->md_cap, read_max, &plans[(size_t)c]);
+        r = extend_prep(ctx, cigar_cap, md_cap, read_max, &plans[(size_t)c]);
         ctx->stream = main_stream;
         ctx->work_slot = 0;
-        if (rc) break;
-        HSQ_CUDA(ctx, cudaEventRecord(ctx->ev_prep[k], ctx->s_prep));
-        if (c >= 1) rc = issue_capture(c - 1);
+        if (r) return r;
+        HSQ_STEP(cudaEventRecord(ctx->ev_prep[k], ctx->s_prep));
+        return HSQ_OK;
+    };
+#undef HSQ_STEP
+    for (int c = 0; c < n_chunks && !rc; c++) {
+        rc = issue_front(c);
+        if (!rc && c >= 1) rc = issue_capture(c - 1);
     }
     if (!rc) rc = issue_capture(n_chunks - 1);
     // everything joins the main stream, which then reads the counters
+    ctx->stream = main_stream;
+    ctx->work_slot = 0;
     cudaStreamSynchronize(ctx->s_prep);
     for (int k = 0; k < 2; k++) cudaStreamSynchronize(ctx->s_cap[k]);
     cudaStreamSynchronize(ctx->s_in);
     cudaStreamSynchronize(ctx->s_out);
     activate_extend_set(ctx, home_set);
     ctx->io = nullptr;
-    int rc2 = rc ? HSQ_OK : extend_fetch_finish(ctx, o);
+    int rc2 = rc ? HSQ_OK : extend_counters(ctx, cells_out);
     for (auto& ps : ctx->parked) ps.ext_n = -1;
     ctx->ext_n = -1;  // no single staged batch remains
     ctx->ext_ran = false;
@@ -435,11 +455,35 @@ extern "C" int32_t hsq_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, h
     if (pairs->n < 0 || out->cigar_cap < 0 || out->md_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
-    // chunks of >= 256 k pairs on average, at most 12 (HSQ_EXTEND_CHUNKS overrides; 1 = no pipelining)
-    int n_chunks = (int)std::min<int64_t>(12, pairs->n / 262144);
-    if (const char* e = getenv("HSQ_EXTEND_CHUNKS")) n_chunks = atoi(e);
-    if (n_chunks > 1 && pairs->n >= n_chunks) {
-        rc = extend_pipelined(ctx, pairs, out, n_chunks);
+    const int n_chunks = pick_chunks(ctx, pairs->n);
+    if (n_chunks > 1) {
+        ExtendChunkIO io;
+        auto window = [&](int64_t a, int64_t m) {
+            hsq_pair_batch w = *pairs;
+            w.n = m;
+            w.probe_id = pairs->probe_id + a;
+            w.read_index = pairs->read_index ? pairs->read_index + a : nullptr;
+            w.r1 = seqs_window(pairs->r1, a, m);
+            w.r2 = seqs_window(pairs->r2, a, m);
+            return w;
+        };
+        io.dims = [&](int64_t a, int64_t m, int* read_max) { return host_chunk_dims(ctx, window(a, m), read_max); };
+        io.stage = [&](int64_t a, int64_t m) {
+            hsq_pair_batch w = window(a, m);
+            return upload_pairs_raw(ctx, &w);
+        };
+        io.fetch = [&](int64_t a, int64_t) {
+            hsq_extend_out w = *out;
+            int32_t** f32[9] = {&w.primer_end, &w.score, &w.pos, &w.read_start, &w.read_stop, &w.nm, &w.tlen, &w.cigar_len, &w.md_len};
+            for (auto f : f32) if (*f) *f += 2 * a;
+            if (w.ok) w.ok += 2 * a;
+            if (w.overflow) w.overflow += 2 * a;
+            if (w.cigar) w.cigar += 2 * a * (int64_t)out->cigar_cap;
+            if (w.md) w.md += 2 * a * (int64_t)out->md_cap;
+            if (w.pair_ok) w.pair_ok += a;
+            return extend_fetch_copies(ctx, &w);
+        };
+        rc = extend_pipelined(ctx, pairs->n, out->cigar_cap, out->md_cap, n_chunks, io, &out->cells);
     } else {
         rc = extend_stage(ctx, pairs);
         if (!rc) rc = extend_run(ctx, out->cigar_cap, out->md_cap);

@@ -107,8 +107,8 @@ int compact_survivors(hsq_ctx* ctx, int64_t n, const uint8_t* d_keep, int32_t* d
     // the compacted reads are never larger than the batch: size the buffers without a second synchronisation
     struct { DevSeqsOwned* src; DevSeqsOwned* dst; } sides[2] = {{&ctx->r1, &ctx->alt_r1}, {&ctx->r2, &ctx->alt_r2}};
     for (auto& s : sides) {
-        HSQ_CUDA(ctx, s.dst->ascii.ensure((size_t)s.src->total + 16));
-        HSQ_CUDA(ctx, s.dst->codes.ensure((size_t)s.src->total + 16));
+        HSQ_CUDA(ctx, s.dst->ascii.ensure((size_t)s.src->total + 32));
+        HSQ_CUDA(ctx, s.dst->codes.ensure((size_t)s.src->total + 32));
         s.dst->n = m;
         if (m > 0) {
             const int blocks = (int)std::min<int64_t>((m * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);

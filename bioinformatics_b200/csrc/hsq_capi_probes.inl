@@ -41,7 +41,7 @@ extern "C" int32_t hsq_set_probes(hsq_ctx* ctx, const hsq_probe_table* t) {
     if ((rc = upload_seqs(ctx, &t->target, &ctx->p_target, d_status(ctx), d_maxlen(ctx, 2)))) return rc;
     ctx->p_full.n = t->n;
     ctx->p_full.total = ctx->p_ext.total + ctx->p_lig.total + ctx->p_target.total;
-    HSQ_CUDA(ctx, ctx->p_full.codes.ensure((size_t)ctx->p_full.total + 16));
+    HSQ_CUDA(ctx, ctx->p_full.codes.ensure((size_t)ctx->p_full.total + 32));
     HSQ_CUDA(ctx, ctx->p_full.offsets.ensure((n + 1) * sizeof(int64_t)));
     concat_probe_kernel<<<(unsigned)((n + 1 + 127) / 128), 128, 0, ctx->stream>>>(ctx->p_ext.view(), ctx->p_target.view(), ctx->p_lig.view(),
                                                                                   t->n, ctx->p_full.codes.as<uint8_t>(),

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <string>
 #include <vector>
+#include <functional>
 #include <cstdio>
 #include "hsq_extend.cuh"
 
@@ -36,8 +37,15 @@ struct DevSeqsOwned {  // encoded ragged batch resident on the device
     DevBuf ascii, codes, offsets;
     int64_t n = 0, total = 0;
     int max_len = 0;
+    // packed staging (hsq_packed_reads): `ascii` then holds the packed words, `lens` the read lengths, `word_off` the first word of
+    // every read (device scan), `exc` the exception records of a 2-bit batch
+    DevBuf lens, word_off, scan_tmp, exc;
+    int packed_bits = 0;       // 0: `ascii` holds ASCII
+    int64_t packed_words = 0;  // 32-bit words of packed data
+    int64_t n_exc = 0;
+    int64_t exc_read_base = 0; // exception read numbers are relative to the caller's batch: first read of this window
     DeviceSeqs view() const { return DeviceSeqs{codes.as<uint8_t>(), offsets.as<int64_t>()}; }
-    void release() { ascii.release(); codes.release(); offsets.release(); }
+    void release() { ascii.release(); codes.release(); offsets.release(); lens.release(); word_off.release(); scan_tmp.release(); exc.release(); }
 };
 
 }  // namespace hsq
@@ -63,11 +71,11 @@ struct hsq_ctx {
     // scratch + outputs
     hsq::DevBuf ptr_words, brow, cols, status, cells, misc, out_i32, out_u8, out_slots, pair_ok;
     hsq::DevBuf sort_a, sort_b, sort_c, sort_d, sort_tmp, flags, slow, colinfo;
-    bool force_dp32 = false;
+    hsq_config cfg{};  // hsq_ctx_create_ex / hsq_ctx_configure
     // probe search windows sorted by (contig, strand, start) for hsq_assign_probes
     hsq::DevBuf rg_start, rg_end, rg_value, rg_off;
     hsq::DevBuf dd_seg;         // dedup segment path: per-probe counters, offsets
-    bool force_dedup_cub = false;  // development / test switch (HSQ_DEDUP_CUB=1): always take the radix-sort path
+    hsq::DevBuf pool_tmp, pool_cursor, pool_dev;  // pooled CIGAR / MD delivery (hsq_extend_packed)
     hsq::DevBuf dd_u8, dd_i32;  // hsq_dedup_extend_batch: dedup answers kept while the extend stage reuses the output buffers
     int64_t rg_n = -1;
     int32_t rg_contigs = 0;
@@ -143,12 +151,16 @@ inline int copy_seqs(hsq_ctx* ctx, const hsq_seqs* s, DevSeqsOwned* d) {
     if (!s || s->n < 0 || !s->offsets) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null sequence batch");
     const int64_t base = s->offsets[0];
     if (base < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "offsets must not be negative");
+    if (s->n > 0 && (s->offsets[1] < base || s->offsets[s->n] < s->offsets[s->n - 1]))  // the interior is checked on the device (max_len_kernel / host_chunk_dims)
+        return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "offsets must not decrease");
     d->n = s->n;
     d->total = s->offsets[s->n] - base;
     if (d->total < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative batch size");
     if (d->total > 0 && !s->data) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null sequence data");
-    HSQ_CUDA(ctx, d->ascii.ensure((size_t)d->total + 16));
-    HSQ_CUDA(ctx, d->codes.ensure((size_t)d->total + 16));
+    d->packed_bits = 0;
+    // 32 bytes of slack: the strip / walker loads of the DP kernels read whole aligned words around a sequence's ends
+    HSQ_CUDA(ctx, d->ascii.ensure((size_t)d->total + 32));
+    HSQ_CUDA(ctx, d->codes.ensure((size_t)d->total + 32));
     HSQ_CUDA(ctx, d->offsets.ensure((size_t)(s->n + 1) * sizeof(int64_t)));
     cudaStream_t st = ctx->io ? ctx->io : ctx->stream;
     if (d->total > 0) HSQ_CUDA(ctx, cudaMemcpyAsync(d->ascii.p, s->data + base, (size_t)d->total, cudaMemcpyHostToDevice, st));

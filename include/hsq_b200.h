@@ -277,8 +277,88 @@ typedef struct hsq_record_out {
     uint8_t* qual;      /* base qualities of the same range, reversed on the - strand */
 } hsq_record_out;
 
+/* ---- N1: read batches packed to 2 or 4 bits per base (north_star subsystem 1) ------------------------------------------ */
+/* The reference itself keeps reads packed (2 bit: COMMON/sequence/NucleotideCodeSequence.java:32-48; 5 bit IUPAC:
+ * COMMON/sequence/IupacNucleotideCodeSequence.java:34-58); this is the form in which a host should hand large batches over
+ * PCIe.  Read k occupies words(len[k]) = (len[k] * bits + 31) / 32 little-endian 32-bit words, reads back to back; base i of a
+ * read sits at bits [bits * (i % (32 / bits)), +bits) of its word i / (32 / bits).
+ *   2 bit: A = 0, C = 1, T = 2, G = 3 (bits 1-2 of the upper-case ASCII letter).  Every base that is not an upper- or
+ *          lower-case A/C/G/T (N, other IUPAC codes, gap characters) is packed as 0 and listed in the exception arrays
+ *          (ascending by read, then position) with its ASCII character; the device restores it.
+ *   4 bit: the IUPAC nucleotide set (A = 1, C = 2, G = 4, T = 8, N = 15, gap = 0); 'U' is not representable
+ *          (hsq_pack_reads fails with HSQ_ERR_UNSUPPORTED), no exception list.
+ * Letter case is folded (the alignment is case blind, IupacNucleotideCode.getCodesFromString :86-104). */
+#define HSQ_PACK_2BIT 2
+#define HSQ_PACK_4BIT 4
+typedef struct hsq_packed_reads {
+    int32_t bits;             /* HSQ_PACK_2BIT or HSQ_PACK_4BIT */
+    int64_t n;
+    const uint8_t* data;      /* 4 * sum(words(len[k])) bytes */
+    const int32_t* len;       /* [n] bases per read */
+    int64_t n_exceptions;     /* 2 bit only */
+    const uint32_t* exc_read; /* [n_exceptions] read index, ascending */
+    const uint32_t* exc_pos;  /* [n_exceptions] base position inside the read */
+    const uint8_t* exc_char;  /* [n_exceptions] the ASCII character at that position */
+} hsq_packed_reads;
+
+/* hsq_pair_batch with packed reads.  Qualities stay bytes, laid out back to back in read order (read k at the sum of the
+ * lengths before it); NULL where a call does not read them (hsq_extend_packed). */
+typedef struct hsq_packed_pairs {
+    int64_t n;
+    const int32_t* probe_id;
+    const int32_t* read_index;
+    hsq_packed_reads r1, r2;
+    const uint8_t* q1;
+    const uint8_t* q2;
+    /* optional, hsq_dedup_packed only: (short) sum(q - 33) per read as hsq_quality_sums computes it (BamFileUtil.getQualityScore,
+     * HSQ/utils/BamFileUtil.java:74-85).  When both are given q1 / q2 are not read and may be NULL: 2 bytes per read cross PCIe
+     * instead of the quality string.  NULL (the default): the device sums q1 / q2. */
+    const int16_t* qsum1;
+    const int16_t* qsum2;
+} hsq_packed_pairs;
+
+/* Results of hsq_extend_packed: the per read end fields of hsq_extend_out (any array may be NULL: it is then not copied to
+ * the host) with CIGAR and MD in one byte pool instead of fixed slots: the CIGAR of read end m is
+ * pool[str_off[m] .. str_off[m] + cigar_len[m]), its MD follows directly.  The pool is filled in read end order.  If `pool` is
+ * pinned host memory (hsq_pinned_alloc) the device writes it directly while later chunks still compute. */
+typedef struct hsq_extend_pooled_out {
+    int32_t cigar_cap, md_cap; /* in: bytes per device-side slot (0 = 64 / 96); a longer string fails the call with HSQ_ERR_OVERFLOW */
+    uint8_t* ok;
+    int32_t* primer_end;
+    int32_t* score;
+    int32_t* pos;
+    int32_t* read_start;
+    int32_t* read_stop;
+    int32_t* nm;
+    int32_t* tlen;
+    int32_t* cigar_len;
+    int32_t* md_len;
+    int64_t* str_off;          /* [2n] */
+    uint8_t* pool;
+    int64_t pool_cap;          /* in: bytes available in pool */
+    int64_t pool_bytes;        /* out: bytes used (needed, when the call fails with HSQ_ERR_OVERFLOW) */
+    uint8_t* pair_ok;          /* [n] */
+    int64_t cells;             /* out */
+} hsq_extend_pooled_out;
+
+/* Library behaviour that a caller (or a test) may change; zero-initialise for the defaults.  Replaces the environment
+ * variables earlier builds read. */
+typedef struct hsq_config {
+    int32_t struct_bytes;       /* sizeof(hsq_config) of the caller's header */
+    int32_t force_dp32;         /* 1: always run the 32-bit DP kernels (the packed u16x2 kernels are the default when the scores fit) */
+    int32_t force_dedup_radix;  /* 1: dedup through the radix-sort cross-check path instead of the per-probe group-by */
+    int32_t extend_chunks;      /* chunks of the host pipeline of hsq_extend_batch / hsq_extend_packed; 0 = automatic */
+    int32_t uniform_chunks;     /* 1: equal chunk sizes instead of the ramp */
+    int32_t band;               /* opt-in band half-width of the capture-target DP; 0 = full matrices.  Results stay those of the
+                                 * full matrix: an alignment whose band is touched is re-run in full (see hsq_band_stats) */
+} hsq_config;
+
 /* ---- context ------------------------------------------------------------------------------ */
 int32_t hsq_ctx_create(int32_t device, hsq_ctx** out);
+/* as hsq_ctx_create, with a configuration (NULL = defaults) */
+int32_t hsq_ctx_create_ex(int32_t device, const hsq_config* config, hsq_ctx** out);
+/* changes the configuration of an existing context (takes effect with the next batch call) */
+int32_t hsq_ctx_configure(hsq_ctx* ctx, const hsq_config* config);
 void hsq_ctx_destroy(hsq_ctx* ctx);
 const char* hsq_last_error(const hsq_ctx* ctx); /* ctx may be NULL: last create error */
 const char* hsq_version(void);
@@ -511,6 +591,27 @@ typedef struct hsq_coord_sort_in {
     hsq_seqs names;
 } hsq_coord_sort_in;
 int32_t hsq_coordinate_order(hsq_ctx* ctx, const hsq_coord_sort_in* in, int32_t* order);
+
+/* ---- N1 entry points ---------------------------------------------------------------------------------------------------- */
+/* Host helper (plain CPU code, no device): packs a ragged ASCII batch into the layout of hsq_packed_reads.  data_out must hold
+ * hsq_packed_bytes(...) bytes, len_out n entries.  2 bit: at most exc_cap exceptions are written, *n_exceptions gets their
+ * number (more than exc_cap: HSQ_ERR_OVERFLOW).  A byte that is not an IUPAC letter or gap character: HSQ_ERR_BAD_CHARACTER.
+ * threads <= 0: all host cores.  hsq_last_error(NULL) holds the message of a failure. */
+int64_t hsq_packed_bytes(const int64_t* offsets, int64_t n, int32_t bits);
+int32_t hsq_pack_reads(const hsq_seqs* reads, int32_t bits, uint8_t* data_out, int32_t* len_out, int64_t exc_cap,
+                       int64_t* n_exceptions, uint32_t* exc_read, uint32_t* exc_pos, uint8_t* exc_char, int32_t threads);
+/* Host helper: out[k] = (short) sum over read k of (quality char - 33), Java short wrap-around included. */
+int32_t hsq_quality_sums(const uint8_t* quals, const int64_t* offsets, int64_t n, int16_t* out, int32_t threads);
+/* Inverse of hsq_pack_reads on the device (test / diagnostic entry point): upper-case ASCII of every read, ragged, with the
+ * offsets it implies; out_data must hold sum(len) bytes, out_offsets n + 1 entries. */
+int32_t hsq_unpack_reads(hsq_ctx* ctx, const hsq_packed_reads* reads, uint8_t* out_data, int64_t* out_offsets);
+/* hsq_extend_batch for packed reads with pooled CIGAR / MD output: same results, about a third of the bytes over PCIe.
+ * Chunks flow through the same H2D | prep | capture | D2H pipeline. */
+int32_t hsq_extend_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs, hsq_extend_pooled_out* out);
+/* hsq_dedup_batch for packed reads: the UID comes from the packed bases (an exception inside a UID: HSQ_ERR_UNSUPPORTED, as a
+ * non-ACGT UID base is for hsq_dedup_batch), the quality sums from q1 / q2. */
+int32_t hsq_dedup_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs, int32_t ext_uid_len, int32_t lig_uid_len, uint8_t* is_best,
+                         int32_t* group_size, hsq_probe_stats* stats);
 
 /* ---- sharded dedup: one process per GPU, exchange by the caller ------------------------------------------------------ */
 /* First half of FilterByUid.reduceReadsByProbeAndUid for this rank's pairs (host buffers in): writes pairs->n key

@@ -112,21 +112,20 @@ def test_extend_adversarial_vs_oracle(ctx):
     ctx.set_scorer(scorer())
 
 
-def test_extend_forced_32bit_kernel(monkeypatch):
-    """HSQ_FORCE_DP32=1 routes hsq_extend_batch through the 32-bit capture kernel: same results."""
-    monkeypatch.setenv("HSQ_FORCE_DP32", "1")
+def test_extend_forced_32bit_kernel():
+    """hsq_config.force_dp32 routes hsq_extend_batch through the 32-bit capture kernel: same results."""
     probes = synth.make_probes(100, seed=5)
     pairs = synth.make_pairs(probes, 3000, read_len=150, ext_uid_len=10, seed=6, sub_rate=0.02, ins_rate=0.003, del_rate=0.003)
-    with Context(0) as c32:
+    with Context(0, config={"force_dp32": 1}) as c32:
         c32.set_probes(probes)
         got = c32.extend_batch(pairs, cigar_cap=64, md_cap=96)
     H.assert_extend_equal(got, O.extend_batch(probes, pairs, cigar_cap=64, md_cap=96, nthreads=8))
 
 
 @pytest.mark.parametrize("chunks", [2, 3, 7])
-def test_extend_chunked_pipeline(ctx, monkeypatch, chunks):
-    """HSQ_EXTEND_CHUNKS forces the H2D | kernels | D2H pipeline of hsq_extend_batch on a small batch: same results."""
-    monkeypatch.setenv("HSQ_EXTEND_CHUNKS", str(chunks))
+def test_extend_chunked_pipeline(ctx, chunks):
+    """hsq_config.extend_chunks forces the H2D | kernels | D2H pipeline of hsq_extend_batch on a small batch: same results."""
+    ctx.configure(extend_chunks=chunks, uniform_chunks=chunks == 3)
     probes = synth.make_probes(80, seed=15)
     pairs = synth.make_pairs(probes, 5001, read_len=150, ext_uid_len=10, seed=16, sub_rate=0.02, ins_rate=0.003, del_rate=0.003)
     ctx.set_probes(probes)
@@ -136,6 +135,7 @@ def test_extend_chunked_pipeline(ctx, monkeypatch, chunks):
     with pytest.raises(HsqError) as e:  # a too small slot in some chunk is reported, after all chunks ran
         ctx.extend_batch(pairs, cigar_cap=3, md_cap=96)
     assert e.value.status == A.HSQ_ERR_OVERFLOW
+    ctx.configure()
 
 
 def test_extend_non_acgt_capture_target(ctx):
@@ -195,7 +195,7 @@ def _dedup_equal(got, exp):
     assert (st.max_pairs_per_uid == est.max_pairs_per_uid).all()
 
 
-def test_dedup_segment_and_radix_paths(ctx, monkeypatch):
+def test_dedup_segment_and_radix_paths(ctx):
     """The per-probe segment path (counting sort by probe + one block sorting and reducing each probe) and the radix-sort path give
     the oracle's answer: skewed panels, a probe larger than a block takes (whole batch falls back), probes without pairs, a sparse
     200 k-probe table, repeated read indexes (ties go to the earlier pair)."""
@@ -224,8 +224,7 @@ def test_dedup_segment_and_radix_paths(ctx, monkeypatch):
     expected = {name: O.dedup_batch(pb, u, v, npr) for name, pb, npr, u, v in cases}
     for name, pb, npr, u, v in cases:
         _dedup_equal(ctx.dedup_batch(pb, u, v, npr), expected[name])
-    monkeypatch.setenv("HSQ_DEDUP_CUB", "1")
-    with Context(0) as radix:
+    with Context(0, config={"force_dedup_radix": 1}) as radix:
         for name, pb, npr, u, v in cases:
             _dedup_equal(radix.dedup_batch(pb, u, v, npr), expected[name])
 

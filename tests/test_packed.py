@@ -1,0 +1,156 @@
+"""N1 (north_star subsystem 1): packed read batches and pooled CIGAR / MD output.
+
+CPU part: the host packing helper of the library against a plain-Python statement of the layout in include/hsq_b200.h.
+GPU part: hsq_unpack_reads round trip, and hsq_extend_packed == the oracle's extendReadsToPrimers on the same reads."""
+import numpy as np
+import pytest
+
+from bioinformatics_b200 import _abi as A
+from bioinformatics_b200 import synth
+from bioinformatics_b200._lib import HsqError, pack_reads, quality_sums
+from bioinformatics_b200.batches import PackedPairsHost, PooledExtendResult
+from tests import helpers as H
+
+CODE2 = {"A": 0, "C": 1, "T": 2, "G": 3}
+IUPAC4 = {"A": 1, "C": 2, "G": 4, "T": 8, "R": 5, "Y": 10, "S": 6, "W": 9, "K": 12, "M": 3, "B": 14, "D": 13, "H": 11, "V": 7, "N": 15,
+          "_": 0, "-": 0, ".": 0}
+
+
+def py_pack(strings, bits):
+    """The layout of hsq_packed_reads, restated: words per read, base i at bits [bits*(i % per), +bits) of word i // per."""
+    per = 32 // bits
+    words, lens, exc = [], [], []
+    for k, s in enumerate(strings):
+        lens.append(len(s))
+        w = [0] * ((len(s) * bits + 31) // 32)
+        for i, ch in enumerate(s):
+            if bits == 2:
+                v = CODE2.get(ch.upper())
+                if v is None:
+                    exc.append((k, i, ord(ch)))
+                    v = 0
+            else:
+                v = IUPAC4[ch.upper()]
+            w[i // per] |= v << (bits * (i % per))
+        words += w
+    return np.array(words, dtype=np.uint32), np.array(lens, dtype=np.int32), exc
+
+
+def random_reads(rng, n, alphabet="ACGT", lo=0, hi=70):
+    return ["".join(rng.choice(list(alphabet), int(rng.integers(lo, hi)))) for _ in range(n)]
+
+
+@pytest.mark.parametrize("bits", [2, 4])
+def test_pack_reads_layout(bits):
+    rng = np.random.default_rng(bits)
+    strings = random_reads(rng, 3000) + ["", "A", "ACGTACGTACGTACGT", "ACGTACGTACGTACGTA", "N" * 33, "acgtn"]
+    strings += random_reads(rng, 6000, "ACGTNacgtRYSWKMBDHV-", 0, 40)  # enough reads for the multi-threaded path
+    p = pack_reads(strings, bits, threads=3)
+    words, lens, exc = py_pack(strings, bits)
+    assert np.array_equal(p.len, lens)
+    assert np.array_equal(p.data.view(np.uint32), words)
+    if bits == 2:
+        assert list(zip(p.exc_read.tolist(), p.exc_pos.tolist(), p.exc_char.tolist())) == exc
+    else:
+        assert len(p.exc_read) == 0
+
+
+def test_pack_reads_errors():
+    with pytest.raises(HsqError) as e:
+        pack_reads(["ACGT", "AC!T"], 2)
+    assert e.value.status == A.HSQ_ERR_BAD_CHARACTER
+    with pytest.raises(HsqError) as e:
+        pack_reads(["ACGU"], 4)
+    assert e.value.status == A.HSQ_ERR_UNSUPPORTED
+    assert pack_reads([], 2).n == 0
+
+
+def test_quality_sums_wrap():
+    """(short) sum(q - 33): Java short arithmetic wraps (BamFileUtil.java:74-85)."""
+    q = A.SeqBatch.from_strings(["I" * 10, "", "~" * 400, "!" * 7])
+    assert quality_sums(q).tolist() == [400, 0, ((93 * 400 + 32768) % 65536) - 32768, 0]
+
+
+# ---- GPU --------------------------------------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def ctx():
+    from bioinformatics_b200._lib import Context
+    with Context(0) as c:
+        yield c
+
+
+def packed_pairs_of(pairs, bits=2, alloc=None):
+    return PackedPairsHost(pairs.probe_id, pack_reads(pairs.r1, bits, alloc), pack_reads(pairs.r2, bits, alloc),
+                           None if pairs.q1 is None else pairs.q1.data, None if pairs.q2 is None else pairs.q2.data, pairs.read_index)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bits", [2, 4])
+def test_unpack_round_trip(ctx, bits):
+    rng = np.random.default_rng(10 + bits)
+    strings = random_reads(rng, 5000, "ACGTN" if bits == 2 else "ACGTNRYSWKMBDHV", 0, 200) + ["", "A" * 16, "C" * 17, "N" * 5]
+    got = ctx.unpack_reads(pack_reads(strings, bits))
+    assert got.strings() == strings
+
+
+def assert_pooled_equal(got, exp):
+    for f in ("ok", "primer_end", "score", "pos", "read_start", "read_stop", "nm", "tlen", "cigar_len", "md_len", "pair_ok"):
+        a, b = getattr(got, f), getattr(exp, f)
+        bad = np.nonzero(a != b)[0]
+        assert len(bad) == 0, "field %s differs at %s: got %s expected %s" % (f, bad[:5], a[bad[:5]], b[bad[:5]])
+    assert got.cigars() == exp.cigars()
+    assert got.mds() == exp.mds()
+    assert got.cells == exp.cells
+    assert got.pool_bytes == int(exp.cigar_len.sum() + exp.md_len.sum())
+    assert np.array_equal(got.str_off, np.concatenate([[0], np.cumsum(exp.cigar_len + exp.md_len)[:-1]]))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bits,chunks,pinned", [(2, 0, False), (4, 0, False), (2, 3, True), (2, 7, False)])
+def test_extend_packed_equals_oracle(ctx, bits, chunks, pinned):
+    """Packed reads (2 bit with the N exceptions, 4 bit) through the chunked pipeline, pool in pinned (written by the device) and in
+    pageable memory: every field, string and the pool layout equal the oracle's extendReadsToPrimers."""
+    from oracle import oracle as O
+    probes = synth.make_probes(90, seed=41)
+    pairs = synth.make_pairs(probes, 6001, read_len=150, ext_uid_len=10, seed=42, sub_rate=0.02, ins_rate=0.004, del_rate=0.004)
+    ctx.configure(extend_chunks=chunks)
+    ctx.set_probes(probes)
+    exp = O.extend_batch(probes, pairs, cigar_cap=64, md_cap=96, nthreads=8)
+    pp = packed_pairs_of(pairs, bits)
+    out = PooledExtendResult(pairs.n, 2 * pairs.n * 40, alloc=ctx.pinned_array if pinned else None)
+    got = ctx.extend_packed(pp, out=out)
+    assert_pooled_equal(got, exp)
+    # a pool that is too small: the call says how much it needs
+    with pytest.raises(HsqError) as e:
+        ctx.extend_packed(pp, pool_cap=1000)
+    assert e.value.status == A.HSQ_ERR_OVERFLOW
+    # only the columns asked for are delivered
+    few = ctx.extend_packed(pp, fields=("pos", "pair_ok"))
+    assert np.array_equal(few.pos, exp.pos) and np.array_equal(few.pair_ok, exp.pair_ok) and few.score is None
+    ctx.configure()
+
+
+@pytest.mark.gpu
+def test_extend_packed_edge_cases(ctx):
+    """Empty batch, ragged read lengths (short mates that never reach the capture DP), IUPAC / lower-case reads through the exception list."""
+    from oracle import oracle as O
+    from bioinformatics_b200.batches import PairBatchHost
+    rng = np.random.default_rng(8)
+    probes = synth.make_probes(40, seed=43)
+    ctx.set_probes(probes)
+    empty = PackedPairsHost(np.zeros(0, dtype=np.int32), pack_reads([], 2), pack_reads([], 2))
+    got = ctx.extend_packed(empty)
+    assert got.cells == 0 and got.pool_bytes == 0
+    base = synth.make_pairs(probes, 900, read_len=150, ext_uid_len=10, seed=44, sub_rate=0.03, ins_rate=0.01, del_rate=0.01)
+    r1, r2 = base.r1.strings(), base.r2.strings()
+    for k in range(0, 900, 3):  # ragged: cut mates to random lengths, sprinkle IUPAC codes and lower case
+        r1[k] = r1[k][:int(rng.integers(0, 150))]
+        r2[k] = r2[k][:int(rng.integers(5, 150))].lower()
+    for k in range(1, 900, 7):
+        s = list(r1[k])
+        s[int(rng.integers(0, len(s)))] = str(rng.choice(list("NRYKM")))
+        r1[k] = "".join(s)
+    pairs = PairBatchHost(base.probe_id, r1, r2)
+    exp = O.extend_batch(probes, pairs, cigar_cap=64, md_cap=96, nthreads=8)
+    assert_pooled_equal(ctx.extend_packed(packed_pairs_of(pairs, 2)), exp)
+    assert_pooled_equal(ctx.extend_packed(packed_pairs_of(pairs, 4)), exp)
