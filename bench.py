@@ -579,22 +579,60 @@ def main():
     value = total_cells / (ms_step * 1e-3) / 1e9
 
     # ---- e2e leg: host buffers in, host buffers out ------------------------------------------------------------
-    for _ in range(1):
-        ctx.extend_batch(pairs, out=out)
+    # (a) the N1 path (north_star subsystem 1): reads packed to 2 bit/base (+ N exceptions) in pinned buffers, results as integer
+    #     columns + one CIGAR/MD pool written straight into pinned memory: hsq_extend_packed.  Packing is the host's input
+    #     format (hsq_pack_reads, timed separately below), not part of the step.
+    # (b) the ASCII path of round 1 (hsq_extend_batch: 1 B/base in, fixed 24 + 40 B string slots out), reported as e2e_ascii.
+    from bioinformatics_b200._lib import pack_reads
+    from bioinformatics_b200.batches import PackedPairsHost, PooledExtendResult
+    t0 = time.perf_counter()
+    packed = PackedPairsHost(pairs.probe_id, pack_reads(pairs.r1, 2, ctx.pinned_array), pack_reads(pairs.r2, 2, ctx.pinned_array))
+    pack_s = time.perf_counter() - t0
+    pool_cap = 2 * n * 24
+    E2E_FIELDS = ("ok", "pair_ok", "pos", "read_start", "read_stop", "nm", "cigar_len", "md_len", "str_off")
+    full = PooledExtendResult(n, pool_cap, alloc=ctx.pinned_array)
+    ctx.extend_packed(packed, out=full)  # warm-up + parity: every column, every string and the pool layout against the resident run
+    lens = np.asarray(out.cigar_len) + np.asarray(out.md_len)
+    both = np.concatenate([np.asarray(out.cigar).reshape(-1, CIGAR_CAP), np.asarray(out.md).reshape(-1, MD_CAP)], axis=1)
+    mask = np.concatenate([np.arange(CIGAR_CAP)[None, :] < np.asarray(out.cigar_len)[:, None],
+                           np.arange(MD_CAP)[None, :] < np.asarray(out.md_len)[:, None]], axis=1)
+    packed_equal = all(np.array_equal(getattr(full, f), getattr(out, f)) for f in ExtendResult.FIELDS_I32 + ("ok", "pair_ok")) and \
+        full.cells == cells and full.pool_bytes == int(lens.sum()) and np.array_equal(full.pool[:full.pool_bytes], both[mask]) and \
+        np.array_equal(full.str_off, np.concatenate([[0], np.cumsum(lens.astype(np.int64))[:-1]]))
+    del both, mask
+    slim = PooledExtendResult(n, pool_cap, fields=E2E_FIELDS, alloc=ctx.pinned_array)
+    ctx.extend_packed(packed, out=slim)
     barrier()
     t0 = time.perf_counter()
     e2e_ms_dev = 0.0
     for _ in range(args.steps):
-        ctx.extend_batch(pairs, out=out)
+        ctx.extend_packed(packed, out=slim)
         e2e_ms_dev += ctx.last_timing()[0]
     barrier()
     e2e_wall = (time.perf_counter() - t0) / args.steps
-    # size-independent property at the full batch size: the chunked host pipeline returns what the resident run returned
-    parity = {"chunked_e2e_equals_resident": bool(digest(out) == digest_resident and out.cells == cells)}
-    assert parity["chunked_e2e_equals_resident"], "hsq_extend_batch (chunked) differs from stage/run/fetch"
-
     e2e_s = max_over_ranks(max(e2e_wall, e2e_ms_dev / args.steps * 1e-3))
     e2e_value = total_cells / e2e_s / 1e9
+    h2d_packed = packed.r1.nbytes + packed.r2.nbytes + packed.probe_id.nbytes
+    d2h_packed = slim.nbytes()
+    packed_equal = packed_equal and all(np.array_equal(getattr(slim, f), getattr(full, f)) for f in E2E_FIELDS) and \
+        np.array_equal(slim.pool[:slim.pool_bytes], full.pool[:full.pool_bytes])
+
+    for _ in range(1):
+        ctx.extend_batch(pairs, out=out)
+    barrier()
+    t0 = time.perf_counter()
+    asc_ms_dev = 0.0
+    for _ in range(args.steps):
+        ctx.extend_batch(pairs, out=out)
+        asc_ms_dev += ctx.last_timing()[0]
+    barrier()
+    asc_wall = (time.perf_counter() - t0) / args.steps
+    asc_s = max_over_ranks(max(asc_wall, asc_ms_dev / args.steps * 1e-3))
+    # size-independent property at the full batch size: the chunked host pipelines return what the resident run returned
+    parity = {"chunked_e2e_equals_resident": bool(digest(out) == digest_resident and out.cells == cells),
+              "packed_e2e_equals_resident": bool(packed_equal)}
+    assert parity["chunked_e2e_equals_resident"], "hsq_extend_batch (chunked) differs from stage/run/fetch"
+    assert parity["packed_e2e_equals_resident"], "hsq_extend_packed differs from stage/run/fetch"
 
     stages = None
     if not args.no_stages:
@@ -611,8 +649,16 @@ def main():
                                        "%dbp UID, %d probes, default scorer 1/-4/-1/-6" % (2 * n, n, READ_LEN, UID, N_PROBES),
                            "cells_per_step_per_gpu": int(cells), "l2": "inputs (%.1f GB) larger than L2; no flush needed" % (h2d / 1e9),
                            "cigar_cap": CIGAR_CAP, "md_cap": MD_CAP},
-                "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                        "read_pairs_per_s": n * world / e2e_s, "ms_per_step": e2e_s * 1e3},
+                "e2e": {"value": e2e_value, "unit": "GCUPS", "h2d_bytes_per_step": int(h2d_packed), "d2h_bytes_per_step": int(d2h_packed),
+                        "read_pairs_per_s": n * world / e2e_s, "ms_per_step": e2e_s * 1e3,
+                        "api": "hsq_extend_packed: reads 2 bit/base + N exception list in pinned host memory, results = integer columns %s + one "
+                               "CIGAR/MD byte pool written into pinned host memory" % (E2E_FIELDS,),
+                        "pack_host_gb_per_s": (pairs.r1.data.nbytes + pairs.r2.data.nbytes) / pack_s / 1e9,
+                        "pack_note": "hsq_pack_reads (host helper, all cores) over the %.2f GB of ASCII reads, once, outside the step: packed reads "
+                                     "are the input format" % ((pairs.r1.data.nbytes + pairs.r2.data.nbytes) / 1e9)},
+                "e2e_ascii": {"value": total_cells / asc_s / 1e9, "unit": "GCUPS", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                              "read_pairs_per_s": n * world / asc_s, "ms_per_step": asc_s * 1e3,
+                              "api": "hsq_extend_batch: ASCII reads, fixed %d + %d byte CIGAR / MD slots (the round-1 path)" % (CIGAR_CAP, MD_CAP)},
                 "gpu_launches": int(launches_per_step * args.steps),
                 "read_pairs_per_s": n * world / (ms_step * 1e-3),
                 "roofline": {"bound": "int32_alu", "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "Tiop/s",

@@ -23,6 +23,7 @@ HSQ_ERR_MALFORMED = -11
 HSQ_PRIMER_NOT_FOUND = -2147483647
 HSQ_ALIGN_PENALIZE_START = 1
 HSQ_ALIGN_PENALIZE_END = 2
+HSQ_COMM_ID_BYTES = 128
 
 u8p = C.POINTER(C.c_uint8)
 i32p = C.POINTER(C.c_int32)

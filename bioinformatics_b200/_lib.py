@@ -23,7 +23,8 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_probe_ranges", "hsq_assign_probes", "hsq_dedup_extend_batch", "hsq_extend_records", "hsq_extend_selected", "hsq_flag_n_pairs",
            "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order",
            "hsq_ctx_create_ex", "hsq_ctx_configure", "hsq_packed_bytes", "hsq_pack_reads", "hsq_quality_sums", "hsq_unpack_reads",
-           "hsq_extend_packed")
+           "hsq_extend_packed", "hsq_dedup_packed", "hsq_comm_unique_id", "hsq_comm_init_rank", "hsq_comm_init_all", "hsq_comm_destroy",
+           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu")
 _NOT_STATUS = {"hsq_last_error": C.c_char_p, "hsq_version": C.c_char_p, "hsq_ctx_destroy": None, "hsq_packed_bytes": C.c_int64}
 
 
@@ -83,6 +84,35 @@ def pack_reads(reads, bits=2, alloc=None, threads=0):
         break
     k = int(n_exc.value)
     return PackedReadsHost(bits, data[:nbytes], lens, *(None if e is None else e[:k] for e in exc))
+
+
+def comm_unique_id():
+    """hsq_comm_unique_id: the 128-byte id a communicator is built from (rank 0 makes it, the host program distributes it)."""
+    lib = load()
+    buf = (C.c_uint8 * A.HSQ_COMM_ID_BYTES)()
+    st = lib.hsq_comm_unique_id(buf)
+    if st != 0:
+        raise HsqError(st, lib.hsq_last_error(None).decode())
+    return bytes(buf)
+
+
+def dedup_extend_multi_gpu(contexts, pair_batches, ext_uid_len, lig_uid_len, extend_duplicates=False, cigar_cap=32, md_cap=48):
+    """hsq_dedup_extend_multi_gpu: one process, one context per GPU, pair_batches[k] belongs to contexts[k]."""
+    lib = load()
+    n = len(contexts)
+    outs = [DedupExtendResult(pb.n, ctx.n_probes, cigar_cap, md_cap) for ctx, pb in zip(contexts, pair_batches)]
+    handles = (C.c_void_p * n)(*[ctx.h for ctx in contexts])
+    pcs = (A.PairBatch * n)(*[pb.c() for pb in pair_batches])
+    ocs = (A.DedupExtendOut * n)(*[o.c() for o in outs])
+    st = lib.hsq_dedup_extend_multi_gpu(handles, C.c_int32(n), pcs, C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                        C.c_int32(1 if extend_duplicates else 0), ocs)
+    for o, oc in zip(outs, ocs):
+        o.n_extended = int(oc.n_extended)
+        o.extend.cells = int(o._ext_c.cells)
+    if st != 0:
+        msgs = [lib.hsq_last_error(ctx.h).decode() for ctx in contexts]
+        raise HsqError(st, " | ".join(m for m in msgs if m))
+    return outs
 
 
 def quality_sums(quals, threads=0):
@@ -394,6 +424,52 @@ class Context:
         rc, oc, lc = reads.c(), out.c(), A.FindLimits(*[int(v) for v in limits])
         st = self.lib.hsq_find_matches(self.h, C.byref(rc), A.ptr(quals.data, A.u8p), C.c_int32(leading_quality), C.c_int32(trailing_quality),
                                        C.c_int32(candidate_limit), C.c_double(min_hit_ratio), C.byref(lc), C.byref(oc))
+        out.finish()
+        self._check(st)
+        return out
+
+    def dedup_packed(self, pairs: PackedPairsHost, ext_uid_len, lig_uid_len, n_probes=None):
+        """hsq_dedup_packed: hsq_dedup_batch for packed reads (quality bytes, or host-made quality sums)."""
+        n_probes = n_probes or self.n_probes
+        is_best = np.zeros(pairs.n, dtype=np.uint8)
+        group_size = np.zeros(pairs.n, dtype=np.int32)
+        stats = ProbeStatsHost(n_probes)
+        pc, sc = pairs.c(), stats.c()
+        self._check(self.lib.hsq_dedup_packed(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                              A.ptr(is_best, A.u8p), A.ptr(group_size, A.i32p), C.byref(sc)))
+        return is_best, group_size, stats
+
+    # ---- multi-GPU inside the library (NCCL) ----
+    def comm_init_rank(self, id_bytes, rank, world):
+        """hsq_comm_init_rank: join the communicator whose id rank 0 made with comm_unique_id()."""
+        buf = (C.c_uint8 * A.HSQ_COMM_ID_BYTES).from_buffer_copy(bytes(id_bytes))
+        self._check(self.lib.hsq_comm_init_rank(self.h, buf, C.c_int32(rank), C.c_int32(world)))
+
+    def comm_init_torch(self, group=None):
+        """One process per GPU under torch.distributed: rank 0 makes the id, broadcast, every rank joins."""
+        import torch.distributed as dist
+        rank, world = dist.get_rank(group), dist.get_world_size(group)
+        box = [comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0, group=group)
+        self.comm_init_rank(box[0], rank, world)
+
+    def dedup_sharded(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, n_probes=None, out=None):
+        """hsq_dedup_sharded (collective): dedup over the union of all ranks' pairs; answers for this rank's pairs."""
+        n_probes = n_probes or self.n_probes
+        is_best, group_size = out if out is not None else (np.zeros(pairs.n, dtype=np.uint8), np.zeros(pairs.n, dtype=np.int32))
+        stats = ProbeStatsHost(n_probes)
+        pc, sc = pairs.c(), stats.c()
+        self._check(self.lib.hsq_dedup_sharded(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                               A.ptr(is_best, A.u8p), A.ptr(group_size, A.i32p), C.byref(sc)))
+        return is_best, group_size, stats
+
+    def dedup_extend_sharded(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, extend_duplicates=False, cigar_cap=32, md_cap=48,
+                             n_probes=None, out=None):
+        """hsq_dedup_extend_sharded (collective)."""
+        out = out or DedupExtendResult(pairs.n, n_probes or self.n_probes, cigar_cap, md_cap)
+        pc, oc = pairs.c(), out.c()
+        st = self.lib.hsq_dedup_extend_sharded(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                               C.c_int32(1 if extend_duplicates else 0), C.byref(oc))
         out.finish()
         self._check(st)
         return out

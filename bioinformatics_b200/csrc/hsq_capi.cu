@@ -98,6 +98,8 @@ DeviceProbes probe_view(const hsq_ctx* ctx) {
     return p;
 }
 
+void comm_release(hsq_ctx* ctx);  // hsq_capi_comm.inl
+
 template <class T>
 int d2h(hsq_ctx* ctx, T* host, const T* dev, size_t count) {
     if (!host || count == 0) return HSQ_OK;
@@ -195,7 +197,8 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
                            &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
                            &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
                            &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->rg_start, &ctx->rg_end,
-                           &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32, &ctx->fi_start, &ctx->fi_len, &ctx->fi_refs, &ctx->fi_size, &ctx->pool_tmp, &ctx->pool_cursor, &ctx->pool_dev};
+                           &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32, &ctx->fi_start, &ctx->fi_len, &ctx->fi_refs, &ctx->fi_size, &ctx->pool_tmp, &ctx->pool_cursor, &ctx->pool_dev,
+                           &ctx->cm_send, &ctx->cm_recv, &ctx->cm_i32, &ctx->cm_cnt, &ctx->cm_tie, &ctx->cm_probe};
     for (auto* b : bufs) b->release();
     for (auto& b : ctx->ing) b.release();
     ctx->dd_seg.release();
@@ -217,6 +220,7 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
             if (ev) cudaEventDestroy(ev);
     for (cudaStream_t st : {ctx->s_cap[0], ctx->s_cap[1], ctx->s_prep, ctx->s_in, ctx->s_out, ctx->stream})
         if (st) cudaStreamDestroy(st);
+    comm_release(ctx);
     delete ctx;
 }
 
@@ -258,6 +262,7 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_resolve.inl"
 #include "hsq_capi_assign.inl"
 #include "hsq_capi_packed.inl"
+#include "hsq_capi_comm.inl"
 #include "hsq_capi_pipeline.inl"
 #include "hsq_capi_records.inl"
 #include "hsq_capi_find.inl"

@@ -150,7 +150,8 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_kernel(const uint
                                                                       const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank,
                                                                       uint8_t* __restrict__ is_best, int32_t* __restrict__ group_size,
                                                                       int32_t* __restrict__ unique_pairs, int32_t* __restrict__ duplicate_pairs,
-                                                                      int32_t* __restrict__ max_pairs, int skip_up_to) {
+                                                                      int32_t* __restrict__ max_pairs, int skip_up_to,
+                                                                      const uint32_t* __restrict__ tie) {
     extern __shared__ __align__(16) unsigned char dedup_smem[];
     // per pair: its UID and its table slot; per table slot (2 x cap of them): claiming pair + 1, best rank, best pair, pairs
     uint64_t* s_uid = reinterpret_cast<uint64_t*>(dedup_smem);
@@ -199,7 +200,7 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_kernel(const uint
         for (int j = tid; j < m; j += DEDUP_SEG_BLOCK) {  // among the pairs with the best rank the earliest pair wins
             const uint32_t i = seg[b + j];
             const int slot = s_slot[j];
-            if ((unsigned long long)rank[i] == t_best[slot]) atomicMin(&t_bidx[slot], i);
+            if ((unsigned long long)rank[i] == t_best[slot]) atomicMin(&t_bidx[slot], tie ? tie[i] : i);
         }
         __syncthreads();
         int mx = 0;
@@ -207,7 +208,7 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_kernel(const uint
             const uint32_t i = seg[b + j];
             const int slot = s_slot[j];
             const int size = t_cnt[slot];
-            is_best[i] = t_bidx[slot] == i ? 1 : 0;
+            is_best[i] = t_bidx[slot] == (tie ? tie[i] : i) ? 1 : 0;
             group_size[i] = size;
             mx = max(mx, size);
         }
@@ -236,7 +237,7 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_small_kernel(cons
                                                                             const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank,
                                                                             uint8_t* __restrict__ is_best, int32_t* __restrict__ group_size,
                                                                             int32_t* __restrict__ unique_pairs, int32_t* __restrict__ duplicate_pairs,
-                                                                            int32_t* __restrict__ max_pairs) {
+                                                                            int32_t* __restrict__ max_pairs, const uint32_t* __restrict__ tie) {
     __shared__ uint64_t s_rank[DEDUP_SEG_BLOCK / 32][32];
     __shared__ uint32_t s_idx[DEDUP_SEG_BLOCK / 32][32];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -248,14 +249,15 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_small_kernel(cons
         if (m == 0 || m > DEDUP_SMALL_MAX) continue;  // warp-uniform; larger probes belong to dedup_group_kernel
         const bool active = lane < m;
         const unsigned amask = __ballot_sync(0xffffffffu, active);
-        uint32_t i = 0;
+        uint32_t i = 0, t = 0;
         uint64_t u = 0, r = 0;
         if (active) {
             i = seg[b + lane];
             u = uid[i];
             r = rank[i];
+            t = tie ? tie[i] : i;  // last tie-break: the pair's place in the whole (possibly sharded) batch
             s_rank[wib][lane] = r;
-            s_idx[wib][lane] = i;
+            s_idx[wib][lane] = t;
         }
         __syncwarp();
         int size = 0;
@@ -268,7 +270,7 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_small_kernel(cons
             for (unsigned q = peers & ~(1u << lane); q; q &= q - 1) {
                 const int o = __ffs(q) - 1;
                 const uint64_t ro = s_rank[wib][o];
-                if (ro < r || (ro == r && s_idx[wib][o] < i)) best = false;
+                if (ro < r || (ro == r && s_idx[wib][o] < t)) best = false;
             }
             is_best[i] = best ? 1 : 0;
             group_size[i] = size;
@@ -300,7 +302,8 @@ __global__ void dedup_pack_keys_kernel(const uint64_t* __restrict__ uid, const u
 }
 
 __global__ void dedup_unpack_keys_kernel(const hsq_dedup_key* __restrict__ in, int64_t n, int64_t n_probes, uint64_t* __restrict__ uid,
-                                         uint64_t* __restrict__ rank, int32_t* __restrict__ probe, uint32_t* __restrict__ idx, int* status) {
+                                         uint64_t* __restrict__ rank, int32_t* __restrict__ probe, uint32_t* __restrict__ idx,
+                                         uint32_t* __restrict__ origin, int* status) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (; i < n; i += stride) {
@@ -309,6 +312,7 @@ __global__ void dedup_unpack_keys_kernel(const hsq_dedup_key* __restrict__ in, i
         rank[i] = k.rank;
         probe[i] = k.probe;
         idx[i] = (uint32_t)i;
+        origin[i] = k.origin;
         if (k.probe < 0 || k.probe >= n_probes) atomicMin(status, HSQ_ERR_INVALID_ARGUMENT);
     }
 }
@@ -386,7 +390,10 @@ int dedup_upload_keygen(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, in
 // Sort + segmented reduce over key columns that are already on the device: probe -> ctx->probe_id, uid -> sort_a,
 // rank -> sort_b, pair index -> sort_d[0..n).  Results (per pair, in input order) go to d_best / d_gs (device) and the
 // per-probe counters to d_stats[3 * np] (device).
-int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_t* d_best, int32_t* d_gs, int32_t* d_stats) {
+// tie: optional last tie-break per pair (smaller wins) among pairs of equal (quality sum, read index); null = the pair index.  The
+// sharded path passes the pair's global position so that the answer does not depend on how the batch was split over ranks.
+int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_t* d_best, int32_t* d_gs, int32_t* d_stats,
+                        const uint32_t* tie = nullptr) {
     const size_t nn = (size_t)n;
     int rc;
     HSQ_CUDA(ctx, ctx->sort_c.ensure(nn * 8 + 16));   // keys pong
@@ -430,11 +437,11 @@ int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_
             const int sblocks = (int)std::max<int64_t>(1, std::min<int64_t>(np, (int64_t)ctx->sm_count * std::max(per_sm, 1)));
             dedup_scatter_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, start, ia, ib);
             const int wblocks = (int)std::max<int64_t>(1, std::min<int64_t>((np + 7) / 8, (int64_t)ctx->sm_count * 8));
-            dedup_group_small_kernel<<<wblocks, DEDUP_SEG_BLOCK, 0, ctx->stream>>>(ib, start, np, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
+            dedup_group_small_kernel<<<wblocks, DEDUP_SEG_BLOCK, 0, ctx->stream>>>(ib, start, np, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np, tie);
             ctx->launches += 2;
             if (max_count > DEDUP_SMALL_MAX) {
                 dedup_group_kernel<<<sblocks, DEDUP_SEG_BLOCK, smem, ctx->stream>>>(ib, start, np, cap, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np,
-                                                                                   DEDUP_SMALL_MAX);
+                                                                                   DEDUP_SMALL_MAX, tie);
                 ctx->launches++;
             }
             HSQ_CUDA(ctx, cudaGetLastError());
@@ -446,20 +453,33 @@ int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_
     }
     if (n > 0) {
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
-        // pass 1: by rank (48 bits) -> ib;  pass 2: by UID -> ia;  pass 3: by probe -> ib
-        if ((rc = sort_pass(ctx, ka, kb, ia, ib, n, 48))) return rc;
-        if (uid_len > 0) {
-            gather_u64_kernel<uint64_t><<<gblocks, 256, 0, ctx->stream>>>(uid, ib, n, ka);
+        // stable LSD passes, least significant key first: [tie] -> rank (48 bits) -> UID -> probe.  cur holds the current order.
+        uint32_t *cur = ia, *nxt = ib;
+        if (tie) {
+            HSQ_CUDA(ctx, ctx->misc.ensure(nn * 8 + 16));
+            uint64_t* rank_copy = ctx->misc.as<uint64_t>();
+            HSQ_CUDA(ctx, cudaMemcpyAsync(rank_copy, ka, nn * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+            gather_u64_kernel<uint32_t><<<gblocks, 256, 0, ctx->stream>>>(tie, cur, n, ka);
             ctx->launches++;
-            if ((rc = sort_pass(ctx, ka, kb, ib, ia, n, 2 * uid_len))) return rc;
-        } else {
-            HSQ_CUDA(ctx, cudaMemcpyAsync(ia, ib, nn * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+            if ((rc = sort_pass(ctx, ka, kb, cur, nxt, n, 32))) return rc;
+            std::swap(cur, nxt);
+            gather_u64_kernel<uint64_t><<<gblocks, 256, 0, ctx->stream>>>(rank_copy, cur, n, ka);
+            ctx->launches++;
         }
-        gather_u64_kernel<int32_t><<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), ia, n, ka);
+        if ((rc = sort_pass(ctx, ka, kb, cur, nxt, n, 48))) return rc;
+        std::swap(cur, nxt);
+        if (uid_len > 0) {
+            gather_u64_kernel<uint64_t><<<gblocks, 256, 0, ctx->stream>>>(uid, cur, n, ka);
+            ctx->launches++;
+            if ((rc = sort_pass(ctx, ka, kb, cur, nxt, n, 2 * uid_len))) return rc;
+            std::swap(cur, nxt);
+        }
+        gather_u64_kernel<int32_t><<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), cur, n, ka);
         ctx->launches++;
-        if ((rc = sort_pass(ctx, ka, kb, ia, ib, n, bits_for((uint64_t)std::max<int64_t>(np, 1))))) return rc;
-        dedup_heads_kernel<<<gblocks, 256, 0, ctx->stream>>>(ib, ctx->probe_id.as<int32_t>(), uid, n, head, d_best);
-        dedup_groups_kernel<<<gblocks, 256, 0, ctx->stream>>>(ib, ctx->probe_id.as<int32_t>(), head, n, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
+        if ((rc = sort_pass(ctx, ka, kb, cur, nxt, n, bits_for((uint64_t)std::max<int64_t>(np, 1))))) return rc;
+        std::swap(cur, nxt);
+        dedup_heads_kernel<<<gblocks, 256, 0, ctx->stream>>>(cur, ctx->probe_id.as<int32_t>(), uid, n, head, d_best);
+        dedup_groups_kernel<<<gblocks, 256, 0, ctx->stream>>>(cur, ctx->probe_id.as<int32_t>(), head, n, d_gs, d_stats, d_stats + np, d_stats + 2 * np);
         ctx->launches += 2;
         HSQ_CUDA(ctx, cudaGetLastError());
     }
@@ -546,17 +566,19 @@ extern "C" int32_t hsq_dedup_reduce_keys(hsq_ctx* ctx, const hsq_dedup_key* d_ke
     HSQ_CUDA(ctx, ctx->sort_d.ensure(nn * 8 + 16));
     HSQ_CUDA(ctx, ctx->probe_id.ensure(nn * 4 + 16));
     HSQ_CUDA(ctx, ctx->out_i32.ensure(3 * (size_t)np * 4 + 16));
+    HSQ_CUDA(ctx, ctx->cm_tie.ensure(nn * 4 + 16));
     if (n > 0) {
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
         dedup_unpack_keys_kernel<<<gblocks, 256, 0, ctx->stream>>>(d_keys, n, np, ctx->sort_a.as<uint64_t>(), ctx->sort_b.as<uint64_t>(),
-                                                                  ctx->probe_id.as<int32_t>(), ctx->sort_d.as<uint32_t>(), d_status(ctx));
+                                                                  ctx->probe_id.as<int32_t>(), ctx->sort_d.as<uint32_t>(), ctx->cm_tie.as<uint32_t>(), d_status(ctx));
         ctx->launches++;
         int w[1];
         if ((rc = read_status(ctx, w, 1))) return rc;
         if (w[0] != 0) return fail(ctx, w[0], "hsq_dedup_reduce_keys: probe out of range in a key record");
     }
     int32_t* d_stats = ctx->out_i32.as<int32_t>();
-    rc = dedup_reduce_device(ctx, n, np, uid_len, d_is_best, d_group_size, d_stats);
+    // the origin field is the last tie-break: with globally unique origins the answer does not depend on the arrival order of the records
+    rc = dedup_reduce_device(ctx, n, np, uid_len, d_is_best, d_group_size, d_stats, ctx->cm_tie.as<uint32_t>());
     if (!rc) rc = fetch_stats(ctx, stats, d_stats);
     int rc2 = timer.finish();
     return rc ? rc : rc2;

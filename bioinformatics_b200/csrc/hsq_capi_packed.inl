@@ -38,13 +38,14 @@ __device__ __forceinline__ uint8_t packed_to_code(uint32_t v, int bits) {
 
 // One warp per read: lane i writes bases i, i + 32, ...  (a warp store covers 32 consecutive code bytes; the packed words of a
 // read are read by all lanes and stay in L1).  HBM: bits/8 B read + 1 B written per base.
+template <int bits>
 __global__ void unpack_kernel(const uint32_t* __restrict__ words, const int64_t* __restrict__ word_off, const int64_t* __restrict__ offsets,
-                              int64_t n, int bits, uint8_t* __restrict__ codes) {
+                              int64_t n, uint8_t* __restrict__ codes) {
     const int lane = threadIdx.x & 31;
     int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    const int per = 32 / bits;
-    const uint32_t mask = (1u << bits) - 1u;
+    constexpr int per = 32 / bits;
+    constexpr uint32_t mask = (1u << bits) - 1u;
     for (; w < n; w += stride) {
         const uint32_t* src = words + word_off[w];
         const int64_t dst = offsets[w];
@@ -361,8 +362,10 @@ int unpack_seqs(hsq_ctx* ctx, DevSeqsOwned* d) {
     if ((rc = scan_i64(ctx, words, n, tiles, d->word_off.as<int64_t>()))) return rc;
     if (n > 0) {
         const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
-        unpack_kernel<<<blocks, 256, 0, ctx->stream>>>(d->ascii.as<uint32_t>(), d->word_off.as<int64_t>(), d->offsets.as<int64_t>(), n, d->packed_bits,
-                                                      d->codes.as<uint8_t>());
+        if (d->packed_bits == 2)
+            unpack_kernel<2><<<blocks, 256, 0, ctx->stream>>>(d->ascii.as<uint32_t>(), d->word_off.as<int64_t>(), d->offsets.as<int64_t>(), n, d->codes.as<uint8_t>());
+        else
+            unpack_kernel<4><<<blocks, 256, 0, ctx->stream>>>(d->ascii.as<uint32_t>(), d->word_off.as<int64_t>(), d->offsets.as<int64_t>(), n, d->codes.as<uint8_t>());
         ctx->launches++;
     }
     if (d->n_exc > 0) {
@@ -403,50 +406,58 @@ int check_packed_reads(hsq_ctx* ctx, const hsq_packed_reads* r, int64_t n, const
     return HSQ_OK;
 }
 
-// Host pass over a packed pair batch: per chunk the first word / exception of both sides, totals, longest read; validates lengths
-// and probe ids.  (Sizes only -- what the copies need to be issued.)
+// Host pass over a packed pair batch, one chunk at a time and in chunk order (so that it overlaps the device work of the chunks
+// before): first word / exception of both sides, totals, longest read; validates lengths and probe ids.  (Sizes only -- what the
+// copies need to be issued.)
 struct PackedChunks {
     std::vector<int64_t> starts;           // n_chunks + 1 pair indexes
     std::vector<int64_t> word[2], base[2]; // cumulative words / bases at every chunk start (n_chunks + 1)
     std::vector<int64_t> exc[2];           // first exception at every chunk start
     std::vector<int> read_max;             // per chunk
-    int chunk_of(int64_t a) const { return (int)(std::lower_bound(starts.begin(), starts.end(), a) - starts.begin()); }
+    int done = 0;                          // chunks scanned so far
+    int chunk_of(int64_t a) const { return (int)(std::upper_bound(starts.begin(), starts.end(), a) - starts.begin()) - 1; }
+    void init() {
+        const size_t nc = starts.size() - 1;
+        read_max.assign(nc, 0);
+        for (int s = 0; s < 2; s++) {
+            word[s].assign(nc + 1, 0);
+            base[s].assign(nc + 1, 0);
+            exc[s].assign(nc + 1, 0);
+        }
+        done = 0;
+    }
 };
 
-int scan_packed_chunks(hsq_ctx* ctx, const hsq_packed_pairs* pb, bool check_probes, PackedChunks* pc) {
-    const int nc = (int)pc->starts.size() - 1;
-    const hsq_packed_reads* sides[2] = {&pb->r1, &pb->r2};
-    pc->read_max.assign((size_t)nc, 0);
-    for (int s = 0; s < 2; s++) {
-        pc->word[s].assign((size_t)nc + 1, 0);
-        pc->base[s].assign((size_t)nc + 1, 0);
-        pc->exc[s].assign((size_t)nc + 1, 0);
-        const hsq_packed_reads* r = sides[s];
-        int64_t w = 0, b = 0;
-        bool bad = false;
-        for (int c = 0; c < nc; c++) {
-            int mx = pc->read_max[(size_t)c];
-            for (int64_t k = pc->starts[(size_t)c]; k < pc->starts[(size_t)c + 1]; k++) {
+int scan_packed_chunk(hsq_ctx* ctx, const hsq_packed_pairs* pb, bool check_probes, PackedChunks* pc, int c) {
+    for (; pc->done <= c; pc->done++) {
+        const size_t cc = (size_t)pc->done;
+        const int64_t k0 = pc->starts[cc], k1 = pc->starts[cc + 1];
+        const hsq_packed_reads* sides[2] = {&pb->r1, &pb->r2};
+        int mx = 0;
+        for (int s = 0; s < 2; s++) {
+            const hsq_packed_reads* r = sides[s];
+            const int bits = r->bits;
+            int64_t w = 0, b = 0;
+            int lo = 0;
+            for (int64_t k = k0; k < k1; k++) {
                 const int32_t l = r->len[k];
-                bad |= l < 0;
+                lo = std::min(lo, l);
                 mx = std::max(mx, l);
-                w += hsq::packed_words_of(l, r->bits);
+                w += ((int64_t)l * bits + 31) >> 5;
                 b += l;
             }
-            pc->read_max[(size_t)c] = mx;
-            pc->word[s][(size_t)c + 1] = w;
-            pc->base[s][(size_t)c + 1] = b;
+            if (lo < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "packed batch: negative read length");
+            pc->word[s][cc + 1] = pc->word[s][cc] + w;
+            pc->base[s][cc + 1] = pc->base[s][cc] + b;
+            pc->exc[s][cc + 1] = r->n_exceptions == 0 ? 0
+                : (int64_t)(std::lower_bound(r->exc_read + pc->exc[s][cc], r->exc_read + r->n_exceptions, (uint32_t)std::min<int64_t>(k1, UINT32_MAX)) - r->exc_read);
         }
-        if (bad) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "packed batch: negative read length");
-        for (int c = 0; c <= nc; c++)
-            pc->exc[s][(size_t)c] = r->n_exceptions == 0 ? 0
-                : (int64_t)(std::lower_bound(r->exc_read, r->exc_read + r->n_exceptions, (uint32_t)std::min<int64_t>(pc->starts[(size_t)c], UINT32_MAX)) - r->exc_read);
-        pc->exc[s][(size_t)nc] = r->n_exceptions;
-    }
-    if (check_probes) {
-        bool bad = false;
-        for (int64_t k = 0; k < pb->n; k++) bad |= (pb->probe_id[k] < 0) | (pb->probe_id[k] >= ctx->n_probes);
-        if (bad) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "packed batch: probe_id out of range");
+        pc->read_max[cc] = mx;
+        if (check_probes) {
+            bool bad = false;
+            for (int64_t k = k0; k < k1; k++) bad |= (pb->probe_id[k] < 0) | (pb->probe_id[k] >= ctx->n_probes);
+            if (bad) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "packed batch: probe_id out of range");
+        }
     }
     return HSQ_OK;
 }
@@ -561,14 +572,16 @@ extern "C" int32_t hsq_extend_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs
     PackedChunks pc;
     const int n_chunks = pick_chunks(ctx, n);
     pc.starts = chunk_starts(ctx, n, n_chunks);
+    pc.init();
     PoolState ps;
-    rc = scan_packed_chunks(ctx, pairs, true, &pc);
-    if (!rc) rc = pool_begin(ctx, out, &ps);
+    rc = pool_begin(ctx, out, &ps);
     if (!rc && n > 0) {
         ExtendChunkIO io;
         io.dims = [&](int64_t a, int64_t, int* read_max) {
-            *read_max = pc.read_max[(size_t)pc.chunk_of(a)];
-            return HSQ_OK;
+            const int c = pc.chunk_of(a);
+            const int r = scan_packed_chunk(ctx, pairs, true, &pc, c);
+            *read_max = pc.read_max[(size_t)c];
+            return r;
         };
         io.stage = [&](int64_t a, int64_t) { return stage_packed_chunk(ctx, pairs, pc, pc.chunk_of(a)); };
         io.fetch = [&](int64_t a, int64_t m) { return fetch_pooled_chunk(ctx, a, m, out, ps); };
@@ -614,4 +627,143 @@ extern "C" int32_t hsq_unpack_reads(hsq_ctx* ctx, const hsq_packed_reads* reads,
     if ((rc = read_status(ctx, w, 1))) return rc;
     if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_unpack_reads: ") + (w[0] == HSQ_ERR_INVALID_ARGUMENT ? "an exception lies outside its read" : status_message(w[0])));
     return timer.finish();
+}
+
+// ---- hsq_dedup_packed: FilterByUid key generation from a packed batch ----------------------------------------------------------
+namespace hsq {
+
+// One warp per pair, as dedup_keygen_kernel, reading device codes (A=1 C=2 G=4 T=8) instead of ASCII.  qs1 / qs2 non-null: the
+// per-read quality sums come from the host (hsq_quality_sums) and the quality bytes are not touched.
+__global__ void dedup_keygen_codes_kernel(const uint8_t* __restrict__ c1, const int64_t* __restrict__ off1, const uint8_t* __restrict__ q1,
+                                          const uint8_t* __restrict__ c2, const int64_t* __restrict__ off2, const uint8_t* __restrict__ q2,
+                                          const int16_t* __restrict__ qs1, const int16_t* __restrict__ qs2, const int32_t* __restrict__ read_index,
+                                          int64_t n, int u, int v, uint64_t* __restrict__ uid_out, uint64_t* __restrict__ rank_out,
+                                          uint32_t* __restrict__ idx_out, int* status) {
+    const int lane = threadIdx.x & 31;
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    for (; w < n; w += stride) {
+        const int64_t b1 = off1[w], b2 = off2[w];
+        const int l1 = (int)(off1[w + 1] - b1), l2 = (int)(off2[w + 1] - b2);
+        int sum = 0;
+        if (qs1) {
+            sum = (int)qs1[w] + (int)qs2[w];
+        } else {
+            for (int i = lane; i < l1; i += 32) sum += (int)q1[b1 + i] - 33;
+            for (int i = lane; i < l2; i += 32) sum += (int)q2[b2 + i] - 33;
+            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        }
+        uint64_t code = 0;
+        bool bad = false, short_read = false;
+        if (lane < u + v) {
+            uint8_t c;
+            if (lane < u) { short_read = lane >= l1; c = short_read ? 1 : c1[b1 + lane]; }
+            else { short_read = (lane - u) >= l2; c = short_read ? 1 : c2[b2 + lane - u]; }
+            switch (c) {
+                case 1: code = 0; break;
+                case 2: code = 1; break;
+                case 4: code = 2; break;
+                case 8: code = 3; break;
+                default: bad = true;
+            }
+            code <<= 2 * (u + v - 1 - lane);
+        }
+        for (int o = 16; o > 0; o >>= 1) code |= __shfl_xor_sync(0xffffffffu, code, o);
+        if (__any_sync(0xffffffffu, short_read)) { if (lane == 0) atomicMin(status, HSQ_ERR_OUT_OF_RANGE); }
+        else if (__any_sync(0xffffffffu, bad)) { if (lane == 0) atomicMin(status, HSQ_ERR_UNSUPPORTED); }
+        if (lane == 0) {
+            const int16_t qsum = (int16_t)sum;
+            uid_out[w] = code;
+            rank_out[w] = ((uint64_t)(uint16_t)(32767 - (int)qsum) << 32) | (uint64_t)((uint32_t)read_index[w] ^ 0x80000000u);
+            idx_out[w] = (uint32_t)w;
+        }
+    }
+}
+
+}  // namespace hsq
+
+namespace {
+
+// host -> device copies of a packed pair batch, unpack, key generation: uid -> sort_a, rank -> sort_b, pair index -> sort_d[0..n)
+int dedup_upload_keygen_packed(hsq_ctx* ctx, const hsq_packed_pairs* pb, int u, int v, int64_t np) {
+    const int64_t n = pb->n;
+    const size_t nn = (size_t)n;
+    int rc = reset_status(ctx);
+    if (rc) return rc;
+    PackedChunks pc;
+    pc.starts = {0, n};
+    pc.init();
+    if ((rc = scan_packed_chunk(ctx, pb, false, &pc, 0))) return rc;
+    if ((rc = stage_packed_chunk(ctx, pb, pc, 0))) return rc;
+    const bool sums = pb->qsum1 && pb->qsum2;
+    struct { hsq::DevBuf* d; const void* h; size_t bytes; } up[] = {
+        {&ctx->q1, sums ? (const void*)pb->qsum1 : (const void*)pb->q1, sums ? nn * 2 : (size_t)pc.base[0][1]},
+        {&ctx->q2, sums ? (const void*)pb->qsum2 : (const void*)pb->q2, sums ? nn * 2 : (size_t)pc.base[1][1]},
+        {&ctx->read_index, pb->read_index, nn * 4}};
+    for (auto& c : up) {
+        if (c.bytes && !c.h) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_dedup_packed: null input array");
+        HSQ_CUDA(ctx, c.d->ensure(c.bytes + 16));
+        if (c.bytes) HSQ_CUDA(ctx, cudaMemcpyAsync(c.d->p, c.h, c.bytes, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if ((rc = unpack_seqs(ctx, &ctx->r1)) || (rc = unpack_seqs(ctx, &ctx->r2))) return rc;
+    HSQ_CUDA(ctx, ctx->sort_a.ensure(nn * 8 + 16));
+    HSQ_CUDA(ctx, ctx->sort_b.ensure(nn * 8 + 16));
+    HSQ_CUDA(ctx, ctx->sort_d.ensure(nn * 8 + 16));
+    if (n > 0) {
+        const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
+        const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        check_probe_ids_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, np > 0 ? np : INT32_MAX, d_status(ctx));
+        dedup_keygen_codes_kernel<<<blocks, 256, 0, ctx->stream>>>(
+            ctx->r1.codes.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), ctx->q1.as<uint8_t>(), ctx->r2.codes.as<uint8_t>(), ctx->r2.offsets.as<int64_t>(),
+            ctx->q2.as<uint8_t>(), sums ? ctx->q1.as<int16_t>() : nullptr, sums ? ctx->q2.as<int16_t>() : nullptr, ctx->read_index.as<int32_t>(), n, u, v,
+            ctx->sort_a.as<uint64_t>(), ctx->sort_b.as<uint64_t>(), ctx->sort_d.as<uint32_t>(), d_status(ctx));
+        ctx->launches += 2;
+        int w[1];
+        if ((rc = read_status(ctx, w, 1))) return rc;
+        if (w[0] != 0)
+            return fail(ctx, w[0], w[0] == HSQ_ERR_UNSUPPORTED ? "hsq_dedup_packed: a UID holds a base other than A,C,G,T (filter N reads first, "
+                                                                 "PrimerReadExtensionAndPcrDuplicateIdentification.java:815-821)"
+                                   : w[0] == HSQ_ERR_INVALID_ARGUMENT ? "hsq_dedup_packed: probe_id out of range, negative length or a misplaced exception"
+                                   : w[0] == HSQ_ERR_BAD_CHARACTER ? "hsq_dedup_packed: an exception character is not an IUPAC code"
+                                                                   : "hsq_dedup_packed: a read is shorter than its UID");
+    }
+    // the staged batch now holds valid codes: a following extend stage must not decode again
+    ctx->r1.packed_bits = ctx->r2.packed_bits = -1;
+    return HSQ_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_dedup_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs, int32_t u, int32_t v, uint8_t* is_best, int32_t* group_size,
+                                    hsq_probe_stats* stats) {
+    if (!ctx || !pairs || (pairs->n > 0 && !is_best)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    const int64_t n = pairs->n;
+    if (n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
+    if (n > 0 && !pairs->probe_id) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe_id is null");
+    if (u < 0 || v < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative UID length");
+    if (u + v > 32) return fail(ctx, HSQ_ERR_UNSUPPORTED, "UID longer than 32 bases in total is outside the accelerated domain");
+    if (!stats || stats->n_probes <= 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe stats (with n_probes) are required");
+    int rc;
+    if ((rc = check_packed_reads(ctx, &pairs->r1, n, "hsq_dedup_packed")) || (rc = check_packed_reads(ctx, &pairs->r2, n, "hsq_dedup_packed"))) return rc;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    const size_t nn = (size_t)n;
+    const int64_t np = stats->n_probes;
+    auto run = [&]() -> int {
+        int rc = dedup_upload_keygen_packed(ctx, pairs, u, v, np);
+        if (rc) return rc;
+        HSQ_CUDA(ctx, ctx->out_u8.ensure(nn + 32));
+        HSQ_CUDA(ctx, ctx->out_i32.ensure((nn + 3 * (size_t)np) * 4 + 16));
+        uint8_t* best = ctx->out_u8.as<uint8_t>();
+        int32_t* d_gs = ctx->out_i32.as<int32_t>();
+        int32_t* d_stats = d_gs + nn;
+        if ((rc = dedup_reduce_device(ctx, n, np, u + v, best, d_gs, d_stats))) return rc;
+        if ((rc = d2h(ctx, is_best, best, nn))) return rc;
+        if ((rc = d2h(ctx, group_size, d_gs, nn))) return rc;
+        return fetch_stats(ctx, stats, d_stats);
+    };
+    rc = run();
+    ctx->r1.packed_bits = ctx->r2.packed_bits = 0;
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
 }

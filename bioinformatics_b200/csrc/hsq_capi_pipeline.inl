@@ -130,8 +130,9 @@ int compact_survivors(hsq_ctx* ctx, int64_t n, const uint8_t* d_keep, int32_t* d
 
 }  // namespace
 
-extern "C" int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, int32_t extend_duplicates,
-                                          hsq_dedup_extend_out* out) {
+namespace {
+
+int dedup_extend_args(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, const hsq_dedup_extend_out* out) {
     if (!ctx || !pairs || !out || !out->is_best || !out->extend || !out->extended_pair) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
     if (pairs->n < 0 || pairs->r1.n != pairs->n || pairs->r2.n != pairs->n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
     if (pairs->n >= (1ll << 31)) return fail(ctx, HSQ_ERR_UNSUPPORTED, "more than 2^31 pairs in one batch");
@@ -142,58 +143,140 @@ extern "C" int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pa
     int rc = extend_args_ok(ctx);
     if (rc) return rc;
     if (out->stats->n_probes != ctx->n_probes) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "stats->n_probes differs from the probe table");
-    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
-    CallTimer timer(ctx);
+    return HSQ_OK;
+}
+
+// The probe task body for this context's pairs.  sharded: the reduction runs over the union of all ranks' pairs (collective, see
+// hsq_capi_comm.inl) and the per-probe counters are those of the whole batch; the extension runs on this rank's own pairs.
+int dedup_extend_run(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, int32_t extend_duplicates, hsq_dedup_extend_out* out, bool sharded) {
     const int64_t n = pairs->n, np = out->stats->n_probes;
     const size_t nn = (size_t)n;
     out->n_extended = 0;
-    auto run = [&]() -> int {
-        int rc;
-        if ((rc = dedup_upload_keygen(ctx, pairs, u, v, np))) return rc;
-        HSQ_CUDA(ctx, ctx->dd_u8.ensure(nn + 32));
-        HSQ_CUDA(ctx, ctx->dd_i32.ensure((2 * nn + 5 * (size_t)np) * 4 + 16));
-        uint8_t* d_best = ctx->dd_u8.as<uint8_t>();
-        int32_t* d_gs = ctx->dd_i32.as<int32_t>();
-        int32_t* d_list = d_gs + nn;
-        int32_t* d_stats = d_list + nn;
-        int32_t* d_unable = d_stats + 3 * np;
-        if ((rc = dedup_reduce_device(ctx, n, np, u + v, d_best, d_gs, d_stats))) return rc;
+    int rc;
+    int bad = dedup_upload_keygen(ctx, pairs, u, v, np);
+    if (bad && !sharded) return bad;
+    const std::string bad_msg = ctx->error;
+    HSQ_CUDA(ctx, ctx->dd_u8.ensure(nn + 32));
+    HSQ_CUDA(ctx, ctx->dd_i32.ensure((2 * nn + 5 * (size_t)np) * 4 + 16));
+    uint8_t* d_best = ctx->dd_u8.as<uint8_t>();
+    int32_t* d_gs = ctx->dd_i32.as<int32_t>();
+    int32_t* d_list = d_gs + nn;
+    int32_t* d_stats = d_list + nn;
+    int32_t* d_unable = d_stats + 3 * np;
+    if (sharded) {  // a rank whose own batch is bad still takes part in the collectives (with no pairs), or the others would hang
+        if (bad) HSQ_CUDA(ctx, cudaMemsetAsync(d_status(ctx), 0, 4, ctx->stream));
+        rc = dedup_exchange_reduce(ctx, bad ? 0 : n, np, u + v, d_best, d_gs, d_stats);
+    } else {
+        rc = dedup_reduce_device(ctx, n, np, u + v, d_best, d_gs, d_stats);
+    }
+    if (rc && !sharded) return rc;
+    const bool skip = bad || rc;  // sharded: the second collective below must still be entered
+    if (!skip) {
         HSQ_CUDA(ctx, cudaMemsetAsync(d_unable, 0, 2 * (size_t)np * 4, ctx->stream));
         if ((rc = d2h(ctx, out->is_best, d_best, nn))) return rc;
         if ((rc = d2h(ctx, out->group_size, d_gs, nn))) return rc;
         if ((rc = fetch_stats(ctx, out->stats, d_stats))) return rc;
-        int64_t m = n;
-        const bool compact = !extend_duplicates && n > 0;
+    }
+    int64_t m = skip ? 0 : n;
+    const bool compact = !extend_duplicates && m > 0;
+    bool swapped = false;
+    int rce = HSQ_OK;
+    if (!skip) {
         if (compact) {
-            if ((rc = compact_survivors(ctx, n, d_best, d_list, &m))) return rc;
-            swap_read_buffers(ctx);  // the compacted pairs are the staged batch now
+            if ((rce = compact_survivors(ctx, n, d_best, d_list, &m))) m = 0;
+            else {
+                swap_read_buffers(ctx);  // the compacted pairs are the staged batch now
+                swapped = true;
+            }
         } else if (n > 0) {
             const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
             iota_kernel<<<gblocks, 256, 0, ctx->stream>>>(d_list, n);
             ctx->launches++;
         }
-        if ((rc = d2h(ctx, out->extended_pair, d_list, (size_t)m))) return rc;
-        ctx->ext_n = m;
-        ctx->keep_counters = false;
-        rc = extend_run(ctx, out->extend->cigar_cap, out->extend->md_cap);
-        if (!rc && m > 0) {
+        if (!rce) rce = d2h(ctx, out->extended_pair, d_list, (size_t)m);
+        if (!rce) {
+            ctx->ext_n = m;
+            ctx->keep_counters = false;
+            rce = extend_run(ctx, out->extend->cigar_cap, out->extend->md_cap);
+        }
+        if (!rce && m > 0) {
             const int gblocks = (int)std::min<int64_t>((m + 255) / 256, (int64_t)ctx->sm_count * 16);
             unable_to_extend_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->pair_ok.as<uint8_t>(), d_list, d_best, ctx->probe_id.as<int32_t>(), m,
                                                                      d_unable, d_unable + np);
             ctx->launches++;
         }
-        if (!rc) rc = d2h(ctx, out->unique_unable_to_extend, d_unable, (size_t)np);
-        if (!rc) rc = d2h(ctx, out->duplicate_unable_to_extend, d_unable + np, (size_t)np);
-        if (!rc) rc = extend_fetch(ctx, out->extend);
-        if (compact) swap_read_buffers(ctx);
-        ctx->ext_n = -1;
-        ctx->ext_ran = false;
-        if (!rc) out->n_extended = m;
-        return rc;
-    };
-    rc = run();
+    } else {
+        HSQ_CUDA(ctx, cudaMemsetAsync(d_unable, 0, 2 * (size_t)np * 4, ctx->stream));
+    }
+    if (sharded) {  // "unable to extend" is counted where the reads are: sum over ranks
+        ncclResult_t r = nccl_api()->AllReduce(d_unable, d_unable, (size_t)(2 * np), ncclInt32, ncclSum, static_cast<ncclComm_t>(ctx->comm), ctx->stream);
+        if (r != ncclSuccess && !rce) rce = fail(ctx, HSQ_ERR_CUDA, std::string("ncclAllReduce: ") + nccl_api()->GetErrorString(r));
+    }
+    if (!skip) {
+        if (!rce) rce = d2h(ctx, out->unique_unable_to_extend, d_unable, (size_t)np);
+        if (!rce) rce = d2h(ctx, out->duplicate_unable_to_extend, d_unable + np, (size_t)np);
+        if (!rce) rce = extend_fetch(ctx, out->extend);
+    }
+    if (swapped) swap_read_buffers(ctx);
+    ctx->ext_n = -1;
+    ctx->ext_ran = false;
+    if (bad) return fail(ctx, bad, bad_msg);
+    if (rc) return rc;
+    if (rce) return rce;
+    out->n_extended = m;
+    return HSQ_OK;
+}
+
+}  // namespace
+
+extern "C" int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, int32_t extend_duplicates,
+                                          hsq_dedup_extend_out* out) {
+    int rc = dedup_extend_args(ctx, pairs, u, v, out);
+    if (rc) return rc;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    rc = dedup_extend_run(ctx, pairs, u, v, extend_duplicates, out, false);
     int rc2 = timer.finish();
     return rc ? rc : rc2;
+}
+
+// hsq_dedup_extend_batch over the union of all ranks' pairs: collective, every rank of the communicator calls it with its own pairs.
+extern "C" int32_t hsq_dedup_extend_sharded(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, int32_t extend_duplicates,
+                                            hsq_dedup_extend_out* out) {
+    int rc = dedup_extend_args(ctx, pairs, u, v, out);
+    if (!rc) rc = comm_ready(ctx);
+    if (rc) return rc;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    rc = dedup_extend_run(ctx, pairs, u, v, extend_duplicates, out, true);
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}
+
+// One process, n GPUs (the reference's shape: one JVM, probe tasks fanned out to a pool, …Identification.java:836-846): pairs[k] /
+// outs[k] belong to ctxs[k]; one host thread per context runs hsq_dedup_extend_sharded.  The contexts get a communicator on first use.
+extern "C" int32_t hsq_dedup_extend_multi_gpu(hsq_ctx** ctxs, int32_t n, const hsq_pair_batch* pairs, int32_t u, int32_t v,
+                                              int32_t extend_duplicates, hsq_dedup_extend_out* outs) {
+    if (!ctxs || n < 1 || !pairs || !outs) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    for (int k = 0; k < n; k++) {
+        if (!ctxs[k]) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "null context");
+        int rc = dedup_extend_args(ctxs[k], &pairs[k], u, v, &outs[k]);  // argument errors before any collective starts
+        if (rc) return rc;
+    }
+    bool have = true;
+    for (int k = 0; k < n; k++) have = have && ctxs[k]->comm && ctxs[k]->comm_world == n && ctxs[k]->comm_rank == k;
+    if (!have) {
+        int rc = hsq_comm_init_all(ctxs, n);
+        if (rc) return rc;
+    }
+    std::vector<int> rcs((size_t)n, 0);
+    std::vector<std::thread> th;
+    for (int k = 0; k < n; k++)
+        th.emplace_back([&, k] { rcs[(size_t)k] = hsq_dedup_extend_sharded(ctxs[k], &pairs[k], u, v, extend_duplicates, &outs[k]); });
+    for (auto& t : th) t.join();
+    for (int k = 0; k < n; k++)
+        if (rcs[(size_t)k]) return rcs[(size_t)k];  // hsq_last_error(ctxs[k]) holds the message
+    return HSQ_OK;
 }
 
 // ExtendReadsToPrimer.extendReadsToPrimers on the pairs the caller flags (keep[k] != 0) -- e.g. the unique pairs of a dedup

@@ -75,6 +75,11 @@ struct hsq_ctx {
     // probe search windows sorted by (contig, strand, start) for hsq_assign_probes
     hsq::DevBuf rg_start, rg_end, rg_value, rg_off;
     hsq::DevBuf dd_seg;         // dedup segment path: per-probe counters, offsets
+    // in-library multi-GPU exchange (hsq_capi_comm.inl): NCCL communicator of this context, exchange buffers
+    void* comm = nullptr;
+    int comm_rank = 0, comm_world = 1;
+    hsq::DevBuf cm_send, cm_recv, cm_i32, cm_cnt, cm_tie, cm_probe;
+    int64_t* h_counts = nullptr;  // pinned: the world x (world + 1) count matrix
     hsq::DevBuf pool_tmp, pool_cursor, pool_dev;  // pooled CIGAR / MD delivery (hsq_extend_packed)
     hsq::DevBuf dd_u8, dd_i32;  // hsq_dedup_extend_batch: dedup answers kept while the extend stage reuses the output buffers
     int64_t rg_n = -1;

@@ -65,7 +65,14 @@ def dedup_sharded(backend, pairs, ext_uid_len, lig_uid_len, n_probes, group=None
     """Dedup of the union of every rank's `pairs`.  Returns (is_best, group_size) for this rank's pairs (numpy, in the
     order of `pairs`) and the owner's per-probe counters (meaningful for probes with owner_of(probe) == rank)."""
     world = dist.get_world_size(group)
-    keys = backend.keys(pairs, ext_uid_len, lig_uid_len, n_probes, 0)
+    rank = dist.get_rank(group)
+    # origin = the pair's place in the rank-major concatenation of all ranks' pairs: the last tie-break of the reduction, so the
+    # answer does not depend on the partition even when read indexes repeat
+    dev = backend.device if hasattr(backend, "device") else "cpu"
+    n_all = [torch.zeros(1, dtype=torch.int64, device=dev) for _ in range(world)]
+    dist.all_gather(n_all, torch.tensor([pairs.n], dtype=torch.int64, device=dev), group=group)
+    origin_base = int(sum(int(c.item()) for c in n_all[:rank]))
+    keys = backend.keys(pairs, ext_uid_len, lig_uid_len, n_probes, origin_base)
     n = keys.shape[0]
     dest = owner_of(_probe_column(keys).to(torch.int64), world)
     order = torch.argsort(dest, stable=True)
@@ -73,7 +80,6 @@ def dedup_sharded(backend, pairs, ext_uid_len, lig_uid_len, n_probes, group=None
     # counts first (world x world), then the payload
     all_counts = [torch.empty_like(send_counts) for _ in range(world)]
     dist.all_gather(all_counts, send_counts, group=group)
-    rank = dist.get_rank(group)
     recv_counts = [int(c[rank]) for c in all_counts]
     send_list = [int(c) for c in send_counts]
     recv_keys = _exchange(keys[order], send_list, recv_counts, group)

@@ -625,6 +625,35 @@ int32_t hsq_dedup_keys(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_ui
 int32_t hsq_dedup_reduce_keys(hsq_ctx* ctx, const hsq_dedup_key* d_keys, int64_t n, int32_t uid_len, uint8_t* d_is_best,
                               int32_t* d_group_size, hsq_probe_stats* stats);
 
+/* ---- multi-GPU behind the C ABI ------------------------------------------------------------------- */
+/* The reference fans its probe tasks out from one JVM (…Identification.java:836-846, task body :1172-1234); here the contexts of a
+ * job -- one per GPU, in one process or in one process per GPU -- share an NCCL communicator and the library does the exchange
+ * itself: key records bucketed by owner (probe mod world) on the device, counts by ncclAllGather, payload by ncclGroupStart +
+ * ncclSend / ncclRecv on device buffers, the owner's reduction, the answers back along the same routes.  Reads never move.  NCCL is
+ * loaded on first use (dlopen of libnccl.so.2); without it these calls return HSQ_ERR_UNSUPPORTED. */
+#define HSQ_COMM_ID_BYTES 128
+/* one process per GPU: rank 0 makes an id, the host program hands it to the other ranks, every rank joins */
+int32_t hsq_comm_unique_id(uint8_t* id_out /* [HSQ_COMM_ID_BYTES] */);
+int32_t hsq_comm_init_rank(hsq_ctx* ctx, const uint8_t* id /* [HSQ_COMM_ID_BYTES] */, int32_t rank, int32_t world);
+/* one process, n contexts on n different GPUs: ctxs[k] becomes rank k */
+int32_t hsq_comm_init_all(hsq_ctx** ctxs, int32_t n);
+int32_t hsq_comm_destroy(hsq_ctx* ctx);
+/* hsq_dedup_batch over the union of all ranks' pairs.  Collective: every rank calls it with its own pairs (possibly none).
+ * is_best / group_size answer this rank's pairs; stats hold the counters of the whole batch on every rank.  Exact ties of
+ * (quality sum, read index) go to the pair that comes first in the rank-major concatenation of the ranks' batches, so the answer
+ * does not depend on how the batch was split. */
+int32_t hsq_dedup_sharded(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len, uint8_t* is_best,
+                          int32_t* group_size, hsq_probe_stats* stats);
+/* hsq_dedup_extend_batch with the reduction over all ranks' pairs (collective); the extension runs on this rank's own pairs, the
+ * per-probe counters (stats, unable-to-extend) are those of the whole batch. */
+int32_t hsq_dedup_extend_sharded(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len,
+                                 int32_t extend_duplicates, hsq_dedup_extend_out* out);
+/* One call for one process that owns n GPUs: pairs[k] / outs[k] belong to ctxs[k]; a host thread per context runs
+ * hsq_dedup_extend_sharded; the communicator is created on first use (hsq_comm_init_all).  On failure the message is in
+ * hsq_last_error of the context that failed. */
+int32_t hsq_dedup_extend_multi_gpu(hsq_ctx** ctxs, int32_t n, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len,
+                                   int32_t extend_duplicates, hsq_dedup_extend_out* outs);
+
 /* ---- measurement helpers ------------------------------------------------------------------- */
 /* CUDA-event stopwatch on the context's stream (the stream every kernel of this library is launched on). */
 int32_t hsq_timer_start(hsq_ctx* ctx);

@@ -272,7 +272,9 @@ def dedup_reduce_keys(keys, n_probes):
     stats = ProbeStatsHost(n_probes)
     if n == 0:
         return is_best, gsize, stats
-    order = np.lexsort((keys["rank"], keys["uid"], keys["probe"]))
+    # last key: the record's origin (the pair's place in the whole batch) -- the single-process path breaks exact ties of
+    # (quality sum, read index) by the earlier pair, and with globally unique origins the sharded answer is the same
+    order = np.lexsort((keys["origin"], keys["rank"], keys["uid"], keys["probe"]))
     p, u = keys["probe"][order], keys["uid"][order]
     head = np.ones(n, dtype=bool)
     head[1:] = (p[1:] != p[:-1]) | (u[1:] != u[:-1])

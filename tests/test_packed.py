@@ -154,3 +154,32 @@ def test_extend_packed_edge_cases(ctx):
     exp = O.extend_batch(probes, pairs, cigar_cap=64, md_cap=96, nthreads=8)
     assert_pooled_equal(ctx.extend_packed(packed_pairs_of(pairs, 2)), exp)
     assert_pooled_equal(ctx.extend_packed(packed_pairs_of(pairs, 4)), exp)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("bits", [2, 4])
+def test_dedup_packed_equals_oracle(ctx, bits):
+    """hsq_dedup_packed (quality bytes on the device, and host-made quality sums) == FilterByUid restatement; a UID with an N is refused
+    like hsq_dedup_batch refuses it."""
+    from oracle import oracle as O
+    probes = synth.make_probes(50, seed=51)
+    raw = synth.make_pairs(probes, 20000, read_len=120, ext_uid_len=7, lig_uid_len=3, seed=52)
+    pairs, _ = synth.drop_n_pairs(raw)
+    pairs.q1.data[::3] = ord("#")
+    exp = O.dedup_batch(pairs, 7, 3, probes.n)
+    pp = packed_pairs_of(pairs, bits)
+    for variant in ("bytes", "sums"):
+        if variant == "sums":
+            pp = PackedPairsHost(pairs.probe_id, pp.r1, pp.r2, None, None, pairs.read_index, quality_sums(pairs.q1), quality_sums(pairs.q2))
+        b, g, st = ctx.dedup_packed(pp, 7, 3, probes.n)
+        assert np.array_equal(b, exp[0]) and np.array_equal(g, exp[1])
+        for f in ("unique_pairs", "duplicate_pairs", "max_pairs_per_uid"):
+            assert np.array_equal(getattr(st, f), getattr(exp[2], f))
+    # N inside a UID (first pair): refused, not grouped
+    r1 = pairs.r1.strings()
+    r1[0] = "N" + r1[0][1:]
+    from bioinformatics_b200.batches import PairBatchHost
+    bad = PairBatchHost(pairs.probe_id, r1, pairs.r2, pairs.q1, pairs.q2, pairs.read_index)
+    with pytest.raises(HsqError) as e:
+        ctx.dedup_packed(packed_pairs_of(bad, bits), 7, 3, probes.n)
+    assert e.value.status == A.HSQ_ERR_UNSUPPORTED

@@ -27,10 +27,14 @@ class OracleBackend:
         return torch.from_numpy(best), torch.from_numpy(gsize), stats
 
 
-def _workload():
+def _workload(ties=False):
     probes = synth.make_probes(37, seed=3)
     pairs, _ = synth.drop_n_pairs(synth.make_pairs(probes, 3000, read_len=80, ext_uid_len=5, lig_uid_len=2, seed=4))
     pairs.q1.data[::5] = ord("5")  # quality-sum ties -> read-index tie-break
+    if ties:  # repeated read indexes and equal qualities: exact ties, broken by the pair's place in the whole batch (origin)
+        pairs.read_index[:] = np.random.default_rng(1).integers(0, 40, size=pairs.n)
+        pairs.q1.data[:] = ord("I")
+        pairs.q2.data[:] = ord("I")
     return probes, pairs
 
 
@@ -39,10 +43,10 @@ def _worker(rank, world, port, partition, ret):
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        probes, pairs = _workload()
+        probes, pairs = _workload(ties=partition == "ties")
         if partition == "interleaved":
             mine = np.arange(rank, pairs.n, world)
-        elif partition == "blocks":
+        elif partition in ("blocks", "ties"):  # rank-major concatenation = the original order, so origins equal pair indexes
             mine = np.array_split(np.arange(pairs.n), world)[rank]
         else:  # everything on rank 0: the other rank sends nothing and still owns probes
             mine = np.arange(pairs.n) if rank == 0 else np.arange(0)
@@ -54,7 +58,7 @@ def _worker(rank, world, port, partition, ret):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("partition", ["interleaved", "blocks", "one_rank"])
+@pytest.mark.parametrize("partition", ["interleaved", "blocks", "one_rank", "ties"])
 def test_sharded_dedup_matches_single_process(partition):
     world = 2
     with socket.socket() as s:
@@ -62,7 +66,7 @@ def test_sharded_dedup_matches_single_process(partition):
         port = s.getsockname()[1]
     ret = mp.Manager().dict()
     mp.spawn(_worker, args=(world, port, partition, ret), nprocs=world, join=True)
-    probes, pairs = _workload()
+    probes, pairs = _workload(ties=partition == "ties")
     eb, egs, est = O.dedup_batch(pairs, 5, 2, probes.n)
     got_b = np.zeros(pairs.n, dtype=np.uint8)
     got_g = np.zeros(pairs.n, dtype=np.int32)
