@@ -109,6 +109,10 @@ def _worker(rank, world, port, kind, mark, ret):
             res = ctx.dedup_extend_sharded(pairs.subset(mine), U, V, extend_duplicates=mark, cigar_cap=64, md_cap=96)
             b, g, st = ctx.dedup_sharded(pairs.subset(mine), U, V)
             assert np.array_equal(b, res.is_best) and np.array_equal(g, res.group_size)
+        for o in (res, res.extend, res.stats):  # ctypes mirrors do not pickle
+            for a in ("_c", "_stats_c", "_ext_c"):
+                if hasattr(o, a):
+                    setattr(o, a, None)
         ret[rank] = res
     finally:
         dist.destroy_process_group()
