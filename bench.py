@@ -41,7 +41,12 @@ def parse():
     ap.add_argument("--pairs", type=int, default=5_000_000, help="read pairs per GPU (10 M read ends)")
     ap.add_argument("--cpu-sample-pairs", type=int, default=0, help="0 = size the CPU sample for ~15 s")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--stage-pairs", type=int, default=1_000_000, help="pairs per GPU of the trim/dedup side measurements")
+    ap.add_argument("--stage-base-pairs", type=int, default=1_250_000, help="generated base batch of the stage shapes (tiled up to c3 / c4 size)")
+    ap.add_argument("--c3-pairs", type=int, default=10_000_000, help="configs[2]: pairs of the dedup shape (N = 1)")
+    ap.add_argument("--c4-pairs", type=int, default=12_500_000, help="configs[3]: pairs per GPU of the whole-exome shape")
+    ap.add_argument("--stage-cpu-pairs", type=int, default=500_000, help="pairs of the CPU-port sample of the stages")
+    ap.add_argument("--no-c3", action="store_true")
+    ap.add_argument("--no-c4", action="store_true")
     ap.add_argument("--no-stages", action="store_true", help="skip the trim/dedup side measurements")
     return ap.parse_args()
 
@@ -119,11 +124,14 @@ class ClockSampler:
         return out
 
 
-def make_workload(n_pairs, rank):
+def make_workload(n_pairs, rank, alloc=None, base_pairs=1_250_000):
+    """configs[1]'s batch.  Generation costs ~10 s per million pairs, so batches above base_pairs are tiles of one generated base with
+    the first two UID bases rotated per tile (synth.tile_pairs): same probes, same noise model, different molecules."""
     from bioinformatics_b200 import synth
     probes = synth.make_probes(N_PROBES)
-    pairs = synth.make_pairs(probes, n_pairs, read_len=READ_LEN, ext_uid_len=UID, seed=synth.SEED_READS + rank,
-                             with_quals=False)
+    tiles = max(1, min(16, -(-n_pairs // base_pairs)))
+    base = synth.make_pairs(probes, -(-n_pairs // tiles), read_len=READ_LEN, ext_uid_len=UID, seed=synth.SEED_READS + rank, with_quals=False)
+    pairs = synth.tile_pairs(base, tiles, alloc) if (tiles > 1 or alloc) else base
     return probes, pairs
 
 
@@ -150,114 +158,274 @@ def cpu_baseline(probes, pairs, sample_pairs, threads, keep=None):
             "pairs_per_s": sample_pairs / dt}, dt, r.cells
 
 
-def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
-    """Side measurements of the HBM-bound stages (trim A8, dedup A6/A7), outside the headline's timed region:
-    read-pairs/s through the C ABI with host buffers, on a 1 M pair batch per GPU (2 x 150 bp with qualities).
-    At N > 1 dedup runs sharded: key records -> NCCL all-to-all by probe owner -> reduce -> all-to-all back."""
-    import torch
-    from bioinformatics_b200 import synth, sharded
-    n = args.stage_pairs
-    probes = synth.make_probes(N_PROBES)
-    pairs, _ = synth.drop_n_pairs(synth.make_pairs(probes, n, read_len=READ_LEN, ext_uid_len=UID, seed=synth.SEED_READS + 100 + rank))
-    pairs.read_index = (pairs.read_index.astype(np.int64) + rank * n).astype(np.int32)  # FASTQ ordinals are global
-    def pin(arr):
-        q = ctx.pinned_array(arr.nbytes).view(arr.dtype)
-        q[:] = arr.reshape(-1)
-        return q
-    for sb in (pairs.r1, pairs.r2, pairs.q1, pairs.q2):
-        sb.data = pin(sb.data)
-        sb.offsets = pin(sb.offsets)
-    pairs.probe_id = pin(pairs.probe_id)
-    pairs.read_index = pin(pairs.read_index)
-    trim_out = (ctx.pinned_array(pairs.r1.data.nbytes), ctx.pinned_array(pairs.r1.data.nbytes),
-                ctx.pinned_array(8 * (pairs.n + 1)).view(np.int64))
-    out = {"pairs_per_gpu": int(pairs.n), "hbm_peak_gbs": None, "host_buffers": "pinned"}
-    # trim: both mates, fixed offsets as HSQUtils trim derives them (UID + primer at 5', 3' clip)
-    first, last = UID + 22, READ_LEN - 23
-    for _ in range(2):
-        ctx.trim_batch(pairs.r1, pairs.q1, first, last, True, out=trim_out)
-    barrier()
-    t0 = time.perf_counter()
-    ms_dev = 0.0
-    for sb, qb in ((pairs.r1, pairs.q1), (pairs.r2, pairs.q2)):
-        ctx.trim_batch(sb, qb, first, last, True, out=trim_out)
-        ms_dev += ctx.last_timing()[0]
-    barrier()
-    dt = max_over_ranks(time.perf_counter() - t0)
-    out["trim"] = {"read_pairs_per_s": pairs.n * world / dt, "ms_host_to_host": dt * 1e3, "ms_device_incl_copies": ms_dev,
-                   "algorithmic_bytes_per_pair": 8 * READ_LEN}
-    # dedup
-    if world == 1:
-        for _ in range(2):
-            ctx.dedup_batch(pairs, UID, 0, probes.n)
-        barrier()
-        t0 = time.perf_counter()
-        best, gs, st = ctx.dedup_batch(pairs, UID, 0, probes.n)
-        ms_dev = ctx.last_timing()[0]
-        barrier()
-        dt = time.perf_counter() - t0
-        uniq = int(best.sum())
-        mode = "hsq_dedup_batch, one GPU"
-    else:
-        be = sharded.DeviceBackend(ctx)
-        for _ in range(2):
-            sharded.dedup_sharded(be, pairs, UID, 0, probes.n)
-        barrier()
-        t0 = time.perf_counter()
-        best, gs, st = sharded.dedup_sharded(be, pairs, UID, 0, probes.n)
-        barrier()
-        dt = max_over_ranks(time.perf_counter() - t0)
-        ms_dev = None
-        t = torch.tensor([float(best.sum())], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t)
-        uniq = int(t.item())
-        mode = "sharded: hsq_dedup_keys -> NCCL all_to_all by probe owner -> hsq_dedup_reduce_keys -> all_to_all back"
-    out["dedup"] = {"read_pairs_per_s": pairs.n * world / dt, "ms_host_to_host": dt * 1e3, "ms_device_incl_copies": ms_dev,
-                    "unique_pairs": uniq, "mode": mode, "algorithmic_bytes_per_pair": 2 * READ_LEN + 16 + 24 + 48 + 25}
-    # dedup + extend: one probe task body per batch (unique pairs only, and with the duplicates as --markDuplicates does)
-    from bioinformatics_b200.batches import DedupExtendResult, ExtendResult
-    ctx.set_probes(probes)
-    res = DedupExtendResult(pairs.n, probes.n, CIGAR_CAP, MD_CAP)
-    for f in ExtendResult.FIELDS_I32 + ("ok", "overflow", "pair_ok", "cigar", "md"):
-        setattr(res.extend, f, pin(getattr(res.extend, f)))
-    for f in ("is_best", "group_size", "extended_pair"):
-        setattr(res, f, pin(getattr(res, f)))
-    for mark in (False, True):
-        if world == 1:
-            def task():
-                r = ctx.dedup_extend_batch(pairs, UID, 0, extend_duplicates=mark, cigar_cap=CIGAR_CAP, md_cap=MD_CAP, out=res)
-                return r.n_extended, int(r.extend.pair_ok[:r.n_extended].sum())
-            mode = "hsq_dedup_extend_batch, one GPU: reads uploaded once, unique pairs compacted on the device"
-        else:
-            def task():
-                b, _, _ = sharded.dedup_sharded(be, pairs, UID, 0, probes.n)
-                if mark:
-                    r = ctx.extend_batch(pairs, CIGAR_CAP, MD_CAP, out=res.extend)
-                    return pairs.n, int(r.pair_ok.sum())
-                m, _, r = ctx.extend_selected(pairs, b, CIGAR_CAP, MD_CAP, out=res.extend, extended_pair=res.extended_pair)
-                return m, int(r.pair_ok[:m].sum())
-            mode = "sharded dedup over NCCL, then hsq_extend_selected (hsq_extend_batch with duplicates) on each rank's own pairs"
-        task()
-        barrier()
-        t0 = time.perf_counter()
-        n_ext, n_ok = task()
-        barrier()
-        dt = max_over_ranks(time.perf_counter() - t0)
-        out["dedup_extend_mark_duplicates" if mark else "dedup_extend"] = {
-            "read_pairs_per_s": pairs.n * world / dt, "ms_host_to_host": dt * 1e3, "pairs_extended_rank0": int(n_ext),
-            "pairs_extended_ok_rank0": n_ok, "mode": mode}
-    # BASELINE.json's "read-pairs/sec trim+dedup": both commands back to back on the same pairs (trim of both mates, then the probe task)
-    for key in ("dedup_extend", "dedup_extend_mark_duplicates"):
-        ms = out["trim"]["ms_host_to_host"] + out[key]["ms_host_to_host"]
-        out["trim_plus_" + key] = {"read_pairs_per_s": pairs.n * world / (ms * 1e-3), "ms_host_to_host": ms,
-                                   "note": "sum of the two host-to-host calls above; the mapper that runs between them in a real run is not part of this path"}
-    if world == 1:
-        out.update(next_row_numbers(ctx, probes, pairs, res))
+HBM_BYTES = {  # algorithmic bytes per pair of the HBM-bound stage kernels (L = read length)
+    "trim": lambda L: 8 * L,                 # 4L read (2 mates x bases + qualities) + <= 4L written
+    "keygen": lambda L: 2 * L + 16 + 24,     # 2L qualities + UID bases read, one 24 B key record written
+    "group": lambda L: 48 + 25,              # sort/group: 2 x 24 B per record moved once; reduce: 24 B read + 1 B written
+}
+
+
+def _hbm_peak():
     try:
-        out["hbm_peak_gbs"] = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"], "MEASURED_PEAKS.json hbm_gbs (burst, torch copy)"
     except Exception:
-        pass
+        return 6554.9, "B200_PROFILING.md fallback (no MEASURED_PEAKS.json on this box)"
+
+
+def _frac(bytes_per_pair, n, ms, peak_gbs):
+    if not ms or ms <= 0:
+        return None
+    return bytes_per_pair * n / (ms * 1e-3) / 1e9 / peak_gbs
+
+
+def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
+    """BASELINE.json's metric leads with "read-pairs/sec trim+dedup": this leg measures that path at the shapes the metric is quoted
+    on, through the C ABI with pinned host buffers, outside the headline's timed region.
+      c3 (N = 1): `HSQUtils dedup` shape, 10 M pairs, 14 bp UID, 10 k probes: hsq_dedup_batch / hsq_dedup_packed / hsq_dedup_extend_batch.
+      c4 (every N): whole-exome shape, 12.5 M pairs per GPU on a 200 k-probe panel: trim -> dedup (sharded inside the library over
+        NCCL at N > 1: hsq_dedup_sharded / hsq_dedup_extend_sharded) -> extension of the unique pairs (all pairs with --markDuplicates).
+    Each stage: read pairs/s host to host, kernel-only CUDA-event spans with their fraction of the HBM roofline (hsq_last_spans), the
+    CPU port timed on a bounded sample at N = 1, and at N > 1 the sharded answer checked against the oracle on a gathered sample."""
+    import torch
+    from bioinformatics_b200 import synth
+    from bioinformatics_b200._lib import pack_reads, quality_sums
+    from bioinformatics_b200.batches import DedupExtendResult, ExtendResult, PackedPairsHost
+    hbm, hbm_src = _hbm_peak()
+    out = {"hbm_peak_gbs": hbm, "hbm_peak_source": hbm_src, "host_buffers": "pinned"}
+    base_n = max(1000, args.stage_base_pairs)
+
+    def pinned_result(n, n_probes):
+        res = DedupExtendResult(n, n_probes, CIGAR_CAP, MD_CAP)
+        for f in ExtendResult.FIELDS_I32 + ("ok", "overflow", "pair_ok", "cigar", "md"):
+            a = getattr(res.extend, f)
+            setattr(res.extend, f, ctx.pinned_array(a.nbytes).view(a.dtype))
+        for f in ("is_best", "group_size", "extended_pair"):
+            a = getattr(res, f)
+            setattr(res, f, ctx.pinned_array(a.nbytes).view(a.dtype))
+        return res
+
+    def timed(fn, sync_ranks=True):
+        """One warm-up call, one timed call; host-to-host seconds (max over ranks when the call is collective)."""
+        fn()
+        barrier()
+        t0 = time.perf_counter()
+        r = fn()
+        dt = time.perf_counter() - t0
+        if sync_ranks:
+            barrier()
+            dt = max_over_ranks(dt)
+        return dt, r
+
+    def dedup_entry(n, dt, spans, extra=None):
+        e = {"read_pairs_per_s": n * world / dt, "ms_host_to_host": dt * 1e3, "keygen_kernel_ms": spans[0], "group_kernels_ms": spans[1],
+             "keygen_hbm_frac": _frac(HBM_BYTES["keygen"](READ_LEN), n, spans[0], hbm), "group_hbm_frac": _frac(HBM_BYTES["group"](READ_LEN), n, spans[1], hbm),
+             "algorithmic_bytes_per_pair": {"keygen": HBM_BYTES["keygen"](READ_LEN), "group": HBM_BYTES["group"](READ_LEN)}}
+        e.update(extra or {})
+        return e
+
+    # ---------------- c3: HSQUtils dedup, 10 M pairs, 14 bp UID, 10 k probes (one GPU) ----------------
+    if world == 1 and not args.no_c3:
+        U3, NP3 = 14, 10000
+        probes3 = synth.make_probes(NP3)
+        base3, _ = synth.drop_n_pairs(synth.make_pairs(probes3, base_n, read_len=READ_LEN, ext_uid_len=U3, seed=synth.SEED_READS + 300))
+        tiles = max(1, min(16, round(args.c3_pairs / base3.n)))
+        pairs3 = synth.tile_pairs(base3, tiles, ctx.pinned_array)
+        n3 = pairs3.n
+        c3 = {"workload": "configs[2]: %d read pairs (%d tiles of a %d-pair base, N pairs dropped), 2x%dbp, %dbp UID, %d probes" %
+                          (n3, tiles, base3.n, READ_LEN, U3, NP3), "pairs": int(n3)}
+        dt, (best, gs, st) = timed(lambda: ctx.dedup_batch(pairs3, U3, 0, NP3))
+        c3["dedup"] = dedup_entry(n3, dt, ctx.last_spans(), {"api": "hsq_dedup_batch (ASCII reads + qualities: %d B/pair over PCIe)" % (4 * READ_LEN + 24),
+                                                              "unique_pairs": int(best.sum())})
+        pk = PackedPairsHost(pairs3.probe_id, pack_reads(pairs3.r1, 2, ctx.pinned_array), pack_reads(pairs3.r2, 2, ctx.pinned_array),
+                             pairs3.q1.data, pairs3.q2.data, pairs3.read_index)
+        dt, (b2, g2, _) = timed(lambda: ctx.dedup_packed(pk, U3, 0, NP3))
+        same_packed = bool(np.array_equal(b2, best) and np.array_equal(g2, gs))
+        c3["dedup_packed"] = dedup_entry(n3, dt, ctx.last_spans(), {"api": "hsq_dedup_packed (reads 2 bit/base + quality bytes: ~%d B/pair over PCIe)" %
+                                                                            (2 * READ_LEN + 2 * 40 + 16), "equals_hsq_dedup_batch": same_packed})
+        t0 = time.perf_counter()
+        qs1, qs2 = quality_sums(pairs3.q1), quality_sums(pairs3.q2)
+        qs_s = time.perf_counter() - t0
+        pks = PackedPairsHost(pairs3.probe_id, pk.r1, pk.r2, None, None, pairs3.read_index, qs1, qs2)
+        dt, (b3, g3, _) = timed(lambda: ctx.dedup_packed(pks, U3, 0, NP3))
+        c3["dedup_packed_host_quality_sums"] = dedup_entry(n3, dt, ctx.last_spans(), {
+            "api": "hsq_dedup_packed with hsq_quality_sums made on the host (opt-in: 2 B per read instead of the quality string, ~%d B/pair over PCIe)" % (2 * 40 + 20),
+            "equals_hsq_dedup_batch": bool(np.array_equal(b3, best) and np.array_equal(g3, gs)), "host_quality_sums_s": qs_s})
+        ctx.set_probes(probes3)
+        res3 = pinned_result(n3, NP3)
+        for mark in (False, True):
+            dt, r = timed(lambda: ctx.dedup_extend_batch(pairs3, U3, 0, extend_duplicates=mark, cigar_cap=CIGAR_CAP, md_cap=MD_CAP, out=res3))
+            sp = ctx.last_spans()
+            c3["dedup_extend_mark_duplicates" if mark else "dedup_extend"] = {
+                "read_pairs_per_s": n3 / dt, "ms_host_to_host": dt * 1e3, "pairs_extended": int(r.n_extended),
+                "pairs_extended_ok": int(r.extend.pair_ok[:r.n_extended].sum()), "keygen_kernel_ms": sp[0], "group_kernels_ms": sp[1],
+                "compaction_kernels_ms": sp[2], "extend_kernels_ms": sp[3], "gcups_extend_kernels": r.extend.cells / (sp[3] * 1e-3) / 1e9 if sp[3] else None,
+                "api": "hsq_dedup_extend_batch"}
+        same_fused = bool(np.array_equal(res3.is_best, best) and int(best.sum()) == int(st.unique_pairs.sum()))
+        # CPU port on a bounded sample + GPU == oracle on that sample
+        from oracle import oracle as O
+        O.build()
+        sample = base3.head(min(base3.n, args.stage_cpu_pairs))
+        t0 = time.perf_counter()
+        eb, egs, est = O.dedup_batch(sample, U3, 0, NP3)
+        cpu_dedup = time.perf_counter() - t0
+        uniq = sample.subset(np.nonzero(eb)[0])
+        threads = os.cpu_count() or 1
+        t0 = time.perf_counter()
+        eext = O.extend_batch(probes3, uniq.head(min(uniq.n, 60000)), nthreads=threads)
+        cpu_ext = (time.perf_counter() - t0) * uniq.n / max(1, min(uniq.n, 60000))
+        gb, gg, gst = ctx.dedup_batch(sample, U3, 0, NP3)
+        c3["cpu_port"] = {"dedup_read_pairs_per_s": sample.n / cpu_dedup, "dedup_extend_read_pairs_per_s": sample.n / (cpu_dedup + cpu_ext),
+                          "cores": {"dedup": 1, "extend": threads}, "kind": "port",
+                          "sample": "%d pairs of the base batch: FilterByUid restatement on 1 thread (%.1f s); extension of its unique pairs timed on %d of "
+                                    "them with %d threads and scaled" % (sample.n, cpu_dedup, min(uniq.n, 60000), threads)}
+        c3["parity"] = {"gpu_equals_cpu_oracle_on_sample": bool(np.array_equal(gb, eb) and np.array_equal(gg, egs) and
+                                                                 np.array_equal(gst.unique_pairs, est.unique_pairs) and np.array_equal(gst.duplicate_pairs, est.duplicate_pairs)),
+                        "packed_equals_ascii_at_full_size": same_packed, "fused_call_equals_dedup_at_full_size": same_fused,
+                        "unique_equals_sum_of_probe_counters": bool(int(best.sum()) == int(st.unique_pairs.sum())),
+                        "tiles_have_equal_unique_counts": bool(len(set(best.reshape(tiles, -1).sum(axis=1).tolist())) == 1)}
+        assert all(c3["parity"].values()), "c3 parity failed: %s" % c3["parity"]
+        out["c3"] = c3
+        out["_c3_state"] = (probes3, base3, res3)
+        del pairs3, pk, pks
+
+    # ---------------- c4: 12.5 M pairs per GPU on the 200 k-probe panel: trim -> dedup -> extend ----------------
+    if not args.no_c4:
+        U4, NP4 = UID, 200000
+        probes4 = synth.make_probes(NP4)
+        base4, _ = synth.drop_n_pairs(synth.make_pairs(probes4, base_n, read_len=READ_LEN, ext_uid_len=U4, seed=synth.SEED_READS + 400 + rank))
+        tiles = max(1, min(16, round(args.c4_pairs / base4.n)))
+        pairs4 = synth.tile_pairs(base4, tiles, ctx.pinned_array)
+        pairs4.read_index = (pairs4.read_index.astype(np.int64) % (1 << 27) + rank * (1 << 27)).astype(np.int32)  # FASTQ ordinals are global
+        ri = ctx.pinned_array(pairs4.read_index.nbytes).view(np.int32)
+        ri[:] = pairs4.read_index
+        pairs4.read_index = ri
+        n4 = pairs4.n
+        c4 = {"workload": "configs[3] per GPU: %d read pairs (%d tiles of a %d-pair base), 2x%dbp, %dbp UID, %d probes; %d GPUs = %d pairs" %
+                          (n4, tiles, base4.n, READ_LEN, U4, NP4, world, n4 * world), "pairs_per_gpu": int(n4)}
+        ctx.set_probes(probes4)
+        if world > 1:
+            ctx.comm_init_torch()
+        # trim: both mates of the first tiles (its rate does not depend on the batch beyond ~1 M reads), offsets as HSQUtils trim derives them
+        nt = min(n4, 2 * base4.n)
+        head = pairs4.head(nt)
+        first, last = U4 + 22, READ_LEN - 23
+        trim_out = (ctx.pinned_array(head.r1.data.nbytes), ctx.pinned_array(head.r1.data.nbytes), ctx.pinned_array(8 * (nt + 1)).view(np.int64))
+        spans = []
+
+        def trim_both():
+            spans.clear()
+            for sb, qb in ((head.r1, head.q1), (head.r2, head.q2)):
+                ctx.trim_batch(sb, qb, first, last, True, out=trim_out)
+                spans.append(ctx.last_spans()[0])
+        dt, _ = timed(trim_both)
+        k_ms = sum(spans)
+        c4["trim"] = {"read_pairs_per_s": nt * world / dt, "ms_host_to_host": dt * 1e3, "pairs": int(nt), "kernel_ms": k_ms,
+                      "hbm_frac": _frac(HBM_BYTES["trim"](READ_LEN), nt, k_ms, hbm), "algorithmic_bytes_per_pair": HBM_BYTES["trim"](READ_LEN),
+                      "api": "hsq_trim_batch on both mates"}
+        trim_ms_per_pair = dt * 1e3 / nt
+        # dedup alone
+        if world == 1:
+            dt, (best, gs, st) = timed(lambda: ctx.dedup_batch(pairs4, U4, 0, NP4))
+            mode = "hsq_dedup_batch"
+        else:
+            dt, (best, gs, st) = timed(lambda: ctx.dedup_sharded(pairs4, U4, 0, NP4))
+            mode = "hsq_dedup_sharded: key records bucketed by owner on the device, ncclAllGather of counts, ncclSend/ncclRecv all-to-all, owner reduces, answers back"
+        c4["dedup"] = dedup_entry(n4, dt, ctx.last_spans(), {"api": mode, "unique_pairs_this_rank": int(best.sum()),
+                                                              "unique_pairs_all_ranks": int(st.unique_pairs.sum())})
+        res4 = pinned_result(n4, NP4)
+        for mark in (False, True):
+            if world == 1:
+                fn = lambda: ctx.dedup_extend_batch(pairs4, U4, 0, extend_duplicates=mark, cigar_cap=CIGAR_CAP, md_cap=MD_CAP, out=res4)
+                mode = "hsq_dedup_extend_batch"
+            else:
+                fn = lambda: ctx.dedup_extend_sharded(pairs4, U4, 0, extend_duplicates=mark, cigar_cap=CIGAR_CAP, md_cap=MD_CAP, out=res4)
+                mode = "hsq_dedup_extend_sharded (exchange inside the library over NCCL), extension on each rank's own pairs"
+            dt, r = timed(fn)
+            sp = ctx.last_spans()
+            key = "dedup_extend_mark_duplicates" if mark else "dedup_extend"
+            c4[key] = {"read_pairs_per_s": n4 * world / dt, "ms_host_to_host": dt * 1e3, "pairs_extended_this_rank": int(r.n_extended),
+                       "pairs_extended_ok_this_rank": int(r.extend.pair_ok[:r.n_extended].sum()), "keygen_kernel_ms": sp[0], "group_or_exchange_ms": sp[1],
+                       "compaction_kernels_ms": sp[2], "extend_kernels_ms": sp[3], "api": mode}
+            ms = trim_ms_per_pair * n4 + dt * 1e3
+            c4["trim_plus_" + key] = {"read_pairs_per_s": n4 * world / (ms * 1e-3), "ms_host_to_host": ms,
+                                      "note": "the two HSQUtils commands back to back: trim of both mates (rate of the trim entry above applied to the whole "
+                                              "batch) + the probe task; the mapper that runs between them in a real run is not part of this path"}
+        c4["parity"] = {"fused_flags_equal_dedup": bool(np.array_equal(res4.is_best, best)),
+                        "unique_equals_sum_of_probe_counters": bool(_sum_ranks(dist, int(best.sum())) == int(st.unique_pairs.sum()))}
+        # the sharded answer against the oracle on a sample gathered to rank 0
+        if world > 1:
+            S = max(1, 1_000_000 // world)
+            smp = pairs4.head(S)
+            sb_, sg_, _ = ctx.dedup_sharded(smp, U4, 0, NP4)
+
+            def gather(a):
+                t = torch.from_numpy(np.ascontiguousarray(a)).cuda()
+                parts = [torch.empty_like(t) for _ in range(world)]
+                dist.all_gather(parts, t)
+                return np.concatenate([x.cpu().numpy() for x in parts])
+            cols = [gather(x) for x in (smp.probe_id, smp.read_index, smp.r1.data[:S * READ_LEN], smp.r2.data[:S * READ_LEN],
+                                        smp.q1.data[:S * READ_LEN], smp.q2.data[:S * READ_LEN], sb_, sg_)]
+            if rank == 0:
+                from oracle import oracle as O
+                from bioinformatics_b200 import _abi as A
+                from bioinformatics_b200.batches import PairBatchHost
+                O.build()
+                fx = lambda a: A.SeqBatch.from_fixed(a.reshape(-1, READ_LEN))
+                union = PairBatchHost(cols[0], fx(cols[2]), fx(cols[3]), fx(cols[4]), fx(cols[5]), cols[1])
+                eb, egs, _ = O.dedup_batch(union, U4, 0, NP4)
+                c4["parity"]["sharded_dedup_equals_oracle"] = bool(np.array_equal(cols[6], eb) and np.array_equal(cols[7], egs))
+                c4["parity"]["sharded_sample"] = "%d pairs per rank x %d ranks gathered to rank 0, FilterByUid restatement on the union" % (S, world)
+        else:
+            from oracle import oracle as O
+            O.build()
+            threads = os.cpu_count() or 1
+            sample = base4.head(min(base4.n, args.stage_cpu_pairs))
+            t0 = time.perf_counter()
+            O.trim_batch(sample.r1, sample.q1, first, last, True)
+            O.trim_batch(sample.r2, sample.q2, first, last, True)
+            cpu_trim = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            eb, egs, est = O.dedup_batch(sample, U4, 0, NP4)
+            cpu_dedup = time.perf_counter() - t0
+            uniq = sample.subset(np.nonzero(eb)[0])
+            m = min(uniq.n, 60000)
+            t0 = time.perf_counter()
+            O.extend_batch(probes4, uniq.head(m), nthreads=threads)
+            cpu_ext = (time.perf_counter() - t0) * uniq.n / max(1, m)
+            gb, gg, gst = ctx.dedup_batch(sample, U4, 0, NP4)
+            c4["cpu_port"] = {"trim_read_pairs_per_s": sample.n / cpu_trim, "dedup_read_pairs_per_s": sample.n / cpu_dedup,
+                              "dedup_extend_read_pairs_per_s": sample.n / (cpu_dedup + cpu_ext),
+                              "trim_plus_dedup_extend_read_pairs_per_s": sample.n / (cpu_trim + cpu_dedup + cpu_ext),
+                              "cores": {"trim": 1, "dedup": 1, "extend": threads}, "kind": "port",
+                              "sample": "%d pairs of the base batch; trim and FilterByUid restatements on 1 thread (%.2f s, %.2f s); extension of the unique "
+                                        "pairs timed on %d of them with %d threads and scaled" % (sample.n, cpu_trim, cpu_dedup, m, threads)}
+            c4["parity"]["gpu_equals_cpu_oracle_on_sample"] = bool(np.array_equal(gb, eb) and np.array_equal(gg, egs) and
+                                                                   np.array_equal(gst.unique_pairs, est.unique_pairs))
+        if rank == 0:
+            assert all(v for v in c4["parity"].values() if isinstance(v, bool)), "c4 parity failed: %s" % c4["parity"]
+        out["c4"] = c4
+        del pairs4, res4
+    if world == 1 and "_c3_state" in out:
+        probes3, base3, res3 = out.pop("_c3_state")
+        ctx.set_probes(probes3)
+        sub = base3.head(min(base3.n, 1_000_000))
+        for sb in (sub.r1, sub.r2, sub.q1, sub.q2):
+            d = ctx.pinned_array(sb.data.nbytes)
+            d[:] = sb.data
+            sb.data = d
+        res = ctx.dedup_extend_batch(sub, 14, 0, extend_duplicates=True, cigar_cap=CIGAR_CAP, md_cap=MD_CAP)
+        out.update(next_row_numbers(ctx, probes3, sub, res))
+    out.pop("_c3_state", None)
     return out
+
+
+def _sum_ranks(dist, x):
+    if dist is None:
+        return x
+    import torch
+    t = torch.tensor([float(x)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(t)
+    return int(t.item())
 
 
 def next_row_numbers(ctx, probes, pairs, res):
@@ -282,7 +450,7 @@ def next_row_numbers(ctx, probes, pairs, res):
     ranges, records = synth.make_mapped_records(probes, pairs, seed=9)
     ctx.set_probe_ranges(ranges)
     dt, a = timed(lambda: ctx.assign_probes(records, 4))
-    sub = 200000
+    sub = min(200000, records.n - 1)
     from bioinformatics_b200.batches import MappedRecordsHost
     ao = records.alt_offsets
     head = MappedRecordsHost(records.contig[:sub], records.negative_strand[:sub], records.second_of_pair[:sub], records.start[:sub],
@@ -316,10 +484,11 @@ def next_row_numbers(ctx, probes, pairs, res):
                              "record_bytes": int(rec.offsets[-1]), "cpu_port_read_pairs_per_s": sub / dt_cpu,
                              "cpu_sample": "%d pairs, 1 thread; the port re-runs the extension to get the record fields" % sub}
     # f3: the primers of the panel as sequences to find, read one of every pair as the FASTQ entries
-    seqs = A.SeqBatch.from_strings(probes.ext.strings() + probes.lig.strings())
+    n_find = min(probes.n, 1000)  # 2000 sequences to find, as in round 1
+    seqs = A.SeqBatch.from_strings(probes.ext.strings()[:n_find] + probes.lig.strings()[:n_find])
     ctx.set_find_sequences(seqs, 5, 15000)
     dt, c = timed(lambda: ctx.find_candidates(pairs.r1, pairs.q1, 20, 20, max_candidates=16))
-    sub = 4000
+    sub = min(4000, pairs.n)
     t0 = time.perf_counter()
     O.find_candidates(seqs, A.SeqBatch(pairs.r1.data, pairs.r1.offsets[:sub + 1]), A.SeqBatch(pairs.q1.data, pairs.q1.offsets[:sub + 1]),
                       leading_quality=20, trailing_quality=20, max_candidates=16)
@@ -327,12 +496,12 @@ def next_row_numbers(ctx, probes, pairs, res):
     out["find_candidates"] = {"reads_per_s": pairs.n / dt, "ms_host_to_host": dt * 1e3, "reads": int(pairs.n), "sequences_to_find": int(seqs.n),
                               "candidates": int(c.n_candidates.sum()), "overflowed_reads": int(c.overflow.sum()),
                               "cpu_port_reads_per_s": sub / dt_cpu, "cpu_sample": "%d reads, 1 thread" % sub}
-    sub = 250000
+    sub = min(250000, pairs.n)
     rs, qs = A.SeqBatch(pairs.r1.data, pairs.r1.offsets[:sub + 1]), A.SeqBatch(pairs.q1.data, pairs.q1.offsets[:sub + 1])
     limits = (2, 1, 1, 1, 1)
     dt, f = timed(lambda: ctx.find_matches(rs, qs, 20, 20, limits, max_candidates=64), reps=1)
     ms_dev = ctx.last_timing()[0]
-    sub_cpu = 1500
+    sub_cpu = min(1500, sub)
     rc_, qc_ = A.SeqBatch(pairs.r1.data, pairs.r1.offsets[:sub_cpu + 1]), A.SeqBatch(pairs.q1.data, pairs.q1.offsets[:sub_cpu + 1])
 
     class _Port:  # the same decision over the CPU port: candidates, then one alignment per candidate
@@ -354,7 +523,7 @@ def next_row_numbers(ctx, probes, pairs, res):
                            "note": "hsq_find_matches: candidates + one alignment per candidate + the five limits in one call; slot arrays "
                                    "(64 per read) returned to pageable host memory"}
     # f2: FASTQ / SAM text -> record indexes -> the FASTQ <-> SAM name join (first dedup configuration), pageable host buffers
-    n_ing = 250000
+    n_ing = 250000 if pairs.n >= 250000 else 20000
     case = synth.make_ingest_case(n_ing, read_len=150, seed=31)
     sam_text = synth.sam_text_of(case, seed=32)
     from bioinformatics_b200.batches import NameJoinHost
@@ -422,13 +591,13 @@ def next_row_numbers(ctx, probes, pairs, res):
                          "equals_cpu_port": bool(same)}
     # f4 output side: order of the final coordinate sort for the records of the extended pairs (names = read indexes as strings)
     rng = np.random.default_rng(5)
-    n_out = 1000000
+    n_out = 1000000 if pairs.n >= 250000 else 50000
     cols = (rng.integers(0, 22, size=n_out), rng.integers(1, 10 ** 8, size=n_out), rng.choice([99, 147, 83, 163], size=n_out), np.full(n_out, 60),
             rng.integers(0, 22, size=n_out), rng.integers(1, 10 ** 8, size=n_out), rng.integers(-400, 400, size=n_out))
     names = A.SeqBatch.from_strings(["%d" % k for k in rng.integers(0, 10 ** 7, size=n_out).tolist()])
     dt, g = timed(lambda: ctx.coordinate_order(*cols, names))
     ms_dev = ctx.last_timing()[0]
-    sub = 200000
+    sub = min(200000, n_out)
     t0 = time.perf_counter()
     c = O.coordinate_order(*[x[:sub] for x in cols], A.SeqBatch(names.data, names.offsets[:sub + 1]))
     dt_cpu = time.perf_counter() - t0
@@ -502,21 +671,15 @@ def main():
     from bioinformatics_b200.batches import ExtendResult
     from bioinformatics_b200 import _abi as A
 
-    probes, pairs = make_workload(args.pairs, rank)
-    n = pairs.n
     ctx = Context(local)
+    probes, pairs = make_workload(args.pairs, rank, ctx.pinned_array)  # pinned host buffers for the e2e legs
+    n = pairs.n
     ctx.set_probes(probes)
 
-    # pinned host buffers for the e2e leg
     def pin(arr):
         p = ctx.pinned_array(arr.nbytes).view(arr.dtype)
         p[:] = arr.reshape(-1)
         return p
-    pairs.r1.data = pin(pairs.r1.data)
-    pairs.r2.data = pin(pairs.r2.data)
-    pairs.r1.offsets = pin(pairs.r1.offsets)
-    pairs.r2.offsets = pin(pairs.r2.offsets)
-    pairs.probe_id = pin(pairs.probe_id)
     out = ExtendResult(n, CIGAR_CAP, MD_CAP)
     for f in ExtendResult.FIELDS_I32 + ("ok", "overflow", "pair_ok", "cigar", "md"):
         setattr(out, f, pin(getattr(out, f)))
@@ -639,8 +802,17 @@ def main():
         stages = stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks)
     line = None
     if rank == 0:
+        # the INT32 micro-kernel runs inside its own clock-sampler window: its rate is only meaningful beside the clock it ran at
+        ps = ClockSampler(local)
+        ps.start()
+        ps.wait_first()
+        ps.mark()
         peak = ctx.int32_peak(2.0)
+        peak_clocks = ps.stop()
         achieved = cells * OPS_PER_CELL / (ms_total / args.steps * 1e-3)
+        sms = torch.cuda.get_device_properties(local).multi_processor_count
+        sm_hz = (clocks.get("sm_mhz") or 1965.0) * 1e6
+        issue_limit = sms * 128 * sm_hz  # 4 warp instructions per clock per SM x 32 lanes, at the SM clock sampled in the timed region
         nominal = 148 * 128 * 1.965e9
         line = {"metric": METRIC, "value": value, "unit": "GCUPS", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
                 "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
@@ -661,18 +833,26 @@ def main():
                               "api": "hsq_extend_batch: ASCII reads, fixed %d + %d byte CIGAR / MD slots (the round-1 path)" % (CIGAR_CAP, MD_CAP)},
                 "gpu_launches": int(launches_per_step * args.steps),
                 "read_pairs_per_s": n * world / (ms_step * 1e-3),
-                "roofline": {"bound": "int32_alu", "achieved": achieved / 1e12, "peak": peak / 1e12, "unit": "Tiop/s",
-                             "frac": achieved / peak,
+                "roofline": {"bound": "int32_alu", "achieved": achieved / 1e12, "peak": issue_limit / 1e12, "unit": "Tiop/s",
+                             "frac": achieved / issue_limit,
+                             "peak_source": "INT32 issue limit at the SM clock sampled during the timed region: %d SMs x 128 lanes x %.0f MHz "
+                                            "(MEASURED_PEAKS.json holds no INT32 figure)" % (sms, sm_hz / 1e6),
+                             "micro_kernel": {"peak": peak / 1e12, "unit": "Tiop/s", "clocks": peak_clocks,
+                                              "warp_instr_per_clk_per_sm": peak / 32.0 / sms / ((peak_clocks.get("sm_mhz") or 1965.0) * 1e6),
+                                              "frac_of_it": achieved / peak,
+                                              "note": "hsq_int32_peak: 2 s of 4 IMAD + 4 VIADDMNMX independent chains per thread, 64 warps per SM, "
+                                                      "timed inside its own clock-sampler window"},
+                             "issued": {"instructions_per_cell_pair": 11, "alu_pipe": 6, "fma_pipe": 5,
+                                        "note": "the packed u16x2 cell issues 6 ALU-pipe + 5 FMA-pipe instructions per TWO cells (SASS count, "
+                                                "profiles/README_r2.md); the 12 algorithmic ops per cell of SURVEY 8(d) are the scalar statement "
+                                                "of the recurrence, so `frac` is an algorithmic-throughput fraction, not issue-slot utilisation "
+                                                "(ncu: profiles/ncu_full_capture2_kernel_r2_*.txt)"},
                              "traffic": TRAFFIC_PER_PAIR_BYTES * n,
                              "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of capture2_kernel from the ncu --set full capture "
                                              "at 500 k pairs (profiles/ncu_full_capture2_kernel_r1_j.txt: 4.97 + 6.40 GB) scaled to this "
                                              "batch: scratch (2-bit pointers, boundary rows), not algorithmic bytes; the kernel is ALU bound",
                              "note": "12 algorithmic INT32 ops per DP cell x cells per step / CUDA-event time of hsq_extend_run "
-                                     "(capture2_kernel + primer2_kernel are ~93%% of it, profiles/launches_r1_j.csv); peak = sustained INT32 issue rate measured in this run by "
-                                     "hsq_int32_peak (IMAD/VIMNMX/LOP3 micro-kernel, 2 s); nominal 148x128x1.965 GHz = %.1f Tiop/s; "
-                                     "MEASURED_PEAKS.json holds no INT32 figure; the packed kernels do two cells per VIADDMNMX.U16x2 / LOP3 / "
-                                     "IMAD, so the fraction of this scalar-op peak can exceed 1 at long reads (profiles/sweep_lengths_r1.jsonl); "
-                                     "ncu (r1_j): issue slots 71%% busy, ALU pipe 66%%" % (nominal / 1e12)},
+                                     "(capture2_kernel + primer2_kernel are ~93%% of it); nominal 148x128x1.965 GHz = %.1f Tiop/s" % (nominal / 1e12)},
                 "clocks": clocks, "stages": stages, "parity": parity}
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         threads = os.cpu_count() or 1

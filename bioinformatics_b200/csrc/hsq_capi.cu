@@ -15,6 +15,7 @@ struct CallTimer {  // brackets the kernels + copies of one batch call with even
     hsq_ctx* ctx;
     explicit CallTimer(hsq_ctx* c) : ctx(c) {
         ctx->launches = 0;
+        for (int k = 0; k < hsq_ctx::N_SPANS; k++) ctx->span_open[k] = ctx->span_done[k] = false;
         cudaEventRecord(ctx->ev0, ctx->stream);
     }
     int finish() {
@@ -22,10 +23,26 @@ struct CallTimer {  // brackets the kernels + copies of one batch call with even
         cudaError_t e = cudaStreamSynchronize(ctx->stream);
         if (e != cudaSuccess) return fail(ctx, HSQ_ERR_CUDA, std::string("stream sync: ") + cudaGetErrorString(e));
         cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->ev0, ctx->ev1);
+        for (int k = 0; k < hsq_ctx::N_SPANS; k++) {
+            ctx->span_ms[k] = -1.f;
+            if (ctx->span_done[k]) cudaEventElapsedTime(&ctx->span_ms[k], ctx->ev_span[k][0], ctx->ev_span[k][1]);
+        }
         ctx->last_launches = ctx->launches;
         return HSQ_OK;
     }
 };
+
+// Kernel-only spans: the events sit on the context's stream between the copies and the kernels of a call, so a span is the device
+// time of the kernels between them (the H2D copies before span_begin have completed when its event fires).
+void span_begin(hsq_ctx* ctx, int k) {
+    cudaEventRecord(ctx->ev_span[k][0], ctx->stream);
+    ctx->span_open[k] = true;
+}
+void span_end(hsq_ctx* ctx, int k) {
+    if (!ctx->span_open[k]) return;
+    cudaEventRecord(ctx->ev_span[k][1], ctx->stream);
+    ctx->span_done[k] = true;
+}
 
 int reset_status(hsq_ctx* ctx) {
     HSQ_CUDA(ctx, ctx->status.ensure(64));
@@ -122,6 +139,8 @@ static int ctx_init(hsq_ctx* ctx, const cudaDeviceProp& prop) {
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev1));
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev_user0));
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev_user1));
+    for (int k = 0; k < hsq_ctx::N_SPANS; k++)
+        for (int e = 0; e < 2; e++) HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev_span[k][e]));
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
     {   // the prep stream's short kernels should get SM slots ahead of the capture kernels' CTAs
@@ -215,6 +234,9 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     if (ctx->h_cells) cudaFreeHost(ctx->h_cells);
     for (cudaEvent_t ev : {ctx->ev0, ctx->ev1, ctx->ev_user0, ctx->ev_user1})
         if (ev) cudaEventDestroy(ev);
+    for (int k = 0; k < hsq_ctx::N_SPANS; k++)
+        for (int e = 0; e < 2; e++)
+            if (ctx->ev_span[k][e]) cudaEventDestroy(ctx->ev_span[k][e]);
     for (int k = 0; k < hsq_ctx::N_EXTEND_SETS; k++)
         for (cudaEvent_t ev : {ctx->ev_in[k], ctx->ev_prep[k], ctx->ev_cap[k], ctx->ev_out[k]})
             if (ev) cudaEventDestroy(ev);
@@ -241,6 +263,12 @@ int32_t hsq_set_scorer(hsq_ctx* ctx, const hsq_scorer* scorer) {
     if (!ctx || !scorer) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
     ctx->scorer = *scorer;
     ctx->have_scorer = true;
+    return HSQ_OK;
+}
+
+int32_t hsq_last_spans(const hsq_ctx* ctx, float* ms4) {
+    if (!ctx || !ms4) return HSQ_ERR_INVALID_ARGUMENT;
+    for (int k = 0; k < hsq_ctx::N_SPANS; k++) ms4[k] = ctx->span_ms[k];
     return HSQ_OK;
 }
 

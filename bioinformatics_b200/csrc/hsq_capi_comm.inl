@@ -168,6 +168,7 @@ int dedup_exchange_reduce(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint
     const size_t nn = (size_t)n;
     int rc;
     if (n >= (1ll << 31)) return fail(ctx, HSQ_ERR_UNSUPPORTED, "more than 2^31 pairs on one rank");
+    span_begin(ctx, 1);
     // counts: row of this rank = [pairs for owner 0 .. W-1, n]
     HSQ_CUDA(ctx, ctx->cm_cnt.ensure(sizeof(int64_t) * (size_t)(W + 1) * (size_t)(W + 2) + 64));
     unsigned long long* my_row = ctx->cm_cnt.as<unsigned long long>();
@@ -258,6 +259,7 @@ int dedup_exchange_reduce(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint
     }
     // every probe was counted on its owner alone: a sum gives all ranks the whole table
     if (np > 0) HSQ_NCCL(ctx, nc->AllReduce(d_stats, d_stats, (size_t)(3 * np), ncclInt32, ncclSum, comm, ctx->stream));
+    span_end(ctx, 1);
     HSQ_CUDA(ctx, cudaGetLastError());
     int w[1];
     if ((rc = read_status(ctx, w, 1))) return rc;

@@ -370,11 +370,13 @@ int dedup_upload_keygen(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, in
     if (n > 0) {
         const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        span_begin(ctx, 0);
         check_probe_ids_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, np > 0 ? np : INT32_MAX, d_status(ctx));
         dedup_keygen_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), ctx->q1.as<uint8_t>(),
                                                             ctx->r2.ascii.as<uint8_t>(), ctx->r2.offsets.as<int64_t>(), ctx->q2.as<uint8_t>(),
                                                             ctx->read_index.as<int32_t>(), n, u, v, ctx->sort_a.as<uint64_t>(),
                                                             ctx->sort_b.as<uint64_t>(), ctx->sort_d.as<uint32_t>(), d_status(ctx));
+        span_end(ctx, 0);
         ctx->launches += 2;
         int w[1];
         if ((rc = read_status(ctx, w, 1))) return rc;
@@ -392,8 +394,20 @@ int dedup_upload_keygen(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, in
 // per-probe counters to d_stats[3 * np] (device).
 // tie: optional last tie-break per pair (smaller wins) among pairs of equal (quality sum, read index); null = the pair index.  The
 // sharded path passes the pair's global position so that the answer does not depend on how the batch was split over ranks.
+int dedup_reduce_device_impl(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_t* d_best, int32_t* d_gs, int32_t* d_stats,
+                             const uint32_t* tie);
+
 int dedup_reduce_device(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_t* d_best, int32_t* d_gs, int32_t* d_stats,
                         const uint32_t* tie = nullptr) {
+    const bool own = !ctx->span_open[1];  // the sharded path opens span 1 around the whole exchange
+    if (own) span_begin(ctx, 1);
+    const int rc = dedup_reduce_device_impl(ctx, n, np, uid_len, d_best, d_gs, d_stats, tie);
+    if (own) span_end(ctx, 1);
+    return rc;
+}
+
+int dedup_reduce_device_impl(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, uint8_t* d_best, int32_t* d_gs, int32_t* d_stats,
+                             const uint32_t* tie) {
     const size_t nn = (size_t)n;
     int rc;
     HSQ_CUDA(ctx, ctx->sort_c.ensure(nn * 8 + 16));   // keys pong

@@ -712,11 +712,13 @@ int dedup_upload_keygen_packed(hsq_ctx* ctx, const hsq_packed_pairs* pb, int u, 
     if (n > 0) {
         const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        span_begin(ctx, 0);
         check_probe_ids_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, np > 0 ? np : INT32_MAX, d_status(ctx));
         dedup_keygen_codes_kernel<<<blocks, 256, 0, ctx->stream>>>(
             ctx->r1.codes.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), ctx->q1.as<uint8_t>(), ctx->r2.codes.as<uint8_t>(), ctx->r2.offsets.as<int64_t>(),
             ctx->q2.as<uint8_t>(), sums ? ctx->q1.as<int16_t>() : nullptr, sums ? ctx->q2.as<int16_t>() : nullptr, ctx->read_index.as<int32_t>(), n, u, v,
             ctx->sort_a.as<uint64_t>(), ctx->sort_b.as<uint64_t>(), ctx->sort_d.as<uint32_t>(), d_status(ctx));
+        span_end(ctx, 0);
         ctx->launches += 2;
         int w[1];
         if ((rc = read_status(ctx, w, 1))) return rc;

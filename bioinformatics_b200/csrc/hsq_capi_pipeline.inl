@@ -182,6 +182,7 @@ int dedup_extend_run(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32
     bool swapped = false;
     int rce = HSQ_OK;
     if (!skip) {
+        span_begin(ctx, 2);
         if (compact) {
             if ((rce = compact_survivors(ctx, n, d_best, d_list, &m))) m = 0;
             else {
@@ -193,11 +194,14 @@ int dedup_extend_run(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32
             iota_kernel<<<gblocks, 256, 0, ctx->stream>>>(d_list, n);
             ctx->launches++;
         }
+        span_end(ctx, 2);
         if (!rce) rce = d2h(ctx, out->extended_pair, d_list, (size_t)m);
         if (!rce) {
             ctx->ext_n = m;
             ctx->keep_counters = false;
+            span_begin(ctx, 3);
             rce = extend_run(ctx, out->extend->cigar_cap, out->extend->md_cap);
+            span_end(ctx, 3);
         }
         if (!rce && m > 0) {
             const int gblocks = (int)std::min<int64_t>((m + 255) / 256, (int64_t)ctx->sm_count * 16);

@@ -68,6 +68,7 @@ extern "C" int32_t hsq_trim_batch(hsq_ctx* ctx, const hsq_seqs* reads, const uin
     int64_t* d_out_off = ctx->sort_b.as<int64_t>();
     uint8_t* d_out_seq = ctx->out_slots.as<uint8_t>();
     uint8_t* d_out_qual = d_out_seq + total + 16;
+    span_begin(ctx, 0);
     if (n > 0) {
         int blocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 8);
         trim_len_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.offsets.as<int64_t>(), n, first, last, three_prime, keep, d_status(ctx));
@@ -84,6 +85,7 @@ extern "C" int32_t hsq_trim_batch(hsq_ctx* ctx, const hsq_seqs* reads, const uin
                                                          d_out_off, n, first, d_out_seq, d_out_qual);
         ctx->launches++;
     }
+    span_end(ctx, 0);
     HSQ_CUDA(ctx, cudaGetLastError());
     HSQ_CUDA(ctx, cudaMemcpyAsync(out_offsets, d_out_off, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
     int w[1];

@@ -56,6 +56,11 @@ struct hsq_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_user0 = nullptr, ev_user1 = nullptr;
     std::string error;
+    // kernel-only spans of the last batch call (events around groups of kernels, copies excluded): hsq_last_spans
+    static constexpr int N_SPANS = 4;
+    cudaEvent_t ev_span[N_SPANS][2] = {};
+    bool span_open[N_SPANS] = {}, span_done[N_SPANS] = {};
+    float span_ms[N_SPANS] = {};
     float last_kernel_ms = 0.f;
     int last_launches = 0;
     int launches = 0;  // running count inside a call

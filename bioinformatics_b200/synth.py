@@ -154,6 +154,44 @@ def make_pairs(probes, n_pairs, read_len=150, ext_uid_len=10, lig_uid_len=0, see
                          np.arange(n_pairs, dtype=np.int32))
 
 
+def tile_pairs(base, tiles, alloc=None):
+    """A batch of tiles * base.n pairs from one generated base batch of fixed-length reads, for the large bench shapes (generation
+    costs ~10 s per million pairs): tile t is the base with the first two bases of read one (the start of the extension UID) rotated
+    by t % 4 and t // 4 letters, so every tile carries its own molecules -- same probes, same family sizes, disjoint UID groups
+    (tiles <= 16) -- and the FASTQ ordinals continue (read_index + t * (largest base ordinal + 1)).  alloc(nbytes) -> uint8 array (e.g. pinned memory)."""
+    assert 1 <= tiles <= 16
+    alloc = alloc or (lambda nbytes: np.empty(nbytes, dtype=np.uint8))
+    n = base.n
+    L1, L2 = len(base.r1.data) // max(n, 1), len(base.r2.data) // max(n, 1)
+
+    def rep(sb, L):
+        if sb is None:
+            return None
+        out = alloc(tiles * n * L)[:tiles * n * L].reshape(tiles, n, L)
+        out[:] = sb.data.reshape(1, n, L)
+        return out
+
+    r1, r2, q1, q2 = rep(base.r1, L1), rep(base.r2, L2), rep(base.q1, L1), rep(base.q2, L2)
+    idx = np.searchsorted(_ACGT, base.r1.data.reshape(n, L1)[:, :2])
+    acgt = _ACGT[np.minimum(idx, 3)] == base.r1.data.reshape(n, L1)[:, :2]
+    for t in range(1, tiles):
+        for col, rot in ((0, t % 4), (1, t // 4)):
+            r1[t, :, col] = np.where(acgt[:, col], _ACGT[(idx[:, col] + rot) % 4], r1[0, :, col])
+    probe = alloc(4 * tiles * n).view(np.int32)[:tiles * n].reshape(tiles, n)
+    probe[:] = base.probe_id[None, :]
+    ri = alloc(4 * tiles * n).view(np.int32)[:tiles * n].reshape(tiles, n)
+    ri[:] = base.read_index[None, :].astype(np.int64) + (np.arange(tiles, dtype=np.int64) * (int(base.read_index.max()) + 1 if n else 0))[:, None]
+
+    def sb_of(a, L):
+        if a is None:
+            return None
+        off = alloc(8 * (tiles * n + 1)).view(np.int64)[:tiles * n + 1]
+        off[:] = np.arange(tiles * n + 1, dtype=np.int64) * L
+        return A.SeqBatch(a.reshape(-1), off)
+
+    return PairBatchHost(probe.reshape(-1), sb_of(r1, L1), sb_of(r2, L2), sb_of(q1, L1), sb_of(q2, L2), ri.reshape(-1))
+
+
 def drop_n_pairs(pairs):
     """The caller-side filter of …Identification.java:815-821: pairs with an 'N'/'n' in either mate are not deduplicated."""
     L1 = pairs.r1.lengths()

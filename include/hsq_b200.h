@@ -371,6 +371,11 @@ int32_t hsq_set_probes(hsq_ctx* ctx, const hsq_probe_table* probes);
 /* Device time (ms, CUDA events on the context's stream) of the kernels of the last batch call,
  * and how many kernels it launched. */
 int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches);
+/* Kernel-only device times (ms, CUDA events between the copies and the kernels) of the last batch call, -1 where the call has no
+ * such span: hsq_trim_batch [0] length + scan + copy kernels; hsq_dedup_batch / hsq_dedup_packed / hsq_dedup_sharded /
+ * hsq_dedup_extend_* [0] key generation, [1] per-probe bucketing + group-by (sharded: the exchange and the owner's reduction),
+ * [2] compaction of the pairs to extend, [3] the extension kernels. */
+int32_t hsq_last_spans(const hsq_ctx* ctx, float* ms4);
 
 /* ---- batch entry points (host buffers in, host buffers out) -------------------------------- */
 /* new NeedlemanWunschGlobalAlignment(ref[k], qry[k], SimpleAlignmentScorer(scorer, flags)).getAlignmentPair() */
