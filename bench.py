@@ -350,7 +350,40 @@ def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
             c4["trim_plus_" + key] = {"read_pairs_per_s": n4 * world / (ms * 1e-3), "ms_host_to_host": ms,
                                       "note": "the two HSQUtils commands back to back: trim of both mates (rate of the trim entry above applied to the whole "
                                               "batch) + the probe task; the mapper that runs between them in a real run is not part of this path"}
-        c4["parity"] = {"fused_flags_equal_dedup": bool(np.array_equal(res4.is_best, best)),
+        # the same probe task in the N1 form: reads 2 bit/base + host-made quality sums in, integer columns + CIGAR/MD pool out
+        from bioinformatics_b200.batches import PooledExtendResult
+        t0 = time.perf_counter()
+        pk4 = PackedPairsHost(pairs4.probe_id, pack_reads(pairs4.r1, 2, ctx.pinned_array), pack_reads(pairs4.r2, 2, ctx.pinned_array), None, None,
+                              pairs4.read_index, quality_sums(pairs4.q1), quality_sums(pairs4.q2))
+        pack_s = time.perf_counter() - t0
+        POOLED_FIELDS = ("ok", "pair_ok", "pos", "read_start", "read_stop", "nm", "cigar_len", "md_len", "str_off")
+        resp = DedupExtendResult(n4, NP4, pooled=PooledExtendResult(n4, 2 * n4 * 24, fields=POOLED_FIELDS, alloc=ctx.pinned_array))
+        for f in ("is_best", "group_size", "extended_pair"):
+            a = getattr(resp, f)
+            setattr(resp, f, ctx.pinned_array(a.nbytes).view(a.dtype))
+        packed_same = True
+        for mark in (False, True):
+            dt, r = timed(lambda: ctx.dedup_extend_packed(pk4, U4, 0, extend_duplicates=mark, sharded=world > 1, out=resp))
+            sp = ctx.last_spans()
+            key = "dedup_extend_packed_mark_duplicates" if mark else "dedup_extend_packed"
+            h2d_b = pk4.r1.nbytes + pk4.r2.nbytes + 4 * n4 * 2 + 2 * n4 * 2
+            d2h_b = resp.pooled.nbytes() * r.n_extended // max(n4, 1) + 5 * n4 + 4 * r.n_extended
+            c4[key] = {"read_pairs_per_s": n4 * world / dt, "ms_host_to_host": dt * 1e3, "pairs_extended_this_rank": int(r.n_extended),
+                       "keygen_kernel_ms": sp[0], "group_or_exchange_ms": sp[1], "compaction_kernels_ms": sp[2], "extend_kernels_ms": sp[3],
+                       "h2d_bytes_per_pair": h2d_b / n4, "d2h_bytes_per_pair": d2h_b / n4,
+                       "api": "hsq_dedup_extend_packed (sharded=%d): reads 2 bit/base + hsq_quality_sums in, columns %s + CIGAR/MD pool out" % (world > 1, POOLED_FIELDS)}
+            ms = trim_ms_per_pair * n4 + dt * 1e3
+            c4["trim_plus_" + key] = {"read_pairs_per_s": n4 * world / (ms * 1e-3), "ms_host_to_host": ms}
+            if mark:  # res4 still holds the ASCII call's mark-duplicates run: same flags, same positions
+                m = r.n_extended
+                packed_same = bool(packed_same and m == res4.n_extended and np.array_equal(resp.is_best, res4.is_best) and
+                                   np.array_equal(resp.pooled.pos[:2 * m], res4.extend.pos[:2 * m]) and
+                                   np.array_equal(resp.pooled.cigar_len[:2 * m], res4.extend.cigar_len[:2 * m]) and
+                                   np.array_equal(resp.pooled.pair_ok[:m], res4.extend.pair_ok[:m]))
+        c4["packing"] = {"host_s": pack_s, "note": "hsq_pack_reads + hsq_quality_sums over the batch (host helpers, all cores), outside the timed calls: "
+                                                     "packed reads + quality sums are the input format of this path"}
+        del pk4, resp
+        c4["parity"] = {"fused_flags_equal_dedup": bool(np.array_equal(res4.is_best, best)), "packed_call_equals_ascii_call": packed_same,
                         "unique_equals_sum_of_probe_counters": bool(_sum_ranks(dist, int(best.sum())) == int(st.unique_pairs.sum()))}
         # the sharded answer against the oracle on a sample gathered to rank 0
         if world > 1:

@@ -98,7 +98,8 @@ class ProbeStats(C.Structure):
 
 class DedupExtendOut(C.Structure):
     _fields_ = [("is_best", u8p), ("group_size", i32p), ("stats", C.POINTER(ProbeStats)), ("unique_unable_to_extend", i32p),
-                ("duplicate_unable_to_extend", i32p), ("n_extended", C.c_int64), ("extended_pair", i32p), ("extend", C.POINTER(ExtendOut))]
+                ("duplicate_unable_to_extend", i32p), ("n_extended", C.c_int64), ("extended_pair", i32p), ("extend", C.POINTER(ExtendOut)),
+                ("extend_pooled", C.c_void_p)]
 
 
 class RecordOut(C.Structure):

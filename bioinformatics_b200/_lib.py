@@ -24,7 +24,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order",
            "hsq_ctx_create_ex", "hsq_ctx_configure", "hsq_packed_bytes", "hsq_pack_reads", "hsq_quality_sums", "hsq_unpack_reads",
            "hsq_extend_packed", "hsq_dedup_packed", "hsq_comm_unique_id", "hsq_comm_init_rank", "hsq_comm_init_all", "hsq_comm_destroy",
-           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans")
+           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed")
 _NOT_STATUS = {"hsq_last_error": C.c_char_p, "hsq_version": C.c_char_p, "hsq_ctx_destroy": None, "hsq_packed_bytes": C.c_int64}
 
 
@@ -444,6 +444,18 @@ class Context:
         self._check(self.lib.hsq_dedup_packed(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
                                               A.ptr(is_best, A.u8p), A.ptr(group_size, A.i32p), C.byref(sc)))
         return is_best, group_size, stats
+
+    def dedup_extend_packed(self, pairs: PackedPairsHost, ext_uid_len, lig_uid_len, extend_duplicates=False, sharded=False, out=None, pool_cap=None,
+                            n_probes=None):
+        """hsq_dedup_extend_packed: the probe task for a packed batch, results pooled (out.pooled); sharded: collective over the communicator."""
+        if out is None:
+            out = DedupExtendResult(pairs.n, n_probes or self.n_probes, pooled=PooledExtendResult(pairs.n, pool_cap if pool_cap is not None else 2 * pairs.n * 48))
+        pc, oc = pairs.c(), out.c()
+        st = self.lib.hsq_dedup_extend_packed(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                              C.c_int32(1 if extend_duplicates else 0), C.c_int32(1 if sharded else 0), C.byref(oc))
+        out.finish()
+        self._check(st)
+        return out
 
     # ---- multi-GPU inside the library (NCCL) ----
     def comm_init_rank(self, id_bytes, rank, world):

@@ -272,29 +272,35 @@ class ProbeStatsHost:
 class DedupExtendResult:
     """hsq_dedup_extend_out with host arrays for n pairs and n_probes probes."""
 
-    def __init__(self, n, n_probes, cigar_cap=32, md_cap=48):
+    def __init__(self, n, n_probes, cigar_cap=32, md_cap=48, pooled=None):
+        """pooled: a PooledExtendResult for hsq_dedup_extend_packed (the slot result `extend` is then not allocated)."""
         self.n = n
+        self.pooled = pooled
         self.is_best = np.zeros(n, dtype=np.uint8)
         self.group_size = np.zeros(n, dtype=np.int32)
         self.stats = ProbeStatsHost(n_probes)
         self.unique_unable_to_extend = np.zeros(n_probes, dtype=np.int32)
         self.duplicate_unable_to_extend = np.zeros(n_probes, dtype=np.int32)
         self.extended_pair = np.zeros(n, dtype=np.int32)
-        self.extend = ExtendResult(n, cigar_cap, md_cap)
+        self.extend = ExtendResult(0 if pooled is not None else n, cigar_cap, md_cap)
         self.n_extended = 0
         self._c = None
 
     def c(self):
         self._stats_c = self.stats.c()
         self._ext_c = self.extend.c()
+        self._pool_c = None if self.pooled is None else self.pooled.c()
         self._c = A.DedupExtendOut(A.ptr(self.is_best, A.u8p), A.ptr(self.group_size, A.i32p), C.pointer(self._stats_c),
                                    A.ptr(self.unique_unable_to_extend, A.i32p), A.ptr(self.duplicate_unable_to_extend, A.i32p), 0,
-                                   A.ptr(self.extended_pair, A.i32p), C.pointer(self._ext_c))
+                                   A.ptr(self.extended_pair, A.i32p), C.pointer(self._ext_c),
+                                   None if self._pool_c is None else C.cast(C.pointer(self._pool_c), C.c_void_p))
         return self._c
 
     def finish(self):
         self.n_extended = int(self._c.n_extended)
         self.extend.cells = int(self._ext_c.cells)
+        if self.pooled is not None:
+            self.pooled.finish()
         return self
 
 

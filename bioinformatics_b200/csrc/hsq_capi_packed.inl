@@ -382,10 +382,11 @@ int unpack_seqs(hsq_ctx* ctx, DevSeqsOwned* d) {
 }
 
 int prepare_codes(hsq_ctx* ctx, DevSeqsOwned* d, int* d_maxlen) {
-    if (d->packed_bits < 0) return HSQ_OK;  // the codes are already in place (device-side compaction of an unpacked batch)
-    if (d->packed_bits > 0) {
-        int rc = unpack_seqs(ctx, d);
-        if (rc) return rc;
+    if (d->packed_bits != 0) {  // < 0: the codes are already in place (device-side compaction of an unpacked batch)
+        if (d->packed_bits > 0) {
+            int rc = unpack_seqs(ctx, d);
+            if (rc) return rc;
+        }
         if (d_maxlen && d->n > 0) {
             const int blocks = (int)std::min<int64_t>((d->n + 255) / 256, (int64_t)ctx->sm_count * 8);
             max_len_kernel<<<blocks, 256, 0, ctx->stream>>>(d->offsets.as<int64_t>(), d->n, d_maxlen);

@@ -110,10 +110,15 @@ int compact_survivors(hsq_ctx* ctx, int64_t n, const uint8_t* d_keep, int32_t* d
         HSQ_CUDA(ctx, s.dst->ascii.ensure((size_t)s.src->total + 32));
         HSQ_CUDA(ctx, s.dst->codes.ensure((size_t)s.src->total + 32));
         s.dst->n = m;
+        // a batch that arrived packed holds device codes already (packed_bits < 0): those are what is compacted, and the extension
+        // will not decode again; an ASCII batch is compacted as ASCII and encoded afterwards
+        const bool coded = s.src->packed_bits < 0;
+        s.dst->packed_bits = coded ? -1 : 0;
         if (m > 0) {
             const int blocks = (int)std::min<int64_t>((m * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
-            survivor_copy_kernel<<<blocks, 256, 0, ctx->stream>>>(s.src->ascii.as<uint8_t>(), s.src->offsets.as<int64_t>(), d_list,
-                                                                 s.dst->offsets.as<int64_t>(), m, s.dst->ascii.as<uint8_t>());
+            survivor_copy_kernel<<<blocks, 256, 0, ctx->stream>>>(coded ? s.src->codes.as<uint8_t>() : s.src->ascii.as<uint8_t>(), s.src->offsets.as<int64_t>(),
+                                                                 d_list, s.dst->offsets.as<int64_t>(), m,
+                                                                 coded ? s.dst->codes.as<uint8_t>() : s.dst->ascii.as<uint8_t>());
             ctx->launches++;
         }
     }
@@ -132,14 +137,30 @@ int compact_survivors(hsq_ctx* ctx, int64_t n, const uint8_t* d_keep, int32_t* d
 
 namespace {
 
-int dedup_extend_args(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, const hsq_dedup_extend_out* out) {
-    if (!ctx || !pairs || !out || !out->is_best || !out->extend || !out->extended_pair) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
-    if (pairs->n < 0 || pairs->r1.n != pairs->n || pairs->r2.n != pairs->n) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
-    if (pairs->n >= (1ll << 31)) return fail(ctx, HSQ_ERR_UNSUPPORTED, "more than 2^31 pairs in one batch");
+// the pairs of a probe-task call: an ASCII batch or a packed one
+struct PairSource {
+    const hsq_pair_batch* a = nullptr;
+    const hsq_packed_pairs* p = nullptr;
+    int64_t n() const { return a ? a->n : p->n; }
+};
+
+int dedup_extend_args(hsq_ctx* ctx, const PairSource& src, int32_t u, int32_t v, const hsq_dedup_extend_out* out, bool pooled) {
+    if (!ctx || (!src.a && !src.p) || !out || !out->is_best || !out->extended_pair) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null argument");
+    if (pooled ? !out->extend_pooled : !out->extend) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null extension output");
+    const int64_t n = src.n();
+    if (src.a && (n < 0 || src.a->r1.n != n || src.a->r2.n != n)) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "pair batch arrays disagree on n");
+    if (src.p) {
+        if (n < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
+        if (n > 0 && !src.p->probe_id) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe_id is null");
+        int rc;
+        if ((rc = check_packed_reads(ctx, &src.p->r1, n, "hsq_dedup_extend_packed")) || (rc = check_packed_reads(ctx, &src.p->r2, n, "hsq_dedup_extend_packed"))) return rc;
+    }
+    if (n >= (1ll << 31)) return fail(ctx, HSQ_ERR_UNSUPPORTED, "more than 2^31 pairs in one batch");
     if (u < 0 || v < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative UID length");
     if (u + v > 32) return fail(ctx, HSQ_ERR_UNSUPPORTED, "UID longer than 32 bases in total is outside the accelerated domain");
     if (!out->stats || out->stats->n_probes <= 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "probe stats (with n_probes) are required");
-    if (out->extend->cigar_cap < 0 || out->extend->md_cap < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
+    if (pooled ? (out->extend_pooled->cigar_cap < 0 || out->extend_pooled->md_cap < 0) : (out->extend->cigar_cap < 0 || out->extend->md_cap < 0))
+        return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative size");
     int rc = extend_args_ok(ctx);
     if (rc) return rc;
     if (out->stats->n_probes != ctx->n_probes) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "stats->n_probes differs from the probe table");
@@ -148,12 +169,21 @@ int dedup_extend_args(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int3
 
 // The probe task body for this context's pairs.  sharded: the reduction runs over the union of all ranks' pairs (collective, see
 // hsq_capi_comm.inl) and the per-probe counters are those of the whole batch; the extension runs on this rank's own pairs.
-int dedup_extend_run(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, int32_t extend_duplicates, hsq_dedup_extend_out* out, bool sharded) {
-    const int64_t n = pairs->n, np = out->stats->n_probes;
+int dedup_extend_run(hsq_ctx* ctx, const PairSource& src, int32_t u, int32_t v, int32_t extend_duplicates, hsq_dedup_extend_out* out, bool sharded,
+                     bool pooled) {
+    const int64_t n = src.n(), np = out->stats->n_probes;
     const size_t nn = (size_t)n;
     out->n_extended = 0;
     int rc;
-    int bad = dedup_upload_keygen(ctx, pairs, u, v, np);
+    const int cigar_cap = pooled ? (out->extend_pooled->cigar_cap ? out->extend_pooled->cigar_cap : 64) : out->extend->cigar_cap;
+    const int md_cap = pooled ? (out->extend_pooled->md_cap ? out->extend_pooled->md_cap : 96) : out->extend->md_cap;
+    PoolState ps;
+    if (pooled) {
+        out->extend_pooled->pool_bytes = 0;
+        out->extend_pooled->cells = 0;
+        if ((rc = pool_begin(ctx, out->extend_pooled, &ps)) && !sharded) return rc;
+    }
+    int bad = src.a ? dedup_upload_keygen(ctx, src.a, u, v, np) : dedup_upload_keygen_packed(ctx, src.p, u, v, np);
     if (bad && !sharded) return bad;
     const std::string bad_msg = ctx->error;
     HSQ_CUDA(ctx, ctx->dd_u8.ensure(nn + 32));
@@ -200,7 +230,7 @@ int dedup_extend_run(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32
             ctx->ext_n = m;
             ctx->keep_counters = false;
             span_begin(ctx, 3);
-            rce = extend_run(ctx, out->extend->cigar_cap, out->extend->md_cap);
+            rce = extend_run(ctx, cigar_cap, md_cap);
             span_end(ctx, 3);
         }
         if (!rce && m > 0) {
@@ -219,9 +249,18 @@ int dedup_extend_run(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32
     if (!skip) {
         if (!rce) rce = d2h(ctx, out->unique_unable_to_extend, d_unable, (size_t)np);
         if (!rce) rce = d2h(ctx, out->duplicate_unable_to_extend, d_unable + np, (size_t)np);
-        if (!rce) rce = extend_fetch(ctx, out->extend);
+        if (!rce && !pooled) rce = extend_fetch(ctx, out->extend);
+        if (!rce && pooled) {
+            rce = fetch_pooled_chunk(ctx, 0, m, out->extend_pooled, ps);
+            if (!rce) rce = extend_counters(ctx, &out->extend_pooled->cells);
+            if (!rce || rce == HSQ_ERR_OVERFLOW) {
+                const int r3 = pool_end(ctx, out->extend_pooled, ps);
+                if (!rce) rce = r3;
+            }
+        }
     }
     if (swapped) swap_read_buffers(ctx);
+    ctx->r1.packed_bits = ctx->r2.packed_bits = ctx->alt_r1.packed_bits = ctx->alt_r2.packed_bits = 0;
     ctx->ext_n = -1;
     ctx->ext_ran = false;
     if (bad) return fail(ctx, bad, bad_msg);
@@ -235,11 +274,13 @@ int dedup_extend_run(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32
 
 extern "C" int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, int32_t extend_duplicates,
                                           hsq_dedup_extend_out* out) {
-    int rc = dedup_extend_args(ctx, pairs, u, v, out);
+    PairSource src;
+    src.a = pairs;
+    int rc = dedup_extend_args(ctx, src, u, v, out, false);
     if (rc) return rc;
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
-    rc = dedup_extend_run(ctx, pairs, u, v, extend_duplicates, out, false);
+    rc = dedup_extend_run(ctx, src, u, v, extend_duplicates, out, false, false);
     int rc2 = timer.finish();
     return rc ? rc : rc2;
 }
@@ -247,12 +288,30 @@ extern "C" int32_t hsq_dedup_extend_batch(hsq_ctx* ctx, const hsq_pair_batch* pa
 // hsq_dedup_extend_batch over the union of all ranks' pairs: collective, every rank of the communicator calls it with its own pairs.
 extern "C" int32_t hsq_dedup_extend_sharded(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t u, int32_t v, int32_t extend_duplicates,
                                             hsq_dedup_extend_out* out) {
-    int rc = dedup_extend_args(ctx, pairs, u, v, out);
+    PairSource src;
+    src.a = pairs;
+    int rc = dedup_extend_args(ctx, src, u, v, out, false);
     if (!rc) rc = comm_ready(ctx);
     if (rc) return rc;
     HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
     CallTimer timer(ctx);
-    rc = dedup_extend_run(ctx, pairs, u, v, extend_duplicates, out, true);
+    rc = dedup_extend_run(ctx, src, u, v, extend_duplicates, out, true, false);
+    int rc2 = timer.finish();
+    return rc ? rc : rc2;
+}
+
+// The probe task for a packed batch, results pooled (out->extend_pooled): what a host should use for large batches -- with host-made
+// quality sums about 100 bytes per pair cross PCIe instead of 624.  sharded != 0: collective over the context's communicator.
+extern "C" int32_t hsq_dedup_extend_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs, int32_t u, int32_t v, int32_t extend_duplicates,
+                                           int32_t sharded, hsq_dedup_extend_out* out) {
+    PairSource src;
+    src.p = pairs;
+    int rc = dedup_extend_args(ctx, src, u, v, out, true);
+    if (!rc && sharded) rc = comm_ready(ctx);
+    if (rc) return rc;
+    HSQ_CUDA(ctx, cudaSetDevice(ctx->device));
+    CallTimer timer(ctx);
+    rc = dedup_extend_run(ctx, src, u, v, extend_duplicates, out, sharded != 0, true);
     int rc2 = timer.finish();
     return rc ? rc : rc2;
 }
@@ -264,7 +323,9 @@ extern "C" int32_t hsq_dedup_extend_multi_gpu(hsq_ctx** ctxs, int32_t n, const h
     if (!ctxs || n < 1 || !pairs || !outs) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "null argument");
     for (int k = 0; k < n; k++) {
         if (!ctxs[k]) return fail(nullptr, HSQ_ERR_INVALID_ARGUMENT, "null context");
-        int rc = dedup_extend_args(ctxs[k], &pairs[k], u, v, &outs[k]);  // argument errors before any collective starts
+        PairSource src;
+        src.a = &pairs[k];
+        int rc = dedup_extend_args(ctxs[k], src, u, v, &outs[k], false);  // argument errors before any collective starts
         if (rc) return rc;
     }
     bool have = true;

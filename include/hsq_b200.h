@@ -261,6 +261,7 @@ typedef struct hsq_dedup_extend_out {
     int64_t n_extended;                 /* out: pairs handed to the extension = slots used in `extend` */
     int32_t* extended_pair;             /* [n] out: extended_pair[j] = index of the pair whose results sit in slot j (ascending) */
     hsq_extend_out* extend;             /* arrays sized for n pairs (2n read ends); slots j < n_extended are written */
+    struct hsq_extend_pooled_out* extend_pooled; /* hsq_dedup_extend_packed writes here instead of `extend` (same slot numbering) */
 } hsq_dedup_extend_out;
 
 /* ---- SAM record fields of extended pairs (SURVEY.md 8(a) A5 outputs, 8(f) f4) ---------------------------------------- */
@@ -617,6 +618,12 @@ int32_t hsq_extend_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs, hsq_exten
  * non-ACGT UID base is for hsq_dedup_batch), the quality sums from q1 / q2. */
 int32_t hsq_dedup_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs, int32_t ext_uid_len, int32_t lig_uid_len, uint8_t* is_best,
                          int32_t* group_size, hsq_probe_stats* stats);
+
+/* hsq_dedup_extend_batch for a packed batch with pooled results (out->extend_pooled; out->extend is not used).  With host-made quality
+ * sums (pairs->qsum1 / qsum2) about 100 bytes per pair cross PCIe instead of 624.  sharded != 0: the reduction is the collective of
+ * hsq_dedup_extend_sharded over the context's communicator. */
+int32_t hsq_dedup_extend_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs, int32_t ext_uid_len, int32_t lig_uid_len,
+                                int32_t extend_duplicates, int32_t sharded, hsq_dedup_extend_out* out);
 
 /* ---- sharded dedup: one process per GPU, exchange by the caller ------------------------------------------------------ */
 /* First half of FilterByUid.reduceReadsByProbeAndUid for this rank's pairs (host buffers in): writes pairs->n key

@@ -183,3 +183,38 @@ def test_dedup_packed_equals_oracle(ctx, bits):
     with pytest.raises(HsqError) as e:
         ctx.dedup_packed(packed_pairs_of(bad, bits), 7, 3, probes.n)
     assert e.value.status == A.HSQ_ERR_UNSUPPORTED
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mark,sums", [(False, False), (True, True), (False, True)])
+def test_dedup_extend_packed_equals_ascii_call(ctx, mark, sums):
+    """hsq_dedup_extend_packed (packed reads in, pooled strings out; quality bytes or host-made sums) returns what hsq_dedup_extend_batch
+    returns for the same pairs, and that equals oracle dedup -> oracle extend (tests/test_pipeline.py pins the ASCII call)."""
+    from oracle import oracle as O
+    probes = synth.make_probes(70, seed=61)
+    pairs, _ = synth.drop_n_pairs(synth.make_pairs(probes, 9000, read_len=150, ext_uid_len=8, lig_uid_len=2, seed=62, sub_rate=0.02, ins_rate=0.004,
+                                                   del_rate=0.004))
+    ctx.set_probes(probes)
+    ref = ctx.dedup_extend_batch(pairs, 8, 2, extend_duplicates=mark, cigar_cap=64, md_cap=96)
+    pp = packed_pairs_of(pairs, 2)
+    if sums:
+        pp = PackedPairsHost(pairs.probe_id, pp.r1, pp.r2, None, None, pairs.read_index, quality_sums(pairs.q1), quality_sums(pairs.q2))
+    got = ctx.dedup_extend_packed(pp, 8, 2, extend_duplicates=mark)
+    m = ref.n_extended
+    assert got.n_extended == m and np.array_equal(got.is_best, ref.is_best) and np.array_equal(got.group_size, ref.group_size)
+    assert np.array_equal(got.extended_pair[:m], ref.extended_pair[:m])
+    for f in ("unique_pairs", "duplicate_pairs", "max_pairs_per_uid"):
+        assert np.array_equal(getattr(got.stats, f), getattr(ref.stats, f))
+    assert np.array_equal(got.unique_unable_to_extend, ref.unique_unable_to_extend)
+    assert np.array_equal(got.duplicate_unable_to_extend, ref.duplicate_unable_to_extend)
+    g, r = got.pooled, ref.extend.head(m)
+    for f in ("ok", "primer_end", "score", "pos", "read_start", "read_stop", "nm", "tlen", "cigar_len", "md_len"):
+        assert np.array_equal(getattr(g, f)[:2 * m], getattr(r, f)), f
+    assert np.array_equal(g.pair_ok[:m], r.pair_ok)
+    assert g.cigars()[:2 * m] == r.cigars() and g.mds()[:2 * m] == r.mds()
+    assert g.cells == ref.extend.cells
+    # and the oracle, end to end
+    eb, _, _ = O.dedup_batch(pairs, 8, 2, probes.n)
+    idx = np.arange(pairs.n) if mark else np.nonzero(eb)[0]
+    ext = O.extend_batch(probes, pairs.subset(idx), cigar_cap=64, md_cap=96, nthreads=8)
+    assert np.array_equal(got.is_best, eb) and np.array_equal(g.pos[:2 * m], ext.pos) and g.cigars()[:2 * m] == ext.cigars()
