@@ -69,7 +69,7 @@ i16p = C.POINTER(C.c_int16)
 
 class PackedReads(C.Structure):
     _fields_ = [("bits", C.c_int32), ("n", C.c_int64), ("data", u8p), ("len", i32p), ("n_exceptions", C.c_int64), ("exc_read", u32p),
-                ("exc_pos", u32p), ("exc_char", u8p)]
+                ("exc_pos", u32p), ("exc_char", u8p), ("data_bytes", C.c_int64), ("n_bases", C.c_int64)]
 
 
 class PackedPairs(C.Structure):

@@ -132,6 +132,7 @@ class PackedReadsHost:
         self.exc_read = np.zeros(0, dtype=np.uint32) if exc_read is None else exc_read
         self.exc_pos = np.zeros(0, dtype=np.uint32) if exc_pos is None else exc_pos
         self.exc_char = np.zeros(0, dtype=np.uint8) if exc_char is None else exc_char
+        self.n_bases = int(self.len.sum(dtype=np.int64))  # the totals travel with the batch: the library need not add up the lengths
 
     @property
     def nbytes(self):
@@ -141,7 +142,7 @@ class PackedReadsHost:
         ne = len(self.exc_read)
         return A.PackedReads(self.bits, self.n, A.ptr(self.data, A.u8p), A.ptr(self.len, A.i32p), ne,
                              A.ptr(self.exc_read if ne else None, A.u32p), A.ptr(self.exc_pos if ne else None, A.u32p),
-                             A.ptr(self.exc_char if ne else None, A.u8p))
+                             A.ptr(self.exc_char if ne else None, A.u8p), self.data.nbytes, self.n_bases)
 
 
 class PackedPairsHost:

@@ -30,6 +30,12 @@ __global__ void packed_lens_kernel(const int32_t* __restrict__ len, int64_t n, i
     }
 }
 
+// caller-supplied totals of a packed batch against the scans of its lengths
+__global__ void packed_totals_kernel(const int64_t* __restrict__ offsets, const int64_t* __restrict__ word_off, int64_t n, int64_t bases, int64_t words,
+                                     int* status) {
+    if (offsets[n] != bases || word_off[n] != words) atomicMin(status, HSQ_ERR_INVALID_ARGUMENT);
+}
+
 // 2 bit: A=0 C=1 T=2 G=3 -> device codes 1, 2, 8, 4;  4 bit: the nucleotide set itself, 0 = gap
 __device__ __forceinline__ uint8_t packed_to_code(uint32_t v, int bits) {
     if (bits == 2) return (uint8_t)((0x4821u >> (4 * v)) & 0xFu);
@@ -360,6 +366,8 @@ int unpack_seqs(hsq_ctx* ctx, DevSeqsOwned* d) {
     }
     if ((rc = scan_i64(ctx, bases, n, tiles, d->offsets.as<int64_t>()))) return rc;
     if ((rc = scan_i64(ctx, words, n, tiles, d->word_off.as<int64_t>()))) return rc;
+    packed_totals_kernel<<<1, 1, 0, ctx->stream>>>(d->offsets.as<int64_t>(), d->word_off.as<int64_t>(), n, d->total, d->packed_words, d_status(ctx));
+    ctx->launches++;
     if (n > 0) {
         const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
         if (d->packed_bits == 2)
@@ -404,6 +412,7 @@ int check_packed_reads(hsq_ctx* ctx, const hsq_packed_reads* r, int64_t n, const
     if (r->n_exceptions < 0 || (r->n_exceptions > 0 && (r->bits != 2 || !r->exc_read || !r->exc_pos || !r->exc_char)))
         return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, std::string(what) + ": bad exception list");
     if (reinterpret_cast<uintptr_t>(r->data) & 3u) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, std::string(what) + ": packed data must be 4-byte aligned");
+    if (r->data_bytes < 0 || (r->data_bytes & 3) || r->n_bases < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, std::string(what) + ": bad totals");
     return HSQ_OK;
 }
 
@@ -429,11 +438,21 @@ struct PackedChunks {
     }
 };
 
-int scan_packed_chunk(hsq_ctx* ctx, const hsq_packed_pairs* pb, bool check_probes, PackedChunks* pc, int c) {
+int scan_packed_chunk(hsq_ctx* ctx, const hsq_packed_pairs* pb, bool check_probes, PackedChunks* pc, int c, bool need_read_max = true) {
     for (; pc->done <= c; pc->done++) {
         const size_t cc = (size_t)pc->done;
         const int64_t k0 = pc->starts[cc], k1 = pc->starts[cc + 1];
         const hsq_packed_reads* sides[2] = {&pb->r1, &pb->r2};
+        if (!need_read_max && !check_probes && k0 == 0 && k1 == pb->n && pb->r1.data_bytes > 0 && pb->r2.data_bytes > 0 && pb->r1.n_bases > 0 &&
+            pb->r2.n_bases > 0) {
+            // the whole batch in one piece with the caller's totals: no pass over the lengths (the device checks the totals)
+            for (int s = 0; s < 2; s++) {
+                pc->word[s][cc + 1] = sides[s]->data_bytes / 4;
+                pc->base[s][cc + 1] = sides[s]->n_bases;
+                pc->exc[s][cc + 1] = sides[s]->n_exceptions;
+            }
+            continue;
+        }
         int mx = 0;
         for (int s = 0; s < 2; s++) {
             const hsq_packed_reads* r = sides[s];
@@ -694,7 +713,7 @@ int dedup_upload_keygen_packed(hsq_ctx* ctx, const hsq_packed_pairs* pb, int u, 
     PackedChunks pc;
     pc.starts = {0, n};
     pc.init();
-    if ((rc = scan_packed_chunk(ctx, pb, false, &pc, 0))) return rc;
+    if ((rc = scan_packed_chunk(ctx, pb, false, &pc, 0, false))) return rc;
     if ((rc = stage_packed_chunk(ctx, pb, pc, 0))) return rc;
     const bool sums = pb->qsum1 && pb->qsum2;
     struct { hsq::DevBuf* d; const void* h; size_t bytes; } up[] = {

@@ -108,7 +108,7 @@ __device__ __forceinline__ int dp_column(int (&D4)[KROWS], int (&H0)[KROWS], con
         if ((r & 3) == 0) sv = pcol[(r >> 2) * DP_BLOCK];  // 4 rows of 4*sub per LDS.128, loaded just before use
         const int sub = (r & 3) == 0 ? sv.x : (r & 3) == 1 ? sv.y : (r & 3) == 2 ? sv.z : sv.w;
         const int dsub = dg + sub;
-        x = __viaddmax_s32(H0[r], sp.kh, __viaddmax_s32(vin, sp.kv, dsub));
+        x = __viaddmax_s32(vin, sp.kv, __viaddmax_s32(H0[r], sp.kh, dsub));  // only the outer max is on the row-to-row chain
         dg = D4[r];
         const int d4 = x & ~3;
         const int b1x2 = x & 2;

@@ -89,7 +89,7 @@ __device__ __forceinline__ uint32_t border2(int k, int pen_start, const ScorePar
 }
 
 // One column of one strip for both alignments.  State per row: D4[r], H0[r] as in dp_column.
-template <bool HFREE, bool VFREE, bool SLOW>
+template <bool HFREE, bool VFREE, bool SLOW, bool SAME>
 __device__ __forceinline__ uint32_t dp_column2(uint32_t (&D4)[KROWS], uint32_t (&H0)[KROWS], const int4* __restrict__ pcolA,
                                                const int4* __restrict__ pcolB, const uint32_t* __restrict__ slow, int64_t nt,
                                                uint32_t up_v0, uint32_t diag_d4, const ScoreParams2& sp, int rstar, uint2* word_out) {
@@ -106,14 +106,20 @@ __device__ __forceinline__ uint32_t dp_column2(uint32_t (&D4)[KROWS], uint32_t (
             int4 sa, sb;
             if ((r & 3) == 0) {
                 sa = pcolA[(r >> 2) * DP2_BLOCK];
-                sb = pcolB[(r >> 2) * DP2_BLOCK];
+                if (!SAME) sb = pcolB[(r >> 2) * DP2_BLOCK];
             }
             const int a = (r & 3) == 0 ? sa.x : (r & 3) == 1 ? sa.y : (r & 3) == 2 ? sa.z : sa.w;
-            const int b = (r & 3) == 0 ? sb.x : (r & 3) == 1 ? sb.y : (r & 3) == 2 ? sb.z : sb.w;
-            sub = __byte_perm((uint32_t)a, (uint32_t)b, 0x7610);  // low half from A's column, high half from B's column
+            if (SAME) {
+                sub = (uint32_t)a;  // both alignments run against the same reference: one profile column serves both halves
+            } else {
+                const int b = (r & 3) == 0 ? sb.x : (r & 3) == 1 ? sb.y : (r & 3) == 2 ? sb.z : sb.w;
+                sub = __byte_perm((uint32_t)a, (uint32_t)b, 0x7610);  // low half from A's column, high half from B's column
+            }
         }
         const uint32_t dsub = dg + sub;
-        x = __viaddmax_u16x2(H0[r], sp.kh2, __viaddmax_u16x2(vin, sp.kv2, dsub));
+        // the horizontal and diagonal candidates do not depend on the row above: only the outer max sits on the row-to-row chain
+        // (max is associative on the tie-break encoded values, so the result is the one of max(h, max(v, d)))
+        x = __viaddmax_u16x2(vin, sp.kv2, __viaddmax_u16x2(H0[r], sp.kh2, dsub));
         dg = D4[r];
         const uint32_t d4 = x & DP2_MASK_D4;
         const uint32_t b1x2 = x & DP2_MASK_B1X2;
@@ -246,7 +252,7 @@ __device__ __forceinline__ void load_strip_codes(const SeqView& q, int i0, int Q
     }
 }
 
-template <bool HFREE>
+template <bool HFREE, bool SAME>
 __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& refB, const SeqView& qryA, const SeqView& qryB,
                                           const ScoreParams2& sp, int pen_start, bool free_end, const DpScratch2& sc, int s,
                                           bool last_strip, uint32_t* final_d4) {
@@ -290,9 +296,9 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
         uint32_t xlast;
         if ((ci & 0x44u) == 0) {
             const int4* pa = prof_t + (ci & 0xFu) * (4 * DP2_BLOCK);
-            const int4* pb = prof_t + (ci >> 4) * (4 * DP2_BLOCK);
-            if (!vfree) xlast = dp_column2<HFREE, false, false>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
-            else xlast = dp_column2<HFREE, true, false>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
+            const int4* pb = SAME ? pa : prof_t + (ci >> 4) * (4 * DP2_BLOCK);
+            if (!vfree) xlast = dp_column2<HFREE, false, false, SAME>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
+            else xlast = dp_column2<HFREE, true, false, SAME>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
         } else {  // ambiguity code, N, U or gap character in a reference: this column's scores go through global scratch
             const uint32_t ca = refA.get(j - 1), cb = refB.get(j - 1);
             uint32_t* sl = sc.slow + sc.tid;
@@ -305,8 +311,8 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
                 const int vb = ((qb & cb & MATCH_MASK) != 0) ? sp.ms4o : sp.mm4o;
                 sl[r * nt] = (uint32_t)va + (uint32_t)vb * 65536u;
             }
-            if (!vfree) xlast = dp_column2<HFREE, false, true>(D4, H0, nullptr, nullptr, sl, nt, up_v0, diag_d4, sp, rstar, &w);
-            else xlast = dp_column2<HFREE, true, true>(D4, H0, nullptr, nullptr, sl, nt, up_v0, diag_d4, sp, rstar, &w);
+            if (!vfree) xlast = dp_column2<HFREE, false, true, SAME>(D4, H0, nullptr, nullptr, sl, nt, up_v0, diag_d4, sp, rstar, &w);
+            else xlast = dp_column2<HFREE, true, true, SAME>(D4, H0, nullptr, nullptr, sl, nt, up_v0, diag_d4, sp, rstar, &w);
         }
         __stcs(wordp, w);  // streamed: read back once by the traceback, must not evict the boundary rows from L2
         if (!last_strip) *browp = xlast;
@@ -322,6 +328,9 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
 }
 
 // Fills both matrices (same shape: refA.len == refB.len, qryA.len == qryB.len).  Scores S[Q][R] go to score[0], score[1].
+// SAME: refA and refB are the same sequence in the same orientation (two reads of one probe and mate): the profile column of a
+// reference position serves both halves, so the cell needs no PRMT merge and one profile load instead of two.
+template <bool SAME = false>
 __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const SeqView& qryA, const SeqView& qryB,
                                 const ScoreParams2& sp, int pen_start, int pen_end, const DpScratch2& sc, int* score) {
     const int R = refA.len, Q = qryA.len;
@@ -348,9 +357,9 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
         }
     }
     uint32_t final_d4 = 0;
-    for (int s = 0; s < n_strips - 1; s++) dp_strip2<false>(refA, refB, qryA, qryB, sp, pen_start, free_end, sc, s, false, &final_d4);
-    if (free_end) dp_strip2<true>(refA, refB, qryA, qryB, sp, pen_start, true, sc, n_strips - 1, true, &final_d4);
-    else dp_strip2<false>(refA, refB, qryA, qryB, sp, pen_start, false, sc, n_strips - 1, true, &final_d4);
+    for (int s = 0; s < n_strips - 1; s++) dp_strip2<false, SAME>(refA, refB, qryA, qryB, sp, pen_start, free_end, sc, s, false, &final_d4);
+    if (free_end) dp_strip2<true, SAME>(refA, refB, qryA, qryB, sp, pen_start, true, sc, n_strips - 1, true, &final_d4);
+    else dp_strip2<false, SAME>(refA, refB, qryA, qryB, sp, pen_start, false, sc, n_strips - 1, true, &final_d4);
     const int off = (int)DP2_BIAS + (Q + R) * sp.sb_half;
     score[0] = ((int)(final_d4 & 0xFFFFu) - off) >> 2;
     score[1] = ((int)(final_d4 >> 16) - off) >> 2;

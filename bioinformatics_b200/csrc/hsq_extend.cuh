@@ -309,7 +309,10 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes prob
 }
 
 // Stage 2, packed: two read ends of the same DP#2 shape per thread, cells as u16x2 halves (hsq_dp2.cuh).
-__global__ void __launch_bounds__(DP2_BLOCK, 5) capture2_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
+#ifndef HSQ_EXP_CTAS
+#define HSQ_EXP_CTAS 5
+#endif
+__global__ void __launch_bounds__(DP2_BLOCK, HSQ_EXP_CTAS) capture2_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
                                                              DeviceSeqs r2, const uint32_t* __restrict__ order,
                                                              const uint32_t* __restrict__ n_active_ptr, ScoreParams2 sp_user,
                                                              ScratchPool2 pool, ExtendDeviceOut out, unsigned long long* cells_total,
@@ -323,15 +326,24 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) capture2_kernel(DeviceProbes pro
         if (t - (threadIdx.x & 31) >= n_slots) break;  // whole warp leaves together
         if (t >= n_slots) continue;
         const uint2 mo = reinterpret_cast<const uint2*>(order)[t];
+#ifdef HSQ_EXPERIMENT_DUPB  // (development experiment: both halves align the same read end, so the two references are identical)
+        const int n_here = 2;
+        const int64_t ma = (int64_t)mo.x, mb = ma;
+#else
         const int n_here = (mo.y != ORDER_HOLE) ? 2 : 1;
         const int64_t ma = (int64_t)mo.x, mb = (int64_t)(n_here == 2 ? mo.y : mo.x);
+#endif
         ReadEndViews va = read_end_views(probes, probe_id, r1, r2, ma);
         ReadEndViews vb = read_end_views(probes, probe_id, r1, r2, mb);
         const int start_a = out.primer_end[ma] + 1, start_b = out.primer_end[mb] + 1;
         SeqView rwa = sub_view(va.read, start_a, va.read.len - start_a);  // read[e+1 .. L-1] (:210)
         SeqView rwb = sub_view(vb.read, start_b, vb.read.len - start_b);
         int score[2];
-        dp_fill2(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score);  // :211
+#ifdef HSQ_EXPERIMENT_SAMEREF
+        dp_fill2<true>(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score);  // :211
+#else
+        dp_fill2<false>(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score);  // :211
+#endif
         const int score_a = score[0], score_b = score[1];
         cells += (int64_t)va.capture.len * rwa.len * n_here;
 #pragma unroll 1

@@ -300,6 +300,10 @@ typedef struct hsq_packed_reads {
     const uint32_t* exc_read; /* [n_exceptions] read index, ascending */
     const uint32_t* exc_pos;  /* [n_exceptions] base position inside the read */
     const uint8_t* exc_char;  /* [n_exceptions] the ASCII character at that position */
+    /* optional totals (0 = the library adds up `len` on the host, a pass over n entries before the first copy can start): bytes of
+     * `data` (hsq_packed_bytes) and sum of len.  When given they are checked on the device (a mismatch: HSQ_ERR_INVALID_ARGUMENT). */
+    int64_t data_bytes;
+    int64_t n_bases;
 } hsq_packed_reads;
 
 /* hsq_pair_batch with packed reads.  Qualities stay bytes, laid out back to back in read order (read k at the sum of the

@@ -5,7 +5,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from bioinformatics_b200 import synth, _lib
 if os.environ.get("HSQ_B200_LIB"):
     _lib.SO_PATH = os.environ["HSQ_B200_LIB"]
-from bioinformatics_b200._lib import Context
+from bioinformatics_b200._lib import Context, HsqError
 from bioinformatics_b200.batches import ExtendResult
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 1000000
@@ -18,7 +18,10 @@ with Context(0) as ctx:
     ctx.extend_stage(pairs)
     for _ in range(3):
         ctx.extend_run(32, 64)
-    ctx.extend_fetch(out)
+    try:
+        ctx.extend_fetch(out)
+    except HsqError as e:  # experiment builds may produce wrong strings that overflow their slots: the timing is still valid
+        print("fetch:", e)
     ctx.timer_start()
     for _ in range(5):
         ctx.extend_run(32, 64)
