@@ -24,7 +24,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order",
            "hsq_ctx_create_ex", "hsq_ctx_configure", "hsq_packed_bytes", "hsq_pack_reads", "hsq_quality_sums", "hsq_unpack_reads",
            "hsq_extend_packed", "hsq_dedup_packed", "hsq_comm_unique_id", "hsq_comm_init_rank", "hsq_comm_init_all", "hsq_comm_destroy",
-           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed")
+           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed", "hsq_variable_length_uid")
 _NOT_STATUS = {"hsq_last_error": C.c_char_p, "hsq_version": C.c_char_p, "hsq_ctx_destroy": None, "hsq_packed_bytes": C.c_int64}
 
 
@@ -232,6 +232,16 @@ class Context:
         st = self.lib.hsq_align_batch(self.h, C.byref(rc), C.byref(qc), C.byref(sc), C.c_uint32(flags), C.byref(oc))
         out.finish()
         self._check(st)
+        return out
+
+    def variable_length_uid(self, reads, primers, sc=None, flags=0):
+        """hsq_variable_length_uid: per item the UID prefix length of the read, -1 where the reference returns null."""
+        reads = reads if isinstance(reads, A.SeqBatch) else A.SeqBatch.from_strings(reads)
+        primers = primers if isinstance(primers, A.SeqBatch) else A.SeqBatch.from_strings(primers)
+        sc = sc or scorer()
+        out = np.zeros(reads.n, dtype=np.int32)
+        rc, pc = reads.c(), primers.c()
+        self._check(self.lib.hsq_variable_length_uid(self.h, C.byref(rc), C.byref(pc), C.byref(sc), C.c_uint32(flags), A.ptr(out, A.i32p)))
         return out
 
     def trim_batch(self, reads, quals, first, last, three_prime=True, out=None):

@@ -283,6 +283,7 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 
 #include "hsq_capi_probes.inl"
 #include "hsq_capi_align.inl"
+#include "hsq_capi_a10.inl"
 #include "hsq_capi_extend.inl"
 #include "hsq_capi_trim.inl"
 #include "hsq_capi_dedup.inl"

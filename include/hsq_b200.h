@@ -386,6 +386,13 @@ int32_t hsq_last_spans(const hsq_ctx* ctx, float* ms4);
 /* new NeedlemanWunschGlobalAlignment(ref[k], qry[k], SimpleAlignmentScorer(scorer, flags)).getAlignmentPair() */
 int32_t hsq_align_batch(hsq_ctx* ctx, const hsq_seqs* refs, const hsq_seqs* queries, const hsq_scorer* scorer,
                         uint32_t flags, hsq_align_out* out);
+/* SAMRecordUtil.getVariableLengthUid (HSQ/utils/SAMRecordUtil.java:223-261; SURVEY row A10, dead in the CLI: allowVariableLengthUids is
+ * false, HSQ/cli/DeduplicationCli.java:120): one NeedlemanWunschGlobalAlignment(read, primer, scorer) per item; uid_len[k] = length of the
+ * read prefix in front of the first column holding a primer base, or -1 where the reference returns null (no such column, or insertions +
+ * deletions + substitutions >= primer length / 4 -- with the reference's never-incremented insertsSinceLastInsertionOrMismatch, :238-250,
+ * every non-match column counts).  The extension side passes the extension primer, the ligation side revcomp(ligation primer) (:215-217). */
+int32_t hsq_variable_length_uid(hsq_ctx* ctx, const hsq_seqs* reads, const hsq_seqs* primers, const hsq_scorer* scorer, uint32_t flags,
+                                int32_t* uid_len);
 /* FastqReadTrimmer.trim(String,String,int,int,boolean) (HSQ/process/FastqReadTrimmer.java:309-328) per read.
  * out_offsets gets n+1 entries; out_seq/out_qual must hold the input's total bytes. */
 int32_t hsq_trim_batch(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals, int32_t first_base_to_keep,

@@ -490,6 +490,25 @@ int32_t hsqo_index_of_first_match_in_reference(const char* ref, const char* qry)
     Scorer sc;
     return index_of_first_match_in_reference(nw_align(encode_string(ref), encode_string(qry), sc).pair);
 }
+// SAMRecordUtil.getVariableLengthUid (HSQ/utils/SAMRecordUtil.java:223-261): length of the UID prefix, -1 for null.
+// insertsSinceLastInsertionOrMismatch is never incremented in the reference (:238-250), so every deletion column counts.
+int32_t hsqo_variable_length_uid(const char* read, const char* primer, const hsq_scorer* scorer, uint32_t flags) {
+    Scorer sc;
+    sc.match = scorer->match; sc.mismatch = scorer->mismatch; sc.gap_extend = scorer->gap_extend; sc.gap_start = scorer->gap_start;
+    sc.penalize_start = (flags & 1u) != 0; sc.penalize_end = (flags & 2u) != 0;
+    const seq_t p = encode_string(primer);
+    NwResult r = nw_align(encode_string(read), p, sc);
+    int uid_end = index_of_first_match_in_reference(r.pair);
+    int ins = 0, del = 0, sub = 0;
+    for (char ch : expanded_cigar(r.pair)) {
+        if (ch == 'X') sub++;
+        else if (ch == 'I') ins++;
+        else if (ch == 'D') del++;
+    }
+    const int edit = ins + del + sub, cutoff = (int)p.size() / 4;
+    if (edit >= cutoff) uid_end = -1;
+    return uid_end;
+}
 int32_t hsqo_cigar_edit_distance(const char* ref, const char* qry) {
     Scorer sc;
     return cigar_edit_distance(expanded_cigar(nw_align(encode_string(ref), encode_string(qry), sc).pair));

@@ -36,7 +36,7 @@ def lib():
         _lib.hsqo_last_error.restype = C.c_char_p
         for name in ("hsqo_align_batch", "hsqo_trim_batch", "hsqo_dedup_batch", "hsqo_extend_batch",
                      "hsqo_resolve_multi_probe", "hsqo_primer_end", "hsqo_index_of_first_match_in_reference",
-                     "hsqo_cigar_edit_distance", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs", "hsqo_assign_probes",
+                     "hsqo_cigar_edit_distance", "hsqo_variable_length_uid", "hsqo_md_trimmed_with_full_cigar", "hsqo_merge_pairs", "hsqo_assign_probes",
                      "hsqo_extend_records", "hsqo_find_candidates", "hsqo_index_fastq", "hsqo_trim_fastq", "hsqo_index_sam", "hsqo_coordinate_order", "hsqo_sam_mapped_records", "hsqo_join_names"):
             getattr(_lib, name).restype = C.c_int32
     return _lib
@@ -225,6 +225,13 @@ def primer_end(primer, read):
     w = C.c_double(0)
     r = lib().hsqo_primer_end(primer.encode(), read.encode(), C.byref(w))
     return (None if r == A.HSQ_PRIMER_NOT_FOUND else r), w.value
+
+
+def variable_length_uid(read, primer, sc=None, flags=0):
+    """SAMRecordUtil.getVariableLengthUid: length of the UID prefix of `read`, None where the reference returns null."""
+    sc = sc or scorer()
+    r = lib().hsqo_variable_length_uid(read.encode(), primer.encode(), C.byref(sc), C.c_uint32(flags))
+    return None if r < 0 else r
 
 
 def index_of_first_match_in_reference(ref, qry):

@@ -423,3 +423,32 @@ def tie_break(r1, r2, probes, ext_uid_len, lig_uid_len):
                 best = {k}
                 lowest, most = edit, m
     return (next(iter(best)) if len(best) == 1 else -1), ms, es
+
+
+# ---- A10: HSQ/utils/SAMRecordUtil.java:223-261 ------------------------------------------------------------------------------------
+def variable_length_uid(read, primer, sc=None):
+    """getVariableLengthUid: the read prefix in front of the first primer-aligned column, None where the reference returns null.
+    (insertsSinceLastInsertionOrMismatch is never incremented there, :238-250: every deletion column counts against the cutoff.)"""
+    sc = sc or Scorer()
+    _, ra, qa = needleman_wunsch(codes(read), codes(primer), sc)
+    end = -1
+    for i, ch in enumerate(qa):  # getIndexOfFirstMatchInReference reads the QUERY alignment (:412-428)
+        if not matches(ch, GAP):
+            end = i
+            break
+    uid = read[:end] if end >= 0 else None
+    ins = dele = sub = 0
+    since = 0
+    for ch in AlignmentPair(ra, qa).expanded_cigar():
+        if ch == "X":
+            sub += 1
+            since = 0
+        elif ch == "I":
+            ins += 1
+            since = 0
+        elif ch == "D":
+            dele += 1
+    dele -= since
+    if ins + dele + sub >= len(codes(primer)) // 4:
+        uid = None
+    return uid
