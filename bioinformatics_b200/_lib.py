@@ -24,7 +24,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order",
            "hsq_ctx_create_ex", "hsq_ctx_configure", "hsq_packed_bytes", "hsq_pack_reads", "hsq_quality_sums", "hsq_unpack_reads",
            "hsq_extend_packed", "hsq_dedup_packed", "hsq_comm_unique_id", "hsq_comm_init_rank", "hsq_comm_init_all", "hsq_comm_destroy",
-           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed", "hsq_variable_length_uid")
+           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed", "hsq_variable_length_uid", "hsq_align_scores_noalloc")
 _NOT_STATUS = {"hsq_last_error": C.c_char_p, "hsq_version": C.c_char_p, "hsq_ctx_destroy": None, "hsq_packed_bytes": C.c_int64}
 
 
@@ -233,6 +233,15 @@ class Context:
         out.finish()
         self._check(st)
         return out
+
+    def align_scores_noalloc(self, d_ref_data, d_ref_offsets, ref_bytes, d_qry_data, d_qry_offsets, qry_bytes, n, max_ref_len, max_qry_len,
+                             d_score, d_n_cols, d_matches, d_mismatches, d_status, sc=None, flags=0):
+        """hsq_align_scores_noalloc: every d_* argument is a DEVICE address (int); the call allocates nothing."""
+        sc = sc or scorer()
+        v = C.c_void_p
+        self._check(self.lib.hsq_align_scores_noalloc(self.h, v(d_ref_data), v(d_ref_offsets), C.c_int64(ref_bytes), v(d_qry_data), v(d_qry_offsets),
+                                                      C.c_int64(qry_bytes), C.c_int64(n), C.c_int32(max_ref_len), C.c_int32(max_qry_len), C.byref(sc),
+                                                      C.c_uint32(flags), v(d_score), v(d_n_cols), v(d_matches), v(d_mismatches), v(d_status)))
 
     def variable_length_uid(self, reads, primers, sc=None, flags=0):
         """hsq_variable_length_uid: per item the UID prefix length of the read, -1 where the reference returns null."""

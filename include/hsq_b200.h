@@ -677,6 +677,29 @@ int32_t hsq_dedup_extend_sharded(hsq_ctx* ctx, const hsq_pair_batch* pairs, int3
 int32_t hsq_dedup_extend_multi_gpu(hsq_ctx** ctxs, int32_t n, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len,
                                    int32_t extend_duplicates, hsq_dedup_extend_out* outs);
 
+/* ---- an entry point that allocates nothing -------------------------------------------------------------------------------------- */
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The DP of hsq_align_batch -- one
+ * NeedlemanWunschGlobalAlignment(ref[k], qry[k], SimpleAlignmentScorer(scorer, flags)) per item -- with scalar results only:
+ * getAlignmentScore, alignment length, getNumberOfMatches, getNumberOfMismatches.  Unlike every other entry point it calls no
+ * cudaMalloc / cudaFree / allocating routine: its scratch (encoded inputs, pointer words, boundary rows) is one 64 MiB file-scope
+ * __device__ array that every GPU loading the library holds until the process exits.
+ *   - ALL data pointers are DEVICE pointers owned by the caller: ASCII bases (ragged, offsets[0] = 0, offsets[n] = *_bytes), four
+ *     int32 outputs of n entries, and one int32 status word (0 = ok, else the HSQ_ERR_* code of the first problem found on the device:
+ *     HSQ_ERR_BAD_CHARACTER, or HSQ_ERR_INVALID_ARGUMENT for offsets that disagree with *_bytes / a sequence longer than declared).
+ *   - limits (beyond them the call returns HSQ_ERR_UNSUPPORTED and launches nothing): ref_bytes, qry_bytes <=
+ *     HSQ_NOALLOC_MAX_BYTES_PER_SIDE; (max_ref_len + 1) * (ceil(max_qry_len / 16) + 1) <= HSQ_NOALLOC_MAX_WORDS (160 x 160 bases fit).
+ *   - the scratch array is shared by all calls on a GPU and keeps the last call's contents (nothing in it needs clearing; the status
+ *     word is cleared by the call).  Calls that overlap on the same GPU -- two contexts, two threads -- race on it: serialise them.
+ *   - the first call on a device looks the array's address up (cudaGetSymbolAddress, which may load the module): make one warm-up call
+ *     before any region that forbids it.  The call returns after synchronising the context's stream. */
+#define HSQ_NOALLOC_MAX_BYTES_PER_SIDE (4 << 20)
+#define HSQ_NOALLOC_MAX_WORDS 1792
+int32_t hsq_align_scores_noalloc(hsq_ctx* ctx, const uint8_t* d_ref_data, const int64_t* d_ref_offsets, int64_t ref_bytes,
+                                 const uint8_t* d_qry_data, const int64_t* d_qry_offsets, int64_t qry_bytes, int64_t n, int32_t max_ref_len,
+                                 int32_t max_qry_len, const hsq_scorer* scorer, uint32_t flags, int32_t* d_score, int32_t* d_n_cols,
+                                 int32_t* d_matches, int32_t* d_mismatches, int32_t* d_status);
+
 /* ---- measurement helpers ------------------------------------------------------------------- */
 /* CUDA-event stopwatch on the context's stream (the stream every kernel of this library is launched on). */
 int32_t hsq_timer_start(hsq_ctx* ctx);
