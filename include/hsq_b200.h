@@ -400,6 +400,10 @@ int32_t hsq_trim_batch(hsq_ctx* ctx, const hsq_seqs* reads, const uint8_t* quals
                        int64_t* out_offsets);
 /* FilterByUid.reduceReadsByProbeAndUid + findBestData over every probe of the batch at once
  * (HSQ/process/FilterByUid.java:71-203,281-297).  is_best[k]=1: pair k represents its (probe,UID) group. */
+/* Accelerated domain of the UID: upper-case A/C/G/T only, at most 32 bases in total.  The reference groups by the raw UID string
+ * (FilterByUid.java:134-147), so "acgt" and "ACGT" are different groups there; the caller has already dropped pairs with an N / n
+ * (…Identification.java:815-821).  A UID with any other byte -- a lower-case base included -- is REFUSED with HSQ_ERR_UNSUPPORTED rather than
+ * grouped differently from the reference; a read shorter than its UID is HSQ_ERR_OUT_OF_RANGE (String.substring throws there). */
 int32_t hsq_dedup_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len,
                         uint8_t* is_best, int32_t* group_size, hsq_probe_stats* stats);
 /* ExtendReadsToPrimer.extendReadsToPrimers (HSQ/process/ExtendReadsToPrimer.java:347-380) for a batch that

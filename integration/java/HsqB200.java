@@ -17,7 +17,8 @@ import static java.lang.foreign.ValueLayout.*;
 public final class HsqB200 implements AutoCloseable {
 
     public static final int HSQ_OK = 0, ERR_INVALID_ARGUMENT = -1, ERR_CUDA = -2, ERR_NO_DEVICE = -3, ERR_BAD_CHARACTER = -4,
-            ERR_UNSUPPORTED = -5, ERR_OUT_OF_RANGE = -6, ERR_OVERFLOW = -7;
+            ERR_UNSUPPORTED = -5, ERR_OUT_OF_RANGE = -6, ERR_OVERFLOW = -7, ERR_NAME_MISMATCH = -8, ERR_NOT_TRIMMED = -9, ERR_NO_MATCHES = -10,
+            ERR_MALFORMED = -11;
     public static final int PRIMER_NOT_FOUND = -2147483647;
 
     private static final Linker LINKER = Linker.nativeLinker();
@@ -57,12 +58,35 @@ public final class HsqB200 implements AutoCloseable {
             ADDRESS.withName("common"), ADDRESS.withName("overflow"));
     static final StructLayout DEDUP_EXTEND_OUT = MemoryLayout.structLayout(ADDRESS.withName("is_best"), ADDRESS.withName("group_size"),
             ADDRESS.withName("stats"), ADDRESS.withName("unique_unable_to_extend"), ADDRESS.withName("duplicate_unable_to_extend"),
-            JAVA_LONG.withName("n_extended"), ADDRESS.withName("extended_pair"), ADDRESS.withName("extend"));
+            JAVA_LONG.withName("n_extended"), ADDRESS.withName("extended_pair"), ADDRESS.withName("extend"), ADDRESS.withName("extend_pooled"));
     static final StructLayout RECORD_OUT = MemoryLayout.structLayout(ADDRESS.withName("flag"), ADDRESS.withName("mate_pos"),
             ADDRESS.withName("offsets"), ADDRESS.withName("seq"), ADDRESS.withName("qual"));
     static final StructLayout MERGE_BATCH = MemoryLayout.structLayout(JAVA_LONG.withName("n"), ADDRESS.withName("negative_strand"),
             SEQS.withName("up"), SEQS.withName("down"), ADDRESS.withName("up_qual"), ADDRESS.withName("down_qual"),
             ADDRESS.withName("up_start"), ADDRESS.withName("down_start"));
+
+    static final StructLayout ALIGN_OUT = MemoryLayout.structLayout(JAVA_INT.withName("cols_cap"), JAVA_INT.withName("md_cap"),
+            ADDRESS.withName("score"), ADDRESS.withName("n_cols"), ADDRESS.withName("ref_aln"), ADDRESS.withName("qry_aln"), ADDRESS.withName("ops"),
+            ADDRESS.withName("first_q"), ADDRESS.withName("last_q"), ADDRESS.withName("first_r"), ADDRESS.withName("last_r"),
+            ADDRESS.withName("matches"), ADDRESS.withName("mismatches"), ADDRESS.withName("non_terminal_gaps"), ADDRESS.withName("edit_distance"),
+            ADDRESS.withName("md_len"), ADDRESS.withName("md"), ADDRESS.withName("rmd_len"), ADDRESS.withName("rmd"), ADDRESS.withName("overflow"),
+            JAVA_LONG.withName("cells"), ADDRESS.withName("find_counts"));
+    static final StructLayout PACKED_READS = MemoryLayout.structLayout(JAVA_INT.withName("bits"), MemoryLayout.paddingLayout(4), JAVA_LONG.withName("n"),
+            ADDRESS.withName("data"), ADDRESS.withName("len"), JAVA_LONG.withName("n_exceptions"), ADDRESS.withName("exc_read"),
+            ADDRESS.withName("exc_pos"), ADDRESS.withName("exc_char"), JAVA_LONG.withName("data_bytes"), JAVA_LONG.withName("n_bases"));
+    static final StructLayout PACKED_PAIRS = MemoryLayout.structLayout(JAVA_LONG.withName("n"), ADDRESS.withName("probe_id"), ADDRESS.withName("read_index"),
+            PACKED_READS.withName("r1"), PACKED_READS.withName("r2"), ADDRESS.withName("q1"), ADDRESS.withName("q2"), ADDRESS.withName("qsum1"),
+            ADDRESS.withName("qsum2"));
+    static final StructLayout EXTEND_POOLED_OUT = MemoryLayout.structLayout(JAVA_INT.withName("cigar_cap"), JAVA_INT.withName("md_cap"),
+            ADDRESS.withName("ok"), ADDRESS.withName("primer_end"), ADDRESS.withName("score"), ADDRESS.withName("pos"), ADDRESS.withName("read_start"),
+            ADDRESS.withName("read_stop"), ADDRESS.withName("nm"), ADDRESS.withName("tlen"), ADDRESS.withName("cigar_len"), ADDRESS.withName("md_len"),
+            ADDRESS.withName("str_off"), ADDRESS.withName("pool"), JAVA_LONG.withName("pool_cap"), JAVA_LONG.withName("pool_bytes"),
+            ADDRESS.withName("pair_ok"), JAVA_LONG.withName("cells"));
+    static final StructLayout CONFIG = MemoryLayout.structLayout(JAVA_INT.withName("struct_bytes"), JAVA_INT.withName("force_dp32"),
+            JAVA_INT.withName("force_dedup_radix"), JAVA_INT.withName("extend_chunks"), JAVA_INT.withName("uniform_chunks"), JAVA_INT.withName("band"));
+    static final StructLayout DEDUP_KEY = MemoryLayout.structLayout(JAVA_LONG.withName("uid"), JAVA_LONG.withName("rank"), JAVA_INT.withName("probe"),
+            JAVA_INT.withName("origin"));
+    public static final int COMM_ID_BYTES = 128, ALIGN_PENALIZE_START = 1, ALIGN_PENALIZE_END = 2;
 
     // ---- downcall handles --------------------------------------------------------------------------------------------
     private static final MethodHandle CTX_CREATE = fn("hsq_ctx_create", FunctionDescriptor.of(JAVA_INT, JAVA_INT, ADDRESS));
@@ -106,8 +130,58 @@ public final class HsqB200 implements AutoCloseable {
     private static final MethodHandle RESOLVE = fn("hsq_resolve_multi_probe", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
             JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
 
+    // operator seam, packed batches, multi-GPU, configuration, measurement
+    private static final MethodHandle ALIGN = fn("hsq_align_batch", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS, JAVA_INT, ADDRESS));
+    private static final MethodHandle VARIABLE_LENGTH_UID = fn("hsq_variable_length_uid", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS,
+            JAVA_INT, ADDRESS));
+    private static final MethodHandle CTX_CREATE_EX = fn("hsq_ctx_create_ex", FunctionDescriptor.of(JAVA_INT, JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle CTX_CONFIGURE = fn("hsq_ctx_configure", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle VERSION = fn("hsq_version", FunctionDescriptor.of(ADDRESS));
+    private static final MethodHandle PACKED_BYTES = fn("hsq_packed_bytes", FunctionDescriptor.of(JAVA_LONG, ADDRESS, JAVA_LONG, JAVA_INT));
+    private static final MethodHandle PACK_READS = fn("hsq_pack_reads", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG,
+            ADDRESS, ADDRESS, ADDRESS, ADDRESS, JAVA_INT));
+    private static final MethodHandle QUALITY_SUMS = fn("hsq_quality_sums", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS, JAVA_INT));
+    private static final MethodHandle UNPACK_READS = fn("hsq_unpack_reads", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle EXTEND_PACKED = fn("hsq_extend_packed", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle DEDUP_PACKED = fn("hsq_dedup_packed", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS,
+            ADDRESS, ADDRESS));
+    private static final MethodHandle DEDUP_EXTEND_PACKED = fn("hsq_dedup_extend_packed", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT,
+            JAVA_INT, JAVA_INT, ADDRESS));
+    private static final MethodHandle EXTEND_STAGE = fn("hsq_extend_stage", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle EXTEND_RUN = fn("hsq_extend_run", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, JAVA_INT));
+    private static final MethodHandle EXTEND_FETCH = fn("hsq_extend_fetch", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle COMM_UNIQUE_ID = fn("hsq_comm_unique_id", FunctionDescriptor.of(JAVA_INT, ADDRESS));
+    private static final MethodHandle COMM_INIT_RANK = fn("hsq_comm_init_rank", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT));
+    private static final MethodHandle COMM_INIT_ALL = fn("hsq_comm_init_all", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT));
+    private static final MethodHandle COMM_DESTROY = fn("hsq_comm_destroy", FunctionDescriptor.of(JAVA_INT, ADDRESS));
+    private static final MethodHandle DEDUP_SHARDED = fn("hsq_dedup_sharded", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS,
+            ADDRESS, ADDRESS));
+    private static final MethodHandle DEDUP_EXTEND_SHARDED = fn("hsq_dedup_extend_sharded", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT,
+            JAVA_INT, JAVA_INT, ADDRESS));
+    private static final MethodHandle DEDUP_EXTEND_MULTI_GPU = fn("hsq_dedup_extend_multi_gpu", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_INT, ADDRESS,
+            JAVA_INT, JAVA_INT, JAVA_INT, ADDRESS));
+    private static final MethodHandle DEDUP_KEYS = fn("hsq_dedup_keys", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, JAVA_LONG,
+            JAVA_INT, ADDRESS));
+    private static final MethodHandle DEDUP_REDUCE_KEYS = fn("hsq_dedup_reduce_keys", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, JAVA_INT,
+            ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle ALIGN_SCORES_NOALLOC = fn("hsq_align_scores_noalloc", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS,
+            JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG, JAVA_LONG, JAVA_INT, JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle LAST_TIMING = fn("hsq_last_timing", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle LAST_SPANS = fn("hsq_last_spans", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle TIMER_START = fn("hsq_timer_start", FunctionDescriptor.of(JAVA_INT, ADDRESS));
+    private static final MethodHandle TIMER_STOP = fn("hsq_timer_stop", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle INT32_PEAK = fn("hsq_int32_peak", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_DOUBLE, ADDRESS));
+
     private final Arena arena = Arena.ofShared();
     private final MemorySegment ctx;
+
+    /** Context with a configuration (hsq_ctx_create_ex); config = CONFIG layout or MemorySegment.NULL. */
+    public HsqB200(int device, MemorySegment config) {
+        MemorySegment out = arena.allocate(ADDRESS);
+        int st = invokeInt(CTX_CREATE_EX, device, config, out);
+        if (st != HSQ_OK) throw new HsqException(st, lastError(MemorySegment.NULL));
+        ctx = out.get(ADDRESS, 0);
+    }
 
     public HsqB200(int device) {
         MemorySegment out = arena.allocate(ADDRESS);
@@ -244,6 +318,189 @@ public final class HsqB200 implements AutoCloseable {
                      MemorySegment outSeq, MemorySegment outQual, MemorySegment outOffsets) {
         check(invokeInt(TRIM, ctx, reads, quals, firstBaseToKeep, lastBaseToKeep, threePrime ? 1 : 0, outSeq, outQual, outOffsets));
     }
+
+    // ---- operator seam --------------------------------------------------------------------------------------------------
+    /** One NeedlemanWunschGlobalAlignment per item (COMMON/alignment/NeedlemanWunschGlobalAlignment.java:44,57,85); alignOut = hsq_align_out.
+     *  GpuNeedlemanWunschGlobalAlignment reads a row of it through the reference's getters. */
+    public void alignBatch(MemorySegment refs, MemorySegment queries, MemorySegment scorer, int flags, MemorySegment alignOut) {
+        check(invokeInt(ALIGN, ctx, refs, queries, scorer, flags, alignOut));
+    }
+
+    /** SAMRecordUtil.getVariableLengthUid per item (HSQ/utils/SAMRecordUtil.java:223-261); uidLen[k] = prefix length or -1 for null. */
+    public void variableLengthUid(MemorySegment reads, MemorySegment primers, MemorySegment scorer, int flags, MemorySegment uidLen) {
+        check(invokeInt(VARIABLE_LENGTH_UID, ctx, reads, primers, scorer, flags, uidLen));
+    }
+
+    // ---- configuration ---------------------------------------------------------------------------------------------------
+    /** hsq_config: forceDp32 / forceDedupRadix / extendChunks / uniformChunks / band (0 = defaults). */
+    public void configure(int forceDp32, int forceDedupRadix, int extendChunks, int uniformChunks, int band) {
+        MemorySegment c = arena.allocate(CONFIG);
+        int[] v = {(int) CONFIG.byteSize(), forceDp32, forceDedupRadix, extendChunks, uniformChunks, band};
+        for (int k = 0; k < v.length; k++) c.set(JAVA_INT, 4L * k, v[k]);
+        check(invokeInt(CTX_CONFIGURE, ctx, c));
+    }
+
+    public static String version() {
+        try {
+            return ((MemorySegment) VERSION.invoke()).reinterpret(256).getString(0, StandardCharsets.ISO_8859_1);
+        } catch (Throwable t) {
+            throw new IllegalStateException(t);
+        }
+    }
+
+    // ---- packed read batches (2 / 4 bit per base) ---------------------------------------------------------------------------
+    /** Bytes hsq_pack_reads writes for a ragged batch with these offsets. */
+    public static long packedBytes(MemorySegment offsets, long n, int bits) {
+        try {
+            return (long) PACKED_BYTES.invoke(offsets, n, bits);
+        } catch (Throwable t) {
+            throw new IllegalStateException(t);
+        }
+    }
+
+    /** Host helper of the library: ASCII batch -> packed words + lengths + (2 bit) exception list; returns the status (ERR_OVERFLOW: more
+     *  exceptions than excCap, nExceptions says how many). */
+    public static int packReads(MemorySegment reads, int bits, MemorySegment dataOut, MemorySegment lenOut, long excCap, MemorySegment nExceptions,
+                                MemorySegment excRead, MemorySegment excPos, MemorySegment excChar, int threads) {
+        return invokeInt(PACK_READS, reads, bits, dataOut, lenOut, excCap, nExceptions, excRead, excPos, excChar, threads);
+    }
+
+    /** (short) sum(q - 33) per read, BamFileUtil.getQualityScore (HSQ/utils/BamFileUtil.java:74-85). */
+    public static void qualitySums(MemorySegment quals, MemorySegment offsets, long n, MemorySegment out, int threads) {
+        int st = invokeInt(QUALITY_SUMS, quals, offsets, n, out, threads);
+        if (st != HSQ_OK) throw new HsqException(st, lastError(MemorySegment.NULL));
+    }
+
+    public void unpackReads(MemorySegment packedReads, MemorySegment outData, MemorySegment outOffsets) {
+        check(invokeInt(UNPACK_READS, ctx, packedReads, outData, outOffsets));
+    }
+
+    /** extendReadsToPrimers for a packed batch, CIGAR / MD pooled; packedPairs = hsq_packed_pairs, pooledOut = hsq_extend_pooled_out. */
+    public void extendPacked(MemorySegment packedPairs, MemorySegment pooledOut) { check(invokeInt(EXTEND_PACKED, ctx, packedPairs, pooledOut)); }
+
+    public void dedupPacked(MemorySegment packedPairs, int extUidLen, int ligUidLen, MemorySegment isBest, MemorySegment groupSize,
+                            MemorySegment probeStats) {
+        check(invokeInt(DEDUP_PACKED, ctx, packedPairs, extUidLen, ligUidLen, isBest, groupSize, probeStats));
+    }
+
+    /** The probe task for a packed batch (results in dedupExtendOut.extend_pooled); sharded: collective over this context's communicator. */
+    public void dedupExtendPacked(MemorySegment packedPairs, int extUidLen, int ligUidLen, boolean extendDuplicates, boolean sharded,
+                                  MemorySegment dedupExtendOut) {
+        check(invokeInt(DEDUP_EXTEND_PACKED, ctx, packedPairs, extUidLen, ligUidLen, extendDuplicates ? 1 : 0, sharded ? 1 : 0, dedupExtendOut));
+    }
+
+    // ---- resident batch: stage once, run, fetch ----------------------------------------------------------------------------
+    public void extendStage(MemorySegment pairBatch) { check(invokeInt(EXTEND_STAGE, ctx, pairBatch)); }
+
+    public void extendRun(int cigarCap, int mdCap) { check(invokeInt(EXTEND_RUN, ctx, cigarCap, mdCap)); }
+
+    public void extendFetch(MemorySegment extendOut) { check(invokeInt(EXTEND_FETCH, ctx, extendOut)); }
+
+    // ---- multi-GPU: the exchange runs inside the library over NCCL ----------------------------------------------------------
+    /** One JVM that owns n GPUs (the reference's shape: probe tasks fanned out from one process, …Identification.java:836-846):
+     *  pairs[k] / outs[k] (arrays of hsq_pair_batch / hsq_dedup_extend_out) belong to contexts[k]. */
+    public static void dedupExtendMultiGpu(HsqB200[] contexts, MemorySegment pairBatches, int extUidLen, int ligUidLen, boolean extendDuplicates,
+                                           MemorySegment dedupExtendOuts) {
+        try (Arena a = Arena.ofConfined()) {
+            MemorySegment handles = a.allocate(ADDRESS, contexts.length);
+            for (int k = 0; k < contexts.length; k++) handles.setAtIndex(ADDRESS, k, contexts[k].ctx);
+            int st = invokeInt(DEDUP_EXTEND_MULTI_GPU, handles, contexts.length, pairBatches, extUidLen, ligUidLen, extendDuplicates ? 1 : 0, dedupExtendOuts);
+            if (st != HSQ_OK) {
+                StringBuilder msg = new StringBuilder();
+                for (HsqB200 c : contexts) msg.append(lastError(c.ctx)).append(" | ");
+                throw new HsqException(st, msg.toString());
+            }
+        }
+    }
+
+    /** Communicator over the contexts of this process (rank k = contexts[k]); dedupExtendMultiGpu does this on first use. */
+    public static void commInitAll(HsqB200[] contexts) {
+        try (Arena a = Arena.ofConfined()) {
+            MemorySegment handles = a.allocate(ADDRESS, contexts.length);
+            for (int k = 0; k < contexts.length; k++) handles.setAtIndex(ADDRESS, k, contexts[k].ctx);
+            int st = invokeInt(COMM_INIT_ALL, handles, contexts.length);
+            if (st != HSQ_OK) throw new HsqException(st, lastError(contexts[0].ctx));
+        }
+    }
+
+    /** One process per GPU: rank 0 makes the id (COMM_ID_BYTES bytes), the host program hands it to the others, every rank joins. */
+    public static byte[] commUniqueId() {
+        try (Arena a = Arena.ofConfined()) {
+            MemorySegment id = a.allocate(COMM_ID_BYTES);
+            int st = invokeInt(COMM_UNIQUE_ID, id);
+            if (st != HSQ_OK) throw new HsqException(st, lastError(MemorySegment.NULL));
+            return id.toArray(JAVA_BYTE);
+        }
+    }
+
+    public void commInitRank(byte[] id, int rank, int world) {
+        MemorySegment seg = arena.allocate(COMM_ID_BYTES);
+        seg.copyFrom(MemorySegment.ofArray(id));
+        check(invokeInt(COMM_INIT_RANK, ctx, seg, rank, world));
+    }
+
+    public void commDestroy() { check(invokeInt(COMM_DESTROY, ctx)); }
+
+    /** Collective: FilterByUid over the union of all ranks' pairs; answers for this rank's pairs, counters of the whole batch. */
+    public void dedupSharded(MemorySegment pairBatch, int extUidLen, int ligUidLen, MemorySegment isBest, MemorySegment groupSize,
+                             MemorySegment probeStats) {
+        check(invokeInt(DEDUP_SHARDED, ctx, pairBatch, extUidLen, ligUidLen, isBest, groupSize, probeStats));
+    }
+
+    public void dedupExtendSharded(MemorySegment pairBatch, int extUidLen, int ligUidLen, boolean extendDuplicates, MemorySegment dedupExtendOut) {
+        check(invokeInt(DEDUP_EXTEND_SHARDED, ctx, pairBatch, extUidLen, ligUidLen, extendDuplicates ? 1 : 0, dedupExtendOut));
+    }
+
+    /** The two halves of the sharded dedup for a host that runs its own exchange (device memory in / out). */
+    public void dedupKeys(MemorySegment pairBatch, int extUidLen, int ligUidLen, long nProbes, int originBase, MemorySegment deviceKeysOut) {
+        check(invokeInt(DEDUP_KEYS, ctx, pairBatch, extUidLen, ligUidLen, nProbes, originBase, deviceKeysOut));
+    }
+
+    public void dedupReduceKeys(MemorySegment deviceKeys, long n, int uidLen, MemorySegment deviceIsBest, MemorySegment deviceGroupSize,
+                                MemorySegment probeStats) {
+        check(invokeInt(DEDUP_REDUCE_KEYS, ctx, deviceKeys, n, uidLen, deviceIsBest, deviceGroupSize, probeStats));
+    }
+
+    /** The alignment DP on caller-owned DEVICE buffers without any allocation inside the library (no counterpart in the reference). */
+    public void alignScoresNoAlloc(MemorySegment dRefData, MemorySegment dRefOffsets, long refBytes, MemorySegment dQryData, MemorySegment dQryOffsets,
+                                   long qryBytes, long n, int maxRefLen, int maxQryLen, MemorySegment scorer, int flags, MemorySegment dScore,
+                                   MemorySegment dNCols, MemorySegment dMatches, MemorySegment dMismatches, MemorySegment dStatus) {
+        check(invokeInt(ALIGN_SCORES_NOALLOC, ctx, dRefData, dRefOffsets, refBytes, dQryData, dQryOffsets, qryBytes, n, maxRefLen, maxQryLen, scorer, flags,
+                dScore, dNCols, dMatches, dMismatches, dStatus));
+    }
+
+    // ---- measurement -----------------------------------------------------------------------------------------------------
+    /** Device time (ms) and kernel launches of the last batch call. */
+    public float[] lastTiming() {
+        MemorySegment ms = arena.allocate(JAVA_FLOAT), n = arena.allocate(JAVA_INT);
+        check(invokeInt(LAST_TIMING, ctx, ms, n));
+        return new float[] {ms.get(JAVA_FLOAT, 0), n.get(JAVA_INT, 0)};
+    }
+
+    /** Kernel-only spans (ms) of the last batch call; -1 where it has none. */
+    public float[] lastSpans() {
+        MemorySegment ms = arena.allocate(JAVA_FLOAT, 4);
+        check(invokeInt(LAST_SPANS, ctx, ms));
+        return ms.toArray(JAVA_FLOAT);
+    }
+
+    public void timerStart() { check(invokeInt(TIMER_START, ctx)); }
+
+    public float timerStop() {
+        MemorySegment ms = arena.allocate(JAVA_FLOAT);
+        check(invokeInt(TIMER_STOP, ctx, ms));
+        return ms.get(JAVA_FLOAT, 0);
+    }
+
+    public double int32Peak(double seconds) {
+        MemorySegment v = arena.allocate(JAVA_DOUBLE);
+        check(invokeInt(INT32_PEAK, ctx, seconds, v));
+        return v.get(JAVA_DOUBLE, 0);
+    }
+
+    MemorySegment handle() { return ctx; }
+
+    Arena arena() { return arena; }
 
     private static int invokeInt(MethodHandle h, Object... args) {
         try {

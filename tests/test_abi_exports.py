@@ -26,6 +26,17 @@ def test_library_exports_every_declared_function():
     assert set(_lib.EXPORTS) == set(names)
 
 
+def test_every_export_has_a_java_handle():
+    """integration/java/HsqB200.java (the reference-side binding, Panama FFM) binds every function the header declares."""
+    java = open(os.path.join(ROOT, "integration", "java", "HsqB200.java")).read()
+    bound = set(re.findall(r'fn\("(hsq_[a-z0-9_]+)"', java))
+    missing = [n for n in _declared() if n not in bound]
+    assert not missing, "no Java downcall handle for %s" % missing
+    # the operator seam and the two batch seams exist as source
+    for f in ("GpuNeedlemanWunschGlobalAlignment.java", "HsqBatcher.java", "FilterByUidGpu.java", "ExtendReadsToPrimerGpu.java"):
+        assert os.path.exists(os.path.join(ROOT, "integration", "java", f)), f
+
+
 def test_struct_sizes():
     assert C.sizeof(A.Scorer) == 16
     assert C.sizeof(A.Seqs) == 24
