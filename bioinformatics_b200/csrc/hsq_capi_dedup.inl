@@ -11,46 +11,77 @@
 #include "hsq_scan.cuh"
 namespace hsq {
 
+// bytes [lo, hi) of a 16-byte chunk kept, the others zeroed (0 <= lo <= hi <= 16)
+__device__ __forceinline__ uint32_t keep_bytes(uint32_t w, int word, int lo, int hi) {
+    const int l = min(max(lo - 4 * word, 0), 4), h = min(max(hi - 4 * word, 0), 4);
+    const uint32_t m = (h <= l) ? 0u : ((h == 4 ? 0xFFFFFFFFu : ((1u << (8 * h)) - 1u)) & (l == 4 ? 0u : (0xFFFFFFFFu << (8 * l))));
+    return w & m;
+}
+
+// sum of the bytes q[b .. e) read as aligned 16-byte chunks (q is 16-byte aligned and has 16 bytes of slack after its last byte): the
+// first and the last chunk are masked, the others go through four __vsadu4 each
+__device__ __forceinline__ int byte_sum(const uint8_t* __restrict__ q, int64_t b, int64_t e) {
+    if (e <= b) return 0;
+    const int64_t p0 = b & ~(int64_t)15;
+    int total = 0;
+    for (int64_t p = p0; p < e; p += 16) {
+        uint4 w = __ldg(reinterpret_cast<const uint4*>(q + p));
+        if (p < b || p + 16 > e) {
+            const int lo = (int)max((int64_t)0, b - p), hi = (int)min((int64_t)16, e - p);
+            w.x = keep_bytes(w.x, 0, lo, hi);
+            w.y = keep_bytes(w.y, 1, lo, hi);
+            w.z = keep_bytes(w.z, 2, lo, hi);
+            w.w = keep_bytes(w.w, 3, lo, hi);
+        }
+        total += (int)(__vsadu4(w.x, 0u) + __vsadu4(w.y, 0u) + __vsadu4(w.z, 0u) + __vsadu4(w.w, 0u));
+    }
+    return total;
+}
+
+// Key generation, one THREAD per pair.  (Up to r2_b a warp took one pair with byte loads: 240 warp instructions per pair, issue bound at
+// 0.13 of the HBM rate.  A thread that walks its own two quality strings in 16-byte chunks issues ~9 warp instructions per pair; consecutive
+// threads take consecutive pairs, so a warp still covers one contiguous stretch of each buffer.)
+//   CODES: the reads are device codes (A=1 C=2 G=4 T=8; packed batches) instead of ASCII.
+//   qs1 / qs2 non-null: the per-read quality sums come from the host (hsq_quality_sums) and the quality bytes are not touched.
+template <bool CODES>
 __global__ void dedup_keygen_kernel(const uint8_t* __restrict__ r1, const int64_t* __restrict__ off1, const uint8_t* __restrict__ q1,
                                     const uint8_t* __restrict__ r2, const int64_t* __restrict__ off2, const uint8_t* __restrict__ q2,
-                                    const int32_t* __restrict__ read_index, int64_t n, int u, int v, uint64_t* __restrict__ uid_out,
-                                    uint64_t* __restrict__ rank_out, uint32_t* __restrict__ idx_out, int* status) {
-    const int lane = threadIdx.x & 31;
-    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (; w < n; w += stride) {
-        const int64_t b1 = off1[w], b2 = off2[w];
-        const int l1 = (int)(off1[w + 1] - b1), l2 = (int)(off2[w + 1] - b2);
-        int sum = 0;  // byte loads: an aligned-word + __vsadu4 variant of these two loops measured 300 us, prefetching the next pair's offsets 216 us,
-        // against 178 us for this form at 500 k pairs (profiles/README_r1.md, r1_o)
-        for (int i = lane; i < l1; i += 32) sum += (int)q1[b1 + i] - 33;
-        for (int i = lane; i < l2; i += 32) sum += (int)q2[b2 + i] - 33;
-        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        // UID bases: lane i < u reads R1[i], lane u <= i < u+v reads R2[i-u]   (u + v <= 32)
+                                    const int16_t* __restrict__ qs1, const int16_t* __restrict__ qs2, const int32_t* __restrict__ read_index,
+                                    int64_t n, int u, int v, uint64_t* __restrict__ uid_out, uint64_t* __restrict__ rank_out,
+                                    uint32_t* __restrict__ idx_out, int* status) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride) {
+        const int64_t b1 = off1[k], e1 = off1[k + 1], b2 = off2[k], e2 = off2[k + 1];
+        int sum;
+        if (qs1) sum = (int)qs1[k] + (int)qs2[k];
+        else sum = byte_sum(q1, b1, e1) + byte_sum(q2, b2, e2) - 33 * (int)((e1 - b1) + (e2 - b2));
+        // UID = R1[0:u] ++ R2[0:v], 2 bit per base, first base most significant (u + v <= 32)
         uint64_t code = 0;
-        bool bad = false, short_read = false;
-        if (lane < u + v) {
-            uint8_t ch;
-            if (lane < u) { short_read = lane >= l1; ch = short_read ? 'A' : r1[b1 + lane]; }
-            else { short_read = (lane - u) >= l2; ch = short_read ? 'A' : r2[b2 + lane - u]; }
-            switch (ch) {
-                case 'A': code = 0; break;
-                case 'C': code = 1; break;
-                case 'G': code = 2; break;
-                case 'T': code = 3; break;
-                default: bad = true;
+        bool bad = false;
+        const bool short_read = (e1 - b1) < u || (e2 - b2) < v;
+        if (!short_read) {
+#pragma unroll 1
+            for (int i = 0; i < u + v; i++) {
+                const uint8_t ch = i < u ? r1[b1 + i] : r2[b2 + i - u];
+                uint32_t c;
+                if (CODES) {  // 1, 2, 4, 8 -> 0, 1, 2, 3
+                    bad |= (ch == 0) | (ch > 8) | ((ch & (ch - 1)) != 0);
+                    c = 31u - (uint32_t)__clz((int)(ch | 1u));
+                } else {      // 'A' 'C' 'G' 'T' -> 0, 1, 2, 3 (bits 1-2 of the letter give A C T G)
+                    bad |= !(ch == 'A' || ch == 'C' || ch == 'G' || ch == 'T');
+                    const uint32_t x = (ch >> 1) & 3u;
+                    c = x ^ (x >> 1);
+                }
+                code = (code << 2) | (c & 3u);
             }
-            code <<= 2 * (u + v - 1 - lane);
         }
-        for (int o = 16; o > 0; o >>= 1) code |= __shfl_xor_sync(0xffffffffu, code, o);
-        if (__any_sync(0xffffffffu, short_read)) { if (lane == 0) atomicMin(status, HSQ_ERR_OUT_OF_RANGE); }
-        else if (__any_sync(0xffffffffu, bad)) { if (lane == 0) atomicMin(status, HSQ_ERR_UNSUPPORTED); }
-        if (lane == 0) {
-            const int16_t qsum = (int16_t)sum;  // Java short arithmetic wraps mod 2^16
-            uid_out[w] = code;
-            rank_out[w] = ((uint64_t)(uint16_t)(32767 - (int)qsum) << 32) | (uint64_t)((uint32_t)read_index[w] ^ 0x80000000u);
-            idx_out[w] = (uint32_t)w;
-        }
+        if (short_read) atomicMin(status, HSQ_ERR_OUT_OF_RANGE);
+        else if (bad) atomicMin(status, HSQ_ERR_UNSUPPORTED);
+        const int16_t qsum = (int16_t)sum;  // Java short arithmetic wraps mod 2^16
+        uid_out[k] = code;
+        rank_out[k] = ((uint64_t)(uint16_t)(32767 - (int)qsum) << 32) | (uint64_t)((uint32_t)read_index[k] ^ 0x80000000u);
+        idx_out[k] = (uint32_t)k;
     }
 }
 
@@ -151,7 +182,7 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_kernel(const uint
                                                                       uint8_t* __restrict__ is_best, int32_t* __restrict__ group_size,
                                                                       int32_t* __restrict__ unique_pairs, int32_t* __restrict__ duplicate_pairs,
                                                                       int32_t* __restrict__ max_pairs, int skip_up_to,
-                                                                      const uint32_t* __restrict__ tie) {
+                                                                      const uint32_t* __restrict__ tie, const int32_t* __restrict__ seg_probe) {
     extern __shared__ __align__(16) unsigned char dedup_smem[];
     // per pair: its UID and its table slot; per table slot (2 x cap of them): claiming pair + 1, best rank, best pair, pairs
     uint64_t* s_uid = reinterpret_cast<uint64_t*>(dedup_smem);
@@ -222,9 +253,16 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_kernel(const uint
         }
         __syncthreads();
         if (tid == 0) {  // FilterByUid.java:149-171,251
-            unique_pairs[p] = s_groups;
-            duplicate_pairs[p] = m - s_groups;
-            max_pairs[p] = s_max;
+            if (seg_probe) {  // this segment is one UID-hash bucket of a split probe: the probe's counters add up over its buckets
+                const int pr = seg_probe[p];
+                atomicAdd(&unique_pairs[pr], s_groups);
+                atomicAdd(&duplicate_pairs[pr], m - s_groups);
+                atomicMax(&max_pairs[pr], s_max);
+            } else {
+                unique_pairs[p] = s_groups;
+                duplicate_pairs[p] = m - s_groups;
+                max_pairs[p] = s_max;
+            }
         }
         __syncthreads();
     }
@@ -237,7 +275,8 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_small_kernel(cons
                                                                             const uint64_t* __restrict__ uid, const uint64_t* __restrict__ rank,
                                                                             uint8_t* __restrict__ is_best, int32_t* __restrict__ group_size,
                                                                             int32_t* __restrict__ unique_pairs, int32_t* __restrict__ duplicate_pairs,
-                                                                            int32_t* __restrict__ max_pairs, const uint32_t* __restrict__ tie) {
+                                                                            int32_t* __restrict__ max_pairs, const uint32_t* __restrict__ tie,
+                                                                            const int32_t* __restrict__ seg_probe) {
     __shared__ uint64_t s_rank[DEDUP_SEG_BLOCK / 32][32];
     __shared__ uint32_t s_idx[DEDUP_SEG_BLOCK / 32][32];
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -278,12 +317,56 @@ __global__ void __launch_bounds__(DEDUP_SEG_BLOCK) dedup_group_small_kernel(cons
         const int groups = __popc(__ballot_sync(0xffffffffu, leader));
         for (int o = 16; o > 0; o >>= 1) size = max(size, __shfl_xor_sync(0xffffffffu, size, o));
         if (lane == 0) {  // FilterByUid.java:149-171,251
-            unique_pairs[p] = groups;
-            duplicate_pairs[p] = m - groups;
-            max_pairs[p] = size;
+            if (seg_probe) {
+                const int pr = seg_probe[p];
+                atomicAdd(&unique_pairs[pr], groups);
+                atomicAdd(&duplicate_pairs[pr], m - groups);
+                atomicMax(&max_pairs[pr], size);
+            } else {
+                unique_pairs[p] = groups;
+                duplicate_pairs[p] = m - groups;
+                max_pairs[p] = size;
+            }
         }
         __syncwarp();  // the shared rows are rewritten by the next probe
     }
+}
+
+// ---- probes with more pairs than a block's table takes (a hot amplicon, or a small panel: 5 M pairs on 1 k probes is 5 k pairs per
+// probe) are split into UID-hash buckets: all pairs of one UID land in one bucket, so every bucket is a segment the two group kernels
+// above reduce on their own, and the probe's counters add up over its buckets (unique = sum, largest group = max).
+static constexpr int DEDUP_BUCKET_TARGET = 1024;  // expected pairs per bucket (the table takes 4096: room for an uneven hash)
+
+// buckets[p] = 1 for a probe a block can take, else the power of two >= pairs / DEDUP_BUCKET_TARGET
+__global__ void dedup_bucket_count_kernel(const int32_t* __restrict__ cnt, int64_t np, int64_t* __restrict__ buckets) {
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; p < np; p += stride) {
+        int64_t b = 1;
+        if (cnt[p] > DEDUP_SEG_MAX)
+            while (b * DEDUP_BUCKET_TARGET < cnt[p]) b <<= 1;
+        buckets[p] = b;
+    }
+}
+
+// virtual segment of every pair = first bucket of its probe + hash(UID) mod buckets; seg_probe[] maps a virtual segment back to its probe
+__global__ void dedup_bucket_key_kernel(const int32_t* __restrict__ probe, const uint64_t* __restrict__ uid, int64_t n, const int64_t* __restrict__ vbase,
+                                        int32_t* __restrict__ vseg) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; i < n; i += stride) {
+        const int p = probe[i];
+        const int64_t b0 = vbase[p], nb = vbase[p + 1] - b0;
+        const uint64_t h = (uid[i] ^ (uid[i] >> 31)) * 0xD6E8FEB86659FD93ull;  // not the multiplier of the in-block table
+        vseg[i] = (int32_t)(b0 + (int64_t)((h >> 40) & (uint64_t)(nb - 1)));
+    }
+}
+
+__global__ void dedup_bucket_probe_kernel(const int64_t* __restrict__ vbase, int64_t np, int32_t* __restrict__ seg_probe) {
+    int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; p < np; p += stride)
+        for (int64_t b = vbase[p]; b < vbase[p + 1]; b++) seg_probe[b] = (int32_t)p;
 }
 
 // key columns <-> 24-byte key records (hsq_dedup_key) for the multi-GPU exchange
@@ -368,14 +451,14 @@ int dedup_upload_keygen(hsq_ctx* ctx, const hsq_pair_batch* pb, int u, int v, in
     HSQ_CUDA(ctx, ctx->sort_b.ensure(nn * 8 + 16));   // keys ping
     HSQ_CUDA(ctx, ctx->sort_d.ensure(nn * 8 + 16));   // idx ping | idx pong (2 x u32)
     if (n > 0) {
-        const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        const int kblocks = (int)std::min<int64_t>((n + 127) / 128, (int64_t)ctx->sm_count * 16);
         span_begin(ctx, 0);
         check_probe_ids_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, np > 0 ? np : INT32_MAX, d_status(ctx));
-        dedup_keygen_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), ctx->q1.as<uint8_t>(),
-                                                            ctx->r2.ascii.as<uint8_t>(), ctx->r2.offsets.as<int64_t>(), ctx->q2.as<uint8_t>(),
-                                                            ctx->read_index.as<int32_t>(), n, u, v, ctx->sort_a.as<uint64_t>(),
-                                                            ctx->sort_b.as<uint64_t>(), ctx->sort_d.as<uint32_t>(), d_status(ctx));
+        dedup_keygen_kernel<false><<<kblocks, 128, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), ctx->q1.as<uint8_t>(),
+                                                                   ctx->r2.ascii.as<uint8_t>(), ctx->r2.offsets.as<int64_t>(), ctx->q2.as<uint8_t>(), nullptr,
+                                                                   nullptr, ctx->read_index.as<int32_t>(), n, u, v, ctx->sort_a.as<uint64_t>(),
+                                                                   ctx->sort_b.as<uint64_t>(), ctx->sort_d.as<uint32_t>(), d_status(ctx));
         span_end(ctx, 0);
         ctx->launches += 2;
         int w[1];
@@ -441,25 +524,59 @@ int dedup_reduce_device_impl(hsq_ctx* ctx, int64_t n, int64_t np, int uid_len, u
         int w[9];
         if ((rc = read_status(ctx, w, 9))) return rc;
         const int max_count = w[8];
-        if (max_count <= DEDUP_SEG_MAX) {
+        // scatter the pair indexes into their segments and reduce every segment: one warp per small segment, one block per larger one
+        auto reduce_segments = [&](const int32_t* seg_of_pair, const int64_t* seg_start, int64_t n_seg, int seg_max, const int32_t* seg_probe) -> int {
             int cap = 32;
-            while (cap < max_count) cap <<= 1;
+            while (cap < seg_max) cap <<= 1;
             const size_t smem = (size_t)cap * 52 + 16;
             HSQ_CUDA(ctx, cudaFuncSetAttribute(dedup_group_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             int per_sm = 1;
             HSQ_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dedup_group_kernel, DEDUP_SEG_BLOCK, smem));
-            const int sblocks = (int)std::max<int64_t>(1, std::min<int64_t>(np, (int64_t)ctx->sm_count * std::max(per_sm, 1)));
-            dedup_scatter_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, start, ia, ib);
-            const int wblocks = (int)std::max<int64_t>(1, std::min<int64_t>((np + 7) / 8, (int64_t)ctx->sm_count * 8));
-            dedup_group_small_kernel<<<wblocks, DEDUP_SEG_BLOCK, 0, ctx->stream>>>(ib, start, np, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np, tie);
+            const int sblocks = (int)std::max<int64_t>(1, std::min<int64_t>(n_seg, (int64_t)ctx->sm_count * std::max(per_sm, 1)));
+            dedup_scatter_kernel<<<gblocks, 256, 0, ctx->stream>>>(seg_of_pair, n, seg_start, ia, ib);
+            const int wblocks = (int)std::max<int64_t>(1, std::min<int64_t>((n_seg + 7) / 8, (int64_t)ctx->sm_count * 8));
+            dedup_group_small_kernel<<<wblocks, DEDUP_SEG_BLOCK, 0, ctx->stream>>>(ib, seg_start, n_seg, uid, ka, d_best, d_gs, d_stats, d_stats + np,
+                                                                                   d_stats + 2 * np, tie, seg_probe);
             ctx->launches += 2;
-            if (max_count > DEDUP_SMALL_MAX) {
-                dedup_group_kernel<<<sblocks, DEDUP_SEG_BLOCK, smem, ctx->stream>>>(ib, start, np, cap, uid, ka, d_best, d_gs, d_stats, d_stats + np, d_stats + 2 * np,
-                                                                                   DEDUP_SMALL_MAX, tie);
+            if (seg_max > DEDUP_SMALL_MAX) {
+                dedup_group_kernel<<<sblocks, DEDUP_SEG_BLOCK, smem, ctx->stream>>>(ib, seg_start, n_seg, cap, uid, ka, d_best, d_gs, d_stats, d_stats + np,
+                                                                                   d_stats + 2 * np, DEDUP_SMALL_MAX, tie, seg_probe);
                 ctx->launches++;
             }
             HSQ_CUDA(ctx, cudaGetLastError());
             return HSQ_OK;
+        };
+        if (max_count <= DEDUP_SEG_MAX) return reduce_segments(ctx->probe_id.as<int32_t>(), start, np, max_count, nullptr);
+        if (uid_len > 0) {
+            // some probe holds more pairs than a block takes: split those probes into UID-hash buckets and reduce the buckets
+            dedup_bucket_count_kernel<<<pblocks, 256, 0, ctx->stream>>>(cnt, np, cnt64);
+            ctx->launches++;
+            if ((rc = scan_i64(ctx, cnt64, np, tiles, start))) return rc;  // start: first bucket of every probe from here on
+            int64_t* h_nv = reinterpret_cast<int64_t*>(ctx->h_cells) + 5;
+            HSQ_CUDA(ctx, cudaMemcpyAsync(h_nv, start + np, 8, cudaMemcpyDeviceToHost, ctx->stream));
+            HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            const int64_t nv = *h_nv;
+            const size_t nvs = (size_t)nv;
+            const int64_t v_tiles = (nv + 1 + SCAN_TILE - 1) / SCAN_TILE;
+            HSQ_CUDA(ctx, ctx->dd_vseg.ensure(nvs * 8 + (nvs + 1) * 16 + (size_t)v_tiles * 8 + 64));
+            int64_t* vcnt64 = ctx->dd_vseg.as<int64_t>();
+            int64_t* vstart = vcnt64 + nvs + 1;
+            int64_t* vtiles = vstart + nvs + 1;
+            int32_t* vcnt = reinterpret_cast<int32_t*>(vtiles + v_tiles);
+            int32_t* seg_probe = vcnt + nvs;
+            int32_t* vseg = reinterpret_cast<int32_t*>(kb);  // the radix path's second key buffer is free here
+            HSQ_CUDA(ctx, cudaMemsetAsync(vcnt, 0, nvs * 4, ctx->stream));
+            HSQ_CUDA(ctx, cudaMemsetAsync(d_max, 0, 4, ctx->stream));
+            const int vblocks = (int)std::max<int64_t>(1, std::min<int64_t>((nv + 255) / 256, (int64_t)ctx->sm_count * 8));
+            dedup_bucket_key_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), uid, n, start, vseg);
+            dedup_bucket_probe_kernel<<<pblocks, 256, 0, ctx->stream>>>(start, np, seg_probe);
+            dedup_probe_hist_kernel<<<gblocks, 256, 0, ctx->stream>>>(vseg, n, vcnt, ia);
+            dedup_seg_prepare_kernel<<<vblocks, 256, 0, ctx->stream>>>(vcnt, nv, vcnt64, d_max);
+            ctx->launches += 4;
+            if ((rc = scan_i64(ctx, vcnt64, nv, vtiles, vstart))) return rc;
+            if ((rc = read_status(ctx, w, 9))) return rc;
+            if (w[8] <= DEDUP_SEG_MAX) return reduce_segments(vseg, vstart, nv, w[8], seg_probe);
+            // one UID group alone (or a very uneven hash) exceeds a block's table: the radix path takes the batch
         }
         dedup_iota_kernel<<<gblocks, 256, 0, ctx->stream>>>(ia, n);  // the radix path wants the pair indexes back in ia
         ctx->launches++;

@@ -221,6 +221,18 @@ def test_dedup_segment_and_radix_paths(ctx):
     cases.append(("ties", ties, 60, 3, 0))
     cases.append(("no uid", base.head(3000), 60, 0, 0))
     cases.append(("one pair", base.head(1), 60, 5, 1))
+    # oversized probes are split into UID-hash buckets; what a bucket cannot hold either falls back to the radix path:
+    nouid_hot = base.subset(np.arange(6000))
+    nouid_hot.probe_id[:] = 3
+    cases.append(("no uid, one probe above a block's table", nouid_hot, 60, 0, 0))
+    one_group = base.subset(np.arange(6000))
+    one_group.probe_id[:] = 9
+    one_group.r1.data.reshape(6000, -1)[:, :5] = np.frombuffer(b"ACGTA", dtype=np.uint8)
+    one_group.r2.data.reshape(6000, -1)[:, :1] = ord("C")
+    cases.append(("one UID group above a block's table", one_group, 60, 5, 1))
+    small_panel = base.subset(np.arange(base.n))
+    small_panel.probe_id[:] = rng.integers(0, 4, size=base.n)  # every probe oversized (7.5 k pairs each): all of them split
+    cases.append(("every probe split", small_panel, 60, 5, 1))
     expected = {name: O.dedup_batch(pb, u, v, npr) for name, pb, npr, u, v in cases}
     for name, pb, npr, u, v in cases:
         _dedup_equal(ctx.dedup_batch(pb, u, v, npr), expected[name])
