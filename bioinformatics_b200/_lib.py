@@ -24,7 +24,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order",
            "hsq_ctx_create_ex", "hsq_ctx_configure", "hsq_packed_bytes", "hsq_pack_reads", "hsq_quality_sums", "hsq_unpack_reads",
            "hsq_extend_packed", "hsq_dedup_packed", "hsq_comm_unique_id", "hsq_comm_init_rank", "hsq_comm_init_all", "hsq_comm_destroy",
-           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed", "hsq_variable_length_uid", "hsq_align_scores_noalloc")
+           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed", "hsq_variable_length_uid", "hsq_align_scores_noalloc", "hsq_band_stats")
 _NOT_STATUS = {"hsq_last_error": C.c_char_p, "hsq_version": C.c_char_p, "hsq_ctx_destroy": None, "hsq_packed_bytes": C.c_int64}
 
 
@@ -198,6 +198,12 @@ class Context:
         ms, n = C.c_float(0), C.c_int32(0)
         self.lib.hsq_last_timing(self.h, C.byref(ms), C.byref(n))
         return ms.value, n.value
+
+    def band_stats(self):
+        """hsq_band_stats: (read ends aligned inside the band, of them redone with full matrices) of the last extend call."""
+        a, b = C.c_int64(0), C.c_int64(0)
+        self.lib.hsq_band_stats(self.h, C.byref(a), C.byref(b))
+        return int(a.value), int(b.value)
 
     def last_spans(self):
         """hsq_last_spans: kernel-only device times (ms) of the last call's kernel groups; None where the call has no such span."""

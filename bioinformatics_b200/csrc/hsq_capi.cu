@@ -46,10 +46,10 @@ void span_end(hsq_ctx* ctx, int k) {
 
 int reset_status(hsq_ctx* ctx) {
     HSQ_CUDA(ctx, ctx->status.ensure(64));
-    HSQ_CUDA(ctx, ctx->cells.ensure(64));
+    HSQ_CUDA(ctx, ctx->cells.ensure(128));
     // words 0..2 (error, max lengths) always; word 3 (slot overflow) and the cell counter only at the start of a call
     HSQ_CUDA(ctx, cudaMemsetAsync(ctx->status.p, 0, ctx->keep_counters ? 12 : 64, ctx->stream));
-    if (!ctx->keep_counters) HSQ_CUDA(ctx, cudaMemsetAsync(ctx->cells.p, 0, 64, ctx->stream));
+    if (!ctx->keep_counters) HSQ_CUDA(ctx, cudaMemsetAsync(ctx->cells.p, 0, 128, ctx->stream));
     return HSQ_OK;
 }
 
@@ -156,7 +156,7 @@ static int ctx_init(hsq_ctx* ctx, const cudaDeviceProp& prop) {
         HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ctx->ev_out[k], cudaEventDisableTiming));
     }
     HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_status, 64));
-    HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_cells, 64));
+    HSQ_CUDA(nullptr, cudaMallocHost((void**)&ctx->h_cells, 128));
     std::vector<double> tbl(POW95_N);
     for (int d = 0; d < POW95_N; d++) tbl[(size_t)d] = std::pow(0.95, (double)d);
     HSQ_CUDA(nullptr, cudaMemcpyToSymbol(c_pow95, tbl.data(), sizeof(double) * POW95_N));
@@ -221,6 +221,7 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     for (auto* b : bufs) b->release();
     for (auto& b : ctx->ing) b.release();
     ctx->dd_seg.release();
+    ctx->dd_vseg.release();
     hsq::DevSeqsOwned* seqs[] = {&ctx->p_ext, &ctx->p_lig, &ctx->p_target, &ctx->p_full, &ctx->r1, &ctx->r2, &ctx->sa, &ctx->sb, &ctx->alt_r1, &ctx->alt_r2, &ctx->fs};
     for (auto* s : seqs) s->release();
     for (auto& ps : ctx->parked) {
@@ -269,6 +270,13 @@ int32_t hsq_set_scorer(hsq_ctx* ctx, const hsq_scorer* scorer) {
 int32_t hsq_last_spans(const hsq_ctx* ctx, float* ms4) {
     if (!ctx || !ms4) return HSQ_ERR_INVALID_ARGUMENT;
     for (int k = 0; k < hsq_ctx::N_SPANS; k++) ms4[k] = ctx->span_ms[k];
+    return HSQ_OK;
+}
+
+int32_t hsq_band_stats(const hsq_ctx* ctx, int64_t* banded, int64_t* redone) {
+    if (!ctx) return HSQ_ERR_INVALID_ARGUMENT;
+    if (banded) *banded = ctx->band_stats[0];
+    if (redone) *redone = ctx->band_stats[1];
     return HSQ_OK;
 }
 

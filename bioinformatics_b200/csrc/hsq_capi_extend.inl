@@ -51,7 +51,30 @@ struct ExtendPlan {
     uint8_t* pair_ok = nullptr;
     unsigned long long* cells = nullptr;
     unsigned long long* work = nullptr;
+    // banded capture stage (hsq_config.band > 0 and the packed kernel runs): what the second, full pass needs to sort again
+    int band = 0;
+    BucketKeys keys{};
+    uint32_t* hist = nullptr;
+    uint32_t* cursor = nullptr;
+    uint32_t* n_active_w = nullptr;
+    uint32_t* order_w = nullptr;
+    int n_keys = 0;
+    size_t order_bytes = 0;
+    int sblocks = 1;
 };
+
+// counting sort of the 2n keys in keys.key into `order` (buckets padded to even sizes); *n_active = entries before the skip bucket
+int bucket_sort_launch(hsq_ctx* ctx, const BucketKeys& keys, int64_t n2, int nk, uint32_t* hist, uint32_t* cursor, uint32_t* n_active,
+                       uint32_t* order, size_t order_bytes, int sblocks) {
+    HSQ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t)nk * 4, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemsetAsync(order, 0xFF, order_bytes, ctx->stream));
+    bucket_hist_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, n2, hist);
+    bucket_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist, nk, cursor);
+    HSQ_CUDA(ctx, cudaMemcpyAsync(n_active, cursor + keys.skip_key, 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    bucket_scatter_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, n2, cursor, order);
+    ctx->launches += 3;
+    return HSQ_OK;
+}
 
 // prep: encode + primer DP + the two bucket sorts of the staged batch, on ctx->stream.
 // host_read_max < 0: the longest read and the probe-id check come from the device (one synchronisation);
@@ -145,16 +168,10 @@ int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, Exte
         unsigned long long* cells = ctx->cells.as<unsigned long long>();
         unsigned long long* work = cells + 1 + 2 * ctx->work_slot;
         const int sblocks = (int)std::min<int64_t>((2 * n + 255) / 256, (int64_t)ctx->sm_count * 8);
-        // counting sort of the keys in keys.key into `order` (padded buckets); n_active = entries before the skip bucket
         auto bucket_sort = [&](int nk, uint32_t skip_key) -> int {
-            HSQ_CUDA(ctx, cudaMemsetAsync(hist, 0, (size_t)nk * 4, ctx->stream));
-            HSQ_CUDA(ctx, cudaMemsetAsync(order, 0xFF, order_bytes, ctx->stream));
-            bucket_hist_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, 2 * n, hist);
-            bucket_scan_kernel<<<1, 1024, 0, ctx->stream>>>(hist, nk, cursor);
-            HSQ_CUDA(ctx, cudaMemcpyAsync(n_active, cursor + skip_key, 4, cudaMemcpyDeviceToDevice, ctx->stream));
-            bucket_scatter_kernel<<<sblocks, 256, 0, ctx->stream>>>(keys.key, 2 * n, cursor, order);
-            ctx->launches += 3;
-            return HSQ_OK;
+            BucketKeys k = keys;
+            k.skip_key = skip_key;
+            return bucket_sort_launch(ctx, k, 2 * n, nk, hist, cursor, n_active, order, order_bytes, sblocks);
         };
         if (packed1) {
             primer_key_kernel<<<sblocks, 256, 0, ctx->stream>>>(pv, pid, v1, v2, n, keys1);
@@ -178,6 +195,20 @@ int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, Exte
         plan->n_active = n_active;
         plan->cells = cells;
         plan->work = work;
+        plan->keys = keys;
+        plan->hist = hist;
+        plan->cursor = cursor;
+        plan->n_active_w = n_active;
+        plan->order_w = order;
+        plan->n_keys = n_keys;
+        plan->order_bytes = order_bytes;
+        plan->sblocks = sblocks;
+    }
+    // the band applies to the packed capture kernel only, and only when an uncomputed cell has a representable value
+    plan->band = 0;
+    if (packed2 && ctx->cfg.band > 0) {
+        sp_user2.neg2 = dp2_band_neg(ctx->scorer.match, ctx->scorer.mismatch, ctx->scorer.gap_extend, ctx->scorer.gap_start, q_max, r_max) * DP2_REP;
+        if (sp_user2.neg2) plan->band = ctx->cfg.band;
     }
     plan->n = n;
     plan->packed2 = packed2;
@@ -194,7 +225,17 @@ int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, Exte
 // capture: the capture-target DP of the read ends that passed the primer stage + the per-pair finalize, on ctx->stream
 int extend_capture(hsq_ctx* ctx, const ExtendPlan& p) {
     if (p.n > 0) {
-        if (p.packed2)
+        if (p.packed2 && p.band > 0) {
+            // pass 1: banded; the read ends it accepts move to the skip bucket.  pass 2: the others, full matrices.
+            capture2_band_kernel<<<p.grid2, DP2_BLOCK, 0, ctx->stream>>>(p.pv, p.pid, p.v1, p.v2, p.order, p.n_active, p.sp_user2, p.pool2, p.d, p.cells,
+                                                                        p.work + 1, p.band, p.keys, p.cells + BAND_STATS_SLOT);
+            ctx->launches++;
+            HSQ_CUDA(ctx, cudaGetLastError());
+            int rc = bucket_sort_launch(ctx, p.keys, 2 * p.n, p.n_keys, p.hist, p.cursor, p.n_active_w, p.order_w, p.order_bytes, p.sblocks);
+            if (rc) return rc;
+            HSQ_CUDA(ctx, cudaMemsetAsync(p.work + 1, 0, 8, ctx->stream));
+            capture2_kernel<<<p.grid2, DP2_BLOCK, 0, ctx->stream>>>(p.pv, p.pid, p.v1, p.v2, p.order, p.n_active, p.sp_user2, p.pool2, p.d, p.cells, p.work + 1);
+        } else if (p.packed2)
             capture2_kernel<<<p.grid2, DP2_BLOCK, 0, ctx->stream>>>(p.pv, p.pid, p.v1, p.v2, p.order, p.n_active, p.sp_user2, p.pool2, p.d, p.cells, p.work + 1);
         else
             capture_kernel<<<p.grid2, DP_BLOCK, 0, ctx->stream>>>(p.pv, p.pid, p.v1, p.v2, p.order, p.n_active, p.sp_user, p.pool, p.d, p.cells);
@@ -239,11 +280,13 @@ int extend_fetch_copies(hsq_ctx* ctx, hsq_extend_out* o) {
 // fetch, part 2: cell counter and status of everything run since the counters were last reset (synchronises)
 int extend_counters(hsq_ctx* ctx, int64_t* cells_out) {
     int rc;
-    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->h_cells, ctx->cells.p, (BAND_STATS_SLOT + 2) * 8, cudaMemcpyDeviceToHost, ctx->stream));
     int w[4];
     if ((rc = read_status(ctx, w, 4))) return rc;
     if (ctx->io && ctx->io != ctx->stream) HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->io));
     *cells_out = (int64_t)ctx->h_cells[0];
+    ctx->band_stats[0] = (int64_t)ctx->h_cells[BAND_STATS_SLOT];
+    ctx->band_stats[1] = (int64_t)ctx->h_cells[BAND_STATS_SLOT + 1];
     if (w[0] != 0) return fail(ctx, w[0], std::string("hsq_extend: ") + status_message(w[0]));
     if (w[3] != 0) return fail(ctx, HSQ_ERR_OVERFLOW, std::string("hsq_extend: ") + status_message(HSQ_ERR_OVERFLOW));
     return HSQ_OK;

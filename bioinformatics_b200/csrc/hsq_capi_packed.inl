@@ -650,58 +650,6 @@ extern "C" int32_t hsq_unpack_reads(hsq_ctx* ctx, const hsq_packed_reads* reads,
 }
 
 // ---- hsq_dedup_packed: FilterByUid key generation from a packed batch ----------------------------------------------------------
-namespace hsq {
-
-// One warp per pair, as dedup_keygen_kernel, reading device codes (A=1 C=2 G=4 T=8) instead of ASCII.  qs1 / qs2 non-null: the
-// per-read quality sums come from the host (hsq_quality_sums) and the quality bytes are not touched.
-__global__ void dedup_keygen_codes_kernel(const uint8_t* __restrict__ c1, const int64_t* __restrict__ off1, const uint8_t* __restrict__ q1,
-                                          const uint8_t* __restrict__ c2, const int64_t* __restrict__ off2, const uint8_t* __restrict__ q2,
-                                          const int16_t* __restrict__ qs1, const int16_t* __restrict__ qs2, const int32_t* __restrict__ read_index,
-                                          int64_t n, int u, int v, uint64_t* __restrict__ uid_out, uint64_t* __restrict__ rank_out,
-                                          uint32_t* __restrict__ idx_out, int* status) {
-    const int lane = threadIdx.x & 31;
-    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int64_t stride = ((int64_t)gridDim.x * blockDim.x) >> 5;
-    for (; w < n; w += stride) {
-        const int64_t b1 = off1[w], b2 = off2[w];
-        const int l1 = (int)(off1[w + 1] - b1), l2 = (int)(off2[w + 1] - b2);
-        int sum = 0;
-        if (qs1) {
-            sum = (int)qs1[w] + (int)qs2[w];
-        } else {
-            for (int i = lane; i < l1; i += 32) sum += (int)q1[b1 + i] - 33;
-            for (int i = lane; i < l2; i += 32) sum += (int)q2[b2 + i] - 33;
-            for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        }
-        uint64_t code = 0;
-        bool bad = false, short_read = false;
-        if (lane < u + v) {
-            uint8_t c;
-            if (lane < u) { short_read = lane >= l1; c = short_read ? 1 : c1[b1 + lane]; }
-            else { short_read = (lane - u) >= l2; c = short_read ? 1 : c2[b2 + lane - u]; }
-            switch (c) {
-                case 1: code = 0; break;
-                case 2: code = 1; break;
-                case 4: code = 2; break;
-                case 8: code = 3; break;
-                default: bad = true;
-            }
-            code <<= 2 * (u + v - 1 - lane);
-        }
-        for (int o = 16; o > 0; o >>= 1) code |= __shfl_xor_sync(0xffffffffu, code, o);
-        if (__any_sync(0xffffffffu, short_read)) { if (lane == 0) atomicMin(status, HSQ_ERR_OUT_OF_RANGE); }
-        else if (__any_sync(0xffffffffu, bad)) { if (lane == 0) atomicMin(status, HSQ_ERR_UNSUPPORTED); }
-        if (lane == 0) {
-            const int16_t qsum = (int16_t)sum;
-            uid_out[w] = code;
-            rank_out[w] = ((uint64_t)(uint16_t)(32767 - (int)qsum) << 32) | (uint64_t)((uint32_t)read_index[w] ^ 0x80000000u);
-            idx_out[w] = (uint32_t)w;
-        }
-    }
-}
-
-}  // namespace hsq
-
 namespace {
 
 // host -> device copies of a packed pair batch, unpack, key generation: uid -> sort_a, rank -> sort_b, pair index -> sort_d[0..n)
@@ -730,11 +678,11 @@ int dedup_upload_keygen_packed(hsq_ctx* ctx, const hsq_packed_pairs* pb, int u, 
     HSQ_CUDA(ctx, ctx->sort_b.ensure(nn * 8 + 16));
     HSQ_CUDA(ctx, ctx->sort_d.ensure(nn * 8 + 16));
     if (n > 0) {
-        const int blocks = (int)std::min<int64_t>((n * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
         const int gblocks = (int)std::min<int64_t>((n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        const int kblocks = (int)std::min<int64_t>((n + 127) / 128, (int64_t)ctx->sm_count * 16);
         span_begin(ctx, 0);
         check_probe_ids_kernel<<<gblocks, 256, 0, ctx->stream>>>(ctx->probe_id.as<int32_t>(), n, np > 0 ? np : INT32_MAX, d_status(ctx));
-        dedup_keygen_codes_kernel<<<blocks, 256, 0, ctx->stream>>>(
+        dedup_keygen_kernel<true><<<kblocks, 128, 0, ctx->stream>>>(
             ctx->r1.codes.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(), ctx->q1.as<uint8_t>(), ctx->r2.codes.as<uint8_t>(), ctx->r2.offsets.as<int64_t>(),
             ctx->q2.as<uint8_t>(), sums ? ctx->q1.as<int16_t>() : nullptr, sums ? ctx->q2.as<int16_t>() : nullptr, ctx->read_index.as<int32_t>(), n, u, v,
             ctx->sort_a.as<uint64_t>(), ctx->sort_b.as<uint64_t>(), ctx->sort_d.as<uint32_t>(), d_status(ctx));

@@ -39,6 +39,8 @@ struct ScoreParams2 {
     int ms4o, mm4o;           // 4*match + SB, 4*mismatch + SB  (both in [0, 65535])
     int sb_half;              // SB/2, a multiple of 4
     int gap_start;
+    uint32_t neg2;            // banded fill only: the value of a cell that is not computed, replicated (0 = band not available)
+    int match, gap_extend;    // raw scores (the acceptance test of the banded kernel)
 };
 
 inline ScoreParams2 make_score_params2(const ScoreParams& s) {
@@ -55,6 +57,9 @@ inline ScoreParams2 make_score_params2(const ScoreParams& s) {
     p.ms4o = s.ms4 + sb;
     p.mm4o = s.mm4 + sb;
     p.gap_start = s.gap_start;
+    p.neg2 = 0;
+    p.match = s.ms4 / 4;
+    p.gap_extend = s.gap_extend;
     return p;
 }
 
@@ -67,6 +72,37 @@ inline bool dp2_score_range_ok(int match, int mismatch, int gap_extend, int gap_
     const int64_t bound = span * (m + 1);       // |score| of any cell or candidate
     const int64_t offset = span * (2 * m + 4);  // (i + j) * SB/2 with SB <= 4*m + 7
     return 4 * (bound + 2 * m + 2) + 3 + offset < 32768;
+}
+
+// Banded fill (opt-in, hsq_config.band): a cell outside the computed staircase reads as NEG, one constant for the whole matrix.
+// With m = the largest |score| of the scorer and span = Q + R + the padding rows:
+//   - every computed cell has a computed predecessor and a step costs at most m, so its score is >= -m * span (free start gaps:
+//     the borders are 0), i.e. its X' is >= 0x8000 + offset(i, j) - 4*m*span;
+//   - a chain of steps from a NEG cell gains at most 4*m per unit of (i + j) on top of the position offset, and never loses (a
+//     diagonal step adds 4*sub + SB >= 0), so a NEG-derived X' stays inside [NEG, NEG + offset(i, j) + 4*m*span];
+//   so with NEG = 0x8000 - 8*m*span - margin a candidate derived from NEG loses against every candidate derived from computed cells,
+//   and with NEG >= margin no candidate formed from it wraps below zero (a wrapped half would win every max).
+// Returns 0 when the two cannot both hold, or when the scorer is not of the shape the acceptance test of the banded kernel assumes
+// (match > 0 and gapStart <= gapExtend <= 0): the caller then fills full matrices.
+inline uint32_t dp2_band_neg(int match, int mismatch, int gap_extend, int gap_start, int q_max, int r_max) {
+    if (match <= 0 || gap_extend > 0 || gap_start > gap_extend) return 0;
+    int64_t m = 1;
+    for (int v : {match, mismatch, gap_extend, gap_start}) m = std::max<int64_t>(m, v < 0 ? -(int64_t)v : v);
+    const int64_t span = (int64_t)q_max + KROWS + r_max + 4;
+    const int64_t neg = 32768 - 8 * m * span - 16 * m - 16;
+    if (neg < 16 * m + 16) return 0;
+    return (uint32_t)neg & ~3u;  // pointer bits clear
+}
+
+// The staircase a banded fill computes: strip s (rows 16s+1 .. 16s+16) covers the columns [lo, hi]; the last strip runs to R because
+// the last row's horizontal moves are free.  A traceback is accepted only while it stays on diagonals |j - i| < band, all of whose
+// predecessors lie inside the staircase.
+struct BandCols { int lo, hi; };
+__device__ __forceinline__ BandCols band_cols(int s, int band, int R, bool last_strip) {
+    BandCols c;
+    c.lo = min(R, max(1, s * KROWS + 1 - band));  // a strip below the band still computes the last column (free vertical moves)
+    c.hi = last_strip ? R : min(R, s * KROWS + KROWS + band);
+    return c;
 }
 
 struct DpScratch2 {
@@ -202,6 +238,42 @@ struct CodeWalker {
     }
 };
 
+// complement_code on the four codes of a word
+__device__ __forceinline__ uint32_t complement_codes4(uint32_t x) {
+    uint32_t t = x & 0x0F0F0F0Fu;
+    t = ((t & 0x05050505u) << 1) | ((t >> 1) & 0x05050505u);
+    t = ((t & 0x03030303u) << 2) | ((t >> 2) & 0x03030303u);
+    return t | (x & (0x01010101u * CODE_GAP));
+}
+
+// Elements e0 .. e0+15 of a view (all inside the view), element e0+m in byte m of the four words: what SeqView::get returns, 16 at a
+// time.  Reads whole aligned words around the elements (inside the slack of every code buffer).
+__device__ __forceinline__ void load_codes16(const SeqView& v, int e0, uint32_t (&w)[4]) {
+    if (v.step == 1) {
+        const uintptr_t a = reinterpret_cast<uintptr_t>(v.base + v.start + e0);
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t sh = (uint32_t)(a & 3) * 8u;
+        uint32_t x[5];
+#pragma unroll
+        for (int k = 0; k < 5; k++) x[k] = wp[k];
+#pragma unroll
+        for (int k = 0; k < 4; k++) w[k] = __funnelshift_r(x[k], x[k + 1], sh);
+    } else {  // step == -1: descending addresses, element e0+15 at the lowest
+        const uintptr_t a = reinterpret_cast<uintptr_t>(v.base + v.start - e0 - 15);
+        const uint32_t* wp = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)3);
+        const uint32_t sh = (uint32_t)(a & 3) * 8u;
+        uint32_t x[5];
+#pragma unroll
+        for (int k = 0; k < 5; k++) x[k] = wp[k];
+#pragma unroll
+        for (int k = 0; k < 4; k++) w[3 - k] = __byte_perm(__funnelshift_r(x[k], x[k + 1], sh), 0u, 0x0123);
+    }
+    if (v.comp) {
+#pragma unroll
+        for (int k = 0; k < 4; k++) w[k] = complement_codes4(w[k]);
+    }
+}
+
 // keeps a per-alignment invariant in ONE register (without it ptxas re-selects it from the two alignments at every step)
 __device__ __forceinline__ void pin(int& x) { asm volatile("" : "+r"(x)); }
 __device__ __forceinline__ void pin(uint32_t& x) { asm volatile("" : "+r"(x)); }
@@ -252,10 +324,10 @@ __device__ __forceinline__ void load_strip_codes(const SeqView& q, int i0, int Q
     }
 }
 
-template <bool HFREE, bool SAME>
+template <bool HFREE, bool SAME, bool BAND = false>
 __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& refB, const SeqView& qryA, const SeqView& qryB,
                                           const ScoreParams2& sp, int pen_start, bool free_end, const DpScratch2& sc, int s,
-                                          bool last_strip, uint32_t* final_d4) {
+                                          bool last_strip, uint32_t* final_d4, int band = 0, int n_strips = 0) {
     const int R = refA.len, Q = qryA.len;
     const int i0 = s * KROWS;
     const int rstar = last_strip ? (Q - 1 - i0) : -1;
@@ -274,17 +346,36 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
         build_profile2(qa, qb, sp, sc.prof);
     }
     uint32_t diag_d4 = (i0 == 0) ? DP2_BIAS * DP2_REP : border2(i0, pen_start, sp);
-    uint2* wordp = &sc.word(s, 1);
-    uint32_t* browp = &sc.b(1);
-    const uint8_t* cip = &sc.ci(1);
+    int jlo = 1, jhi = R;
+    if (BAND) {
+        const BandCols bc = band_cols(s, band, R, last_strip);
+        jlo = bc.lo;
+        jhi = bc.hi;
+        if (jlo > 1) {  // the column to the left of the strip's first column is not computed
+#pragma unroll
+            for (int r = 0; r < KROWS; r++) D4[r] = H0[r] = sp.neg2;
+            // the cell above-left: computed by the strip above unless that strip, too, was cut down to the last column
+            const bool above = jlo - 1 >= max(1, (s - 1) * KROWS + 1 - band);
+            diag_d4 = above ? (sc.b(jlo - 1) & DP2_MASK_D4) : sp.neg2;
+        }
+    }
+    uint2* wordp = &sc.word(s, jlo);
+    uint32_t* browp = &sc.b(jlo);
+    const uint8_t* cip = &sc.ci(jlo);
     const int64_t nt = sc.nthreads;
     const int4* prof_t = sc.prof + threadIdx.x;
-    uint32_t next_ci = *cip;
-    uint32_t next_up = *browp;
-    for (int j = 1; j <= R; j++) {
+    uint32_t next_ci = 0, next_up = 0;
+    if (!BAND || jlo <= jhi) {
+        next_ci = *cip;
+        next_up = *browp;
+    }
+#ifdef HSQ_EXPERIMENT_NO_COLUMNS  // (development experiment: what a strip costs without its columns)
+    jhi = jlo - 1;
+#endif
+    for (int j = jlo; j <= jhi; j++) {
         const uint32_t ci = next_ci;
         const uint32_t upx = next_up;
-        if (j < R) {
+        if (j < jhi) {
             cip += nt;
             next_ci = *cip;
             next_up = browp[nt];
@@ -320,6 +411,11 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
         wordp += nt;
         browp += nt;
     }
+    if (BAND && !last_strip) {
+        // the row above the next strip, to the right of this strip's last column, is not computed (browp is at column jhi + 1)
+        const int next_hi = (s + 2 == n_strips) ? R : min(R, jhi + KROWS);
+        for (int j = max(jhi, jlo - 1) + 1; j <= next_hi; j++, browp += nt) *browp = sp.neg2;
+    }
     if (last_strip) {
 #pragma unroll
         for (int r = 0; r < KROWS; r++)
@@ -330,9 +426,10 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
 // Fills both matrices (same shape: refA.len == refB.len, qryA.len == qryB.len).  Scores S[Q][R] go to score[0], score[1].
 // SAME: refA and refB are the same sequence in the same orientation (two reads of one probe and mate): the profile column of a
 // reference position serves both halves, so the cell needs no PRMT merge and one profile load instead of two.
-template <bool SAME = false>
+// BAND (free terminal gaps on both ends only: pen_start == pen_end == 0): only the staircase of band_cols is computed.
+template <bool SAME = false, bool BAND = false>
 __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const SeqView& qryA, const SeqView& qryB,
-                                const ScoreParams2& sp, int pen_start, int pen_end, const DpScratch2& sc, int* score) {
+                                const ScoreParams2& sp, int pen_start, int pen_end, const DpScratch2& sc, int* score, int band = 0) {
     const int R = refA.len, Q = qryA.len;
     if (Q == 0 || R == 0) {
         const int k = Q == 0 ? R : Q;
@@ -357,9 +454,10 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
         }
     }
     uint32_t final_d4 = 0;
-    for (int s = 0; s < n_strips - 1; s++) dp_strip2<false, SAME>(refA, refB, qryA, qryB, sp, pen_start, free_end, sc, s, false, &final_d4);
-    if (free_end) dp_strip2<true, SAME>(refA, refB, qryA, qryB, sp, pen_start, true, sc, n_strips - 1, true, &final_d4);
-    else dp_strip2<false, SAME>(refA, refB, qryA, qryB, sp, pen_start, false, sc, n_strips - 1, true, &final_d4);
+    for (int s = 0; s < n_strips - 1; s++)
+        dp_strip2<false, SAME, BAND>(refA, refB, qryA, qryB, sp, pen_start, free_end, sc, s, false, &final_d4, band, n_strips);
+    if (free_end) dp_strip2<true, SAME, BAND>(refA, refB, qryA, qryB, sp, pen_start, true, sc, n_strips - 1, true, &final_d4, band, n_strips);
+    else dp_strip2<false, SAME, BAND>(refA, refB, qryA, qryB, sp, pen_start, false, sc, n_strips - 1, true, &final_d4, band, n_strips);
     const int off = (int)DP2_BIAS + (Q + R) * sp.sb_half;
     score[0] = ((int)(final_d4 & 0xFFFFu) - off) >> 2;
     score[1] = ((int)(final_d4 >> 16) - off) >> 2;
@@ -368,9 +466,13 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
 // Streamed traceback of alignment `which` of the pair (NeedlemanWunschGlobalAlignment.java:85-114): walks from (Q,R) to
 // (0,0) and hands every column, LAST column first, to sink.push(ref code | qry code << 8) (CODE_GAP where the pointer
 // did not consume that sequence).  Pointer words come through a 16-column window in the thread's own profile slots.
-template <class Sink>
-__device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView& qry, const DpScratch2& sc, int which, Sink& sink) {
+// BAND: the walk stops and returns false as soon as it stands on a cell that is outside the diagonals |j - i| < band (cells of the
+// last row and of the last column, where the free terminal gaps run, only have to lie inside the staircase); the caller then
+// discards what the sink has seen and the alignment is redone with full matrices.
+template <bool BAND = false, class Sink>
+__device__ __forceinline__ bool dp_traceback2(const SeqView& ref, const SeqView& qry, const DpScratch2& sc, int which, Sink& sink, int band = 0) {
     int i = qry.len, j = ref.len;
+    const int Q = qry.len, R = ref.len;
     int ws = -1, whi = 0;
     // window slot k of this thread: shared address win_s + (k >> 1) * 16 * DP2_BLOCK + (k & 1) * 8
     uint32_t win_s = (uint32_t)__cvta_generic_to_shared(sc.prof + threadIdx.x);
@@ -388,6 +490,15 @@ __device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView&
         else if (j == 0) p = P_UP;
         else {
             const int s = (int)((uint32_t)(i - 1) / KROWS), r = (int)((uint32_t)(i - 1) % KROWS);
+            bool off_band = false;
+            if (BAND) {
+                off_band = (uint32_t)(j - i + band - 1) > (uint32_t)(2 * band - 2);
+                if (off_band) {  // not on a diagonal strictly inside the band
+                    if (i != Q && j != R) return false;
+                    const BandCols bc = band_cols(s, band, R, s == (Q - 1) / KROWS);
+                    if (j < bc.lo || j > bc.hi) return false;
+                }
+            }
             if (s != ws || j <= whi - TB_WINDOW) {
                 ws = s;
                 whi = j;
@@ -398,11 +509,44 @@ __device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView&
                     t[k] = (j - k >= 1) ? __ldcs(g) : make_uint2(0u, 0u);
                     g -= nt;
                 }
+                uint32_t not_diag = 1u;
+#ifdef HSQ_EXPERIMENT_STRIP_FAST  // (development experiment, slower as it stands: three dependent load latencies per strip instead of 16 short steps)
+                if constexpr (Sink::HAS_FAST) {
+                    // entering a strip at its last row: are the next 16 steps all diagonal?  (row 15-k of column j-k: bit k + shift)
+                    if (r == KROWS - 1 && j >= KROWS && !off_band && sink.fast_ready()) {
+                        uint32_t acc = 0;
+#pragma unroll
+                        for (int k = 0; k < TB_WINDOW; k++) acc |= (t[k].x | t[k].y) >> k;
+                        not_diag = (acc >> shift) & 1u;
+                    }
+                }
+#endif
 #pragma unroll
                 for (int k = 0; k < TB_WINDOW; k++)
                     asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(win_s + (uint32_t)((k >> 1) * 16 * DP2_BLOCK + (k & 1) * 8)),
                                  "r"(t[k].x), "r"(t[k].y)
                                  : "memory");
+#ifdef HSQ_EXPERIMENT_STRIP_FAST
+                if constexpr (Sink::HAS_FAST) {
+                    // ... over 16 equal, non-gap bases?  Then the whole strip is one extension of the sink's run of matches.
+                    if (!not_diag) {
+                        uint32_t rc[4], qc[4];
+                        load_codes16(ref, j - KROWS, rc);
+                        load_codes16(qry, i - KROWS, qc);
+                        const uint32_t diff = (rc[0] ^ qc[0]) | (rc[1] ^ qc[1]) | (rc[2] ^ qc[2]) | (rc[3] ^ qc[3]);
+                        const uint32_t any = rc[0] | rc[1] | rc[2] | rc[3];
+                        if (diff == 0 && (any & (0x01010101u * CODE_GAP)) == 0) {
+                            sink.fast_match_n(KROWS);
+                            i -= KROWS;
+                            j -= KROWS;
+                            rw.init(ref, j);
+                            qw.init(qry, i);
+                            continue;  // (the window now belongs to the strip that was skipped: s != ws reloads it)
+                        }
+                    }
+                }
+#endif
+                (void)not_diag;
             }
             const uint32_t k = (uint32_t)(whi - j);
             uint2 w;
@@ -441,6 +585,7 @@ __device__ __forceinline__ void dp_traceback2(const SeqView& ref, const SeqView&
         }
         sink.push(rc | (qc << 8));
     }
+    return true;
 }
 
 }  // namespace hsq

@@ -183,6 +183,13 @@ struct CigarMdStream {
         last_entry = 1;
         prev_op = '=';
     }
+    __device__ inline void fast_match_n(int n) {  // n times fast_match
+        ref_len += n;
+        run_n += n;
+        match_count = (last_entry == 1) ? match_count + n : n;
+        last_entry = 1;
+        prev_op = '=';
+    }
     __device__ inline bool drops_query_gaps() const { return !started; }
     __device__ inline void flush_run() {
         if (run_n > 0) {

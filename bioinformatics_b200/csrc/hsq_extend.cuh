@@ -178,7 +178,7 @@ __global__ void bucket_scatter_kernel(const uint32_t* __restrict__ key, int64_t 
 // What follows DP#2 for one read end (:212-236): acceptance test, streamed traceback into the CIGAR / MD state machine,
 // NM / POS, result stores.  `traceback(sink)` walks the alignment last column first.
 template <class Traceback>
-__device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqView& rw, int start, int score, Traceback traceback,
+__device__ __forceinline__ int capture_finish(const ReadEndViews& v, const SeqView& rw, int start, int score, Traceback traceback,
                                                const ExtendDeviceOut& out, int64_t m) {
     int ok = 0, pos = 0, read_start = 0, read_stop = 0;
     CigarMdStream st;
@@ -206,6 +206,7 @@ __device__ __forceinline__ void capture_finish(const ReadEndViews& v, const SeqV
     out.cigar_len[m] = st.cw.len;
     out.md_len[m] = st.mw.len;
     out.overflow[m] = (uint8_t)((st.cw.len > st.cw.cap ? 1 : 0) | (st.mw.len > st.mw.cap ? 2 : 0));
+    return ok;
 }
 
 static constexpr uint32_t ORDER_HOLE = 0xFFFFFFFFu;  // padding entry of an odd-sized bucket
@@ -309,17 +310,26 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes prob
 }
 
 // Stage 2, packed: two read ends of the same DP#2 shape per thread, cells as u16x2 halves (hsq_dp2.cuh).
+// BAND (hsq_config.band > 0): the fill computes the staircase of band_cols only.  A read end keeps its banded result only if
+//   (1) its score is above what any path that starts inside the band and reaches a diagonal |j - i| = band can score:
+//       match * min(Q, R) + gapStart + (band - 1) * gapExtend (such a path carries a net run of >= band gaps), and
+//   (2) its traceback stays on the diagonals |j - i| < band (terminal free-gap cells excepted);
+// every other read end keeps its bucket key and is redone by the full kernel in a second pass (extend_capture), the accepted ones move
+// to the skip bucket.  What neither test sees is an alignment that lies outside the band from its first to its last column (a
+// read matching a shifted copy of its target better than the target itself); DESIGN.md 4.1 has the measured rate (0).
+// band_stats: [0] read ends aligned in the band, [1] of them handed to the full pass.
 #ifndef HSQ_EXP_CTAS
 #define HSQ_EXP_CTAS 5
 #endif
-__global__ void __launch_bounds__(DP2_BLOCK, HSQ_EXP_CTAS) capture2_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
-                                                             DeviceSeqs r2, const uint32_t* __restrict__ order,
-                                                             const uint32_t* __restrict__ n_active_ptr, ScoreParams2 sp_user,
-                                                             ScratchPool2 pool, ExtendDeviceOut out, unsigned long long* cells_total,
-                                                             unsigned long long* work_counter) {
-    __shared__ int4 prof[PROF2_INT4_PER_THREAD * DP2_BLOCK];
+template <bool BAND>
+__device__ __forceinline__ void capture2_body(const DeviceProbes& probes, const int32_t* __restrict__ probe_id, const DeviceSeqs& r1,
+                                              const DeviceSeqs& r2, const uint32_t* __restrict__ order, const uint32_t* __restrict__ n_active_ptr,
+                                              const ScoreParams2& sp_user, const ScratchPool2& pool, const ExtendDeviceOut& out,
+                                              unsigned long long* cells_total, unsigned long long* work_counter, int band, BucketKeys keys,
+                                              unsigned long long* band_stats, int4* prof) {
     DpScratch2 sc = thread_scratch2(pool, prof);
     int64_t cells = 0;
+    int n_banded = 0, n_redo = 0;
     const int64_t n_slots = (int64_t)*n_active_ptr >> 1;  // bucket sizes are even
     for (;;) {
         const int64_t t = next_slot(work_counter);
@@ -340,22 +350,65 @@ __global__ void __launch_bounds__(DP2_BLOCK, HSQ_EXP_CTAS) capture2_kernel(Devic
         SeqView rwb = sub_view(vb.read, start_b, vb.read.len - start_b);
         int score[2];
 #ifdef HSQ_EXPERIMENT_SAMEREF
-        dp_fill2<true>(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score);  // :211
+        dp_fill2<true, BAND>(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score, band);  // :211
 #else
-        dp_fill2<false>(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score);  // :211
+        dp_fill2<false, BAND>(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score, band);  // :211
 #endif
         const int score_a = score[0], score_b = score[1];
-        cells += (int64_t)va.capture.len * rwa.len * n_here;
+        if (!BAND) cells += (int64_t)va.capture.len * rwa.len * n_here;  // (a banded read end's cells are counted when it is accepted)
 #pragma unroll 1
         for (int which = 0; which < n_here; which++) {
             const ReadEndViews v = which ? vb : va;  // by value: selected once, not at every use inside the column loop
             const SeqView rw = which ? rwb : rwa;
-            capture_finish(v, rw, which ? start_b : start_a, which ? score_b : score_a,
-                           [&](CigarMdStream& st) { dp_traceback2(v.capture, rw, sc, which, st); }, out, which ? mb : ma);
+            const int64_t m = which ? mb : ma;
+            const int score_x = which ? score_b : score_a;
+            bool inside = true;
+            int ok = 0;
+            if (!BAND || score_x > sp_user.match * min(rw.len, v.capture.len) + sp_user.gap_start + (band - 1) * sp_user.gap_extend)
+                ok = capture_finish(v, rw, which ? start_b : start_a, score_x,
+                                    [&](CigarMdStream& st) { inside = dp_traceback2<BAND>(v.capture, rw, sc, which, st, band); }, out, m);
+            if (BAND) {
+                n_banded++;
+                if (ok && inside) {
+                    keys.key[m] = keys.skip_key;
+                    cells += (int64_t)v.capture.len * rw.len;  // the cells the reference fills for this read end
+                } else {
+                    n_redo++;
+                }
+            }
         }
     }
     for (int o = 16; o > 0; o >>= 1) cells += __shfl_xor_sync(0xffffffffu, cells, o);
     if ((threadIdx.x & 31) == 0 && cells) atomicAdd(cells_total, (unsigned long long)cells);
+    if (BAND) {
+        for (int o = 16; o > 0; o >>= 1) {
+            n_banded += __shfl_xor_sync(0xffffffffu, n_banded, o);
+            n_redo += __shfl_xor_sync(0xffffffffu, n_redo, o);
+        }
+        if ((threadIdx.x & 31) == 0 && n_banded) {
+            atomicAdd(&band_stats[0], (unsigned long long)n_banded);
+            if (n_redo) atomicAdd(&band_stats[1], (unsigned long long)n_redo);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(DP2_BLOCK, HSQ_EXP_CTAS) capture2_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
+                                                             DeviceSeqs r2, const uint32_t* __restrict__ order,
+                                                             const uint32_t* __restrict__ n_active_ptr, ScoreParams2 sp_user,
+                                                             ScratchPool2 pool, ExtendDeviceOut out, unsigned long long* cells_total,
+                                                             unsigned long long* work_counter) {
+    __shared__ int4 prof[PROF2_INT4_PER_THREAD * DP2_BLOCK];
+    capture2_body<false>(probes, probe_id, r1, r2, order, n_active_ptr, sp_user, pool, out, cells_total, work_counter, 0, BucketKeys{}, nullptr, prof);
+}
+
+__global__ void __launch_bounds__(DP2_BLOCK, HSQ_EXP_CTAS) capture2_band_kernel(DeviceProbes probes, const int32_t* __restrict__ probe_id, DeviceSeqs r1,
+                                                                  DeviceSeqs r2, const uint32_t* __restrict__ order,
+                                                                  const uint32_t* __restrict__ n_active_ptr, ScoreParams2 sp_user,
+                                                                  ScratchPool2 pool, ExtendDeviceOut out, unsigned long long* cells_total,
+                                                                  unsigned long long* work_counter, int band, BucketKeys keys,
+                                                                  unsigned long long* band_stats) {
+    __shared__ int4 prof[PROF2_INT4_PER_THREAD * DP2_BLOCK];
+    capture2_body<true>(probes, probe_id, r1, r2, order, n_active_ptr, sp_user, pool, out, cells_total, work_counter, band, keys, band_stats, prof);
 }
 
 }  // namespace hsq

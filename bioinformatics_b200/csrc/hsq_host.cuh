@@ -50,6 +50,8 @@ struct DevSeqsOwned {  // encoded ragged batch resident on the device
 
 }  // namespace hsq
 
+static constexpr int BAND_STATS_SLOT = 8;  // words 8, 9 of hsq_ctx::cells: read ends aligned in the band, of them redone in full
+
 struct hsq_ctx {
     int device = 0;
     int sm_count = 0;
@@ -80,6 +82,7 @@ struct hsq_ctx {
     // probe search windows sorted by (contig, strand, start) for hsq_assign_probes
     hsq::DevBuf rg_start, rg_end, rg_value, rg_off;
     hsq::DevBuf dd_seg;         // dedup segment path: per-probe counters, offsets
+    hsq::DevBuf dd_vseg;        // the same per UID-hash bucket when oversized probes are split
     // in-library multi-GPU exchange (hsq_capi_comm.inl): NCCL communicator of this context, exchange buffers
     void* comm = nullptr;
     int comm_rank = 0, comm_world = 1;
@@ -120,6 +123,7 @@ struct hsq_ctx {
     hsq::ExtendDeviceOut ext_out{};
     int* h_status = nullptr;  // pinned
     unsigned long long* h_cells = nullptr;
+    int64_t band_stats[2] = {0, 0};              // last extend call: read ends aligned in the band, of them redone with full matrices
 };
 
 namespace hsq {

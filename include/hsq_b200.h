@@ -381,6 +381,10 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
  * hsq_dedup_extend_* [0] key generation, [1] per-probe bucketing + group-by (sharded: the exchange and the owner's reduction),
  * [2] compaction of the pairs to extend, [3] the extension kernels. */
 int32_t hsq_last_spans(const hsq_ctx* ctx, float* ms4);
+/* The opt-in band (hsq_config.band) in the last extend call: *banded = read ends whose capture-target DP ran inside the band,
+ * *redone = those of them whose traceback left the diagonals |j - i| < band (or that were not traced back at all) and that were
+ * therefore aligned again with full matrices.  Both 0 when the band is off.  Either pointer may be NULL. */
+int32_t hsq_band_stats(const hsq_ctx* ctx, int64_t* banded, int64_t* redone);
 
 /* ---- batch entry points (host buffers in, host buffers out) -------------------------------- */
 /* new NeedlemanWunschGlobalAlignment(ref[k], qry[k], SimpleAlignmentScorer(scorer, flags)).getAlignmentPair() */

@@ -168,6 +168,7 @@ public final class HsqB200 implements AutoCloseable {
             JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG, JAVA_LONG, JAVA_INT, JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle LAST_TIMING = fn("hsq_last_timing", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle LAST_SPANS = fn("hsq_last_spans", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle BAND_STATS = fn("hsq_band_stats", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle TIMER_START = fn("hsq_timer_start", FunctionDescriptor.of(JAVA_INT, ADDRESS));
     private static final MethodHandle TIMER_STOP = fn("hsq_timer_stop", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
     private static final MethodHandle INT32_PEAK = fn("hsq_int32_peak", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_DOUBLE, ADDRESS));
@@ -482,6 +483,13 @@ public final class HsqB200 implements AutoCloseable {
         MemorySegment ms = arena.allocate(JAVA_FLOAT, 4);
         check(invokeInt(LAST_SPANS, ctx, ms));
         return ms.toArray(JAVA_FLOAT);
+    }
+
+    /** hsq_band_stats: {read ends aligned inside the band, of them redone with full matrices} of the last extend call. */
+    public long[] bandStats() {
+        MemorySegment a = arena.allocate(JAVA_LONG), b = arena.allocate(JAVA_LONG);
+        check(invokeInt(BAND_STATS, ctx, a, b));
+        return new long[] {a.get(JAVA_LONG, 0), b.get(JAVA_LONG, 0)};
     }
 
     public void timerStart() { check(invokeInt(TIMER_START, ctx)); }

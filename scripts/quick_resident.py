@@ -1,4 +1,4 @@
-"""Resident timing of hsq_extend_run (development aid).  Usage: quick_resident.py [pairs] [read_len]
+"""Resident timing of hsq_extend_run (development aid).  Usage: quick_resident.py [pairs] [read_len] [band]
 HSQ_B200_LIB selects an alternative build of the library (experiments)."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -12,7 +12,8 @@ n = int(sys.argv[1]) if len(sys.argv) > 1 else 1000000
 L = int(sys.argv[2]) if len(sys.argv) > 2 else 150
 probes = synth.make_probes(1000, target_len=(L - 50, L + 10))
 pairs = synth.make_pairs(probes, n, read_len=L, with_quals=False)
-with Context(0) as ctx:
+band = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+with Context(0, config={"band": band}) as ctx:
     ctx.set_probes(probes)
     out = ExtendResult(n, 32, 64)
     ctx.extend_stage(pairs)
@@ -26,4 +27,4 @@ with Context(0) as ctx:
     for _ in range(5):
         ctx.extend_run(32, 64)
     ms = ctx.timer_stop() / 5
-    print("%s: %d pairs L=%d: %.2f ms/step, %.0f GCUPS, pair_ok %.3f" % (os.path.basename(_lib.SO_PATH), n, L, ms, out.cells / ms / 1e6, out.pair_ok.mean()))
+    print("%s: %d pairs L=%d band %d: %.2f ms/step, %.0f GCUPS, pair_ok %.3f, band stats %s" % (os.path.basename(_lib.SO_PATH), n, L, band, ms, out.cells / ms / 1e6, out.pair_ok.mean(), ctx.band_stats()))
