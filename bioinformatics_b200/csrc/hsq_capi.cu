@@ -86,7 +86,7 @@ int alloc_scratch(hsq_ctx* ctx, int64_t nthreads, int64_t nthreads2, int q_max, 
     HSQ_CUDA(ctx, ctx->ptr_words.ensure(std::max(t1 * sizeof(uint32_t), t2 * sizeof(uint2)) * n_strips * rs));
     HSQ_CUDA(ctx, ctx->brow.ensure(std::max(t1, t2) * rs * sizeof(int32_t)));
     HSQ_CUDA(ctx, ctx->cols.ensure(t1 * (size_t)(q_max + r_max + 1) * sizeof(uint16_t) + 16));
-    HSQ_CUDA(ctx, ctx->colinfo.ensure(t2 * rs + 16));
+    HSQ_CUDA(ctx, ctx->colinfo.ensure(t2 * ((rs + 3) / 4 + 1) * sizeof(uint32_t) + 16));  // one byte per column, packed four to a word
     HSQ_CUDA(ctx, ctx->slow.ensure(t2 * KROWS * sizeof(uint32_t) + 16));
     pool->r_stride = r_max + 1;
     pool->ptr_words = ctx->ptr_words.as<uint32_t>();
@@ -96,7 +96,8 @@ int alloc_scratch(hsq_ctx* ctx, int64_t nthreads, int64_t nthreads2, int q_max, 
         pool2->r_stride = r_max + 1;
         pool2->ptr_words = ctx->ptr_words.as<uint2>();
         pool2->brow = ctx->brow.as<uint32_t>();
-        pool2->colinfo = ctx->colinfo.as<uint8_t>();
+        pool2->colinfo = ctx->colinfo.as<uint32_t>();
+        pool2->nthreads = 0;  // set at every launch site
         pool2->slow = ctx->slow.as<uint32_t>();
     }
     return HSQ_OK;

@@ -178,6 +178,7 @@ int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, Exte
             ctx->launches++;
             if ((rc = bucket_sort(n_keys1, keys1.skip_key))) return rc;
             HSQ_CUDA(ctx, cudaMemsetAsync(work, 0, 16, ctx->stream));  // work counters of the two packed kernels
+            pool2.nthreads = (uint32_t)grid1 * DP2_BLOCK;
             primer2_kernel<<<grid1, DP2_BLOCK, 0, ctx->stream>>>(pv, pid, v1, v2, order, n_active, sp_default2, pool2, d, keys, d_status(ctx),
                                                                 cells, work);
         } else {
@@ -217,6 +218,7 @@ int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, Exte
     plan->sp_user2 = sp_user2;
     plan->pool = pool;
     plan->pool2 = pool2;
+    plan->pool2.nthreads = (uint32_t)grid2 * DP2_BLOCK;
     plan->d = d;
     plan->pair_ok = ctx->pair_ok.as<uint8_t>();
     return HSQ_OK;

@@ -37,10 +37,11 @@ __device__ __forceinline__ uint4 load16_unaligned(const uint8_t* s) {
     }
 }
 
-// One warp per read: lanes 0-15 copy the bases, lanes 16-31 the qualities of [first, first+keep) to the packed outputs, one 16-byte
-// aligned chunk of the destination per lane and round (a 150-base read takes one round).  A chunk that lies inside the read is one
-// 16-byte store assembled from the two aligned source vectors around it; the chunks at the two ends are written byte by byte.
-// (Up to r2_c every lane moved one byte per step: 20 load / store instructions per read, 1.9 TB/s.)
+// One warp per read: lanes 0-15 copy the bases, lanes 16-31 the qualities of [first, first+keep) to the packed outputs.  The 16-byte
+// aligned chunks of the destination that lie inside the read are one 16-byte store each, assembled from the two aligned source
+// vectors around them (one chunk per lane and round; a 150-base read takes one round); the up to 15 bytes before the first and
+// after the last such chunk are one byte per lane.
+// (Up to r2_c every lane moved one byte per step: 20 load / store instructions per read.)
 __global__ void trim_copy_kernel(const uint8_t* __restrict__ seq, const uint8_t* __restrict__ qual, const int64_t* __restrict__ offsets,
                                  const int64_t* __restrict__ out_offsets, int64_t n, int first, uint8_t* __restrict__ out_seq,
                                  uint8_t* __restrict__ out_qual) {
@@ -53,14 +54,16 @@ __global__ void trim_copy_kernel(const uint8_t* __restrict__ seq, const uint8_t*
         const int64_t src = offsets[w] + first, dst = out_offsets[w];
         const int64_t end = out_offsets[w + 1];
         // destination chunks are aligned in the ADDRESS space of `out` (both output arrays sit at 16-byte aligned addresses)
-        const int64_t a16 = dst & ~(int64_t)15;
-        for (int64_t c = a16 + 16 * sub; c < end; c += 256) {
-            if (c >= dst && c + 16 <= end) {
+        const int64_t body_lo = (dst + 15) & ~(int64_t)15, body_hi = end & ~(int64_t)15;
+        if (body_lo <= body_hi) {
+            for (int64_t c = body_lo + 16 * sub; c < body_hi; c += 256)
                 *reinterpret_cast<uint4*>(out + c) = load16_unaligned(in + src + (c - dst));
-            } else {
-                const int64_t lo = max(c, dst), hi = min(c + 16, end);
-                for (int64_t x = lo; x < hi; x++) out[x] = in[src + (x - dst)];
-            }
+            const int64_t h = dst + sub, t = body_hi + sub;
+            if (h < body_lo) out[h] = in[src + sub];
+            if (t < end) out[t] = in[src + (t - dst)];
+        } else {  // fewer than 16 bytes, none of them on a chunk boundary
+            const int64_t h = dst + sub;
+            if (h < end) out[h] = in[src + sub];
         }
     }
 }

@@ -105,18 +105,19 @@ __device__ __forceinline__ BandCols band_cols(int s, int band, int R, bool last_
     return c;
 }
 
-struct DpScratch2 {
+struct DpScratch2 {  // every pointer is already offset to this thread's element 0; consecutive elements are nthreads apart
     uint2* ptr_words;   // [n_strips_max * (r_max + 1)] per thread: (U word, L word)
     uint32_t* brow;     // [r_max + 1] per thread: packed X' of the row above the current strip
-    uint8_t* colinfo;   // [r_max + 1] per thread: profile column of alignment A (low nibble) and B (high nibble); 4 = not A/C/G/T
+    uint32_t* colinfo;  // [(r_max + 4) / 4] per thread: byte j & 3 of word j >> 2 = profile column of alignment A (low nibble) and B
+                        // (high nibble) at reference position j; 4 = not A/C/G/T
     uint32_t* slow;     // [KROWS] per thread: packed substitution scores of a column with a non-ACGT reference code
     int4* prof;         // shared memory: [PROF2_INT4_PER_THREAD][DP2_BLOCK]
-    int64_t nthreads;
-    int64_t tid;
+    int64_t nthreads;   // a kernel parameter (ScratchPool2::nthreads), not gridDim * blockDim: the compiler re-derives either wherever
+                        // it runs out of registers, and a constant-bank operand costs nothing
     int r_stride;
-    __device__ inline uint2& word(int strip, int j) const { return ptr_words[((int64_t)strip * r_stride + j) * nthreads + tid]; }
-    __device__ inline uint32_t& b(int j) const { return brow[(int64_t)j * nthreads + tid]; }
-    __device__ inline uint8_t& ci(int j) const { return colinfo[(int64_t)j * nthreads + tid]; }
+    __device__ inline uint2& word(int strip, int j) const { return ptr_words[((int64_t)strip * r_stride + j) * nthreads]; }
+    __device__ inline uint32_t& b(int j) const { return brow[(int64_t)j * nthreads]; }
+    __device__ inline uint32_t& ciw(int w) const { return colinfo[(int64_t)w * nthreads]; }
 };
 
 // packed, biased, offset 4*border_score of border cell k (row 0 or column 0)
@@ -361,24 +362,31 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
     }
     uint2* wordp = &sc.word(s, jlo);
     uint32_t* browp = &sc.b(jlo);
-    const uint8_t* cip = &sc.ci(jlo);
+    const uint32_t* cwp = &sc.ciw(jlo >> 2);
     const int64_t nt = sc.nthreads;
     const int4* prof_t = sc.prof + threadIdx.x;
-    uint32_t next_ci = 0, next_up = 0;
+    // the row above arrives two columns ahead of its use, the profile columns a word (four columns) ahead: one column of cells
+    // does not cover the latency of a load that misses L1 (r2_d: 5 % of the kernel's samples waited here with one column of lead)
+    uint32_t up0 = 0, up1 = 0, ciw = 0, ciw_next = 0;
+    const int cw_last = jhi >> 2;
     if (!BAND || jlo <= jhi) {
-        next_ci = *cip;
-        next_up = *browp;
+        up0 = *browp;
+        if (jlo < jhi) up1 = browp[nt];
+        ciw = *cwp;
+        if ((jlo >> 2) < cw_last) ciw_next = cwp[nt];
     }
 #ifdef HSQ_EXPERIMENT_NO_COLUMNS  // (development experiment: what a strip costs without its columns)
     jhi = jlo - 1;
 #endif
     for (int j = jlo; j <= jhi; j++) {
-        const uint32_t ci = next_ci;
-        const uint32_t upx = next_up;
-        if (j < jhi) {
-            cip += nt;
-            next_ci = *cip;
-            next_up = browp[nt];
+        const uint32_t ci = (ciw >> (8 * (j & 3))) & 0xFFu;
+        const uint32_t upx = up0;
+        up0 = up1;
+        if (j + 2 <= jhi) up1 = browp[2 * nt];
+        if ((j & 3) == 3) {
+            ciw = ciw_next;
+            cwp += nt;
+            if (((j + 1) >> 2) < cw_last) ciw_next = cwp[nt];
         }
         const uint32_t up_d4 = upx & DP2_MASK_D4;
         const bool vfree = free_end && (j == R);
@@ -392,7 +400,7 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
             else xlast = dp_column2<HFREE, true, false, SAME>(D4, H0, pa, pb, nullptr, nt, up_v0, diag_d4, sp, rstar, &w);
         } else {  // ambiguity code, N, U or gap character in a reference: this column's scores go through global scratch
             const uint32_t ca = refA.get(j - 1), cb = refB.get(j - 1);
-            uint32_t* sl = sc.slow + sc.tid;
+            uint32_t* sl = sc.slow;
 #pragma unroll 1
             for (int r = 0; r < KROWS; r++) {
                 const int i = i0 + 1 + r;
@@ -440,18 +448,25 @@ __device__ inline void dp_fill2(const SeqView& refA, const SeqView& refB, const 
     const bool free_end = !pen_end;
     {   // matrix row 0 (cells point LEFT: never an UP continuation) and the profile column of every reference position
         uint32_t* bp = &sc.b(R);
-        uint8_t* cp = &sc.ci(R);
+        uint32_t* cwp = &sc.ciw(R >> 2);
+        uint32_t cw = 0;
         CodeWalker wa, wb;  // last column first: the walkers read from the end of a view
         wa.init(refA, R);
         wb.init(refB, R);
-        for (int j = R; j >= 1; j--, bp -= sc.nthreads, cp -= sc.nthreads) {
+        for (int j = R; j >= 1; j--, bp -= sc.nthreads) {
             *bp = border2(j, pen_start, sp) + (uint32_t)P_LEFT * DP2_REP;
             const uint32_t ba = (uint32_t)prof_slot(wa.peek_raw(), refA.comp);
             const uint32_t bb = (uint32_t)prof_slot(wb.peek_raw(), refB.comp);
-            *cp = (uint8_t)(ba | (bb << 4));
+            cw |= (ba | (bb << 4)) << (8 * (j & 3));
+            if ((j & 3) == 0) {
+                *cwp = cw;
+                cwp -= sc.nthreads;
+                cw = 0;
+            }
             wa.advance(j);
             wb.advance(j);
         }
+        *cwp = cw;  // word 0: columns 1 .. 3
     }
     uint32_t final_d4 = 0;
     for (int s = 0; s < n_strips - 1; s++)

@@ -249,20 +249,21 @@ __global__ void __launch_bounds__(DP_BLOCK, 5) capture_kernel(DeviceProbes probe
 struct ScratchPool2 {
     uint2* ptr_words;
     uint32_t* brow;
-    uint8_t* colinfo;
+    uint32_t* colinfo;
     uint32_t* slow;
     int r_stride;
+    uint32_t nthreads;  // threads of the launch this copy of the pool is passed to (set at every launch site)
 };
 
 __device__ inline DpScratch2 thread_scratch2(const ScratchPool2& pool, int4* prof) {
     DpScratch2 sc;
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x;
     sc.prof = prof;
-    sc.ptr_words = pool.ptr_words;
-    sc.brow = pool.brow;
-    sc.colinfo = pool.colinfo;
-    sc.slow = pool.slow;
-    sc.nthreads = (int64_t)gridDim.x * blockDim.x;
-    sc.tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    sc.ptr_words = pool.ptr_words + tid;
+    sc.brow = pool.brow + tid;
+    sc.colinfo = pool.colinfo + tid;
+    sc.slow = pool.slow + tid;
+    sc.nthreads = (int64_t)pool.nthreads;
     sc.r_stride = pool.r_stride;
     return sc;
 }
