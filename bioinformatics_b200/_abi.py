@@ -96,6 +96,20 @@ class ProbeStats(C.Structure):
     _fields_ = [("n_probes", C.c_int64), ("unique_pairs", i32p), ("duplicate_pairs", i32p), ("max_pairs_per_uid", i32p)]
 
 
+HSQ_BAM_FIELDS = ("record", "qname", "cigar", "seq", "qual", "tags")
+HSQ_BAM_VALUES = ("refid", "pos", "flag", "mapq", "next_refid", "pnext", "tlen", "ref_len")  # planes 6..13 of val
+
+
+class BamIndex(C.Structure):
+    _fields_ = [("cap", C.c_int64), ("n", C.c_int64), ("n_ref", C.c_int64), ("text_bytes", C.c_int64), ("first_record", C.c_int64),
+                ("payload_bytes", C.c_int64), ("payload_cap", C.c_int64), ("payload", u8p), ("off", i64p), ("val", i32p),
+                ("exact_walk", C.c_int32)]
+
+
+class UidReport(C.Structure):
+    _fields_ = [("uid_len", C.c_int32), ("unique_by_position", i32p), ("weighted_by_position", i32p)]
+
+
 class DedupExtendOut(C.Structure):
     _fields_ = [("is_best", u8p), ("group_size", i32p), ("stats", C.POINTER(ProbeStats)), ("unique_unable_to_extend", i32p),
                 ("duplicate_unable_to_extend", i32p), ("n_extended", C.c_int64), ("extended_pair", i32p), ("extend", C.POINTER(ExtendOut)),

@@ -24,7 +24,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order",
            "hsq_ctx_create_ex", "hsq_ctx_configure", "hsq_packed_bytes", "hsq_pack_reads", "hsq_quality_sums", "hsq_unpack_reads",
            "hsq_extend_packed", "hsq_dedup_packed", "hsq_comm_unique_id", "hsq_comm_init_rank", "hsq_comm_init_all", "hsq_comm_destroy",
-           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed", "hsq_variable_length_uid", "hsq_align_scores_noalloc", "hsq_band_stats")
+           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed", "hsq_variable_length_uid", "hsq_align_scores_noalloc", "hsq_band_stats", "hsq_dedup_batch_report", "hsq_pair_reasons", "hsq_index_bam")
 _NOT_STATUS = {"hsq_last_error": C.c_char_p, "hsq_version": C.c_char_p, "hsq_ctx_destroy": None, "hsq_packed_bytes": C.c_int64}
 
 
@@ -285,6 +285,43 @@ class Context:
         self._check(self.lib.hsq_dedup_batch(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
                                              A.ptr(is_best, A.u8p), A.ptr(group_size, A.i32p), C.byref(sc)))
         return is_best, group_size, stats
+
+    def index_bam(self, data, cap=None, want_payload=False):
+        """hsq_index_bam: level-0 BGZF BAM bytes -> BamIndexResult (offsets into the uncompressed stream, kept on the device)."""
+        from .batches import BamIndexResult
+        data = np.ascontiguousarray(np.frombuffer(data, dtype=np.uint8) if isinstance(data, (bytes, bytearray)) else data)
+        cap = cap if cap is not None else max(1, len(data) // 37)
+        res = BamIndexResult(cap, len(data) if want_payload else 0)
+        rc_ = res.c()
+        st = self.lib.hsq_index_bam(self.h, A.ptr(data, A.u8p), C.c_int64(len(data)), C.byref(rc_))
+        res.finish()
+        self._check(st)
+        return res
+
+    def dedup_batch_report(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, n_probes=None):
+        """hsq_dedup_batch_report: hsq_dedup_batch + the per-probe UID composition tables [n_probes, uid_len, 4] (A, C, G, T):
+        returns (is_best, group_size, stats, unique_by_position, weighted_by_position)."""
+        n_probes = n_probes or self.n_probes
+        L = ext_uid_len + lig_uid_len
+        is_best = np.zeros(pairs.n, dtype=np.uint8)
+        group_size = np.zeros(pairs.n, dtype=np.int32)
+        stats = ProbeStatsHost(n_probes)
+        unique = np.zeros((n_probes, L, 4), dtype=np.int32)
+        weighted = np.zeros((n_probes, L, 4), dtype=np.int32)
+        rep = A.UidReport(0, A.ptr(unique, A.i32p), A.ptr(weighted, A.i32p))
+        pc, sc = pairs.c(), stats.c()
+        self._check(self.lib.hsq_dedup_batch_report(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
+                                                    A.ptr(is_best, A.u8p), A.ptr(group_size, A.i32p), C.byref(sc), C.byref(rep)))
+        assert rep.uid_len == L
+        return is_best, group_size, stats, unique, weighted
+
+    def pair_reasons(self, result, extend_duplicates=False):
+        """hsq_pair_reasons: one HSQ_PAIR_* code per pair of a DedupExtendResult (host helper)."""
+        reason = np.zeros(result.n, dtype=np.uint8)
+        oc = result.c()
+        oc.n_extended = result.n_extended
+        self._check(self.lib.hsq_pair_reasons(C.byref(oc), C.c_int64(result.n), C.c_int32(1 if extend_duplicates else 0), A.ptr(reason, A.u8p)))
+        return reason
 
     def dedup_extend_batch(self, pairs: PairBatchHost, ext_uid_len, lig_uid_len, extend_duplicates=False, cigar_cap=32, md_cap=48,
                            n_probes=None, out=None):

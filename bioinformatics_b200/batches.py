@@ -547,6 +547,39 @@ class SamRecordsResult:
                                  (self.alt_offsets[:n + 1], self.alt_contig[:m], self.alt_negative[:m], self.alt_start[:m], self.alt_stop[:m]))
 
 
+class BamIndexResult:
+    """hsq_bam_index with host planes for `cap` records (and room for the uncompressed stream when want_payload)."""
+
+    def __init__(self, cap, payload_cap=0):
+        self.cap = cap
+        self.off = np.zeros((len(A.HSQ_BAM_FIELDS), max(cap, 1)), dtype=np.int64)
+        self.val = np.zeros((len(A.HSQ_BAM_FIELDS) + len(A.HSQ_BAM_VALUES), max(cap, 1)), dtype=np.int32)
+        self.payload = np.zeros(payload_cap, dtype=np.uint8) if payload_cap else None
+        self.n = self.n_ref = self.text_bytes = self.first_record = self.payload_bytes = self.exact_walk = 0
+        self._c = None
+
+    def c(self):
+        self._c = A.BamIndex(self.cap, 0, 0, 0, 0, 0, 0 if self.payload is None else len(self.payload), A.ptr(self.payload, A.u8p),
+                             A.ptr(self.off, A.i64p), A.ptr(self.val, A.i32p), 0)
+        return self._c
+
+    def finish(self):
+        c = self._c
+        self.n, self.n_ref, self.text_bytes, self.first_record = int(c.n), int(c.n_ref), int(c.text_bytes), int(c.first_record)
+        self.payload_bytes, self.exact_walk = int(c.payload_bytes), int(c.exact_walk)
+        return self
+
+    def columns(self):
+        """dict: <field>_off / <field>_len for the six parts, and the eight fixed columns, each cut to n records"""
+        out = {}
+        for f, name in enumerate(A.HSQ_BAM_FIELDS):
+            out[name + "_off"] = self.off[f, :self.n]
+            out[name + "_len"] = self.val[f, :self.n]
+        for v, name in enumerate(A.HSQ_BAM_VALUES):
+            out[name] = self.val[len(A.HSQ_BAM_FIELDS) + v, :self.n]
+        return out
+
+
 class NameJoinHost:
     """hsq_name_join: what FastqAndBamFileMerger reads off the SAM records and the two FASTQ files
     (HSQ/process/FastqAndBamFileMerger.java:107-158,213-345)."""

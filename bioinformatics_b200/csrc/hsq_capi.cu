@@ -305,5 +305,6 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_records.inl"
 #include "hsq_capi_find.inl"
 #include "hsq_capi_ingest.inl"
+#include "hsq_capi_bam.inl"
 #include "hsq_capi_peak.inl"
 #include "hsq_capi_noalloc.inl"

@@ -85,6 +85,25 @@ __global__ void dedup_keygen_kernel(const uint8_t* __restrict__ r1, const int64_
     }
 }
 
+// Per-probe nucleotide counts of the UIDs by position (the inputs of NucleotideCompositionUtil.getNucleotideComposition[ByPosition],
+// FilterByUid.java:245-249): `weighted` counts every pair's UID, `unique` one UID per group (its best pair).  Tables are
+// [probe][position][A, C, G, T]; uid holds the first base in its most significant used bit pair.
+__global__ void uid_composition_kernel(const uint64_t* __restrict__ uid, const int32_t* __restrict__ probe, const uint8_t* __restrict__ is_best,
+                                       int64_t n, int uid_len, int32_t* __restrict__ unique, int32_t* __restrict__ weighted) {
+    int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; k < n; k += stride) {
+        const uint64_t code = uid[k];
+        const int64_t row = (int64_t)probe[k] * uid_len;
+        const bool best = is_best[k] != 0;
+        for (int i = 0; i < uid_len; i++) {
+            const int c = (int)((code >> (2 * (uid_len - 1 - i))) & 3u);
+            atomicAdd(&weighted[(row + i) * 4 + c], 1);
+            if (best) atomicAdd(&unique[(row + i) * 4 + c], 1);
+        }
+    }
+}
+
 template <class T>
 __global__ void gather_u64_kernel(const T* __restrict__ src, const uint32_t* __restrict__ idx, int64_t n, uint64_t* __restrict__ out) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -658,6 +677,34 @@ extern "C" int32_t hsq_dedup_batch(hsq_ctx* ctx, const hsq_pair_batch* pairs, in
     int rc = run_dedup(ctx, pairs, ext_uid_len, lig_uid_len, is_best, group_size, stats);
     int rc2 = timer.finish();
     return rc ? rc : rc2;
+}
+
+extern "C" int32_t hsq_dedup_batch_report(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len, uint8_t* is_best,
+                                          int32_t* group_size, hsq_probe_stats* stats, hsq_uid_report* report) {
+    if (!report || !report->unique_by_position || !report->weighted_by_position) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "null report");
+    int rc = hsq_dedup_batch(ctx, pairs, ext_uid_len, lig_uid_len, is_best, group_size, stats);
+    if (rc) return rc;
+    // the UID codes (sort_a), the probe ids and the answers of the reduction are still on the device
+    const int L = ext_uid_len + lig_uid_len;
+    report->uid_len = L;
+    const size_t cells = (size_t)stats->n_probes * (size_t)L * 4;
+    if (cells == 0) return HSQ_OK;
+    // (no CallTimer: hsq_last_timing / hsq_last_spans keep describing the dedup call)
+    HSQ_CUDA(ctx, ctx->misc.ensure(2 * cells * 4 + 16));
+    int32_t* d_unique = ctx->misc.as<int32_t>();
+    int32_t* d_weighted = d_unique + cells;
+    HSQ_CUDA(ctx, cudaMemsetAsync(d_unique, 0, 2 * cells * 4, ctx->stream));
+    if (pairs->n > 0) {
+        const int blocks = (int)std::min<int64_t>((pairs->n + 255) / 256, (int64_t)ctx->sm_count * 16);
+        uid_composition_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->sort_a.as<uint64_t>(), ctx->probe_id.as<int32_t>(), ctx->out_u8.as<uint8_t>(),
+                                                                 pairs->n, L, d_unique, d_weighted);
+        ctx->last_launches++;
+        HSQ_CUDA(ctx, cudaGetLastError());
+    }
+    if ((rc = d2h(ctx, report->unique_by_position, d_unique, cells))) return rc;
+    if ((rc = d2h(ctx, report->weighted_by_position, d_weighted, cells))) return rc;
+    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return HSQ_OK;
 }
 
 // ---- sharded dedup: the two halves of hsq_dedup_batch around the caller's all-to-all -----------------

@@ -434,3 +434,27 @@ extern "C" int32_t hsq_flag_n_pairs(hsq_ctx* ctx, const hsq_pair_batch* pairs, u
     }
     return timer.finish();
 }
+
+// ---- host helper: per-pair reason codes from the outputs of a probe task ------------------------------------------------------------
+extern "C" int32_t hsq_pair_reasons(const hsq_dedup_extend_out* out, int64_t n, int32_t extend_duplicates, uint8_t* reason) {
+    if (!out || n < 0 || (n > 0 && (!reason || !out->is_best || !out->extended_pair))) return HSQ_ERR_INVALID_ARGUMENT;
+    const int32_t* primer_end = out->extend_pooled ? out->extend_pooled->primer_end : (out->extend ? out->extend->primer_end : nullptr);
+    const uint8_t* ok = out->extend_pooled ? out->extend_pooled->ok : (out->extend ? out->extend->ok : nullptr);
+    if (out->n_extended > 0 && (!primer_end || !ok)) return HSQ_ERR_INVALID_ARGUMENT;  // the two columns this needs were not fetched
+    if (out->n_extended < 0 || out->n_extended > n) return HSQ_ERR_INVALID_ARGUMENT;
+    for (int64_t k = 0; k < n; k++) reason[k] = HSQ_PAIR_DUPLICATE_DROPPED;  // a pair that was not extended: not the best of its group
+    for (int64_t j = 0; j < out->n_extended; j++) {
+        const int64_t k = out->extended_pair[j];
+        if (k < 0 || k >= n) return HSQ_ERR_INVALID_ARGUMENT;
+        uint8_t r;
+        const int32_t e1 = primer_end[2 * j], e2 = primer_end[2 * j + 1];
+        if (e1 == HSQ_PRIMER_NOT_FOUND || e1 < 0) r = HSQ_PAIR_PRIMER_NOT_FOUND_ONE;
+        else if (e2 == HSQ_PRIMER_NOT_FOUND || e2 < 0) r = HSQ_PAIR_PRIMER_NOT_FOUND_TWO;
+        else if (!ok[2 * j]) r = HSQ_PAIR_NOT_ALIGNED_ONE;
+        else if (!ok[2 * j + 1]) r = HSQ_PAIR_NOT_ALIGNED_TWO;
+        else r = out->is_best[k] ? HSQ_PAIR_WRITTEN_UNIQUE : HSQ_PAIR_WRITTEN_DUPLICATE;
+        reason[k] = r;
+    }
+    (void)extend_duplicates;  // (an extended pair that is not the best of its group exists only when duplicates are extended)
+    return HSQ_OK;
+}

@@ -251,6 +251,20 @@ typedef struct hsq_assign_out {
 #define HSQ_ASSIGN_AMBIGUOUS_NAME (-2) /* the read name occurs on four or more usable records */
 #define HSQ_ASSIGN_IGNORED (-3)        /* the record's contig holds no probe */
 
+/* ---- report inputs of a probe task beyond the three counters ---------------------------------------------------------- */
+/* FilterByUid.java:149-171,245-252 hands NucleotideCompositionUtil the set of a probe's UIDs and the list of its pairs' UIDs; the
+ * strings it formats are ratios of these counts.  Tables are [n_probes][uid_len][4] in the order A, C, G, T (the accelerated UID
+ * domain, see hsq_dedup_batch).  The per-UID tallies of the same report (uid:count, :213-237) are the UID and group_size of the
+ * pairs whose is_best is 1. */
+typedef struct hsq_uid_report {
+    int32_t uid_len;                /* out: ext_uid_len + lig_uid_len */
+    int32_t* unique_by_position;    /* one UID per group */
+    int32_t* weighted_by_position;  /* every pair's UID */
+} hsq_uid_report;
+/* hsq_dedup_batch plus the UID composition tables, counted on the device from the keys of the same call */
+int32_t hsq_dedup_batch_report(hsq_ctx* ctx, const hsq_pair_batch* pairs, int32_t ext_uid_len, int32_t lig_uid_len, uint8_t* is_best,
+                               int32_t* group_size, hsq_probe_stats* stats, hsq_uid_report* report);
+
 /* ---- one probe task, batched: dedup then extend (…Identification.java:1172-1234) ----------------------------------- */
 typedef struct hsq_dedup_extend_out {
     uint8_t* is_best;                   /* [n] as hsq_dedup_batch */
@@ -263,6 +277,20 @@ typedef struct hsq_dedup_extend_out {
     hsq_extend_out* extend;             /* arrays sized for n pairs (2n read ends); slots j < n_extended are written */
     struct hsq_extend_pooled_out* extend_pooled; /* hsq_dedup_extend_packed writes here instead of `extend` (same slot numbering) */
 } hsq_dedup_extend_out;
+
+/* Why a pair of a probe task was or was not written (the analogue of ReadNameTracking's messages, HSQ/process/ReadNameTracking.java:30-66,
+ * FilterByUid.java:176-198, ...Identification.java:1185-1212), from the outputs of hsq_dedup_extend_batch / _packed.  Host helper, no device work.
+ * extend_duplicates as passed to that call.  reason[k] for pair k: */
+enum {
+    HSQ_PAIR_WRITTEN_UNIQUE = 0,          /* best pair of its UID group, both reads extended */
+    HSQ_PAIR_WRITTEN_DUPLICATE = 1,       /* --markDuplicates: written with the duplicate flag */
+    HSQ_PAIR_DUPLICATE_DROPPED = 2,       /* not the best pair of its group, duplicates are not written */
+    HSQ_PAIR_PRIMER_NOT_FOUND_ONE = 3,    /* extension primer not found in read one (getPrimerEndIndexInRead) */
+    HSQ_PAIR_PRIMER_NOT_FOUND_TWO = 4,    /* ligation primer not found in read two */
+    HSQ_PAIR_NOT_ALIGNED_ONE = 5,         /* read one did not align to the capture target (score <= 0 or too short, ExtendReadsToPrimer.java:212) */
+    HSQ_PAIR_NOT_ALIGNED_TWO = 6
+};
+int32_t hsq_pair_reasons(const hsq_dedup_extend_out* out, int64_t n, int32_t extend_duplicates, uint8_t* reason);
 
 /* ---- SAM record fields of extended pairs (SURVEY.md 8(a) A5 outputs, 8(f) f4) ---------------------------------------- */
 /* What ExtendReadsToPrimer.extendReadPair / createRecord and SAMRecordUtil.setSAMRecordsAsPair put on the two records of a
@@ -535,6 +563,35 @@ typedef struct hsq_sam_index {
     int32_t* val;           /* [HSQ_SAM_N_VALUES][cap] */
 } hsq_sam_index;
 int32_t hsq_index_sam(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_sam_index* out);
+
+/* Record index of a BAM file whose BGZF blocks were written at compression level 0 -- the way the reference writes its intermediate
+ * BAMs (HSQ/process/FastqAndBamFileMerger.java:131-133; records added at :386-396, read back through htsjdk at
+ * ...Identification.java:439-474).  At level 0 every BGZF block holds `stored` deflate blocks, so the record bytes are in the file as
+ * they are: the library gathers them into one uncompressed stream on the device (kept there; copied to `payload` if that is not
+ * NULL) and indexes its alignment records.  A deflate-compressed block: HSQ_ERR_UNSUPPORTED (no inflate here; the empty end-of-file
+ * block is accepted).  Offsets are byte offsets into the uncompressed stream.  Planes: off[f * cap + k] / val[f * cap + k] =
+ * offset / size of part f of record k -- RECORD: the whole record incl. its block_size word (bytes); QNAME (bytes, without the NUL);
+ * CIGAR (operations, 4 bytes each); SEQ (bases, 4 bit each); QUAL (bytes); TAGS (bytes) -- and val[v * cap + k] for the fixed
+ * columns, POS and PNEXT 1-based as in SAM text, REF_LEN = reference bases the CIGAR consumes (alignment end = POS + REF_LEN - 1).
+ * More records than cap: HSQ_ERR_OVERFLOW with n set.  exact_walk: 1 when bytes inside some record looked like a record header and
+ * the index came from the sequential block_size walk instead of the parallel test (same result, slower). */
+enum { HSQ_BAM_RECORD = 0, HSQ_BAM_QNAME = 1, HSQ_BAM_CIGAR = 2, HSQ_BAM_SEQ = 3, HSQ_BAM_QUAL = 4, HSQ_BAM_TAGS = 5, HSQ_BAM_N_FIELDS = 6 };
+enum { HSQ_BAM_REFID = 6, HSQ_BAM_POS = 7, HSQ_BAM_FLAG = 8, HSQ_BAM_MAPQ = 9, HSQ_BAM_NEXT_REFID = 10, HSQ_BAM_PNEXT = 11, HSQ_BAM_TLEN = 12,
+       HSQ_BAM_REF_LEN = 13, HSQ_BAM_N_VALUES = 14 };
+typedef struct hsq_bam_index {
+    int64_t cap;            /* in: records the planes can hold */
+    int64_t n;              /* out: alignment records */
+    int64_t n_ref;          /* out: reference sequences of the header */
+    int64_t text_bytes;     /* out: l_text; the header text sits at offset 8 of the stream */
+    int64_t first_record;   /* out: offset of the first alignment record (= end of the reference table) */
+    int64_t payload_bytes;  /* out: size of the uncompressed stream */
+    int64_t payload_cap;    /* in: bytes available in payload */
+    uint8_t* payload;       /* may be NULL */
+    int64_t* off;           /* [HSQ_BAM_N_FIELDS][cap] */
+    int32_t* val;           /* [HSQ_BAM_N_VALUES][cap] */
+    int32_t exact_walk;     /* out */
+} hsq_bam_index;
+int32_t hsq_index_bam(hsq_ctx* ctx, const uint8_t* file, int64_t n_bytes, hsq_bam_index* out);
 
 /* SAM text -> the columns hsq_assign_probes takes (hsq_mapped_records), as ReadToProbeAssigner.assignProbesToReads reads
  * them off the merged BAM's records (…Identification.java:439-474): records with the unmapped or mate-unmapped flag are dropped

@@ -168,6 +168,10 @@ public final class HsqB200 implements AutoCloseable {
             JAVA_LONG, ADDRESS, ADDRESS, JAVA_LONG, JAVA_LONG, JAVA_INT, JAVA_INT, ADDRESS, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle LAST_TIMING = fn("hsq_last_timing", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle LAST_SPANS = fn("hsq_last_spans", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
+    private static final MethodHandle DEDUP_BATCH_REPORT = fn("hsq_dedup_batch_report",
+            FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
+    private static final MethodHandle PAIR_REASONS = fn("hsq_pair_reasons", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, JAVA_INT, ADDRESS));
+    private static final MethodHandle INDEX_BAM = fn("hsq_index_bam", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
     private static final MethodHandle BAND_STATS = fn("hsq_band_stats", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle TIMER_START = fn("hsq_timer_start", FunctionDescriptor.of(JAVA_INT, ADDRESS));
     private static final MethodHandle TIMER_STOP = fn("hsq_timer_stop", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS));
@@ -484,6 +488,22 @@ public final class HsqB200 implements AutoCloseable {
         check(invokeInt(LAST_SPANS, ctx, ms));
         return ms.toArray(JAVA_FLOAT);
     }
+
+    /** hsq_dedup_batch_report: hsq_dedup_batch + the UID composition tables (hsq_uid_report: int32 uid_len, two int32 tables
+     *  [nProbes][uidLen][A, C, G, T]) that NucleotideCompositionUtil's strings are ratios of (FilterByUid.java:245-249). */
+    public void dedupBatchReport(MemorySegment pairs, int extUidLen, int ligUidLen, MemorySegment isBest, MemorySegment groupSize,
+                                 MemorySegment stats, MemorySegment uidReport) {
+        check(invokeInt(DEDUP_BATCH_REPORT, ctx, pairs, extUidLen, ligUidLen, isBest, groupSize, stats, uidReport));
+    }
+
+    /** hsq_pair_reasons (host helper): one HSQ_PAIR_* code per pair of a probe task's outputs -- what ReadNameTracking's messages say. */
+    public void pairReasons(MemorySegment dedupExtendOut, long n, boolean extendDuplicates, MemorySegment reason) {
+        check(invokeInt(PAIR_REASONS, dedupExtendOut, n, extendDuplicates ? 1 : 0, reason));
+    }
+
+    /** hsq_index_bam: record index of a level-0 BGZF BAM (the intermediate files of FastqAndBamFileMerger.java:131-133); `index` is an
+     *  hsq_bam_index: seven int64 (cap, n, n_ref, text_bytes, first_record, payload_bytes, payload_cap), three pointers, one int32. */
+    public void indexBam(MemorySegment file, long nBytes, MemorySegment index) { check(invokeInt(INDEX_BAM, ctx, file, nBytes, index)); }
 
     /** hsq_band_stats: {read ends aligned inside the band, of them redone with full matrices} of the last extend call. */
     public long[] bandStats() {

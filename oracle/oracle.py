@@ -295,3 +295,75 @@ def dedup_reduce_keys(keys, n_probes):
         stats.duplicate_pairs[pr] += sz - 1
         stats.max_pairs_per_uid[pr] = max(stats.max_pairs_per_uid[pr], sz)
     return is_best, gsize, stats
+
+
+def bam_index(data):
+    """CPU statement of hsq_index_bam: what a sequential reader of the BAM (htsjdk BAMFileReader / BAMRecordCodec: SAM/BAM format
+    specification 4.1-4.2) sees, record by record.  Inflates whatever level the blocks were written at.  Returns a dict with the
+    uncompressed stream, header sizes and, per record, the columns of include/hsq_b200.h's hsq_bam_index."""
+    import struct
+    import zlib
+    pos, stream = 0, bytearray()
+    data = bytes(data)
+    while pos < len(data):
+        if data[pos:pos + 4] != b"\x1f\x8b\x08\x04":
+            raise ValueError("not a BGZF block at %d" % pos)
+        xlen = struct.unpack_from("<H", data, pos + 10)[0]
+        x, bsize = pos + 12, None
+        while x < pos + 12 + xlen:
+            si1, si2, slen = data[x], data[x + 1], struct.unpack_from("<H", data, x + 2)[0]
+            if si1 == 66 and si2 == 67 and slen == 2:
+                bsize = struct.unpack_from("<H", data, x + 4)[0]
+            x += 4 + slen
+        if bsize is None:
+            raise ValueError("no BC field")
+        cdata = data[pos + 12 + xlen:pos + bsize + 1 - 8]
+        crc, isize = struct.unpack_from("<II", data, pos + bsize + 1 - 8)
+        raw = zlib.decompress(cdata, -15) if isize else b""
+        if len(raw) != isize or (zlib.crc32(raw) & 0xFFFFFFFF) != crc:
+            raise ValueError("BGZF block at %d: size or CRC mismatch" % pos)
+        stream += raw
+        pos += bsize + 1
+    stream = bytes(stream)
+    if stream[:4] != b"BAM\1":
+        raise ValueError("not a BAM stream")
+    l_text = struct.unpack_from("<i", stream, 4)[0]
+    p = 8 + l_text
+    n_ref = struct.unpack_from("<i", stream, p)[0]
+    p += 4
+    for _ in range(n_ref):
+        l_name = struct.unpack_from("<i", stream, p)[0]
+        p += 4 + l_name + 4
+    first = p
+    names = ("record", "qname", "cigar", "seq", "qual", "tags")
+    cols = {k + "_off": [] for k in names}
+    cols.update({k + "_len": [] for k in names})
+    for k in ("refid", "pos", "flag", "mapq", "next_refid", "pnext", "tlen", "ref_len"):
+        cols[k] = []
+    while p < len(stream):
+        bs = struct.unpack_from("<i", stream, p)[0]
+        ref_id, bpos, l_name, mapq, _bin, n_cig, flag, l_seq, nref, npos, tlen = struct.unpack_from("<iiBBHHHiiii", stream, p + 4)
+        name = p + 36
+        cigar = name + l_name
+        seq = cigar + 4 * n_cig
+        qual = seq + (l_seq + 1) // 2
+        tags = qual + l_seq
+        end = p + 4 + bs
+        if tags > end or end > len(stream) or stream[cigar - 1] != 0:
+            raise ValueError("broken record at %d" % p)
+        ref_len = 0
+        for c in range(n_cig):
+            op = struct.unpack_from("<I", stream, cigar + 4 * c)[0]
+            if (op & 15) in (0, 2, 3, 7, 8):
+                ref_len += op >> 4
+        for key, o, ln in (("record", p, bs + 4), ("qname", name, l_name - 1), ("cigar", cigar, n_cig), ("seq", seq, l_seq), ("qual", qual, l_seq),
+                           ("tags", tags, end - tags)):
+            cols[key + "_off"].append(o)
+            cols[key + "_len"].append(ln)
+        for key, v in (("refid", ref_id), ("pos", bpos + 1), ("flag", flag), ("mapq", mapq), ("next_refid", nref), ("pnext", npos + 1), ("tlen", tlen),
+                       ("ref_len", ref_len)):
+            cols[key].append(v)
+        p = end
+    out = {k: np.asarray(v, dtype=np.int64 if k.endswith("_off") else np.int32) for k, v in cols.items()}
+    out.update(stream=stream, n=len(cols["pos"]), n_ref=n_ref, text_bytes=l_text, first_record=first)
+    return out
