@@ -597,6 +597,57 @@ def next_row_numbers(ctx, probes, pairs, res):
                          "ms_device_incl_copies": ms_dev, "text_bytes_in": len(ptext), "text_bytes_out": int(len(g)), "records": int(nrec),
                          "cpu_port_records_per_s": nrec / dt_cpu, "cpu_sample": "the same text, 1 thread", "equals_cpu_port": bool(np.array_equal(g, c)),
                          "algorithmic_bytes_per_record": (len(ptext) + len(g)) / max(nrec, 1)}
+    # BASELINE.json configs[4], band axis at 2 x 150 bp (the full length x band grid: scripts/sweep_lengths.py, profiles/band_sweep_r2_*.jsonl):
+    # resident GCUPS of the capture stage with the opt-in band, the share of read ends redone with full matrices, results against band 0
+    from bioinformatics_b200.batches import ExtendResult
+    n_band = min(pairs.n, 1_000_000)
+    bp = pairs.head(n_band)
+    ctx.set_probes(probes)
+    band_rows, full = [], None
+    for band in (0, 8, 16, 32, 64):
+        ctx.configure(band=band)
+        ro = ExtendResult(n_band, 32, 64)
+        ctx.extend_stage(bp)
+        ctx.extend_run(32, 64)
+        ctx.extend_fetch(ro)
+        banded, redone = ctx.band_stats()
+        ctx.timer_start()
+        for _ in range(3):
+            ctx.extend_run(32, 64)
+        ms = ctx.timer_stop() / 3
+        if band == 0:
+            full = ro
+        same = all(np.array_equal(getattr(ro, f), getattr(full, f)) for f in ("primer_end", "score", "pos", "read_start", "read_stop", "nm", "tlen",
+                                                                              "cigar_len", "md_len", "ok", "pair_ok")) and \
+            ro.cigars() == full.cigars() and ro.mds() == full.mds() and ro.cells == full.cells
+        band_rows.append({"band": band if band else "full", "GCUPS_resident": ro.cells / ms / 1e6, "ms": ms, "read_ends_banded": banded,
+                          "read_ends_redone_in_full": redone, "fallback_rate": (redone / banded) if banded else None,
+                          "equals_full_matrices": bool(same)})
+    ctx.configure()
+    out["band_150bp"] = {"pairs": n_band, "rows": band_rows,
+                         "api": "hsq_config.band: staircase fill + score bound + in-band traceback, every other read end redone by the full kernel"}
+    # f2, binary side: record index of a level-0 BGZF BAM (the reference's intermediate files, FastqAndBamFileMerger.java:131-133)
+    from tests import bamio
+    rngb = np.random.default_rng(13)
+    n_bam = 200000 if pairs.n >= 250000 else 20000
+    seq150 = "ACGT" * 37 + "AC"
+    recs = [dict(name="%d" % (k // 2), flag=99 if k % 2 == 0 else 147, ref_id=int(k % 22), pos=int(rngb.integers(0, 10 ** 8)), mapq=60,
+                 cigar=[("M", 150)], seq=seq150, qual=bytes([30 + k % 10] * 150), next_ref_id=int(k % 22), next_pos=int(rngb.integers(0, 10 ** 8)),
+                 tlen=300, tags=b"NMC\x01") for k in range(n_bam)]
+    stream, _ = bamio.bam_stream(b"@HD\tVN:1.4\n", [("chr%d" % c, 10 ** 8) for c in range(1, 23)], recs)
+    bam = pinned_text(bamio.bgzf(stream))
+    dt, g = timed(lambda: ctx.index_bam(bam, cap=n_bam + 8))
+    ms_dev, ms_kernels = ctx.last_timing()[0], ctx.last_spans()[0]
+    t0 = time.perf_counter()
+    c = O.bam_index(bam.tobytes())
+    dt_cpu = time.perf_counter() - t0
+    gc = g.columns()
+    ing["index_bam"] = {"records_per_s": g.n / dt, "file_gb_per_s_host_to_host": len(bam) / dt / 1e9, "ms_host_to_host": dt * 1e3,
+                        "ms_device_incl_copies": ms_dev, "kernel_ms": ms_kernels, "file_bytes": int(len(bam)), "records": int(g.n),
+                        "exact_walk": int(g.exact_walk), "cpu_port_records_per_s": c["n"] / dt_cpu,
+                        "cpu_sample": "the same file, 1 thread, the oracle's Python parser (zlib + struct)",
+                        "equals_cpu_port": bool(g.n == c["n"] and all(np.array_equal(v, c[k]) for k, v in gc.items())),
+                        "algorithmic_bytes_per_record": 2 * len(bam) / max(g.n, 1) + 6 * 8 + 14 * 4}
     contigs = ["chr%d" % c for c in range(1, 23)]
     merged_text = pinned_text(synth.sam_text_of(case, seed=32, index_names=True))  # the merged BAM's records: names are FASTQ ordinals
     dt, g = timed(lambda: ctx.sam_mapped_records(merged_text, contigs))

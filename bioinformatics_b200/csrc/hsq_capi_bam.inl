@@ -7,7 +7,8 @@
 //   device : segments gathered into one contiguous stream; EVERY byte position is tested for "a record could start here" (sizes
 //            consistent, reference ids in range, read name NUL terminated); the survivors, in order, are the records if each one ends
 //            where the next begins -- checked for all of them at once.  Where that check fails (bytes inside a record that look like
-//            a record header) one thread walks the block_size chain instead: slow, exact, and not seen on real data.
+//            a record header: it happens) the records are the candidates on the path first -> next -> ... -> end, marked by binary
+//            lifting over the candidate list (log2(n) rounds of n-element kernels): exact, and still parallel.
 //   device : one thread per record: offsets / lengths of the variable fields, the fixed columns, reference length of the CIGAR.
 // BAM layout: SAM/BAM format specification 4.2 (htsjdk BAMRecordCodec writes it).
 #include <vector>
@@ -89,20 +90,59 @@ __global__ void bam_chain_check_kernel(const uint8_t* __restrict__ d, const int6
     }
 }
 
-// the exact walk: one thread follows block_size from the first record.  out_n = records, or -1 - (offset of the record that breaks)
-__global__ void bam_chain_walk_kernel(const uint8_t* __restrict__ d, int64_t first, int64_t end, int n_ref, int64_t cap, int64_t* __restrict__ cand,
-                                      int64_t* out_n) {
-    int64_t p = first, n = 0;
-    while (p < end) {
-        if (!bam_start_plausible(d, p, end, n_ref)) {
-            *out_n = -1 - p;
-            return;
+// ---- the exact chain when some candidate is not a record: path marking by binary lifting over the candidate list -------------
+// Node r < n is candidate r; node n = END (the end of the stream), node n + 1 = BAD (a successor that is not a candidate).
+// succ[r] = node of cand[r] + 4 + block_size; END and BAD point to themselves.
+__global__ void bam_succ_kernel(const uint8_t* __restrict__ d, const int64_t* __restrict__ cand, int64_t n, int64_t end, uint32_t* __restrict__ succ) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n + 2; r += stride) {
+        if (r >= n) {
+            succ[r] = (uint32_t)r;
+            continue;
         }
-        if (n < cap) cand[n] = p;
-        n++;
-        p += 4 + (int64_t)ld_u32(d + p);
+        const int64_t nxt = cand[r] + 4 + (int64_t)ld_u32(d + cand[r]);
+        uint32_t to = (uint32_t)(n + 1);
+        if (nxt == end) to = (uint32_t)n;
+        else {
+            int64_t lo = r + 1, hi = n;  // first candidate at or after nxt
+            while (lo < hi) {
+                const int64_t mid = (lo + hi) >> 1;
+                if (cand[mid] < nxt) lo = mid + 1;
+                else hi = mid;
+            }
+            if (lo < n && cand[lo] == nxt) to = (uint32_t)lo;
+        }
+        succ[r] = to;
     }
-    *out_n = n;
+}
+__global__ void bam_lift_kernel(const uint32_t* __restrict__ prev, int64_t n_nodes, uint32_t* __restrict__ next) {  // next = prev o prev
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n_nodes; r += stride) next[r] = prev[prev[r]];
+}
+// every marked node marks its 2^k-th successor (marked nodes are on the path from the first record, so what they mark is too)
+__global__ void bam_mark_kernel(const uint32_t* __restrict__ jump, int64_t n_nodes, uint8_t* __restrict__ mark) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n_nodes; r += stride)
+        if (mark[r]) mark[jump[r]] = 1;
+}
+__global__ void bam_mark_flags_kernel(const uint8_t* __restrict__ mark, const uint32_t* __restrict__ succ, const int64_t* __restrict__ cand, int64_t n,
+                                      int64_t* __restrict__ flags, unsigned long long* first_break) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n; r += stride) {
+        flags[r] = mark[r] ? 1 : 0;
+        if (mark[r] && succ[r] == (uint32_t)(n + 1)) atomicMin(first_break, (unsigned long long)cand[r]);
+    }
+}
+__global__ void bam_keep_marked_kernel(const int64_t* __restrict__ cand, const int64_t* __restrict__ flags, const int64_t* __restrict__ pos, int64_t n,
+                                       int64_t* __restrict__ rec) {
+    int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (; r < n; r += stride)
+        if (flags[r]) rec[pos[r]] = cand[r];
 }
 
 // reference bases a CIGAR consumes: M D N = X (ops 0 2 3 7 8)
@@ -301,18 +341,54 @@ extern "C" int32_t hsq_index_bam(hsq_ctx* ctx, const uint8_t* file, int64_t n_by
         HSQ_CUDA(ctx, cudaMemcpyAsync(&flag, d_flag, 4, cudaMemcpyDeviceToHost, ctx->stream));
         HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         n_rec = n_cand;
-        if (flag) {  // some candidate is not a record (or the file is broken): the exact walk decides
+        int64_t* d_rec = d_cand;
+        if (flag) {  // some candidate is not a record (or the file is broken): mark the path first -> ... -> end among the candidates
             out->exact_walk = 1;
-            bam_chain_walk_kernel<<<1, 1, 0, ctx->stream>>>(d, first, P, n_ref, max_records, d_cand, d_walk);
-            ctx->launches++;
-            int64_t walked = 0;
-            HSQ_CUDA(ctx, cudaMemcpyAsync(&walked, d_walk, 8, cudaMemcpyDeviceToHost, ctx->stream));
-            HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-            if (walked < 0) {
+            if (n_cand + 2 >= (1ll << 32)) return fail(ctx, HSQ_ERR_UNSUPPORTED, "hsq_index_bam: more than 2^32 record candidates");
+            if (n_cand == 0) {
                 timer.finish();
-                return fail(ctx, HSQ_ERR_MALFORMED, "hsq_index_bam: no alignment record can start at byte " + std::to_string(-1 - walked) + " of the uncompressed stream");
+                return fail(ctx, HSQ_ERR_MALFORMED, "hsq_index_bam: no alignment record can start at byte " + std::to_string(first) + " of the uncompressed stream");
             }
-            n_rec = walked;
+            const int64_t nodes = n_cand + 2;
+            int levels = 1;
+            while ((1ll << levels) < nodes) levels++;
+            // two jump tables (ping-pong: level k is needed only to build level k + 1 ... but the marking runs high to low, so all
+            // levels are kept), the marks, the flags and their scan
+            HSQ_CUDA(ctx, ctx->misc.ensure((size_t)levels * (size_t)nodes * 4 + (size_t)nodes + 64));
+            HSQ_CUDA(ctx, ctx->sort_d.ensure(std::max<size_t>((size_t)(3 * nodes + 8) * 8, 64)));
+            uint32_t* jump = ctx->misc.as<uint32_t>();
+            uint8_t* mark = reinterpret_cast<uint8_t*>(jump + (size_t)levels * (size_t)nodes);
+            int64_t* flags = ctx->sort_d.as<int64_t>();
+            int64_t* pos = flags + nodes;
+            int64_t* kept = pos + nodes + 1;
+            const unsigned g = (unsigned)std::min<int64_t>((nodes + 255) / 256, (int64_t)ctx->sm_count * 16);
+            bam_succ_kernel<<<g, 256, 0, ctx->stream>>>(d, d_cand, n_cand, P, jump);
+            for (int k = 1; k < levels; k++) bam_lift_kernel<<<g, 256, 0, ctx->stream>>>(jump + (size_t)(k - 1) * nodes, nodes, jump + (size_t)k * nodes);
+            HSQ_CUDA(ctx, cudaMemsetAsync(mark, 0, (size_t)nodes, ctx->stream));
+            HSQ_CUDA(ctx, cudaMemsetAsync(mark, 1, 1, ctx->stream));  // cand[0] is the first record (checked below), or nothing is
+            for (int k = levels - 1; k >= 0; k--) bam_mark_kernel<<<g, 256, 0, ctx->stream>>>(jump + (size_t)k * nodes, nodes, mark);
+            unsigned long long* d_break = reinterpret_cast<unsigned long long*>(d_walk);
+            HSQ_CUDA(ctx, cudaMemsetAsync(d_break, 0xff, 8, ctx->stream));
+            bam_mark_flags_kernel<<<g, 256, 0, ctx->stream>>>(mark, jump, d_cand, n_cand, flags, d_break);
+            ctx->launches += 2 * levels + 1;
+            HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)((nodes + SCAN_TILE) / SCAN_TILE + 2) * 8 + 16));
+            if ((rc = scan_i64(ctx, flags, n_cand, ctx->sort_c.as<int64_t>(), pos))) return rc;
+            bam_keep_marked_kernel<<<g, 256, 0, ctx->stream>>>(d_cand, flags, pos, n_cand, kept);
+            ctx->launches++;
+            struct { int64_t first_cand; unsigned long long brk; int64_t n_kept; uint8_t end_marked; } h{};
+            HSQ_CUDA(ctx, cudaMemcpyAsync(&h.first_cand, d_cand, 8, cudaMemcpyDeviceToHost, ctx->stream));
+            HSQ_CUDA(ctx, cudaMemcpyAsync(&h.brk, d_break, 8, cudaMemcpyDeviceToHost, ctx->stream));
+            HSQ_CUDA(ctx, cudaMemcpyAsync(&h.n_kept, pos + n_cand, 8, cudaMemcpyDeviceToHost, ctx->stream));
+            HSQ_CUDA(ctx, cudaMemcpyAsync(&h.end_marked, mark + n_cand, 1, cudaMemcpyDeviceToHost, ctx->stream));
+            HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+            if (h.first_cand != first || h.brk != ~0ull || !h.end_marked) {
+                timer.finish();
+                const int64_t at = h.first_cand != first ? first : (h.brk != ~0ull ? (int64_t)h.brk : first);
+                return fail(ctx, HSQ_ERR_MALFORMED, "hsq_index_bam: the chain of alignment records breaks at (or after) byte " + std::to_string(at) +
+                                                        " of the uncompressed stream");
+            }
+            n_rec = h.n_kept;
+            d_rec = kept;
         }
         out->n = n_rec;
         if (n_rec > out->cap) {
@@ -321,15 +397,15 @@ extern "C" int32_t hsq_index_bam(hsq_ctx* ctx, const uint8_t* file, int64_t n_by
         }
         if (n_rec) {
             const size_t cap = (size_t)out->cap;
-            HSQ_CUDA(ctx, ctx->sort_d.ensure(cap * HSQ_BAM_N_FIELDS * 8 + 16));
+            HSQ_CUDA(ctx, ctx->flags.ensure(cap * HSQ_BAM_N_FIELDS * 8 + 16));
             HSQ_CUDA(ctx, ctx->out_i32.ensure(cap * HSQ_BAM_N_VALUES * 4 + 16));
             bam_fields_kernel<<<(unsigned)std::min<int64_t>((n_rec + 255) / 256, (int64_t)ctx->sm_count * 16), 256, 0, ctx->stream>>>(
-                d, d_cand, n_rec, out->cap, ctx->sort_d.as<int64_t>(), ctx->out_i32.as<int32_t>());
+                d, d_rec, n_rec, out->cap, ctx->flags.as<int64_t>(), ctx->out_i32.as<int32_t>());
             ctx->launches++;
             span_end(ctx, 0);  // kernels only: the copies below are not part of the span
             HSQ_CUDA(ctx, cudaGetLastError());
             for (int f = 0; f < HSQ_BAM_N_FIELDS; f++)
-                if ((rc = d2h(ctx, out->off + (size_t)f * cap, ctx->sort_d.as<int64_t>() + (size_t)f * cap, (size_t)n_rec))) return rc;
+                if ((rc = d2h(ctx, out->off + (size_t)f * cap, ctx->flags.as<int64_t>() + (size_t)f * cap, (size_t)n_rec))) return rc;
             for (int v = 0; v < HSQ_BAM_N_VALUES; v++)
                 if ((rc = d2h(ctx, out->val + (size_t)v * cap, ctx->out_i32.as<int32_t>() + (size_t)v * cap, (size_t)n_rec))) return rc;
         }

@@ -573,8 +573,9 @@ int32_t hsq_index_sam(hsq_ctx* ctx, const uint8_t* text, int64_t n_bytes, hsq_sa
  * offset / size of part f of record k -- RECORD: the whole record incl. its block_size word (bytes); QNAME (bytes, without the NUL);
  * CIGAR (operations, 4 bytes each); SEQ (bases, 4 bit each); QUAL (bytes); TAGS (bytes) -- and val[v * cap + k] for the fixed
  * columns, POS and PNEXT 1-based as in SAM text, REF_LEN = reference bases the CIGAR consumes (alignment end = POS + REF_LEN - 1).
- * More records than cap: HSQ_ERR_OVERFLOW with n set.  exact_walk: 1 when bytes inside some record looked like a record header and
- * the index came from the sequential block_size walk instead of the parallel test (same result, slower). */
+ * More records than cap: HSQ_ERR_OVERFLOW with n set.  exact_walk: 1 when bytes inside some record looked like a record header, so
+ * that the records had to be picked from the candidates by following the block_size chain (path marking by binary lifting on the
+ * device; same result as a sequential reader's, a little slower than the direct test). */
 enum { HSQ_BAM_RECORD = 0, HSQ_BAM_QNAME = 1, HSQ_BAM_CIGAR = 2, HSQ_BAM_SEQ = 3, HSQ_BAM_QUAL = 4, HSQ_BAM_TAGS = 5, HSQ_BAM_N_FIELDS = 6 };
 enum { HSQ_BAM_REFID = 6, HSQ_BAM_POS = 7, HSQ_BAM_FLAG = 8, HSQ_BAM_MAPQ = 9, HSQ_BAM_NEXT_REFID = 10, HSQ_BAM_PNEXT = 11, HSQ_BAM_TLEN = 12,
        HSQ_BAM_REF_LEN = 13, HSQ_BAM_N_VALUES = 14 };
