@@ -144,6 +144,8 @@ static int ctx_init(hsq_ctx* ctx, const cudaDeviceProp& prop) {
         for (int e = 0; e < 2; e++) HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev_span[k][e]));
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
+    ctx->trim_events.assign(17, nullptr);
+    for (auto& ev : ctx->trim_events) HSQ_CUDA(nullptr, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     {   // the prep stream's short kernels should get SM slots ahead of the capture kernels' CTAs
         int lo = 0, hi = 0;
         HSQ_CUDA(nullptr, cudaDeviceGetStreamPriorityRange(&lo, &hi));
@@ -171,7 +173,7 @@ static int apply_config(hsq_ctx* ctx, const hsq_config* config) {
             return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "hsq_config.struct_bytes must be sizeof(hsq_config) of the caller's header");
         std::memcpy(&c, config, (size_t)config->struct_bytes);  // an older, shorter struct leaves the newer fields at their defaults
     }
-    if (c.extend_chunks < 0 || c.band < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative value in hsq_config");
+    if (c.extend_chunks < 0 || c.band < 0 || c.trim_chunks < 0) return fail(ctx, HSQ_ERR_INVALID_ARGUMENT, "negative value in hsq_config");
     ctx->cfg = c;
     return HSQ_OK;
 }
@@ -242,6 +244,8 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     for (int k = 0; k < hsq_ctx::N_EXTEND_SETS; k++)
         for (cudaEvent_t ev : {ctx->ev_in[k], ctx->ev_prep[k], ctx->ev_cap[k], ctx->ev_out[k]})
             if (ev) cudaEventDestroy(ev);
+    for (cudaEvent_t ev : ctx->trim_events)
+        if (ev) cudaEventDestroy(ev);
     for (cudaStream_t st : {ctx->s_cap[0], ctx->s_cap[1], ctx->s_prep, ctx->s_in, ctx->s_out, ctx->stream})
         if (st) cudaStreamDestroy(st);
     comm_release(ctx);

@@ -90,10 +90,7 @@ extern "C" int32_t hsq_trim_batch(hsq_ctx* ctx, const hsq_seqs* reads, const uin
     const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
     HSQ_CUDA(ctx, ctx->sort_c.ensure((size_t)n_tiles * 8 + 16));
     HSQ_CUDA(ctx, ctx->out_slots.ensure(2 * (size_t)total + 64));
-    if (total) {
-        HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->r1.ascii.p, reads->data, (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
-        HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q1.p, quals, (size_t)total, cudaMemcpyHostToDevice, ctx->stream));
-    }
+    // Phase 1: the offsets alone give every kept length and output offset (8 B in, 8 B out per read against 300 B of bases and qualities).
     HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->r1.offsets.p, reads->offsets, (size_t)(n + 1) * 8, cudaMemcpyHostToDevice, ctx->stream));
     int64_t* keep = ctx->sort_a.as<int64_t>();
     int64_t* d_out_off = ctx->sort_b.as<int64_t>();
@@ -109,13 +106,6 @@ extern "C" int32_t hsq_trim_batch(hsq_ctx* ctx, const hsq_seqs* reads, const uin
     scan_sums_kernel<<<1, SCAN_BLOCK, 0, ctx->stream>>>(ctx->sort_c.as<int64_t>(), n_tiles);
     scan_apply_kernel<<<(unsigned)n_tiles, SCAN_BLOCK, 0, ctx->stream>>>(keep, n, ctx->sort_c.as<int64_t>(), d_out_off);
     ctx->launches += 3;
-    if (n > 0) {
-        int64_t warps = n;
-        int blocks = (int)std::min<int64_t>((warps * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
-        trim_copy_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->q1.as<uint8_t>(), ctx->r1.offsets.as<int64_t>(),
-                                                         d_out_off, n, first, d_out_seq, d_out_qual);
-        ctx->launches++;
-    }
     span_end(ctx, 0);
     HSQ_CUDA(ctx, cudaGetLastError());
     HSQ_CUDA(ctx, cudaMemcpyAsync(out_offsets, d_out_off, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
@@ -125,10 +115,51 @@ extern "C" int32_t hsq_trim_batch(hsq_ctx* ctx, const hsq_seqs* reads, const uin
         timer.finish();
         return fail(ctx, w[0], "hsq_trim_batch: unable to trim: first base to keep is beyond the end of a read");
     }
-    const int64_t out_total = out_offsets[n];
-    if (out_total) {
-        HSQ_CUDA(ctx, cudaMemcpyAsync(out_seq, d_out_seq, (size_t)out_total, cudaMemcpyDeviceToHost, ctx->stream));
-        HSQ_CUDA(ctx, cudaMemcpyAsync(out_qual, d_out_qual, (size_t)out_total, cudaMemcpyDeviceToHost, ctx->stream));
+    // Phase 2: the bytes, in chunks of reads: H2D of chunk c + 1 | copy kernel of chunk c | D2H of chunk c - 1 on three streams (the two
+    // PCIe directions run at the same time; with one chunk this is copy in, kernel, copy out as before).
+    int n_chunks = ctx->cfg.trim_chunks > 0 ? ctx->cfg.trim_chunks : (int)std::min<int64_t>(8, std::max<int64_t>(1, total / (48ll << 20)));
+    n_chunks = (int)std::max<int64_t>(1, std::min<int64_t>(n_chunks, std::min<int64_t>(n, ((int64_t)ctx->trim_events.size() - 1) / 2)));
+    if (n_chunks > 1) HSQ_CUDA(ctx, cudaEventRecord(ctx->trim_events[0], ctx->stream));  // the copy streams start after phase 1
+    for (int c = 0; c < n_chunks && n > 0; c++) {
+        const int64_t a = n * c / n_chunks, b = n * (c + 1) / n_chunks;
+        const int64_t in0 = reads->offsets[a], in1 = reads->offsets[b], o0 = out_offsets[a], o1 = out_offsets[b];
+        cudaStream_t sin = n_chunks > 1 ? ctx->s_in : ctx->stream, sout = n_chunks > 1 ? ctx->s_out : ctx->stream;
+        cudaEvent_t ev_in = ctx->trim_events[(size_t)(1 + 2 * c)], ev_k = ctx->trim_events[(size_t)(2 + 2 * c)];
+        if (n_chunks > 1 && c == 0) {
+            HSQ_CUDA(ctx, cudaStreamWaitEvent(sin, ctx->trim_events[0], 0));
+            HSQ_CUDA(ctx, cudaStreamWaitEvent(sout, ctx->trim_events[0], 0));
+        }
+        if (in1 > in0) {
+            HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->r1.ascii.as<uint8_t>() + in0, reads->data + in0, (size_t)(in1 - in0), cudaMemcpyHostToDevice, sin));
+            HSQ_CUDA(ctx, cudaMemcpyAsync(ctx->q1.as<uint8_t>() + in0, quals + in0, (size_t)(in1 - in0), cudaMemcpyHostToDevice, sin));
+        }
+        if (n_chunks > 1) {
+            HSQ_CUDA(ctx, cudaEventRecord(ev_in, sin));
+            HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ev_in, 0));
+        }
+        {
+            const int64_t m = b - a;
+            if (n_chunks == 1) span_begin(ctx, 1);  // one chunk: the copy kernel alone (the stream reaches this after the copies in)
+            int blocks = (int)std::min<int64_t>((m * 32 + 255) / 256, (int64_t)ctx->sm_count * 16);
+            trim_copy_kernel<<<blocks, 256, 0, ctx->stream>>>(ctx->r1.ascii.as<uint8_t>(), ctx->q1.as<uint8_t>(), ctx->r1.offsets.as<int64_t>() + a,
+                                                             d_out_off + a, m, first, d_out_seq, d_out_qual);
+            ctx->launches++;
+            if (n_chunks == 1) span_end(ctx, 1);
+        }
+        if (n_chunks > 1) {
+            HSQ_CUDA(ctx, cudaEventRecord(ev_k, ctx->stream));
+            HSQ_CUDA(ctx, cudaStreamWaitEvent(sout, ev_k, 0));
+        }
+        if (o1 > o0) {
+            HSQ_CUDA(ctx, cudaMemcpyAsync(out_seq + o0, d_out_seq + o0, (size_t)(o1 - o0), cudaMemcpyDeviceToHost, sout));
+            HSQ_CUDA(ctx, cudaMemcpyAsync(out_qual + o0, d_out_qual + o0, (size_t)(o1 - o0), cudaMemcpyDeviceToHost, sout));
+        }
+    }
+    // (with more than one chunk the copy kernels wait for copies in: hsq_last_spans then holds the phase-1 kernels only)
+    HSQ_CUDA(ctx, cudaGetLastError());
+    if (n_chunks > 1) {  // the call's stream ends after the last copy back
+        HSQ_CUDA(ctx, cudaEventRecord(ctx->trim_events[0], ctx->s_out));
+        HSQ_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->trim_events[0], 0));
     }
     return timer.finish();
 }

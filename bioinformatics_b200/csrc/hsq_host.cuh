@@ -116,6 +116,7 @@ struct hsq_ctx {
     int work_slot = 0;                           // which pair of work counters the packed kernels of this run use
     cudaStream_t io = nullptr;      // stream the host<->device copies of the current call go to (default: stream)
     cudaStream_t s_in = nullptr, s_out = nullptr;
+    std::vector<cudaEvent_t> trim_events;       // hsq_trim_batch's chunk pipeline: [0] phase boundary, then (copied in, kernel done) per chunk
     cudaEvent_t ev_in[N_EXTEND_SETS] = {}, ev_prep[N_EXTEND_SETS] = {}, ev_cap[N_EXTEND_SETS] = {}, ev_out[N_EXTEND_SETS] = {};
     bool keep_counters = false;     // chunks after the first: keep the cell counter and the overflow flag
     int64_t ext_n = -1;  // staged extend batch

@@ -83,7 +83,7 @@ public final class HsqB200 implements AutoCloseable {
             ADDRESS.withName("str_off"), ADDRESS.withName("pool"), JAVA_LONG.withName("pool_cap"), JAVA_LONG.withName("pool_bytes"),
             ADDRESS.withName("pair_ok"), JAVA_LONG.withName("cells"));
     static final StructLayout CONFIG = MemoryLayout.structLayout(JAVA_INT.withName("struct_bytes"), JAVA_INT.withName("force_dp32"),
-            JAVA_INT.withName("force_dedup_radix"), JAVA_INT.withName("extend_chunks"), JAVA_INT.withName("uniform_chunks"), JAVA_INT.withName("band"));
+            JAVA_INT.withName("force_dedup_radix"), JAVA_INT.withName("extend_chunks"), JAVA_INT.withName("uniform_chunks"), JAVA_INT.withName("band"), JAVA_INT.withName("trim_chunks"));
     static final StructLayout DEDUP_KEY = MemoryLayout.structLayout(JAVA_LONG.withName("uid"), JAVA_LONG.withName("rank"), JAVA_INT.withName("probe"),
             JAVA_INT.withName("origin"));
     public static final int COMM_ID_BYTES = 128, ALIGN_PENALIZE_START = 1, ALIGN_PENALIZE_END = 2;
@@ -337,10 +337,10 @@ public final class HsqB200 implements AutoCloseable {
     }
 
     // ---- configuration ---------------------------------------------------------------------------------------------------
-    /** hsq_config: forceDp32 / forceDedupRadix / extendChunks / uniformChunks / band (0 = defaults). */
-    public void configure(int forceDp32, int forceDedupRadix, int extendChunks, int uniformChunks, int band) {
+    /** hsq_config: forceDp32 / forceDedupRadix / extendChunks / uniformChunks / band / trimChunks (0 = defaults). */
+    public void configure(int forceDp32, int forceDedupRadix, int extendChunks, int uniformChunks, int band, int trimChunks) {
         MemorySegment c = arena.allocate(CONFIG);
-        int[] v = {(int) CONFIG.byteSize(), forceDp32, forceDedupRadix, extendChunks, uniformChunks, band};
+        int[] v = {(int) CONFIG.byteSize(), forceDp32, forceDedupRadix, extendChunks, uniformChunks, band, trimChunks};
         for (int k = 0; k < v.length; k++) c.set(JAVA_INT, 4L * k, v[k]);
         check(invokeInt(CTX_CONFIGURE, ctx, c));
     }

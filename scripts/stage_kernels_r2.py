@@ -24,6 +24,10 @@ with Context(0) as ctx:
             b2, _, _ = ctx.dedup_packed(pk, u, 0, n_probes)
             assert (b2 == best).all()
             print("%-45s dedup_packed (host sums): call %.3f ms, keygen %.3f ms, group %.3f ms" % ((name, ctx.last_timing()[0]) + tuple(ctx.last_spans()[:2])), flush=True)
-            for sb, qb in ((pairs.r1, pairs.q1), (pairs.r2, pairs.q2)):
-                ctx.trim_batch(sb, qb, u + 22, 150 - 23, True)
-                print("%-45s trim_batch: call %.3f ms, kernels %.3f ms" % (name, ctx.last_timing()[0], ctx.last_spans()[0]), flush=True)
+            tout = (ctx.pinned_array(pairs.r1.data.nbytes), ctx.pinned_array(pairs.r1.data.nbytes), ctx.pinned_array(8 * (pairs.n + 1)).view(np.int64))
+            for chunks in (1, 0):
+                ctx.configure(trim_chunks=chunks)
+                for sb, qb in ((pairs.r1, pairs.q1), (pairs.r2, pairs.q2)):
+                    ctx.trim_batch(sb, qb, u + 22, 150 - 23, True, out=tout)
+                    print("%-45s trim_batch (trim_chunks %d, pinned in and out): call %.3f ms, spans %s" % (name, chunks, ctx.last_timing()[0], ctx.last_spans()[:2]), flush=True)
+            ctx.configure()

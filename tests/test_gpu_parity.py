@@ -318,6 +318,15 @@ def test_trim_vs_oracle(ctx):
     assert e.value.status == A.HSQ_ERR_OUT_OF_RANGE
     s, q = ctx.trim_batch([], [], 1, 5, True)
     assert s.n == 0
+    # the chunked copy-in | kernel | copy-out pipeline (hsq_config.trim_chunks) on a small batch: same bytes
+    for chunks in (2, 3, 8):
+        ctx.configure(trim_chunks=chunks)
+        gs, gq = ctx.trim_batch(reads, quals, 7, 99, True)
+        es, eq = O.trim_batch(reads, quals, 7, 99, True)
+        assert (gs.offsets == es.offsets).all() and (gs.data == es.data).all() and (gq.data == eq.data).all()
+        gs, gq = ctx.trim_batch(reads[:3], quals[:3], 7, 99, True)  # fewer reads than chunks
+        assert gs.strings() == [r[7:100] for r in reads[:3]]
+    ctx.configure()
 
 
 def test_resolve_multi_probe_vs_oracle(ctx):
