@@ -85,7 +85,7 @@ class ExtendPooledOut(C.Structure):
 
 class Config(C.Structure):
     _fields_ = [("struct_bytes", C.c_int32), ("force_dp32", C.c_int32), ("force_dedup_radix", C.c_int32), ("extend_chunks", C.c_int32),
-                ("uniform_chunks", C.c_int32), ("band", C.c_int32), ("trim_chunks", C.c_int32)]
+                ("uniform_chunks", C.c_int32), ("band", C.c_int32), ("trim_chunks", C.c_int32), ("l2_persist_rows", C.c_int32)]
 
     def __init__(self, **kw):
         super().__init__(**kw)

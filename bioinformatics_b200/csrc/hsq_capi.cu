@@ -84,9 +84,9 @@ int alloc_scratch(hsq_ctx* ctx, int64_t nthreads, int64_t nthreads2, int q_max, 
     if (n_strips < 1) n_strips = 1;
     const size_t rs = (size_t)r_max + 1, t1 = (size_t)nthreads, t2 = (size_t)nthreads2;
     HSQ_CUDA(ctx, ctx->ptr_words.ensure(std::max(t1 * sizeof(uint32_t), t2 * sizeof(uint2)) * n_strips * rs));
-    HSQ_CUDA(ctx, ctx->brow.ensure(std::max(t1, t2) * rs * sizeof(int32_t)));
+    HSQ_CUDA(ctx, ctx->brow.ensure(std::max(t1, t2) * (rs + 2) * sizeof(int32_t)));  // two spare columns: the packed fill prefetches the row above two columns ahead without a bounds test
     HSQ_CUDA(ctx, ctx->cols.ensure(t1 * (size_t)(q_max + r_max + 1) * sizeof(uint16_t) + 16));
-    HSQ_CUDA(ctx, ctx->colinfo.ensure(t2 * ((rs + 3) / 4 + 1) * sizeof(uint32_t) + 16));  // one byte per column, packed four to a word
+    HSQ_CUDA(ctx, ctx->colinfo.ensure(t2 * ((rs + 3) / 4 + 2) * sizeof(uint32_t) + 16));  // one byte per column, packed four to a word
     HSQ_CUDA(ctx, ctx->slow.ensure(t2 * KROWS * sizeof(uint32_t) + 16));
     pool->r_stride = r_max + 1;
     pool->ptr_words = ctx->ptr_words.as<uint32_t>();
@@ -135,6 +135,8 @@ const char* hsq_last_error(const hsq_ctx* ctx) { return ctx ? ctx->error.c_str()
 
 static int ctx_init(hsq_ctx* ctx, const cudaDeviceProp& prop) {
     ctx->sm_count = prop.multiProcessorCount;
+    ctx->l2_window_max = (size_t)prop.accessPolicyMaxWindowSize;
+    ctx->l2_persist_max = (size_t)prop.persistingL2CacheMaxSize;
     HSQ_CUDA(nullptr, cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev0));
     HSQ_CUDA(nullptr, cudaEventCreate(&ctx->ev1));

@@ -226,6 +226,21 @@ int extend_prep(hsq_ctx* ctx, int cigar_cap, int md_cap, int host_read_max, Exte
 
 // capture: the capture-target DP of the read ends that passed the primer stage + the per-pair finalize, on ctx->stream
 int extend_capture(hsq_ctx* ctx, const ExtendPlan& p) {
+    if (p.n > 0 && p.packed2 && ctx->cfg.l2_persist_rows && ctx->l2_window_max > 0 && ctx->l2_persist_max > 0) {
+        // the boundary rows are rewritten and re-read once per strip while 8 B per cell column of pointer words stream past them
+        const size_t bytes = (size_t)p.pool2.nthreads * (size_t)p.pool2.r_stride * 4;
+        if (!ctx->l2_limit_set) {
+            HSQ_CUDA(ctx, cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, std::min(ctx->l2_persist_max, bytes + (8u << 20))));
+            ctx->l2_limit_set = true;
+        }
+        cudaStreamAttrValue a{};
+        a.accessPolicyWindow.base_ptr = p.pool2.brow;
+        a.accessPolicyWindow.num_bytes = std::min(bytes, ctx->l2_window_max);
+        a.accessPolicyWindow.hitRatio = 1.0f;
+        a.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        a.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        HSQ_CUDA(ctx, cudaStreamSetAttribute(ctx->stream, cudaStreamAttributeAccessPolicyWindow, &a));
+    }
     if (p.n > 0) {
         if (p.packed2 && p.band > 0) {
             // pass 1: banded; the read ends it accepts move to the skip bucket.  pass 2: the others, full matrices.

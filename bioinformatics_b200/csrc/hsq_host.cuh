@@ -55,6 +55,8 @@ static constexpr int BAND_STATS_SLOT = 8;  // words 8, 9 of hsq_ctx::cells: read
 struct hsq_ctx {
     int device = 0;
     int sm_count = 0;
+    size_t l2_window_max = 0, l2_persist_max = 0;  // cudaDeviceProp: accessPolicyMaxWindowSize, persistingL2CacheMaxSize
+    bool l2_limit_set = false;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev_user0 = nullptr, ev_user1 = nullptr;
     std::string error;

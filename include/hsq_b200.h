@@ -385,6 +385,7 @@ typedef struct hsq_config {
     int32_t band;               /* opt-in band half-width of the capture-target DP; 0 = full matrices.  Results stay those of the
                                  * full matrix: an alignment whose band is touched is re-run in full (see hsq_band_stats) */
     int32_t trim_chunks;        /* chunks of hsq_trim_batch's copy-in | kernel | copy-out pipeline; 0 = automatic (by size), 1 = none */
+    int32_t l2_persist_rows;    /* 1: the boundary rows of the packed DP kernels are given an L2 persisting access window (experiment) */
 } hsq_config;
 
 /* ---- context ------------------------------------------------------------------------------ */

@@ -1,4 +1,4 @@
-"""Resident timing of hsq_extend_run (development aid).  Usage: quick_resident.py [pairs] [read_len] [band]
+"""Resident timing of hsq_extend_run (development aid).  Usage: quick_resident.py [pairs] [read_len] [band] [l2_persist_rows]
 HSQ_B200_LIB selects an alternative build of the library (experiments)."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -13,7 +13,8 @@ L = int(sys.argv[2]) if len(sys.argv) > 2 else 150
 probes = synth.make_probes(1000, target_len=(L - 50, L + 10))
 pairs = synth.make_pairs(probes, n, read_len=L, with_quals=False)
 band = int(sys.argv[3]) if len(sys.argv) > 3 else 0
-with Context(0, config={"band": band}) as ctx:
+persist = int(sys.argv[4]) if len(sys.argv) > 4 else 0
+with Context(0, config={"band": band, "l2_persist_rows": persist}) as ctx:
     ctx.set_probes(probes)
     out = ExtendResult(n, 32, 64)
     ctx.extend_stage(pairs)
