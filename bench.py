@@ -385,6 +385,54 @@ def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
                                    np.array_equal(resp.pooled.pos[:2 * m], res4.extend.pos[:2 * m]) and
                                    np.array_equal(resp.pooled.cigar_len[:2 * m], res4.extend.cigar_len[:2 * m]) and
                                    np.array_equal(resp.pooled.pair_ok[:m], res4.extend.pair_ok[:m]))
+        if world == 1:
+            # Two batches in flight on two contexts of the same GPU (one host thread each): a call is copy in -> kernels -> copy out in
+            # sequence, so a second context's copies run under the first one's kernels.  This is how a host with more than one batch
+            # queued (HsqBatcher: one flusher per context) is meant to drive a GPU.  Each context gets the first half of the batch.
+            import threading
+            from bioinformatics_b200._lib import Context as _Ctx
+            nh = n4 // 2
+            half = pairs4.head(nh)
+            pkh = PackedPairsHost(half.probe_id, pack_reads(half.r1, 2, ctx.pinned_array), pack_reads(half.r2, 2, ctx.pinned_array), None, None,
+                                  half.read_index, quality_sums(half.q1), quality_sums(half.q2))
+            ctx_b = _Ctx(rank)
+            ctx_b.set_probes(probes4)
+            outs = []
+            for c_ in (ctx, ctx_b):
+                o = DedupExtendResult(nh, NP4, pooled=PooledExtendResult(nh, 2 * nh * 24, fields=POOLED_FIELDS, alloc=c_.pinned_array))
+                for f in ("is_best", "group_size", "extended_pair"):
+                    a = getattr(o, f)
+                    setattr(o, f, c_.pinned_array(a.nbytes).view(a.dtype))
+                outs.append(o)
+
+            CALLS = 4  # per context, back to back: after the first call the two contexts run out of step (copies under kernels)
+
+            def run_calls(c_, o):
+                for _ in range(CALLS):
+                    c_.dedup_extend_packed(pkh, U4, 0, extend_duplicates=False, out=o)
+
+            def both():
+                th = [threading.Thread(target=run_calls, args=(c_, o)) for c_, o in zip((ctx, ctx_b), outs)]
+                for t in th:
+                    t.start()
+                for t in th:
+                    t.join()
+            dt1, r1_ = timed(lambda: run_calls(ctx, outs[0]))
+            dt1 /= CALLS
+            dt2, _ = timed(both)
+            dt2 /= CALLS
+            m_ = outs[0].n_extended
+            same2 = bool(outs[1].n_extended == m_ and np.array_equal(outs[0].is_best, outs[1].is_best) and
+                         np.array_equal(outs[0].pooled.pos[:2 * m_], outs[1].pooled.pos[:2 * m_]) and
+                         np.array_equal(outs[0].pooled.str_off[:2 * m_ + 1], outs[1].pooled.str_off[:2 * m_ + 1]))
+            c4["dedup_extend_packed_two_contexts"] = {
+                "read_pairs_per_s": 2 * nh / dt2, "ms_host_to_host": dt2 * 1e3, "pairs_per_context": int(nh),
+                "one_context_same_batch_read_pairs_per_s": nh / dt1, "both_contexts_equal": same2,
+                "calls_per_context": CALLS,
+                "api": "hsq_dedup_extend_packed on two contexts of one GPU from two host threads, half-size batches back to back: the copies of "
+                       "one context's call run under the kernels of the other's"}
+            del pkh, outs
+            ctx_b.close()
         c4["packing"] = {"host_s": pack_s, "note": "hsq_pack_reads + hsq_quality_sums over the batch (host helpers, all cores), outside the timed calls: "
                                                      "packed reads + quality sums are the input format of this path"}
         del pk4, resp
