@@ -147,3 +147,34 @@ def test_ingest_full_size():
         again = NameJoinHost(list(names[rec]), gs.flag[rec], gs.seq_len[rec], case["fq1_headers"], case["fq2_headers"], check_trim=False)
         g2 = ctx.join_names(again)
         assert g2.n_emitted == len(rec) and (g2.emitted()[0] == np.arange(len(rec))).all() and (g2.emitted()[1] == fq).all()
+
+
+@pytest.mark.gpu
+def test_band_equals_full_matrices_at_scale():
+    """configs[4] at bench scale (2 M read pairs, 2 x 150 bp): with the opt-in band every column of hsq_extend_out and every
+    CIGAR / MD string equals the full-matrix run's, and the two counters add up (banded = read ends that reached DP#2)."""
+    from bioinformatics_b200 import synth
+    from bioinformatics_b200._lib import Context
+    from bioinformatics_b200.batches import ExtendResult
+    n = 2_000_000
+    probes = synth.make_probes(1000)
+    pairs = synth.make_pairs(probes, n, read_len=150, ext_uid_len=10, with_quals=False)
+    with Context(0) as ctx:
+        ctx.set_probes(probes)
+        full = None
+        for band in (0, 12, 40):
+            ctx.configure(band=band)
+            out = ExtendResult(n, 32, 64)
+            ctx.extend_stage(pairs)
+            ctx.extend_run(32, 64)
+            ctx.extend_fetch(out)
+            banded, redone = ctx.band_stats()
+            if band == 0:
+                full = out
+                assert (banded, redone) == (0, 0)
+                continue
+            for f in ExtendResult.FIELDS_I32 + ("ok", "pair_ok", "overflow"):
+                assert np.array_equal(getattr(out, f), getattr(full, f)), f
+            assert out.cigars() == full.cigars() and out.mds() == full.mds() and out.cells == full.cells
+            reached = int(((full.primer_end >= 0) & (full.primer_end != A.HSQ_PRIMER_NOT_FOUND)).sum())
+            assert 0.95 * reached <= banded <= 2 * n and 0 <= redone < 0.2 * banded
