@@ -365,13 +365,11 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
     const uint32_t* cwp = &sc.ciw(jlo >> 2);
     const int64_t nt = sc.nthreads;
     const int4* prof_t = sc.prof + threadIdx.x;
-    // the row above arrives two columns ahead of its use, the profile columns a word (four columns) ahead: one column of cells
-    // does not cover the latency of a load that misses L1 (r2_d: 5 % of the kernel's samples waited here with one column of lead)
-    uint32_t up0 = 0, up1 = 0, ciw = 0, ciw_next = 0;
+    // the row above arrives one column ahead of its use, the profile columns a word (four columns) ahead
+    uint32_t up0 = 0, ciw = 0, ciw_next = 0;
     const int cw_last = jhi >> 2;
     if (!BAND || jlo <= jhi) {
         up0 = *browp;
-        if (jlo < jhi) up1 = browp[nt];
         ciw = *cwp;
         if ((jlo >> 2) < cw_last) ciw_next = cwp[nt];
     }
@@ -381,8 +379,7 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
     for (int j = jlo; j <= jhi; j++) {
         const uint32_t ci = (ciw >> (8 * (j & 3))) & 0xFFu;
         const uint32_t upx = up0;
-        up0 = up1;
-        if (j + 2 <= jhi) up1 = browp[2 * nt];
+        if (j < jhi) up0 = browp[nt];  // (two columns ahead costs more in register moves than the wait it saves: +2 % this way)
         if ((j & 3) == 3) {
             ciw = ciw_next;
             cwp += nt;

@@ -312,6 +312,7 @@ __global__ void __launch_bounds__(DP2_BLOCK, 5) primer2_kernel(DeviceProbes prob
 
 // Stage 2, packed: two read ends of the same DP#2 shape per thread, cells as u16x2 halves (hsq_dp2.cuh).
 // BAND (hsq_config.band > 0): the fill computes the staircase of band_cols only.  A read end keeps its banded result only if
+//   (0) its matrix is much larger than the band: min(Q, R) >= 2 * band + 16,
 //   (1) its score is above what any path that starts inside the band and reaches a diagonal |j - i| = band can score:
 //       match * min(Q, R) + gapStart + (band - 1) * gapExtend (such a path carries a net run of >= band gaps), and
 //   (2) its traceback stays on the diagonals |j - i| < band (terminal free-gap cells excepted);
@@ -349,6 +350,13 @@ __device__ __forceinline__ void capture2_body(const DeviceProbes& probes, const 
         const int start_a = out.primer_end[ma] + 1, start_b = out.primer_end[mb] + 1;
         SeqView rwa = sub_view(va.read, start_a, va.read.len - start_a);  // read[e+1 .. L-1] (:210)
         SeqView rwb = sub_view(vb.read, start_b, vb.read.len - start_b);
+        if (BAND && min(rwa.len, va.capture.len) < 2 * band + KROWS) {
+            // a matrix that is not much larger than the band: the band says nothing about where in it the alignment lies (a
+            // three-base target matches anywhere along a read); both read ends keep their keys and go to the full pass
+            n_banded += n_here;
+            n_redo += n_here;
+            continue;
+        }
         int score[2];
 #ifdef HSQ_EXPERIMENT_SAMEREF
         dp_fill2<true, BAND>(va.capture, vb.capture, rwa, rwb, sp_user, 0, 0, sc, score, band);  // :211

@@ -47,8 +47,10 @@ def test_band_results_equal_full_matrices(band):
     reached = int((got.primer_end >= 0).sum())
     assert 0 < banded <= 2 * pairs.n and banded >= reached * 0.9  # every read end that reached DP#2 went through the band first
     assert 0 < redone <= banded                                    # the long indels (and the unaligned read ends) were redone in full
-    if band >= 16:
+    if 16 <= band <= 32:
         assert redone < banded * 0.6                               # ... and a good part of the read ends was not
+    if band == 64:
+        assert redone > 0.9 * banded                               # 2 * 64 + 16 rows and columns: hardly a matrix of a 150-base read is that large
 
 
 def test_band_off_and_unavailable():
@@ -85,3 +87,48 @@ def test_band_through_the_chunked_and_packed_calls(chunks):
         from tests.test_packed import assert_pooled_equal, packed_pairs_of
         assert_pooled_equal(ctx.extend_packed(packed_pairs_of(pairs, 2)), exp)
         assert ctx.band_stats() == (banded, redone)
+
+
+@pytest.mark.parametrize("band", [2, 5, 16, 40])
+def test_band_on_adversarial_shapes(band):
+    """Random reads against random probes, capture targets of 1 .. 170 bases against read remainders of 0 .. 160 (targets much shorter
+    and much longer than the read, so the free terminal gaps run along the last column or the last row for most of the matrix), IUPAC
+    primers, N in reads, three scorers the band accepts and one it must ignore: every result equals the oracle's full matrices."""
+    from bioinformatics_b200.batches import ProbeTableHost
+    rng = np.random.default_rng(900 + band)
+    n_probes, n = 40, 1500
+    ext = [H.random_seq(rng, int(rng.integers(5, 30)), "ACGTN" if k % 5 == 0 else "ACGT") for k in range(n_probes)]
+    lig = [H.random_seq(rng, int(rng.integers(5, 30))) for _ in range(n_probes)]
+    tgt = [H.random_seq(rng, int(rng.integers(1, 170)), "ACGTR" if k % 7 == 0 else "ACGT") for k in range(n_probes)]
+    z = np.arange(n_probes, dtype=np.int32) * 500
+    probes = ProbeTableHost(np.arange(n_probes) % 2, z + 10, z + 30, z + 300, z + 320, z + 31, z + 299, ext, lig, tgt)
+    pid = rng.integers(0, n_probes, n)
+    r1, r2 = [], []
+    for k in range(n):
+        p = int(pid[k])
+        mol = ext[p].replace("N", "A") + tgt[p].replace("R", "G") + lig[p]
+        rc = mol[::-1].translate(str.maketrans("ACGT", "TGCA"))
+        L = int(rng.integers(12, 190))
+        if k % 4 == 0:
+            a, b = H.random_seq(rng, int(rng.integers(0, 160))), H.random_seq(rng, int(rng.integers(0, 160)))
+        else:
+            shift = H.random_seq(rng, int(rng.integers(0, 12))) if k % 3 == 0 else ""  # reads that start off the expected diagonal
+            a = (H.random_seq(rng, 6) + H.mutate(rng, mol[:len(ext[p])], 0.02, 0.0) + shift + H.mutate(rng, mol[len(ext[p]):], 0.04, 0.03) + H.random_seq(rng, 200))[:L]
+            b = (H.mutate(rng, rc, 0.04, 0.03) + H.random_seq(rng, 200))[:L]
+            if k % 4 == 3:
+                a = a.replace("A", "N", 1)
+        r1.append(a)
+        r2.append(b)
+    pairs = PairBatchHost(pid, r1, r2)
+    with Context(0, config={"band": band}) as ctx:
+        ctx.set_probes(probes)
+        for sc in (scorer(), scorer(2, -3, -2, -4), scorer(5, -4, 0, -7), scorer(1, -4, 1, 2)):
+            ctx.set_scorer(sc)
+            got = ctx.extend_batch(pairs, cigar_cap=1600, md_cap=2400)
+            exp = O.extend_batch(probes, pairs, sc, cigar_cap=1600, md_cap=2400, nthreads=8)
+            H.assert_extend_equal(got, exp)
+            banded, redone = ctx.band_stats()
+            if sc.gap_extend > 0:
+                assert banded == 0  # gapExtend > 0: not a scorer the acceptance bound holds for, full matrices
+            else:
+                assert banded > 0 and redone > 0
