@@ -379,7 +379,7 @@ __device__ __forceinline__ void dp_strip2(const SeqView& refA, const SeqView& re
     for (int j = jlo; j <= jhi; j++) {
         const uint32_t ci = (ciw >> (8 * (j & 3))) & 0xFFu;
         const uint32_t upx = up0;
-        if (j < jhi) up0 = browp[nt];  // (two columns ahead costs more in register moves than the wait it saves: +2 % this way)
+        if (j < jhi) up0 = browp[nt];  // (two columns ahead costs more in register moves than the wait it saves; so does dropping the test)
         if ((j & 3) == 3) {
             ciw = ciw_next;
             cwp += nt;
