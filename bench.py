@@ -424,7 +424,7 @@ def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
             m_ = outs[0].n_extended
             same2 = bool(outs[1].n_extended == m_ and np.array_equal(outs[0].is_best, outs[1].is_best) and
                          np.array_equal(outs[0].pooled.pos[:2 * m_], outs[1].pooled.pos[:2 * m_]) and
-                         np.array_equal(outs[0].pooled.str_off[:2 * m_ + 1], outs[1].pooled.str_off[:2 * m_ + 1]))
+                         np.array_equal(outs[0].pooled.str_off[:2 * m_], outs[1].pooled.str_off[:2 * m_]))
             c4["dedup_extend_packed_two_contexts"] = {
                 "read_pairs_per_s": 2 * nh / dt2, "ms_host_to_host": dt2 * 1e3, "pairs_per_context": int(nh),
                 "one_context_same_batch_read_pairs_per_s": nh / dt1, "both_contexts_equal": same2,
@@ -433,10 +433,46 @@ def stage_numbers(ctx, args, rank, world, dist, barrier, max_over_ranks):
                        "one context's call run under the kernels of the other's"}
             del pkh, outs
             ctx_b.close()
+        # keys first: the reduction from 20 bytes per pair, then the reads in chunks under the kernels (same results)
+        from bioinformatics_b200._lib import uid_keys as _uid_keys
+        t0 = time.perf_counter()
+        keys4 = _uid_keys(pk4.r1, pk4.r2, U4, 0)
+        keys_s = time.perf_counter() - t0
+        pk_keys = ctx.pinned_array(keys4.nbytes).view(np.uint64)
+        pk_keys[:] = keys4
+        for nm_ in ("qsum1", "qsum2"):
+            a_ = getattr(pk4, nm_)
+            p_ = ctx.pinned_array(a_.nbytes).view(a_.dtype)
+            p_[:] = a_
+            setattr(pk4, nm_, p_)
+        resk = DedupExtendResult(n4, NP4, pooled=PooledExtendResult(n4, 2 * n4 * 24, fields=POOLED_FIELDS, alloc=ctx.pinned_array))
+        for f in ("is_best", "group_size", "extended_pair"):
+            a = getattr(resk, f)
+            setattr(resk, f, ctx.pinned_array(a.nbytes).view(a.dtype))
+        keys_same = True
+        for mark in (False, True):
+            dt, r = timed(lambda: ctx.dedup_extend_packed_keys(pk4, pk_keys, U4, 0, extend_duplicates=mark, sharded=world > 1, out=resk))
+            key = "dedup_extend_packed_keys_mark_duplicates" if mark else "dedup_extend_packed_keys"
+            c4[key] = {"read_pairs_per_s": n4 * world / dt, "ms_host_to_host": dt * 1e3, "pairs_extended_this_rank": int(r.n_extended),
+                       "api": "hsq_dedup_extend_packed_keys (sharded=%d): uid keys + quality sums + probe + read index first (20 B/pair), reduction, "
+                              "then the packed reads in chunks copied in under the extension of the previous chunk" % (world > 1)}
+            ms = trim_ms_per_pair * n4 + dt * 1e3
+            c4["trim_plus_" + key] = {"read_pairs_per_s": n4 * world / (ms * 1e-3), "ms_host_to_host": ms}
+            ctx.dedup_extend_packed(pk4, U4, 0, extend_duplicates=mark, sharded=world > 1, out=resp)
+            m = resp.n_extended
+            keys_same = bool(keys_same and r.n_extended == m and np.array_equal(resk.is_best, resp.is_best) and
+                             np.array_equal(resk.extended_pair[:m], resp.extended_pair[:m]) and
+                             all(np.array_equal(getattr(resk.pooled, f)[:2 * m], getattr(resp.pooled, f)[:2 * m])
+                                 for f in ("pos", "read_start", "read_stop", "nm", "cigar_len", "md_len", "ok")) and
+                             np.array_equal(resk.pooled.str_off[:2 * m], resp.pooled.str_off[:2 * m]) and
+                             resk.pooled.pool_bytes == resp.pooled.pool_bytes and
+                             np.array_equal(resk.pooled.pool[:resk.pooled.pool_bytes], resp.pooled.pool[:resp.pooled.pool_bytes]))
+        c4["uid_keys_host_s"] = keys_s
+        del resk
         c4["packing"] = {"host_s": pack_s, "note": "hsq_pack_reads + hsq_quality_sums over the batch (host helpers, all cores), outside the timed calls: "
                                                      "packed reads + quality sums are the input format of this path"}
         del pk4, resp
-        c4["parity"] = {"fused_flags_equal_dedup": bool(np.array_equal(res4.is_best, best)), "packed_call_equals_ascii_call": packed_same,
+        c4["parity"] = {"fused_flags_equal_dedup": bool(np.array_equal(res4.is_best, best)), "packed_call_equals_ascii_call": packed_same, "keys_first_call_equals_packed_call": keys_same,
                         "unique_equals_sum_of_probe_counters": bool(_sum_ranks(dist, int(best.sum())) == int(st.unique_pairs.sum()))}
         # the sharded answer against the oracle on a sample gathered to rank 0
         if world > 1:

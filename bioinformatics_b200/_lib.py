@@ -24,7 +24,7 @@ EXPORTS = ("hsq_ctx_create", "hsq_ctx_destroy", "hsq_last_error", "hsq_version",
            "hsq_set_find_sequences", "hsq_find_candidates", "hsq_find_matches", "hsq_index_fastq", "hsq_trim_fastq", "hsq_index_sam", "hsq_sam_mapped_records", "hsq_join_names", "hsq_gather_rows", "hsq_coordinate_order",
            "hsq_ctx_create_ex", "hsq_ctx_configure", "hsq_packed_bytes", "hsq_pack_reads", "hsq_quality_sums", "hsq_unpack_reads",
            "hsq_extend_packed", "hsq_dedup_packed", "hsq_comm_unique_id", "hsq_comm_init_rank", "hsq_comm_init_all", "hsq_comm_destroy",
-           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed", "hsq_variable_length_uid", "hsq_align_scores_noalloc", "hsq_band_stats", "hsq_dedup_batch_report", "hsq_pair_reasons", "hsq_index_bam")
+           "hsq_dedup_sharded", "hsq_dedup_extend_sharded", "hsq_dedup_extend_multi_gpu", "hsq_last_spans", "hsq_dedup_extend_packed", "hsq_variable_length_uid", "hsq_align_scores_noalloc", "hsq_band_stats", "hsq_dedup_batch_report", "hsq_pair_reasons", "hsq_index_bam", "hsq_uid_keys", "hsq_dedup_extend_packed_keys")
 _NOT_STATUS = {"hsq_last_error": C.c_char_p, "hsq_version": C.c_char_p, "hsq_ctx_destroy": None, "hsq_packed_bytes": C.c_int64}
 
 
@@ -122,6 +122,17 @@ def quality_sums(quals, threads=0):
     st = lib.hsq_quality_sums(A.ptr(quals.data, A.u8p), A.ptr(quals.offsets, A.i64p), C.c_int64(quals.n), A.ptr(out, A.i16p), C.c_int32(threads))
     if st != 0:
         raise HsqError(st, lib.hsq_last_error(None).decode())
+    return out
+
+
+def uid_keys(r1, r2, ext_uid_len, lig_uid_len):
+    """hsq_uid_keys (host helper): uint64 UID code per pair from two PackedReadsHost."""
+    lib = load()
+    out = np.zeros(r1.n, dtype=np.uint64)
+    c1, c2 = r1.c(), r2.c()
+    st = lib.hsq_uid_keys(C.byref(c1), C.byref(c2), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len), out.ctypes.data_as(C.POINTER(C.c_uint64)))
+    if st != 0:
+        raise HsqError(st, "hsq_uid_keys failed (a UID holds a base other than A/C/G/T, or a read is shorter than its UID)")
     return out
 
 
@@ -515,6 +526,20 @@ class Context:
         pc, oc = pairs.c(), out.c()
         st = self.lib.hsq_dedup_extend_packed(self.h, C.byref(pc), C.c_int32(ext_uid_len), C.c_int32(lig_uid_len),
                                               C.c_int32(1 if extend_duplicates else 0), C.c_int32(1 if sharded else 0), C.byref(oc))
+        out.finish()
+        self._check(st)
+        return out
+
+    def dedup_extend_packed_keys(self, pairs: PackedPairsHost, uid, ext_uid_len, lig_uid_len, extend_duplicates=False, sharded=False, out=None,
+                                 pool_cap=None, n_probes=None):
+        """hsq_dedup_extend_packed_keys: the same probe task, reduction from (uid, quality sums, probe, read index) first, reads in chunks."""
+        if out is None:
+            out = DedupExtendResult(pairs.n, n_probes or self.n_probes, pooled=PooledExtendResult(pairs.n, pool_cap if pool_cap is not None else 2 * pairs.n * 48))
+        uid = np.ascontiguousarray(uid, dtype=np.uint64)
+        pc, oc = pairs.c(), out.c()
+        st = self.lib.hsq_dedup_extend_packed_keys(self.h, C.byref(pc), uid.ctypes.data_as(C.POINTER(C.c_uint64)), C.c_int32(ext_uid_len),
+                                                   C.c_int32(lig_uid_len), C.c_int32(1 if extend_duplicates else 0), C.c_int32(1 if sharded else 0),
+                                                   C.byref(oc))
         out.finish()
         self._check(st)
         return out

@@ -220,7 +220,7 @@ void hsq_ctx_destroy(hsq_ctx* ctx) {
     hsq::DevBuf* bufs[] = {&ctx->p_rev, &ctx->p_ext_start, &ctx->p_ext_stop, &ctx->p_lig_start, &ctx->p_lig_stop, &ctx->q1, &ctx->q2,
                            &ctx->probe_id, &ctx->read_index, &ctx->ptr_words, &ctx->brow, &ctx->cols, &ctx->status, &ctx->cells,
                            &ctx->misc, &ctx->out_i32, &ctx->out_u8, &ctx->out_slots, &ctx->pair_ok, &ctx->sort_a, &ctx->sort_b,
-                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->alt_probe_id, &ctx->rg_start, &ctx->rg_end,
+                           &ctx->sort_c, &ctx->sort_d, &ctx->sort_tmp, &ctx->flags, &ctx->slow, &ctx->colinfo, &ctx->kf_pos, &ctx->kf_local, &ctx->alt_probe_id, &ctx->rg_start, &ctx->rg_end,
                            &ctx->rg_value, &ctx->rg_off, &ctx->dd_u8, &ctx->dd_i32, &ctx->fi_start, &ctx->fi_len, &ctx->fi_refs, &ctx->fi_size, &ctx->pool_tmp, &ctx->pool_cursor, &ctx->pool_dev,
                            &ctx->cm_send, &ctx->cm_recv, &ctx->cm_i32, &ctx->cm_cnt, &ctx->cm_tie, &ctx->cm_probe};
     for (auto* b : bufs) b->release();
@@ -308,6 +308,7 @@ int32_t hsq_last_timing(const hsq_ctx* ctx, float* kernel_ms, int32_t* launches)
 #include "hsq_capi_packed.inl"
 #include "hsq_capi_comm.inl"
 #include "hsq_capi_pipeline.inl"
+#include "hsq_capi_keysfirst.inl"
 #include "hsq_capi_records.inl"
 #include "hsq_capi_find.inl"
 #include "hsq_capi_ingest.inl"

@@ -408,6 +408,9 @@ struct ExtendChunkIO {
     std::function<int(int64_t a, int64_t m)> stage;
     // device -> host delivery of the active set's results for the chunk, on ctx->io (the set's capture kernels have finished)
     std::function<int(int64_t a, int64_t m)> fetch;
+    // optional: runs on the prep stream after the chunk's copies have arrived and before its prep; may replace the staged pairs by a
+    // subset of them (hsq_dedup_extend_packed_keys: the unique pairs) and says how many pairs the prep is to see
+    std::function<int(int64_t a, int64_t m, int64_t* m_out)> filter;
 };
 
 // A large batch flows through
@@ -471,6 +474,16 @@ int extend_pipelined(hsq_ctx* ctx, int64_t n, int cigar_cap, int md_cap, int n_c
         HSQ_STEP(cudaStreamWaitEvent(ctx->s_prep, ctx->ev_in[k], 0));
         ctx->stream = ctx->s_prep;
         ctx->work_slot = k;
+        if (io.filter) {
+            int64_t m_eff = m;
+            r = io.filter(a, m, &m_eff);
+            if (r) {
+                ctx->stream = main_stream;
+                ctx->work_slot = 0;
+                return r;
+            }
+            ctx->ext_n = m_eff;
+        }
         r = extend_prep(ctx, cigar_cap, md_cap, read_max, &plans[(size_t)c]);
         ctx->stream = main_stream;
         ctx->work_slot = 0;

@@ -66,7 +66,8 @@ void swap_read_buffers(hsq_ctx* ctx) {
 }
 
 // compacts the flagged pairs of the staged batch (ctx->r1/r2/probe_id) into the second buffer set; returns their number
-int compact_survivors(hsq_ctx* ctx, int64_t n, const uint8_t* d_keep, int32_t* d_list, int64_t* m_out) {
+// known_m >= 0: the caller knows how many pairs are flagged (and the batch holds device codes): nothing here waits for the device
+int compact_survivors(hsq_ctx* ctx, int64_t n, const uint8_t* d_keep, int32_t* d_list, int64_t* m_out, int64_t known_m = -1) {
     const size_t nn = (size_t)n;
     int rc;
     const int64_t n_tiles = (n + 1 + SCAN_TILE - 1) / SCAN_TILE;
@@ -81,9 +82,11 @@ int compact_survivors(hsq_ctx* ctx, int64_t n, const uint8_t* d_keep, int32_t* d
     ctx->launches++;
     if ((rc = scan_i64(ctx, a, n, tiles, b))) return rc;
     int64_t* h_m = reinterpret_cast<int64_t*>(ctx->h_cells) + 1;  // pinned
-    HSQ_CUDA(ctx, cudaMemcpyAsync(h_m, b + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
-    HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    const int64_t m = *h_m;
+    if (known_m < 0) {
+        HSQ_CUDA(ctx, cudaMemcpyAsync(h_m, b + n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        HSQ_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    const int64_t m = known_m < 0 ? *h_m : known_m;
     *m_out = m;
     const size_t mm = (size_t)m;
     HSQ_CUDA(ctx, ctx->alt_probe_id.ensure(mm * 4 + 16));
@@ -123,6 +126,12 @@ int compact_survivors(hsq_ctx* ctx, int64_t n, const uint8_t* d_keep, int32_t* d
         }
     }
     HSQ_CUDA(ctx, cudaGetLastError());
+    if (known_m >= 0 && ctx->r1.packed_bits < 0 && ctx->r2.packed_bits < 0) {
+        // device codes are not encoded again: the totals only size buffers, and the uncompacted totals bound them
+        ctx->alt_r1.total = ctx->r1.total;
+        ctx->alt_r2.total = ctx->r2.total;
+        return HSQ_OK;
+    }
     // totals of the compacted sides (needed by the encoder's launch size)
     int64_t* h_tot = reinterpret_cast<int64_t*>(ctx->h_cells) + 2;
     HSQ_CUDA(ctx, cudaMemcpyAsync(h_tot, ctx->alt_r1.offsets.as<int64_t>() + m, 8, cudaMemcpyDeviceToHost, ctx->stream));

@@ -91,6 +91,7 @@ struct hsq_ctx {
     hsq::DevBuf cm_send, cm_recv, cm_i32, cm_cnt, cm_tie, cm_probe;
     int64_t* h_counts = nullptr;  // pinned: the world x (world + 1) count matrix
     hsq::DevBuf pool_tmp, pool_cursor, pool_dev;  // pooled CIGAR / MD delivery (hsq_extend_packed)
+    hsq::DevBuf kf_pos, kf_local;  // hsq_dedup_extend_packed_keys: positions of the kept pairs, a chunk's local survivor list
     hsq::DevBuf dd_u8, dd_i32;  // hsq_dedup_extend_batch: dedup answers kept while the extend stage reuses the output buffers
     int64_t rg_n = -1;
     int32_t rg_contigs = 0;

@@ -698,6 +698,19 @@ int32_t hsq_extend_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs, hsq_exten
 int32_t hsq_dedup_packed(hsq_ctx* ctx, const hsq_packed_pairs* pairs, int32_t ext_uid_len, int32_t lig_uid_len, uint8_t* is_best,
                          int32_t* group_size, hsq_probe_stats* stats);
 
+/* Host helper (no device): the UID code of every pair from its packed reads, as the key generation computes it -- R1[0:u] ++ R2[0:v],
+ * 2 bit per base in the order A, C, G, T, first base most significant (u + v <= 32).  A base other than A/C/G/T inside a UID (an
+ * exception of a 2-bit read, an IUPAC nibble of a 4-bit one): HSQ_ERR_UNSUPPORTED, as for hsq_dedup_batch; a read shorter than its
+ * UID: HSQ_ERR_OUT_OF_RANGE. */
+int32_t hsq_uid_keys(const hsq_packed_reads* r1, const hsq_packed_reads* r2, int32_t ext_uid_len, int32_t lig_uid_len, uint64_t* out);
+
+/* hsq_dedup_extend_packed with the reduction fed by keys: uid_keys (hsq_uid_keys), pairs->qsum1 / qsum2 (hsq_quality_sums), probe_id and
+ * read_index -- 20 bytes per pair -- go to the device first and are reduced; the reads then follow in chunks, each copied in while the
+ * previous one is aligned, cut down to its unique pairs on the device and extended.  Same results, slot for slot; what changes is that
+ * the copy of the reads (80 of the 100 bytes per pair) no longer waits in front of the kernels.  All four key inputs are required. */
+int32_t hsq_dedup_extend_packed_keys(hsq_ctx* ctx, const hsq_packed_pairs* pairs, const uint64_t* uid_keys, int32_t ext_uid_len,
+                                     int32_t lig_uid_len, int32_t extend_duplicates, int32_t sharded, hsq_dedup_extend_out* out);
+
 /* hsq_dedup_extend_batch for a packed batch with pooled results (out->extend_pooled; out->extend is not used).  With host-made quality
  * sums (pairs->qsum1 / qsum2) about 100 bytes per pair cross PCIe instead of 624.  sharded != 0: the reduction is the collective of
  * hsq_dedup_extend_sharded over the context's communicator. */

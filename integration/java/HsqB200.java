@@ -171,6 +171,9 @@ public final class HsqB200 implements AutoCloseable {
     private static final MethodHandle DEDUP_BATCH_REPORT = fn("hsq_dedup_batch_report",
             FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle PAIR_REASONS = fn("hsq_pair_reasons", FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, JAVA_INT, ADDRESS));
+    private static final MethodHandle UID_KEYS = fn("hsq_uid_keys", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, ADDRESS));
+    private static final MethodHandle DEDUP_EXTEND_PACKED_KEYS = fn("hsq_dedup_extend_packed_keys",
+            FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, JAVA_INT, JAVA_INT, ADDRESS));
     private static final MethodHandle INDEX_BAM = fn("hsq_index_bam", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, JAVA_LONG, ADDRESS));
     private static final MethodHandle BAND_STATS = fn("hsq_band_stats", FunctionDescriptor.of(JAVA_INT, ADDRESS, ADDRESS, ADDRESS));
     private static final MethodHandle TIMER_START = fn("hsq_timer_start", FunctionDescriptor.of(JAVA_INT, ADDRESS));
@@ -499,6 +502,18 @@ public final class HsqB200 implements AutoCloseable {
     /** hsq_pair_reasons (host helper): one HSQ_PAIR_* code per pair of a probe task's outputs -- what ReadNameTracking's messages say. */
     public void pairReasons(MemorySegment dedupExtendOut, long n, boolean extendDuplicates, MemorySegment reason) {
         check(invokeInt(PAIR_REASONS, dedupExtendOut, n, extendDuplicates ? 1 : 0, reason));
+    }
+
+    /** hsq_uid_keys (host helper): one uint64 UID code per pair from the two packed read batches. */
+    public void uidKeys(MemorySegment packedR1, MemorySegment packedR2, int extUidLen, int ligUidLen, MemorySegment out) {
+        check(invokeInt(UID_KEYS, packedR1, packedR2, extUidLen, ligUidLen, out));
+    }
+
+    /** hsq_dedup_extend_packed_keys: hsq_dedup_extend_packed with the reduction fed by 20 bytes of keys per pair, the reads following in
+     *  chunks under the kernels (same results). */
+    public void dedupExtendPackedKeys(MemorySegment packedPairs, MemorySegment uidKeys, int extUidLen, int ligUidLen, boolean extendDuplicates,
+                                      boolean sharded, MemorySegment out) {
+        check(invokeInt(DEDUP_EXTEND_PACKED_KEYS, ctx, packedPairs, uidKeys, extUidLen, ligUidLen, extendDuplicates ? 1 : 0, sharded ? 1 : 0, out));
     }
 
     /** hsq_index_bam: record index of a level-0 BGZF BAM (the intermediate files of FastqAndBamFileMerger.java:131-133); `index` is an

@@ -109,6 +109,18 @@ def _worker(rank, world, port, kind, mark, ret):
             res = ctx.dedup_extend_sharded(pairs.subset(mine), U, V, extend_duplicates=mark, cigar_cap=64, md_cap=96)
             b, g, st = ctx.dedup_sharded(pairs.subset(mine), U, V)
             assert np.array_equal(b, res.is_best) and np.array_equal(g, res.group_size)
+            # the keys-first form of the same collective call on packed reads: same flags, same slots, same positions
+            from bioinformatics_b200._lib import pack_reads, quality_sums, uid_keys
+            from bioinformatics_b200.batches import PackedPairsHost
+            sub = pairs.subset(mine)
+            pk = PackedPairsHost(sub.probe_id, pack_reads(sub.r1, 2), pack_reads(sub.r2, 2), None, None, sub.read_index, quality_sums(sub.q1),
+                                 quality_sums(sub.q2))
+            kf = ctx.dedup_extend_packed_keys(pk, uid_keys(pk.r1, pk.r2, U, V), U, V, extend_duplicates=mark, sharded=True)
+            m = res.n_extended
+            assert kf.n_extended == m and np.array_equal(kf.is_best, res.is_best) and np.array_equal(kf.group_size, res.group_size)
+            assert np.array_equal(kf.extended_pair[:m], res.extended_pair[:m]) and np.array_equal(kf.pooled.pos[:2 * m], res.extend.pos[:2 * m])
+            assert np.array_equal(kf.stats.unique_pairs, res.stats.unique_pairs)
+            assert np.array_equal(kf.unique_unable_to_extend, res.unique_unable_to_extend)
         for o in (res, res.extend, res.stats):  # ctypes mirrors do not pickle
             for a in ("_c", "_stats_c", "_ext_c"):
                 if hasattr(o, a):

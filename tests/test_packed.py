@@ -218,3 +218,69 @@ def test_dedup_extend_packed_equals_ascii_call(ctx, mark, sums):
     idx = np.arange(pairs.n) if mark else np.nonzero(eb)[0]
     ext = O.extend_batch(probes, pairs.subset(idx), cigar_cap=64, md_cap=96, nthreads=8)
     assert np.array_equal(got.is_best, eb) and np.array_equal(g.pos[:2 * m], ext.pos) and g.cigars()[:2 * m] == ext.cigars()
+
+
+# ---- keys first: hsq_uid_keys (host) and hsq_dedup_extend_packed_keys ------------------------------------------------------------------
+def test_uid_keys_host_helper():
+    """hsq_uid_keys against the definition: R1[0:u] ++ R2[0:v], 2 bit per base in the order A C G T, first base most significant."""
+    from bioinformatics_b200._lib import uid_keys
+    rng = np.random.default_rng(3)
+    r1 = [H.random_seq(rng, int(rng.integers(12, 40))) for _ in range(500)]
+    r2 = [H.random_seq(rng, int(rng.integers(12, 40))) for _ in range(500)]
+    order = {"A": 0, "C": 1, "G": 2, "T": 3}
+    for bits in (2, 4):
+        p1, p2 = pack_reads(A.SeqBatch.from_strings(r1), bits), pack_reads(A.SeqBatch.from_strings(r2), bits)
+        for u, v in ((10, 0), (7, 5), (0, 12), (0, 0)):
+            want = [int("".join(str(order[c]) for c in (a[:u] + b[:v])) or "0", 4) for a, b in zip(r1, r2)]
+            assert uid_keys(p1, p2, u, v).tolist() == want
+    bad = list(r1)
+    bad[17] = bad[17][:3] + "N" + bad[17][4:]
+    for bits in (2, 4):
+        pb = pack_reads(A.SeqBatch.from_strings(bad), bits)
+        with pytest.raises(HsqError) as e:
+            uid_keys(pb, pack_reads(A.SeqBatch.from_strings(r2), bits), 10, 0)
+        assert e.value.status == A.HSQ_ERR_UNSUPPORTED
+        assert len(uid_keys(pb, pack_reads(A.SeqBatch.from_strings(r2), bits), 3, 0)) == 500  # the N lies behind a 3-base UID
+    with pytest.raises(HsqError) as e:
+        uid_keys(pack_reads(A.SeqBatch.from_strings(r1), 2), pack_reads(A.SeqBatch.from_strings(r2), 2), 41, 0)
+    assert e.value.status in (A.HSQ_ERR_UNSUPPORTED, A.HSQ_ERR_OUT_OF_RANGE)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("chunks,mark", [(0, False), (3, False), (7, False), (3, True)])
+def test_dedup_extend_packed_keys_equals_the_sequential_call(ctx, chunks, mark):
+    """The keys-first probe task (reduction from 20 bytes per pair, reads in chunks under the kernels) against hsq_dedup_extend_packed and the
+    oracle: flags, group sizes, counters, slot numbering, every pooled column and string."""
+    from bioinformatics_b200._lib import uid_keys
+    from bioinformatics_b200.batches import DedupExtendResult
+    from oracle import oracle as O
+    probes = synth.make_probes(120, seed=51)
+    pairs, _ = synth.drop_n_pairs(synth.make_pairs(probes, 9001, read_len=150, ext_uid_len=10, seed=52, sub_rate=0.02, ins_rate=0.004, del_rate=0.004,
+                                                   mean_family=3.0))
+    ctx.configure(extend_chunks=chunks)
+    ctx.set_probes(probes)
+    pk = PackedPairsHost(pairs.probe_id, pack_reads(pairs.r1, 2), pack_reads(pairs.r2, 2), None, None, pairs.read_index, quality_sums(pairs.q1),
+                         quality_sums(pairs.q2))
+    keys = uid_keys(pk.r1, pk.r2, 10, 0)
+    a = ctx.dedup_extend_packed(pk, 10, 0, extend_duplicates=mark)
+    b = ctx.dedup_extend_packed_keys(pk, keys, 10, 0, extend_duplicates=mark)
+    assert a.n_extended == b.n_extended and a.n_extended > 0
+    m = a.n_extended
+    for f in ("is_best", "group_size", "unique_unable_to_extend", "duplicate_unable_to_extend"):
+        assert np.array_equal(getattr(a, f), getattr(b, f)), f
+    assert np.array_equal(a.extended_pair[:m], b.extended_pair[:m])
+    for f in ("unique_pairs", "duplicate_pairs", "max_pairs_per_uid"):
+        assert np.array_equal(getattr(a.stats, f), getattr(b.stats, f)), f
+    for f in ("primer_end", "score", "pos", "read_start", "read_stop", "nm", "tlen", "cigar_len", "md_len", "ok"):
+        assert np.array_equal(getattr(a.pooled, f)[:2 * m], getattr(b.pooled, f)[:2 * m]), f
+    assert np.array_equal(a.pooled.pair_ok[:m], b.pooled.pair_ok[:m])
+    assert a.pooled.cigars()[:2 * m] == b.pooled.cigars()[:2 * m] and a.pooled.mds()[:2 * m] == b.pooled.mds()[:2 * m]
+    assert a.pooled.cells == b.pooled.cells and a.pooled.pool_bytes == b.pooled.pool_bytes
+    # and against the oracle: the reduction, then the extension of the kept pairs
+    best, gs, st = O.dedup_batch(pairs, 10, 0, probes.n)
+    assert np.array_equal(b.is_best, best) and np.array_equal(b.group_size, gs)
+    kept = np.arange(pairs.n) if mark else np.nonzero(best)[0]
+    assert np.array_equal(b.extended_pair[:m], kept)
+    exp = O.extend_batch(probes, pairs.subset(kept), cigar_cap=64, md_cap=96, nthreads=8)
+    assert np.array_equal(b.pooled.pos[:2 * m], exp.pos) and b.pooled.cigars()[:2 * m] == exp.cigars() and b.pooled.mds()[:2 * m] == exp.mds()
+    ctx.configure()
