@@ -29,7 +29,7 @@ READ_LEN = 150
 UID = 10
 CIGAR_CAP, MD_CAP = 24, 40
 OPS_PER_CELL = 12  # algorithmic INT32 ops per DP cell
-TRAFFIC_PER_PAIR_BYTES = (4.673063e9 + 6.289670e9) / 500000  # measured DRAM traffic of capture2_kernel per read pair (ncu --set full, r2_e)
+TRAFFIC_PER_PAIR_BYTES = (4.690506e9 + 6.299373e9) / 500000  # measured DRAM traffic of capture2_kernel per read pair (ncu --set full, r2_h)
 
 
 def parse():
@@ -1022,7 +1022,7 @@ def main():
                                                 "(ncu: profiles/ncu_full_capture2_kernel_r2_*.txt)"},
                              "traffic": TRAFFIC_PER_PAIR_BYTES * n,
                              "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of capture2_kernel from the ncu --set full capture "
-                                             "at 500 k pairs (profiles/ncu_full_capture2_kernel_r2_e.txt: 4.67 + 6.29 GB) scaled to this "
+                                             "at 500 k pairs (profiles/ncu_full_capture2_kernel_r2_h.txt: 4.69 + 6.30 GB) scaled to this "
                                              "batch: scratch (2-bit pointers, boundary rows), not algorithmic bytes; the kernel is ALU bound",
                              "note": "12 algorithmic INT32 ops per DP cell x cells per step / CUDA-event time of hsq_extend_run "
                                      "(capture2_kernel + primer2_kernel are ~93%% of it); nominal 148x128x1.965 GHz = %.1f Tiop/s" % (nominal / 1e12)},
