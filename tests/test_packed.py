@@ -284,3 +284,33 @@ def test_dedup_extend_packed_keys_equals_the_sequential_call(ctx, chunks, mark):
     exp = O.extend_batch(probes, pairs.subset(kept), cigar_cap=64, md_cap=96, nthreads=8)
     assert np.array_equal(b.pooled.pos[:2 * m], exp.pos) and b.pooled.cigars()[:2 * m] == exp.cigars() and b.pooled.mds()[:2 * m] == exp.mds()
     ctx.configure()
+
+
+@pytest.mark.gpu
+def test_dedup_extend_packed_keys_refusals_and_empty_batch(ctx):
+    """Missing key inputs are refused before anything runs; an empty batch is a no-op; pool overflow is reported with the size needed."""
+    from bioinformatics_b200._lib import uid_keys
+    from bioinformatics_b200.batches import DedupExtendResult
+    probes = synth.make_probes(30, seed=61)
+    pairs, _ = synth.drop_n_pairs(synth.make_pairs(probes, 700, read_len=150, ext_uid_len=10, seed=62))
+    ctx.set_probes(probes)
+    pk = PackedPairsHost(pairs.probe_id, pack_reads(pairs.r1, 2), pack_reads(pairs.r2, 2), None, None, pairs.read_index, quality_sums(pairs.q1),
+                         quality_sums(pairs.q2))
+    keys = uid_keys(pk.r1, pk.r2, 10, 0)
+    no_sums = PackedPairsHost(pairs.probe_id, pk.r1, pk.r2, pairs.q1.data, pairs.q2.data, pairs.read_index)
+    with pytest.raises(HsqError) as e:
+        ctx.dedup_extend_packed_keys(no_sums, keys, 10, 0)
+    assert e.value.status == A.HSQ_ERR_INVALID_ARGUMENT
+    with pytest.raises(HsqError) as e:  # more UID bases than fit a key
+        ctx.dedup_extend_packed_keys(pk, keys, 20, 20)
+    assert e.value.status == A.HSQ_ERR_UNSUPPORTED
+    with pytest.raises(HsqError) as e:  # a pool that cannot hold the strings
+        ctx.dedup_extend_packed_keys(pk, keys, 10, 0, pool_cap=64)
+    assert e.value.status == A.HSQ_ERR_OVERFLOW
+    ok = ctx.dedup_extend_packed_keys(pk, keys, 10, 0)  # and the context is usable afterwards
+    ref = ctx.dedup_extend_packed(pk, 10, 0)
+    assert ok.n_extended == ref.n_extended and np.array_equal(ok.pooled.pos[:2 * ok.n_extended], ref.pooled.pos[:2 * ref.n_extended])
+    empty = PackedPairsHost(np.zeros(0, dtype=np.int32), pack_reads([], 2), pack_reads([], 2), None, None, np.zeros(0, dtype=np.int32),
+                            np.zeros(0, dtype=np.int16), np.zeros(0, dtype=np.int16))
+    out = ctx.dedup_extend_packed_keys(empty, np.zeros(0, dtype=np.uint64), 10, 0)
+    assert out.n_extended == 0 and out.pooled.pool_bytes == 0
