@@ -41,36 +41,69 @@ extern "C" int32_t hsq_uid_keys(const hsq_packed_reads* r1, const hsq_packed_rea
     const int64_t n = r1->n;
     const hsq_packed_reads* sides[2] = {r1, r2};
     const int want[2] = {u, v};
-    for (int64_t k = 0; k < n; k++) out[k] = 0;
     for (int s = 0; s < 2; s++) {
         const hsq_packed_reads* r = sides[s];
-        const int L = want[s];
         if (r->bits != 2 && r->bits != 4) return HSQ_ERR_INVALID_ARGUMENT;
-        if (n > 0 && (!r->len || (L > 0 && !r->data))) return HSQ_ERR_INVALID_ARGUMENT;
-        const uint32_t* words = reinterpret_cast<const uint32_t*>(r->data);
-        const int per = 32 / r->bits;
-        int64_t w0 = 0;
-        for (int64_t k = 0; k < n; k++) {
-            const int len = r->len[k];
-            if (len < L) return HSQ_ERR_OUT_OF_RANGE;  // a read shorter than its UID
-            uint64_t code = 0;
-            for (int i = 0; i < L; i++) {
-                const uint32_t x = (words[w0 + i / per] >> (r->bits * (i % per))) & (r->bits == 2 ? 3u : 15u);
-                uint32_t c;
-                if (r->bits == 2) c = x ^ (x >> 1);  // packed A C T G = 0 1 2 3 -> key order A C G T
-                else {
-                    if (x != 1 && x != 2 && x != 4 && x != 8) return HSQ_ERR_UNSUPPORTED;  // an IUPAC code inside a UID
-                    c = x == 1 ? 0u : x == 2 ? 1u : x == 4 ? 2u : 3u;
-                }
-                code = (code << 2) | c;
-            }
-            out[k] = (out[k] << (2 * L)) | code;
-            w0 += hsq::packed_words_of(len, r->bits);
-        }
+        if (n > 0 && (!r->len || (want[s] > 0 && !r->data))) return HSQ_ERR_INVALID_ARGUMENT;
         // 2 bit: a base that is not A/C/G/T was packed as 0 and listed as an exception; one inside a UID is outside the accelerated domain
         for (int64_t e = 0; e < r->n_exceptions; e++)
-            if (r->exc_pos[e] < L) return HSQ_ERR_UNSUPPORTED;
+            if ((int64_t)r->exc_pos[e] < want[s]) return HSQ_ERR_UNSUPPORTED;
     }
+    // pieces of the batch on the host's cores (the reads of a side lie back to back: a piece needs the word offset of its first read)
+    const int n_threads = (int)std::max<int64_t>(1, std::min<int64_t>(std::min<unsigned>(std::max(1u, std::thread::hardware_concurrency()), 32u), n / 65536));
+    std::vector<int64_t> first_word[2];
+    for (int s = 0; s < 2; s++) {
+        first_word[s].assign((size_t)n_threads + 1, 0);
+        int64_t w = 0;
+        int t = 0;
+        for (int64_t k = 0; k < n; k++) {
+            while (t < n_threads && k == n * t / n_threads) first_word[s][(size_t)t++] = w;
+            w += hsq::packed_words_of(sides[s]->len[k] < 0 ? 0 : sides[s]->len[k], sides[s]->bits);
+        }
+        while (t <= n_threads) first_word[s][(size_t)t++] = w;
+    }
+    std::vector<int> status((size_t)n_threads, HSQ_OK);
+    auto piece = [&](int t) {
+        const int64_t k0 = n * t / n_threads, k1 = n * (t + 1) / n_threads;
+        for (int64_t k = k0; k < k1; k++) out[k] = 0;
+        for (int s = 0; s < 2; s++) {
+            const hsq_packed_reads* r = sides[s];
+            const int L = want[s], bits = r->bits, per = 32 / bits;
+            const uint32_t* words = reinterpret_cast<const uint32_t*>(r->data);
+            int64_t w0 = first_word[s][(size_t)t];
+            for (int64_t k = k0; k < k1; k++) {
+                const int len = r->len[k];
+                if (len < L) {  // a read shorter than its UID
+                    status[(size_t)t] = HSQ_ERR_OUT_OF_RANGE;
+                    return;
+                }
+                uint64_t code = 0;
+                for (int i = 0; i < L; i++) {
+                    const uint32_t x = (words[w0 + i / per] >> (bits * (i % per))) & (bits == 2 ? 3u : 15u);
+                    uint32_t c;
+                    if (bits == 2) c = x ^ (x >> 1);  // packed A C T G = 0 1 2 3 -> key order A C G T
+                    else {
+                        if (x != 1 && x != 2 && x != 4 && x != 8) {  // an IUPAC code inside a UID
+                            status[(size_t)t] = HSQ_ERR_UNSUPPORTED;
+                            return;
+                        }
+                        c = x == 1 ? 0u : x == 2 ? 1u : x == 4 ? 2u : 3u;
+                    }
+                    code = (code << 2) | c;
+                }
+                out[k] = (out[k] << (2 * L)) | code;
+                w0 += hsq::packed_words_of(len, bits);
+            }
+        }
+    };
+    if (n_threads == 1) piece(0);
+    else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < n_threads; t++) pool.emplace_back(piece, t);
+        for (auto& th : pool) th.join();
+    }
+    for (int st : status)
+        if (st != HSQ_OK) return st;
     return HSQ_OK;
 }
 
